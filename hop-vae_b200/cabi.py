@@ -1,0 +1,130 @@
+"""ctypes binding of `include/hop_sm100.h` (the C-ABI drop-in boundary).
+
+The library is loaded from the in-tree `libhop_sm100.so`.  There is no CPU
+fallback: if the library is missing `load()` raises, and every wrapper raises
+`RuntimeError` with the library's own message on a non-zero status.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libhop_sm100.so")
+
+ABI_VERSION = 1
+
+# hop_desc.flags
+F_NORM_STATE, F_NORM_STORED, F_NORM_PROJ = 1 << 0, 1 << 1, 1 << 2
+F_PROJ_STATE, F_PROJ_STORED, F_PROJ_PATTERN, F_OUT_PROJ = 1 << 3, 1 << 4, 1 << 5, 1 << 6
+# hop_desc.path
+PATH_AUTO, PATH_FP32_SIMT, PATH_TC_F16, PATH_TC_BF16 = 0, 1, 2, 3
+PATH_NAMES = {"auto": PATH_AUTO, "fp32": PATH_FP32_SIMT, "f16": PATH_TC_F16, "bf16": PATH_TC_BF16}
+
+STATUS_NAMES = {1: "HOP_ERR_BAD_ARG", 2: "HOP_ERR_BAD_SHAPE", 3: "HOP_ERR_BAD_ALIGN", 4: "HOP_ERR_BAD_ARCH",
+                5: "HOP_ERR_CUDA", 6: "HOP_ERR_WORKSPACE", 7: "HOP_ERR_UNSUPPORTED"}
+
+_fp = C.c_void_p  # device pointers travel as integers
+
+
+class HopDesc(C.Structure):
+    _fields_ = [("abi_version", C.c_uint32), ("flags", C.c_uint32), ("path", C.c_int32),
+                ("n_rows", C.c_int32), ("n_patterns", C.c_int32), ("d_in", C.c_int32),
+                ("d_assoc", C.c_int32), ("d_v", C.c_int32), ("d_out", C.c_int32),
+                ("update_steps", C.c_int32), ("pattern_offset", C.c_int32),
+                ("beta", C.c_float), ("ln_eps", C.c_float)]
+
+
+_PARAM_FIELDS = ["lookup", "lookup_targets", "ln_state_w", "ln_state_b", "ln_stored_w", "ln_stored_b",
+                 "ln_proj_w", "ln_proj_b", "wq", "bq", "wk", "bk", "wv", "bv", "wo", "bo"]
+_PATTERN_FIELDS = ["khat", "vhat", "k16", "kt16", "vt16"]
+_GRAD_FIELDS = ["d_x", "d_lookup", "d_lookup_targets", "d_ln_state_w", "d_ln_state_b", "d_ln_stored_w",
+                "d_ln_stored_b", "d_ln_proj_w", "d_ln_proj_b", "d_wq", "d_bq", "d_wk", "d_bk", "d_wv", "d_bv",
+                "d_wo", "d_bo"]
+
+
+class HopParams(C.Structure):
+    _fields_ = [(n, _fp) for n in _PARAM_FIELDS]
+
+
+class HopPatterns(C.Structure):
+    _fields_ = [(n, _fp) for n in _PATTERN_FIELDS]
+
+
+class HopGrads(C.Structure):
+    _fields_ = [(n, _fp) for n in _GRAD_FIELDS]
+
+
+EXPORTS = ["hop_sm100_version", "hop_sm100_last_error", "hop_sm100_select_path", "hop_sm100_pattern_bytes",
+           "hop_sm100_workspace_bytes", "hop_sm100_prepare_patterns", "hop_sm100_forward", "hop_sm100_backward",
+           "hop_sm100_merge_shards", "hop_sm100_out_projection", "hop_sm100_launch_count"]
+
+_lib: Optional[C.CDLL] = None
+
+
+def load() -> C.CDLL:
+    """Load the C-ABI library (once).  Fails loudly when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: the sm_100a Hopfield kernels are not built. Run "
+            f"`python hop-vae_b200/build.py` (or `__graft_entry__.build()`); there is no CPU fallback.")
+    lib = C.CDLL(LIB_PATH)
+    P = C.POINTER
+    lib.hop_sm100_version.restype = C.c_uint32
+    lib.hop_sm100_version.argtypes = []
+    lib.hop_sm100_last_error.restype = C.c_char_p
+    lib.hop_sm100_last_error.argtypes = []
+    lib.hop_sm100_launch_count.restype = C.c_uint64
+    lib.hop_sm100_launch_count.argtypes = []
+    lib.hop_sm100_select_path.restype = C.c_int
+    lib.hop_sm100_select_path.argtypes = [P(HopDesc), P(C.c_int32)]
+    lib.hop_sm100_pattern_bytes.restype = C.c_int
+    lib.hop_sm100_pattern_bytes.argtypes = [P(HopDesc)] + [P(C.c_size_t)] * 5
+    lib.hop_sm100_workspace_bytes.restype = C.c_int
+    lib.hop_sm100_workspace_bytes.argtypes = [P(HopDesc), C.c_int, P(C.c_size_t)]
+    lib.hop_sm100_prepare_patterns.restype = C.c_int
+    lib.hop_sm100_prepare_patterns.argtypes = [P(HopDesc), P(HopParams), P(HopPatterns), _fp]
+    lib.hop_sm100_forward.restype = C.c_int
+    lib.hop_sm100_forward.argtypes = [P(HopDesc), P(HopParams), P(HopPatterns), _fp, _fp, _fp, _fp, _fp, _fp, _fp,
+                                      _fp, C.c_size_t, _fp]
+    lib.hop_sm100_backward.restype = C.c_int
+    lib.hop_sm100_backward.argtypes = [P(HopDesc), P(HopParams), P(HopPatterns), _fp, _fp, _fp, _fp, _fp,
+                                       P(HopGrads), _fp, C.c_size_t, _fp]
+    lib.hop_sm100_merge_shards.restype = C.c_int
+    lib.hop_sm100_merge_shards.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int32, _fp, _fp, _fp, _fp, _fp, _fp,
+                                           _fp]
+    lib.hop_sm100_out_projection.restype = C.c_int
+    lib.hop_sm100_out_projection.argtypes = [C.c_int32, C.c_int32, C.c_int32, _fp, _fp, _fp, _fp, _fp]
+    got = lib.hop_sm100_version()
+    if got != ABI_VERSION:
+        raise RuntimeError(f"libhop_sm100.so ABI version {got} != binding {ABI_VERSION}; rebuild the library")
+    _lib = lib
+    return lib
+
+
+def check(status: int, what: str) -> None:
+    if status != 0:
+        msg = load().hop_sm100_last_error().decode("utf-8", "replace")
+        name = STATUS_NAMES.get(status, str(status))
+        if status == 7:
+            raise NotImplementedError(f"{what}: {name}: {msg}")
+        raise RuntimeError(f"{what}: {name}: {msg}")
+
+
+def launch_count() -> int:
+    return int(load().hop_sm100_launch_count())
+
+
+def make_desc(*, flags: int, path: int, n_rows: int, n_patterns: int, d_in: int, d_assoc: int, d_v: int,
+              d_out: int, update_steps: int, beta: float, ln_eps: float = 1e-5, pattern_offset: int = 0) -> HopDesc:
+    return HopDesc(ABI_VERSION, flags, path, n_rows, n_patterns, d_in, d_assoc, d_v, d_out, update_steps,
+                   pattern_offset, beta, ln_eps)
+
+
+def ptr(t) -> Optional[int]:
+    """Device pointer of a tensor (None -> NULL)."""
+    return None if t is None else t.data_ptr()

@@ -1,0 +1,277 @@
+// C-ABI entry points (include/hop_sm100.h): argument checking, path selection
+// and orchestration of the kernels.  No device allocation, no host sync.
+#include <atomic>
+#include <cstdarg>
+#include <cstring>
+#include <mutex>
+
+#include "hop_common.cuh"
+
+namespace hop {
+
+namespace {
+thread_local char g_err[512] = "";
+std::atomic<uint64_t> g_launches{0};
+std::mutex g_dev_mu;
+int g_dev_checked[64];   // 0 unknown, 1 ok (cc 10.x), 2 wrong arch
+int g_dev_sms[64];
+}  // namespace
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+
+static int device_info(int* sms_out) {
+  int dev = 0;
+  HOP_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) HOP_FAIL(HOP_ERR_BAD_ARG, "device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lk(g_dev_mu);
+  if (g_dev_checked[dev] == 0) {
+    int major = 0, sms = 0;
+    HOP_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+    HOP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    g_dev_sms[dev] = sms;
+    g_dev_checked[dev] = (major == 10) ? 1 : 2;
+  }
+  if (g_dev_checked[dev] != 1)
+    HOP_FAIL(HOP_ERR_BAD_ARCH, "device %d is not compute capability 10.x (this library is sm_100a only)", dev);
+  if (sms_out) *sms_out = g_dev_sms[dev];
+  return HOP_OK;
+}
+
+int num_sms() {
+  int sms = 148;
+  if (device_info(&sms) != HOP_OK) return 148;
+  return sms;
+}
+
+int validate_desc(const hop_desc* d) {
+  if (!d) HOP_FAIL(HOP_ERR_BAD_ARG, "desc is NULL");
+  if (d->abi_version != HOP_SM100_ABI_VERSION)
+    HOP_FAIL(HOP_ERR_BAD_ARG, "desc.abi_version %u != library %u", d->abi_version, HOP_SM100_ABI_VERSION);
+  if (d->n_rows <= 0 || d->n_patterns <= 0 || d->d_in <= 0 || d->d_assoc <= 0 || d->d_v <= 0)
+    HOP_FAIL(HOP_ERR_BAD_SHAPE, "non-positive dimension (N=%d P=%d Din=%d H=%d Dv=%d)", d->n_rows, d->n_patterns,
+             d->d_in, d->d_assoc, d->d_v);
+  if ((d->flags & HOP_F_OUT_PROJ) && d->d_out <= 0) HOP_FAIL(HOP_ERR_BAD_SHAPE, "HOP_F_OUT_PROJ with d_out=%d", d->d_out);
+  if (d->update_steps < 0) HOP_FAIL(HOP_ERR_BAD_ARG, "update_steps must be >= 0 (fixed-count semantics)");
+  if (!(d->flags & HOP_F_PROJ_STATE) && d->d_assoc != d->d_in)
+    HOP_FAIL(HOP_ERR_BAD_SHAPE, "static state pattern needs d_assoc == d_in (%d vs %d)", d->d_assoc, d->d_in);
+  if (!(d->flags & HOP_F_PROJ_STORED) && d->d_assoc != d->d_in)
+    HOP_FAIL(HOP_ERR_BAD_SHAPE, "static stored pattern needs d_assoc == d_in (%d vs %d)", d->d_assoc, d->d_in);
+  if (!(d->flags & HOP_F_PROJ_PATTERN) && d->d_v != d->d_in)
+    HOP_FAIL(HOP_ERR_BAD_SHAPE, "static pattern projection needs d_v == d_in (%d vs %d)", d->d_v, d->d_in);
+  if (d->path < HOP_PATH_AUTO || d->path > HOP_PATH_TC_BF16) HOP_FAIL(HOP_ERR_BAD_ARG, "unknown path %d", d->path);
+  if (!(d->beta > 0.f) || !(d->ln_eps >= 0.f)) HOP_FAIL(HOP_ERR_BAD_ARG, "beta must be > 0 and ln_eps >= 0");
+  return HOP_OK;
+}
+
+int resolve_path(const hop_desc* d) {
+  if (d->path == HOP_PATH_FP32_SIMT) return HOP_PATH_FP32_SIMT;
+  const bool tc_ok = tc_supported(d->d_assoc, d->d_v);
+  if (d->path == HOP_PATH_TC_F16 || d->path == HOP_PATH_TC_BF16) {
+    if (!tc_ok) {
+      set_error("tensor-core path is not built for H=%d Dv=%d (needs H == Dv in {64,128,256})", d->d_assoc, d->d_v);
+      return -HOP_ERR_UNSUPPORTED;
+    }
+    return d->path;
+  }
+  // AUTO: exact fp32 kernels for the reference's own (launch-bound, argmax-tight) sizes and for
+  // widths the MMA cannot take; tcgen05 once the N x P score block is large.
+  const long long np = (long long)d->n_rows * d->n_patterns;
+  if (tc_ok && np >= (1ll << 25)) return HOP_PATH_TC_F16;
+  return HOP_PATH_FP32_SIMT;
+}
+
+}  // namespace hop
+
+using namespace hop;
+
+extern "C" {
+
+uint32_t hop_sm100_version(void) { return HOP_SM100_ABI_VERSION; }
+
+const char* hop_sm100_last_error(void) { return g_err; }
+
+uint64_t hop_sm100_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int hop_sm100_select_path(const hop_desc* desc, int32_t* path_out) {
+  HOP_TRY(validate_desc(desc));
+  if (!path_out) HOP_FAIL(HOP_ERR_BAD_ARG, "path_out is NULL");
+  const int p = resolve_path(desc);
+  if (p < 0) return -p;
+  *path_out = p;
+  return HOP_OK;
+}
+
+int hop_sm100_pattern_bytes(const hop_desc* desc, size_t* khat, size_t* vhat, size_t* k16, size_t* kt16,
+                            size_t* vt16) {
+  HOP_TRY(validate_desc(desc));
+  const int path = resolve_path(desc);
+  if (path < 0) return -path;
+  const bool tc = (path != HOP_PATH_FP32_SIMT);
+  const size_t P = (size_t)desc->n_patterns, Pp = (size_t)padded_patterns(desc->n_patterns);
+  if (khat) *khat = P * desc->d_assoc * sizeof(float);
+  if (vhat) *vhat = P * desc->d_v * sizeof(float);
+  if (k16) *k16 = tc ? Pp * desc->d_assoc * 2 : 0;
+  if (kt16) *kt16 = (tc && desc->update_steps > 0) ? Pp * desc->d_assoc * 2 : 0;
+  if (vt16) *vt16 = tc ? Pp * desc->d_v * 2 : 0;
+  return HOP_OK;
+}
+
+int hop_sm100_workspace_bytes(const hop_desc* desc, int for_backward, size_t* bytes) {
+  HOP_TRY(validate_desc(desc));
+  if (!bytes) HOP_FAIL(HOP_ERR_BAD_ARG, "bytes is NULL");
+  const size_t N = (size_t)desc->n_rows;
+  if (for_backward) {
+    *bytes = simt_backward_workspace(*desc);
+  } else {
+    // two ping-pong query-state buffers (N,H) + one read-out buffer (N,Dv), each 256-byte aligned
+    *bytes = 2 * round_up_sz(N * desc->d_assoc * sizeof(float), 256) + round_up_sz(N * desc->d_v * sizeof(float), 256);
+  }
+  return HOP_OK;
+}
+
+int hop_sm100_prepare_patterns(const hop_desc* desc, const hop_params* params, const hop_patterns* patterns,
+                               void* stream) {
+  HOP_TRY(validate_desc(desc));
+  HOP_TRY(device_info(nullptr));
+  if (!params || !patterns) HOP_FAIL(HOP_ERR_BAD_ARG, "params / patterns is NULL");
+  if (!params->lookup || !patterns->khat || !patterns->vhat) HOP_FAIL(HOP_ERR_BAD_ARG, "lookup / khat / vhat is NULL");
+  const int path = resolve_path(desc);
+  if (path < 0) return -path;
+  if (path != HOP_PATH_FP32_SIMT) {
+    if (!patterns->k16 || !patterns->vt16 || (desc->update_steps > 0 && !patterns->kt16))
+      HOP_FAIL(HOP_ERR_BAD_ARG, "tensor-core path needs the k16 / vt16 (/ kt16 when T > 0) buffers");
+    if (!aligned16(patterns->k16) || !aligned16(patterns->vt16) || !aligned16(patterns->kt16))
+      HOP_FAIL(HOP_ERR_BAD_ALIGN, "16-bit pattern packs must be 16-byte aligned");
+  }
+  if (!aligned16(params->lookup) || !aligned16(patterns->khat) || !aligned16(patterns->vhat))
+    HOP_FAIL(HOP_ERR_BAD_ALIGN, "lookup / khat / vhat must be 16-byte aligned");
+  return launch_prepare_patterns(*desc, *params, *patterns, path, (cudaStream_t)stream);
+}
+
+int hop_sm100_forward(const hop_desc* desc, const hop_params* params, const hop_patterns* patterns, const float* x,
+                      float* out, float* retrieved, float* qhat, float* lse, int32_t* argmax, float* rowmax,
+                      void* workspace, size_t workspace_bytes, void* stream) {
+  HOP_TRY(validate_desc(desc));
+  HOP_TRY(device_info(nullptr));
+  if (!params || !patterns || !x || !out) HOP_FAIL(HOP_ERR_BAD_ARG, "params / patterns / x / out is NULL");
+  if (!aligned16(x) || !aligned16(out) || !aligned16(retrieved) || !aligned16(qhat) || !aligned16(workspace))
+    HOP_FAIL(HOP_ERR_BAD_ALIGN, "x / out / retrieved / qhat / workspace must be 16-byte aligned");
+  const hop_desc& d = *desc;
+  const hop_params& p = *params;
+  const int path = resolve_path(desc);
+  if (path < 0) return -path;
+  size_t need = 0;
+  HOP_TRY(hop_sm100_workspace_bytes(desc, 0, &need));
+  const bool out_proj = (d.flags & HOP_F_OUT_PROJ) != 0;
+  const bool q_proj = (d.flags & HOP_F_PROJ_STATE) != 0;
+  const bool need_ws = q_proj || d.update_steps > 0 || (path != HOP_PATH_FP32_SIMT && out_proj && !retrieved);
+  if (need_ws && (!workspace || workspace_bytes < need))
+    HOP_FAIL(HOP_ERR_WORKSPACE, "workspace of %zu bytes needed, %zu given", need, workspace_bytes);
+  if (out_proj && (!p.wo)) HOP_FAIL(HOP_ERR_BAD_ARG, "HOP_F_OUT_PROJ set but params.wo is NULL");
+  cudaStream_t st = (cudaStream_t)stream;
+
+  const size_t qbytes = round_up_sz((size_t)d.n_rows * d.d_assoc * sizeof(float), 256);
+  float* qbuf[2] = {reinterpret_cast<float*>(workspace),
+                    workspace ? reinterpret_cast<float*>(static_cast<char*>(workspace) + qbytes) : nullptr};
+  float* rbuf = workspace ? reinterpret_cast<float*>(static_cast<char*>(workspace) + 2 * qbytes) : nullptr;
+
+  const float* qs = nullptr;  // prepared beta*Q^ when not fused
+  if (q_proj) {
+    HOP_TRY(launch_prepare_queries(d, p, x, qbuf[0], st));
+    qs = qbuf[0];
+  }
+
+  if (path == HOP_PATH_FP32_SIMT) {
+    int cur = 0;  // index of the buffer holding the current state when qs != nullptr
+    for (int t = 0; t < d.update_steps; ++t) {
+      SimtPassArgs a{};
+      a.x_raw = qs ? nullptr : x; a.lnq_w = p.ln_state_w; a.lnq_b = p.ln_state_b; a.ln_eps = d.ln_eps;
+      a.has_ln = (d.flags & HOP_F_NORM_STATE) ? 1 : 0; a.beta = d.beta; a.qs = qs;
+      a.khat = patterns->khat; a.bmat = patterns->khat;
+      a.n = d.n_rows; a.p = d.n_patterns; a.h = d.d_assoc; a.dr = d.d_assoc; a.out_scale = d.beta;
+      const int nxt = qs ? (cur ^ 1) : 0;
+      a.res = qbuf[nxt];
+      HOP_TRY(launch_simt_pass(a, st));
+      qs = qbuf[nxt];
+      cur = nxt;
+    }
+    SimtPassArgs a{};
+    a.x_raw = qs ? nullptr : x; a.lnq_w = p.ln_state_w; a.lnq_b = p.ln_state_b; a.ln_eps = d.ln_eps;
+    a.has_ln = (d.flags & HOP_F_NORM_STATE) ? 1 : 0; a.beta = d.beta; a.qs = qs;
+    a.khat = patterns->khat; a.bmat = patterns->vhat;
+    a.n = d.n_rows; a.p = d.n_patterns; a.h = d.d_assoc; a.dr = d.d_v; a.out_scale = 1.f;
+    a.qsave = qhat; a.lse = lse; a.argmax = argmax; a.rowmax = rowmax; a.pattern_offset = d.pattern_offset;
+    if (out_proj) {
+      a.res = retrieved; a.wo = p.wo; a.bo = p.bo; a.dout = d.d_out; a.out = out;
+    } else {
+      a.res = out;
+    }
+    HOP_TRY(launch_simt_pass(a, st));
+    if (!out_proj && retrieved && retrieved != out)
+      HOP_CUDA(cudaMemcpyAsync(retrieved, out, (size_t)d.n_rows * d.d_v * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    return HOP_OK;
+  }
+
+  // tensor-core path: one persistent kernel runs all T+1 passes; out_proj is a second (HBM-bound) launch
+  TcPassArgs a{};
+  a.x_raw = qs ? nullptr : x; a.lnq_w = p.ln_state_w; a.lnq_b = p.ln_state_b; a.ln_eps = d.ln_eps;
+  a.has_ln = (d.flags & HOP_F_NORM_STATE) ? 1 : 0; a.beta = d.beta; a.qs = qs;
+  a.k16 = patterns->k16; a.kt16 = patterns->kt16; a.vt16 = patterns->vt16;
+  a.n = d.n_rows; a.p = d.n_patterns; a.h = d.d_assoc; a.dv = d.d_v; a.update_steps = d.update_steps;
+  a.bf16 = (path == HOP_PATH_TC_BF16);
+  a.retrieved = out_proj ? (retrieved ? retrieved : rbuf) : out;
+  a.qsave = qhat; a.lse = lse; a.argmax = argmax; a.rowmax = rowmax; a.pattern_offset = d.pattern_offset;
+  HOP_TRY(launch_tc_forward(a, st));
+  if (out_proj) HOP_TRY(launch_linear(d.n_rows, d.d_v, d.d_out, a.retrieved, p.wo, p.bo, out, st));
+  else if (retrieved && retrieved != out)
+    HOP_CUDA(cudaMemcpyAsync(retrieved, out, (size_t)d.n_rows * d.d_v * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  return HOP_OK;
+}
+
+int hop_sm100_backward(const hop_desc* desc, const hop_params* params, const hop_patterns* patterns, const float* x,
+                       const float* qhat, const float* retrieved, const float* lse, const float* grad_out,
+                       const hop_grads* grads, void* workspace, size_t workspace_bytes, void* stream) {
+  HOP_TRY(validate_desc(desc));
+  HOP_TRY(device_info(nullptr));
+  if (!params || !patterns || !x || !qhat || !retrieved || !lse || !grad_out || !grads)
+    HOP_FAIL(HOP_ERR_BAD_ARG, "a required backward argument is NULL");
+  if (desc->update_steps != 0)
+    HOP_FAIL(HOP_ERR_UNSUPPORTED, "backward is implemented for update_steps == 0 (what the reference trains with)");
+  size_t need = 0;
+  HOP_TRY(hop_sm100_workspace_bytes(desc, 1, &need));
+  if (!workspace || workspace_bytes < need)
+    HOP_FAIL(HOP_ERR_WORKSPACE, "backward workspace of %zu bytes needed, %zu given", need, workspace_bytes);
+  if (!aligned16(workspace) || !aligned16(grad_out) || !aligned16(qhat) || !aligned16(retrieved))
+    HOP_FAIL(HOP_ERR_BAD_ALIGN, "backward buffers must be 16-byte aligned");
+  return launch_simt_backward(*desc, *params, *patterns, x, qhat, retrieved, lse, grad_out, *grads, workspace,
+                              workspace_bytes, (cudaStream_t)stream);
+}
+
+int hop_sm100_merge_shards(int32_t n_rows, int32_t d_v, int32_t n_shards, int32_t shard, const float* lse_all,
+                           const float* rowmax_all, const int32_t* argmax_all, float* retrieved, float* lse_out,
+                           int32_t* argmax_out, void* stream) {
+  HOP_TRY(device_info(nullptr));
+  if (n_rows <= 0 || d_v <= 0 || n_shards <= 0 || shard < 0 || shard >= n_shards)
+    HOP_FAIL(HOP_ERR_BAD_SHAPE, "merge: bad sizes (N=%d Dv=%d G=%d g=%d)", n_rows, d_v, n_shards, shard);
+  if (!lse_all || !retrieved) HOP_FAIL(HOP_ERR_BAD_ARG, "merge: lse_all / retrieved is NULL");
+  if (!aligned16(retrieved)) HOP_FAIL(HOP_ERR_BAD_ALIGN, "merge: retrieved must be 16-byte aligned");
+  return launch_merge(n_rows, d_v, n_shards, shard, lse_all, rowmax_all, argmax_all, retrieved, lse_out, argmax_out,
+                      (cudaStream_t)stream);
+}
+
+int hop_sm100_out_projection(int32_t n_rows, int32_t d_v, int32_t d_out, const float* retrieved, const float* wo,
+                             const float* bo, float* out, void* stream) {
+  HOP_TRY(device_info(nullptr));
+  if (n_rows <= 0 || d_v <= 0 || d_out <= 0) HOP_FAIL(HOP_ERR_BAD_SHAPE, "out_projection: bad sizes");
+  if (!retrieved || !wo || !out) HOP_FAIL(HOP_ERR_BAD_ARG, "out_projection: NULL argument");
+  return launch_linear(n_rows, d_v, d_out, retrieved, wo, bo, out, (cudaStream_t)stream);
+}
+
+}  // extern "C"

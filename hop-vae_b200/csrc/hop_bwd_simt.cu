@@ -1,0 +1,691 @@
+// Backward of the association for update_steps == 0 (SURVEY.md section 8a row
+// a11: the autograd mirrors of LayerNorm x3, V-projection, score bmm, softmax,
+// read-out bmm and out_proj that `loss.backward()` at main.py:35 runs).
+//
+// Flash-style: A = exp(S - lse) is recomputed tile by tile from the saved
+// beta*Q^ and lse; no N x P tensor is ever stored.
+//
+//   dR   = G Wo                      (N,Dv)      [linear, transposed weight]
+//   dWo  = G^T R, dbo = sum G                     [wgrad]
+//   delta= rowsum(dR * R)
+//   dS   = A * (dR V^T - delta)      (tile)
+//   dqs  = dS K^            (N,H)                 [core_q]
+//   dK^  = dS^T qs          (P,H),  dV^ = A^T dR  (P,Dv)   [core_kv, split over N, fp32 RED]
+//   then LayerNorm / projection backward on the query side and (twice) on the
+//   pattern side, both paths summing into d_lookup.
+#include "hop_common.cuh"
+
+namespace hop {
+
+namespace {
+
+constexpr int NT = 256;
+constexpr int BP = 64;
+constexpr int PS = BP + 4;
+
+__device__ __forceinline__ void load_tile_pad(float* __restrict__ dst, const float* __restrict__ src, int r0,
+                                              int rows, int nrows_total, int w, int wpad, int stride) {
+  if ((w & 3) == 0) {
+    const int w4 = wpad >> 2;
+    for (int idx = threadIdx.x; idx < rows * w4; idx += NT) {
+      const int r = idx / w4, c = (idx - r * w4) << 2;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (r0 + r < nrows_total && c < w) v = __ldg(reinterpret_cast<const float4*>(src + (size_t)(r0 + r) * w + c));
+      *reinterpret_cast<float4*>(dst + r * stride + c) = v;
+    }
+  } else {
+    for (int idx = threadIdx.x; idx < rows * wpad; idx += NT) {
+      const int r = idx / wpad, c = idx - r * wpad;
+      float v = 0.f;
+      if (r0 + r < nrows_total && c < w) v = __ldg(src + (size_t)(r0 + r) * w + c);
+      dst[r * stride + c] = v;
+    }
+  }
+}
+
+// acc[i][b] += sum_k A[(ty*RM+i)][k] * B[(tx+16b)][k]   (both k-contiguous, stride given)
+template <int RM>
+__device__ __forceinline__ void mma_nt(float (&acc)[RM][4], const float* __restrict__ A, int as,
+                                       const float* __restrict__ B, int bs, int k4, int ty, int tx) {
+  for (int k = 0; k < k4; k += 4) {
+    float4 a[RM];
+#pragma unroll
+    for (int i = 0; i < RM; ++i) a[i] = *reinterpret_cast<const float4*>(A + (ty * RM + i) * as + k);
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      const float4 bb = *reinterpret_cast<const float4*>(B + (tx + 16 * b) * bs + k);
+#pragma unroll
+      for (int i = 0; i < RM; ++i) {
+        acc[i][b] = fmaf(a[i].x, bb.x, acc[i][b]);
+        acc[i][b] = fmaf(a[i].y, bb.y, acc[i][b]);
+        acc[i][b] = fmaf(a[i].z, bb.z, acc[i][b]);
+        acc[i][b] = fmaf(a[i].w, bb.w, acc[i][b]);
+      }
+    }
+  }
+}
+
+struct CoreArgs {
+  const float* qs; const float* khat; const float* vhat; const float* lse;
+  const float* dr; const float* r;   // dR (N,Dv), R (N,Dv)
+  float* delta;                      // (N)  written by core_q, read by core_kv
+  float* dqs;                        // (N,H)
+  float* dkhat; float* dvhat;        // (P,H), (P,Dv) accumulated with RED (pre-zeroed)
+  int n, p, h, dv;
+  int rows_per_split;                // core_kv: query rows handled by one blockIdx.y
+};
+
+// ------------------------------------------------------------------ core_q
+template <int RM, int HC, int DVC>
+__global__ void __launch_bounds__(NT) bwd_core_q_kernel(CoreArgs a) {
+  extern __shared__ __align__(16) float smem[];
+  constexpr int BM = 16 * RM;
+  constexpr int HS = 64 * HC + 4, VS = 64 * DVC + 4;
+  float* Qs = smem;
+  float* Gs = Qs + BM * HS;
+  float* Ks = Gs + BM * VS;
+  float* Vs = Ks + BP * HS;
+  float* Ps = Vs + BP * VS;
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int row0 = blockIdx.x * BM;
+  const int h4 = (a.h + 3) & ~3, dv4 = (a.dv + 3) & ~3;
+
+  load_tile_pad(Qs, a.qs, row0, BM, a.n, a.h, 64 * HC, HS);
+  load_tile_pad(Gs, a.dr, row0, BM, a.n, a.dv, 64 * DVC, VS);
+
+  float lse_r[RM], delta_r[RM];
+#pragma unroll
+  for (int i = 0; i < RM; ++i) {
+    const int gr = row0 + ty * RM + i;
+    float part = 0.f;
+    if (gr < a.n)
+      for (int c = tx; c < a.dv; c += 16) part = fmaf(__ldg(a.dr + (size_t)gr * a.dv + c), __ldg(a.r + (size_t)gr * a.dv + c), part);
+#pragma unroll
+    for (int off = 8; off > 0; off >>= 1) part += __shfl_xor_sync(0xffffffffu, part, off);
+    delta_r[i] = part;
+    lse_r[i] = gr < a.n ? __ldg(a.lse + gr) : 0.f;
+    if (tx == 0 && gr < a.n) a.delta[gr] = part;
+  }
+
+  float dq[RM][HC][4];
+#pragma unroll
+  for (int i = 0; i < RM; ++i)
+#pragma unroll
+    for (int c = 0; c < HC; ++c)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) dq[i][c][e] = 0.f;
+
+  const int n_tiles = (a.p + BP - 1) / BP;
+  for (int t = 0; t < n_tiles; ++t) {
+    const int p0 = t * BP;
+    __syncthreads();
+    load_tile_pad(Ks, a.khat, p0, BP, a.p, a.h, 64 * HC, HS);
+    load_tile_pad(Vs, a.vhat, p0, BP, a.p, a.dv, 64 * DVC, VS);
+    __syncthreads();
+    float s[RM][4], da[RM][4];
+#pragma unroll
+    for (int i = 0; i < RM; ++i)
+#pragma unroll
+      for (int b = 0; b < 4; ++b) s[i][b] = da[i][b] = 0.f;
+    mma_nt<RM>(s, Qs, HS, Ks, HS, h4, ty, tx);
+    mma_nt<RM>(da, Gs, VS, Vs, VS, dv4, ty, tx);
+#pragma unroll
+    for (int i = 0; i < RM; ++i)
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        const int col = p0 + tx + 16 * b;
+        const float prob = (col < a.p) ? __expf(s[i][b] - lse_r[i]) : 0.f;
+        Ps[(ty * RM + i) * PS + tx + 16 * b] = prob * (da[i][b] - delta_r[i]);
+      }
+    __syncthreads();
+    for (int j = 0; j < BP; j += 4) {
+      float4 pv[RM];
+#pragma unroll
+      for (int i = 0; i < RM; ++i) pv[i] = *reinterpret_cast<const float4*>(Ps + (ty * RM + i) * PS + j);
+#pragma unroll
+      for (int jj = 0; jj < 4; ++jj)
+#pragma unroll
+        for (int c = 0; c < HC; ++c) {
+          const float4 kk = *reinterpret_cast<const float4*>(Ks + (j + jj) * HS + 4 * tx + 64 * c);
+#pragma unroll
+          for (int i = 0; i < RM; ++i) {
+            const float w = jj == 0 ? pv[i].x : jj == 1 ? pv[i].y : jj == 2 ? pv[i].z : pv[i].w;
+            dq[i][c][0] = fmaf(w, kk.x, dq[i][c][0]);
+            dq[i][c][1] = fmaf(w, kk.y, dq[i][c][1]);
+            dq[i][c][2] = fmaf(w, kk.z, dq[i][c][2]);
+            dq[i][c][3] = fmaf(w, kk.w, dq[i][c][3]);
+          }
+        }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < RM; ++i) {
+    const int gr = row0 + ty * RM + i;
+    if (gr >= a.n) continue;
+#pragma unroll
+    for (int c = 0; c < HC; ++c)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int col = 4 * tx + 64 * c + e;
+        if (col < a.h) a.dqs[(size_t)gr * a.h + col] = dq[i][c][e];
+      }
+  }
+}
+
+// ----------------------------------------------------------------- core_kv
+template <int HC, int DVC>
+__global__ void __launch_bounds__(NT) bwd_core_kv_kernel(CoreArgs a) {
+  extern __shared__ __align__(16) float smem[];
+  constexpr int RQ = 2, BQ = 16 * RQ;
+  constexpr int HS = 64 * HC + 4, VS = 64 * DVC + 4;
+  float* Ks = smem;
+  float* Vs = Ks + BP * HS;
+  float* Qs = Vs + BP * VS;
+  float* Gs = Qs + BQ * HS;
+  float* As = Gs + BQ * VS;
+  float* Ds = As + BQ * PS;
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int p0 = blockIdx.x * BP;
+  const int h4 = (a.h + 3) & ~3, dv4 = (a.dv + 3) & ~3;
+  const int q_begin = blockIdx.y * a.rows_per_split;
+  const int q_end = min(a.n, q_begin + a.rows_per_split);
+
+  load_tile_pad(Ks, a.khat, p0, BP, a.p, a.h, 64 * HC, HS);
+  load_tile_pad(Vs, a.vhat, p0, BP, a.p, a.dv, 64 * DVC, VS);
+
+  float dk[4][HC][4], dvv[4][DVC][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+#pragma unroll
+    for (int c = 0; c < HC; ++c)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) dk[i][c][e] = 0.f;
+#pragma unroll
+    for (int c = 0; c < DVC; ++c)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) dvv[i][c][e] = 0.f;
+  }
+
+  for (int q0 = q_begin; q0 < q_end; q0 += BQ) {
+    __syncthreads();
+    load_tile_pad(Qs, a.qs, q0, BQ, q_end, a.h, 64 * HC, HS);
+    load_tile_pad(Gs, a.dr, q0, BQ, q_end, a.dv, 64 * DVC, VS);
+    __syncthreads();
+    float s[RQ][4], da[RQ][4];
+#pragma unroll
+    for (int i = 0; i < RQ; ++i)
+#pragma unroll
+      for (int b = 0; b < 4; ++b) s[i][b] = da[i][b] = 0.f;
+    mma_nt<RQ>(s, Qs, HS, Ks, HS, h4, ty, tx);
+    mma_nt<RQ>(da, Gs, VS, Vs, VS, dv4, ty, tx);
+#pragma unroll
+    for (int i = 0; i < RQ; ++i) {
+      const int gr = q0 + ty * RQ + i;
+      const bool rv = gr < q_end;
+      const float lse_r = rv ? __ldg(a.lse + gr) : 0.f;
+      const float delta_r = rv ? __ldg(a.delta + gr) : 0.f;
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        const int col = p0 + tx + 16 * b;
+        const float prob = (rv && col < a.p) ? __expf(s[i][b] - lse_r) : 0.f;
+        As[(ty * RQ + i) * PS + tx + 16 * b] = prob;
+        Ds[(ty * RQ + i) * PS + tx + 16 * b] = prob * (da[i][b] - delta_r);
+      }
+    }
+    __syncthreads();
+    for (int r = 0; r < BQ; ++r) {
+      const float4 a4 = *reinterpret_cast<const float4*>(As + r * PS + ty * 4);
+      const float4 d4 = *reinterpret_cast<const float4*>(Ds + r * PS + ty * 4);
+      const float av[4] = {a4.x, a4.y, a4.z, a4.w};
+      const float dvl[4] = {d4.x, d4.y, d4.z, d4.w};
+#pragma unroll
+      for (int c = 0; c < DVC; ++c) {
+        const float4 g = *reinterpret_cast<const float4*>(Gs + r * VS + 4 * tx + 64 * c);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          dvv[i][c][0] = fmaf(av[i], g.x, dvv[i][c][0]);
+          dvv[i][c][1] = fmaf(av[i], g.y, dvv[i][c][1]);
+          dvv[i][c][2] = fmaf(av[i], g.z, dvv[i][c][2]);
+          dvv[i][c][3] = fmaf(av[i], g.w, dvv[i][c][3]);
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < HC; ++c) {
+        const float4 q = *reinterpret_cast<const float4*>(Qs + r * HS + 4 * tx + 64 * c);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          dk[i][c][0] = fmaf(dvl[i], q.x, dk[i][c][0]);
+          dk[i][c][1] = fmaf(dvl[i], q.y, dk[i][c][1]);
+          dk[i][c][2] = fmaf(dvl[i], q.z, dk[i][c][2]);
+          dk[i][c][3] = fmaf(dvl[i], q.w, dk[i][c][3]);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int gp = p0 + ty * 4 + i;
+    if (gp >= a.p) continue;
+#pragma unroll
+    for (int c = 0; c < HC; ++c)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int col = 4 * tx + 64 * c + e;
+        if (col < a.h) atomicAdd(a.dkhat + (size_t)gp * a.h + col, dk[i][c][e]);
+      }
+#pragma unroll
+    for (int c = 0; c < DVC; ++c)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int col = 4 * tx + 64 * c + e;
+        if (col < a.dv) atomicAdd(a.dvhat + (size_t)gp * a.dv + col, dvv[i][c][e]);
+      }
+  }
+}
+
+// ------------------------------------------------------- LayerNorm backward
+// For rows of y = LN(x) (or y = x when !has_ln):  dx (+)= d/dx <scale*g, y>, and the
+// affine grads dgamma += sum_rows scale*g*xhat, dbeta += sum_rows scale*g (fp32 RED).
+struct LnBwdArgs {
+  const float* x; const float* g; int rows; int d;
+  int has_ln; const float* gamma; float eps; float scale;
+  float* dx; int accumulate;
+  float* dgamma; float* dbeta;   // pre-zeroed; nullptr when no affine / not wanted
+};
+
+__global__ void __launch_bounds__(NT) ln_bwd_kernel(LnBwdArgs a) {
+  extern __shared__ float sh[];  // [2*d] column partials
+  float* sg = sh;
+  float* sb = sh + a.d;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool want_affine = a.has_ln && (a.dgamma || a.dbeta);
+  if (want_affine) {
+    for (int i = threadIdx.x; i < 2 * a.d; i += NT) sh[i] = 0.f;
+    __syncthreads();
+  }
+  for (int r = blockIdx.x * (NT / 32) + warp; r < a.rows; r += gridDim.x * (NT / 32)) {
+    const float* xr = a.x + (size_t)r * a.d;
+    const float* gr = a.g + (size_t)r * a.d;
+    float* dxr = a.dx + (size_t)r * a.d;
+    if (!a.has_ln) {
+      for (int i = lane; i < a.d; i += 32) {
+        const float v = a.scale * gr[i];
+        dxr[i] = a.accumulate ? dxr[i] + v : v;
+      }
+      continue;
+    }
+    float mean, rstd;
+    warp_row_stats(xr, a.d, a.eps, mean, rstd);
+    float c1 = 0.f, c2 = 0.f;
+    for (int i = lane; i < a.d; i += 32) {
+      const float xh = (xr[i] - mean) * rstd;
+      const float gy = a.scale * gr[i] * (a.gamma ? __ldg(a.gamma + i) : 1.f);
+      c1 += gy;
+      c2 += gy * xh;
+    }
+    c1 = warp_sum(c1) / (float)a.d;
+    c2 = warp_sum(c2) / (float)a.d;
+    for (int i = lane; i < a.d; i += 32) {
+      const float xh = (xr[i] - mean) * rstd;
+      const float gs = a.scale * gr[i];
+      const float gy = gs * (a.gamma ? __ldg(a.gamma + i) : 1.f);
+      const float v = rstd * (gy - c1 - xh * c2);
+      dxr[i] = a.accumulate ? dxr[i] + v : v;
+      if (want_affine) {
+        atomicAdd(sg + i, gs * xh);
+        atomicAdd(sb + i, gs);
+      }
+    }
+  }
+  if (want_affine) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < a.d; i += NT) {
+      if (a.dgamma) atomicAdd(a.dgamma + i, sg[i]);
+      if (a.dbeta) atomicAdd(a.dbeta + i, sb[i]);
+    }
+  }
+}
+
+int launch_ln_bwd(const LnBwdArgs& a, cudaStream_t st) {
+  const int sms = num_sms();
+  int grid = (a.rows + 7) / 8;
+  if (grid > 2 * sms) grid = 2 * sms;
+  if (grid < 1) grid = 1;
+  ln_bwd_kernel<<<grid, NT, 2 * a.d * sizeof(float), st>>>(a);
+  HOP_LAUNCH_CHECK("ln_bwd_kernel");
+  return HOP_OK;
+}
+
+// ------------------------------------------------------------ weight grads
+// dW[o][i] += sum_n dY[n][o] * Xn[n][i],  db[o] += sum_n dY[n][o]   (fp32 RED; pre-zeroed)
+// Xn = LN(x) with affine when has_ln (recomputed), else x.
+struct WgradArgs {
+  const float* dy; const float* x; int rows; int dout; int din;
+  int has_ln; const float* gamma; const float* beta_ln; float eps;
+  float* dw; float* db; int rows_per_cta; float scale;
+};
+
+__global__ void __launch_bounds__(NT) wgrad_kernel(WgradArgs a) {
+  constexpr int BR = 32, ST = 68;
+  __shared__ __align__(16) float Ys[BR * ST];
+  __shared__ __align__(16) float Xs[BR * ST];
+  __shared__ float s_mean[BR], s_rstd[BR];
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4, warp = tid >> 5, lane = tid & 31;
+  const int o0 = blockIdx.x * 64, i0 = blockIdx.y * 64;
+  const int r_begin = blockIdx.z * a.rows_per_cta, r_end = min(a.rows, r_begin + a.rows_per_cta);
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+  float bsum[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int r0 = r_begin; r0 < r_end; r0 += BR) {
+    __syncthreads();
+    if (a.has_ln) {
+      for (int r = warp; r < BR; r += NT / 32) {
+        float mean = 0.f, rstd = 1.f;
+        if (r0 + r < r_end) warp_row_stats(a.x + (size_t)(r0 + r) * a.din, a.din, a.eps, mean, rstd);
+        if (lane == 0) {
+          s_mean[r] = mean;
+          s_rstd[r] = rstd;
+        }
+      }
+      __syncthreads();
+    }
+    for (int idx = tid; idx < BR * 64; idx += NT) {
+      const int r = idx >> 6, c = idx & 63;
+      float yv = 0.f, xv = 0.f;
+      if (r0 + r < r_end) {
+        if (o0 + c < a.dout) yv = __ldg(a.dy + (size_t)(r0 + r) * a.dout + o0 + c);
+        if (i0 + c < a.din) {
+          xv = __ldg(a.x + (size_t)(r0 + r) * a.din + i0 + c);
+          if (a.has_ln) {
+            xv = (xv - s_mean[r]) * s_rstd[r];
+            if (a.gamma) xv *= __ldg(a.gamma + i0 + c);
+            if (a.beta_ln) xv += __ldg(a.beta_ln + i0 + c);
+          }
+        }
+      }
+      Ys[r * ST + c] = yv;
+      Xs[r * ST + c] = xv;
+    }
+    __syncthreads();
+#pragma unroll 4
+    for (int r = 0; r < BR; ++r) {
+      const float4 y4 = *reinterpret_cast<const float4*>(Ys + r * ST + ty * 4);
+      const float4 x4 = *reinterpret_cast<const float4*>(Xs + r * ST + tx * 4);
+      const float yv[4] = {y4.x, y4.y, y4.z, y4.w};
+      const float xv[4] = {x4.x, x4.y, x4.z, x4.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        bsum[i] += yv[i];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(yv[i], xv[j], acc[i][j]);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int o = o0 + ty * 4 + i;
+    if (o >= a.dout) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int c = i0 + tx * 4 + j;
+      if (c < a.din) atomicAdd(a.dw + (size_t)o * a.din + c, acc[i][j] * a.scale);
+    }
+    if (a.db && blockIdx.y == 0 && tx == 0) atomicAdd(a.db + o, bsum[i] * a.scale);
+  }
+}
+
+int launch_wgrad(WgradArgs a, cudaStream_t st) {
+  const int sms = num_sms();
+  const int tiles = ((a.dout + 63) / 64) * ((a.din + 63) / 64);
+  int splits = (2 * sms + tiles - 1) / tiles;
+  const int max_splits = (a.rows + 31) / 32;
+  if (splits > max_splits) splits = max_splits;
+  if (splits < 1) splits = 1;
+  a.rows_per_cta = round_up((a.rows + splits - 1) / splits, 32);
+  splits = (a.rows + a.rows_per_cta - 1) / a.rows_per_cta;
+  dim3 grid((a.dout + 63) / 64, (a.din + 63) / 64, splits);
+  wgrad_kernel<<<grid, NT, 0, st>>>(a);
+  HOP_LAUNCH_CHECK("wgrad_kernel");
+  return HOP_OK;
+}
+
+// y[n][j] = sum_o g[n][o] * w[o][j]   (w row-major (dout_w, din_w); i.e. g . W, no transpose)
+__global__ void __launch_bounds__(NT) linear_nn_kernel(const float* __restrict__ g, const float* __restrict__ w,
+                                                       float* __restrict__ y, int n, int k, int m) {
+  // CTA: 32 rows x 64 output columns; contraction streamed in chunks of 32
+  constexpr int BR = 32, KC = 32;
+  __shared__ __align__(16) float Gs[BR * (KC + 4)];
+  __shared__ __align__(16) float Ws[KC * 68];
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int row0 = blockIdx.x * BR, c0 = blockIdx.y * 64;
+  float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+  for (int k0 = 0; k0 < k; k0 += KC) {
+    __syncthreads();
+    for (int idx = tid; idx < BR * KC; idx += NT) {
+      const int r = idx / KC, kk = idx - r * KC;
+      Gs[r * (KC + 4) + kk] = (row0 + r < n && k0 + kk < k) ? __ldg(g + (size_t)(row0 + r) * k + k0 + kk) : 0.f;
+    }
+    for (int idx = tid; idx < KC * 64; idx += NT) {
+      const int kk = idx >> 6, c = idx & 63;
+      Ws[kk * 68 + c] = (k0 + kk < k && c0 + c < m) ? __ldg(w + (size_t)(k0 + kk) * m + c0 + c) : 0.f;
+    }
+    __syncthreads();
+#pragma unroll 8
+    for (int kk = 0; kk < KC; ++kk) {
+      const float4 wv = *reinterpret_cast<const float4*>(Ws + kk * 68 + 4 * tx);
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const float gv = Gs[(ty * 2 + i) * (KC + 4) + kk];
+        acc[i][0] = fmaf(gv, wv.x, acc[i][0]);
+        acc[i][1] = fmaf(gv, wv.y, acc[i][1]);
+        acc[i][2] = fmaf(gv, wv.z, acc[i][2]);
+        acc[i][3] = fmaf(gv, wv.w, acc[i][3]);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const int gr = row0 + ty * 2 + i;
+    if (gr >= n) continue;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int c = c0 + 4 * tx + e;
+      if (c < m) y[(size_t)gr * m + c] = acc[i][e];
+    }
+  }
+}
+
+int launch_linear_nn(const float* g, const float* w, float* y, int n, int k, int m, cudaStream_t st) {
+  dim3 grid((n + 31) / 32, (m + 63) / 64);
+  linear_nn_kernel<<<grid, NT, 0, st>>>(g, w, y, n, k, m);
+  HOP_LAUNCH_CHECK("linear_nn_kernel");
+  return HOP_OK;
+}
+
+template <int RM, int HC, int DVC>
+int launch_core_q(const CoreArgs& a, cudaStream_t st) {
+  constexpr int BM = 16 * RM, HS = 64 * HC + 4, VS = 64 * DVC + 4;
+  const size_t smem = sizeof(float) * (size_t)(BM * HS + BM * VS + BP * HS + BP * VS + BM * PS);
+  auto kern = bwd_core_q_kernel<RM, HC, DVC>;
+  if (smem > 48 * 1024) HOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<(a.n + BM - 1) / BM, NT, smem, st>>>(a);
+  HOP_LAUNCH_CHECK("bwd_core_q_kernel");
+  return HOP_OK;
+}
+
+template <int HC, int DVC>
+int launch_core_kv(CoreArgs a, cudaStream_t st) {
+  constexpr int BQ = 32, HS = 64 * HC + 4, VS = 64 * DVC + 4;
+  const size_t smem = sizeof(float) * (size_t)(BP * HS + BP * VS + BQ * HS + BQ * VS + 2 * BQ * PS);
+  auto kern = bwd_core_kv_kernel<HC, DVC>;
+  if (smem > 48 * 1024) HOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int sms = num_sms();
+  const int ptiles = (a.p + BP - 1) / BP;
+  int splits = (3 * sms + ptiles - 1) / ptiles;
+  const int max_splits = (a.n + BQ - 1) / BQ;
+  if (splits > max_splits) splits = max_splits;
+  if (splits < 1) splits = 1;
+  a.rows_per_split = round_up((a.n + splits - 1) / splits, BQ);
+  splits = (a.n + a.rows_per_split - 1) / a.rows_per_split;
+  kern<<<dim3(ptiles, splits), NT, smem, st>>>(a);
+  HOP_LAUNCH_CHECK("bwd_core_kv_kernel");
+  return HOP_OK;
+}
+
+template <int HC, int DVC>
+int launch_core(const CoreArgs& a, cudaStream_t st) {
+  const int sms = num_sms();
+  if (a.n >= 32 * 2 * sms) HOP_TRY((launch_core_q<2, HC, DVC>(a, st)));
+  else HOP_TRY((launch_core_q<1, HC, DVC>(a, st)));
+  return launch_core_kv<HC, DVC>(a, st);
+}
+
+struct BwdWs {
+  float *dr, *dqs, *delta, *dkhat, *dvhat, *dvn, *dkn, *dqn;
+  size_t total;
+};
+
+BwdWs carve(const hop_desc& d, void* ws) {
+  BwdWs w{};
+  size_t off = 0;
+  auto take = [&](size_t elems) {
+    float* p = ws ? reinterpret_cast<float*>(static_cast<char*>(ws) + off) : nullptr;
+    off += round_up_sz(elems * sizeof(float), 256);
+    return p;
+  };
+  const size_t N = d.n_rows, P = d.n_patterns;
+  w.dr = take(N * d.d_v);
+  w.dqs = take(N * d.d_assoc);
+  w.delta = take(N);
+  w.dkhat = take(P * d.d_assoc);
+  w.dvhat = take(P * d.d_v);
+  w.dvn = take(P * d.d_in);
+  w.dkn = take(P * d.d_in);
+  w.dqn = take(N * d.d_in);
+  w.total = off;
+  return w;
+}
+
+}  // namespace
+
+size_t simt_backward_workspace(const hop_desc& d) { return carve(d, nullptr).total; }
+
+int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patterns& pt, const float* x,
+                         const float* qhat, const float* retrieved, const float* lse, const float* grad_out,
+                         const hop_grads& g, void* ws, size_t ws_bytes, cudaStream_t st) {
+  (void)ws_bytes;
+  if (d.d_assoc > 128 || d.d_v > 128)
+    HOP_FAIL(HOP_ERR_UNSUPPORTED, "backward is built for H, Dv <= 128 (got %d, %d)", d.d_assoc, d.d_v);
+  const BwdWs w = carve(d, ws);
+  const int N = d.n_rows, P = d.n_patterns, H = d.d_assoc, Dv = d.d_v, Din = d.d_in;
+  const bool out_proj = d.flags & HOP_F_OUT_PROJ, q_proj = d.flags & HOP_F_PROJ_STATE;
+  const bool k_proj = d.flags & HOP_F_PROJ_STORED, v_proj = d.flags & HOP_F_PROJ_PATTERN;
+  const bool sep_targets = p.lookup_targets != nullptr;
+
+  auto zero = [&](float* ptr, size_t elems) -> int {
+    if (ptr) HOP_CUDA(cudaMemsetAsync(ptr, 0, elems * sizeof(float), st));
+    return HOP_OK;
+  };
+
+  // 1. out-projection backward
+  const float* dR = grad_out;
+  if (out_proj) {
+    HOP_TRY(launch_linear_nn(grad_out, p.wo, w.dr, N, d.d_out, Dv, st));
+    dR = w.dr;
+    if (g.d_wo) {
+      HOP_TRY(zero(g.d_wo, (size_t)d.d_out * Dv));
+      HOP_TRY(zero(g.d_bo, d.d_out));
+      WgradArgs wa{grad_out, retrieved, N, d.d_out, Dv, 0, nullptr, nullptr, 0.f, g.d_wo, g.d_bo, 0, 1.f};
+      HOP_TRY(launch_wgrad(wa, st));
+    }
+  }
+
+  // 2. association core
+  HOP_TRY(zero(w.dkhat, (size_t)P * H));
+  HOP_TRY(zero(w.dvhat, (size_t)P * Dv));
+  CoreArgs ca{qhat, pt.khat, pt.vhat, lse, dR, retrieved, w.delta, w.dqs, w.dkhat, w.dvhat, N, P, H, Dv, 0};
+  const int hc = (H + 63) / 64, dvc = (Dv + 63) / 64;
+  if (hc == 1 && dvc == 1) HOP_TRY((launch_core<1, 1>(ca, st)));
+  else if (hc == 1 && dvc == 2) HOP_TRY((launch_core<1, 2>(ca, st)));
+  else if (hc == 2 && dvc == 1) HOP_TRY((launch_core<2, 1>(ca, st)));
+  else HOP_TRY((launch_core<2, 2>(ca, st)));
+
+  // 3. query side: dqs -> [Wq] -> LN_q -> dx
+  {
+    const float* gq = w.dqs;     // gradient w.r.t. beta*Qproj
+    float scale = d.beta;
+    if (q_proj) {
+      // dWq = (beta dqs)^T LN(x), dbq = sum beta dqs ; dqn = beta dqs . Wq
+      if (g.d_wq) {
+        HOP_TRY(zero(g.d_wq, (size_t)H * Din));
+        HOP_TRY(zero(g.d_bq, H));
+        WgradArgs wa{w.dqs, x, N, H, Din, (d.flags & HOP_F_NORM_STATE) ? 1 : 0, p.ln_state_w, p.ln_state_b, d.ln_eps,
+                     g.d_wq, g.d_bq, 0, d.beta};
+        HOP_TRY(launch_wgrad(wa, st));
+      }
+      HOP_TRY(launch_linear_nn(w.dqs, p.wq, w.dqn, N, H, Din, st));
+      gq = w.dqn;
+    }
+    if (g.d_x) {
+      HOP_TRY(zero(g.d_ln_state_w, Din));
+      HOP_TRY(zero(g.d_ln_state_b, Din));
+      LnBwdArgs la{x, gq, N, Din, (d.flags & HOP_F_NORM_STATE) ? 1 : 0, p.ln_state_w, d.ln_eps, scale,
+                   g.d_x, 0, g.d_ln_state_w, g.d_ln_state_b};
+      HOP_TRY(launch_ln_bwd(la, st));
+    }
+  }
+
+  // 4. pattern side, V^ path: dV^ -> [Wv] -> LN_v -> d_lookup(_targets)
+  const float* Wt = sep_targets ? p.lookup_targets : p.lookup;
+  float* d_wt = sep_targets ? g.d_lookup_targets : g.d_lookup;
+  {
+    const float* gv = w.dvhat;
+    if (v_proj) {
+      if (g.d_wv) {
+        HOP_TRY(zero(g.d_wv, (size_t)Dv * Din));
+        HOP_TRY(zero(g.d_bv, Dv));
+        WgradArgs wa{w.dvhat, Wt, P, Dv, Din, (d.flags & HOP_F_NORM_PROJ) ? 1 : 0, p.ln_proj_w, p.ln_proj_b, d.ln_eps,
+                     g.d_wv, g.d_bv, 0, 1.f};
+        HOP_TRY(launch_wgrad(wa, st));
+      }
+      HOP_TRY(launch_linear_nn(w.dvhat, p.wv, w.dvn, P, Dv, Din, st));
+      gv = w.dvn;
+    }
+    if (d_wt) {
+      HOP_TRY(zero(g.d_ln_proj_w, Din));
+      HOP_TRY(zero(g.d_ln_proj_b, Din));
+      LnBwdArgs la{Wt, gv, P, Din, (d.flags & HOP_F_NORM_PROJ) ? 1 : 0, p.ln_proj_w, d.ln_eps, 1.f,
+                   d_wt, 0, g.d_ln_proj_w, g.d_ln_proj_b};
+      HOP_TRY(launch_ln_bwd(la, st));
+    }
+  }
+  // 5. pattern side, K^ path (accumulates into d_lookup when it shares the V^ path's buffer)
+  {
+    const float* gk = w.dkhat;
+    if (k_proj) {
+      if (g.d_wk) {
+        HOP_TRY(zero(g.d_wk, (size_t)H * Din));
+        HOP_TRY(zero(g.d_bk, H));
+        WgradArgs wa{w.dkhat, p.lookup, P, H, Din, (d.flags & HOP_F_NORM_STORED) ? 1 : 0, p.ln_stored_w, p.ln_stored_b,
+                     d.ln_eps, g.d_wk, g.d_bk, 0, 1.f};
+        HOP_TRY(launch_wgrad(wa, st));
+      }
+      HOP_TRY(launch_linear_nn(w.dkhat, p.wk, w.dkn, P, H, Din, st));
+      gk = w.dkn;
+    }
+    if (g.d_lookup) {
+      HOP_TRY(zero(g.d_ln_stored_w, Din));
+      HOP_TRY(zero(g.d_ln_stored_b, Din));
+      const int accumulate = (!sep_targets && d_wt != nullptr) ? 1 : 0;
+      LnBwdArgs la{p.lookup, gk, P, Din, (d.flags & HOP_F_NORM_STORED) ? 1 : 0, p.ln_stored_w, d.ln_eps, 1.f,
+                   g.d_lookup, accumulate, g.d_ln_stored_w, g.d_ln_stored_b};
+      HOP_TRY(launch_ln_bwd(la, st));
+    }
+  }
+  return HOP_OK;
+}
+
+}  // namespace hop

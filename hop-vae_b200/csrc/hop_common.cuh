@@ -1,0 +1,140 @@
+// Shared host/device helpers of the sm_100a Hopfield retrieval library.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/hop_sm100.h"
+
+namespace hop {
+
+// ---------------------------------------------------------------- host side
+void set_error(const char* fmt, ...);
+void count_launch(int n = 1);
+
+#define HOP_FAIL(code, ...)            \
+  do {                                 \
+    ::hop::set_error(__VA_ARGS__);     \
+    return (code);                     \
+  } while (0)
+
+#define HOP_CUDA(expr)                                                              \
+  do {                                                                              \
+    cudaError_t e__ = (expr);                                                       \
+    if (e__ != cudaSuccess)                                                         \
+      HOP_FAIL(HOP_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), \
+               __FILE__, __LINE__);                                                 \
+  } while (0)
+
+#define HOP_LAUNCH_CHECK(name)                                                     \
+  do {                                                                             \
+    cudaError_t e__ = cudaGetLastError();                                          \
+    if (e__ != cudaSuccess)                                                        \
+      HOP_FAIL(HOP_ERR_CUDA, "launch of %s failed: %s", name, cudaGetErrorString(e__)); \
+    ::hop::count_launch();                                                         \
+  } while (0)
+
+#define HOP_TRY(expr)          \
+  do {                         \
+    int s__ = (expr);          \
+    if (s__ != HOP_OK) return s__; \
+  } while (0)
+
+static inline int round_up(int x, int m) { return (x + m - 1) / m * m; }
+static inline size_t round_up_sz(size_t x, size_t m) { return (x + m - 1) / m * m; }
+static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// Pattern count padded for the 16-bit transposed packs (TMA row pitch must be a
+// multiple of 16 bytes; we pad to a full 128-pattern tile so tiles never straddle).
+static inline int padded_patterns(int p) { return round_up(p, 128); }
+
+int validate_desc(const hop_desc* d);   // common checks, sets error
+int resolve_path(const hop_desc* d);    // HOP_PATH_* actually run (never AUTO), <0 on error
+int num_sms();
+
+// Entry points implemented per translation unit ------------------------------
+// hop_prep.cu
+int launch_prepare_patterns(const hop_desc& d, const hop_params& p, const hop_patterns& pt, int path,
+                            cudaStream_t st);
+int launch_prepare_queries(const hop_desc& d, const hop_params& p, const float* x, float* qhat,
+                           cudaStream_t st);  // qhat = beta * ([LN](x)[Wq^T+bq])  (N,H)
+int launch_linear(int n, int din, int dout, const float* x, const float* w, const float* b, float* y,
+                  cudaStream_t st);           // y = x w^T + b
+// hop_fwd_simt.cu
+// One association pass on prepared operands.  If `x_raw` != nullptr the kernel
+// fuses LN_q (+beta) itself, else it reads prepared `qs` (N,H).
+// `bmat` is the read-out matrix (P,Dr) (V^ for the last pass, K^ for an update
+// pass).  Writes res (N,Dr) scaled by out_scale, optional lse/argmax/rowmax/qsave,
+// and the fused out-projection when wo != nullptr.
+struct SimtPassArgs {
+  const float* x_raw; const float* lnq_w; const float* lnq_b; float ln_eps; int has_ln; float beta;
+  const float* qs;
+  const float* khat; const float* bmat;
+  int n, p, h, dr;
+  float out_scale;
+  float* res;       // (N, Dr) or nullptr
+  float* qsave;     // (N, H)  or nullptr
+  float* lse; int32_t* argmax; float* rowmax; int pattern_offset;
+  const float* wo; const float* bo; int dout; float* out;   // fused out-proj (optional)
+};
+int launch_simt_pass(const SimtPassArgs& a, cudaStream_t st);
+// hop_bwd_simt.cu
+int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patterns& pt, const float* x,
+                         const float* qhat, const float* retrieved, const float* lse,
+                         const float* grad_out, const hop_grads& g, void* ws, size_t ws_bytes,
+                         cudaStream_t st);
+size_t simt_backward_workspace(const hop_desc& d);
+// hop_fwd_tc.cu
+struct TcPassArgs {
+  const float* x_raw; const float* lnq_w; const float* lnq_b; float ln_eps; int has_ln; float beta;
+  const float* qs;          // prepared beta*Q^ (N,H) fp32 if x_raw == nullptr
+  const void* k16; const void* kt16; const void* vt16;
+  int n, p, h, dv, update_steps; int bf16;
+  float* retrieved;         // (N,Dv)
+  float* qsave;             // (N,H) or nullptr
+  float* lse; int32_t* argmax; float* rowmax; int pattern_offset;
+};
+int launch_tc_forward(const TcPassArgs& a, cudaStream_t st);
+bool tc_supported(int h, int dv);
+// hop_merge.cu
+int launch_merge(int n, int dv, int g, int shard, const float* lse_all, const float* rowmax_all,
+                 const int32_t* argmax_all, float* retrieved, float* lse_out, int32_t* argmax_out,
+                 cudaStream_t st);
+
+// -------------------------------------------------------------- device side
+#ifdef __CUDACC__
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// LayerNorm of one row held by one warp: lane owns elements lane, lane+32, ...
+// Two-pass (mean, then centred variance) in registers -- matches nn.LayerNorm's
+// biased variance.  Returns (mean, rstd).
+__device__ __forceinline__ void warp_row_stats(const float* __restrict__ row, int d, float eps,
+                                               float& mean, float& rstd) {
+  const int lane = threadIdx.x & 31;
+  float s = 0.f;
+  for (int i = lane; i < d; i += 32) s += row[i];
+  mean = warp_sum(s) / (float)d;
+  float v = 0.f;
+  for (int i = lane; i < d; i += 32) {
+    const float c = row[i] - mean;
+    v += c * c;
+  }
+  rstd = rsqrtf(warp_sum(v) / (float)d + eps);
+}
+
+#endif  // __CUDACC__
+
+}  // namespace hop

@@ -1,0 +1,313 @@
+// Exact fp32 (CUDA-core) association pass: flash-style, the N x P score matrix
+// lives only in registers / shared memory.
+//
+// Replaces, for small or argmax-tight problems (the reference's own sizes:
+// P=512, D in {64, 3}):
+//   q*scaling, torch.bmm(q,k^T), softmax(dim=-1), torch.bmm(A,v), out_proj
+// of upstream hopfield_core_forward, reached from HopVAE.py:193,215,216,234,
+// 255,257,271.  LN_q (row a3) is fused into the prologue, out_proj (a10) into
+// the epilogue.
+//
+// Tiling: a CTA of 256 threads owns BM = 16*RM query rows and sweeps the
+// patterns in tiles of 64.  Threads form a 16 x 16 grid: ty owns RM rows, tx
+// owns 4 score columns (tx + 16 b) and 4*DVC read-out columns (4 tx + 64 c).
+// The 16 threads of a row group keep the running (max, sum, argmax) replicated
+// via half-warp butterfly shuffles.
+#include "hop_common.cuh"
+
+namespace hop {
+
+namespace {
+
+constexpr int NT = 256;
+constexpr int BP = 64;
+constexpr int PS = BP + 4;  // stride of the probability tile
+
+struct SimtSmemLayout {
+  int hs;      // stride of Q / K tiles (floats)
+  int ds;      // stride of read-out tile (floats) = 64*DVC
+  int q_off, k_off, b_off, p_off, total;  // float offsets
+};
+
+__host__ __device__ inline SimtSmemLayout simt_layout(int bm, int h, int dvc) {
+  SimtSmemLayout L;
+  const int h4 = (h + 3) / 4 * 4;
+  L.hs = h4 + 4;
+  L.ds = 64 * dvc;
+  L.q_off = 0;
+  L.k_off = L.q_off + bm * L.hs;
+  L.b_off = L.k_off + BP * L.hs;
+  const int b_elems = (BP > bm ? BP : bm) * L.ds;  // reused as the O tile in the epilogue
+  L.p_off = L.b_off + b_elems;
+  L.total = L.p_off + bm * PS;
+  return L;
+}
+
+// Load rows [r0, r0+rows) x [0, w) of a (nrows_total, w) fp32 matrix into smem
+// with stride `stride`, zero-filling rows >= nrows_total and columns in [w, wpad).
+__device__ __forceinline__ void load_tile(float* __restrict__ dst, const float* __restrict__ src, int r0,
+                                          int rows, int nrows_total, int w, int wpad, int stride) {
+  if ((w & 3) == 0) {
+    const int w4 = wpad >> 2;
+    for (int idx = threadIdx.x; idx < rows * w4; idx += NT) {
+      const int r = idx / w4, c = (idx - r * w4) << 2;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (r0 + r < nrows_total && c < w) v = __ldg(reinterpret_cast<const float4*>(src + (size_t)(r0 + r) * w + c));
+      *reinterpret_cast<float4*>(dst + r * stride + c) = v;
+    }
+  } else {
+    for (int idx = threadIdx.x; idx < rows * wpad; idx += NT) {
+      const int r = idx / wpad, c = idx - r * wpad;
+      float v = 0.f;
+      if (r0 + r < nrows_total && c < w) v = __ldg(src + (size_t)(r0 + r) * w + c);
+      dst[r * stride + c] = v;
+    }
+  }
+}
+
+template <int RM, int DVC>
+__global__ void __launch_bounds__(NT) hop_fwd_simt_kernel(SimtPassArgs a) {
+  extern __shared__ __align__(16) float smem[];
+  constexpr int BM = 16 * RM;
+  const SimtSmemLayout L = simt_layout(BM, a.h, DVC);
+  float* Qs = smem + L.q_off;
+  float* Ks = smem + L.k_off;
+  float* Bs = smem + L.b_off;
+  float* Ps = smem + L.p_off;
+
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;
+  const int warp = tid >> 5, lane = tid & 31;
+  const int row0 = blockIdx.x * BM;
+  const int h4 = (a.h + 3) / 4 * 4;
+
+  // ---- prologue: queries -> smem (fused LayerNorm + beta when x_raw given) ----
+  if (a.x_raw != nullptr) {
+    for (int r = warp; r < BM; r += NT / 32) {
+      const int gr = row0 + r;
+      if (gr < a.n) {
+        const float* xr = a.x_raw + (size_t)gr * a.h;
+        float mean = 0.f, rstd = 1.f;
+        if (a.has_ln) warp_row_stats(xr, a.h, a.ln_eps, mean, rstd);
+        for (int i = lane; i < L.hs; i += 32) {
+          float v = 0.f;
+          if (i < a.h) {
+            v = xr[i];
+            if (a.has_ln) {
+              v = (v - mean) * rstd;
+              if (a.lnq_w) v *= __ldg(a.lnq_w + i);
+              if (a.lnq_b) v += __ldg(a.lnq_b + i);
+            }
+            v *= a.beta;
+            if (a.qsave) a.qsave[(size_t)gr * a.h + i] = v;
+          }
+          Qs[r * L.hs + i] = v;
+        }
+      } else {
+        for (int i = lane; i < L.hs; i += 32) Qs[r * L.hs + i] = 0.f;
+      }
+    }
+  } else {
+    load_tile(Qs, a.qs, row0, BM, a.n, a.h, h4, L.hs);
+    if (a.qsave) {
+      for (int idx = tid; idx < BM * a.h; idx += NT) {
+        const int r = idx / a.h, c = idx - r * a.h;
+        if (row0 + r < a.n) a.qsave[(size_t)(row0 + r) * a.h + c] = a.qs[(size_t)(row0 + r) * a.h + c];
+      }
+    }
+  }
+
+  float m_run[RM], l_run[RM];
+  int arg_run[RM];
+  float o[RM][DVC][4];
+#pragma unroll
+  for (int i = 0; i < RM; ++i) {
+    m_run[i] = -INFINITY;
+    l_run[i] = 0.f;
+    arg_run[i] = 0;
+#pragma unroll
+    for (int c = 0; c < DVC; ++c)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) o[i][c][e] = 0.f;
+  }
+
+  const int n_tiles = (a.p + BP - 1) / BP;
+  for (int t = 0; t < n_tiles; ++t) {
+    const int p0 = t * BP;
+    __syncthreads();  // previous tile's consumers are done with Ks / Bs / Ps (and Qs is written)
+    load_tile(Ks, a.khat, p0, BP, a.p, a.h, h4, L.hs);
+    load_tile(Bs, a.bmat, p0, BP, a.p, a.dr, L.ds, L.ds);
+    __syncthreads();
+
+    // ---- phase 1: scores  s[i][b] = <q_row, k_col> ----
+    float s[RM][4];
+#pragma unroll
+    for (int i = 0; i < RM; ++i)
+#pragma unroll
+      for (int b = 0; b < 4; ++b) s[i][b] = 0.f;
+    for (int k = 0; k < h4; k += 4) {
+      float4 q[RM];
+#pragma unroll
+      for (int i = 0; i < RM; ++i) q[i] = *reinterpret_cast<const float4*>(Qs + (ty * RM + i) * L.hs + k);
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        const float4 kk = *reinterpret_cast<const float4*>(Ks + (tx + 16 * b) * L.hs + k);
+#pragma unroll
+        for (int i = 0; i < RM; ++i) {
+          s[i][b] = fmaf(q[i].x, kk.x, s[i][b]);
+          s[i][b] = fmaf(q[i].y, kk.y, s[i][b]);
+          s[i][b] = fmaf(q[i].z, kk.z, s[i][b]);
+          s[i][b] = fmaf(q[i].w, kk.w, s[i][b]);
+        }
+      }
+    }
+
+    // ---- phase 2: online softmax over this tile ----
+#pragma unroll
+    for (int i = 0; i < RM; ++i) {
+      float tmax = -INFINITY;
+      int targ = 0x7fffffff;
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        const int col = p0 + tx + 16 * b;
+        if (col >= a.p) s[i][b] = -INFINITY;
+        if (s[i][b] > tmax) {  // strict: lowest column wins ties inside the thread
+          tmax = s[i][b];
+          targ = col;
+        }
+      }
+#pragma unroll
+      for (int off = 8; off > 0; off >>= 1) {
+        const float om = __shfl_xor_sync(0xffffffffu, tmax, off);
+        const int oa = __shfl_xor_sync(0xffffffffu, targ, off);
+        if (om > tmax || (om == tmax && oa < targ)) {
+          tmax = om;
+          targ = oa;
+        }
+      }
+      if (tmax > m_run[i]) arg_run[i] = targ;  // strict: earlier tile keeps ties
+      const float m_new = fmaxf(m_run[i], tmax);
+      const float corr = __expf(m_run[i] - m_new);  // exp(-inf) = 0 on the first tile
+      float psum = 0.f;
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        const float p = __expf(s[i][b] - m_new);
+        psum += p;
+        Ps[(ty * RM + i) * PS + tx + 16 * b] = p;
+      }
+#pragma unroll
+      for (int off = 8; off > 0; off >>= 1) psum += __shfl_xor_sync(0xffffffffu, psum, off);
+      l_run[i] = l_run[i] * corr + psum;
+      m_run[i] = m_new;
+#pragma unroll
+      for (int c = 0; c < DVC; ++c)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) o[i][c][e] *= corr;
+    }
+    __syncthreads();
+
+    // ---- phase 3: read-out  o += P . B ----
+    for (int j = 0; j < BP; j += 4) {
+      float4 pv[RM];
+#pragma unroll
+      for (int i = 0; i < RM; ++i) pv[i] = *reinterpret_cast<const float4*>(Ps + (ty * RM + i) * PS + j);
+#pragma unroll
+      for (int jj = 0; jj < 4; ++jj) {
+#pragma unroll
+        for (int c = 0; c < DVC; ++c) {
+          const float4 v = *reinterpret_cast<const float4*>(Bs + (j + jj) * L.ds + 4 * tx + 64 * c);
+#pragma unroll
+          for (int i = 0; i < RM; ++i) {
+            const float p = jj == 0 ? pv[i].x : jj == 1 ? pv[i].y : jj == 2 ? pv[i].z : pv[i].w;
+            o[i][c][0] = fmaf(p, v.x, o[i][c][0]);
+            o[i][c][1] = fmaf(p, v.y, o[i][c][1]);
+            o[i][c][2] = fmaf(p, v.z, o[i][c][2]);
+            o[i][c][3] = fmaf(p, v.w, o[i][c][3]);
+          }
+        }
+      }
+    }
+  }
+
+  // ---- epilogue ----
+  __syncthreads();
+  float* Os = Bs;  // [BM][ds], normalised read-out rows for the fused out-projection
+#pragma unroll
+  for (int i = 0; i < RM; ++i) {
+    const int r = ty * RM + i, gr = row0 + r;
+    const float inv = 1.f / l_run[i];
+#pragma unroll
+    for (int c = 0; c < DVC; ++c) {
+      float4 v = make_float4(o[i][c][0] * inv, o[i][c][1] * inv, o[i][c][2] * inv, o[i][c][3] * inv);
+      *reinterpret_cast<float4*>(Os + r * L.ds + 4 * tx + 64 * c) = v;
+      if (a.res != nullptr && gr < a.n) {
+        const int col = 4 * tx + 64 * c;
+        const float vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+          if (col + e < a.dr) a.res[(size_t)gr * a.dr + col + e] = vv[e] * a.out_scale;
+      }
+    }
+    if (tx == 0 && gr < a.n) {
+      if (a.lse) a.lse[gr] = m_run[i] + __logf(l_run[i]);
+      if (a.argmax) a.argmax[gr] = arg_run[i] + a.pattern_offset;
+      if (a.rowmax) a.rowmax[gr] = m_run[i];
+    }
+  }
+  if (a.wo != nullptr) {
+    __syncthreads();
+    for (int idx = tid; idx < BM * a.dout; idx += NT) {
+      const int r = idx / a.dout, oc = idx - r * a.dout;
+      if (row0 + r >= a.n) continue;
+      const float* w = a.wo + (size_t)oc * a.dr;
+      float acc = a.bo ? __ldg(a.bo + oc) : 0.f;
+      for (int j = 0; j < a.dr; ++j) acc = fmaf(Os[r * L.ds + j], __ldg(w + j), acc);
+      a.out[(size_t)(row0 + r) * a.dout + oc] = acc;
+    }
+  }
+}
+
+template <int RM, int DVC>
+int launch_inst(const SimtPassArgs& a, cudaStream_t st) {
+  constexpr int BM = 16 * RM;
+  const SimtSmemLayout L = simt_layout(BM, a.h, DVC);
+  const size_t smem = (size_t)L.total * sizeof(float);
+  if (smem > 227 * 1024) HOP_FAIL(HOP_ERR_BAD_SHAPE, "fp32 path: tile for H=%d Dr=%d needs %zu B of shared memory", a.h, a.dr, smem);
+  auto kern = hop_fwd_simt_kernel<RM, DVC>;
+  if (smem > 48 * 1024) HOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int grid = (a.n + BM - 1) / BM;
+  kern<<<grid, NT, smem, st>>>(a);
+  HOP_LAUNCH_CHECK("hop_fwd_simt_kernel");
+  return HOP_OK;
+}
+
+template <int RM>
+int launch_rm(const SimtPassArgs& a, cudaStream_t st) {
+  const int dvc = (a.dr + 63) / 64;
+  switch (dvc) {
+    case 1: return launch_inst<RM, 1>(a, st);
+    case 2: return launch_inst<RM, 2>(a, st);
+    case 3:
+    case 4: return launch_inst<RM, 4>(a, st);
+    default: HOP_FAIL(HOP_ERR_UNSUPPORTED, "fp32 path supports read-out width <= 256 (got %d)", a.dr);
+  }
+}
+
+}  // namespace
+
+int launch_simt_pass(const SimtPassArgs& a, cudaStream_t st) {
+  if (a.h > 256) HOP_FAIL(HOP_ERR_UNSUPPORTED, "fp32 path supports association width <= 256 (got %d)", a.h);
+  // Rows per CTA: large tiles once there are enough rows to give every SM >= 2 CTAs.
+  const int sms = num_sms();
+  int rm = 1;
+  if (a.n >= 64 * 2 * sms) rm = 4;
+  else if (a.n >= 32 * 2 * sms) rm = 2;
+  if (rm == 4 && (a.h > 128 || a.dr > 128)) rm = 2;  // keep the tile under the shared-memory limit
+  switch (rm) {
+    case 4: return launch_rm<4>(a, st);
+    case 2: return launch_rm<2>(a, st);
+    default: return launch_rm<1>(a, st);
+  }
+}
+
+}  // namespace hop

@@ -1,0 +1,218 @@
+// Row-wise [LayerNorm] -> [Linear] -> scale, with optional 16-bit row-major and
+// transposed packs for the tensor-core path.
+//
+// One kernel serves:
+//   K^ = [LN_k](W)[Wk^T + bk]       -> fp32 (P,H), 16-bit (Ppad,H), 16-bit^T (H,Ppad)
+//   V^ = [LN_v](Wt)[Wv^T + bv]      -> fp32 (P,Dv), 16-bit^T (Dv,Ppad)
+//   Q^ = beta * [LN_q](x)[Wq^T+bq]  -> fp32 (N,H)         (only when Q is projected)
+//   out = retrieved . Wo^T + bo     -> fp32 (N,Dout)      (after a shard merge / TC path)
+// Upstream does the K^/V^ work on the batch-expanded lookup matrix, i.e. B
+// times per forward; here it runs once per parameter update.
+#include "hop_common.cuh"
+
+namespace hop {
+
+namespace {
+
+constexpr int NT = 256;
+constexpr int TN = 64;        // output-column tile
+constexpr int KC = 64;        // contraction chunk
+constexpr int XS = KC + 4;    // smem stride of X / W chunks
+constexpr int YS = TN + 1;    // smem stride of the staged output tile
+
+struct LnLinearArgs {
+  const float* x; int rows; int rows_pad; int din;
+  int has_ln; const float* ln_w; const float* ln_b; float ln_eps;
+  const float* w; const float* b; int dout;   // w == nullptr -> identity (dout == din)
+  float scale;
+  float* y;            // (rows, dout) fp32 or nullptr
+  void* y16;           // (rows_pad, dout) 16-bit or nullptr
+  void* yt16;          // (dout, rows_pad) 16-bit or nullptr
+  int bf16;            // 16-bit encoding: 0 = fp16 (saturating), 1 = bf16
+};
+
+__device__ __forceinline__ uint16_t to16(float v, int bf16) {
+  if (bf16) return __bfloat16_as_ushort(__float2bfloat16_rn(v));
+  // fp16: clamp to the finite range so an outlier cannot turn into inf inside the MMA
+  v = fminf(fmaxf(v, -65504.f), 65504.f);
+  return __half_as_ushort(__float2half_rn(v));
+}
+
+template <int RM>
+__global__ void __launch_bounds__(NT) ln_linear_kernel(LnLinearArgs a) {
+  constexpr int BR = 16 * RM;
+  __shared__ __align__(16) float Xs[BR * XS];
+  __shared__ __align__(16) float Ws[TN * XS];
+  __shared__ float s_mean[BR], s_rstd[BR];
+  float* Ys = Xs;  // the staged output tile aliases the input chunk (BR*YS <= BR*XS), see the barriers below
+  static_assert(YS <= XS, "output staging tile must fit in the input chunk");
+
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int warp = tid >> 5, lane = tid & 31;
+  const int row0 = blockIdx.x * BR;
+
+  // per-row LayerNorm statistics
+  for (int r = warp; r < BR; r += NT / 32) {
+    float mean = 0.f, rstd = 1.f;
+    if (a.has_ln && row0 + r < a.rows) warp_row_stats(a.x + (size_t)(row0 + r) * a.din, a.din, a.ln_eps, mean, rstd);
+    if (lane == 0) {
+      s_mean[r] = mean;
+      s_rstd[r] = rstd;
+    }
+  }
+  __syncthreads();
+
+  for (int c0 = 0; c0 < a.dout; c0 += TN) {
+    float acc[RM][4];
+#pragma unroll
+    for (int i = 0; i < RM; ++i)
+#pragma unroll
+      for (int bb = 0; bb < 4; ++bb) acc[i][bb] = 0.f;
+
+    const int k_begin = a.w ? 0 : c0;
+    const int k_end = a.w ? a.din : min(c0 + KC, a.din);
+    for (int k0 = k_begin; k0 < k_end; k0 += KC) {
+      __syncthreads();
+      // normalised input chunk
+      for (int idx = tid; idx < BR * KC; idx += NT) {
+        const int r = idx / KC, k = idx - r * KC;
+        float v = 0.f;
+        if (row0 + r < a.rows && k0 + k < a.din) {
+          v = __ldg(a.x + (size_t)(row0 + r) * a.din + k0 + k);
+          if (a.has_ln) {
+            v = (v - s_mean[r]) * s_rstd[r];
+            if (a.ln_w) v *= __ldg(a.ln_w + k0 + k);
+            if (a.ln_b) v += __ldg(a.ln_b + k0 + k);
+          }
+        }
+        Xs[r * XS + k] = v;
+      }
+      if (a.w) {
+        for (int idx = tid; idx < TN * KC; idx += NT) {
+          const int c = idx / KC, k = idx - c * KC;
+          float v = 0.f;
+          if (c0 + c < a.dout && k0 + k < a.din) v = __ldg(a.w + (size_t)(c0 + c) * a.din + k0 + k);
+          Ws[c * XS + k] = v;
+        }
+      }
+      __syncthreads();
+      if (a.w) {
+#pragma unroll 4
+        for (int k = 0; k < KC; k += 4) {
+          float4 xv[RM];
+#pragma unroll
+          for (int i = 0; i < RM; ++i) xv[i] = *reinterpret_cast<const float4*>(Xs + (ty * RM + i) * XS + k);
+#pragma unroll
+          for (int bb = 0; bb < 4; ++bb) {
+            const float4 wv = *reinterpret_cast<const float4*>(Ws + (tx + 16 * bb) * XS + k);
+#pragma unroll
+            for (int i = 0; i < RM; ++i) {
+              acc[i][bb] = fmaf(xv[i].x, wv.x, acc[i][bb]);
+              acc[i][bb] = fmaf(xv[i].y, wv.y, acc[i][bb]);
+              acc[i][bb] = fmaf(xv[i].z, wv.z, acc[i][bb]);
+              acc[i][bb] = fmaf(xv[i].w, wv.w, acc[i][bb]);
+            }
+          }
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < RM; ++i)
+#pragma unroll
+          for (int bb = 0; bb < 4; ++bb) acc[i][bb] = Xs[(ty * RM + i) * XS + tx + 16 * bb];
+      }
+    }
+
+    // stage the finished (BR x TN) tile, then write every requested layout coalesced
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < RM; ++i)
+#pragma unroll
+      for (int bb = 0; bb < 4; ++bb) {
+        const int c = tx + 16 * bb;
+        float v = acc[i][bb];
+        if (a.w && a.b && c0 + c < a.dout) v += __ldg(a.b + c0 + c);
+        Ys[(ty * RM + i) * YS + c] = v * a.scale;
+      }
+    __syncthreads();
+    for (int idx = tid; idx < BR * TN; idx += NT) {
+      const int r = idx / TN, c = idx - r * TN;
+      const int gr = row0 + r, gc = c0 + c;
+      if (gc >= a.dout) continue;
+      const float v = (gr < a.rows) ? Ys[r * YS + c] : 0.f;
+      if (a.y && gr < a.rows) a.y[(size_t)gr * a.dout + gc] = v;
+      if (a.y16 && gr < a.rows_pad) reinterpret_cast<uint16_t*>(a.y16)[(size_t)gr * a.dout + gc] = to16(v, a.bf16);
+    }
+    if (a.yt16) {
+      for (int idx = tid; idx < BR * TN; idx += NT) {
+        const int c = idx / BR, r = idx - c * BR;
+        const int gr = row0 + r, gc = c0 + c;
+        if (gc >= a.dout || gr >= a.rows_pad) continue;
+        const float v = (gr < a.rows) ? Ys[r * YS + c] : 0.f;
+        reinterpret_cast<uint16_t*>(a.yt16)[(size_t)gc * a.rows_pad + gr] = to16(v, a.bf16);
+      }
+    }
+  }
+}
+
+int launch_ln_linear(const LnLinearArgs& a, cudaStream_t st) {
+  const int total_rows = (a.y16 || a.yt16) ? a.rows_pad : a.rows;
+  if (total_rows <= 0) return HOP_OK;
+  const int sms = num_sms();
+  if (total_rows >= 64 * sms) {
+    ln_linear_kernel<4><<<(total_rows + 63) / 64, NT, 0, st>>>(a);
+  } else if (total_rows >= 32 * sms) {
+    ln_linear_kernel<2><<<(total_rows + 31) / 32, NT, 0, st>>>(a);
+  } else {
+    ln_linear_kernel<1><<<(total_rows + 15) / 16, NT, 0, st>>>(a);
+  }
+  HOP_LAUNCH_CHECK("ln_linear_kernel");
+  return HOP_OK;
+}
+
+}  // namespace
+
+int launch_prepare_patterns(const hop_desc& d, const hop_params& p, const hop_patterns& pt, int path,
+                            cudaStream_t st) {
+  const bool tc = (path == HOP_PATH_TC_F16 || path == HOP_PATH_TC_BF16);
+  const int ppad = padded_patterns(d.n_patterns);
+  LnLinearArgs k{};
+  k.x = p.lookup; k.rows = d.n_patterns; k.rows_pad = ppad; k.din = d.d_in;
+  k.has_ln = (d.flags & HOP_F_NORM_STORED) ? 1 : 0; k.ln_w = p.ln_stored_w; k.ln_b = p.ln_stored_b; k.ln_eps = d.ln_eps;
+  k.w = (d.flags & HOP_F_PROJ_STORED) ? p.wk : nullptr; k.b = (d.flags & HOP_F_PROJ_STORED) ? p.bk : nullptr;
+  k.dout = d.d_assoc; k.scale = 1.f; k.y = pt.khat;
+  k.y16 = tc ? pt.k16 : nullptr; k.yt16 = (tc && d.update_steps > 0) ? pt.kt16 : nullptr;
+  k.bf16 = (path == HOP_PATH_TC_BF16);
+  if ((d.flags & HOP_F_PROJ_STORED) && !p.wk) HOP_FAIL(HOP_ERR_BAD_ARG, "HOP_F_PROJ_STORED set but params.wk is NULL");
+  HOP_TRY(launch_ln_linear(k, st));
+
+  LnLinearArgs v{};
+  v.x = p.lookup_targets ? p.lookup_targets : p.lookup; v.rows = d.n_patterns; v.rows_pad = ppad; v.din = d.d_in;
+  v.has_ln = (d.flags & HOP_F_NORM_PROJ) ? 1 : 0; v.ln_w = p.ln_proj_w; v.ln_b = p.ln_proj_b; v.ln_eps = d.ln_eps;
+  v.w = (d.flags & HOP_F_PROJ_PATTERN) ? p.wv : nullptr; v.b = (d.flags & HOP_F_PROJ_PATTERN) ? p.bv : nullptr;
+  v.dout = d.d_v; v.scale = 1.f; v.y = pt.vhat;
+  v.y16 = nullptr; v.yt16 = tc ? pt.vt16 : nullptr;
+  v.bf16 = (path == HOP_PATH_TC_BF16);
+  if ((d.flags & HOP_F_PROJ_PATTERN) && !p.wv) HOP_FAIL(HOP_ERR_BAD_ARG, "HOP_F_PROJ_PATTERN set but params.wv is NULL");
+  HOP_TRY(launch_ln_linear(v, st));
+  return HOP_OK;
+}
+
+int launch_prepare_queries(const hop_desc& d, const hop_params& p, const float* x, float* qhat, cudaStream_t st) {
+  LnLinearArgs q{};
+  q.x = x; q.rows = d.n_rows; q.rows_pad = d.n_rows; q.din = d.d_in;
+  q.has_ln = (d.flags & HOP_F_NORM_STATE) ? 1 : 0; q.ln_w = p.ln_state_w; q.ln_b = p.ln_state_b; q.ln_eps = d.ln_eps;
+  q.w = (d.flags & HOP_F_PROJ_STATE) ? p.wq : nullptr; q.b = (d.flags & HOP_F_PROJ_STATE) ? p.bq : nullptr;
+  q.dout = d.d_assoc; q.scale = d.beta; q.y = qhat;
+  if ((d.flags & HOP_F_PROJ_STATE) && !p.wq) HOP_FAIL(HOP_ERR_BAD_ARG, "HOP_F_PROJ_STATE set but params.wq is NULL");
+  return launch_ln_linear(q, st);
+}
+
+int launch_linear(int n, int din, int dout, const float* x, const float* w, const float* b, float* y,
+                  cudaStream_t st) {
+  LnLinearArgs l{};
+  l.x = x; l.rows = n; l.rows_pad = n; l.din = din; l.has_ln = 0; l.ln_eps = 0.f;
+  l.w = w; l.b = b; l.dout = dout; l.scale = 1.f; l.y = y;
+  return launch_ln_linear(l, st);
+}
+
+}  // namespace hop

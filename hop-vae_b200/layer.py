@@ -1,0 +1,259 @@
+"""`HopfieldLayer` -- host-side mirror of the reference's operator interface.
+
+Same constructor surface, forward signature and state-dict layout as the
+third-party `hflayers.HopfieldLayer` that joejenb/Hop-VAE imports
+(/root/reference/HopVAE.py:7, constructed at HopVAE.py:149-170, called at
+HopVAE.py:193,215,216,234,255,257,271), so `HopVAE.py`, `main.py` and
+`checkpoints/MNIST-28.ckpt` work unchanged.  The arithmetic runs in the sm_100a
+kernels behind `include/hop_sm100.h`; this file only holds parameters, builds
+the op description and caches the prepared pattern operands.
+
+State-dict keys (pinned by the shipped checkpoint):
+    lookup_weights                                   (1, quantity, input_size)
+    hopfield.association_core.in_proj_weight / _bias  (rows, input_size) / (rows)
+    hopfield.association_core.out_proj.weight / .bias
+    hopfield.norm_stored_pattern.weight / .bias
+    hopfield.norm_state_pattern.weight / .bias
+    hopfield.norm_pattern_projection.weight / .bias
+"""
+from __future__ import annotations
+
+import math
+import os
+from typing import Dict, Optional, Tuple
+
+import torch
+import torch.nn as nn
+from torch import Tensor
+
+from . import cabi
+from .ops import (LayerSpec, HopfieldAssociation, prepare_patterns_op, retrieve_op, resolve_path, _PATTERN_SIDE,
+                  _QUERY_SIDE, _PARAM_ORDER)
+
+_NOT_BUILT = dict(num_heads=1, normalize_hopfield_space=False, normalize_hopfield_space_affine=False,
+                  pattern_projection_as_connected=False, association_activation=None, dropout=0.0,
+                  concat_bias_pattern=False, add_zero_association=False, batch_first=True)
+
+
+class _AssociationCore(nn.Module):
+    """Parameter container named like upstream `HopfieldCore` (in_proj_* and out_proj)."""
+
+    def __init__(self, d_in: int, d_assoc: int, d_v: int, d_out: int, q_static: bool, k_static: bool,
+                 v_static: bool, bias: bool, out_projection: bool):
+        super().__init__()
+        self.rows_q = 0 if q_static else d_assoc
+        self.rows_k = 0 if k_static else d_assoc
+        self.rows_v = 0 if v_static else d_v
+        rows = self.rows_q + self.rows_k + self.rows_v
+        if rows:
+            self.in_proj_weight = nn.Parameter(torch.empty(rows, d_in))
+            self.in_proj_bias = nn.Parameter(torch.empty(rows)) if bias else None
+        else:
+            self.register_parameter("in_proj_weight", None)
+            self.register_parameter("in_proj_bias", None)
+        self.out_proj = nn.Linear(d_v, d_out, bias=bias) if out_projection else None
+        self.reset_parameters()
+
+    def reset_parameters(self) -> None:
+        if self.in_proj_weight is not None:
+            nn.init.normal_(self.in_proj_weight, mean=0.0, std=0.02)
+        if self.in_proj_bias is not None:
+            nn.init.zeros_(self.in_proj_bias)
+        if self.out_proj is not None:
+            nn.init.normal_(self.out_proj.weight, mean=0.0, std=0.02)
+            if self.out_proj.bias is not None:
+                nn.init.zeros_(self.out_proj.bias)
+
+    def split(self) -> Dict[str, Optional[Tensor]]:
+        """Views of the q / k / v slices of in_proj (order q, k, v; static ones absent)."""
+        out: Dict[str, Optional[Tensor]] = dict(wq=None, bq=None, wk=None, bk=None, wv=None, bv=None)
+        o = 0
+        for tag, rows in (("q", self.rows_q), ("k", self.rows_k), ("v", self.rows_v)):
+            if rows:
+                out["w" + tag] = self.in_proj_weight[o:o + rows]
+                out["b" + tag] = None if self.in_proj_bias is None else self.in_proj_bias[o:o + rows]
+                o += rows
+        return out
+
+
+class _Hopfield(nn.Module):
+    """Container named like upstream `Hopfield` (three LayerNorms + association core)."""
+
+    def __init__(self, d_in, d_assoc, d_v, d_out, norms, statics, bias, out_projection):
+        super().__init__()
+        (n_k, a_k, n_q, a_q, n_v, a_v) = norms
+        (k_static, q_static, v_static) = statics
+        self.association_core = _AssociationCore(d_in, d_assoc, d_v, d_out, q_static, k_static, v_static, bias,
+                                                 out_projection)
+        self.norm_stored_pattern = nn.LayerNorm(d_in, elementwise_affine=a_k) if n_k else None
+        self.norm_state_pattern = nn.LayerNorm(d_in, elementwise_affine=a_q) if n_q else None
+        self.norm_pattern_projection = nn.LayerNorm(d_in, elementwise_affine=a_v) if n_v else None
+
+
+class HopfieldLayer(nn.Module):
+    """Drop-in `hflayers.HopfieldLayer` whose CUDA path is the sm_100a library.
+
+    forward(input): (B, L, input_size) or (N, input_size), float32, CUDA ->
+    (B, L, output_size or input_size).  After a call, `last_argmax` holds the
+    nearest-pattern index per query row (int32, flattened rows).
+
+    `kernel_path` ("auto" | "fp32" | "f16" | "bf16", or env HOP_SM100_PATH)
+    selects the kernel family for inference; training always uses the exact
+    fp32 kernels (forward and backward on the same arithmetic).
+    """
+
+    def __init__(self, input_size: int, hidden_size: Optional[int] = None, output_size: Optional[int] = None,
+                 pattern_size: Optional[int] = None, num_heads: int = 1, scaling: Optional[float] = None,
+                 update_steps_max: int = 0, update_steps_eps: float = 1e-4,
+                 lookup_weights_as_separated: bool = False, lookup_targets_as_trainable: bool = True,
+                 normalize_stored_pattern: bool = True, normalize_stored_pattern_affine: bool = True,
+                 normalize_state_pattern: bool = True, normalize_state_pattern_affine: bool = True,
+                 normalize_pattern_projection: bool = True, normalize_pattern_projection_affine: bool = True,
+                 normalize_hopfield_space: bool = False, normalize_hopfield_space_affine: bool = False,
+                 stored_pattern_as_static: bool = False, state_pattern_as_static: bool = False,
+                 pattern_projection_as_static: bool = False, pattern_projection_as_connected: bool = False,
+                 stored_pattern_size: Optional[int] = None, pattern_projection_size: Optional[int] = None,
+                 batch_first: bool = True, association_activation: Optional[str] = None, dropout: float = 0.0,
+                 input_bias: bool = True, concat_bias_pattern: bool = False, add_zero_association: bool = False,
+                 disable_out_projection: bool = False, quantity: int = 1, trainable: bool = True):
+        super().__init__()
+        given = dict(num_heads=num_heads, normalize_hopfield_space=normalize_hopfield_space,
+                     normalize_hopfield_space_affine=normalize_hopfield_space_affine,
+                     pattern_projection_as_connected=pattern_projection_as_connected,
+                     association_activation=association_activation, dropout=dropout,
+                     concat_bias_pattern=concat_bias_pattern, add_zero_association=add_zero_association,
+                     batch_first=batch_first)
+        for name, default in _NOT_BUILT.items():
+            if given[name] != default:
+                raise NotImplementedError(f"HopfieldLayer({name}={given[name]!r}) is not built: Hop-VAE "
+                                          f"(HopVAE.py:149-170) leaves it at {default!r}")
+        if stored_pattern_size not in (None, input_size) or pattern_projection_size not in (None, input_size):
+            raise NotImplementedError("stored_pattern_size / pattern_projection_size other than input_size")
+        if update_steps_max is None or update_steps_max < 0:
+            raise NotImplementedError("update_steps_max < 0 (iterate until convergence) is not built; "
+                                      "give a fixed number of update steps")
+        d_in = int(input_size)
+        d_assoc = d_in if hidden_size is None else int(hidden_size)
+        d_v = d_assoc if pattern_size is None else int(pattern_size)
+        d_out = d_in if output_size is None else int(output_size)
+        if (stored_pattern_as_static or state_pattern_as_static) and d_assoc != d_in:
+            raise ValueError("static stored/state patterns live in the input space: hidden_size must equal input_size")
+        if pattern_projection_as_static and d_v != d_in:
+            raise ValueError("static pattern projection needs pattern_size == input_size")
+        self.input_size, self.hidden_size, self.pattern_size, self.output_size = d_in, d_assoc, d_v, d_out
+        self.quantity = int(quantity)
+        self.scaling = scaling
+        self.update_steps_max = int(update_steps_max)
+        self.update_steps_eps = float(update_steps_eps)
+        self.hopfield = _Hopfield(
+            d_in, d_assoc, d_v, d_out,
+            (normalize_stored_pattern, normalize_stored_pattern_affine, normalize_state_pattern,
+             normalize_state_pattern_affine, normalize_pattern_projection, normalize_pattern_projection_affine),
+            (stored_pattern_as_static, state_pattern_as_static, pattern_projection_as_static),
+            input_bias, not disable_out_projection)
+        self.lookup_weights = nn.Parameter(torch.empty(1, self.quantity, d_in), requires_grad=trainable)
+        if lookup_weights_as_separated:
+            self.lookup_targets = nn.Parameter(torch.empty(1, self.quantity, d_in),
+                                               requires_grad=lookup_targets_as_trainable)
+        else:
+            self.register_parameter("lookup_targets", None)
+        flags = 0
+        flags |= cabi.F_NORM_STATE if normalize_state_pattern else 0
+        flags |= cabi.F_NORM_STORED if normalize_stored_pattern else 0
+        flags |= cabi.F_NORM_PROJ if normalize_pattern_projection else 0
+        flags |= 0 if state_pattern_as_static else cabi.F_PROJ_STATE
+        flags |= 0 if stored_pattern_as_static else cabi.F_PROJ_STORED
+        flags |= 0 if pattern_projection_as_static else cabi.F_PROJ_PATTERN
+        flags |= 0 if disable_out_projection else cabi.F_OUT_PROJ
+        self._flags = flags
+        self.kernel_path = os.environ.get("HOP_SM100_PATH", "auto")
+        self.last_argmax: Optional[Tensor] = None
+        self._cache_key = None
+        self._cache = None
+        self.reset_parameters()
+
+    # ---------------------------------------------------------------- parameters
+    def reset_parameters(self) -> None:
+        nn.init.normal_(self.lookup_weights, mean=0.0, std=0.02)
+        if self.lookup_targets is not None:
+            nn.init.normal_(self.lookup_targets, mean=0.0, std=0.02)
+
+    @property
+    def beta(self) -> float:
+        return float(self.scaling) if self.scaling is not None else 1.0 / math.sqrt(self.hidden_size)
+
+    def spec(self) -> LayerSpec:
+        path = cabi.PATH_NAMES.get(self.kernel_path)
+        if path is None:
+            raise ValueError(f"kernel_path must be one of {sorted(cabi.PATH_NAMES)}, got {self.kernel_path!r}")
+        return LayerSpec(flags=self._flags, path=path, d_in=self.input_size, d_assoc=self.hidden_size,
+                         d_v=self.pattern_size, d_out=self.output_size, update_steps=self.update_steps_max,
+                         beta=self.beta, ln_eps=1e-5)
+
+    def param_pack(self) -> Dict[str, Optional[Tensor]]:
+        """The module's tensors under the hop_params names."""
+        h = self.hopfield
+        core = h.association_core
+        ln = lambda m: (None, None) if m is None else (m.weight, m.bias)
+        pack: Dict[str, Optional[Tensor]] = dict(
+            lookup=self.lookup_weights[0],
+            lookup_targets=None if self.lookup_targets is None else self.lookup_targets[0])
+        pack["ln_state_w"], pack["ln_state_b"] = ln(h.norm_state_pattern)
+        pack["ln_stored_w"], pack["ln_stored_b"] = ln(h.norm_stored_pattern)
+        pack["ln_proj_w"], pack["ln_proj_b"] = ln(h.norm_pattern_projection)
+        pack.update(core.split())
+        pack["wo"] = None if core.out_proj is None else core.out_proj.weight
+        pack["bo"] = None if core.out_proj is None else core.out_proj.bias
+        return pack
+
+    # ------------------------------------------------------------------- caching
+    def _prepared(self, pack, spec: LayerSpec, path: int):
+        """Prepared pattern operands, recomputed only when a pattern-side tensor changed."""
+        key = (path, spec.update_steps) + tuple(
+            (None if pack[k] is None else (pack[k].data_ptr(), pack[k]._version, pack[k].device))
+            for k in _PATTERN_SIDE)
+        if key != self._cache_key:
+            with torch.no_grad():
+                self._cache = prepare_patterns_op(*[None if pack[k] is None else pack[k].detach().contiguous()
+                                                    for k in _PATTERN_SIDE],
+                                                  spec.flags, path, spec.d_assoc, spec.d_v, spec.update_steps,
+                                                  spec.ln_eps)
+            self._cache_key = key
+        return self._cache
+
+    # ------------------------------------------------------------------- forward
+    def forward(self, input: Tensor, stored_pattern_padding_mask: Optional[Tensor] = None,
+                association_mask: Optional[Tensor] = None) -> Tensor:
+        if stored_pattern_padding_mask is not None or association_mask is not None:
+            raise NotImplementedError("masks are not used by Hop-VAE and are not built")
+        if not input.is_cuda:
+            raise RuntimeError("hflayers.HopfieldLayer (hop_sm100): input is on the CPU; this layer runs only on an "
+                               "sm_100a GPU and has no CPU fallback")
+        if input.shape[-1] != self.input_size:
+            raise ValueError(f"expected last dimension {self.input_size}, got {tuple(input.shape)}")
+        lead = input.shape[:-1]
+        x = input.reshape(-1, self.input_size)
+        if x.dtype != torch.float32:
+            raise RuntimeError(f"hop_sm100: float32 input expected, got {x.dtype}")
+        x = x.contiguous()
+        spec = self.spec()
+        pack = self.param_pack()
+        needs_grad = torch.is_grad_enabled() and (
+            x.requires_grad or any(t is not None and t.requires_grad for t in pack.values()))
+        if needs_grad:
+            out, argmax = HopfieldAssociation.apply(spec, x, *[None if pack[k] is None else pack[k].contiguous()
+                                                               for k in _PARAM_ORDER])
+        else:
+            path = resolve_path(spec, x.shape[0], self.quantity)
+            pats = self._prepared(pack, spec, path)
+            res = retrieve_op(x.detach(), *pats, *[None if pack[k] is None else pack[k].detach().contiguous()
+                                                   for k in _QUERY_SIDE],
+                              spec.flags, path, spec.d_in, spec.d_out, spec.update_steps, spec.beta, spec.ln_eps, 0)
+            out, argmax = res[0], res[4]
+        self.last_argmax = argmax
+        return out.reshape(*lead, out.shape[-1])
+
+    def extra_repr(self) -> str:
+        return (f"input_size={self.input_size}, hidden_size={self.hidden_size}, pattern_size={self.pattern_size}, "
+                f"output_size={self.output_size}, quantity={self.quantity}, beta={self.beta:.6g}, "
+                f"update_steps_max={self.update_steps_max}, kernel_path={self.kernel_path!r}")

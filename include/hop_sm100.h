@@ -1,0 +1,214 @@
+/*
+ * hop_sm100.h -- C-ABI of the B200-native (sm_100a) Hopfield retrieval library.
+ *
+ * This is the drop-in boundary for ONE path of joejenb/Hop-VAE: the
+ * `hflayers.HopfieldLayer` association that HopVAE.py places between encoder
+ * and decoder.  The reference has no FFI of its own for this path (it is a
+ * Python nn.Module API, /root/reference/HopVAE.py:7 `from hflayers import
+ * HopfieldLayer`); every entry point below therefore cites the reference /
+ * upstream interface it stands in for, and `INTEGRATION.md` shows the ctypes
+ * stub that binds it behind the unchanged module API.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch / C++ types;
+ *   - every pointer is a DEVICE pointer unless the name ends in `_host`;
+ *   - all tensors are fp32, row-major, contiguous, 16-byte aligned;
+ *   - the library never allocates or frees device memory and never
+ *     synchronises the host: the caller passes outputs and a workspace whose
+ *     size it queried first, and a `cudaStream_t` (as `void*`) on which all
+ *     work is enqueued;
+ *   - every function returns a `hop_status`; `hop_sm100_last_error()` gives
+ *     the thread-local message of the last non-zero status;
+ *   - there is NO CPU fallback and no non-sm_100 code path.
+ *
+ * Shapes:  N query rows ("latents"), P stored patterns, Din raw width
+ * (`input_size`), H association width, Dv pattern-projection width, Dout
+ * output width, T extra retrieve updates (`update_steps_max`).
+ */
+#ifndef HOP_SM100_H_
+#define HOP_SM100_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HOP_SM100_ABI_VERSION 1u
+
+typedef enum hop_status {
+  HOP_OK = 0,
+  HOP_ERR_BAD_ARG = 1,      /* null pointer, bad abi_version, bad enum            */
+  HOP_ERR_BAD_SHAPE = 2,    /* a dimension is <= 0 or outside what is built       */
+  HOP_ERR_BAD_ALIGN = 3,    /* a pointer is not 16-byte aligned                   */
+  HOP_ERR_BAD_ARCH = 4,     /* current device is not compute capability 10.x      */
+  HOP_ERR_CUDA = 5,         /* a CUDA call failed (message has the CUDA error)    */
+  HOP_ERR_WORKSPACE = 6,    /* workspace too small                                */
+  HOP_ERR_UNSUPPORTED = 7   /* valid request that this build does not implement   */
+} hop_status;
+
+/* hop_desc.flags -- which optional stages of upstream `Hopfield._associate` /
+ * `HopfieldCore` are present.  Hop-VAE's three layers (HopVAE.py:149-170,
+ * stored/state patterns static) use NORM_* | PROJ_PATTERN | OUT_PROJ.         */
+enum {
+  HOP_F_NORM_STATE   = 1u << 0,  /* LayerNorm on queries   (normalize_state_pattern)      */
+  HOP_F_NORM_STORED  = 1u << 1,  /* LayerNorm on patterns  (normalize_stored_pattern)     */
+  HOP_F_NORM_PROJ    = 1u << 2,  /* LayerNorm on patterns  (normalize_pattern_projection) */
+  HOP_F_PROJ_STATE   = 1u << 3,  /* Q projection present   (state_pattern_as_static=False)  */
+  HOP_F_PROJ_STORED  = 1u << 4,  /* K projection present   (stored_pattern_as_static=False) */
+  HOP_F_PROJ_PATTERN = 1u << 5,  /* V projection present   (pattern_projection_as_static=False) */
+  HOP_F_OUT_PROJ     = 1u << 6   /* out_proj present       (disable_out_projection=False)  */
+};
+
+/* hop_desc.path -- which kernel family evaluates the association.            */
+enum {
+  HOP_PATH_AUTO      = 0,  /* library picks (see hop_sm100_select_path)                         */
+  HOP_PATH_FP32_SIMT = 1,  /* exact fp32 CUDA-core kernels (small / argmax-tight problems, D<16) */
+  HOP_PATH_TC_F16    = 2,  /* tcgen05 kind::f16 MMAs, fp16-encoded operands, fp32 accumulate    */
+  HOP_PATH_TC_BF16   = 3   /* same kernels, bf16-encoded operands (fails the 1e-3 parity bar;
+                              kept for throughput comparison)                                    */
+};
+
+typedef struct hop_desc {
+  uint32_t abi_version;     /* HOP_SM100_ABI_VERSION                                   */
+  uint32_t flags;           /* HOP_F_*                                                 */
+  int32_t  path;            /* HOP_PATH_*                                              */
+  int32_t  n_rows;          /* N                                                       */
+  int32_t  n_patterns;      /* P  (`quantity`; this shard's count when sharded)        */
+  int32_t  d_in;            /* Din (`input_size`)                                      */
+  int32_t  d_assoc;         /* H  (`hidden_size`, = Din when Q/K are static)           */
+  int32_t  d_v;             /* Dv (`pattern_size`, = H by default)                     */
+  int32_t  d_out;           /* Dout (`output_size`), ignored without HOP_F_OUT_PROJ    */
+  int32_t  update_steps;    /* T  (`update_steps_max`, >= 0; fixed-count semantics)    */
+  int32_t  pattern_offset;  /* global index of this shard's first pattern (argmax)     */
+  float    beta;            /* `scaling` (1/sqrt(H) when upstream's is None)           */
+  float    ln_eps;          /* LayerNorm eps (1e-5)                                    */
+} hop_desc;
+
+/* Module parameters, exactly the tensors of the reference's state-dict
+ * (checkpoints/MNIST-28.ckpt keys).  NULL where a stage is
+ * absent; LayerNorm weight/bias NULL means "no affine".                      */
+typedef struct hop_params {
+  const float* lookup;         /* lookup_weights[0]                         (P, Din)  */
+  const float* lookup_targets; /* lookup_targets[0] or NULL (= lookup)      (P, Din)  */
+  const float* ln_state_w;     /* hopfield.norm_state_pattern.weight        (Din)     */
+  const float* ln_state_b;     /* hopfield.norm_state_pattern.bias          (Din)     */
+  const float* ln_stored_w;    /* hopfield.norm_stored_pattern.weight       (Din)     */
+  const float* ln_stored_b;    /* hopfield.norm_stored_pattern.bias         (Din)     */
+  const float* ln_proj_w;      /* hopfield.norm_pattern_projection.weight   (Din)     */
+  const float* ln_proj_b;      /* hopfield.norm_pattern_projection.bias     (Din)     */
+  const float* wq; const float* bq;  /* in_proj_weight/bias q-slice  (H, Din), (H)    */
+  const float* wk; const float* bk;  /* in_proj_weight/bias k-slice  (H, Din), (H)    */
+  const float* wv; const float* bv;  /* in_proj_weight/bias v-slice  (Dv, Din), (Dv)  */
+  const float* wo; const float* bo;  /* out_proj.weight/bias         (Dout, Dv), (Dout) */
+} hop_params;
+
+/* Prepared pattern-side operands: written by hop_sm100_prepare_patterns, read
+ * by forward/backward.  Sizes from hop_sm100_pattern_bytes.  The 16-bit packs
+ * are only needed (and only written) for the tensor-core paths.              */
+typedef struct hop_patterns {
+  float* khat;   /* K^ = [LN_k](W)[Wk^T + bk]            (P, H)   fp32                 */
+  float* vhat;   /* V^ = [LN_v](Wt)[Wv^T + bv]           (P, Dv)  fp32                 */
+  void*  k16;    /* K^ 16-bit, K-major for the score MMA (Ppad, H)                     */
+  void*  kt16;   /* K^ transposed, for retrieve updates  (H, Ppad)  (T > 0 only)       */
+  void*  vt16;   /* V^ transposed, for the read-out MMA  (Dv, Ppad)                    */
+} hop_patterns;
+
+/* Gradients written (overwritten, not accumulated) by hop_sm100_backward.
+ * Same shapes as the corresponding hop_params members; NULL = not wanted.    */
+typedef struct hop_grads {
+  float* d_x;            /* (N, Din)  gradient w.r.t. the queries */
+  float* d_lookup;       /* (P, Din)  via K^ and via V^ (summed; lookup_targets == NULL) */
+  float* d_lookup_targets;
+  float* d_ln_state_w;  float* d_ln_state_b;
+  float* d_ln_stored_w; float* d_ln_stored_b;
+  float* d_ln_proj_w;   float* d_ln_proj_b;
+  float* d_wq; float* d_bq;
+  float* d_wk; float* d_bk;
+  float* d_wv; float* d_bv;
+  float* d_wo; float* d_bo;
+} hop_grads;
+
+/* ABI / build identification.  Returns HOP_SM100_ABI_VERSION.                */
+uint32_t hop_sm100_version(void);
+
+/* Thread-local message of the last failing call on this thread ("" if none). */
+const char* hop_sm100_last_error(void);
+
+/* Path the library would run for `desc` (resolves HOP_PATH_AUTO): the exact
+ * fp32 kernels for small problems or H < 16, the tcgen05 kernels otherwise.  */
+int hop_sm100_select_path(const hop_desc* desc, int32_t* path_out);
+
+/* Byte sizes of the five hop_patterns buffers (0 where not needed).          */
+int hop_sm100_pattern_bytes(const hop_desc* desc, size_t* khat, size_t* vhat,
+                            size_t* k16, size_t* kt16, size_t* vt16);
+
+/* Workspace bytes needed by forward (for_backward == 0) or backward (!= 0).  */
+int hop_sm100_workspace_bytes(const hop_desc* desc, int for_backward, size_t* bytes);
+
+/* Pattern-side preparation, once per parameter update (replaces the B-times
+ * redundant LayerNorm / projection of the batch-expanded lookup matrix that
+ * upstream `HopfieldLayer._prepare_input` + `Hopfield._associate` +
+ * `HopfieldCore` in-projection perform; called from HopVAE.py:193,215,216,
+ * 234,255,257,271 through `HopfieldLayer.forward`).                          */
+int hop_sm100_prepare_patterns(const hop_desc* desc, const hop_params* params,
+                               const hop_patterns* patterns, void* stream);
+
+/* The association itself: upstream `hopfield_core_forward` as reached from
+ * `HopfieldLayer.forward` (call sites HopVAE.py:193,215,216,234,255,257,271):
+ * LN_q, optional Q projection, beta scaling, score contraction, row softmax,
+ * T retrieve updates, read-out, out-projection.
+ *   x          (N, Din)   queries
+ *   out        (N, Dout)  layer output ((N, Dv) without HOP_F_OUT_PROJ)
+ *   retrieved  (N, Dv)    A.V^ before out_proj            (optional, NULL ok)
+ *   qhat       (N, H)     beta * Q^ of the LAST pass      (optional; needed for backward)
+ *   lse        (N)        log-sum-exp of the last pass' scores (natural log)
+ *   argmax     (N)        index of the nearest (highest-score) pattern, + pattern_offset
+ * When sharded, `out` of each shard is the shard-local normalised result and
+ * (`retrieved`, `lse`, `argmax`, `rowmax`) feed hop_sm100_merge_shards.
+ *   rowmax     (N)        max score of the last pass (optional, NULL ok)     */
+int hop_sm100_forward(const hop_desc* desc, const hop_params* params,
+                      const hop_patterns* patterns, const float* x,
+                      float* out, float* retrieved, float* qhat, float* lse,
+                      int32_t* argmax, float* rowmax,
+                      void* workspace, size_t workspace_bytes, void* stream);
+
+/* Backward of hop_sm100_forward for T == 0 (what every reference config
+ * trains with: update_steps_max defaults to 0, main.py:35 `loss.backward()`).
+ * Flash-style: the N x P matrices are recomputed from (qhat, lse), never
+ * stored.  `retrieved` is the forward's A.V^ (N, Dv).                        */
+int hop_sm100_backward(const hop_desc* desc, const hop_params* params,
+                       const hop_patterns* patterns, const float* x,
+                       const float* qhat, const float* retrieved, const float* lse,
+                       const float* grad_out, const hop_grads* grads,
+                       void* workspace, size_t workspace_bytes, void* stream);
+
+/* Pattern-sharded mode (new; the reference is single-device): combine G
+ * shard-local results with the log-sum-exp monoid.
+ *   lse_all     (G, N)      every shard's lse   (after an all-gather)
+ *   rowmax_all  (G, N)      every shard's row max, argmax_all (G, N) its index
+ *   retrieved   (N, Dv)     in: this shard's normalised A_g.V^_g ; out: scaled by
+ *                            w_g = exp(lse_g - lse) so that a SUM all-reduce over
+ *                            shards yields the global read-out
+ *   lse_out     (N)         global lse;  argmax_out (N) global nearest pattern
+ *                            (ties -> lowest index)                              */
+int hop_sm100_merge_shards(int32_t n_rows, int32_t d_v, int32_t n_shards, int32_t shard,
+                           const float* lse_all, const float* rowmax_all,
+                           const int32_t* argmax_all, float* retrieved,
+                           float* lse_out, int32_t* argmax_out, void* stream);
+
+/* out = retrieved . Wo^T + bo on (N, Dv) -> (N, Dout); used after a shard
+ * merge (upstream `out_proj`, ckpt keys ...association_core.out_proj.*).     */
+int hop_sm100_out_projection(int32_t n_rows, int32_t d_v, int32_t d_out,
+                             const float* retrieved, const float* wo, const float* bo,
+                             float* out, void* stream);
+
+/* Number of kernel launches this library has enqueued since load (for the
+ * bench's `gpu_launches` claim); thread-safe, monotonically increasing.      */
+uint64_t hop_sm100_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HOP_SM100_H_ */

@@ -1,0 +1,130 @@
+"""CPU: the C-ABI library loads and exports every symbol include/hop_sm100.h declares,
+the ctypes structs match the C layout (checked against a gcc-compiled probe), and the
+reference-facing `hflayers.HopfieldLayer` mirrors the upstream interface.  No compute."""
+import ctypes as C
+import inspect
+import os
+import re
+import subprocess
+import sys
+
+import pytest
+import torch
+
+from util import ROOT, load_ckpt, layer_state
+
+HEADER = os.path.join(ROOT, "include", "hop_sm100.h")
+
+
+@pytest.fixture(scope="module")
+def impl():
+    sys.path.insert(0, ROOT)
+    if not os.path.exists(os.path.join(ROOT, "hop-vae_b200", "libhop_sm100.so")):
+        import __graft_entry__
+        __graft_entry__.build()
+    import hflayers
+    return hflayers._impl
+
+
+def test_library_exports_every_declared_symbol(impl):
+    text = open(HEADER).read()
+    declared = sorted(set(re.findall(r"\b(hop_sm100_\w+)\s*\(", text)))
+    assert len(declared) >= 11
+    lib = impl.cabi.load()
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in include/hop_sm100.h but not exported"
+    assert sorted(impl.cabi.EXPORTS) == declared
+    assert lib.hop_sm100_version() == impl.cabi.ABI_VERSION == 1
+
+
+def test_struct_layouts_match_c(impl, tmp_path):
+    src = tmp_path / "probe.c"
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "hop_sm100.h"\n'
+                   'int main(void){printf("%zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(hop_desc), sizeof(hop_params),'
+                   ' sizeof(hop_patterns), sizeof(hop_grads), offsetof(hop_desc, beta), offsetof(hop_desc, n_patterns),'
+                   ' offsetof(hop_params, wo), offsetof(hop_grads, d_wo)); return 0;}\n')
+    exe = tmp_path / "probe"
+    subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    got = [int(v) for v in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()]
+    cb = impl.cabi
+    want = [C.sizeof(cb.HopDesc), C.sizeof(cb.HopParams), C.sizeof(cb.HopPatterns), C.sizeof(cb.HopGrads),
+            cb.HopDesc.beta.offset, cb.HopDesc.n_patterns.offset, cb.HopParams.wo.offset, cb.HopGrads.d_wo.offset]
+    assert got == want
+
+
+def test_error_reporting_without_gpu(impl):
+    """Argument validation happens before any CUDA call: status code + thread-local message."""
+    cb = impl.cabi
+    lib = cb.load()
+    d = cb.make_desc(flags=0, path=0, n_rows=4, n_patterns=0, d_in=8, d_assoc=8, d_v=8, d_out=8, update_steps=0,
+                     beta=0.3)
+    out = C.c_int32(0)
+    st = lib.hop_sm100_select_path(C.byref(d), C.byref(out))
+    assert st == 2 and b"non-positive" in lib.hop_sm100_last_error()
+    d.n_patterns = 16
+    d.abi_version = 99
+    assert lib.hop_sm100_select_path(C.byref(d), C.byref(out)) == 1
+    with pytest.raises(RuntimeError, match="HOP_ERR_BAD_ARG"):
+        cb.check(1, "probe")
+    d.abi_version = 1
+    assert lib.hop_sm100_select_path(C.byref(d), C.byref(out)) == 0 and out.value == cb.PATH_FP32_SIMT
+    # the reference's own shapes stay on the exact fp32 kernels; the big sweep goes to tcgen05
+    big = cb.make_desc(flags=0, path=0, n_rows=16384, n_patterns=65536, d_in=256, d_assoc=256, d_v=256, d_out=256,
+                       update_steps=0, beta=1 / 16)
+    assert lib.hop_sm100_select_path(C.byref(big), C.byref(out)) == 0
+    assert out.value in (cb.PATH_TC_F16, cb.PATH_FP32_SIMT)
+    sizes = [C.c_size_t(0) for _ in range(5)]
+    assert lib.hop_sm100_pattern_bytes(C.byref(big), *[C.byref(s) for s in sizes]) == 0
+    assert sizes[0].value == 65536 * 256 * 4
+
+
+def test_constructor_signature_mirrors_upstream(impl):
+    from oracle import hflayers_oracle as O
+    ours = inspect.signature(impl.HopfieldLayer.__init__)
+    ref = inspect.signature(O.HopfieldLayer.__init__)
+    assert list(ours.parameters) == list(ref.parameters)
+    for name, p in ref.parameters.items():
+        assert ours.parameters[name].default == p.default, name
+    fwd = list(inspect.signature(impl.HopfieldLayer.forward).parameters)
+    assert fwd[:4] == ["self", "input", "stored_pattern_padding_mask", "association_mask"]
+
+
+@pytest.mark.parametrize("name,kw", [
+    ("hopfield", dict(input_size=64)),
+    ("embedding_to_index", dict(input_size=64, output_size=3)),
+    ("index_to_embedding", dict(input_size=3, output_size=64)),
+])
+def test_state_dict_contract(impl, name, kw):
+    """HopVAE.py:149-170 construction + utils/__init__.py:36-49 loader: same names, same shapes, nn.Parameters."""
+    import hflayers
+    layer = hflayers.HopfieldLayer(quantity=512, stored_pattern_as_static=True, state_pattern_as_static=True, **kw)
+    sd = layer_state(load_ckpt(), name)
+    res = layer.load_state_dict(sd, strict=True)
+    assert not res.missing_keys and not res.unexpected_keys
+    assert all(isinstance(p, torch.nn.Parameter) for p in layer.parameters())
+    assert set(layer.state_dict()) == set(sd)
+    assert abs(layer.beta - (kw["input_size"] ** -0.5)) < 1e-7
+
+
+def test_no_cpu_fallback_and_unsupported_options(impl):
+    import hflayers
+    layer = hflayers.HopfieldLayer(input_size=8, quantity=4, stored_pattern_as_static=True,
+                                   state_pattern_as_static=True)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        layer(torch.randn(2, 3, 8))
+    for bad in (dict(num_heads=2), dict(dropout=0.1), dict(normalize_hopfield_space=True),
+                dict(add_zero_association=True), dict(update_steps_max=-1)):
+        with pytest.raises(NotImplementedError):
+            hflayers.HopfieldLayer(input_size=8, **bad)
+    with pytest.raises(NotImplementedError):
+        layer.forward(torch.randn(1, 1, 8), association_mask=torch.zeros(1, 4, dtype=torch.bool))
+
+
+def test_product_path_never_imports_oracle():
+    """The shipped packages must not reference oracle/ (only tests, smoke() and bench's CPU legs may)."""
+    for pkg in ("hop-vae_b200", "hflayers"):
+        for dirpath, _, files in os.walk(os.path.join(ROOT, pkg)):
+            for f in files:
+                if f.endswith((".py", ".cu", ".cuh", ".h")):
+                    text = open(os.path.join(dirpath, f)).read()
+                    assert not re.search(r"^\s*(from|import)\s+oracle\b", text, re.M), (dirpath, f)

@@ -1,0 +1,295 @@
+"""GPU (-m gpu): parity of the sm_100a kernels, called through the C-ABI, against the CPU oracle.
+
+Tolerances (BASELINE.json north_star): rel-L2 <= 1e-3 on retrieved latents / layer outputs, identical
+nearest-pattern indices, <= 0.5 % relative on reconstruction MSE.  The exact fp32 kernels are held to a
+much tighter bar (1e-5) -- they must be *the same arithmetic* as the reference's fp32 path.
+"""
+import math
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+import hopvae_harness as H
+from oracle import hflayers_oracle as O
+from util import REL_L2_BAR, RECON_MSE_REL_BAR, load_ckpt, load_golden, rel_l2, randomize_
+
+pytestmark = pytest.mark.gpu
+
+FP32_BAR = 1e-5
+
+
+@pytest.fixture(scope="module")
+def hf():
+    import hflayers
+    hflayers._impl.cabi.load()          # fail loudly if the extension is missing
+    return hflayers
+
+
+def make_pair(hf, seed=0, scale=1.0, **kw):
+    ref = randomize_(O.HopfieldLayer(**kw), seed, scale)
+    dut = hf.HopfieldLayer(**kw)
+    dut.load_state_dict(ref.state_dict())
+    return ref, dut.cuda()
+
+
+def check_argmax(ref_layer, x, got):
+    """Nearest-pattern index must be identical wherever the oracle's own top-1/top-2 gap is above fp32 noise."""
+    with torch.no_grad():
+        _, _, scores, _ = ref_layer(x, return_details=True)
+    s = scores.reshape(-1, scores.shape[-1])
+    want = s.argmax(-1)
+    if s.shape[-1] > 1:
+        top2 = s.topk(2, dim=-1).values
+        decided = (top2[:, 0] - top2[:, 1]) > 1e-5 * top2[:, 0].abs().clamp_min(1.0)
+    else:
+        decided = torch.ones_like(want, dtype=torch.bool)
+    got = got.cpu().long()
+    assert torch.equal(got[decided], want[decided]), "nearest-pattern index differs where the oracle is decided"
+    assert (got == want).float().mean() > 0.995
+
+
+STATIC = dict(stored_pattern_as_static=True, state_pattern_as_static=True)
+CASES = {
+    "mnist_hopfield": (dict(input_size=64, quantity=512, **STATIC), (32, 64)),
+    "mnist_emb2idx": (dict(input_size=64, output_size=3, quantity=512, **STATIC), (32, 64)),
+    "mnist_idx2emb": (dict(input_size=3, output_size=64, quantity=512, **STATIC), (32, 64)),
+    "ffhq64_rows": (dict(input_size=64, quantity=512, **STATIC), (32, 289)),
+    "ragged_rows": (dict(input_size=64, quantity=512, **STATIC), (3, 7)),
+    "single_row": (dict(input_size=64, quantity=512, **STATIC), (1, 1)),
+    "ragged_patterns": (dict(input_size=32, quantity=100, **STATIC), (4, 33)),
+    "one_pattern": (dict(input_size=16, quantity=1, **STATIC), (2, 5)),
+    "odd_width": (dict(input_size=17, output_size=5, quantity=77, **STATIC), (3, 11)),
+    "wide_128": (dict(input_size=128, quantity=300, **STATIC), (2, 50)),
+    "wide_256": (dict(input_size=256, quantity=130, **STATIC), (2, 40)),
+    "no_out_proj": (dict(input_size=32, quantity=64, disable_out_projection=True, **STATIC), (2, 9)),
+    "no_layernorm": (dict(input_size=32, quantity=64, normalize_stored_pattern=False,
+                          normalize_state_pattern=False, normalize_pattern_projection=False, **STATIC), (2, 9)),
+    "no_affine": (dict(input_size=32, quantity=64, normalize_stored_pattern_affine=False,
+                       normalize_state_pattern_affine=False, normalize_pattern_projection_affine=False,
+                       **STATIC), (2, 9)),
+    "static_projection": (dict(input_size=32, quantity=64, pattern_projection_as_static=True, **STATIC), (2, 9)),
+    "projected_qk": (dict(input_size=24, hidden_size=40, pattern_size=48, output_size=10, quantity=90), (3, 13)),
+    "beta_given": (dict(input_size=32, quantity=64, scaling=0.7, **STATIC), (2, 9)),
+    "separate_targets": (dict(input_size=32, quantity=64, lookup_weights_as_separated=True, **STATIC), (2, 9)),
+    "no_bias": (dict(input_size=32, quantity=64, input_bias=False, **STATIC), (2, 9)),
+}
+
+
+@pytest.mark.parametrize("name", list(CASES))
+def test_forward_parity_fp32(hf, name):
+    kw, (b, l) = CASES[name]
+    ref, dut = make_pair(hf, seed=11, **kw)
+    x = torch.randn(b, l, kw["input_size"], generator=torch.Generator().manual_seed(12))
+    with torch.no_grad():
+        want = ref(x)
+        got = dut(x.cuda())
+    assert got.shape == want.shape
+    r = rel_l2(got, want)
+    print(f"{name}: rel-L2 {r:.3e}")
+    assert r < FP32_BAR
+    check_argmax(ref, x, dut.last_argmax)
+
+
+@pytest.mark.parametrize("T", [1, 3])
+@pytest.mark.parametrize("d", [64, 3, 40])
+def test_update_steps_parity(hf, T, d):
+    """Fixed-point iteration xi <- X^T softmax(beta X xi): T extra retrieve updates (fixed-count semantics)."""
+    kw = dict(input_size=d, quantity=200, update_steps_max=T, update_steps_eps=0.0, **STATIC)
+    ref, dut = make_pair(hf, seed=21, **kw)
+    x = torch.randn(4, 50, d, generator=torch.Generator().manual_seed(22))
+    with torch.no_grad():
+        want = ref(x)
+        got = dut(x.cuda())
+    r = rel_l2(got, want)
+    print(f"T={T} d={d}: rel-L2 {r:.3e}")
+    assert r < 1e-4
+    # upstream's default eps early-stop stays within the documented O(eps) of fixed-T
+    ref.hopfield.update_steps_eps = 1e-4
+    with torch.no_grad():
+        assert rel_l2(got, ref(x)) < REL_L2_BAR
+
+
+def test_2d_input_and_dtype_errors(hf):
+    kw = dict(input_size=64, quantity=128, **STATIC)
+    ref, dut = make_pair(hf, seed=31, **kw)
+    x = torch.randn(100, 64)
+    with torch.no_grad():
+        assert rel_l2(dut(x.cuda()), ref(x)) < FP32_BAR
+    with pytest.raises(RuntimeError, match="float32"):
+        dut(x.cuda().half())
+    with pytest.raises(ValueError):
+        dut(torch.randn(4, 63).cuda())
+
+
+def test_pattern_cache_invalidation(hf):
+    """Prepared K^/V^ are cached across calls and refreshed when a parameter changes in place."""
+    kw = dict(input_size=32, quantity=64, **STATIC)
+    ref, dut = make_pair(hf, seed=41, **kw)
+    x = torch.randn(2, 9, 32)
+    with torch.no_grad():
+        a = dut(x.cuda()).clone()
+        cache = dut._cache
+        b = dut(x.cuda())
+        assert dut._cache is cache and torch.equal(a, b)
+        dut.lookup_weights.mul_(1.5)
+        ref.lookup_weights.mul_(1.5)
+        c = dut(x.cuda())
+        assert dut._cache is not cache
+        assert rel_l2(c, ref(x)) < FP32_BAR
+
+
+# ----------------------------------------------------------------------------- golden checkpoint
+@pytest.fixture(scope="module")
+def ckpt_models(hf):
+    sd = load_ckpt()
+    ref = H.HopVAEHarness(H.MNIST_28, O.HopfieldLayer)
+    ref.load_state_dict(sd, strict=True)
+    dut = H.HopVAEHarness(H.MNIST_28, hf.HopfieldLayer)
+    res = dut.load_state_dict(sd, strict=True)          # the shipped checkpoint loads unchanged
+    assert not res.missing_keys and not res.unexpected_keys
+    return ref.eval(), dut.cuda().eval()
+
+
+@pytest.mark.parametrize("tag", ["strokes", "randn"])
+def test_checkpoint_golden_parity(ckpt_models, tag):
+    """MNIST-28.ckpt on the committed reference-generated vectors: latents, indices, reconstruction."""
+    ref, dut = ckpt_models
+    g = load_golden()
+    x = torch.from_numpy(g[f"{tag}_x"])
+    with torch.no_grad():
+        z = torch.from_numpy(g[f"{tag}_z"]).cuda()
+        b = dut.bottleneck(z)
+        am = {n: getattr(dut, n).last_argmax.cpu().numpy() for n in
+              ("hopfield", "embedding_to_index", "index_to_embedding")}
+        x_recon = dut.decode(b["emb"])
+        mse = float(F.mse_loss(x_recon.cpu(), x))
+    for k in ("emb", "logits", "emb_recon"):
+        r = rel_l2(b[k], g[f"{tag}_{k}"])
+        print(f"{tag} {k}: rel-L2 {r:.3e}")
+        assert r < REL_L2_BAR
+    # quantised indices feed the third layer: identical levels are required for identical latents
+    assert (b["idx"].cpu().numpy() == g[f"{tag}_idx"]).mean() > 0.9995
+    for n, a in am.items():
+        same = (a == g[f"{tag}_argmax_{n}"]).mean()
+        print(f"{tag} argmax {n}: identical {same:.6f}")
+        assert same == 1.0 or (n == "index_to_embedding" and same > 0.999)   # D=3: gaps down to 3e-6
+    want_mse = float(g[f"{tag}_recon_mse"])
+    print(f"{tag} recon MSE {mse:.6e} vs {want_mse:.6e}")
+    assert abs(mse - want_mse) <= RECON_MSE_REL_BAR * want_mse
+    assert abs(float(b["emb_recon_loss"]) - float(g[f"{tag}_emb_recon_loss"])) <= 5e-3 * float(g[f"{tag}_emb_recon_loss"])
+
+
+def test_checkpoint_full_forward(ckpt_models):
+    """Whole model through the unchanged caller glue on the GPU: known answers of SURVEY.md B.4."""
+    ref, dut = ckpt_models
+    x = H.stroke_batch(32)
+    with torch.no_grad():
+        xr, loss = dut(x.cuda())
+    assert abs(float(loss) - 1.08e-5) < 3e-7
+    assert abs(float(F.mse_loss(xr.cpu(), x)) - 5.19e-4) < 3e-6
+
+
+# ----------------------------------------------------------------------------- backward
+BWD_CASES = {
+    "mnist_hopfield": (dict(input_size=64, quantity=512, **STATIC), (8, 64)),
+    "mnist_emb2idx": (dict(input_size=64, output_size=3, quantity=512, **STATIC), (8, 64)),
+    "mnist_idx2emb": (dict(input_size=3, output_size=64, quantity=512, **STATIC), (8, 64)),
+    "ragged": (dict(input_size=40, output_size=7, quantity=100, **STATIC), (3, 11)),
+    "wide_128": (dict(input_size=128, quantity=96, **STATIC), (2, 37)),
+    "projected_qk": (dict(input_size=24, hidden_size=40, pattern_size=48, output_size=10, quantity=90), (3, 13)),
+    "no_out_proj": (dict(input_size=32, quantity=64, disable_out_projection=True, **STATIC), (2, 9)),
+    "no_layernorm": (dict(input_size=32, quantity=64, normalize_stored_pattern=False,
+                          normalize_state_pattern=False, normalize_pattern_projection=False, **STATIC), (2, 9)),
+    "separate_targets": (dict(input_size=32, quantity=64, lookup_weights_as_separated=True, **STATIC), (2, 9)),
+}
+
+
+@pytest.mark.parametrize("name", list(BWD_CASES))
+def test_backward_parity(hf, name):
+    """Gradients of every parameter and of the input vs the oracle's autograd (T = 0)."""
+    kw, (b, l) = BWD_CASES[name]
+    ref, dut = make_pair(hf, seed=51, **kw)
+    g = torch.Generator().manual_seed(52)
+    x = torch.randn(b, l, kw["input_size"], generator=g)
+    xr = x.clone().requires_grad_(True)
+    xd = x.cuda().requires_grad_(True)
+    yr = ref(xr)
+    w = torch.randn(yr.shape, generator=g)
+    (yr * w).sum().backward()
+    yd = dut(xd)
+    assert rel_l2(yd.detach(), yr.detach()) < FP32_BAR
+    (yd * w.cuda()).sum().backward()
+    torch.cuda.synchronize()
+    worst = rel_l2(xd.grad, xr.grad)
+    print(f"{name}: d_x rel-L2 {worst:.3e}")
+    assert worst < 1e-4
+    rp, dp = dict(ref.named_parameters()), dict(dut.named_parameters())
+    assert set(rp) == set(dp)
+    for k in rp:
+        assert dp[k].grad is not None, k
+        r = rel_l2(dp[k].grad, rp[k].grad)
+        print(f"{name}: {k} rel-L2 {r:.3e}")
+        assert r < 1e-4, k
+
+
+def test_training_step_matches_oracle(ckpt_models):
+    """fwd + bwd through the whole harness model (main.py:26-36's step): loss and lookup grads."""
+    ref, dut = ckpt_models
+    ref.train(); dut.train()
+    try:
+        x = H.stroke_batch(8)
+        for m, xx in ((ref, x), (dut, x.cuda())):
+            m.zero_grad(set_to_none=True)
+            xr, aux = m(xx)
+            (F.mse_loss(xr, xx) + aux).backward()
+        for name in ("hopfield", "embedding_to_index", "index_to_embedding"):
+            gr = getattr(ref, name).lookup_weights.grad
+            gd = getattr(dut, name).lookup_weights.grad
+            r = rel_l2(gd, gr)
+            print(f"{name}.lookup_weights.grad rel-L2 {r:.3e}")
+            assert r < REL_L2_BAR
+        r = rel_l2(dut.encoder.conv_1.weight.grad, ref.encoder.conv_1.weight.grad)
+        print(f"encoder.conv_1.weight.grad rel-L2 {r:.3e}")
+        assert r < 5e-3
+    finally:
+        ref.eval(); dut.eval()
+
+
+# ----------------------------------------------------------------------------- sharded merge on one GPU
+@pytest.mark.parametrize("G", [2, 8])
+def test_pattern_sharded_merge_single_gpu(hf, G):
+    """G pattern shards evaluated one after another on one GPU + the library's LSE merge == unsharded."""
+    impl = hf._impl
+    kw = dict(input_size=64, quantity=512, disable_out_projection=True, **STATIC)
+    ref, dut = make_pair(hf, seed=61, **kw)
+    x = torch.randn(300, 64, generator=torch.Generator().manual_seed(62))
+    with torch.no_grad():
+        want = ref(x)
+        _, _, scores, _ = ref(x, return_details=True)
+    spec = dut.spec()
+    pack = dut.param_pack()
+    per = 512 // G
+    outs, lses, maxs, args = [], [], [], []
+    with torch.no_grad():
+        for gidx in range(G):
+            sl = slice(gidx * per, (gidx + 1) * per)
+            pats = impl.prepare_patterns_op(pack["lookup"][sl].contiguous(), None, pack["ln_stored_w"],
+                                            pack["ln_stored_b"], pack["ln_proj_w"], pack["ln_proj_b"], None, None,
+                                            pack["wv"], pack["bv"], spec.flags, impl.cabi.PATH_FP32_SIMT,
+                                            spec.d_assoc, spec.d_v, 0, spec.ln_eps)
+            res = impl.retrieve_op(x.cuda(), *pats, pack["ln_state_w"], pack["ln_state_b"], None, None, None, None,
+                                   spec.flags, impl.cabi.PATH_FP32_SIMT, spec.d_in, spec.d_out, 0, spec.beta,
+                                   spec.ln_eps, gidx * per)
+            outs.append(res[1]); lses.append(res[3]); args.append(res[4]); maxs.append(res[5])
+        lse_all, max_all, arg_all = torch.stack(lses), torch.stack(maxs), torch.stack(args)
+        total = torch.zeros_like(outs[0])
+        for gidx in range(G):
+            from hop_vae_b200.ops import merge_shards
+            lse, arg = merge_shards(outs[gidx], lse_all, max_all, arg_all, gidx)
+            total += outs[gidx]
+    assert rel_l2(total, want) < FP32_BAR
+    s = scores.reshape(-1, 512)
+    assert torch.equal(arg.cpu().long(), s.argmax(-1))
+    assert rel_l2(lse, torch.logsumexp(s, -1)) < 1e-5
