@@ -170,7 +170,8 @@ def test_checkpoint_golden_parity(ckpt_models, tag):
         print(f"{tag} {k}: rel-L2 {r:.3e}")
         assert r < REL_L2_BAR
     # quantised indices feed the third layer: identical levels are required for identical latents
-    assert (b["idx"].cpu().numpy() == g[f"{tag}_idx"]).mean() > 0.9995
+    # (levels compared as integers: torch's CUDA `x / 511` multiplies by a reciprocal, 1 ulp off the CPU's division)
+    assert (np.rint(b["idx"].cpu().numpy() * 511) == np.rint(g[f"{tag}_idx"] * 511)).mean() > 0.9995
     for n, a in am.items():
         same = (a == g[f"{tag}_argmax_{n}"]).mean()
         print(f"{tag} argmax {n}: identical {same:.6f}")
