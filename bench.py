@@ -1,0 +1,378 @@
+#!/usr/bin/env python
+"""bench.py -- retrieved latents/sec of the fused Hopfield retrieval on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
+
+One "step" = one forward pass of the Hopfield association over one batch of synthetic queries
+(SURVEY.md section 8d).  Default workload = the smallest point of BASELINE.json config 5 (the one the
+"% of bf16 tensor peak" target is quoted on): N = 16,384 query rows per GPU, P = 65,536 stored
+patterns, D = Dv = 256, T = 0 extra update steps, beta = 1/sqrt(D).  With --gpus N the latent batch
+is data-parallel (every rank holds the patterns and its own N rows; no data-path collective; weak
+scaling).  Rank 0 prints ONE JSON line.
+
+`--impl reference` times the reference's own CPU path for the same metric on a bounded sample of
+the same workload: PyTorch-eager fp32 through the restated `hflayers` (oracle/; upstream
+hopfield-layers cannot be installed offline -- see DESIGN.md), all host threads.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (N rows per GPU, P patterns, D = Dv, T update steps)
+    "sweep_p64k_d256": (16384, 65536, 256, 0),
+    "sweep_p64k_d256_t1": (16384, 65536, 256, 1),
+    "sweep_p64k_d128": (16384, 65536, 128, 0),
+    "sweep_p64k_d64": (16384, 65536, 64, 0),
+    "sweep_p256k_d256": (16384, 262144, 256, 0),
+    "ffhq32_layer": (2592, 512, 64, 0),       # one `hopfield` layer of FFHQ-32 (launch-bound; context only)
+    "tiny": (1024, 4096, 64, 0),              # plumbing check
+}
+DEFAULT_WORKLOAD = "sweep_p64k_d256"
+METRIC = "retrieved latents/sec (Hopfield fwd, iters=cfg)"
+UNIT = "latents/s"
+
+
+def fwd_flops(n, p, d, dv, t):
+    """Algorithmic FLOPs of one forward: T+1 score GEMMs, T state updates, 1 read-out."""
+    return 2.0 * n * p * ((2 * t + 1) * d + dv)
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            j = json.load(f)
+        return dict(bf16_tflops=float(j["bf16_tflops"]), bf16_tflops_sustained=float(j.get("bf16_tflops_sustained", 0)),
+                    hbm_gbs=float(j["hbm_gbs"]), source="measured (MEASURED_PEAKS.json)")
+    return dict(bf16_tflops=1590.0, bf16_tflops_sustained=1400.0, hbm_gbs=6650.0,
+                source="fallback (B200_PROFILING.md)")
+
+
+def make_state(p, d, t, seed=1265):
+    """Synthetic config-5 layer: W ~ N(0,1), LN affine identity, Wv ~ N(0, 1/D)."""
+    import torch
+    g = torch.Generator().manual_seed(seed)
+    w = torch.randn(p, d, generator=g)
+    g2 = torch.Generator().manual_seed(seed + 1)
+    wv = torch.randn(d, d, generator=g2) / math.sqrt(d)
+    wo = torch.randn(d, d, generator=g2) / math.sqrt(d)
+    return w, wv, wo
+
+
+def make_queries(w, n, seed=1267):
+    import torch
+    g = torch.Generator().manual_seed(seed)
+    idx = torch.randint(0, w.shape[0], (n,), generator=g)
+    return w[idx] + 0.5 * torch.randn(n, w.shape[1], generator=g), idx
+
+
+def build_layer(cls, p, d, t, w, wv, wo):
+    import torch
+    layer = cls(input_size=d, quantity=p, stored_pattern_as_static=True, state_pattern_as_static=True,
+                update_steps_max=t)
+    with torch.no_grad():
+        layer.lookup_weights.copy_(w.unsqueeze(0))
+        core = layer.hopfield.association_core
+        core.in_proj_weight.copy_(wv)
+        core.in_proj_bias.zero_()
+        core.out_proj.weight.copy_(wo)
+        core.out_proj.bias.zero_()
+    return layer.eval()
+
+
+# ------------------------------------------------------------------------------------------ CPU arms
+def cpu_reference_run(n, p, d, t, steps, warmup, budget_s=12.0):
+    """Reference CPU path (restated hflayers, PyTorch eager fp32, all host threads) on a bounded sample
+    of the workload's query rows; returns (latents/s, sample description, cores, ms per step, rows)."""
+    import torch
+    from oracle import hflayers_oracle as O          # checker / CPU baseline only
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    w, wv, wo = make_state(p, d, t)
+    layer = build_layer(O.HopfieldLayer, p, d, t, w, wv, wo)
+    # size the sample: probe with 64 rows, then scale to about budget_s of total CPU work
+    xq, _ = make_queries(w, min(n, 4096))
+    with torch.no_grad():
+        t0 = time.perf_counter(); layer(xq[:64]); probe = time.perf_counter() - t0
+        t0 = time.perf_counter(); layer(xq[:64]); probe = min(probe, time.perf_counter() - t0)
+    per_row = probe / 64
+    total_steps = max(1, steps + warmup)
+    rows = int(max(64, min(xq.shape[0], budget_s / total_steps / max(per_row, 1e-9))))
+    x = xq[:rows].contiguous()
+    with torch.no_grad():
+        for _ in range(warmup):
+            layer(x)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            layer(x)
+        dt = time.perf_counter() - t0
+    ms = dt / steps * 1e3
+    sample = (f"{rows} of {n} query rows per step, all P={p} patterns, D={d}, T={t}; oracle restatement of hflayers "
+              f"(upstream hopfield-layers not installable offline), torch eager fp32, {cores} threads")
+    return rows * steps / dt, sample, cores, ms, rows
+
+
+class ClockSampler:
+    """Samples nvidia-smi SM clocks / throttle reasons while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thr = threading.Thread(target=self._read, daemon=True)
+            self.thr.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [s.strip() for s in ln.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------ GPU arm
+class RawForward:
+    """Direct C-ABI call (include/hop_sm100.h) of the association without out_proj on preallocated
+    buffers: isolates the fused retrieval kernel for the roofline timing."""
+
+    def __init__(self, impl, layer, x_dev, path):
+        import ctypes as C
+        import torch
+        cabi = impl.cabi
+        self.C, self.cabi, self.lib = C, cabi, cabi.load()
+        spec = layer.spec()
+        n, p = x_dev.shape[0], layer.quantity
+        flags = spec.flags & ~cabi.F_OUT_PROJ
+        self.desc = cabi.make_desc(flags=flags, path=path, n_rows=n, n_patterns=p, d_in=spec.d_in,
+                                   d_assoc=spec.d_assoc, d_v=spec.d_v, d_out=1, update_steps=spec.update_steps,
+                                   beta=spec.beta, ln_eps=spec.ln_eps)
+        pack = layer.param_pack()
+        self.keep = pack
+        self.pats_t = layer._prepared(pack, spec, path)
+        khat, vhat, k16, kt16, vt16 = self.pats_t
+        dev = x_dev.device
+        self.x = x_dev
+        self.out = torch.empty((n, spec.d_v), device=dev)
+        self.lse = torch.empty((n,), device=dev)
+        self.rowmax = torch.empty((n,), device=dev)
+        self.argmax = torch.empty((n,), device=dev, dtype=torch.int32)
+        need = C.c_size_t(0)
+        cabi.check(self.lib.hop_sm100_workspace_bytes(C.byref(self.desc), 0, C.byref(need)), "workspace_bytes")
+        self.ws = torch.empty((max(int(need.value), 16),), device=dev, dtype=torch.uint8)
+        self.ws_bytes = int(need.value)
+        self.params = cabi.HopParams(ln_state_w=cabi.ptr(pack["ln_state_w"]), ln_state_b=cabi.ptr(pack["ln_state_b"]))
+        self.pats = cabi.HopPatterns(khat=cabi.ptr(khat), vhat=cabi.ptr(vhat),
+                                     k16=cabi.ptr(k16) if k16.numel() else None,
+                                     kt16=cabi.ptr(kt16) if kt16.numel() else None,
+                                     vt16=cabi.ptr(vt16) if vt16.numel() else None)
+
+    def __call__(self):
+        import torch
+        C, cabi = self.C, self.cabi
+        st = torch.cuda.current_stream().cuda_stream
+        cabi.check(self.lib.hop_sm100_forward(C.byref(self.desc), C.byref(self.params), C.byref(self.pats),
+                                              cabi.ptr(self.x), cabi.ptr(self.out), None, None, cabi.ptr(self.lse),
+                                              cabi.ptr(self.argmax), cabi.ptr(self.rowmax), cabi.ptr(self.ws),
+                                              self.ws_bytes, st), "hop_sm100_forward")
+
+
+def timed_steps(fn, steps, flush, torch):
+    """Runs fn() `steps` times, L2 flushed (outside the timed events) before each; returns per-step ms."""
+    evs = []
+    for _ in range(steps):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        evs.append((e0, e1))
+    torch.cuda.synchronize()
+    return [a.elapsed_time(b) for a, b in evs]
+
+
+def gpu_run(args):
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the Hopfield retrieval op is sm_100a only; no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    import hflayers
+    impl = hflayers._impl
+    cabi = impl.cabi
+    cabi.load()
+    n, p, d, t = WORKLOADS[args.workload]
+    w, wv, wo = make_state(p, d, t)
+    layer = build_layer(hflayers.HopfieldLayer, p, d, t, w, wv, wo).to(dev)
+    layer.kernel_path = args.path
+    x_host, _ = make_queries(w, n, seed=1267 + rank)
+    x_host = x_host.contiguous().pin_memory()
+    out_host = torch.empty((n, d), dtype=torch.float32).pin_memory()
+    x_dev = x_host.to(dev)
+    x_stage = torch.empty_like(x_dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    path = impl.resolve_path(layer.spec(), n, p)
+    raw = RawForward(impl, layer, x_dev, path)
+
+    def step_dev():
+        with torch.no_grad():
+            return layer(x_dev)
+
+    def step_e2e():
+        with torch.no_grad():
+            x_stage.copy_(x_host, non_blocking=True)
+            y = layer(x_stage)
+            out_host.copy_(y.reshape(n, d), non_blocking=True)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        tt = torch.tensor([v], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        return float(tt.item())
+
+    for _ in range(max(args.warmup, 3)):
+        step_dev(); raw(); step_e2e()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = cabi.launch_count()
+    barrier()
+    ms_steps = timed_steps(step_dev, args.steps, flush, torch)
+    barrier()
+    launches = cabi.launch_count() - l0
+    ms_total = max_over_ranks(sum(ms_steps))
+    ms_kernel = timed_steps(raw, args.steps, flush, torch)
+    barrier()
+    ms_e2e_total = max_over_ranks(sum(timed_steps(step_e2e, args.steps, flush, torch)))
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+
+    if rank == 0:
+        pk = peaks()
+        ms_step = ms_total / args.steps
+        value = world * n * args.steps / (ms_total * 1e-3)
+        e2e = world * n * args.steps / (ms_e2e_total * 1e-3)
+        k_ms = sum(ms_kernel) / len(ms_kernel)
+        fl = fwd_flops(n, p, d, d, t)
+        achieved = fl / (k_ms * 1e-3) / 1e12
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": {1: "f32", 2: "f16", 3: "bf16"}[path] + " operands, f32 accumulate",
+            "data": "synthetic (config-5 recipe, SURVEY.md 8d; seeds 1265/1266/1267+rank)",
+            "config": {"workload": args.workload, "rows_per_gpu": n, "patterns": p, "dim": d, "update_steps": t,
+                       "beta": 1.0 / math.sqrt(d), "parallelism": f"batch-dp{world}", "kernel_path":
+                       {1: "fp32_simt", 2: "tc_f16", 3: "tc_bf16"}[path],
+                       "l2": "flushed between timed steps (256 MiB memset outside the events)"},
+            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": x_host.numel() * 4,
+                    "d2h_bytes_per_step": out_host.numel() * 4},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "tensor", "achieved": achieved, "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
+                         "frac": achieved / pk["bf16_tflops"], "traffic": None,
+                         "kernel_ms": k_ms, "algorithmic_flops": fl, "peak_source": pk["source"],
+                         "frac_of_sustained": (achieved / pk["bf16_tflops_sustained"]) if pk["bf16_tflops_sustained"] else None},
+            "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            v, sample, cores, ms, rows = cpu_reference_run(n, p, d, t, steps=2, warmup=1, budget_s=15.0)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def reference_run(args):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if rank != 0:
+        return
+    n, p, d, t = WORKLOADS[args.workload]
+    v, sample, cores, ms, rows = cpu_reference_run(n, p, d, t, steps=args.steps, warmup=args.warmup, budget_s=60.0)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic (config-5 recipe, SURVEY.md 8d)",
+        "config": {"workload": args.workload, "rows_per_gpu": n, "patterns": p, "dim": d, "update_steps": t,
+                   "beta": 1.0 / math.sqrt(d), "parallelism": "host cores", "sample_rows_per_step": rows},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--path", default="auto", choices=["auto", "fp32", "f16", "bf16"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    if args.impl == "reference":
+        reference_run(args)
+    else:
+        gpu_run(args)
+
+
+if __name__ == "__main__":
+    main()

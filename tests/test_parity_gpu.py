@@ -230,6 +230,13 @@ def test_backward_parity(hf, name):
     assert set(rp) == set(dp)
     for k in rp:
         assert dp[k].grad is not None, k
+        if k.endswith("norm_stored_pattern.bias"):
+            # softmax is shift-invariant: a bias added to every K^ row moves all scores of a query row by
+            # the same amount, so this gradient is exactly 0 in exact arithmetic; both sides hold only
+            # rounding noise.  Bound it absolutely against the scale of the matching weight gradient.
+            scale = float(rp[k.replace(".bias", ".weight")].grad.norm())
+            assert float(dp[k].grad.norm()) < 1e-4 * scale and float(rp[k].grad.norm()) < 1e-4 * scale, k
+            continue
         r = rel_l2(dp[k].grad, rp[k].grad)
         print(f"{name}: {k} rel-L2 {r:.3e}")
         assert r < 1e-4, k
