@@ -132,6 +132,10 @@ int hop_sm100_workspace_bytes(const hop_desc* desc, int for_backward, size_t* by
   } else {
     // two ping-pong query-state buffers (N,H) + one read-out buffer (N,Dv), each 256-byte aligned
     *bytes = 2 * round_up_sz(N * desc->d_assoc * sizeof(float), 256) + round_up_sz(N * desc->d_v * sizeof(float), 256);
+    const int path = resolve_path(desc);
+    if (path < 0) return -path;
+    if (path != HOP_PATH_FP32_SIMT)  // partial results of the intra-GPU pattern splits
+      *bytes += tc_forward_workspace(desc->n_rows, desc->n_patterns, desc->d_assoc, desc->update_steps);
   }
   return HOP_OK;
 }
@@ -171,7 +175,9 @@ int hop_sm100_forward(const hop_desc* desc, const hop_params* params, const hop_
   HOP_TRY(hop_sm100_workspace_bytes(desc, 0, &need));
   const bool out_proj = (d.flags & HOP_F_OUT_PROJ) != 0;
   const bool q_proj = (d.flags & HOP_F_PROJ_STATE) != 0;
-  const bool need_ws = q_proj || d.update_steps > 0 || (path != HOP_PATH_FP32_SIMT && out_proj && !retrieved);
+  const size_t tc_ws = (path != HOP_PATH_FP32_SIMT) ? tc_forward_workspace(d.n_rows, d.n_patterns, d.d_assoc, d.update_steps) : 0;
+  const bool need_ws = q_proj || (path == HOP_PATH_FP32_SIMT && d.update_steps > 0) || tc_ws > 0 ||
+                       (path != HOP_PATH_FP32_SIMT && out_proj && !retrieved);
   if (need_ws && (!workspace || workspace_bytes < need))
     HOP_FAIL(HOP_ERR_WORKSPACE, "workspace of %zu bytes needed, %zu given", need, workspace_bytes);
   if (out_proj && (!p.wo)) HOP_FAIL(HOP_ERR_BAD_ARG, "HOP_F_OUT_PROJ set but params.wo is NULL");
@@ -228,6 +234,9 @@ int hop_sm100_forward(const hop_desc* desc, const hop_params* params, const hop_
   a.bf16 = (path == HOP_PATH_TC_BF16);
   a.retrieved = out_proj ? (retrieved ? retrieved : rbuf) : out;
   a.qsave = qhat; a.lse = lse; a.argmax = argmax; a.rowmax = rowmax; a.pattern_offset = d.pattern_offset;
+  a.ws = workspace ? static_cast<char*>(workspace) + 2 * qbytes + round_up_sz((size_t)d.n_rows * d.d_v * sizeof(float), 256)
+                   : nullptr;
+  a.ws_bytes = tc_ws;
   HOP_TRY(launch_tc_forward(a, st));
   if (out_proj) HOP_TRY(launch_linear(d.n_rows, d.d_v, d.d_out, a.retrieved, p.wo, p.bo, out, st));
   else if (retrieved && retrieved != out)

@@ -96,7 +96,10 @@ struct TcPassArgs {
   float* retrieved;         // (N,Dv)
   float* qsave;             // (N,H) or nullptr
   float* lse; int32_t* argmax; float* rowmax; int pattern_offset;
+  void* ws; size_t ws_bytes;   // partial results of the pattern splits (tc_forward_workspace bytes)
 };
+int tc_choose_splits(int n, int p, int update_steps);
+size_t tc_forward_workspace(int n, int p, int d, int update_steps);
 int launch_tc_forward(const TcPassArgs& a, cudaStream_t st);
 bool tc_supported(int h, int dv);
 // hop_merge.cu

@@ -1,6 +1,637 @@
-// placeholder, replaced below
+// Fused Hopfield retrieval forward on the sm_100a tensor pipe (tcgen05 + TMEM + TMA).
+//
+// Replaces, in one launch, upstream hflayers `hopfield_core_forward` as reached from
+// `HopfieldLayer.forward` (call sites /root/reference/HopVAE.py:193,215,216,234,255,257,271):
+// LN_q + beta, score contraction, row softmax, T retrieve updates, pattern read-out.  The N x P
+// score matrix lives only in TMEM / registers / shared memory.
+//
+// One CTA owns 128 query rows for all T+1 passes and, optionally, one of `splits` contiguous
+// pattern ranges (flash-decoding style; partials are combined by tc_combine_kernel).
+//   warp 0      TMA producer: ring of 16 KiB operand chunks (K^ rows for the score MMA, then
+//               V^T / K^T rows for the read-out MMA), 128-byte swizzle, mbarrier-tracked
+//   warp 1      MMA issuer (one elected lane): S = Q K^T into a double-buffered TMEM tile,
+//               O += P~ B into TMEM columns [256, 256+Dr)
+//   warps 2..5  softmax: tcgen05.ld S, online max / lazy rescale, ex2, 16-bit P~ into swizzled
+//               shared memory, epilogue (O / l -> HBM, or -> next pass' Q tile in smem)
+#include <cuda.h>
+
+#include <cstdlib>
+#include <mutex>
+
 #include "hop_common.cuh"
+#include "hop_tc_ptx.cuh"
+
 namespace hop {
-bool tc_supported(int h, int dv) { (void)h; (void)dv; return false; }
-int launch_tc_forward(const TcPassArgs& a, cudaStream_t st) { (void)a; (void)st; HOP_FAIL(HOP_ERR_UNSUPPORTED, "tensor-core path not built"); }
+
+namespace {
+
+constexpr int kTileM = 128;          // query rows per CTA (TMEM lanes)
+constexpr int kTileP = 128;          // patterns per score tile
+constexpr int kChunkBytes = 16384;   // 128 rows x 64 16-bit elements, 128B-swizzled
+constexpr int kThreads = 192;
+constexpr int kSoftmaxThreads = 128;
+constexpr uint32_t kTmemCols = 512;
+constexpr uint32_t kTmemO = 256;     // O accumulator starts after the two S buffers
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+constexpr float kRescaleThreshold = 8.f;   // log2 units: P~ <= 2^8, safe in fp16 / bf16
+
+template <int D>
+struct TcCfg {
+  static constexpr int kKChunks = D / 64;                 // 64-wide K chunks of the Q / K^ tiles
+  static constexpr int kBRows = D < 128 ? D : 128;        // read-out chunk rows (N of the PV MMA)
+  static constexpr int kDHalves = D / kBRows;             // read-out column groups
+  static constexpr int kQBytes = kKChunks * kChunkBytes;  // Q tile
+  static constexpr int kPBytes = 2 * kChunkBytes;         // one P~ buffer (128 x 128 x 2B)
+  static constexpr int kStages = (D >= 256) ? 6 : 8;
+  static constexpr int kSmemBytes = 1024 /*align slack*/ + kQBytes + 2 * kPBytes + kStages * kChunkBytes + 256;
+};
+
+struct TcKernelArgs {
+  const float* x_raw; const float* lnq_w; const float* lnq_b; float ln_eps; int has_ln; float beta;
+  const float* qs;
+  int n, p, update_steps, bf16;
+  int splits, tiles_per_split;          // pattern tiles (of 128) handled by one CTA
+  float* retrieved; float* qsave; float* lse; int32_t* argmax; float* rowmax; int pattern_offset;
+  // partial outputs when splits > 1: (splits, N, D), (splits, N) x3
+  float* part_o; float* part_lse; float* part_max; int32_t* part_arg;
+};
+
+__device__ __forceinline__ uint32_t pack16(float a, float b, int bf16) {
+  if (bf16) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&v);
+  }
+  __half2 v = __floats2half2_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
 }
+
+// Byte offset of 16-byte chunk `c16` (0..7) of row `r` inside a 128B-swizzled [rows x 64] tile.
+__device__ __forceinline__ uint32_t sw128_off(int r, int c16) {
+  return (uint32_t)(r * 128 + ((c16 ^ (r & 7)) << 4));
+}
+
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
+template <int D>
+__global__ void __launch_bounds__(kThreads, 1)
+hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_kt,
+                  const __grid_constant__ CUtensorMap tm_vt, const TcKernelArgs a) {
+  using Cfg = TcCfg<D>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t q_smem = smem_base;
+  const uint32_t p_smem = q_smem + Cfg::kQBytes;
+  const uint32_t ring = p_smem + 2 * Cfg::kPBytes;
+  const uint32_t bars = ring + Cfg::kStages * kChunkBytes;
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (Cfg::kStages + s); };
+  const uint32_t misc = bars + 16u * Cfg::kStages;
+  auto s_full = [&](int b) { return misc + 8u * b; };
+  auto s_empty = [&](int b) { return misc + 16u + 8u * b; };
+  auto p_full = [&](int b) { return misc + 32u + 8u * b; };
+  auto p_empty = [&](int b) { return misc + 48u + 8u * b; };
+  const uint32_t q_ready = misc + 64u;
+  const uint32_t tmem_slot = misc + 72u;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int split = blockIdx.y;
+  const int nt_total = (a.p + kTileP - 1) / kTileP;
+  const int t0 = split * a.tiles_per_split;
+  const int nt = min(a.tiles_per_split, nt_total - t0);
+  const int passes = a.update_steps + 1;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < Cfg::kStages; ++s) { ptx::mbar_init(full_bar(s), 1); ptx::mbar_init(empty_bar(s), 1); }
+    for (int b = 0; b < 2; ++b) {
+      ptx::mbar_init(s_full(b), 1); ptx::mbar_init(s_empty(b), kSoftmaxThreads);
+      ptx::mbar_init(p_full(b), kSoftmaxThreads); ptx::mbar_init(p_empty(b), 1);
+    }
+    ptx::mbar_init(q_ready, kSoftmaxThreads);
+    ptx::fence_barrier_init();
+    ptx::prefetch_tmap(&tm_k); ptx::prefetch_tmap(&tm_kt); ptx::prefetch_tmap(&tm_vt);
+  }
+  if (warp == 0) {
+    __syncwarp();
+    ptx::tmem_alloc(tmem_slot, kTmemCols);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer
+    if (ptx::elect_one()) {
+      uint32_t it = 0;
+      auto produce = [&](const CUtensorMap* m, int c0, int c1, uint32_t bytes) {
+        const int s = it % Cfg::kStages;
+        ptx::mbar_wait(empty_bar(s), ((it / Cfg::kStages) & 1) ^ 1);
+        ptx::mbar_arrive_expect_tx(full_bar(s), bytes);
+        ptx::tma_load_2d(ring + s * kChunkBytes, m, full_bar(s), c0, c1);
+        ++it;
+      };
+      for (int pass = 0; pass < passes; ++pass) {
+        const CUtensorMap* bm = (pass < a.update_steps) ? &tm_kt : &tm_vt;
+        auto load_k = [&](int tile) {
+          for (int kc = 0; kc < Cfg::kKChunks; ++kc) produce(&tm_k, kc * 64, tile * kTileP, kChunkBytes);
+        };
+        auto load_b = [&](int tile) {
+          for (int kc = 0; kc < 2; ++kc)
+            for (int dh = 0; dh < Cfg::kDHalves; ++dh)
+              produce(bm, tile * kTileP + kc * 64, dh * Cfg::kBRows, Cfg::kBRows * 128);
+        };
+        load_k(t0);
+        for (int j = 0; j < nt; ++j) {
+          if (j + 1 < nt) load_k(t0 + j + 1);
+          load_b(t0 + j);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // -------------------------------------------------------------- MMA issuer
+    if (ptx::elect_one()) {
+      const int fmt = a.bf16 ? 1 : 0;
+      const uint32_t idesc_qk = ptx::umma_idesc_f16(kTileM, kTileP, fmt);
+      const uint32_t idesc_pv = ptx::umma_idesc_f16(kTileM, Cfg::kBRows, fmt);
+      uint32_t it = 0, g = 0;
+      for (int pass = 0; pass < passes; ++pass) {
+        ptx::mbar_wait(q_ready, pass & 1);
+        ptx::tc_fence_after();
+        auto issue_qk = [&](uint32_t gg) {
+          const int b = gg & 1;
+          ptx::mbar_wait(s_empty(b), ((gg >> 1) & 1) ^ 1);
+          ptx::tc_fence_after();
+          for (int kc = 0; kc < Cfg::kKChunks; ++kc) {
+            const int s = it % Cfg::kStages;
+            ptx::mbar_wait(full_bar(s), (it / Cfg::kStages) & 1);
+            ptx::tc_fence_after();
+            const uint64_t ad = ptx::umma_desc_sw128(q_smem + kc * kChunkBytes);
+            const uint64_t bd = ptx::umma_desc_sw128(ring + s * kChunkBytes);
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              ptx::umma_f16_ss(tmem_base + b * kTileP, ad + 2 * k, bd + 2 * k, idesc_qk, (kc | k) != 0);
+            ptx::umma_commit(empty_bar(s));
+            ++it;
+          }
+          ptx::umma_commit(s_full(b));
+        };
+        issue_qk(g);
+        for (int j = 0; j < nt; ++j) {
+          if (j + 1 < nt) issue_qk(g + j + 1);
+          const uint32_t gg = g + j;
+          const int b = gg & 1;
+          ptx::mbar_wait(p_full(b), (gg >> 1) & 1);
+          ptx::tc_fence_after();
+          for (int kc = 0; kc < 2; ++kc) {
+            for (int dh = 0; dh < Cfg::kDHalves; ++dh) {
+              const int s = it % Cfg::kStages;
+              ptx::mbar_wait(full_bar(s), (it / Cfg::kStages) & 1);
+              ptx::tc_fence_after();
+              const uint64_t ad = ptx::umma_desc_sw128(p_smem + b * Cfg::kPBytes + kc * kChunkBytes);
+              const uint64_t bd = ptx::umma_desc_sw128(ring + s * kChunkBytes);
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                ptx::umma_f16_ss(tmem_base + kTmemO + dh * Cfg::kBRows, ad + 2 * k, bd + 2 * k, idesc_pv,
+                                 (j | kc | k) != 0);
+              ptx::umma_commit(empty_bar(s));
+              ++it;
+            }
+          }
+          ptx::umma_commit(p_empty(b));
+        }
+        g += nt;
+      }
+    }
+    __syncwarp();
+  } else {
+    // ------------------------------------------------------ softmax / epilogue
+    const int wq = warp & 3;                      // TMEM lane quarter this warp may access
+    const int row = wq * 32 + lane;               // row of the tile owned by this thread
+    const long long grow = (long long)blockIdx.x * kTileM + row;
+    const uint32_t lane_base = tmem_base + ((uint32_t)(wq * 32) << 16);
+    const bool row_ok = grow < a.n;
+    const float qscale = a.beta;                  // natural-units scale of the state pattern
+
+    // ---- pass-0 Q tile: one warp per row, coalesced; LN_q + beta, fp32 qsave, 16-bit swizzled smem
+    {
+      constexpr int kVec = (D + 127) / 128;       // float4 per lane
+      float4 w4[kVec], b4[kVec];
+#pragma unroll
+      for (int v = 0; v < kVec; ++v) {
+        const int e = lane * 4 + v * 128;
+        w4[v] = make_float4(1.f, 1.f, 1.f, 1.f);
+        b4[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (e < D && a.x_raw && a.has_ln) {
+          if (a.lnq_w) w4[v] = *reinterpret_cast<const float4*>(a.lnq_w + e);
+          if (a.lnq_b) b4[v] = *reinterpret_cast<const float4*>(a.lnq_b + e);
+        }
+      }
+      const float* src = a.x_raw ? a.x_raw : a.qs;
+      for (int rr = 0; rr < 32; ++rr) {
+        const int r = wq * 32 + rr;
+        const long long gr = (long long)blockIdx.x * kTileM + r;
+        float4 xv[kVec];
+#pragma unroll
+        for (int v = 0; v < kVec; ++v) {
+          const int e = lane * 4 + v * 128;
+          xv[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (e < D && gr < a.n) xv[v] = *reinterpret_cast<const float4*>(src + gr * D + e);
+        }
+        if (a.x_raw) {
+          if (a.has_ln) {
+            float s = 0.f;
+#pragma unroll
+            for (int v = 0; v < kVec; ++v) s += (xv[v].x + xv[v].y) + (xv[v].z + xv[v].w);
+            const float mean = warp_sum(s) * (1.f / D);
+            float q = 0.f;
+#pragma unroll
+            for (int v = 0; v < kVec; ++v) {
+              const int e = lane * 4 + v * 128;
+              if (e < D) {
+                xv[v].x -= mean; xv[v].y -= mean; xv[v].z -= mean; xv[v].w -= mean;
+                q += xv[v].x * xv[v].x + xv[v].y * xv[v].y + xv[v].z * xv[v].z + xv[v].w * xv[v].w;
+              }
+            }
+            const float rstd = rsqrtf(warp_sum(q) * (1.f / D) + a.ln_eps);
+#pragma unroll
+            for (int v = 0; v < kVec; ++v) {
+              xv[v].x = xv[v].x * rstd * w4[v].x + b4[v].x; xv[v].y = xv[v].y * rstd * w4[v].y + b4[v].y;
+              xv[v].z = xv[v].z * rstd * w4[v].z + b4[v].z; xv[v].w = xv[v].w * rstd * w4[v].w + b4[v].w;
+            }
+          }
+#pragma unroll
+          for (int v = 0; v < kVec; ++v) { xv[v].x *= qscale; xv[v].y *= qscale; xv[v].z *= qscale; xv[v].w *= qscale; }
+        }
+#pragma unroll
+        for (int v = 0; v < kVec; ++v) {
+          const int e = lane * 4 + v * 128;
+          if (e < D) {
+            if (a.qsave && a.update_steps == 0 && gr < a.n && split == 0)
+              *reinterpret_cast<float4*>(a.qsave + gr * D + e) = xv[v];
+            const uint32_t lo = pack16(xv[v].x * kLog2e, xv[v].y * kLog2e, a.bf16);
+            const uint32_t hi = pack16(xv[v].z * kLog2e, xv[v].w * kLog2e, a.bf16);
+            const uint32_t addr = q_smem + (e >> 6) * kChunkBytes + sw128_off(r, (e & 63) >> 3) + ((e & 4) << 1);
+            asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr), "r"(lo), "r"(hi) : "memory");
+          }
+        }
+      }
+    }
+
+    uint32_t g = 0;
+    for (int pass = 0; pass < passes; ++pass) {
+      ptx::fence_proxy_async_smem();
+      ptx::mbar_arrive(q_ready);
+
+      float m_run = -INFINITY, l = 0.f, tmax = -INFINITY;
+      int targ = 0;
+      for (int j = 0; j < nt; ++j) {
+        const uint32_t gg = g + j;
+        const int b = gg & 1;
+        const int col0 = (t0 + j) * kTileP;           // global pattern index of the tile's column 0
+        const int valid = a.p - col0;                 // columns >= valid are padding
+        ptx::mbar_wait(s_full(b), (gg >> 1) & 1);
+        ptx::tc_fence_after();
+        const uint32_t s_addr = lane_base + b * kTileP;
+
+        // pass A: tile max (+ nearest-pattern index)
+        float cmax = -INFINITY;
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+          uint32_t v[32];
+          ptx::tmem_ld_x32(s_addr + c * 32, v);
+          ptx::tmem_wait_ld();
+          float cm = -INFINITY;
+          if (valid >= (c + 1) * 32) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) cm = fmaxf(cm, __uint_as_float(v[i]));
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              if (c * 32 + i >= valid) v[i] = __float_as_uint(-INFINITY);
+              cm = fmaxf(cm, __uint_as_float(v[i]));
+            }
+          }
+          if (cm > tmax) {
+            int idx = 31;
+#pragma unroll
+            for (int i = 31; i >= 0; --i) idx = (__uint_as_float(v[i]) == cm) ? i : idx;
+            tmax = cm;
+            targ = col0 + c * 32 + idx;
+          }
+          cmax = fmaxf(cmax, cm);
+        }
+
+        // lazy rescale of (l, O): only when some row of the warp outgrew its reference max by 2^8
+        const bool need = cmax > m_run + kRescaleThreshold;
+        if (__any_sync(0xffffffffu, need)) {
+          const float m_new = fmaxf(m_run, cmax);
+          if (j > 0) {
+            const uint32_t pg = gg - 1;
+            ptx::mbar_wait(p_empty(pg & 1), (pg >> 1) & 1);   // read-out MMA of the previous tile done
+            ptx::tc_fence_after();
+            const float f = ptx::ex2(m_run - m_new);
+            l *= f;
+#pragma unroll 1
+            for (int c = 0; c < D / 32; ++c) {
+              uint32_t v[32];
+              ptx::tmem_ld_x32(lane_base + kTmemO + c * 32, v);
+              ptx::tmem_wait_ld();
+#pragma unroll
+              for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * f);
+              ptx::tmem_st_x32(lane_base + kTmemO + c * 32, v);
+            }
+            ptx::tmem_wait_st();
+          }
+          m_run = m_new;
+        }
+
+        // pass B: P~ = 2^(s - m_run) as 16-bit into the swizzled A-operand buffer
+        ptx::mbar_wait(p_empty(b), ((gg >> 1) & 1) ^ 1);
+        const uint32_t p_addr = p_smem + b * Cfg::kPBytes;
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+          uint32_t v[32];
+          ptx::tmem_ld_x32(s_addr + c * 32, v);
+          ptx::tmem_wait_ld();
+          uint32_t pk[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            float p0 = ptx::ex2(__uint_as_float(v[2 * i]) - m_run);
+            float p1 = ptx::ex2(__uint_as_float(v[2 * i + 1]) - m_run);
+            if (c * 32 + 2 * i >= valid) p0 = 0.f;
+            if (c * 32 + 2 * i + 1 >= valid) p1 = 0.f;
+            l += p0 + p1;
+            pk[i] = pack16(p0, p1, a.bf16);
+          }
+          const uint32_t base = p_addr + (c >> 1) * kChunkBytes;
+#pragma unroll
+          for (int q4 = 0; q4 < 4; ++q4)
+            st_shared_v4(base + sw128_off(row, (c & 1) * 4 + q4), pk[4 * q4], pk[4 * q4 + 1], pk[4 * q4 + 2],
+                         pk[4 * q4 + 3]);
+        }
+        ptx::tc_fence_before();
+        ptx::mbar_arrive(s_empty(b));
+        ptx::fence_proxy_async_smem();
+        ptx::mbar_arrive(p_full(b));
+      }
+
+      // ---- epilogue of the pass: wait for the last read-out MMA, normalise
+      const uint32_t last = g + nt - 1;
+      ptx::mbar_wait(p_empty(last & 1), (last >> 1) & 1);
+      ptx::tc_fence_after();
+      const float inv = 1.f / l;
+      if (pass < a.update_steps) {
+        // retrieve update: q <- beta * (A K^) becomes the next pass' Q tile (never leaves the SM)
+        const bool save = (pass == a.update_steps - 1) && a.qsave && row_ok;
+        const float sc = inv * qscale;
+#pragma unroll 1
+        for (int c = 0; c < D / 32; ++c) {
+          uint32_t v[32];
+          ptx::tmem_ld_x32(lane_base + kTmemO + c * 32, v);
+          ptx::tmem_wait_ld();
+          uint32_t pk[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const float q0 = __uint_as_float(v[2 * i]) * sc, q1 = __uint_as_float(v[2 * i + 1]) * sc;
+            v[2 * i] = __float_as_uint(q0); v[2 * i + 1] = __float_as_uint(q1);
+            pk[i] = pack16(q0 * kLog2e, q1 * kLog2e, a.bf16);
+          }
+          if (save) {
+            float4* dst = reinterpret_cast<float4*>(a.qsave + grow * D + c * 32);
+#pragma unroll
+            for (int q4 = 0; q4 < 8; ++q4)
+              dst[q4] = make_float4(__uint_as_float(v[4 * q4]), __uint_as_float(v[4 * q4 + 1]),
+                                    __uint_as_float(v[4 * q4 + 2]), __uint_as_float(v[4 * q4 + 3]));
+          }
+          const uint32_t base = q_smem + (c >> 1) * kChunkBytes;
+#pragma unroll
+          for (int q4 = 0; q4 < 4; ++q4)
+            st_shared_v4(base + sw128_off(row, (c & 1) * 4 + q4), pk[4 * q4], pk[4 * q4 + 1], pk[4 * q4 + 2],
+                         pk[4 * q4 + 3]);
+        }
+        ptx::tc_fence_before();
+      } else {
+        float* o_dst = (a.splits > 1) ? a.part_o + ((long long)split * a.n + grow) * D : a.retrieved + grow * D;
+#pragma unroll 1
+        for (int c = 0; c < D / 32; ++c) {
+          uint32_t v[32];
+          ptx::tmem_ld_x32(lane_base + kTmemO + c * 32, v);
+          ptx::tmem_wait_ld();
+          if (row_ok) {
+            float4* dst = reinterpret_cast<float4*>(o_dst + c * 32);
+#pragma unroll
+            for (int q4 = 0; q4 < 8; ++q4)
+              dst[q4] = make_float4(__uint_as_float(v[4 * q4]) * inv, __uint_as_float(v[4 * q4 + 1]) * inv,
+                                    __uint_as_float(v[4 * q4 + 2]) * inv, __uint_as_float(v[4 * q4 + 3]) * inv);
+          }
+        }
+        if (row_ok) {
+          const float lse = kLn2 * (m_run + ptx::lg2(l));
+          if (a.splits > 1) {
+            const long long o = (long long)split * a.n + grow;
+            a.part_lse[o] = lse; a.part_max[o] = tmax * kLn2; a.part_arg[o] = targ + a.pattern_offset;
+          } else {
+            if (a.lse) a.lse[grow] = lse;
+            if (a.rowmax) a.rowmax[grow] = tmax * kLn2;
+            if (a.argmax) a.argmax[grow] = targ + a.pattern_offset;
+          }
+        }
+        ptx::tc_fence_before();
+      }
+      g += nt;
+    }
+  }
+
+  __syncthreads();
+  if (warp == 0) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+// Combine `splits` partial results of one row (flash-decoding merge): weights exp(lse_s - lse).
+template <int D>
+__global__ void tc_combine_kernel(int n, int splits, const float* __restrict__ part_o,
+                                  const float* __restrict__ part_lse, const float* __restrict__ part_max,
+                                  const int32_t* __restrict__ part_arg, float* __restrict__ retrieved,
+                                  float* __restrict__ lse, int32_t* __restrict__ argmax, float* __restrict__ rowmax) {
+  const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp_global >= n) return;
+  const long long r = warp_global;
+  float m = -INFINITY;
+  for (int s = 0; s < splits; ++s) m = fmaxf(m, part_lse[(long long)s * n + r]);
+  float z = 0.f;
+  for (int s = 0; s < splits; ++s) z += __expf(part_lse[(long long)s * n + r] - m);
+  const float inv = 1.f / z;
+  constexpr int kVec = (D + 127) / 128;
+  float4 acc[kVec];
+#pragma unroll
+  for (int v = 0; v < kVec; ++v) acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+  float best = -INFINITY;
+  int arg = 0;
+  for (int s = 0; s < splits; ++s) {
+    const long long o = (long long)s * n + r;
+    const float w = __expf(part_lse[o] - m) * inv;
+    const float pm = part_max[o];
+    if (pm > best) { best = pm; arg = part_arg[o]; }   // splits are in pattern order: ties keep the lowest index
+#pragma unroll
+    for (int v = 0; v < kVec; ++v) {
+      const int e = lane * 4 + v * 128;
+      if (e < D) {
+        const float4 t = *reinterpret_cast<const float4*>(part_o + o * D + e);
+        acc[v].x += w * t.x; acc[v].y += w * t.y; acc[v].z += w * t.z; acc[v].w += w * t.w;
+      }
+    }
+  }
+#pragma unroll
+  for (int v = 0; v < kVec; ++v) {
+    const int e = lane * 4 + v * 128;
+    if (e < D) *reinterpret_cast<float4*>(retrieved + r * D + e) = acc[v];
+  }
+  if (lane == 0) {
+    if (lse) lse[r] = m + __logf(z);
+    if (rowmax) rowmax[r] = best;
+    if (argmax) argmax[r] = arg;
+  }
+}
+
+// ------------------------------------------------------------------ host side
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+// 2-D row-major 16-bit matrix (rows, cols) -> boxes of (box_rows x 64 columns), 128-byte swizzle.
+int make_map(CUtensorMap* m, const void* base, int rows, int cols, int box_rows, int bf16) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) HOP_FAIL(HOP_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
+  const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
+  const cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1u, 1u};
+  const CUresult r = fn(m, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
+                        const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) HOP_FAIL(HOP_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) for a %d x %d matrix", (int)r, rows, cols);
+  return HOP_OK;
+}
+
+template <int D>
+int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
+  using Cfg = TcCfg<D>;
+  const int ppad = padded_patterns(a.p);
+  CUtensorMap tk, tkt, tvt;
+  HOP_TRY(make_map(&tk, a.k16, ppad, D, kTileP, a.bf16));
+  HOP_TRY(make_map(&tvt, a.vt16, D, ppad, Cfg::kBRows, a.bf16));
+  if (a.update_steps > 0) HOP_TRY(make_map(&tkt, a.kt16, D, ppad, Cfg::kBRows, a.bf16));
+  else tkt = tvt;
+
+  TcKernelArgs k{};
+  k.x_raw = a.x_raw; k.lnq_w = a.lnq_w; k.lnq_b = a.lnq_b; k.ln_eps = a.ln_eps; k.has_ln = a.has_ln; k.beta = a.beta;
+  k.qs = a.qs; k.n = a.n; k.p = a.p; k.update_steps = a.update_steps; k.bf16 = a.bf16;
+  const int nt_total = ppad / kTileP;
+  k.tiles_per_split = (nt_total + splits - 1) / splits;
+  k.splits = (nt_total + k.tiles_per_split - 1) / k.tiles_per_split;   // every split owns >= 1 tile
+  k.retrieved = a.retrieved; k.qsave = a.qsave; k.lse = a.lse; k.argmax = a.argmax; k.rowmax = a.rowmax;
+  k.pattern_offset = a.pattern_offset;
+  if (k.splits > 1) {
+    const size_t need = tc_forward_workspace(a.n, a.p, D, a.update_steps);
+    if (!a.ws || a.ws_bytes < need)
+      HOP_FAIL(HOP_ERR_WORKSPACE, "tensor-core forward needs %zu workspace bytes for %d pattern splits, %zu given", need,
+               k.splits, a.ws_bytes);
+    char* w = static_cast<char*>(a.ws);
+    const size_t rows = (size_t)splits * a.n;
+    k.part_o = reinterpret_cast<float*>(w); w += round_up_sz(rows * D * sizeof(float), 256);
+    k.part_lse = reinterpret_cast<float*>(w); w += round_up_sz(rows * sizeof(float), 256);
+    k.part_max = reinterpret_cast<float*>(w); w += round_up_sz(rows * sizeof(float), 256);
+    k.part_arg = reinterpret_cast<int32_t*>(w);
+  }
+
+  static std::once_flag attr_once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(attr_once, [] {
+    attr_err = cudaFuncSetAttribute(hop_fwd_tc_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+  });
+  // the attribute is per device: set it again cheaply when another device is current
+  HOP_CUDA(cudaFuncSetAttribute(hop_fwd_tc_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+  (void)attr_err;
+  const dim3 grid((a.n + kTileM - 1) / kTileM, k.splits);
+  hop_fwd_tc_kernel<D><<<grid, kThreads, Cfg::kSmemBytes, st>>>(tk, tkt, tvt, k);
+  HOP_LAUNCH_CHECK("hop_fwd_tc_kernel");
+  if (k.splits > 1) {
+    const int threads = 256, rows_per_block = threads / 32;
+    tc_combine_kernel<D><<<(a.n + rows_per_block - 1) / rows_per_block, threads, 0, st>>>(
+        a.n, k.splits, k.part_o, k.part_lse, k.part_max, k.part_arg, a.retrieved, a.lse, a.argmax, a.rowmax);
+    HOP_LAUNCH_CHECK("tc_combine_kernel");
+  }
+  return HOP_OK;
+}
+
+}  // namespace
+
+bool tc_supported(int h, int dv) { return h == dv && (h == 64 || h == 128 || h == 256); }
+
+// Pattern splits per 128-row tile: the smallest count that fills >= 95 % of the last wave of SMs
+// (retrieve updates need the full softmax per pass, so T > 0 never splits).
+int tc_choose_splits(int n, int p, int update_steps) {
+  if (update_steps > 0) return 1;
+  const int nt_all = padded_patterns(p) / kTileP;
+  if (const char* e = getenv("HOP_TC_SPLITS")) {          // test knob: force a split count
+    const int s = atoi(e);
+    if (s >= 1) return s < nt_all ? s : nt_all;
+  }
+  const int sms = num_sms();
+  const int row_tiles = (n + kTileM - 1) / kTileM;
+  const int nt_total = padded_patterns(p) / kTileP;
+  const int max_splits = nt_total < 32 ? nt_total : 32;
+  int best = 1;
+  double best_eff = 0.0;
+  for (int s = 1; s <= max_splits; ++s) {
+    if (nt_total / s < 4 && s > 1) break;                 // keep >= 4 tiles per CTA
+    const long long items = (long long)row_tiles * s;
+    const long long waves = (items + sms - 1) / sms;
+    const double eff = (double)items / (double)(waves * sms);
+    if (eff > best_eff + 1e-9) { best_eff = eff; best = s; }
+    if (eff >= 0.95) break;
+  }
+  return best;
+}
+
+size_t tc_forward_workspace(int n, int p, int d, int update_steps) {
+  const int splits = tc_choose_splits(n, p, update_steps);
+  if (splits <= 1) return 0;
+  const size_t rows = (size_t)splits * n;
+  return round_up_sz(rows * d * sizeof(float), 256) + 3 * round_up_sz(rows * sizeof(float), 256);
+}
+
+int launch_tc_forward(const TcPassArgs& a, cudaStream_t st) {
+  if (!tc_supported(a.h, a.dv)) HOP_FAIL(HOP_ERR_UNSUPPORTED, "tensor-core path needs H == Dv in {64,128,256}");
+  if (!a.retrieved) HOP_FAIL(HOP_ERR_BAD_ARG, "tensor-core forward: retrieved is NULL");
+  const int splits = tc_choose_splits(a.n, a.p, a.update_steps);
+  switch (a.h) {
+    case 64: return launch_d<64>(a, splits, st);
+    case 128: return launch_d<128>(a, splits, st);
+    default: return launch_d<256>(a, splits, st);
+  }
+}
+
+}  // namespace hop

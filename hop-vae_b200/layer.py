@@ -168,6 +168,7 @@ class HopfieldLayer(nn.Module):
         self._flags = flags
         self.kernel_path = os.environ.get("HOP_SM100_PATH", "auto")
         self.last_argmax: Optional[Tensor] = None
+        self.last_lse: Optional[Tensor] = None
         self._cache_key = None
         self._cache = None
         self.reset_parameters()
@@ -250,6 +251,7 @@ class HopfieldLayer(nn.Module):
                                                    for k in _QUERY_SIDE],
                               spec.flags, path, spec.d_in, spec.d_out, spec.update_steps, spec.beta, spec.ln_eps, 0)
             out, argmax = res[0], res[4]
+            self.last_lse = res[3]
         self.last_argmax = argmax
         return out.reshape(*lead, out.shape[-1])
 

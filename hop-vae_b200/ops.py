@@ -140,7 +140,7 @@ def retrieve_op(x: Tensor, khat: Tensor, vhat: Tensor, k16: Tensor, kt16: Tensor
     argmax = torch.empty((N,), device=dev, dtype=torch.int32)
     need = C.c_size_t(0)
     cabi.check(lib.hop_sm100_workspace_bytes(C.byref(d), 0, C.byref(need)), "hop_sm100_workspace_bytes")
-    use_ws = bool(flags & cabi.F_PROJ_STATE) or update_steps > 0
+    use_ws = bool(flags & cabi.F_PROJ_STATE) or update_steps > 0 or path != cabi.PATH_FP32_SIMT
     ws = torch.empty((int(need.value),), device=dev, dtype=torch.uint8) if use_ws else None
     params = cabi.HopParams(ln_state_w=cabi.ptr(ln_state_w), ln_state_b=cabi.ptr(ln_state_b), wq=cabi.ptr(wq),
                             bq=cabi.ptr(bq), wo=cabi.ptr(wo), bo=cabi.ptr(bo))

@@ -301,3 +301,70 @@ def test_pattern_sharded_merge_single_gpu(hf, G):
     s = scores.reshape(-1, 512)
     assert torch.equal(arg.cpu().long(), s.argmax(-1))
     assert rel_l2(lse, torch.logsumexp(s, -1)) < 1e-5
+
+
+# --------------------------------------------------------------------------- tensor-core (tcgen05) path
+TC_CASES = {
+    # name: (D, P, rows, T)
+    "d64_p512": (64, 512, 2048, 0),
+    "d64_ragged": (64, 1000, 300, 0),
+    "d128_p4k": (128, 4096, 1024, 0),
+    "d256_p2k": (256, 2048, 512, 0),
+    "d256_ragged": (256, 1100, 257, 0),
+    "d64_T1": (64, 640, 384, 1),
+    "d128_T3": (128, 512, 256, 3),
+    "d256_T1": (256, 1024, 256, 1),
+}
+
+
+def _sweep_layer(hf, D, P, T, seed=31):
+    """Config-5 style layer: patterns ~ N(0,1), queries near stored patterns."""
+    kw = dict(input_size=D, quantity=P, update_steps_max=T, update_steps_eps=0.0, **STATIC)
+    ref = randomize_(O.HopfieldLayer(**kw), seed, 1.0)
+    g = torch.Generator().manual_seed(seed + 1)
+    with torch.no_grad():
+        ref.lookup_weights.copy_(torch.randn(1, P, D, generator=g))
+    dut = hf.HopfieldLayer(**kw)
+    dut.load_state_dict(ref.state_dict())
+    return ref, dut.cuda(), g
+
+
+@pytest.mark.parametrize("splits", [0, 3])
+@pytest.mark.parametrize("name", list(TC_CASES))
+def test_forward_parity_tensor_core(hf, name, splits, monkeypatch):
+    """tcgen05 fp16-operand / fp32-accumulate path against the fp32 oracle: rel-L2 <= 1e-3 (north-star bar),
+    nearest-pattern index identical wherever the oracle's top-1/top-2 gap exceeds the 16-bit operand noise."""
+    D, P, N, T = TC_CASES[name]
+    if splits and T > 0:
+        pytest.skip("retrieve updates never split the pattern axis")
+    if splits:
+        monkeypatch.setenv("HOP_TC_SPLITS", str(splits))
+    ref, dut, g = _sweep_layer(hf, D, P, T)
+    idx = torch.randint(0, P, (N,), generator=g)
+    x = ref.lookup_weights[0, idx].detach() + 0.5 * torch.randn(N, D, generator=g)
+    dut.kernel_path = "f16"
+    with torch.no_grad():
+        want, _, scores, _ = ref(x[None], return_details=True)
+        got = dut(x.cuda())
+    r = rel_l2(got, want[0])
+    print(f"{name} splits={splits}: rel-L2 {r:.3e}")
+    assert r < REL_L2_BAR
+    s = scores.reshape(N, P)
+    top2 = s.topk(2, dim=-1).values
+    decided = (top2[:, 0] - top2[:, 1]) > 2e-2
+    got_idx = dut.last_argmax.cpu().long().reshape(-1)
+    assert torch.equal(got_idx[decided], s.argmax(-1)[decided])
+    assert decided.float().mean() > 0.5
+    lse_want = torch.logsumexp(s, -1)
+    assert (dut.last_lse.cpu().reshape(-1) - lse_want).abs().max() < 2e-2
+
+
+def test_tensor_core_bf16_runs(hf):
+    """bf16 operands: same kernels, looser numerics (documented as failing the 1e-3 bar on tight problems)."""
+    ref, dut, g = _sweep_layer(hf, 128, 1024, 0)
+    x = torch.randn(512, 128, generator=g)
+    dut.kernel_path = "bf16"
+    with torch.no_grad():
+        r = rel_l2(dut(x.cuda()), ref(x[None])[0])
+    print(f"bf16 rel-L2 {r:.3e}")
+    assert r < 2e-2
