@@ -299,32 +299,36 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         ptx::tc_fence_after();
         const uint32_t s_addr = lane_base + b * kTileP;
 
-        // pass A: tile max (+ nearest-pattern index)
-        float cmax = -INFINITY;
-#pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
-          uint32_t v[32];
-          ptx::tmem_ld_x32(s_addr + c * 32, v);
-          ptx::tmem_wait_ld();
-          float cm = -INFINITY;
-          if (valid >= (c + 1) * 32) {
+        // whole score row of the tile into registers (one TMEM round trip), then free the S buffer at once
+        uint32_t v[128];
+        ptx::tmem_ld_x32p(s_addr, v);
+        ptx::tmem_ld_x32p(s_addr + 32, v + 32);
+        ptx::tmem_ld_x32p(s_addr + 64, v + 64);
+        ptx::tmem_ld_x32p(s_addr + 96, v + 96);
+        ptx::tmem_wait_ld();
+        ptx::tc_fence_before();
+        ptx::mbar_arrive(s_empty(b));
+        if (valid < kTileP) {
 #pragma unroll
-            for (int i = 0; i < 32; ++i) cm = fmaxf(cm, __uint_as_float(v[i]));
-          } else {
+          for (int i = 0; i < 128; ++i)
+            if (i >= valid) v[i] = __float_as_uint(-INFINITY);
+        }
+
+        // tile max on four independent chains (FMNMX3), nearest-pattern index only when the max moved
+        float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-              if (c * 32 + i >= valid) v[i] = __float_as_uint(-INFINITY);
-              cm = fmaxf(cm, __uint_as_float(v[i]));
-            }
-          }
-          if (cm > tmax) {
-            int idx = 31;
+        for (int i = 0; i < 128; i += 8) {
 #pragma unroll
-            for (int i = 31; i >= 0; --i) idx = (__uint_as_float(v[i]) == cm) ? i : idx;
-            tmax = cm;
-            targ = col0 + c * 32 + idx;
-          }
-          cmax = fmaxf(cmax, cm);
+          for (int u = 0; u < 4; ++u)
+            mx[u] = fmaxf(mx[u], fmaxf(__uint_as_float(v[i + 2 * u]), __uint_as_float(v[i + 2 * u + 1])));
+        }
+        const float cmax = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+        if (cmax > tmax) {
+          int idx = 127;
+#pragma unroll
+          for (int i = 127; i >= 0; --i) idx = (__uint_as_float(v[i]) == cmax) ? i : idx;
+          tmax = cmax;
+          targ = col0 + idx;
         }
 
         // lazy rescale of (l, O): only when some row of the warp outgrew its reference max by 2^8
@@ -339,44 +343,36 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
             l *= f;
 #pragma unroll 1
             for (int c = 0; c < D / 32; ++c) {
-              uint32_t v[32];
-              ptx::tmem_ld_x32(lane_base + kTmemO + c * 32, v);
+              uint32_t o[32];
+              ptx::tmem_ld_x32(lane_base + kTmemO + c * 32, o);
               ptx::tmem_wait_ld();
 #pragma unroll
-              for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * f);
-              ptx::tmem_st_x32(lane_base + kTmemO + c * 32, v);
+              for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * f);
+              ptx::tmem_st_x32(lane_base + kTmemO + c * 32, o);
             }
             ptx::tmem_wait_st();
+            ptx::tc_fence_before();
           }
           m_run = m_new;
         }
 
-        // pass B: P~ = 2^(s - m_run) as 16-bit into the swizzled A-operand buffer
+        // P~ = 2^(s - m_run) as 16-bit into the swizzled A-operand buffer
         ptx::mbar_wait(p_empty(b), ((gg >> 1) & 1) ^ 1);
         const uint32_t p_addr = p_smem + b * Cfg::kPBytes;
-#pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
-          uint32_t v[32];
-          ptx::tmem_ld_x32(s_addr + c * 32, v);
-          ptx::tmem_wait_ld();
-          uint32_t pk[16];
+        float ls[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            float p0 = ptx::ex2(__uint_as_float(v[2 * i]) - m_run);
-            float p1 = ptx::ex2(__uint_as_float(v[2 * i + 1]) - m_run);
-            if (c * 32 + 2 * i >= valid) p0 = 0.f;
-            if (c * 32 + 2 * i + 1 >= valid) p1 = 0.f;
-            l += p0 + p1;
-            pk[i] = pack16(p0, p1, a.bf16);
+        for (int c16 = 0; c16 < 16; ++c16) {        // 16-byte chunk = 8 patterns
+          uint32_t pk[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const float p0 = ptx::ex2(__uint_as_float(v[c16 * 8 + 2 * u]) - m_run);
+            const float p1 = ptx::ex2(__uint_as_float(v[c16 * 8 + 2 * u + 1]) - m_run);
+            ls[u] += p0 + p1;
+            pk[u] = pack16(p0, p1, a.bf16);
           }
-          const uint32_t base = p_addr + (c >> 1) * kChunkBytes;
-#pragma unroll
-          for (int q4 = 0; q4 < 4; ++q4)
-            st_shared_v4(base + sw128_off(row, (c & 1) * 4 + q4), pk[4 * q4], pk[4 * q4 + 1], pk[4 * q4 + 2],
-                         pk[4 * q4 + 3]);
+          st_shared_v4(p_addr + (c16 >> 3) * kChunkBytes + sw128_off(row, c16 & 7), pk[0], pk[1], pk[2], pk[3]);
         }
-        ptx::tc_fence_before();
-        ptx::mbar_arrive(s_empty(b));
+        l += (ls[0] + ls[1]) + (ls[2] + ls[3]);
         ptx::fence_proxy_async_smem();
         ptx::mbar_arrive(p_full(b));
       }

@@ -18,6 +18,10 @@ def pytest_collection_modifyitems(config, items):
     try:
         import torch
         has_gpu = torch.cuda.is_available()
+        # the reference is an fp32 path: the surrounding cuDNN convs / cuBLAS calls of the
+        # harness model must not silently run in TF32 when they are compared with the CPU oracle
+        torch.backends.cudnn.allow_tf32 = False
+        torch.backends.cuda.matmul.allow_tf32 = False
     except Exception:
         has_gpu = False
     if has_gpu:
