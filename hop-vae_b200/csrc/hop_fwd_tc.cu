@@ -10,9 +10,13 @@
 //   warp 0      TMA producer: ring of 16 KiB operand chunks (K^ rows for the score MMA, then
 //               V^T / K^T rows for the read-out MMA), 128-byte swizzle, mbarrier-tracked
 //   warp 1      MMA issuer (one elected lane): S = Q K^T into a double-buffered TMEM tile,
-//               O += P~ B into TMEM columns [256, 256+Dr)
-//   warps 2..5  softmax: tcgen05.ld S, online max / lazy rescale, ex2, 16-bit P~ into swizzled
-//               shared memory, epilogue (O / l -> HBM, or -> next pass' Q tile in smem)
+//               O += P~ B into TMEM columns [256, 256+D) with one N = D instruction per K step
+//   warps 2..9  softmax, two warps per TMEM lane quarter (= two per SM sub-partition, so each
+//               hides the other's MUFU / TMEM latency): warp pair (q, h) owns rows 32q..32q+31 and
+//               score columns 64h..64h+63 of every tile; the pair agrees on the row maximum through
+//               shared memory + a 64-thread named barrier, then each half does ex2, the 16-bit P~
+//               pack into swizzled shared memory and half of every O-column job (lazy rescale,
+//               epilogue, next pass' Q tile).
 #include <cuda.h>
 
 #include <cstdlib>
@@ -27,9 +31,11 @@ namespace {
 
 constexpr int kTileM = 128;          // query rows per CTA (TMEM lanes)
 constexpr int kTileP = 128;          // patterns per score tile
+constexpr int kHalfP = 64;           // score columns per softmax thread
 constexpr int kChunkBytes = 16384;   // 128 rows x 64 16-bit elements, 128B-swizzled
-constexpr int kThreads = 192;
-constexpr int kSoftmaxThreads = 128;
+constexpr int kSoftmaxWarps = 8;
+constexpr int kSoftmaxThreads = kSoftmaxWarps * 32;
+constexpr int kThreads = 64 + kSoftmaxThreads;
 constexpr uint32_t kTmemCols = 512;
 constexpr uint32_t kTmemO = 256;     // O accumulator starts after the two S buffers
 constexpr float kLog2e = 1.4426950408889634f;
@@ -39,31 +45,36 @@ constexpr float kRescaleThreshold = 8.f;   // log2 units: P~ <= 2^8, safe in fp1
 template <int D>
 struct TcCfg {
   static constexpr int kKChunks = D / 64;                 // 64-wide K chunks of the Q / K^ tiles
-  static constexpr int kBRows = D < 128 ? D : 128;        // read-out chunk rows (N of the PV MMA)
-  static constexpr int kDHalves = D / kBRows;             // read-out column groups
+  static constexpr int kBStages = D > 128 ? D / 128 : 1;  // ring stages of one read-out chunk (D rows x 64 patterns)
+  static constexpr int kBRows = D / kBStages;             // rows per TMA box of the read-out operand
   static constexpr int kQBytes = kKChunks * kChunkBytes;  // Q tile
   static constexpr int kPBytes = 2 * kChunkBytes;         // one P~ buffer (128 x 128 x 2B)
-  static constexpr int kStages = (D >= 256) ? 6 : 8;
-  static constexpr int kSmemBytes = 1024 /*align slack*/ + kQBytes + 2 * kPBytes + kStages * kChunkBytes + 256;
+  static constexpr int kStages = (D >= 256) ? 6 : 8;      // even: a 2-stage read-out chunk never wraps
+  static constexpr int kBarBytes = 256;                   // mbarriers + TMEM slot
+  static constexpr int kXchBytes = 2 * 2 * kTileM * 4;    // [parity][half][row] floats exchanged by a warp pair
+  static constexpr int kSmemBytes = kQBytes + 2 * kPBytes + kStages * kChunkBytes + kBarBytes + kXchBytes;
+  static_assert(kStages % 2 == 0 && (kKChunks % 2 == 0 || kBStages == 1), "2-stage chunks must stay pair-aligned");
 };
 
 struct TcKernelArgs {
   const float* x_raw; const float* lnq_w; const float* lnq_b; float ln_eps; int has_ln; float beta;
   const float* qs;
-  int n, p, update_steps, bf16;
+  int n, p, update_steps;
   int splits, tiles_per_split;          // pattern tiles (of 128) handled by one CTA
   float* retrieved; float* qsave; float* lse; int32_t* argmax; float* rowmax; int pattern_offset;
   // partial outputs when splits > 1: (splits, N, D), (splits, N) x3
   float* part_o; float* part_lse; float* part_max; int32_t* part_arg;
 };
 
-__device__ __forceinline__ uint32_t pack16(float a, float b, int bf16) {
-  if (bf16) {
+template <bool kBf16>
+__device__ __forceinline__ uint32_t pack16(float a, float b) {
+  if constexpr (kBf16) {
     __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
     return *reinterpret_cast<uint32_t*>(&v);
+  } else {
+    __half2 v = __floats2half2_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&v);
   }
-  __half2 v = __floats2half2_rn(a, b);
-  return *reinterpret_cast<uint32_t*>(&v);
 }
 
 // Byte offset of 16-byte chunk `c16` (0..7) of row `r` inside a 128B-swizzled [rows x 64] tile.
@@ -74,14 +85,23 @@ __device__ __forceinline__ uint32_t sw128_off(int r, int c16) {
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
+__device__ __forceinline__ void st_shared_f32(uint32_t addr, float v) {
+  asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ float ld_shared_f32(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
+  return v;
+}
 
-template <int D>
+template <int D, bool kBf16>
 __global__ void __launch_bounds__(kThreads, 1)
 hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_kt,
                   const __grid_constant__ CUtensorMap tm_vt, const TcKernelArgs a) {
   using Cfg = TcCfg<D>;
-  extern __shared__ uint8_t smem_raw[];
-  const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t smem_base = ptx::smem_u32(smem_raw);
+  if ((smem_base & 1023u) != 0) __trap();       // the 128B-swizzle atoms need a 1 KiB-aligned base
   const uint32_t q_smem = smem_base;
   const uint32_t p_smem = q_smem + Cfg::kQBytes;
   const uint32_t ring = p_smem + 2 * Cfg::kPBytes;
@@ -95,6 +115,8 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
   auto p_empty = [&](int b) { return misc + 48u + 8u * b; };
   const uint32_t q_ready = misc + 64u;
   const uint32_t tmem_slot = misc + 72u;
+  const uint32_t xch = bars + Cfg::kBarBytes;   // [parity][half][row]
+  auto xch_at = [&](int parity, int half, int r) { return xch + (uint32_t)(((parity * 2 + half) * kTileM + r) * 4); };
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int split = blockIdx.y;
@@ -142,8 +164,8 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         };
         auto load_b = [&](int tile) {
           for (int kc = 0; kc < 2; ++kc)
-            for (int dh = 0; dh < Cfg::kDHalves; ++dh)
-              produce(bm, tile * kTileP + kc * 64, dh * Cfg::kBRows, Cfg::kBRows * 128);
+            for (int bs = 0; bs < Cfg::kBStages; ++bs)
+              produce(bm, tile * kTileP + kc * 64, bs * Cfg::kBRows, Cfg::kBRows * 128);
         };
         load_k(t0);
         for (int j = 0; j < nt; ++j) {
@@ -156,9 +178,9 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
   } else if (warp == 1) {
     // -------------------------------------------------------------- MMA issuer
     if (ptx::elect_one()) {
-      const int fmt = a.bf16 ? 1 : 0;
-      const uint32_t idesc_qk = ptx::umma_idesc_f16(kTileM, kTileP, fmt);
-      const uint32_t idesc_pv = ptx::umma_idesc_f16(kTileM, Cfg::kBRows, fmt);
+      constexpr int fmt = kBf16 ? 1 : 0;
+      constexpr uint32_t idesc_qk = ptx::umma_idesc_f16(kTileM, kTileP, fmt);
+      constexpr uint32_t idesc_pv = ptx::umma_idesc_f16(kTileM, D, fmt);
       uint32_t it = 0, g = 0;
       for (int pass = 0; pass < passes; ++pass) {
         ptx::mbar_wait(q_ready, pass & 1);
@@ -189,17 +211,20 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
           ptx::mbar_wait(p_full(b), (gg >> 1) & 1);
           ptx::tc_fence_after();
           for (int kc = 0; kc < 2; ++kc) {
-            for (int dh = 0; dh < Cfg::kDHalves; ++dh) {
-              const int s = it % Cfg::kStages;
-              ptx::mbar_wait(full_bar(s), (it / Cfg::kStages) & 1);
-              ptx::tc_fence_after();
-              const uint64_t ad = ptx::umma_desc_sw128(p_smem + b * Cfg::kPBytes + kc * kChunkBytes);
-              const uint64_t bd = ptx::umma_desc_sw128(ring + s * kChunkBytes);
+            // one read-out chunk = D rows x 64 patterns = kBStages consecutive (pair-aligned) ring stages
+            const int s = it % Cfg::kStages;
+            for (int bs = 0; bs < Cfg::kBStages; ++bs) {
+              const uint32_t i2 = it + bs;
+              ptx::mbar_wait(full_bar(i2 % Cfg::kStages), (i2 / Cfg::kStages) & 1);
+            }
+            ptx::tc_fence_after();
+            const uint64_t ad = ptx::umma_desc_sw128(p_smem + b * Cfg::kPBytes + kc * kChunkBytes);
+            const uint64_t bd = ptx::umma_desc_sw128(ring + s * kChunkBytes);
 #pragma unroll
-              for (int k = 0; k < 4; ++k)
-                ptx::umma_f16_ss(tmem_base + kTmemO + dh * Cfg::kBRows, ad + 2 * k, bd + 2 * k, idesc_pv,
-                                 (j | kc | k) != 0);
-              ptx::umma_commit(empty_bar(s));
+            for (int k = 0; k < 4; ++k)
+              ptx::umma_f16_ss(tmem_base + kTmemO, ad + 2 * k, bd + 2 * k, idesc_pv, (j | kc | k) != 0);
+            for (int bs = 0; bs < Cfg::kBStages; ++bs) {
+              ptx::umma_commit(empty_bar(it % Cfg::kStages));
               ++it;
             }
           }
@@ -212,15 +237,22 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
   } else {
     // ------------------------------------------------------ softmax / epilogue
     const int wq = warp & 3;                      // TMEM lane quarter this warp may access
-    const int row = wq * 32 + lane;               // row of the tile owned by this thread
+    const int half = (warp - 2) >> 2;             // which 64 score columns / which half of the O columns
+    const int row = wq * 32 + lane;               // row of the tile owned by this thread (shared with the partner warp)
     const long long grow = (long long)blockIdx.x * kTileM + row;
     const uint32_t lane_base = tmem_base + ((uint32_t)(wq * 32) << 16);
     const bool row_ok = grow < a.n;
     const float qscale = a.beta;                  // natural-units scale of the state pattern
+    const uint32_t pair_bar = 1 + wq;             // named barrier of the warp pair (64 threads)
+    constexpr int kOGroups = D / 64;              // 32-column O groups per half
+    const int og0 = half * kOGroups;
 
-    // ---- pass-0 Q tile: one warp per row, coalesced; LN_q + beta, fp32 qsave, 16-bit swizzled smem
+    // ---- pass-0 Q tile: one warp per row, 4 rows in flight; LN_q + beta, fp32 qsave, 16-bit swizzled smem
     {
       constexpr int kVec = (D + 127) / 128;       // float4 per lane
+      constexpr int kRowsInFlight = 4;
+      constexpr int kRowsPerWarp = kTileM / kSoftmaxWarps;
+      const int sw = warp - 2;
       float4 w4[kVec], b4[kVec];
 #pragma unroll
       for (int v = 0; v < kVec; ++v) {
@@ -233,51 +265,61 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         }
       }
       const float* src = a.x_raw ? a.x_raw : a.qs;
-      for (int rr = 0; rr < 32; ++rr) {
-        const int r = wq * 32 + rr;
-        const long long gr = (long long)blockIdx.x * kTileM + r;
-        float4 xv[kVec];
+      for (int rr = 0; rr < kRowsPerWarp; rr += kRowsInFlight) {
+        float4 xv[kRowsInFlight][kVec];
 #pragma unroll
-        for (int v = 0; v < kVec; ++v) {
-          const int e = lane * 4 + v * 128;
-          xv[v] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (e < D && gr < a.n) xv[v] = *reinterpret_cast<const float4*>(src + gr * D + e);
+        for (int u = 0; u < kRowsInFlight; ++u) {
+          const long long gr = (long long)blockIdx.x * kTileM + sw * kRowsPerWarp + rr + u;
+#pragma unroll
+          for (int v = 0; v < kVec; ++v) {
+            const int e = lane * 4 + v * 128;
+            xv[u][v] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (e < D && gr < a.n) xv[u][v] = __ldg(reinterpret_cast<const float4*>(src + gr * D + e));
+          }
         }
-        if (a.x_raw) {
-          if (a.has_ln) {
-            float s = 0.f;
 #pragma unroll
-            for (int v = 0; v < kVec; ++v) s += (xv[v].x + xv[v].y) + (xv[v].z + xv[v].w);
-            const float mean = warp_sum(s) * (1.f / D);
-            float q = 0.f;
+        for (int u = 0; u < kRowsInFlight; ++u) {
+          const int r = sw * kRowsPerWarp + rr + u;
+          const long long gr = (long long)blockIdx.x * kTileM + r;
+          if (a.x_raw) {
+            if (a.has_ln) {
+              float s = 0.f;
 #pragma unroll
-            for (int v = 0; v < kVec; ++v) {
-              const int e = lane * 4 + v * 128;
-              if (e < D) {
-                xv[v].x -= mean; xv[v].y -= mean; xv[v].z -= mean; xv[v].w -= mean;
-                q += xv[v].x * xv[v].x + xv[v].y * xv[v].y + xv[v].z * xv[v].z + xv[v].w * xv[v].w;
+              for (int v = 0; v < kVec; ++v) s += (xv[u][v].x + xv[u][v].y) + (xv[u][v].z + xv[u][v].w);
+              const float mean = warp_sum(s) * (1.f / D);
+              float q = 0.f;
+#pragma unroll
+              for (int v = 0; v < kVec; ++v) {
+                const int e = lane * 4 + v * 128;
+                if (e < D) {
+                  xv[u][v].x -= mean; xv[u][v].y -= mean; xv[u][v].z -= mean; xv[u][v].w -= mean;
+                  q += xv[u][v].x * xv[u][v].x + xv[u][v].y * xv[u][v].y + xv[u][v].z * xv[u][v].z +
+                       xv[u][v].w * xv[u][v].w;
+                }
+              }
+              const float rstd = rsqrtf(warp_sum(q) * (1.f / D) + a.ln_eps);
+#pragma unroll
+              for (int v = 0; v < kVec; ++v) {
+                xv[u][v].x = xv[u][v].x * rstd * w4[v].x + b4[v].x; xv[u][v].y = xv[u][v].y * rstd * w4[v].y + b4[v].y;
+                xv[u][v].z = xv[u][v].z * rstd * w4[v].z + b4[v].z; xv[u][v].w = xv[u][v].w * rstd * w4[v].w + b4[v].w;
               }
             }
-            const float rstd = rsqrtf(warp_sum(q) * (1.f / D) + a.ln_eps);
 #pragma unroll
             for (int v = 0; v < kVec; ++v) {
-              xv[v].x = xv[v].x * rstd * w4[v].x + b4[v].x; xv[v].y = xv[v].y * rstd * w4[v].y + b4[v].y;
-              xv[v].z = xv[v].z * rstd * w4[v].z + b4[v].z; xv[v].w = xv[v].w * rstd * w4[v].w + b4[v].w;
+              xv[u][v].x *= qscale; xv[u][v].y *= qscale; xv[u][v].z *= qscale; xv[u][v].w *= qscale;
             }
           }
 #pragma unroll
-          for (int v = 0; v < kVec; ++v) { xv[v].x *= qscale; xv[v].y *= qscale; xv[v].z *= qscale; xv[v].w *= qscale; }
-        }
-#pragma unroll
-        for (int v = 0; v < kVec; ++v) {
-          const int e = lane * 4 + v * 128;
-          if (e < D) {
-            if (a.qsave && a.update_steps == 0 && gr < a.n && split == 0)
-              *reinterpret_cast<float4*>(a.qsave + gr * D + e) = xv[v];
-            const uint32_t lo = pack16(xv[v].x * kLog2e, xv[v].y * kLog2e, a.bf16);
-            const uint32_t hi = pack16(xv[v].z * kLog2e, xv[v].w * kLog2e, a.bf16);
-            const uint32_t addr = q_smem + (e >> 6) * kChunkBytes + sw128_off(r, (e & 63) >> 3) + ((e & 4) << 1);
-            asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr), "r"(lo), "r"(hi) : "memory");
+          for (int v = 0; v < kVec; ++v) {
+            const int e = lane * 4 + v * 128;
+            if (e < D) {
+              if (a.qsave && a.update_steps == 0 && gr < a.n && split == 0)
+                *reinterpret_cast<float4*>(a.qsave + gr * D + e) = xv[u][v];
+              const uint32_t lo = pack16<kBf16>(xv[u][v].x * kLog2e, xv[u][v].y * kLog2e);
+              const uint32_t hi = pack16<kBf16>(xv[u][v].z * kLog2e, xv[u][v].w * kLog2e);
+              const uint32_t addr = q_smem + (e >> 6) * kChunkBytes + sw128_off(r, (e & 63) >> 3) + ((e & 4) << 1);
+              asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr), "r"(lo), "r"(hi) : "memory");
+            }
           }
         }
       }
@@ -288,48 +330,62 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
       ptx::fence_proxy_async_smem();
       ptx::mbar_arrive(q_ready);
 
+      // m_run is shared by the pair (identical in both threads of a row); l, tmax, targ are per half
       float m_run = -INFINITY, l = 0.f, tmax = -INFINITY;
       int targ = 0;
       for (int j = 0; j < nt; ++j) {
         const uint32_t gg = g + j;
         const int b = gg & 1;
-        const int col0 = (t0 + j) * kTileP;           // global pattern index of the tile's column 0
-        const int valid = a.p - col0;                 // columns >= valid are padding
+        const int col0 = (t0 + j) * kTileP + half * kHalfP;   // global pattern index of this thread's column 0
+        const int valid = a.p - col0;                          // columns >= valid are padding
         ptx::mbar_wait(s_full(b), (gg >> 1) & 1);
         ptx::tc_fence_after();
-        const uint32_t s_addr = lane_base + b * kTileP;
+        const uint32_t s_addr = lane_base + b * kTileP + half * kHalfP;
 
-        // whole score row of the tile into registers (one TMEM round trip), then free the S buffer at once
-        uint32_t v[128];
+        // this thread's 64 scores into registers (one TMEM round trip), then free the S buffer at once
+        uint32_t v[kHalfP];
         ptx::tmem_ld_x32p(s_addr, v);
         ptx::tmem_ld_x32p(s_addr + 32, v + 32);
-        ptx::tmem_ld_x32p(s_addr + 64, v + 64);
-        ptx::tmem_ld_x32p(s_addr + 96, v + 96);
         ptx::tmem_wait_ld();
         ptx::tc_fence_before();
         ptx::mbar_arrive(s_empty(b));
-        if (valid < kTileP) {
+        if (valid < kHalfP) {
 #pragma unroll
-          for (int i = 0; i < 128; ++i)
+          for (int i = 0; i < kHalfP; ++i)
             if (i >= valid) v[i] = __float_as_uint(-INFINITY);
         }
 
-        // tile max on four independent chains (FMNMX3), nearest-pattern index only when the max moved
+        // max of the 64 columns on four independent chains (FMNMX3); chain u holds elements 8g + 2u + {0,1}
         float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-        for (int i = 0; i < 128; i += 8) {
+        for (int i = 0; i < kHalfP; i += 8) {
 #pragma unroll
           for (int u = 0; u < 4; ++u)
             mx[u] = fmaxf(mx[u], fmaxf(__uint_as_float(v[i + 2 * u]), __uint_as_float(v[i + 2 * u + 1])));
         }
-        const float cmax = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
-        if (cmax > tmax) {
-          int idx = 127;
+        const float hmax = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+        // publish the half maximum; the row maximum decides the (rare) rescale identically in both halves
+        st_shared_f32(xch_at(b, half, row), hmax);
+        // nearest-pattern index, only when the half maximum moved: scan just the chains that hold it
+        if (hmax > tmax) {
+          int idx = kHalfP - 1;
 #pragma unroll
-          for (int i = 127; i >= 0; --i) idx = (__uint_as_float(v[i]) == cmax) ? i : idx;
-          tmax = cmax;
+          for (int u = 3; u >= 0; --u) {
+            if (mx[u] == hmax) {
+              int iu = kHalfP;
+#pragma unroll
+              for (int gq = 7; gq >= 0; --gq) {
+                iu = (__uint_as_float(v[8 * gq + 2 * u + 1]) == hmax) ? 8 * gq + 2 * u + 1 : iu;
+                iu = (__uint_as_float(v[8 * gq + 2 * u]) == hmax) ? 8 * gq + 2 * u : iu;
+              }
+              idx = min(idx, iu);
+            }
+          }
+          tmax = hmax;
           targ = col0 + idx;
         }
+        ptx::named_bar_sync(pair_bar, 64);
+        const float cmax = fmaxf(hmax, ld_shared_f32(xch_at(b, half ^ 1, row)));
 
         // lazy rescale of (l, O): only when some row of the warp outgrew its reference max by 2^8
         const bool need = cmax > m_run + kRescaleThreshold;
@@ -342,7 +398,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
             const float f = ptx::ex2(m_run - m_new);
             l *= f;
 #pragma unroll 1
-            for (int c = 0; c < D / 32; ++c) {
+            for (int c = og0; c < og0 + kOGroups; ++c) {
               uint32_t o[32];
               ptx::tmem_ld_x32(lane_base + kTmemO + c * 32, o);
               ptx::tmem_wait_ld();
@@ -356,54 +412,71 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
           m_run = m_new;
         }
 
-        // P~ = 2^(s - m_run) as 16-bit into the swizzled A-operand buffer
+        // P~ = 2^(s - m_run) as 16-bit into this half's 64-column chunk of the swizzled A-operand buffer
         ptx::mbar_wait(p_empty(b), ((gg >> 1) & 1) ^ 1);
-        const uint32_t p_addr = p_smem + b * Cfg::kPBytes;
+        const uint32_t p_addr = p_smem + b * Cfg::kPBytes + half * kChunkBytes;
         float ls[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-        for (int c16 = 0; c16 < 16; ++c16) {        // 16-byte chunk = 8 patterns
+        for (int i = 0; i < kHalfP; ++i) v[i] = __float_as_uint(ptx::ex2(__uint_as_float(v[i]) - m_run));
+#pragma unroll
+        for (int c16 = 0; c16 < 8; ++c16) {         // 16-byte chunk = 8 patterns
           uint32_t pk[4];
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
-            const float p0 = ptx::ex2(__uint_as_float(v[c16 * 8 + 2 * u]) - m_run);
-            const float p1 = ptx::ex2(__uint_as_float(v[c16 * 8 + 2 * u + 1]) - m_run);
+            const float p0 = __uint_as_float(v[c16 * 8 + 2 * u]);
+            const float p1 = __uint_as_float(v[c16 * 8 + 2 * u + 1]);
             ls[u] += p0 + p1;
-            pk[u] = pack16(p0, p1, a.bf16);
+            pk[u] = pack16<kBf16>(p0, p1);
           }
-          st_shared_v4(p_addr + (c16 >> 3) * kChunkBytes + sw128_off(row, c16 & 7), pk[0], pk[1], pk[2], pk[3]);
+          st_shared_v4(p_addr + sw128_off(row, c16), pk[0], pk[1], pk[2], pk[3]);
         }
         l += (ls[0] + ls[1]) + (ls[2] + ls[3]);
         ptx::fence_proxy_async_smem();
         ptx::mbar_arrive(p_full(b));
       }
 
-      // ---- epilogue of the pass: wait for the last read-out MMA, normalise
+      // ---- end of the pass: the pair combines (l, tmax, targ); slots of the other parity are idle
+      const int pl = (g + nt - 1) & 1;
+      st_shared_f32(xch_at(pl ^ 1, half, row), l);
+      ptx::named_bar_sync(pair_bar, 64);
+      const float l_tot = l + ld_shared_f32(xch_at(pl ^ 1, half ^ 1, row));
+      if (half == 1) {
+        st_shared_f32(xch_at(pl, 1, row), tmax);
+        st_shared_f32(xch_at(pl, 0, row), __int_as_float(targ));
+      }
+      ptx::named_bar_sync(pair_bar, 64);
+      if (half == 0) {
+        const float om = ld_shared_f32(xch_at(pl, 1, row));
+        const int oa = __float_as_int(ld_shared_f32(xch_at(pl, 0, row)));
+        if (om > tmax) { tmax = om; targ = oa; }       // ties keep the lower (half-0) index
+      }
+      // wait for the last read-out MMA, normalise
       const uint32_t last = g + nt - 1;
       ptx::mbar_wait(p_empty(last & 1), (last >> 1) & 1);
       ptx::tc_fence_after();
-      const float inv = 1.f / l;
+      const float inv = 1.f / l_tot;
       if (pass < a.update_steps) {
         // retrieve update: q <- beta * (A K^) becomes the next pass' Q tile (never leaves the SM)
         const bool save = (pass == a.update_steps - 1) && a.qsave && row_ok;
         const float sc = inv * qscale;
 #pragma unroll 1
-        for (int c = 0; c < D / 32; ++c) {
-          uint32_t v[32];
-          ptx::tmem_ld_x32(lane_base + kTmemO + c * 32, v);
+        for (int c = og0; c < og0 + kOGroups; ++c) {
+          uint32_t o[32];
+          ptx::tmem_ld_x32(lane_base + kTmemO + c * 32, o);
           ptx::tmem_wait_ld();
           uint32_t pk[16];
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
-            const float q0 = __uint_as_float(v[2 * i]) * sc, q1 = __uint_as_float(v[2 * i + 1]) * sc;
-            v[2 * i] = __float_as_uint(q0); v[2 * i + 1] = __float_as_uint(q1);
-            pk[i] = pack16(q0 * kLog2e, q1 * kLog2e, a.bf16);
+            const float q0 = __uint_as_float(o[2 * i]) * sc, q1 = __uint_as_float(o[2 * i + 1]) * sc;
+            o[2 * i] = __float_as_uint(q0); o[2 * i + 1] = __float_as_uint(q1);
+            pk[i] = pack16<kBf16>(q0 * kLog2e, q1 * kLog2e);
           }
           if (save) {
             float4* dst = reinterpret_cast<float4*>(a.qsave + grow * D + c * 32);
 #pragma unroll
             for (int q4 = 0; q4 < 8; ++q4)
-              dst[q4] = make_float4(__uint_as_float(v[4 * q4]), __uint_as_float(v[4 * q4 + 1]),
-                                    __uint_as_float(v[4 * q4 + 2]), __uint_as_float(v[4 * q4 + 3]));
+              dst[q4] = make_float4(__uint_as_float(o[4 * q4]), __uint_as_float(o[4 * q4 + 1]),
+                                    __uint_as_float(o[4 * q4 + 2]), __uint_as_float(o[4 * q4 + 3]));
           }
           const uint32_t base = q_smem + (c >> 1) * kChunkBytes;
 #pragma unroll
@@ -415,20 +488,20 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
       } else {
         float* o_dst = (a.splits > 1) ? a.part_o + ((long long)split * a.n + grow) * D : a.retrieved + grow * D;
 #pragma unroll 1
-        for (int c = 0; c < D / 32; ++c) {
-          uint32_t v[32];
-          ptx::tmem_ld_x32(lane_base + kTmemO + c * 32, v);
+        for (int c = og0; c < og0 + kOGroups; ++c) {
+          uint32_t o[32];
+          ptx::tmem_ld_x32(lane_base + kTmemO + c * 32, o);
           ptx::tmem_wait_ld();
           if (row_ok) {
             float4* dst = reinterpret_cast<float4*>(o_dst + c * 32);
 #pragma unroll
             for (int q4 = 0; q4 < 8; ++q4)
-              dst[q4] = make_float4(__uint_as_float(v[4 * q4]) * inv, __uint_as_float(v[4 * q4 + 1]) * inv,
-                                    __uint_as_float(v[4 * q4 + 2]) * inv, __uint_as_float(v[4 * q4 + 3]) * inv);
+              dst[q4] = make_float4(__uint_as_float(o[4 * q4]) * inv, __uint_as_float(o[4 * q4 + 1]) * inv,
+                                    __uint_as_float(o[4 * q4 + 2]) * inv, __uint_as_float(o[4 * q4 + 3]) * inv);
           }
         }
-        if (row_ok) {
-          const float lse = kLn2 * (m_run + ptx::lg2(l));
+        if (row_ok && half == 0) {
+          const float lse = kLn2 * (m_run + ptx::lg2(l_tot));
           if (a.splits > 1) {
             const long long o = (long long)split * a.n + grow;
             a.part_lse[o] = lse; a.part_max[o] = tmax * kLn2; a.part_arg[o] = targ + a.pattern_offset;
@@ -531,7 +604,7 @@ int make_map(CUtensorMap* m, const void* base, int rows, int cols, int box_rows,
   return HOP_OK;
 }
 
-template <int D>
+template <int D, bool kBf16>
 int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
   using Cfg = TcCfg<D>;
   const int ppad = padded_patterns(a.p);
@@ -543,7 +616,7 @@ int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
 
   TcKernelArgs k{};
   k.x_raw = a.x_raw; k.lnq_w = a.lnq_w; k.lnq_b = a.lnq_b; k.ln_eps = a.ln_eps; k.has_ln = a.has_ln; k.beta = a.beta;
-  k.qs = a.qs; k.n = a.n; k.p = a.p; k.update_steps = a.update_steps; k.bf16 = a.bf16;
+  k.qs = a.qs; k.n = a.n; k.p = a.p; k.update_steps = a.update_steps;
   const int nt_total = ppad / kTileP;
   k.tiles_per_split = (nt_total + splits - 1) / splits;
   k.splits = (nt_total + k.tiles_per_split - 1) / k.tiles_per_split;   // every split owns >= 1 tile
@@ -562,16 +635,10 @@ int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
     k.part_arg = reinterpret_cast<int32_t*>(w);
   }
 
-  static std::once_flag attr_once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(attr_once, [] {
-    attr_err = cudaFuncSetAttribute(hop_fwd_tc_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
-  });
-  // the attribute is per device: set it again cheaply when another device is current
-  HOP_CUDA(cudaFuncSetAttribute(hop_fwd_tc_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
-  (void)attr_err;
+  // the attribute is per device and cheap to set: do it on every launch so that any current device works
+  HOP_CUDA(cudaFuncSetAttribute(hop_fwd_tc_kernel<D, kBf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
   const dim3 grid((a.n + kTileM - 1) / kTileM, k.splits);
-  hop_fwd_tc_kernel<D><<<grid, kThreads, Cfg::kSmemBytes, st>>>(tk, tkt, tvt, k);
+  hop_fwd_tc_kernel<D, kBf16><<<grid, kThreads, Cfg::kSmemBytes, st>>>(tk, tkt, tvt, k);
   HOP_LAUNCH_CHECK("hop_fwd_tc_kernel");
   if (k.splits > 1) {
     const int threads = 256, rows_per_block = threads / 32;
@@ -623,10 +690,17 @@ int launch_tc_forward(const TcPassArgs& a, cudaStream_t st) {
   if (!tc_supported(a.h, a.dv)) HOP_FAIL(HOP_ERR_UNSUPPORTED, "tensor-core path needs H == Dv in {64,128,256}");
   if (!a.retrieved) HOP_FAIL(HOP_ERR_BAD_ARG, "tensor-core forward: retrieved is NULL");
   const int splits = tc_choose_splits(a.n, a.p, a.update_steps);
+  if (a.bf16) {
+    switch (a.h) {
+      case 64: return launch_d<64, true>(a, splits, st);
+      case 128: return launch_d<128, true>(a, splits, st);
+      default: return launch_d<256, true>(a, splits, st);
+    }
+  }
   switch (a.h) {
-    case 64: return launch_d<64>(a, splits, st);
-    case 128: return launch_d<128>(a, splits, st);
-    default: return launch_d<256>(a, splits, st);
+    case 64: return launch_d<64, false>(a, splits, st);
+    case 128: return launch_d<128, false>(a, splits, st);
+    default: return launch_d<256, false>(a, splits, st);
   }
 }
 
