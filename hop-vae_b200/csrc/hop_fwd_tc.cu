@@ -48,11 +48,10 @@ struct TcCfg {
   static constexpr int kBStages = D > 128 ? D / 128 : 1;  // ring stages of one read-out chunk (D rows x 64 patterns)
   static constexpr int kBRows = D / kBStages;             // rows per TMA box of the read-out operand
   static constexpr int kQBytes = kKChunks * kChunkBytes;  // Q tile
-  static constexpr int kPBytes = 2 * kChunkBytes;         // one P~ buffer (128 x 128 x 2B)
-  static constexpr int kStages = (D >= 256) ? 6 : 8;      // even: a 2-stage read-out chunk never wraps
-  static constexpr int kBarBytes = 256;                   // mbarriers + TMEM slot
+  static constexpr int kStages = (D >= 256) ? 10 : 12;    // even: a 2-stage read-out chunk never wraps
+  static constexpr int kBarBytes = 512;                   // mbarriers + TMEM slot
   static constexpr int kXchBytes = 2 * 2 * kTileM * 4;    // [parity][half][row] floats exchanged by a warp pair
-  static constexpr int kSmemBytes = kQBytes + 2 * kPBytes + kStages * kChunkBytes + kBarBytes + kXchBytes;
+  static constexpr int kSmemBytes = kQBytes + kStages * kChunkBytes + kBarBytes + kXchBytes;
   static_assert(kStages % 2 == 0 && (kKChunks % 2 == 0 || kBStages == 1), "2-stage chunks must stay pair-aligned");
 };
 
@@ -103,14 +102,12 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
   const uint32_t smem_base = ptx::smem_u32(smem_raw);
   if ((smem_base & 1023u) != 0) __trap();       // the 128B-swizzle atoms need a 1 KiB-aligned base
   const uint32_t q_smem = smem_base;
-  const uint32_t p_smem = q_smem + Cfg::kQBytes;
-  const uint32_t ring = p_smem + 2 * Cfg::kPBytes;
+  const uint32_t ring = q_smem + Cfg::kQBytes;
   const uint32_t bars = ring + Cfg::kStages * kChunkBytes;
   auto full_bar = [&](int s) { return bars + 8u * s; };
   auto empty_bar = [&](int s) { return bars + 8u * (Cfg::kStages + s); };
   const uint32_t misc = bars + 16u * Cfg::kStages;
   auto s_full = [&](int b) { return misc + 8u * b; };
-  auto s_empty = [&](int b) { return misc + 16u + 8u * b; };
   auto p_full = [&](int b) { return misc + 32u + 8u * b; };
   auto p_empty = [&](int b) { return misc + 48u + 8u * b; };
   const uint32_t q_ready = misc + 64u;
@@ -128,7 +125,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
   if (threadIdx.x == 0) {
     for (int s = 0; s < Cfg::kStages; ++s) { ptx::mbar_init(full_bar(s), 1); ptx::mbar_init(empty_bar(s), 1); }
     for (int b = 0; b < 2; ++b) {
-      ptx::mbar_init(s_full(b), 1); ptx::mbar_init(s_empty(b), kSoftmaxThreads);
+      ptx::mbar_init(s_full(b), 1);
       ptx::mbar_init(p_full(b), kSoftmaxThreads); ptx::mbar_init(p_empty(b), 1);
     }
     ptx::mbar_init(q_ready, kSoftmaxThreads);
@@ -186,9 +183,9 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         ptx::mbar_wait(q_ready, pass & 1);
         ptx::tc_fence_after();
         auto issue_qk = [&](uint32_t gg) {
+          // S buffer b also holds P~ of tile gg-2: its read-out MMA was issued before this point and
+          // tcgen05.mma instructions of one thread execute in issue order, so no barrier is needed
           const int b = gg & 1;
-          ptx::mbar_wait(s_empty(b), ((gg >> 1) & 1) ^ 1);
-          ptx::tc_fence_after();
           for (int kc = 0; kc < Cfg::kKChunks; ++kc) {
             const int s = it % Cfg::kStages;
             ptx::mbar_wait(full_bar(s), (it / Cfg::kStages) & 1);
@@ -218,11 +215,11 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
               ptx::mbar_wait(full_bar(i2 % Cfg::kStages), (i2 / Cfg::kStages) & 1);
             }
             ptx::tc_fence_after();
-            const uint64_t ad = ptx::umma_desc_sw128(p_smem + b * Cfg::kPBytes + kc * kChunkBytes);
+            const uint32_t at = tmem_base + b * kTileP + kc * 32;   // P~ (16-bit pairs) aliases the S buffer
             const uint64_t bd = ptx::umma_desc_sw128(ring + s * kChunkBytes);
 #pragma unroll
             for (int k = 0; k < 4; ++k)
-              ptx::umma_f16_ss(tmem_base + kTmemO, ad + 2 * k, bd + 2 * k, idesc_pv, (j | kc | k) != 0);
+              ptx::umma_f16_ts(tmem_base + kTmemO, at + 8 * k, bd + 2 * k, idesc_pv, (j | kc | k) != 0);
             for (int bs = 0; bs < Cfg::kBStages; ++bs) {
               ptx::umma_commit(empty_bar(it % Cfg::kStages));
               ++it;
@@ -347,8 +344,6 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         ptx::tmem_ld_x32p(s_addr, v);
         ptx::tmem_ld_x32p(s_addr + 32, v + 32);
         ptx::tmem_wait_ld();
-        ptx::tc_fence_before();
-        ptx::mbar_arrive(s_empty(b));
         if (valid < kHalfP) {
 #pragma unroll
           for (int i = 0; i < kHalfP; ++i)
@@ -412,26 +407,23 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
           m_run = m_new;
         }
 
-        // P~ = 2^(s - m_run) as 16-bit into this half's 64-column chunk of the swizzled A-operand buffer
-        ptx::mbar_wait(p_empty(b), ((gg >> 1) & 1) ^ 1);
-        const uint32_t p_addr = p_smem + b * Cfg::kPBytes + half * kChunkBytes;
+        // P~ = 2^(s - m_run) as 16-bit pairs into TMEM, over the first 64 columns of the S buffer just read
+        // (this half's 64 patterns -> columns 32h..32h+31; the partner finished its tcgen05.ld of those
+        // columns before the pair barrier above); the A operand of the read-out MMA
         float ls[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
         for (int i = 0; i < kHalfP; ++i) v[i] = __float_as_uint(ptx::ex2(__uint_as_float(v[i]) - m_run));
+        uint32_t pk[32];
 #pragma unroll
-        for (int c16 = 0; c16 < 8; ++c16) {         // 16-byte chunk = 8 patterns
-          uint32_t pk[4];
-#pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            const float p0 = __uint_as_float(v[c16 * 8 + 2 * u]);
-            const float p1 = __uint_as_float(v[c16 * 8 + 2 * u + 1]);
-            ls[u] += p0 + p1;
-            pk[u] = pack16<kBf16>(p0, p1);
-          }
-          st_shared_v4(p_addr + sw128_off(row, c16), pk[0], pk[1], pk[2], pk[3]);
+        for (int i = 0; i < 32; ++i) {
+          const float p0 = __uint_as_float(v[2 * i]), p1 = __uint_as_float(v[2 * i + 1]);
+          ls[i & 3] += p0 + p1;
+          pk[i] = pack16<kBf16>(p0, p1);
         }
+        ptx::tmem_st_x32(lane_base + b * kTileP + half * 32, pk);
         l += (ls[0] + ls[1]) + (ls[2] + ls[3]);
-        ptx::fence_proxy_async_smem();
+        ptx::tmem_wait_st();
+        ptx::tc_fence_before();
         ptx::mbar_arrive(p_full(b));
       }
 
