@@ -193,7 +193,7 @@ class RawForward:
         pack = layer.param_pack()
         self.keep = pack
         self.pats_t = layer._prepared(pack, spec, path)
-        khat, vhat, k16, kt16, vt16 = self.pats_t
+        khat, vhat, k16, kt16, vt16 = self.pats_t[:5]
         dev = x_dev.device
         self.x = x_dev
         self.out = torch.empty((n, spec.d_v), device=dev)

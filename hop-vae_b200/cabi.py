@@ -13,7 +13,7 @@ from typing import Optional
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libhop_sm100.so")
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 # hop_desc.flags
 F_NORM_STATE, F_NORM_STORED, F_NORM_PROJ = 1 << 0, 1 << 1, 1 << 2
@@ -38,7 +38,7 @@ class HopDesc(C.Structure):
 
 _PARAM_FIELDS = ["lookup", "lookup_targets", "ln_state_w", "ln_state_b", "ln_stored_w", "ln_stored_b",
                  "ln_proj_w", "ln_proj_b", "wq", "bq", "wk", "bk", "wv", "bv", "wo", "bo"]
-_PATTERN_FIELDS = ["khat", "vhat", "k16", "kt16", "vt16"]
+_PATTERN_FIELDS = ["khat", "vhat", "k16", "kt16", "vt16", "vot16"]
 _GRAD_FIELDS = ["d_x", "d_lookup", "d_lookup_targets", "d_ln_state_w", "d_ln_state_b", "d_ln_stored_w",
                 "d_ln_stored_b", "d_ln_proj_w", "d_ln_proj_b", "d_wq", "d_bq", "d_wk", "d_bk", "d_wv", "d_bv",
                 "d_wo", "d_bo"]
@@ -83,7 +83,7 @@ def load() -> C.CDLL:
     lib.hop_sm100_select_path.restype = C.c_int
     lib.hop_sm100_select_path.argtypes = [P(HopDesc), P(C.c_int32)]
     lib.hop_sm100_pattern_bytes.restype = C.c_int
-    lib.hop_sm100_pattern_bytes.argtypes = [P(HopDesc)] + [P(C.c_size_t)] * 5
+    lib.hop_sm100_pattern_bytes.argtypes = [P(HopDesc)] + [P(C.c_size_t)] * 6
     lib.hop_sm100_workspace_bytes.restype = C.c_int
     lib.hop_sm100_workspace_bytes.argtypes = [P(HopDesc), C.c_int, P(C.c_size_t)]
     lib.hop_sm100_prepare_patterns.restype = C.c_int

@@ -70,6 +70,11 @@ int validate_desc(const hop_desc* d) {
   return HOP_OK;
 }
 
+// out_proj can be folded into the read-out operand when the fused kernel's single width serves it
+bool out_proj_foldable(const hop_desc& d) {
+  return (d.flags & HOP_F_OUT_PROJ) && d.d_out == d.d_assoc && tc_supported(d.d_assoc, d.d_v);
+}
+
 int resolve_path(const hop_desc* d) {
   if (d->path == HOP_PATH_FP32_SIMT) return HOP_PATH_FP32_SIMT;
   const bool tc_ok = tc_supported(d->d_assoc, d->d_v);
@@ -109,7 +114,7 @@ int hop_sm100_select_path(const hop_desc* desc, int32_t* path_out) {
 }
 
 int hop_sm100_pattern_bytes(const hop_desc* desc, size_t* khat, size_t* vhat, size_t* k16, size_t* kt16,
-                            size_t* vt16) {
+                            size_t* vt16, size_t* vot16) {
   HOP_TRY(validate_desc(desc));
   const int path = resolve_path(desc);
   if (path < 0) return -path;
@@ -120,6 +125,7 @@ int hop_sm100_pattern_bytes(const hop_desc* desc, size_t* khat, size_t* vhat, si
   if (k16) *k16 = tc ? Pp * desc->d_assoc * 2 : 0;
   if (kt16) *kt16 = (tc && desc->update_steps > 0) ? Pp * desc->d_assoc * 2 : 0;
   if (vt16) *vt16 = tc ? Pp * desc->d_v * 2 : 0;
+  if (vot16) *vot16 = (tc && out_proj_foldable(*desc)) ? Pp * desc->d_out * 2 : 0;
   return HOP_OK;
 }
 
@@ -153,6 +159,8 @@ int hop_sm100_prepare_patterns(const hop_desc* desc, const hop_params* params, c
       HOP_FAIL(HOP_ERR_BAD_ARG, "tensor-core path needs the k16 / vt16 (/ kt16 when T > 0) buffers");
     if (!aligned16(patterns->k16) || !aligned16(patterns->vt16) || !aligned16(patterns->kt16))
       HOP_FAIL(HOP_ERR_BAD_ALIGN, "16-bit pattern packs must be 16-byte aligned");
+    if (patterns->vot16 && (!out_proj_foldable(*desc) || !params->wo || !aligned16(patterns->vot16)))
+      HOP_FAIL(HOP_ERR_BAD_ARG, "vot16 given but out_proj cannot be folded (needs HOP_F_OUT_PROJ, Dout == H == Dv, wo, alignment)");
   }
   if (!aligned16(params->lookup) || !aligned16(patterns->khat) || !aligned16(patterns->vhat))
     HOP_FAIL(HOP_ERR_BAD_ALIGN, "lookup / khat / vhat must be 16-byte aligned");
@@ -177,7 +185,8 @@ int hop_sm100_forward(const hop_desc* desc, const hop_params* params, const hop_
   const bool q_proj = (d.flags & HOP_F_PROJ_STATE) != 0;
   const size_t tc_ws = (path != HOP_PATH_FP32_SIMT) ? tc_forward_workspace(d.n_rows, d.n_patterns, d.d_assoc, d.update_steps) : 0;
   const bool need_ws = q_proj || (path == HOP_PATH_FP32_SIMT && d.update_steps > 0) || tc_ws > 0 ||
-                       (path != HOP_PATH_FP32_SIMT && out_proj && !retrieved);
+                       (path != HOP_PATH_FP32_SIMT && out_proj && !retrieved &&
+                        !(patterns->vot16 && out_proj_foldable(d)));
   if (need_ws && (!workspace || workspace_bytes < need))
     HOP_FAIL(HOP_ERR_WORKSPACE, "workspace of %zu bytes needed, %zu given", need, workspace_bytes);
   if (out_proj && (!p.wo)) HOP_FAIL(HOP_ERR_BAD_ARG, "HOP_F_OUT_PROJ set but params.wo is NULL");
@@ -225,19 +234,23 @@ int hop_sm100_forward(const hop_desc* desc, const hop_params* params, const hop_
     return HOP_OK;
   }
 
-  // tensor-core path: one persistent kernel runs all T+1 passes; out_proj is a second (HBM-bound) launch
+  // tensor-core path: one persistent kernel runs all T+1 passes.  With the folded operand (V^ Wo^T)^T the
+  // kernel's read-out IS the layer output; otherwise out_proj is a second (HBM-bound) launch.
+  const bool folded = out_proj && !retrieved && patterns->vot16 && out_proj_foldable(d);
   TcPassArgs a{};
   a.x_raw = qs ? nullptr : x; a.lnq_w = p.ln_state_w; a.lnq_b = p.ln_state_b; a.ln_eps = d.ln_eps;
   a.has_ln = (d.flags & HOP_F_NORM_STATE) ? 1 : 0; a.beta = d.beta; a.qs = qs;
-  a.k16 = patterns->k16; a.kt16 = patterns->kt16; a.vt16 = patterns->vt16;
+  a.k16 = patterns->k16; a.kt16 = patterns->kt16; a.vt16 = folded ? patterns->vot16 : patterns->vt16;
+  a.bias = folded ? p.bo : nullptr;
   a.n = d.n_rows; a.p = d.n_patterns; a.h = d.d_assoc; a.dv = d.d_v; a.update_steps = d.update_steps;
   a.bf16 = (path == HOP_PATH_TC_BF16);
-  a.retrieved = out_proj ? (retrieved ? retrieved : rbuf) : out;
+  a.retrieved = folded ? out : (out_proj ? (retrieved ? retrieved : rbuf) : out);
   a.qsave = qhat; a.lse = lse; a.argmax = argmax; a.rowmax = rowmax; a.pattern_offset = d.pattern_offset;
   a.ws = workspace ? static_cast<char*>(workspace) + 2 * qbytes + round_up_sz((size_t)d.n_rows * d.d_v * sizeof(float), 256)
                    : nullptr;
   a.ws_bytes = tc_ws;
   HOP_TRY(launch_tc_forward(a, st));
+  if (folded) return HOP_OK;
   if (out_proj) HOP_TRY(launch_linear(d.n_rows, d.d_v, d.d_out, a.retrieved, p.wo, p.bo, out, st));
   else if (retrieved && retrieved != out)
     HOP_CUDA(cudaMemcpyAsync(retrieved, out, (size_t)d.n_rows * d.d_v * sizeof(float), cudaMemcpyDeviceToDevice, st));

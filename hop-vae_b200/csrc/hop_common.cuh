@@ -54,6 +54,7 @@ static inline int padded_patterns(int p) { return round_up(p, 128); }
 int validate_desc(const hop_desc* d);   // common checks, sets error
 int resolve_path(const hop_desc* d);    // HOP_PATH_* actually run (never AUTO), <0 on error
 int num_sms();
+bool out_proj_foldable(const hop_desc& d);  // HOP_F_OUT_PROJ can be folded into the TC read-out operand
 
 // Entry points implemented per translation unit ------------------------------
 // hop_prep.cu
@@ -92,6 +93,7 @@ struct TcPassArgs {
   const float* x_raw; const float* lnq_w; const float* lnq_b; float ln_eps; int has_ln; float beta;
   const float* qs;          // prepared beta*Q^ (N,H) fp32 if x_raw == nullptr
   const void* k16; const void* kt16; const void* vt16;
+  const float* bias;        // (Dv) added to the read-out (folded out_proj bias) or nullptr
   int n, p, h, dv, update_steps; int bf16;
   float* retrieved;         // (N,Dv)
   float* qsave;             // (N,H) or nullptr

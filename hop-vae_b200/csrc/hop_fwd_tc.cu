@@ -57,7 +57,7 @@ struct TcCfg {
 
 struct TcKernelArgs {
   const float* x_raw; const float* lnq_w; const float* lnq_b; float ln_eps; int has_ln; float beta;
-  const float* qs;
+  const float* qs; const float* bias;
   int n, p, update_steps;
   int splits, tiles_per_split;          // pattern tiles (of 128) handled by one CTA
   float* retrieved; float* qsave; float* lse; int32_t* argmax; float* rowmax; int pattern_offset;
@@ -486,10 +486,14 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
           ptx::tmem_wait_ld();
           if (row_ok) {
             float4* dst = reinterpret_cast<float4*>(o_dst + c * 32);
+            const float4* bia = (a.bias && a.splits == 1) ? reinterpret_cast<const float4*>(a.bias + c * 32) : nullptr;
 #pragma unroll
-            for (int q4 = 0; q4 < 8; ++q4)
-              dst[q4] = make_float4(__uint_as_float(o[4 * q4]) * inv, __uint_as_float(o[4 * q4 + 1]) * inv,
-                                    __uint_as_float(o[4 * q4 + 2]) * inv, __uint_as_float(o[4 * q4 + 3]) * inv);
+            for (int q4 = 0; q4 < 8; ++q4) {
+              float4 r = make_float4(__uint_as_float(o[4 * q4]) * inv, __uint_as_float(o[4 * q4 + 1]) * inv,
+                                     __uint_as_float(o[4 * q4 + 2]) * inv, __uint_as_float(o[4 * q4 + 3]) * inv);
+              if (bia) { const float4 bb = __ldg(bia + q4); r.x += bb.x; r.y += bb.y; r.z += bb.z; r.w += bb.w; }
+              dst[q4] = r;
+            }
           }
         }
         if (row_ok && half == 0) {
@@ -520,8 +524,9 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
 template <int D>
 __global__ void tc_combine_kernel(int n, int splits, const float* __restrict__ part_o,
                                   const float* __restrict__ part_lse, const float* __restrict__ part_max,
-                                  const int32_t* __restrict__ part_arg, float* __restrict__ retrieved,
-                                  float* __restrict__ lse, int32_t* __restrict__ argmax, float* __restrict__ rowmax) {
+                                  const int32_t* __restrict__ part_arg, const float* __restrict__ bias,
+                                  float* __restrict__ retrieved, float* __restrict__ lse,
+                                  int32_t* __restrict__ argmax, float* __restrict__ rowmax) {
   const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp_global >= n) return;
   const long long r = warp_global;
@@ -533,7 +538,10 @@ __global__ void tc_combine_kernel(int n, int splits, const float* __restrict__ p
   constexpr int kVec = (D + 127) / 128;
   float4 acc[kVec];
 #pragma unroll
-  for (int v = 0; v < kVec; ++v) acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int v = 0; v < kVec; ++v) {
+    const int e = lane * 4 + v * 128;
+    acc[v] = (bias && e < D) ? __ldg(reinterpret_cast<const float4*>(bias + e)) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
   float best = -INFINITY;
   int arg = 0;
   for (int s = 0; s < splits; ++s) {
@@ -608,7 +616,7 @@ int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
 
   TcKernelArgs k{};
   k.x_raw = a.x_raw; k.lnq_w = a.lnq_w; k.lnq_b = a.lnq_b; k.ln_eps = a.ln_eps; k.has_ln = a.has_ln; k.beta = a.beta;
-  k.qs = a.qs; k.n = a.n; k.p = a.p; k.update_steps = a.update_steps;
+  k.qs = a.qs; k.bias = a.bias; k.n = a.n; k.p = a.p; k.update_steps = a.update_steps;
   const int nt_total = ppad / kTileP;
   k.tiles_per_split = (nt_total + splits - 1) / splits;
   k.splits = (nt_total + k.tiles_per_split - 1) / k.tiles_per_split;   // every split owns >= 1 tile
@@ -635,7 +643,7 @@ int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
   if (k.splits > 1) {
     const int threads = 256, rows_per_block = threads / 32;
     tc_combine_kernel<D><<<(a.n + rows_per_block - 1) / rows_per_block, threads, 0, st>>>(
-        a.n, k.splits, k.part_o, k.part_lse, k.part_max, k.part_arg, a.retrieved, a.lse, a.argmax, a.rowmax);
+        a.n, k.splits, k.part_o, k.part_lse, k.part_max, k.part_arg, a.bias, a.retrieved, a.lse, a.argmax, a.rowmax);
     HOP_LAUNCH_CHECK("tc_combine_kernel");
   }
   return HOP_OK;

@@ -194,6 +194,15 @@ int launch_prepare_patterns(const hop_desc& d, const hop_params& p, const hop_pa
   v.bf16 = (path == HOP_PATH_TC_BF16);
   if ((d.flags & HOP_F_PROJ_PATTERN) && !p.wv) HOP_FAIL(HOP_ERR_BAD_ARG, "HOP_F_PROJ_PATTERN set but params.wv is NULL");
   HOP_TRY(launch_ln_linear(v, st));
+
+  if (tc && pt.vot16) {
+    // out_proj folded into the read-out operand: (V^ Wo^T)^T, 16-bit, from the fp32 V^ just written
+    LnLinearArgs o{};
+    o.x = pt.vhat; o.rows = d.n_patterns; o.rows_pad = ppad; o.din = d.d_v; o.has_ln = 0; o.ln_eps = 0.f;
+    o.w = p.wo; o.b = nullptr; o.dout = d.d_out; o.scale = 1.f; o.y = nullptr; o.y16 = nullptr; o.yt16 = pt.vot16;
+    o.bf16 = (path == HOP_PATH_TC_BF16);
+    HOP_TRY(launch_ln_linear(o, st));
+  }
   return HOP_OK;
 }
 

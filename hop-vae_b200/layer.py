@@ -249,7 +249,8 @@ class HopfieldLayer(nn.Module):
             pats = self._prepared(pack, spec, path)
             res = retrieve_op(x.detach(), *pats, *[None if pack[k] is None else pack[k].detach().contiguous()
                                                    for k in _QUERY_SIDE],
-                              spec.flags, path, spec.d_in, spec.d_out, spec.update_steps, spec.beta, spec.ln_eps, 0)
+                              spec.flags, path, spec.d_in, spec.d_out, spec.update_steps, spec.beta, spec.ln_eps, 0,
+                              False)
             out, argmax = res[0], res[4]
             self.last_lse = res[3]
         self.last_argmax = argmax

@@ -16,7 +16,7 @@ from torch import Tensor
 from . import cabi
 
 _PATTERN_SIDE = ("lookup", "lookup_targets", "ln_stored_w", "ln_stored_b", "ln_proj_w", "ln_proj_b",
-                 "wk", "bk", "wv", "bv")
+                 "wk", "bk", "wv", "bv", "wo")
 _QUERY_SIDE = ("ln_state_w", "ln_state_b", "wq", "bq", "wo", "bo")
 
 
@@ -70,19 +70,21 @@ def resolve_path(spec: LayerSpec, n_rows: int, n_patterns: int) -> int:
 def prepare_patterns_op(lookup: Tensor, lookup_targets: Optional[Tensor], ln_stored_w: Optional[Tensor],
                         ln_stored_b: Optional[Tensor], ln_proj_w: Optional[Tensor], ln_proj_b: Optional[Tensor],
                         wk: Optional[Tensor], bk: Optional[Tensor], wv: Optional[Tensor], bv: Optional[Tensor],
-                        flags: int, path: int, d_assoc: int, d_v: int, update_steps: int,
+                        wo: Optional[Tensor], flags: int, path: int, d_assoc: int, d_v: int, update_steps: int,
                         ln_eps: float) -> List[Tensor]:
-    """lookup (P, Din) -> [khat (P,H), vhat (P,Dv), k16, kt16, vt16] (16-bit packs empty on the fp32 path).
+    """lookup (P, Din) -> [khat (P,H), vhat (P,Dv), k16, kt16, vt16, vot16] (16-bit packs empty on the fp32
+    path; vot16 = out_proj folded into the read-out operand, only when Dout == H == Dv).
     `path` must already be resolved (not AUTO)."""
     import ctypes as C
     lib = cabi.load()
     for name, t in (("lookup", lookup), ("lookup_targets", lookup_targets), ("ln_stored_w", ln_stored_w),
                     ("ln_stored_b", ln_stored_b), ("ln_proj_w", ln_proj_w), ("ln_proj_b", ln_proj_b), ("wk", wk),
-                    ("bk", bk), ("wv", wv), ("bv", bv)):
+                    ("bk", bk), ("wv", wv), ("bv", bv), ("wo", wo)):
         _req_cuda_f32(t, name)
     P, d_in = lookup.shape
-    d = _desc(flags, path, 1, P, d_in, d_assoc, d_v, 1, update_steps, 1.0, ln_eps)
-    sizes = [C.c_size_t(0) for _ in range(5)]
+    d_out = wo.shape[0] if (wo is not None and (flags & cabi.F_OUT_PROJ)) else 1
+    d = _desc(flags, path, 1, P, d_in, d_assoc, d_v, d_out, update_steps, 1.0, ln_eps)
+    sizes = [C.c_size_t(0) for _ in range(6)]
     cabi.check(lib.hop_sm100_pattern_bytes(C.byref(d), *[C.byref(s) for s in sizes]), "hop_sm100_pattern_bytes")
     dev = lookup.device
     khat = torch.empty((P, d_assoc), device=dev, dtype=torch.float32)
@@ -91,11 +93,12 @@ def prepare_patterns_op(lookup: Tensor, lookup_targets: Optional[Tensor], ln_sto
     params = cabi.HopParams(lookup=cabi.ptr(lookup), lookup_targets=cabi.ptr(lookup_targets),
                             ln_stored_w=cabi.ptr(ln_stored_w), ln_stored_b=cabi.ptr(ln_stored_b),
                             ln_proj_w=cabi.ptr(ln_proj_w), ln_proj_b=cabi.ptr(ln_proj_b), wk=cabi.ptr(wk),
-                            bk=cabi.ptr(bk), wv=cabi.ptr(wv), bv=cabi.ptr(bv))
+                            bk=cabi.ptr(bk), wv=cabi.ptr(wv), bv=cabi.ptr(bv), wo=cabi.ptr(wo))
     pats = cabi.HopPatterns(khat=cabi.ptr(khat), vhat=cabi.ptr(vhat),
                             k16=cabi.ptr(packs[0]) if packs[0].numel() else None,
                             kt16=cabi.ptr(packs[1]) if packs[1].numel() else None,
-                            vt16=cabi.ptr(packs[2]) if packs[2].numel() else None)
+                            vt16=cabi.ptr(packs[2]) if packs[2].numel() else None,
+                            vot16=cabi.ptr(packs[3]) if packs[3].numel() else None)
     with torch.cuda.device(dev):
         cabi.check(lib.hop_sm100_prepare_patterns(C.byref(d), C.byref(params), C.byref(pats), _stream()),
                    "hop_sm100_prepare_patterns")
@@ -103,24 +106,29 @@ def prepare_patterns_op(lookup: Tensor, lookup_targets: Optional[Tensor], ln_sto
 
 
 @prepare_patterns_op.register_fake
-def _(lookup, lookup_targets, ln_stored_w, ln_stored_b, ln_proj_w, ln_proj_b, wk, bk, wv, bv, flags, path, d_assoc,
-      d_v, update_steps, ln_eps):
+def _(lookup, lookup_targets, ln_stored_w, ln_stored_b, ln_proj_w, ln_proj_b, wk, bk, wv, bv, wo, flags, path,
+      d_assoc, d_v, update_steps, ln_eps):
     P = lookup.shape[0]
     ppad = (P + 127) // 128 * 128
     tc = path in (cabi.PATH_TC_F16, cabi.PATH_TC_BF16)
     mk = lambda n: lookup.new_empty((n,), dtype=torch.int16)
+    fold = (tc and wo is not None and bool(flags & cabi.F_OUT_PROJ) and wo.shape[0] == d_assoc == d_v
+            and d_assoc in (64, 128, 256))
     return [lookup.new_empty((P, d_assoc)), lookup.new_empty((P, d_v)), mk(ppad * d_assoc if tc else 0),
-            mk(ppad * d_assoc if tc and update_steps > 0 else 0), mk(ppad * d_v if tc else 0)]
+            mk(ppad * d_assoc if tc and update_steps > 0 else 0), mk(ppad * d_v if tc else 0),
+            mk(ppad * d_assoc if fold else 0)]
 
 
 # --------------------------------------------------------------------------- retrieve (forward)
 @torch.library.custom_op("hop_sm100::retrieve", mutates_args=(), device_types="cuda")
-def retrieve_op(x: Tensor, khat: Tensor, vhat: Tensor, k16: Tensor, kt16: Tensor, vt16: Tensor,
+def retrieve_op(x: Tensor, khat: Tensor, vhat: Tensor, k16: Tensor, kt16: Tensor, vt16: Tensor, vot16: Tensor,
                 ln_state_w: Optional[Tensor], ln_state_b: Optional[Tensor], wq: Optional[Tensor],
                 bq: Optional[Tensor], wo: Optional[Tensor], bo: Optional[Tensor], flags: int, path: int,
                 d_in: int, d_out: int, update_steps: int, beta: float, ln_eps: float,
-                pattern_offset: int) -> List[Tensor]:
-    """x (N, Din) -> [out (N,Dout|Dv), retrieved (N,Dv), qhat (N,H), lse (N), argmax (N) int32, rowmax (N)]."""
+                pattern_offset: int, want_retrieved: bool = True) -> List[Tensor]:
+    """x (N, Din) -> [out (N,Dout|Dv), retrieved (N,Dv), qhat (N,H), lse (N), argmax (N) int32, rowmax (N)].
+    With want_retrieved=False and a folded read-out operand (vot16) the tensor-core kernel writes `out`
+    directly and `retrieved` is returned empty."""
     import ctypes as C
     lib = cabi.load()
     for name, t in (("x", x), ("khat", khat), ("vhat", vhat), ("ln_state_w", ln_state_w), ("ln_state_b", ln_state_b),
@@ -133,7 +141,11 @@ def retrieve_op(x: Tensor, khat: Tensor, vhat: Tensor, k16: Tensor, kt16: Tensor
     d = _desc(flags, path, N, P, d_in, H, Dv, d_out if out_proj else 1, update_steps, beta, ln_eps, pattern_offset)
     dev = x.device
     out = torch.empty((N, d_out if out_proj else Dv), device=dev, dtype=torch.float32)
-    retrieved = torch.empty((N, Dv), device=dev, dtype=torch.float32) if out_proj else out
+    folded = out_proj and not want_retrieved and vot16.numel() > 0 and path != cabi.PATH_FP32_SIMT
+    if folded:
+        retrieved = None
+    else:
+        retrieved = torch.empty((N, Dv), device=dev, dtype=torch.float32) if out_proj else out
     qhat = torch.empty((N, H), device=dev, dtype=torch.float32)
     lse = torch.empty((N,), device=dev, dtype=torch.float32)
     rowmax = torch.empty((N,), device=dev, dtype=torch.float32)
@@ -147,22 +159,27 @@ def retrieve_op(x: Tensor, khat: Tensor, vhat: Tensor, k16: Tensor, kt16: Tensor
     pats = cabi.HopPatterns(khat=cabi.ptr(khat), vhat=cabi.ptr(vhat),
                             k16=cabi.ptr(k16) if k16.numel() else None,
                             kt16=cabi.ptr(kt16) if kt16.numel() else None,
-                            vt16=cabi.ptr(vt16) if vt16.numel() else None)
+                            vt16=cabi.ptr(vt16) if vt16.numel() else None,
+                            vot16=cabi.ptr(vot16) if vot16.numel() else None)
     with torch.cuda.device(dev):
         cabi.check(lib.hop_sm100_forward(C.byref(d), C.byref(params), C.byref(pats), cabi.ptr(x), cabi.ptr(out),
                                          cabi.ptr(retrieved), cabi.ptr(qhat), cabi.ptr(lse), cabi.ptr(argmax),
                                          cabi.ptr(rowmax), cabi.ptr(ws), int(need.value) if use_ws else 0,
                                          _stream()), "hop_sm100_forward")
+    if folded:
+        return [out, torch.empty((0, Dv), device=dev, dtype=torch.float32), qhat, lse, argmax, rowmax]
     return [out, retrieved if out_proj else out.clone(), qhat, lse, argmax, rowmax]
 
 
 @retrieve_op.register_fake
-def _(x, khat, vhat, k16, kt16, vt16, ln_state_w, ln_state_b, wq, bq, wo, bo, flags, path, d_in, d_out, update_steps,
-      beta, ln_eps, pattern_offset):
+def _(x, khat, vhat, k16, kt16, vt16, vot16, ln_state_w, ln_state_b, wq, bq, wo, bo, flags, path, d_in, d_out,
+      update_steps, beta, ln_eps, pattern_offset, want_retrieved=True):
     N = x.shape[0]
     H, Dv = khat.shape[1], vhat.shape[1]
     out_w = d_out if (flags & cabi.F_OUT_PROJ) else Dv
-    return [x.new_empty((N, out_w)), x.new_empty((N, Dv)), x.new_empty((N, H)), x.new_empty((N,)),
+    folded = (bool(flags & cabi.F_OUT_PROJ) and not want_retrieved and vot16.numel() > 0
+              and path != cabi.PATH_FP32_SIMT)
+    return [x.new_empty((N, out_w)), x.new_empty((0 if folded else N, Dv)), x.new_empty((N, H)), x.new_empty((N,)),
             x.new_empty((N,), dtype=torch.int32), x.new_empty((N,))]
 
 

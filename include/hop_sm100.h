@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define HOP_SM100_ABI_VERSION 1u
+#define HOP_SM100_ABI_VERSION 2u
 
 typedef enum hop_status {
   HOP_OK = 0,
@@ -113,6 +113,10 @@ typedef struct hop_patterns {
   void*  k16;    /* K^ 16-bit, K-major for the score MMA (Ppad, H)                     */
   void*  kt16;   /* K^ transposed, for retrieve updates  (H, Ppad)  (T > 0 only)       */
   void*  vt16;   /* V^ transposed, for the read-out MMA  (Dv, Ppad)                    */
+  void*  vot16;  /* (V^ . Wo^T) transposed (Dout, Ppad): upstream `out_proj` folded into
+                    the read-out operand, A.(V^ Wo^T) + bo == (A.V^) Wo^T + bo; written and
+                    used on the tensor-core paths when HOP_F_OUT_PROJ and Dout == H == Dv,
+                    so that inference needs no separate out-projection launch            */
 } hop_patterns;
 
 /* Gradients written (overwritten, not accumulated) by hop_sm100_backward.
@@ -140,9 +144,9 @@ const char* hop_sm100_last_error(void);
  * fp32 kernels for small problems or H < 16, the tcgen05 kernels otherwise.  */
 int hop_sm100_select_path(const hop_desc* desc, int32_t* path_out);
 
-/* Byte sizes of the five hop_patterns buffers (0 where not needed).          */
+/* Byte sizes of the six hop_patterns buffers (0 where not needed).           */
 int hop_sm100_pattern_bytes(const hop_desc* desc, size_t* khat, size_t* vhat,
-                            size_t* k16, size_t* kt16, size_t* vt16);
+                            size_t* k16, size_t* kt16, size_t* vt16, size_t* vot16);
 
 /* Workspace bytes needed by forward (for_backward == 0) or backward (!= 0).  */
 int hop_sm100_workspace_bytes(const hop_desc* desc, int for_backward, size_t* bytes);
@@ -167,7 +171,10 @@ int hop_sm100_prepare_patterns(const hop_desc* desc, const hop_params* params,
  *   argmax     (N)        index of the nearest (highest-score) pattern, + pattern_offset
  * When sharded, `out` of each shard is the shard-local normalised result and
  * (`retrieved`, `lse`, `argmax`, `rowmax`) feed hop_sm100_merge_shards.
- *   rowmax     (N)        max score of the last pass (optional, NULL ok)     */
+ *   rowmax     (N)        max score of the last pass (optional, NULL ok)
+ * On the tensor-core paths, when `retrieved` is NULL and patterns->vot16 is
+ * given, the folded read-out operand is used and `out` comes straight from the
+ * fused kernel (no out-projection launch).                                   */
 int hop_sm100_forward(const hop_desc* desc, const hop_params* params,
                       const hop_patterns* patterns, const float* x,
                       float* out, float* retrieved, float* qhat, float* lse,

@@ -34,7 +34,7 @@ def test_library_exports_every_declared_symbol(impl):
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in include/hop_sm100.h but not exported"
     assert sorted(impl.cabi.EXPORTS) == declared
-    assert lib.hop_sm100_version() == impl.cabi.ABI_VERSION == 1
+    assert lib.hop_sm100_version() == impl.cabi.ABI_VERSION == 2
 
 
 def test_struct_layouts_match_c(impl, tmp_path):
@@ -66,16 +66,20 @@ def test_error_reporting_without_gpu(impl):
     assert lib.hop_sm100_select_path(C.byref(d), C.byref(out)) == 1
     with pytest.raises(RuntimeError, match="HOP_ERR_BAD_ARG"):
         cb.check(1, "probe")
-    d.abi_version = 1
+    d.abi_version = cb.ABI_VERSION
     assert lib.hop_sm100_select_path(C.byref(d), C.byref(out)) == 0 and out.value == cb.PATH_FP32_SIMT
     # the reference's own shapes stay on the exact fp32 kernels; the big sweep goes to tcgen05
     big = cb.make_desc(flags=0, path=0, n_rows=16384, n_patterns=65536, d_in=256, d_assoc=256, d_v=256, d_out=256,
                        update_steps=0, beta=1 / 16)
     assert lib.hop_sm100_select_path(C.byref(big), C.byref(out)) == 0
     assert out.value in (cb.PATH_TC_F16, cb.PATH_FP32_SIMT)
-    sizes = [C.c_size_t(0) for _ in range(5)]
+    sizes = [C.c_size_t(0) for _ in range(6)]
     assert lib.hop_sm100_pattern_bytes(C.byref(big), *[C.byref(s) for s in sizes]) == 0
     assert sizes[0].value == 65536 * 256 * 4
+    assert sizes[5].value == 0                      # no HOP_F_OUT_PROJ -> nothing to fold
+    big.flags = cb.F_OUT_PROJ
+    assert lib.hop_sm100_pattern_bytes(C.byref(big), *[C.byref(s) for s in sizes]) == 0
+    assert sizes[5].value == (65536 * 256 * 2 if out.value == cb.PATH_TC_F16 else 0)
 
 
 def test_constructor_signature_mirrors_upstream(impl):

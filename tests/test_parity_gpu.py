@@ -285,7 +285,7 @@ def test_pattern_sharded_merge_single_gpu(hf, G):
             sl = slice(gidx * per, (gidx + 1) * per)
             pats = impl.prepare_patterns_op(pack["lookup"][sl].contiguous(), None, pack["ln_stored_w"],
                                             pack["ln_stored_b"], pack["ln_proj_w"], pack["ln_proj_b"], None, None,
-                                            pack["wv"], pack["bv"], spec.flags, impl.cabi.PATH_FP32_SIMT,
+                                            pack["wv"], pack["bv"], None, spec.flags, impl.cabi.PATH_FP32_SIMT,
                                             spec.d_assoc, spec.d_v, 0, spec.ln_eps)
             res = impl.retrieve_op(x.cuda(), *pats, pack["ln_state_w"], pack["ln_state_b"], None, None, None, None,
                                    spec.flags, impl.cabi.PATH_FP32_SIMT, spec.d_in, spec.d_out, 0, spec.beta,
@@ -368,3 +368,31 @@ def test_tensor_core_bf16_runs(hf):
         r = rel_l2(dut(x.cuda()), ref(x[None])[0])
     print(f"bf16 rel-L2 {r:.3e}")
     assert r < 2e-2
+
+
+@pytest.mark.parametrize("splits", [0, 2])
+def test_folded_out_projection_matches_unfolded(hf, splits, monkeypatch):
+    """out_proj folded into the read-out operand (V^ Wo^T, hop_patterns.vot16) vs the two-launch form."""
+    impl = hf._impl
+    if splits:
+        monkeypatch.setenv("HOP_TC_SPLITS", str(splits))
+    ref, dut, g = _sweep_layer(hf, 128, 1024, 0)
+    x = ref.lookup_weights[0, :384].detach() + 0.5 * torch.randn(384, 128, generator=g)
+    spec, pack = dut.spec(), dut.param_pack()
+    path = impl.cabi.PATH_TC_F16
+    with torch.no_grad():
+        want = ref(x[None])[0]
+        pats = impl.prepare_patterns_op(*[None if pack[k] is None else pack[k].detach().contiguous()
+                                          for k in impl.ops._PATTERN_SIDE], spec.flags, path, spec.d_assoc,
+                                        spec.d_v, 0, spec.ln_eps)
+        assert pats[5].numel() == 1024 * 128
+        q = [None if pack[k] is None else pack[k].detach().contiguous() for k in impl.ops._QUERY_SIDE]
+        two = impl.retrieve_op(x.cuda(), *pats, *q, spec.flags, path, spec.d_in, spec.d_out, 0, spec.beta,
+                               spec.ln_eps, 0, True)
+        one = impl.retrieve_op(x.cuda(), *pats, *q, spec.flags, path, spec.d_in, spec.d_out, 0, spec.beta,
+                               spec.ln_eps, 0, False)
+    assert one[1].numel() == 0 and two[1].shape == (384, 128)
+    r1, r2 = rel_l2(one[0], want), rel_l2(two[0], want)
+    print(f"folded rel-L2 {r1:.3e}, two-launch rel-L2 {r2:.3e}")
+    assert r1 < REL_L2_BAR and r2 < REL_L2_BAR
+    assert torch.equal(one[4], two[4])
