@@ -1,0 +1,193 @@
+"""Multi-GPU modes of the Hopfield retrieval (new design; the reference is single-device).
+
+One process per GPU (`torchrun`), `torch.distributed` for the plumbing.
+
+* **batch-parallel** (`batch_parallel_rows`): query rows are independent, so N is split across ranks and
+  every rank holds all patterns; the forward needs no collective at all.
+* **pattern-sharded** (`PatternShardedHopfield`): the stored patterns are split into G contiguous shards;
+  every rank sees all N queries and evaluates the fused retrieval on its shard, producing per row the
+  shard-local normalised read-out O_g, `lse_g`, the row max and its (global) index.  Softmax over P is a
+  (max, sum) monoid, so one exchange per pass finishes the job:
+
+      lse = log sum_g exp(lse_g),  w_g = exp(lse_g - lse),  O = sum_g w_g O_g
+
+  `all_gather` of the 3 per-row statistics (12 bytes/row/shard), the library's merge kernel scales the local
+  O_g by w_g in place, one `all_reduce(SUM)` over NVLink gives O (or `reduce_scatter` when the consumer is
+  row-sharded: `scatter_rows=True`).  With T > 0 retrieve updates the merge happens after every pass
+  (the state q <- beta * A K^ is itself a read-out over the sharded K^), so it is one launch per pass.
+
+The arithmetic is injected as a small backend object: `CudaBackend` calls the C-ABI ops (the product);
+the CPU `gloo` tests inject an oracle-backed stand-in to exercise the sharding / exchange logic.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+from torch import Tensor
+
+from . import cabi
+
+
+def shard_range(n_patterns: int, n_shards: int, shard: int, align: int = 128) -> Tuple[int, int]:
+    """Contiguous [start, start+count) of shard `shard`; boundaries on multiples of `align` patterns (one
+    score tile) where P allows, so no shard pays for a padded tile but the last."""
+    if not (0 <= shard < n_shards):
+        raise ValueError(f"shard {shard} out of range for {n_shards} shards")
+    if n_patterns < n_shards:
+        raise ValueError(f"cannot split {n_patterns} patterns over {n_shards} shards")
+    tiles = (n_patterns + align - 1) // align
+    if tiles >= n_shards:
+        base, extra = divmod(tiles, n_shards)
+        t0 = shard * base + min(shard, extra)
+        t1 = t0 + base + (1 if shard < extra else 0)
+        start, end = t0 * align, min(t1 * align, n_patterns)
+    else:
+        base, extra = divmod(n_patterns, n_shards)
+        start = shard * base + min(shard, extra)
+        end = start + base + (1 if shard < extra else 0)
+    return start, end - start
+
+
+def batch_parallel_rows(n_rows: int, world: int, rank: int) -> Tuple[int, int]:
+    """Rows [start, start+count) of rank `rank` in batch-parallel mode (even split, remainder to the first ranks)."""
+    base, extra = divmod(n_rows, world)
+    start = rank * base + min(rank, extra)
+    return start, base + (1 if rank < extra else 0)
+
+
+class CudaBackend:
+    """The product path: sm_100a kernels through the C-ABI custom ops."""
+
+    def prepare(self, pack: Dict[str, Optional[Tensor]], flags: int, path: int, d_assoc: int, d_v: int,
+                update_steps: int, ln_eps: float) -> List[Tensor]:
+        from .ops import prepare_patterns_op, _PATTERN_SIDE
+        args = [None if pack.get(k) is None else pack[k].detach().contiguous() for k in _PATTERN_SIDE]
+        return prepare_patterns_op(*args, flags, path, d_assoc, d_v, update_steps, ln_eps)
+
+    def retrieve(self, x: Tensor, pats: List[Tensor], ln_w: Optional[Tensor], ln_b: Optional[Tensor], flags: int,
+                 path: int, d_in: int, beta: float, ln_eps: float, pattern_offset: int, over_keys: bool,
+                 fold: Optional[Tuple[Tensor, Optional[Tensor]]] = None):
+        """One association pass on this shard.  `over_keys` reads out over K^ (a retrieve update).  With
+        `fold=(wo, bo)` and a folded operand in `pats`, the pass returns O_g Wo^T + bo (the shard weights sum
+        to 1, so the bias survives the merge unchanged); the second return value says whether it did."""
+        from .ops import retrieve_op
+        khat, vhat, k16, kt16, vt16, vot16 = pats
+        if over_keys:
+            vhat, vt16 = khat, kt16
+        empty = vot16.new_empty((0,))
+        if fold is not None and not over_keys and vot16.numel() > 0 and path != cabi.PATH_FP32_SIMT:
+            wo, bo = fold
+            res = retrieve_op(x, khat, vhat, k16, empty, vt16, vot16, ln_w, ln_b, None, None, wo, bo,
+                              flags | cabi.F_OUT_PROJ, path, d_in, wo.shape[0], 0, beta, ln_eps, pattern_offset, False)
+            return (res[0], res[3], res[5], res[4]), True
+        res = retrieve_op(x, khat, vhat, k16, empty, vt16, empty, ln_w, ln_b, None, None, None, None,
+                          flags & ~cabi.F_OUT_PROJ, path, d_in, 1, 0, beta, ln_eps, pattern_offset, True)
+        # no out_proj: out == read-out.  (O_g, lse_g, rowmax_g, argmax_g)
+        return (res[0], res[3], res[5], res[4]), False
+
+    def merge(self, retrieved: Tensor, lse_all: Tensor, rowmax_all: Tensor, argmax_all: Tensor, shard: int):
+        from .ops import merge_shards
+        return merge_shards(retrieved, lse_all, rowmax_all, argmax_all, shard)
+
+    def out_projection(self, retrieved: Tensor, wo: Tensor, bo: Optional[Tensor]) -> Tensor:
+        from .ops import out_projection
+        return out_projection(retrieved, wo, bo)
+
+    def resolve_path(self, spec, n_rows: int, n_patterns: int) -> int:
+        from .ops import resolve_path
+        return resolve_path(spec, n_rows, n_patterns)
+
+
+class PatternShardedHopfield:
+    """Pattern-sharded evaluation of one `HopfieldLayer` over a process group (inference).
+
+    Built on every rank from the *full* layer (or any object with `spec()` / `param_pack()` / `quantity`);
+    each rank keeps only its contiguous slice of the pattern-side tensors.
+    """
+
+    def __init__(self, layer, group: Optional[dist.ProcessGroup] = None, backend=None, scatter_rows: bool = False):
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.backend = backend if backend is not None else CudaBackend()
+        self.scatter_rows = scatter_rows
+        self.spec = layer.spec()
+        if self.spec.flags & (cabi.F_PROJ_STATE | cabi.F_PROJ_STORED):
+            raise NotImplementedError("pattern-sharded mode is built for static state/stored patterns "
+                                      "(what Hop-VAE uses, HopVAE.py:149-170)")
+        self.n_patterns = int(layer.quantity)
+        self.start, self.count = shard_range(self.n_patterns, self.world, self.rank)
+        pack = layer.param_pack()
+        sl = slice(self.start, self.start + self.count)
+        self.pack = dict(pack)
+        self.pack["lookup"] = pack["lookup"].detach()[sl].contiguous()
+        if pack.get("lookup_targets") is not None:
+            self.pack["lookup_targets"] = pack["lookup_targets"].detach()[sl].contiguous()
+        self._pats = None
+        self._path = None
+        self.last_argmax: Optional[Tensor] = None
+        self.last_lse: Optional[Tensor] = None
+
+    # ------------------------------------------------------------------ one (local pass + exchange) round
+    def _exchange(self, o: Tensor, lse: Tensor, rowmax: Tensor, argmax: Tensor) -> Tuple[Tensor, Tensor, Tensor]:
+        """Shard-local (O_g, lse_g, max_g, arg_g) -> global (O, lse, argmax) on every rank."""
+        if self.world == 1:
+            return o, lse, argmax
+        n = lse.shape[0]
+        stats = torch.stack([lse, rowmax, argmax.view(torch.float32)])          # (3, N), 12 bytes per row
+        gathered = torch.empty((self.world * 3, n), device=stats.device, dtype=torch.float32)
+        dist.all_gather_into_tensor(gathered, stats, group=self.group)
+        gathered = gathered.view(self.world, 3, n)
+        lse_all = gathered[:, 0].contiguous()
+        max_all = gathered[:, 1].contiguous()
+        arg_all = gathered[:, 2].contiguous().view(torch.int32)
+        g_lse, g_arg = self.backend.merge(o, lse_all, max_all, arg_all, self.rank)   # o *= exp(lse_g - lse)
+        if self.scatter_rows:
+            if n % self.world != 0:
+                raise ValueError("scatter_rows needs N divisible by the world size")
+            rows = n // self.world
+            mine = torch.empty((rows, o.shape[1]), device=o.device, dtype=o.dtype)
+            dist.reduce_scatter_tensor(mine, o, op=dist.ReduceOp.SUM, group=self.group)
+            return mine, g_lse, g_arg
+        dist.all_reduce(o, op=dist.ReduceOp.SUM, group=self.group)
+        return o, g_lse, g_arg
+
+    def forward(self, x: Tensor) -> Tensor:
+        spec = self.spec
+        lead = x.shape[:-1]
+        x2 = x.reshape(-1, spec.d_in).contiguous()
+        n = x2.shape[0]
+        if self._pats is None:
+            # path chosen on the GLOBAL problem so that every rank runs the same kernel family
+            self._path = self.backend.resolve_path(spec, n, self.n_patterns)
+            self._pats = self.backend.prepare(self.pack, spec.flags, self._path, spec.d_assoc, spec.d_v,
+                                              spec.update_steps, spec.ln_eps)
+        flags = spec.flags & ~cabi.F_OUT_PROJ
+        state, st_flags = x2, flags
+        ln_w, ln_b = self.pack.get("ln_state_w"), self.pack.get("ln_state_b")
+        if self.scatter_rows and spec.update_steps > 0:
+            raise NotImplementedError("scatter_rows with retrieve updates (every pass needs all rows' state)")
+        for t in range(spec.update_steps):
+            (o, lse, rowmax, argmax), _ = self.backend.retrieve(state, self._pats, ln_w, ln_b, st_flags, self._path,
+                                                                spec.d_in, spec.beta, spec.ln_eps, self.start, True)
+            state, _, _ = self._exchange(o, lse, rowmax, argmax)        # q <- A K^ (beta applied by the next pass)
+            st_flags = flags & ~cabi.F_NORM_STATE                        # upstream does not re-normalise the state
+            ln_w = ln_b = None
+        fold = None
+        if spec.flags & cabi.F_OUT_PROJ:
+            fold = (self.pack["wo"].detach().contiguous(),
+                    None if self.pack.get("bo") is None else self.pack["bo"].detach().contiguous())
+        (o, lse, rowmax, argmax), folded = self.backend.retrieve(state, self._pats, ln_w, ln_b, st_flags, self._path,
+                                                                 spec.d_in, spec.beta, spec.ln_eps, self.start, False,
+                                                                 fold)
+        o, g_lse, g_arg = self._exchange(o, lse, rowmax, argmax)
+        self.last_lse, self.last_argmax = g_lse, g_arg
+        if fold is not None and not folded:
+            o = self.backend.out_projection(o, fold[0], fold[1])
+        if self.scatter_rows:
+            return o
+        return o.reshape(*lead, o.shape[-1])
+
+    __call__ = forward

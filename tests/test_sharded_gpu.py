@@ -1,0 +1,62 @@
+"""GPU (-m gpu), needs >= 2 B200s: pattern-sharded retrieval over NCCL vs the unsharded oracle."""
+import os
+import socket
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+WORKER = r'''
+import os, sys
+sys.path.insert(0, os.environ["HOP_ROOT"]); sys.path.insert(0, os.path.join(os.environ["HOP_ROOT"], "tests"))
+import torch, torch.distributed as dist
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+torch.cuda.set_device(rank)
+dist.init_process_group("nccl", device_id=torch.device("cuda", rank))
+import hflayers
+from oracle import hflayers_oracle as O
+from util import randomize_, rel_l2
+impl = hflayers._impl
+for (D, P, N, T, path, bar) in [(64, 512, 300, 0, "fp32", 1e-5), (64, 515, 77, 2, "fp32", 1e-4),
+                                (128, 4096, 1024, 0, "f16", 1e-3), (256, 2048, 512, 1, "f16", 1e-3)]:
+    kw = dict(input_size=D, quantity=P, update_steps_max=T, update_steps_eps=0.0,
+              stored_pattern_as_static=True, state_pattern_as_static=True)
+    ref = randomize_(O.HopfieldLayer(**kw), 5, 1.0)
+    g = torch.Generator().manual_seed(6)
+    with torch.no_grad():
+        ref.lookup_weights.copy_(torch.randn(1, P, D, generator=g))
+    full = impl.HopfieldLayer(**kw); full.load_state_dict(ref.state_dict()); full = full.cuda(); full.kernel_path = path
+    idx = torch.randint(0, P, (N,), generator=g)
+    x = ref.lookup_weights[0, idx].detach() + 0.5 * torch.randn(N, D, generator=g)
+    sh = impl.PatternShardedHopfield(full)
+    with torch.no_grad():
+        want, _, scores, _ = ref(x[None], return_details=True)
+        got = sh(x.cuda())
+    r = rel_l2(got, want[0])
+    s = scores.reshape(N, P); top2 = s.topk(2, -1).values
+    decided = (top2[:, 0] - top2[:, 1]) > (2e-2 if path == "f16" else 1e-5)
+    if T == 0:
+        assert torch.equal(sh.last_argmax.cpu().long()[decided], s.argmax(-1)[decided])
+    print(f"rank {rank}: D={D} P={P} T={T} {path}: rel-L2 {r:.3e}", flush=True)
+    assert r < bar, r
+dist.destroy_process_group()
+'''
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_pattern_sharded_nccl_two_gpus(tmp_path):
+    script = tmp_path / "worker.py"
+    script.write_text(WORKER)
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    env = dict(os.environ, HOP_ROOT=ROOT)
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                        "--master-addr", "127.0.0.1", "--master-port", str(port), str(script)],
+                       env=env, capture_output=True, text=True, timeout=600)
+    print(r.stdout[-3000:], r.stderr[-3000:])
+    assert r.returncode == 0
