@@ -281,10 +281,14 @@ def gpu_run(args):
             return runner(x_dev)
 
     def step_e2e():
+        # the reference-facing call with HOST buffers: pinned x in, pinned result out, copies inside the timed region
         with torch.no_grad():
-            x_stage.copy_(x_host, non_blocking=True)
-            y = runner(x_stage)
-            out_host.copy_(y.reshape(n, d), non_blocking=True)
+            if sharded:
+                x_stage.copy_(x_host, non_blocking=True)
+                y = runner(x_stage)
+                out_host.copy_(y.reshape(n, d), non_blocking=True)
+            else:
+                layer.forward_host(x_host, out_host, chunks=args.e2e_chunks)
 
     def barrier():
         torch.cuda.synchronize()
@@ -338,7 +342,9 @@ def gpu_run(args):
                        {1: "fp32_simt", 2: "tc_f16", 3: "tc_bf16"}[path],
                        "l2": "flushed between timed steps (256 MiB memset outside the events)"},
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": x_host.numel() * 4,
-                    "d2h_bytes_per_step": out_host.numel() * 4},
+                    "d2h_bytes_per_step": out_host.numel() * 4,
+                    "api": ("PatternShardedHopfield.forward on a staged copy" if sharded else
+                            "HopfieldLayer.forward_host (pinned host in/out, H2D / kernel / D2H pipelined in row chunks)")},
             "gpu_launches": int(launches),
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
                          "frac": achieved / pk["bf16_tflops"], "traffic": None,
@@ -385,6 +391,7 @@ def main():
     ap.add_argument("--mode", default="batch", choices=["batch", "sharded"],
                     help="multi-GPU mode: batch-parallel rows (default, weak scaling) or pattern-sharded with an "
                          "NCCL log-sum-exp merge (strong scaling in P)")
+    ap.add_argument("--e2e-chunks", type=int, default=None, help="row chunks of the pipelined host-buffer call")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")

@@ -256,6 +256,60 @@ class HopfieldLayer(nn.Module):
         self.last_argmax = argmax
         return out.reshape(*lead, out.shape[-1])
 
+    # ------------------------------------------------------- host-buffer entry point
+    def forward_host(self, x_host: Tensor, out_host: Optional[Tensor] = None, chunks: Optional[int] = None) -> Tensor:
+        """Host-buffer call: `x_host` (N, input_size) pinned fp32 -> `out_host` (N, output_size) pinned fp32.
+
+        The rows are cut into `chunks` pieces (multiples of 128 rows); the host->device copy of piece i+1, the
+        fused retrieval of piece i and the device->host copy of piece i-1 run on three streams, so the PCIe
+        transfers hide behind the kernels.  Returns once all work is *enqueued*; the current stream waits for
+        the last device->host copy, so a synchronize / event on the current stream covers everything.
+        Inference only (no autograd)."""
+        dev = self.lookup_weights.device
+        if dev.type != "cuda":
+            raise RuntimeError("hflayers.HopfieldLayer (hop_sm100): the layer is on the CPU; no CPU fallback")
+        if x_host.is_cuda or x_host.dtype != torch.float32 or x_host.dim() != 2 or x_host.shape[1] != self.input_size:
+            raise ValueError("forward_host expects a 2-D float32 host tensor (N, input_size)")
+        if not x_host.is_pinned():
+            raise ValueError("forward_host needs pinned host memory (asynchronous copies)")
+        n = x_host.shape[0]
+        if out_host is None:
+            out_host = torch.empty((n, self.output_size if (self._flags & cabi.F_OUT_PROJ) else self.pattern_size),
+                                   dtype=torch.float32).pin_memory()
+        if chunks is None:
+            chunks = 4 if n >= 8192 else (2 if n >= 2048 else 1)
+        rows = max(128, (-(-n // max(chunks, 1)) + 127) // 128 * 128)
+        bounds = [(a, min(a + rows, n)) for a in range(0, n, rows)]
+        if getattr(self, "_host_streams", None) is None or self._host_streams[0].device != dev:
+            self._host_streams = tuple(torch.cuda.Stream(device=dev) for _ in range(3))
+        if getattr(self, "_x_stage", None) is None or self._x_stage.shape[0] < n or self._x_stage.device != dev:
+            self._x_stage = torch.empty((n, self.input_size), device=dev, dtype=torch.float32)
+        h2d, comp, d2h = self._host_streams
+        cur = torch.cuda.current_stream(dev)
+        for st in self._host_streams:
+            st.wait_stream(cur)
+        args = []
+        with torch.no_grad():
+            for a, b in bounds:
+                xs = self._x_stage[a:b]
+                with torch.cuda.stream(h2d):
+                    xs.copy_(x_host[a:b], non_blocking=True)
+                    e1 = h2d.record_event()
+                with torch.cuda.stream(comp):
+                    comp.wait_event(e1)
+                    y = self.forward(xs)
+                    args.append(self.last_argmax)
+                    e2 = comp.record_event()
+                with torch.cuda.stream(d2h):
+                    d2h.wait_event(e2)
+                    out_host[a:b].copy_(y, non_blocking=True)
+                    y.record_stream(d2h)
+            with torch.cuda.stream(comp):
+                self.last_argmax = torch.cat(args) if len(args) > 1 else args[0]
+        cur.wait_stream(comp)
+        cur.wait_stream(d2h)
+        return out_host
+
     def extra_repr(self) -> str:
         return (f"input_size={self.input_size}, hidden_size={self.hidden_size}, pattern_size={self.pattern_size}, "
                 f"output_size={self.output_size}, quantity={self.quantity}, beta={self.beta:.6g}, "

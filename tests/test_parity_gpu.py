@@ -396,3 +396,21 @@ def test_folded_out_projection_matches_unfolded(hf, splits, monkeypatch):
     print(f"folded rel-L2 {r1:.3e}, two-launch rel-L2 {r2:.3e}")
     assert r1 < REL_L2_BAR and r2 < REL_L2_BAR
     assert torch.equal(one[4], two[4])
+
+
+def test_forward_host_pipelined_matches_forward(hf):
+    """Host-buffer entry point (pinned in/out, 3-stream chunk pipeline) == the device-tensor call."""
+    ref, dut, g = _sweep_layer(hf, 64, 640, 0)
+    x = torch.randn(1000, 64, generator=g)
+    dut.kernel_path = "f16"
+    xh = x.pin_memory()
+    with torch.no_grad():
+        want = dut(x.cuda()).cpu()
+        arg = dut.last_argmax.cpu()
+        for chunks in (1, 3, 8):
+            got = dut.forward_host(xh, chunks=chunks)
+            torch.cuda.synchronize()
+            assert torch.equal(got, want), chunks
+            assert torch.equal(dut.last_argmax.cpu(), arg)
+    with pytest.raises(ValueError, match="pinned"):
+        dut.forward_host(x)
