@@ -39,16 +39,21 @@ def _stale(target: str, deps) -> bool:
     return any(os.path.exists(d) and os.path.getmtime(d) > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    os.makedirs(OBJ, exist_ok=True)
+def build(force: bool = False, verbose: bool = False, trace: bool = False) -> str:
+    """trace=True builds the debug variant libhop_sm100_trace.so (-DHOP_TC_TRACE: per-tile clock64 timeline of
+    one CTA of the fused forward; never loaded by the product, see scripts/tc_timeline.py)."""
+    obj_dir = OBJ + ("_trace" if trace else "")
+    lib = LIB.replace(".so", "_trace.so") if trace else LIB
+    os.makedirs(obj_dir, exist_ok=True)
     nvcc = _nvcc()
     objs, jobs = [], []
+    flags = NVCC_FLAGS + (["-DHOP_TC_TRACE"] if trace else [])
     for src in SOURCES:
         s = os.path.join(CSRC, src)
-        o = os.path.join(OBJ, src.replace(".cu", ".o"))
+        o = os.path.join(obj_dir, src.replace(".cu", ".o"))
         objs.append(o)
         if force or _stale(o, [s] + HEADERS):
-            jobs.append([nvcc] + NVCC_FLAGS + ["-c", s, "-o", o])
+            jobs.append([nvcc] + flags + ["-c", s, "-o", o])
 
     def run(cmd):
         if verbose:
@@ -60,10 +65,10 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if jobs:
         with ThreadPoolExecutor(max_workers=min(len(jobs), os.cpu_count() or 4)) as ex:
             list(ex.map(run, jobs))
-    if force or jobs or _stale(LIB, objs):
-        run([nvcc, "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"])
-    return LIB
+    if force or jobs or _stale(lib, objs):
+        run([nvcc, "-shared", "-o", lib] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"])
+    return lib
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose=True))
+    print(build(force="--force" in sys.argv, verbose=True, trace="--trace" in sys.argv))

@@ -11,7 +11,7 @@ import os
 from typing import Optional
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libhop_sm100.so")
+LIB_PATH = os.environ.get("HOP_SM100_LIB") or os.path.join(HERE, "libhop_sm100.so")   # env: debug builds only
 
 ABI_VERSION = 2
 

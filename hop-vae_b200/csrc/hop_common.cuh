@@ -101,6 +101,7 @@ struct TcPassArgs {
   void* ws; size_t ws_bytes;   // partial results of the pattern splits (tc_forward_workspace bytes)
 };
 int tc_choose_splits(int n, int p, int update_steps);
+int tc_choose_cluster(int n);
 size_t tc_forward_workspace(int n, int p, int d, int update_steps);
 int launch_tc_forward(const TcPassArgs& a, cudaStream_t st);
 bool tc_supported(int h, int dv);

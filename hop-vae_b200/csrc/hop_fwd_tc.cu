@@ -42,6 +42,19 @@ constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 constexpr float kRescaleThreshold = 8.f;   // log2 units: P~ <= 2^8, safe in fp16 / bf16
 
+#ifdef HOP_TC_TRACE
+// Debug build only (libhop_sm100_trace.so): per-tile clock64() timestamps of CTA (0,0) for timeline analysis.
+constexpr int kTraceTiles = 64, kTraceEvents = 8, kTraceRoles = 9;
+__device__ long long g_trace[kTraceRoles * kTraceTiles * kTraceEvents];
+#define HOP_TRACE(role, tile, ev)                                                                  \
+  do {                                                                                             \
+    if (blockIdx.x == 0 && blockIdx.y == 0 && (tile) < kTraceTiles)                                \
+      g_trace[((role) * kTraceTiles + (tile)) * kTraceEvents + (ev)] = clock64();                  \
+  } while (0)
+#else
+#define HOP_TRACE(role, tile, ev) do {} while (0)
+#endif
+
 template <int D>
 struct TcCfg {
   static constexpr int kKChunks = D / 64;                 // 64-wide K chunks of the Q / K^ tiles
@@ -93,7 +106,10 @@ __device__ __forceinline__ float ld_shared_f32(uint32_t addr) {
   return v;
 }
 
-template <int D, bool kBf16>
+// kCluster CTAs (consecutive row tiles, same pattern split) form a cluster and share every K^ / V^T stage:
+// each loads 1/kCluster of the rows of a stage and multicasts it into all of them, so the L2 -> SM
+// traffic of the streamed operands drops by kCluster (the kernel is L2-bandwidth-bound otherwise).
+template <int D, bool kBf16, int kCluster>
 __global__ void __launch_bounds__(kThreads, 1)
 hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_kt,
                   const __grid_constant__ CUtensorMap tm_vt, const TcKernelArgs a) {
@@ -123,7 +139,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
   const int passes = a.update_steps + 1;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < Cfg::kStages; ++s) { ptx::mbar_init(full_bar(s), 1); ptx::mbar_init(empty_bar(s), 1); }
+    for (int s = 0; s < Cfg::kStages; ++s) { ptx::mbar_init(full_bar(s), 1); ptx::mbar_init(empty_bar(s), kCluster); }
     for (int b = 0; b < 2; ++b) {
       ptx::mbar_init(s_full(b), 1);
       ptx::mbar_init(p_full(b), kSoftmaxThreads); ptx::mbar_init(p_empty(b), 1);
@@ -139,6 +155,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
   }
   ptx::tc_fence_before();
   __syncthreads();
+  if constexpr (kCluster > 1) ptx::cluster_sync();   // peers' barriers are initialised before any remote arrive
   ptx::tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
@@ -147,22 +164,30 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
     // ------------------------------------------------------------ TMA producer
     if (ptx::elect_one()) {
       uint32_t it = 0;
-      auto produce = [&](const CUtensorMap* m, int c0, int c1, uint32_t bytes) {
+      const int crank = kCluster > 1 ? (int)ptx::cluster_ctarank() : 0;
+      constexpr uint16_t kMask = (uint16_t)((1u << kCluster) - 1u);
+      // `rows` = rows of the whole stage box (coordinate c1 counts rows); this CTA loads rows/kCluster of them
+      auto produce = [&](const CUtensorMap* m, int c0, int c1, int rows) {
         const int s = it % Cfg::kStages;
-        ptx::mbar_wait(empty_bar(s), ((it / Cfg::kStages) & 1) ^ 1);
-        ptx::mbar_arrive_expect_tx(full_bar(s), bytes);
-        ptx::tma_load_2d(ring + s * kChunkBytes, m, full_bar(s), c0, c1);
+        ptx::mbar_wait(empty_bar(s), ((it / Cfg::kStages) & 1) ^ 1);    // all kCluster consumers released it
+        ptx::mbar_arrive_expect_tx(full_bar(s), (uint32_t)rows * 128u);
+        if constexpr (kCluster > 1) {
+          const int part = rows / kCluster;
+          ptx::tma_load_2d_mc(ring + s * kChunkBytes + crank * part * 128, m, full_bar(s), c0, c1 + crank * part, kMask);
+        } else {
+          ptx::tma_load_2d(ring + s * kChunkBytes, m, full_bar(s), c0, c1);
+        }
         ++it;
       };
       for (int pass = 0; pass < passes; ++pass) {
         const CUtensorMap* bm = (pass < a.update_steps) ? &tm_kt : &tm_vt;
         auto load_k = [&](int tile) {
-          for (int kc = 0; kc < Cfg::kKChunks; ++kc) produce(&tm_k, kc * 64, tile * kTileP, kChunkBytes);
+          for (int kc = 0; kc < Cfg::kKChunks; ++kc) produce(&tm_k, kc * 64, tile * kTileP, kTileP);
         };
         auto load_b = [&](int tile) {
           for (int kc = 0; kc < 2; ++kc)
             for (int bs = 0; bs < Cfg::kBStages; ++bs)
-              produce(bm, tile * kTileP + kc * 64, bs * Cfg::kBRows, Cfg::kBRows * 128);
+              produce(bm, tile * kTileP + kc * 64, bs * Cfg::kBRows, Cfg::kBRows);
         };
         load_k(t0);
         for (int j = 0; j < nt; ++j) {
@@ -179,6 +204,11 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
       constexpr uint32_t idesc_qk = ptx::umma_idesc_f16(kTileM, kTileP, fmt);
       constexpr uint32_t idesc_pv = ptx::umma_idesc_f16(kTileM, D, fmt);
       uint32_t it = 0, g = 0;
+      // a ring stage is free again once the MMAs of EVERY CTA of the cluster that read it have completed
+      auto release = [&](uint32_t bar) {
+        if constexpr (kCluster > 1) ptx::umma_commit_mc(bar, (uint16_t)((1u << kCluster) - 1u));
+        else ptx::umma_commit(bar);
+      };
       for (int pass = 0; pass < passes; ++pass) {
         ptx::mbar_wait(q_ready, pass & 1);
         ptx::tc_fence_after();
@@ -195,18 +225,21 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
 #pragma unroll
             for (int k = 0; k < 4; ++k)
               ptx::umma_f16_ss(tmem_base + b * kTileP, ad + 2 * k, bd + 2 * k, idesc_qk, (kc | k) != 0);
-            ptx::umma_commit(empty_bar(s));
+            release(empty_bar(s));
             ++it;
           }
           ptx::umma_commit(s_full(b));
         };
         issue_qk(g);
         for (int j = 0; j < nt; ++j) {
+          HOP_TRACE(0, j, 0);
           if (j + 1 < nt) issue_qk(g + j + 1);
+          HOP_TRACE(0, j, 1);
           const uint32_t gg = g + j;
           const int b = gg & 1;
           ptx::mbar_wait(p_full(b), (gg >> 1) & 1);
           ptx::tc_fence_after();
+          HOP_TRACE(0, j, 2);
           for (int kc = 0; kc < 2; ++kc) {
             // one read-out chunk = D rows x 64 patterns = kBStages consecutive (pair-aligned) ring stages
             const int s = it % Cfg::kStages;
@@ -221,11 +254,12 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
             for (int k = 0; k < 4; ++k)
               ptx::umma_f16_ts(tmem_base + kTmemO, at + 8 * k, bd + 2 * k, idesc_pv, (j | kc | k) != 0);
             for (int bs = 0; bs < Cfg::kBStages; ++bs) {
-              ptx::umma_commit(empty_bar(it % Cfg::kStages));
+              release(empty_bar(it % Cfg::kStages));
               ++it;
             }
           }
           ptx::umma_commit(p_empty(b));
+          HOP_TRACE(0, j, 3);
         }
         g += nt;
       }
@@ -335,8 +369,16 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         const int b = gg & 1;
         const int col0 = (t0 + j) * kTileP + half * kHalfP;   // global pattern index of this thread's column 0
         const int valid = a.p - col0;                          // columns >= valid are padding
+#ifdef HOP_TC_TRACE
+        const int trole = (lane == 0) ? warp - 1 : -1;   // roles 1..8 = softmax warps 2..9
+#define HOP_STRACE(ev) do { if (trole > 0) HOP_TRACE(trole, j, ev); } while (0)
+#else
+#define HOP_STRACE(ev) do {} while (0)
+#endif
+        HOP_STRACE(0);
         ptx::mbar_wait(s_full(b), (gg >> 1) & 1);
         ptx::tc_fence_after();
+        HOP_STRACE(1);
         const uint32_t s_addr = lane_base + b * kTileP + half * kHalfP;
 
         // this thread's 64 scores into registers (one TMEM round trip), then free the S buffer at once
@@ -344,6 +386,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         ptx::tmem_ld_x32p(s_addr, v);
         ptx::tmem_ld_x32p(s_addr + 32, v + 32);
         ptx::tmem_wait_ld();
+        HOP_STRACE(2);
         if (valid < kHalfP) {
 #pragma unroll
           for (int i = 0; i < kHalfP; ++i)
@@ -381,6 +424,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         }
         ptx::named_bar_sync(pair_bar, 64);
         const float cmax = fmaxf(hmax, ld_shared_f32(xch_at(b, half ^ 1, row)));
+        HOP_STRACE(3);
 
         // lazy rescale of (l, O): only when some row of the warp outgrew its reference max by 2^8
         const bool need = cmax > m_run + kRescaleThreshold;
@@ -407,6 +451,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
           m_run = m_new;
         }
 
+        HOP_STRACE(4);
         // P~ = 2^(s - m_run) as 16-bit pairs into TMEM, over the first 64 columns of the S buffer just read
         // (this half's 64 patterns -> columns 32h..32h+31; the partner finished its tcgen05.ld of those
         // columns before the pair barrier above); the A operand of the read-out MMA
@@ -420,11 +465,13 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
           ls[i & 3] += p0 + p1;
           pk[i] = pack16<kBf16>(p0, p1);
         }
+        HOP_STRACE(5);
         ptx::tmem_st_x32(lane_base + b * kTileP + half * 32, pk);
         l += (ls[0] + ls[1]) + (ls[2] + ls[3]);
         ptx::tmem_wait_st();
         ptx::tc_fence_before();
         ptx::mbar_arrive(p_full(b));
+        HOP_STRACE(6);
       }
 
       // ---- end of the pass: the pair combines (l, tmax, targ); slots of the other parity are idle
@@ -514,6 +561,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
   }
 
   __syncthreads();
+  if constexpr (kCluster > 1) ptx::cluster_sync();   // no CTA leaves while a peer may still signal its barriers
   if (warp == 0) {
     ptx::tc_fence_after();
     ptx::tmem_dealloc(tmem_base, kTmemCols);
@@ -604,14 +652,14 @@ int make_map(CUtensorMap* m, const void* base, int rows, int cols, int box_rows,
   return HOP_OK;
 }
 
-template <int D, bool kBf16>
+template <int D, bool kBf16, int kCluster>
 int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
   using Cfg = TcCfg<D>;
   const int ppad = padded_patterns(a.p);
   CUtensorMap tk, tkt, tvt;
-  HOP_TRY(make_map(&tk, a.k16, ppad, D, kTileP, a.bf16));
-  HOP_TRY(make_map(&tvt, a.vt16, D, ppad, Cfg::kBRows, a.bf16));
-  if (a.update_steps > 0) HOP_TRY(make_map(&tkt, a.kt16, D, ppad, Cfg::kBRows, a.bf16));
+  HOP_TRY(make_map(&tk, a.k16, ppad, D, kTileP / kCluster, a.bf16));
+  HOP_TRY(make_map(&tvt, a.vt16, D, ppad, Cfg::kBRows / kCluster, a.bf16));
+  if (a.update_steps > 0) HOP_TRY(make_map(&tkt, a.kt16, D, ppad, Cfg::kBRows / kCluster, a.bf16));
   else tkt = tvt;
 
   TcKernelArgs k{};
@@ -636,9 +684,19 @@ int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
   }
 
   // the attribute is per device and cheap to set: do it on every launch so that any current device works
-  HOP_CUDA(cudaFuncSetAttribute(hop_fwd_tc_kernel<D, kBf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
-  const dim3 grid((a.n + kTileM - 1) / kTileM, k.splits);
-  hop_fwd_tc_kernel<D, kBf16><<<grid, kThreads, Cfg::kSmemBytes, st>>>(tk, tkt, tvt, k);
+  auto* kern = hop_fwd_tc_kernel<D, kBf16, kCluster>;
+  HOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+  const int row_tiles = (a.n + kTileM - 1) / kTileM;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((row_tiles + kCluster - 1) / kCluster * kCluster, k.splits);   // whole clusters; extra CTAs are masked
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = kCluster; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  HOP_CUDA(cudaLaunchKernelEx(&cfg, kern, tk, tkt, tvt, k));
   HOP_LAUNCH_CHECK("hop_fwd_tc_kernel");
   if (k.splits > 1) {
     const int threads = 256, rows_per_block = threads / 32;
@@ -650,6 +708,13 @@ int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
 }
 
 }  // namespace
+
+#ifdef HOP_TC_TRACE
+extern "C" int hop_sm100_debug_trace(long long* dst_host, int n) {
+  const int total = kTraceRoles * kTraceTiles * kTraceEvents;
+  return (int)cudaMemcpyFromSymbol(dst_host, g_trace, sizeof(long long) * (n < total ? n : total));
+}
+#endif
 
 bool tc_supported(int h, int dv) { return h == dv && (h == 64 || h == 128 || h == 256); }
 
@@ -663,7 +728,8 @@ int tc_choose_splits(int n, int p, int update_steps) {
     if (s >= 1) return s < nt_all ? s : nt_all;
   }
   const int sms = num_sms();
-  const int row_tiles = (n + kTileM - 1) / kTileM;
+  const int cl = tc_choose_cluster(n);
+  const int row_tiles = ((n + kTileM - 1) / kTileM + cl - 1) / cl * cl;
   const int nt_total = padded_patterns(p) / kTileP;
   const int max_splits = nt_total < 32 ? nt_total : 32;
   int best = 1;
@@ -679,6 +745,20 @@ int tc_choose_splits(int n, int p, int update_steps) {
   return best;
 }
 
+// CTAs per cluster sharing the streamed operands through TMA multicast (knob: HOP_TC_CLUSTER = 1 | 2 | 4).
+// Measured on B200 (r01): no gain -- the L2 already de-duplicates the unicast streams (1169 / 1195 / 1099
+// TFLOP/s at cluster 1 / 2 / 4, P=64k D=256), so the default stays 1.
+int tc_choose_cluster(int n) {
+  const int row_tiles = (n + kTileM - 1) / kTileM;
+  int want = 1;
+  if (const char* e = getenv("HOP_TC_CLUSTER")) {
+    const int c = atoi(e);
+    if (c == 1 || c == 2 || c == 4) want = c;
+  }
+  while (want > 1 && row_tiles < want) want >>= 1;
+  return want;
+}
+
 size_t tc_forward_workspace(int n, int p, int d, int update_steps) {
   const int splits = tc_choose_splits(n, p, update_steps);
   if (splits <= 1) return 0;
@@ -690,18 +770,26 @@ int launch_tc_forward(const TcPassArgs& a, cudaStream_t st) {
   if (!tc_supported(a.h, a.dv)) HOP_FAIL(HOP_ERR_UNSUPPORTED, "tensor-core path needs H == Dv in {64,128,256}");
   if (!a.retrieved) HOP_FAIL(HOP_ERR_BAD_ARG, "tensor-core forward: retrieved is NULL");
   const int splits = tc_choose_splits(a.n, a.p, a.update_steps);
+  const int cl = tc_choose_cluster(a.n);
+#define HOP_TC_DISPATCH(DD, BF)                                            \
+  do {                                                                     \
+    if (cl == 4) return launch_d<DD, BF, 4>(a, splits, st);                \
+    if (cl == 2) return launch_d<DD, BF, 2>(a, splits, st);                \
+    return launch_d<DD, BF, 1>(a, splits, st);                             \
+  } while (0)
   if (a.bf16) {
     switch (a.h) {
-      case 64: return launch_d<64, true>(a, splits, st);
-      case 128: return launch_d<128, true>(a, splits, st);
-      default: return launch_d<256, true>(a, splits, st);
+      case 64: HOP_TC_DISPATCH(64, true);
+      case 128: HOP_TC_DISPATCH(128, true);
+      default: HOP_TC_DISPATCH(256, true);
     }
   }
   switch (a.h) {
-    case 64: return launch_d<64, false>(a, splits, st);
-    case 128: return launch_d<128, false>(a, splits, st);
-    default: return launch_d<256, false>(a, splits, st);
+    case 64: HOP_TC_DISPATCH(64, false);
+    case 128: HOP_TC_DISPATCH(128, false);
+    default: HOP_TC_DISPATCH(256, false);
   }
+#undef HOP_TC_DISPATCH
 }
 
 }  // namespace hop
