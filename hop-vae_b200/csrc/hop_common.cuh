@@ -100,8 +100,9 @@ struct TcPassArgs {
   float* lse; int32_t* argmax; float* rowmax; int pattern_offset;
   void* ws; size_t ws_bytes;   // partial results of the pattern splits (tc_forward_workspace bytes)
 };
-int tc_choose_splits(int n, int p, int update_steps);
-int tc_choose_cluster(int n);
+int tc_choose_splits(int n, int p, int d, int update_steps);
+int tc_choose_cluster(int n, int d);
+bool tc_use_pair(int n, int d);
 size_t tc_forward_workspace(int n, int p, int d, int update_steps);
 int launch_tc_forward(const TcPassArgs& a, cudaStream_t st);
 bool tc_supported(int h, int dv);

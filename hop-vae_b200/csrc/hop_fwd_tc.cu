@@ -109,7 +109,13 @@ __device__ __forceinline__ float ld_shared_f32(uint32_t addr) {
 // kCluster CTAs (consecutive row tiles, same pattern split) form a cluster and share every K^ / V^T stage:
 // each loads 1/kCluster of the rows of a stage and multicasts it into all of them, so the L2 -> SM
 // traffic of the streamed operands drops by kCluster (the kernel is L2-bandwidth-bound otherwise).
-template <int D, bool kBf16, int kCluster>
+//
+// kPair: the two CTAs of a cluster form a tcgen05 CTA pair (cta_group::2, M = 256).  Each keeps its own 128 query
+// rows (Q tile, S / P~ / O in its own TMEM, its own softmax warps) but holds only HALF of every streamed K^ / V^T
+// tile in shared memory; one thread of the leader CTA issues the MMAs for both.  Per SM this halves the TMA
+// writes and the B-operand reads of shared memory -- the SS-mode score MMA alone needs 128 B/clk of operand
+// fetch in the single-CTA form, i.e. the whole shared-memory bandwidth (measured: 1400 instead of 1024 cycles).
+template <int D, bool kBf16, int kCluster, bool kPair>
 __global__ void __launch_bounds__(kThreads, 1)
 hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_kt,
                   const __grid_constant__ CUtensorMap tm_vt, const TcKernelArgs a) {
@@ -131,7 +137,10 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
   const uint32_t xch = bars + Cfg::kBarBytes;   // [parity][half][row]
   auto xch_at = [&](int parity, int half, int r) { return xch + (uint32_t)(((parity * 2 + half) * kTileM + r) * 4); };
 
+  static_assert(!kPair || kCluster == 2, "a CTA pair is a cluster of two");
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t crank = kCluster > 1 ? ptx::cluster_ctarank() : 0u;
+  constexpr uint32_t kArrivers = kSoftmaxThreads * (kPair ? 2 : 1);   // softmax threads feeding the MMA issuer
   const int split = blockIdx.y;
   const int nt_total = (a.p + kTileP - 1) / kTileP;
   const int t0 = split * a.tiles_per_split;
@@ -139,19 +148,22 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
   const int passes = a.update_steps + 1;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < Cfg::kStages; ++s) { ptx::mbar_init(full_bar(s), 1); ptx::mbar_init(empty_bar(s), kCluster); }
+    for (int s = 0; s < Cfg::kStages; ++s) {
+      ptx::mbar_init(full_bar(s), 1);
+      ptx::mbar_init(empty_bar(s), kPair ? 1 : kCluster);   // pair: one multicast commit of the leader's MMA thread
+    }
     for (int b = 0; b < 2; ++b) {
       ptx::mbar_init(s_full(b), 1);
-      ptx::mbar_init(p_full(b), kSoftmaxThreads); ptx::mbar_init(p_empty(b), 1);
+      ptx::mbar_init(p_full(b), kArrivers); ptx::mbar_init(p_empty(b), 1);
     }
-    ptx::mbar_init(q_ready, kSoftmaxThreads);
+    ptx::mbar_init(q_ready, kArrivers);
     ptx::fence_barrier_init();
     ptx::prefetch_tmap(&tm_k); ptx::prefetch_tmap(&tm_kt); ptx::prefetch_tmap(&tm_vt);
   }
   if (warp == 0) {
     __syncwarp();
-    ptx::tmem_alloc(tmem_slot, kTmemCols);
-    ptx::tmem_relinquish();
+    if constexpr (kPair) { ptx::tmem_alloc_pair(tmem_slot, kTmemCols); ptx::tmem_relinquish_pair(); }
+    else { ptx::tmem_alloc(tmem_slot, kTmemCols); ptx::tmem_relinquish(); }
   }
   ptx::tc_fence_before();
   __syncthreads();
@@ -162,9 +174,48 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
+    if constexpr (kPair) {
+      if (ptx::elect_one()) {
+        // each CTA streams ITS half of every tile into its own ring; bytes are counted on the leader's barrier
+        uint32_t it = 0;
+        constexpr int kKPerStage = Cfg::kKChunks >= 2 ? 2 : 1;          // 8 KiB K^ chunks (64 patterns x 64) per stage
+        constexpr int kKStages = Cfg::kKChunks / kKPerStage;
+        auto acquire = [&](uint32_t total_bytes) {
+          const int s = it % Cfg::kStages;
+          ptx::mbar_wait(empty_bar(s), ((it / Cfg::kStages) & 1) ^ 1);
+          if (crank == 0) ptx::mbar_arrive_expect_tx(full_bar(s), total_bytes);
+          return s;
+        };
+        for (int pass = 0; pass < passes; ++pass) {
+          const CUtensorMap* bm = (pass < a.update_steps) ? &tm_kt : &tm_vt;
+          auto load_k = [&](int tile) {
+            for (int ks = 0; ks < kKStages; ++ks) {
+              const int s = acquire(2u * kKPerStage * 8192u);
+              const uint32_t fb = ptx::map_to_cta(full_bar(s), 0);
+              for (int c = 0; c < kKPerStage; ++c)
+                ptx::tma_load_2d_pair(ring + s * kChunkBytes + c * 8192, &tm_k, fb, (ks * kKPerStage + c) * 64,
+                                      tile * kTileP + (int)crank * 64);
+              ++it;
+            }
+          };
+          auto load_b = [&](int tile) {
+            for (int kc = 0; kc < 2; ++kc) {
+              const int s = acquire(2u * (D / 2) * 128u);
+              ptx::tma_load_2d_pair(ring + s * kChunkBytes, bm, ptx::map_to_cta(full_bar(s), 0),
+                                    tile * kTileP + kc * 64, (int)crank * (D / 2));
+              ++it;
+            }
+          };
+          load_k(t0);
+          for (int j = 0; j < nt; ++j) {
+            if (j + 1 < nt) load_k(t0 + j + 1);
+            load_b(t0 + j);
+          }
+        }
+      }
+    } else
     if (ptx::elect_one()) {
       uint32_t it = 0;
-      const int crank = kCluster > 1 ? (int)ptx::cluster_ctarank() : 0;
       constexpr uint16_t kMask = (uint16_t)((1u << kCluster) - 1u);
       // `rows` = rows of the whole stage box (coordinate c1 counts rows); this CTA loads rows/kCluster of them
       auto produce = [&](const CUtensorMap* m, int c0, int c1, int rows) {
@@ -173,7 +224,8 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         ptx::mbar_arrive_expect_tx(full_bar(s), (uint32_t)rows * 128u);
         if constexpr (kCluster > 1) {
           const int part = rows / kCluster;
-          ptx::tma_load_2d_mc(ring + s * kChunkBytes + crank * part * 128, m, full_bar(s), c0, c1 + crank * part, kMask);
+          ptx::tma_load_2d_mc(ring + s * kChunkBytes + (int)crank * part * 128, m, full_bar(s), c0,
+                              c1 + (int)crank * part, kMask);
         } else {
           ptx::tma_load_2d(ring + s * kChunkBytes, m, full_bar(s), c0, c1);
         }
@@ -199,6 +251,65 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
     __syncwarp();
   } else if (warp == 1) {
     // -------------------------------------------------------------- MMA issuer
+    if constexpr (kPair) {
+      if (crank == 0 && ptx::elect_one()) {
+        constexpr int fmt = kBf16 ? 1 : 0;
+        constexpr uint32_t idesc_qk = ptx::umma_idesc_f16(2 * kTileM, kTileP, fmt);
+        constexpr uint32_t idesc_pv = ptx::umma_idesc_f16(2 * kTileM, D, fmt);
+        constexpr int kKPerStage = Cfg::kKChunks >= 2 ? 2 : 1;
+        constexpr int kKStages = Cfg::kKChunks / kKPerStage;
+        uint32_t it = 0, g = 0;
+        for (int pass = 0; pass < passes; ++pass) {
+          ptx::mbar_wait_cluster(q_ready, pass & 1);           // both CTAs' Q tiles are in their shared memory
+          ptx::tc_fence_after();
+          auto issue_qk = [&](uint32_t gg) {
+            const int b = gg & 1;
+            for (int ks = 0; ks < kKStages; ++ks) {
+              const int s = it % Cfg::kStages;
+              ptx::mbar_wait_cluster(full_bar(s), (it / Cfg::kStages) & 1);
+              ptx::tc_fence_after();
+#pragma unroll
+              for (int c = 0; c < kKPerStage; ++c) {
+                const uint64_t ad = ptx::umma_desc_sw128(q_smem + (ks * kKPerStage + c) * kChunkBytes);
+                const uint64_t bd = ptx::umma_desc_sw128(ring + s * kChunkBytes + c * 8192);
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                  ptx::umma2_f16_ss(tmem_base + b * kTileP, ad + 2 * k, bd + 2 * k, idesc_qk, (ks | c | k) != 0);
+              }
+              ptx::umma2_commit_both(empty_bar(s));
+              ++it;
+            }
+            ptx::umma2_commit_both(s_full(b));
+          };
+          issue_qk(g);
+          for (int j = 0; j < nt; ++j) {
+            HOP_TRACE(0, j, 0);
+            if (j + 1 < nt) issue_qk(g + j + 1);
+            HOP_TRACE(0, j, 1);
+            const uint32_t gg = g + j;
+            const int b = gg & 1;
+            ptx::mbar_wait_cluster(p_full(b), (gg >> 1) & 1);  // P~ of both CTAs is in their TMEM
+            ptx::tc_fence_after();
+            HOP_TRACE(0, j, 2);
+            for (int kc = 0; kc < 2; ++kc) {
+              const int s = it % Cfg::kStages;
+              ptx::mbar_wait_cluster(full_bar(s), (it / Cfg::kStages) & 1);
+              ptx::tc_fence_after();
+              const uint32_t at = tmem_base + b * kTileP + kc * 32;
+              const uint64_t bd = ptx::umma_desc_sw128(ring + s * kChunkBytes);
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                ptx::umma2_f16_ts(tmem_base + kTmemO, at + 8 * k, bd + 2 * k, idesc_pv, (j | kc | k) != 0);
+              ptx::umma2_commit_both(empty_bar(s));
+              ++it;
+            }
+            ptx::umma2_commit_both(p_empty(b));
+            HOP_TRACE(0, j, 3);
+          }
+          g += nt;
+        }
+      }
+    } else
     if (ptx::elect_one()) {
       constexpr int fmt = kBf16 ? 1 : 0;
       constexpr uint32_t idesc_qk = ptx::umma_idesc_f16(kTileM, kTileP, fmt);
@@ -277,6 +388,11 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
     const uint32_t pair_bar = 1 + wq;             // named barrier of the warp pair (64 threads)
     constexpr int kOGroups = D / 64;              // 32-column O groups per half
     const int og0 = half * kOGroups;
+    // q_ready / p_full are waited on by the MMA issuer: in a CTA pair that is the leader's thread
+    auto arrive_issuer = [&](uint32_t bar) {
+      if constexpr (kPair) ptx::mbar_arrive_cluster(ptx::map_to_cta(bar, 0));
+      else ptx::mbar_arrive(bar);
+    };
 
     // ---- pass-0 Q tile: one warp per row, 4 rows in flight; LN_q + beta, fp32 qsave, 16-bit swizzled smem
     {
@@ -359,7 +475,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
     uint32_t g = 0;
     for (int pass = 0; pass < passes; ++pass) {
       ptx::fence_proxy_async_smem();
-      ptx::mbar_arrive(q_ready);
+      arrive_issuer(q_ready);
 
       // m_run is shared by the pair (identical in both threads of a row); l, tmax, targ are per half
       float m_run = -INFINITY, l = 0.f, tmax = -INFINITY;
@@ -470,7 +586,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         l += (ls[0] + ls[1]) + (ls[2] + ls[3]);
         ptx::tmem_wait_st();
         ptx::tc_fence_before();
-        ptx::mbar_arrive(p_full(b));
+        arrive_issuer(p_full(b));
         HOP_STRACE(6);
       }
 
@@ -564,7 +680,8 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
   if constexpr (kCluster > 1) ptx::cluster_sync();   // no CTA leaves while a peer may still signal its barriers
   if (warp == 0) {
     ptx::tc_fence_after();
-    ptx::tmem_dealloc(tmem_base, kTmemCols);
+    if constexpr (kPair) ptx::tmem_dealloc_pair(tmem_base, kTmemCols);
+    else ptx::tmem_dealloc(tmem_base, kTmemCols);
   }
 }
 
@@ -652,14 +769,17 @@ int make_map(CUtensorMap* m, const void* base, int rows, int cols, int box_rows,
   return HOP_OK;
 }
 
-template <int D, bool kBf16, int kCluster>
+template <int D, bool kBf16, int kCluster, bool kPair>
 int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
   using Cfg = TcCfg<D>;
   const int ppad = padded_patterns(a.p);
   CUtensorMap tk, tkt, tvt;
-  HOP_TRY(make_map(&tk, a.k16, ppad, D, kTileP / kCluster, a.bf16));
-  HOP_TRY(make_map(&tvt, a.vt16, D, ppad, Cfg::kBRows / kCluster, a.bf16));
-  if (a.update_steps > 0) HOP_TRY(make_map(&tkt, a.kt16, D, ppad, Cfg::kBRows / kCluster, a.bf16));
+  // TMA boxes: pair = this CTA's half of a tile (64 patterns of K^, D/2 rows of V^T); else 1/kCluster of a stage
+  const int k_rows = kPair ? kTileP / 2 : kTileP / kCluster;
+  const int b_rows = kPair ? D / 2 : Cfg::kBRows / kCluster;
+  HOP_TRY(make_map(&tk, a.k16, ppad, D, k_rows, a.bf16));
+  HOP_TRY(make_map(&tvt, a.vt16, D, ppad, b_rows, a.bf16));
+  if (a.update_steps > 0) HOP_TRY(make_map(&tkt, a.kt16, D, ppad, b_rows, a.bf16));
   else tkt = tvt;
 
   TcKernelArgs k{};
@@ -684,7 +804,7 @@ int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
   }
 
   // the attribute is per device and cheap to set: do it on every launch so that any current device works
-  auto* kern = hop_fwd_tc_kernel<D, kBf16, kCluster>;
+  auto* kern = hop_fwd_tc_kernel<D, kBf16, kCluster, kPair>;
   HOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
   const int row_tiles = (a.n + kTileM - 1) / kTileM;
   cudaLaunchConfig_t cfg{};
@@ -720,7 +840,7 @@ bool tc_supported(int h, int dv) { return h == dv && (h == 64 || h == 128 || h =
 
 // Pattern splits per 128-row tile: the smallest count that fills >= 95 % of the last wave of SMs
 // (retrieve updates need the full softmax per pass, so T > 0 never splits).
-int tc_choose_splits(int n, int p, int update_steps) {
+int tc_choose_splits(int n, int p, int d, int update_steps) {
   if (update_steps > 0) return 1;
   const int nt_all = padded_patterns(p) / kTileP;
   if (const char* e = getenv("HOP_TC_SPLITS")) {          // test knob: force a split count
@@ -728,7 +848,7 @@ int tc_choose_splits(int n, int p, int update_steps) {
     if (s >= 1) return s < nt_all ? s : nt_all;
   }
   const int sms = num_sms();
-  const int cl = tc_choose_cluster(n);
+  const int cl = tc_choose_cluster(n, d);
   const int row_tiles = ((n + kTileM - 1) / kTileM + cl - 1) / cl * cl;
   const int nt_total = padded_patterns(p) / kTileP;
   const int max_splits = nt_total < 32 ? nt_total : 32;
@@ -745,10 +865,19 @@ int tc_choose_splits(int n, int p, int update_steps) {
   return best;
 }
 
+// tcgen05 CTA pairs (cta_group::2): on for D = 256 when there are at least two row tiles (knob: HOP_TC_PAIR =
+// 0 | 1 forces it off / on for every D).  Measured (r01, P = 64k / 256k): D = 256 1174 -> 1220 / 1226 -> 1367
+// TFLOP/s; D = 128 and 64 are MUFU-bound and do not gain (824 -> 798, 440 -> 438).
+bool tc_use_pair(int n, int d) {
+  if (const char* e = getenv("HOP_TC_PAIR")) return atoi(e) != 0 && n > kTileM;
+  return n > kTileM && d >= 256;
+}
+
 // CTAs per cluster sharing the streamed operands through TMA multicast (knob: HOP_TC_CLUSTER = 1 | 2 | 4).
 // Measured on B200 (r01): no gain -- the L2 already de-duplicates the unicast streams (1169 / 1195 / 1099
 // TFLOP/s at cluster 1 / 2 / 4, P=64k D=256), so the default stays 1.
-int tc_choose_cluster(int n) {
+int tc_choose_cluster(int n, int d) {
+  if (tc_use_pair(n, d)) return 2;
   const int row_tiles = (n + kTileM - 1) / kTileM;
   int want = 1;
   if (const char* e = getenv("HOP_TC_CLUSTER")) {
@@ -760,7 +889,7 @@ int tc_choose_cluster(int n) {
 }
 
 size_t tc_forward_workspace(int n, int p, int d, int update_steps) {
-  const int splits = tc_choose_splits(n, p, update_steps);
+  const int splits = tc_choose_splits(n, p, d, update_steps);
   if (splits <= 1) return 0;
   const size_t rows = (size_t)splits * n;
   return round_up_sz(rows * d * sizeof(float), 256) + 3 * round_up_sz(rows * sizeof(float), 256);
@@ -769,13 +898,15 @@ size_t tc_forward_workspace(int n, int p, int d, int update_steps) {
 int launch_tc_forward(const TcPassArgs& a, cudaStream_t st) {
   if (!tc_supported(a.h, a.dv)) HOP_FAIL(HOP_ERR_UNSUPPORTED, "tensor-core path needs H == Dv in {64,128,256}");
   if (!a.retrieved) HOP_FAIL(HOP_ERR_BAD_ARG, "tensor-core forward: retrieved is NULL");
-  const int splits = tc_choose_splits(a.n, a.p, a.update_steps);
-  const int cl = tc_choose_cluster(a.n);
+  const int splits = tc_choose_splits(a.n, a.p, a.h, a.update_steps);
+  const int cl = tc_choose_cluster(a.n, a.h);
+  const bool pair = tc_use_pair(a.n, a.h);
 #define HOP_TC_DISPATCH(DD, BF)                                            \
   do {                                                                     \
-    if (cl == 4) return launch_d<DD, BF, 4>(a, splits, st);                \
-    if (cl == 2) return launch_d<DD, BF, 2>(a, splits, st);                \
-    return launch_d<DD, BF, 1>(a, splits, st);                             \
+    if (pair) return launch_d<DD, BF, 2, true>(a, splits, st);             \
+    if (cl == 4) return launch_d<DD, BF, 4, false>(a, splits, st);         \
+    if (cl == 2) return launch_d<DD, BF, 2, false>(a, splits, st);         \
+    return launch_d<DD, BF, 1, false>(a, splits, st);                      \
   } while (0)
   if (a.bf16) {
     switch (a.h) {
