@@ -39,15 +39,17 @@ def _stale(target: str, deps) -> bool:
     return any(os.path.exists(d) and os.path.getmtime(d) > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False, trace: bool = False) -> str:
+def build(force: bool = False, verbose: bool = False, trace: bool = False, tag: str = "", defines=()) -> str:
     """trace=True builds the debug variant libhop_sm100_trace.so (-DHOP_TC_TRACE: per-tile clock64 timeline of
     one CTA of the fused forward; never loaded by the product, see scripts/tc_timeline.py)."""
-    obj_dir = OBJ + ("_trace" if trace else "")
-    lib = LIB.replace(".so", "_trace.so") if trace else LIB
+    # `tag` + `defines`: tuning variants (libhop_sm100_<tag>.so), loaded through HOP_SM100_LIB by scripts only
+    suffix = ("_trace" if trace else "") + (("_" + tag) if tag else "")
+    obj_dir = OBJ + suffix
+    lib = LIB.replace(".so", suffix + ".so") if suffix else LIB
     os.makedirs(obj_dir, exist_ok=True)
     nvcc = _nvcc()
     objs, jobs = [], []
-    flags = NVCC_FLAGS + (["-DHOP_TC_TRACE"] if trace else [])
+    flags = NVCC_FLAGS + (["-DHOP_TC_TRACE"] if trace else []) + ["-D" + d for d in defines]
     for src in SOURCES:
         s = os.path.join(CSRC, src)
         o = os.path.join(obj_dir, src.replace(".cu", ".o"))
@@ -71,4 +73,7 @@ def build(force: bool = False, verbose: bool = False, trace: bool = False) -> st
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose=True, trace="--trace" in sys.argv))
+    _tag = next((a.split("=", 1)[1] for a in sys.argv if a.startswith("--tag=")), "")
+    _defs = [a[2:] for a in sys.argv if a.startswith("-D")]
+    print(build(force="--force" in sys.argv, verbose="--quiet" not in sys.argv, trace="--trace" in sys.argv, tag=_tag,
+                defines=_defs))

@@ -40,7 +40,7 @@ constexpr uint32_t kTmemCols = 512;
 constexpr uint32_t kTmemO = 256;     // O accumulator starts after the two S buffers
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
-constexpr float kRescaleThreshold = 8.f;   // log2 units: P~ <= 2^8, safe in fp16 / bf16
+constexpr float kRescaleThreshold = 15.f;  // log2 units: P~ <= 2^15 = 32768 < 65504, the fp16 maximum
 
 #ifdef HOP_TC_TRACE
 // Debug build only (libhop_sm100_trace.so): per-tile clock64() timestamps of CTA (0,0) for timeline analysis.
@@ -55,8 +55,20 @@ __device__ long long g_trace[kTraceRoles * kTraceTiles * kTraceEvents];
 #define HOP_TRACE(role, tile, ev) do {} while (0)
 #endif
 
+// Every kPolyPeriod-th score column takes ex2_poly instead of MUFU (0 = never).  Tunable at build time.
+#ifndef HOP_POLY_D256
+#define HOP_POLY_D256 4
+#endif
+#ifndef HOP_POLY_D128
+#define HOP_POLY_D128 4
+#endif
+#ifndef HOP_POLY_D64
+#define HOP_POLY_D64 4
+#endif
+
 template <int D>
 struct TcCfg {
+  static constexpr int kPolyPeriod = D >= 256 ? HOP_POLY_D256 : (D >= 128 ? HOP_POLY_D128 : HOP_POLY_D64);
   static constexpr int kKChunks = D / 64;                 // 64-wide K chunks of the Q / K^ tiles
   static constexpr int kBStages = D > 128 ? D / 128 : 1;  // ring stages of one read-out chunk (D rows x 64 patterns)
   static constexpr int kBRows = D / kBStages;             // rows per TMA box of the read-out operand
@@ -542,30 +554,13 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         const float cmax = fmaxf(hmax, ld_shared_f32(xch_at(b, half ^ 1, row)));
         HOP_STRACE(3);
 
-        // lazy rescale of (l, O): only when some row of the warp outgrew its reference max by 2^8
+        // lazy rescale of (l, O): only when some row of the warp outgrew its reference max by 2^15.  The new
+        // reference is fixed here, but O is touched only AFTER this tile's exponentials: by then the previous
+        // tile's read-out MMA (which must finish before O may be rescaled) is done instead of being waited for.
         const bool need = cmax > m_run + kRescaleThreshold;
-        if (__any_sync(0xffffffffu, need)) {
-          const float m_new = fmaxf(m_run, cmax);
-          if (j > 0) {
-            const uint32_t pg = gg - 1;
-            ptx::mbar_wait(p_empty(pg & 1), (pg >> 1) & 1);   // read-out MMA of the previous tile done
-            ptx::tc_fence_after();
-            const float f = ptx::ex2(m_run - m_new);
-            l *= f;
-#pragma unroll 1
-            for (int c = og0; c < og0 + kOGroups; ++c) {
-              uint32_t o[32];
-              ptx::tmem_ld_x32(lane_base + kTmemO + c * 32, o);
-              ptx::tmem_wait_ld();
-#pragma unroll
-              for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * f);
-              ptx::tmem_st_x32(lane_base + kTmemO + c * 32, o);
-            }
-            ptx::tmem_wait_st();
-            ptx::tc_fence_before();
-          }
-          m_run = m_new;
-        }
+        const bool any_need = __any_sync(0xffffffffu, need);
+        const float m_old = m_run;
+        if (any_need) m_run = fmaxf(m_run, cmax);
 
         HOP_STRACE(4);
         // P~ = 2^(s - m_run) as 16-bit pairs into TMEM, over the first 64 columns of the S buffer just read
@@ -573,13 +568,33 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         // columns before the pair barrier above); the A operand of the read-out MMA
         float ls[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-        for (int i = 0; i < kHalfP; ++i) v[i] = __float_as_uint(ptx::ex2(__uint_as_float(v[i]) - m_run));
+        for (int i = 0; i < kHalfP; ++i) {
+          const float xs = __uint_as_float(v[i]) - m_run;
+          const bool poly = Cfg::kPolyPeriod > 0 && (i % (Cfg::kPolyPeriod > 0 ? Cfg::kPolyPeriod : 1)) == 0;
+          v[i] = __float_as_uint(poly ? ptx::ex2_poly(xs) : ptx::ex2(xs));
+        }
         uint32_t pk[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
           const float p0 = __uint_as_float(v[2 * i]), p1 = __uint_as_float(v[2 * i + 1]);
           ls[i & 3] += p0 + p1;
           pk[i] = pack16<kBf16>(p0, p1);
+        }
+        if (any_need && j > 0) {
+          const uint32_t pg = gg - 1;
+          ptx::mbar_wait(p_empty(pg & 1), (pg >> 1) & 1);   // read-out MMA of the previous tile done
+          ptx::tc_fence_after();
+          const float f = ptx::ex2(m_old - m_run);
+          l *= f;
+#pragma unroll 1
+          for (int c = og0; c < og0 + kOGroups; ++c) {
+            uint32_t o[32];
+            ptx::tmem_ld_x32(lane_base + kTmemO + c * 32, o);
+            ptx::tmem_wait_ld();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * f);
+            ptx::tmem_st_x32(lane_base + kTmemO + c * 32, o);
+          }
         }
         HOP_STRACE(5);
         ptx::tmem_st_x32(lane_base + b * kTileP + half * 32, pk);

@@ -292,6 +292,20 @@ __device__ __forceinline__ float ex2(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+// 2^x on the FMA / ALU pipes (no MUFU): round-to-nearest split x = n + f, f in [-0.5, 0.5], degree-3 minimax
+// polynomial for 2^f (max relative error 7.5e-5, below the fp16 rounding of P~), exponent bits added as an
+// integer.  Used for a fixed fraction of the score columns so that the MUFU unit (16 ex2 / clk / SM) stops
+// being the softmax bottleneck.  Valid for x >= -126; the caller's x is <= the lazy-rescale threshold.
+__device__ __forceinline__ float ex2_poly(float x) {
+  x = fmaxf(x, -126.f);
+  const float r = x + 12582912.f;                  // 1.5 * 2^23: the low mantissa bits now hold round(x)
+  const float f = x - (r - 12582912.f);
+  float p = 0.055171459913253784f;
+  p = fmaf(p, f, 0.2426108568906784f);
+  p = fmaf(p, f, 0.6932609677314758f);
+  p = fmaf(p, f, 0.9999281167984009f);
+  return __int_as_float(__float_as_int(p) + (__float_as_int(r) << 23));
+}
 __device__ __forceinline__ float lg2(float x) {
   float y;
   asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
