@@ -1,0 +1,112 @@
+"""Latency of the three-layer Hopfield bottleneck at the reference's own model shapes (BASELINE.json
+configs 1-3: MNIST-28, FFHQ-32, FFHQ-64; B = 32, P = 512, D = 64/64/3) on one B200:
+
+  ours      hflayers.HopfieldLayer (sm_100a library, exact fp32 kernels; HOP_PATH_AUTO)
+  eager     the oracle restatement run on the SAME GPU with PyTorch's stock kernels (ATen LayerNorm /
+            softmax + cuBLAS, TF32 off) -- what the reference itself does on a CUDA device, both in the
+            de-duplicated form and in the upstream-faithful form (patterns expanded over the batch)
+
+These sizes are launch-latency bound (<= 2.5 GFLOP): the numbers reported are microseconds per bottleneck
+(forward, and forward+backward), library launches per call, and retrieved latents/s -- not a roofline.
+
+    python scripts/bench_model_configs.py            # on the GPU box
+"""
+import json
+import os
+import sys
+
+import torch
+import torch.nn.functional as F
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import hflayers  # noqa: E402
+import hopvae_harness as H  # noqa: E402
+from oracle import hflayers_oracle as O  # noqa: E402  (baseline / checker only)
+
+torch.backends.cuda.matmul.allow_tf32 = False
+torch.backends.cudnn.allow_tf32 = False
+impl = hflayers._impl
+dev = torch.device("cuda", 0)
+
+
+def timed(fn, iters=50, warm=10):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters * 1e3   # microseconds
+
+
+def graphed(fn):
+    """Capture fn() (static shapes, no host sync inside) into a CUDA graph; returns a replay callable."""
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        for _ in range(3):
+            fn()
+    torch.cuda.current_stream().wait_stream(s)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        fn()
+    return g.replay
+
+
+rows = []
+for name, cfg in (("mnist28", H.MNIST_28), ("ffhq32", H.FFHQ_32), ("ffhq64", H.FFHQ_64)):
+    torch.manual_seed(1265)
+    ref = H.HopVAEHarness(cfg, O.HopfieldLayer).to(dev).eval()
+    dut = H.HopVAEHarness(cfg, hflayers.HopfieldLayer)
+    dut.load_state_dict(ref.state_dict())
+    dut = dut.to(dev).eval()
+    R = cfg["representation_dim"]
+    n = 32 * R * R
+    z = torch.randn(32, R * R, cfg["embedding_dim"], device=dev)
+    with torch.no_grad():
+        a, b = dut.bottleneck(z), ref.bottleneck(z)
+        rel = float((a["emb_recon"] - b["emb_recon"]).norm() / b["emb_recon"].norm())
+    res = {"config": name, "rows": n, "parity_rel_l2": rel}
+
+    def fwd(m):
+        def f():
+            with torch.no_grad():
+                m.bottleneck(z)
+        return f
+
+    l0 = impl.cabi.launch_count()
+    fwd(dut)()
+    res["launches_fwd_ours"] = impl.cabi.launch_count() - l0
+    res["us_fwd_ours"] = timed(fwd(dut))
+    for layer in (ref.hopfield, ref.embedding_to_index, ref.index_to_embedding):
+        layer.faithful = False
+    res["us_fwd_eager"] = timed(fwd(ref))
+    try:
+        res["us_fwd_ours_graph"] = timed(graphed(fwd(dut)))
+    except Exception as e:  # noqa: BLE001
+        res["us_fwd_ours_graph"] = f"capture failed: {type(e).__name__}"
+    for layer in (ref.hopfield, ref.embedding_to_index, ref.index_to_embedding):
+        layer.faithful = True
+    res["us_fwd_eager_upstream_shape"] = timed(fwd(ref))
+
+    def fb(m):
+        zz = z.clone().requires_grad_(True)
+
+        def f():
+            m.zero_grad(set_to_none=True)
+            out = m.bottleneck(zz)
+            (out["emb_recon"].square().mean() + out["emb_recon_loss"]).backward()
+        return f
+
+    dut.train(); ref.train()
+    res["us_fwdbwd_ours"] = timed(fb(dut), iters=30)
+    res["us_fwdbwd_eager_upstream_shape"] = timed(fb(ref), iters=30)
+    res["latents_per_s_fwd_ours"] = n / (res["us_fwd_ours"] * 1e-6)
+    res["latents_per_s_fwd_eager"] = n / (res["us_fwd_eager"] * 1e-6)
+    rows.append(res)
+    print(json.dumps(res), flush=True)
