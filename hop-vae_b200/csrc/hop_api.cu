@@ -80,7 +80,7 @@ int resolve_path(const hop_desc* d) {
   const bool tc_ok = tc_supported(d->d_assoc, d->d_v);
   if (d->path == HOP_PATH_TC_F16 || d->path == HOP_PATH_TC_BF16) {
     if (!tc_ok) {
-      set_error("tensor-core path is not built for H=%d Dv=%d (needs H == Dv in {64,128,256})", d->d_assoc, d->d_v);
+      set_error("tensor-core path is not built for H=%d Dv=%d (needs H == Dv in {64,128,256,512})", d->d_assoc, d->d_v);
       return -HOP_ERR_UNSUPPORTED;
     }
     return d->path;
@@ -88,7 +88,7 @@ int resolve_path(const hop_desc* d) {
   // AUTO: exact fp32 kernels for the reference's own (launch-bound, argmax-tight) sizes and for
   // widths the MMA cannot take; tcgen05 once the N x P score block is large.
   const long long np = (long long)d->n_rows * d->n_patterns;
-  if (tc_ok && np >= (1ll << 25)) return HOP_PATH_TC_F16;
+  if (tc_ok && (np >= (1ll << 25) || d->d_assoc > 256)) return HOP_PATH_TC_F16;   // the fp32 kernels stop at width 256
   return HOP_PATH_FP32_SIMT;
 }
 
@@ -185,6 +185,7 @@ int hop_sm100_forward(const hop_desc* desc, const hop_params* params, const hop_
   const bool q_proj = (d.flags & HOP_F_PROJ_STATE) != 0;
   const size_t tc_ws = (path != HOP_PATH_FP32_SIMT) ? tc_forward_workspace(d.n_rows, d.n_patterns, d.d_assoc, d.update_steps) : 0;
   const bool need_ws = q_proj || (path == HOP_PATH_FP32_SIMT && d.update_steps > 0) || tc_ws > 0 ||
+                       (path != HOP_PATH_FP32_SIMT && d.update_steps > 0 && d.d_assoc > 256) ||
                        (path != HOP_PATH_FP32_SIMT && out_proj && !retrieved &&
                         !(patterns->vot16 && out_proj_foldable(d)));
   if (need_ws && (!workspace || workspace_bytes < need))
@@ -241,7 +242,7 @@ int hop_sm100_forward(const hop_desc* desc, const hop_params* params, const hop_
   a.x_raw = qs ? nullptr : x; a.lnq_w = p.ln_state_w; a.lnq_b = p.ln_state_b; a.ln_eps = d.ln_eps;
   a.has_ln = (d.flags & HOP_F_NORM_STATE) ? 1 : 0; a.beta = d.beta; a.qs = qs;
   a.k16 = patterns->k16; a.kt16 = patterns->kt16; a.vt16 = folded ? patterns->vot16 : patterns->vt16;
-  a.bias = folded ? p.bo : nullptr;
+  a.bias = folded ? p.bo : nullptr; a.out_scale = 1.f; a.qtmp[0] = qbuf[0]; a.qtmp[1] = qbuf[1];
   a.n = d.n_rows; a.p = d.n_patterns; a.h = d.d_assoc; a.dv = d.d_v; a.update_steps = d.update_steps;
   a.bf16 = (path == HOP_PATH_TC_BF16);
   a.retrieved = folded ? out : (out_proj ? (retrieved ? retrieved : rbuf) : out);

@@ -94,6 +94,8 @@ struct TcPassArgs {
   const float* qs;          // prepared beta*Q^ (N,H) fp32 if x_raw == nullptr
   const void* k16; const void* kt16; const void* vt16;
   const float* bias;        // (Dv) added to the read-out (folded out_proj bias) or nullptr
+  float out_scale;          // scale of the normalised read-out (1 except for an update pass run as its own launch)
+  float* qtmp[2];           // two (N,H) fp32 state buffers, needed when T > 0 and H > 256 (one launch per pass)
   int n, p, h, dv, update_steps; int bf16;
   float* retrieved;         // (N,Dv)
   float* qsave;             // (N,H) or nullptr

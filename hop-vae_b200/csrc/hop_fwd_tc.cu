@@ -66,24 +66,31 @@ __device__ long long g_trace[kTraceRoles * kTraceTiles * kTraceEvents];
 #define HOP_POLY_D64 4
 #endif
 
-template <int D>
+// H  = association width (contraction length of the score MMA, Q tile width);
+// DV = read-out columns accumulated by ONE CTA.  The O accumulator owns TMEM columns [256, 256+DV), so DV <= 256:
+// a wider read-out (Dv = 512) is cut into Dv/DV column chunks along gridDim.z, each CTA recomputing the score
+// tile of its rows (the redundant score MMA is the price of the 512-column TMEM).
+template <int H, int DV>
 struct TcCfg {
-  static constexpr int kPolyPeriod = D >= 256 ? HOP_POLY_D256 : (D >= 128 ? HOP_POLY_D128 : HOP_POLY_D64);
-  static constexpr int kKChunks = D / 64;                 // 64-wide K chunks of the Q / K^ tiles
-  static constexpr int kBStages = D > 128 ? D / 128 : 1;  // ring stages of one read-out chunk (D rows x 64 patterns)
-  static constexpr int kBRows = D / kBStages;             // rows per TMA box of the read-out operand
+  static constexpr int kPolyPeriod = H >= 256 ? HOP_POLY_D256 : (H >= 128 ? HOP_POLY_D128 : HOP_POLY_D64);
+  static constexpr int kKChunks = H / 64;                 // 64-wide K chunks of the Q / K^ tiles
+  static constexpr int kBStages = DV > 128 ? DV / 128 : 1;  // ring stages of one read-out chunk (DV rows x 64 patterns)
+  static constexpr int kBRows = DV / kBStages;            // rows per TMA box of the read-out operand
   static constexpr int kQBytes = kKChunks * kChunkBytes;  // Q tile
-  static constexpr int kStages = (D >= 256) ? 10 : 12;    // even: a 2-stage read-out chunk never wraps
+  static constexpr int kStages = (H >= 512) ? 6 : (H >= 256) ? 10 : 12;   // even: a 2-stage read-out chunk never wraps
   static constexpr int kBarBytes = 512;                   // mbarriers + TMEM slot
   static constexpr int kXchBytes = 2 * 2 * kTileM * 4;    // [parity][half][row] floats exchanged by a warp pair
   static constexpr int kSmemBytes = kQBytes + kStages * kChunkBytes + kBarBytes + kXchBytes;
   static_assert(kStages % 2 == 0 && (kKChunks % 2 == 0 || kBStages == 1), "2-stage chunks must stay pair-aligned");
+  static_assert(DV <= 256 && DV <= H && H % DV == 0 && kSmemBytes <= 232448, "TMEM / shared-memory budget");
 };
 
 struct TcKernelArgs {
   const float* x_raw; const float* lnq_w; const float* lnq_b; float ln_eps; int has_ln; float beta;
   const float* qs; const float* bias;
   int n, p, update_steps;
+  int dv_total;                         // row pitch of the read-out (gridDim.z chunks of DV columns)
+  float out_scale;                      // applied to the normalised read-out (beta when it is the next state)
   int splits, tiles_per_split;          // pattern tiles (of 128) handled by one CTA
   float* retrieved; float* qsave; float* lse; int32_t* argmax; float* rowmax; int pattern_offset;
   // partial outputs when splits > 1: (splits, N, D), (splits, N) x3
@@ -127,11 +134,11 @@ __device__ __forceinline__ float ld_shared_f32(uint32_t addr) {
 // tile in shared memory; one thread of the leader CTA issues the MMAs for both.  Per SM this halves the TMA
 // writes and the B-operand reads of shared memory -- the SS-mode score MMA alone needs 128 B/clk of operand
 // fetch in the single-CTA form, i.e. the whole shared-memory bandwidth (measured: 1400 instead of 1024 cycles).
-template <int D, bool kBf16, int kCluster, bool kPair>
+template <int H, int DV, bool kBf16, int kCluster, bool kPair>
 __global__ void __launch_bounds__(kThreads, 1)
 hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_kt,
                   const __grid_constant__ CUtensorMap tm_vt, const TcKernelArgs a) {
-  using Cfg = TcCfg<D>;
+  using Cfg = TcCfg<H, DV>;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t smem_base = ptx::smem_u32(smem_raw);
   if ((smem_base & 1023u) != 0) __trap();       // the 128B-swizzle atoms need a 1 KiB-aligned base
@@ -154,6 +161,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
   const uint32_t crank = kCluster > 1 ? ptx::cluster_ctarank() : 0u;
   constexpr uint32_t kArrivers = kSoftmaxThreads * (kPair ? 2 : 1);   // softmax threads feeding the MMA issuer
   const int split = blockIdx.y;
+  const int zoff = (int)blockIdx.z * DV;       // first read-out column of this CTA
   const int nt_total = (a.p + kTileP - 1) / kTileP;
   const int t0 = split * a.tiles_per_split;
   const int nt = min(a.tiles_per_split, nt_total - t0);
@@ -212,9 +220,9 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
           };
           auto load_b = [&](int tile) {
             for (int kc = 0; kc < 2; ++kc) {
-              const int s = acquire(2u * (D / 2) * 128u);
+              const int s = acquire(2u * (DV / 2) * 128u);
               ptx::tma_load_2d_pair(ring + s * kChunkBytes, bm, ptx::map_to_cta(full_bar(s), 0),
-                                    tile * kTileP + kc * 64, (int)crank * (D / 2));
+                                    tile * kTileP + kc * 64, zoff + (int)crank * (DV / 2));
               ++it;
             }
           };
@@ -251,7 +259,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         auto load_b = [&](int tile) {
           for (int kc = 0; kc < 2; ++kc)
             for (int bs = 0; bs < Cfg::kBStages; ++bs)
-              produce(bm, tile * kTileP + kc * 64, bs * Cfg::kBRows, Cfg::kBRows);
+              produce(bm, tile * kTileP + kc * 64, zoff + bs * Cfg::kBRows, Cfg::kBRows);
         };
         load_k(t0);
         for (int j = 0; j < nt; ++j) {
@@ -267,7 +275,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
       if (crank == 0 && ptx::elect_one()) {
         constexpr int fmt = kBf16 ? 1 : 0;
         constexpr uint32_t idesc_qk = ptx::umma_idesc_f16(2 * kTileM, kTileP, fmt);
-        constexpr uint32_t idesc_pv = ptx::umma_idesc_f16(2 * kTileM, D, fmt);
+        constexpr uint32_t idesc_pv = ptx::umma_idesc_f16(2 * kTileM, DV, fmt);
         constexpr int kKPerStage = Cfg::kKChunks >= 2 ? 2 : 1;
         constexpr int kKStages = Cfg::kKChunks / kKPerStage;
         uint32_t it = 0, g = 0;
@@ -325,7 +333,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
     if (ptx::elect_one()) {
       constexpr int fmt = kBf16 ? 1 : 0;
       constexpr uint32_t idesc_qk = ptx::umma_idesc_f16(kTileM, kTileP, fmt);
-      constexpr uint32_t idesc_pv = ptx::umma_idesc_f16(kTileM, D, fmt);
+      constexpr uint32_t idesc_pv = ptx::umma_idesc_f16(kTileM, DV, fmt);
       uint32_t it = 0, g = 0;
       // a ring stage is free again once the MMAs of EVERY CTA of the cluster that read it have completed
       auto release = [&](uint32_t bar) {
@@ -398,7 +406,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
     const bool row_ok = grow < a.n;
     const float qscale = a.beta;                  // natural-units scale of the state pattern
     const uint32_t pair_bar = 1 + wq;             // named barrier of the warp pair (64 threads)
-    constexpr int kOGroups = D / 64;              // 32-column O groups per half
+    constexpr int kOGroups = DV / 64;             // 32-column O groups per half
     const int og0 = half * kOGroups;
     // q_ready / p_full are waited on by the MMA issuer: in a CTA pair that is the leader's thread
     auto arrive_issuer = [&](uint32_t bar) {
@@ -408,8 +416,8 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
 
     // ---- pass-0 Q tile: one warp per row, 4 rows in flight; LN_q + beta, fp32 qsave, 16-bit swizzled smem
     {
-      constexpr int kVec = (D + 127) / 128;       // float4 per lane
-      constexpr int kRowsInFlight = 4;
+      constexpr int kVec = (H + 127) / 128;       // float4 per lane
+      constexpr int kRowsInFlight = H > 256 ? 2 : 4;
       constexpr int kRowsPerWarp = kTileM / kSoftmaxWarps;
       const int sw = warp - 2;
       float4 w4[kVec], b4[kVec];
@@ -418,7 +426,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         const int e = lane * 4 + v * 128;
         w4[v] = make_float4(1.f, 1.f, 1.f, 1.f);
         b4[v] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (e < D && a.x_raw && a.has_ln) {
+        if (e < H && a.x_raw && a.has_ln) {
           if (a.lnq_w) w4[v] = *reinterpret_cast<const float4*>(a.lnq_w + e);
           if (a.lnq_b) b4[v] = *reinterpret_cast<const float4*>(a.lnq_b + e);
         }
@@ -433,7 +441,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
           for (int v = 0; v < kVec; ++v) {
             const int e = lane * 4 + v * 128;
             xv[u][v] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (e < D && gr < a.n) xv[u][v] = __ldg(reinterpret_cast<const float4*>(src + gr * D + e));
+            if (e < H && gr < a.n) xv[u][v] = __ldg(reinterpret_cast<const float4*>(src + gr * H + e));
           }
         }
 #pragma unroll
@@ -445,18 +453,18 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
               float s = 0.f;
 #pragma unroll
               for (int v = 0; v < kVec; ++v) s += (xv[u][v].x + xv[u][v].y) + (xv[u][v].z + xv[u][v].w);
-              const float mean = warp_sum(s) * (1.f / D);
+              const float mean = warp_sum(s) * (1.f / H);
               float q = 0.f;
 #pragma unroll
               for (int v = 0; v < kVec; ++v) {
                 const int e = lane * 4 + v * 128;
-                if (e < D) {
+                if (e < H) {
                   xv[u][v].x -= mean; xv[u][v].y -= mean; xv[u][v].z -= mean; xv[u][v].w -= mean;
                   q += xv[u][v].x * xv[u][v].x + xv[u][v].y * xv[u][v].y + xv[u][v].z * xv[u][v].z +
                        xv[u][v].w * xv[u][v].w;
                 }
               }
-              const float rstd = rsqrtf(warp_sum(q) * (1.f / D) + a.ln_eps);
+              const float rstd = rsqrtf(warp_sum(q) * (1.f / H) + a.ln_eps);
 #pragma unroll
               for (int v = 0; v < kVec; ++v) {
                 xv[u][v].x = xv[u][v].x * rstd * w4[v].x + b4[v].x; xv[u][v].y = xv[u][v].y * rstd * w4[v].y + b4[v].y;
@@ -471,9 +479,9 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
 #pragma unroll
           for (int v = 0; v < kVec; ++v) {
             const int e = lane * 4 + v * 128;
-            if (e < D) {
-              if (a.qsave && a.update_steps == 0 && gr < a.n && split == 0)
-                *reinterpret_cast<float4*>(a.qsave + gr * D + e) = xv[u][v];
+            if (e < H) {
+              if (a.qsave && a.update_steps == 0 && gr < a.n && split == 0 && blockIdx.z == 0)
+                *reinterpret_cast<float4*>(a.qsave + gr * H + e) = xv[u][v];
               const uint32_t lo = pack16<kBf16>(xv[u][v].x * kLog2e, xv[u][v].y * kLog2e);
               const uint32_t hi = pack16<kBf16>(xv[u][v].z * kLog2e, xv[u][v].w * kLog2e);
               const uint32_t addr = q_smem + (e >> 6) * kChunkBytes + sw128_off(r, (e & 63) >> 3) + ((e & 4) << 1);
@@ -625,7 +633,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
       ptx::mbar_wait(p_empty(last & 1), (last >> 1) & 1);
       ptx::tc_fence_after();
       const float inv = 1.f / l_tot;
-      if (pass < a.update_steps) {
+      if (H == DV && pass < a.update_steps) {   // (a chunked read-out runs its updates as separate launches)
         // retrieve update: q <- beta * (A K^) becomes the next pass' Q tile (never leaves the SM)
         const bool save = (pass == a.update_steps - 1) && a.qsave && row_ok;
         const float sc = inv * qscale;
@@ -642,7 +650,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
             pk[i] = pack16<kBf16>(q0 * kLog2e, q1 * kLog2e);
           }
           if (save) {
-            float4* dst = reinterpret_cast<float4*>(a.qsave + grow * D + c * 32);
+            float4* dst = reinterpret_cast<float4*>(a.qsave + grow * H + c * 32);
 #pragma unroll
             for (int q4 = 0; q4 < 8; ++q4)
               dst[q4] = make_float4(__uint_as_float(o[4 * q4]), __uint_as_float(o[4 * q4 + 1]),
@@ -656,7 +664,9 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         }
         ptx::tc_fence_before();
       } else {
-        float* o_dst = (a.splits > 1) ? a.part_o + ((long long)split * a.n + grow) * D : a.retrieved + grow * D;
+        float* o_dst = ((a.splits > 1) ? a.part_o + ((long long)split * a.n + grow) * a.dv_total
+                                       : a.retrieved + grow * a.dv_total) + zoff;
+        const float osc = (a.splits > 1) ? inv : inv * a.out_scale;
 #pragma unroll 1
         for (int c = og0; c < og0 + kOGroups; ++c) {
           uint32_t o[32];
@@ -664,17 +674,17 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
           ptx::tmem_wait_ld();
           if (row_ok) {
             float4* dst = reinterpret_cast<float4*>(o_dst + c * 32);
-            const float4* bia = (a.bias && a.splits == 1) ? reinterpret_cast<const float4*>(a.bias + c * 32) : nullptr;
+            const float4* bia = (a.bias && a.splits == 1) ? reinterpret_cast<const float4*>(a.bias + zoff + c * 32) : nullptr;
 #pragma unroll
             for (int q4 = 0; q4 < 8; ++q4) {
-              float4 r = make_float4(__uint_as_float(o[4 * q4]) * inv, __uint_as_float(o[4 * q4 + 1]) * inv,
-                                     __uint_as_float(o[4 * q4 + 2]) * inv, __uint_as_float(o[4 * q4 + 3]) * inv);
+              float4 r = make_float4(__uint_as_float(o[4 * q4]) * osc, __uint_as_float(o[4 * q4 + 1]) * osc,
+                                     __uint_as_float(o[4 * q4 + 2]) * osc, __uint_as_float(o[4 * q4 + 3]) * osc);
               if (bia) { const float4 bb = __ldg(bia + q4); r.x += bb.x; r.y += bb.y; r.z += bb.z; r.w += bb.w; }
               dst[q4] = r;
             }
           }
         }
-        if (row_ok && half == 0) {
+        if (row_ok && half == 0 && blockIdx.z == 0) {
           const float lse = kLn2 * (m_run + ptx::lg2(l_tot));
           if (a.splits > 1) {
             const long long o = (long long)split * a.n + grow;
@@ -705,7 +715,7 @@ template <int D>
 __global__ void tc_combine_kernel(int n, int splits, const float* __restrict__ part_o,
                                   const float* __restrict__ part_lse, const float* __restrict__ part_max,
                                   const int32_t* __restrict__ part_arg, const float* __restrict__ bias,
-                                  float* __restrict__ retrieved, float* __restrict__ lse,
+                                  float out_scale, float* __restrict__ retrieved, float* __restrict__ lse,
                                   int32_t* __restrict__ argmax, float* __restrict__ rowmax) {
   const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp_global >= n) return;
@@ -726,7 +736,7 @@ __global__ void tc_combine_kernel(int n, int splits, const float* __restrict__ p
   int arg = 0;
   for (int s = 0; s < splits; ++s) {
     const long long o = (long long)s * n + r;
-    const float w = __expf(part_lse[o] - m) * inv;
+    const float w = __expf(part_lse[o] - m) * inv * out_scale;
     const float pm = part_max[o];
     if (pm > best) { best = pm; arg = part_arg[o]; }   // splits are in pattern order: ties keep the lowest index
 #pragma unroll
@@ -784,46 +794,49 @@ int make_map(CUtensorMap* m, const void* base, int rows, int cols, int box_rows,
   return HOP_OK;
 }
 
-template <int D, bool kBf16, int kCluster, bool kPair>
+template <int H, int DV, bool kBf16, int kCluster, bool kPair>
 int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
-  using Cfg = TcCfg<D>;
+  using Cfg = TcCfg<H, DV>;
   const int ppad = padded_patterns(a.p);
+  if (a.update_steps > 0 && H != DV) HOP_FAIL(HOP_ERR_UNSUPPORTED, "on-chip retrieve updates need H == DV (internal)");
   CUtensorMap tk, tkt, tvt;
-  // TMA boxes: pair = this CTA's half of a tile (64 patterns of K^, D/2 rows of V^T); else 1/kCluster of a stage
+  // TMA boxes: pair = this CTA's half of a tile (64 patterns of K^, DV/2 rows of V^T); else 1/kCluster of a stage
   const int k_rows = kPair ? kTileP / 2 : kTileP / kCluster;
-  const int b_rows = kPair ? D / 2 : Cfg::kBRows / kCluster;
-  HOP_TRY(make_map(&tk, a.k16, ppad, D, k_rows, a.bf16));
-  HOP_TRY(make_map(&tvt, a.vt16, D, ppad, b_rows, a.bf16));
-  if (a.update_steps > 0) HOP_TRY(make_map(&tkt, a.kt16, D, ppad, b_rows, a.bf16));
+  const int b_rows = kPair ? DV / 2 : Cfg::kBRows / kCluster;
+  HOP_TRY(make_map(&tk, a.k16, ppad, H, k_rows, a.bf16));
+  HOP_TRY(make_map(&tvt, a.vt16, a.dv, ppad, b_rows, a.bf16));
+  if (a.update_steps > 0) HOP_TRY(make_map(&tkt, a.kt16, H, ppad, b_rows, a.bf16));
   else tkt = tvt;
 
   TcKernelArgs k{};
   k.x_raw = a.x_raw; k.lnq_w = a.lnq_w; k.lnq_b = a.lnq_b; k.ln_eps = a.ln_eps; k.has_ln = a.has_ln; k.beta = a.beta;
   k.qs = a.qs; k.bias = a.bias; k.n = a.n; k.p = a.p; k.update_steps = a.update_steps;
+  k.dv_total = a.dv; k.out_scale = a.out_scale;
   const int nt_total = ppad / kTileP;
   k.tiles_per_split = (nt_total + splits - 1) / splits;
   k.splits = (nt_total + k.tiles_per_split - 1) / k.tiles_per_split;   // every split owns >= 1 tile
   k.retrieved = a.retrieved; k.qsave = a.qsave; k.lse = a.lse; k.argmax = a.argmax; k.rowmax = a.rowmax;
   k.pattern_offset = a.pattern_offset;
   if (k.splits > 1) {
-    const size_t need = tc_forward_workspace(a.n, a.p, D, a.update_steps);
+    const size_t need = tc_forward_workspace(a.n, a.p, a.dv, a.update_steps);
     if (!a.ws || a.ws_bytes < need)
       HOP_FAIL(HOP_ERR_WORKSPACE, "tensor-core forward needs %zu workspace bytes for %d pattern splits, %zu given", need,
                k.splits, a.ws_bytes);
     char* w = static_cast<char*>(a.ws);
     const size_t rows = (size_t)splits * a.n;
-    k.part_o = reinterpret_cast<float*>(w); w += round_up_sz(rows * D * sizeof(float), 256);
+    k.part_o = reinterpret_cast<float*>(w); w += round_up_sz(rows * a.dv * sizeof(float), 256);
     k.part_lse = reinterpret_cast<float*>(w); w += round_up_sz(rows * sizeof(float), 256);
     k.part_max = reinterpret_cast<float*>(w); w += round_up_sz(rows * sizeof(float), 256);
     k.part_arg = reinterpret_cast<int32_t*>(w);
   }
 
   // the attribute is per device and cheap to set: do it on every launch so that any current device works
-  auto* kern = hop_fwd_tc_kernel<D, kBf16, kCluster, kPair>;
+  auto* kern = hop_fwd_tc_kernel<H, DV, kBf16, kCluster, kPair>;
   HOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
   const int row_tiles = (a.n + kTileM - 1) / kTileM;
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3((row_tiles + kCluster - 1) / kCluster * kCluster, k.splits);   // whole clusters; extra CTAs are masked
+  // whole clusters (extra CTAs are masked) x pattern splits x read-out column chunks
+  cfg.gridDim = dim3((row_tiles + kCluster - 1) / kCluster * kCluster, k.splits, a.dv / DV);
   cfg.blockDim = dim3(kThreads);
   cfg.dynamicSmemBytes = Cfg::kSmemBytes;
   cfg.stream = st;
@@ -835,8 +848,9 @@ int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
   HOP_LAUNCH_CHECK("hop_fwd_tc_kernel");
   if (k.splits > 1) {
     const int threads = 256, rows_per_block = threads / 32;
-    tc_combine_kernel<D><<<(a.n + rows_per_block - 1) / rows_per_block, threads, 0, st>>>(
-        a.n, k.splits, k.part_o, k.part_lse, k.part_max, k.part_arg, a.bias, a.retrieved, a.lse, a.argmax, a.rowmax);
+    tc_combine_kernel<H><<<(a.n + rows_per_block - 1) / rows_per_block, threads, 0, st>>>(
+        a.n, k.splits, k.part_o, k.part_lse, k.part_max, k.part_arg, a.bias, a.out_scale, a.retrieved, a.lse, a.argmax,
+        a.rowmax);
     HOP_LAUNCH_CHECK("tc_combine_kernel");
   }
   return HOP_OK;
@@ -851,12 +865,16 @@ extern "C" int hop_sm100_debug_trace(long long* dst_host, int n) {
 }
 #endif
 
-bool tc_supported(int h, int dv) { return h == dv && (h == 64 || h == 128 || h == 256); }
+bool tc_supported(int h, int dv) { return h == dv && (h == 64 || h == 128 || h == 256 || h == 512); }
+
+// read-out column chunks (gridDim.z): the O accumulator of one CTA holds at most 256 fp32 TMEM columns
+static inline int tc_dv_chunks(int d) { return d > 256 ? d / 256 : 1; }
 
 // Pattern splits per 128-row tile: the smallest count that fills >= 95 % of the last wave of SMs
-// (retrieve updates need the full softmax per pass, so T > 0 never splits).
+// (on-chip retrieve updates need the full softmax per pass, so T > 0 never splits; D = 512 runs its updates as
+// separate launches and may split every one of them).
 int tc_choose_splits(int n, int p, int d, int update_steps) {
-  if (update_steps > 0) return 1;
+  if (update_steps > 0 && tc_dv_chunks(d) == 1) return 1;
   const int nt_all = padded_patterns(p) / kTileP;
   if (const char* e = getenv("HOP_TC_SPLITS")) {          // test knob: force a split count
     const int s = atoi(e);
@@ -864,7 +882,7 @@ int tc_choose_splits(int n, int p, int d, int update_steps) {
   }
   const int sms = num_sms();
   const int cl = tc_choose_cluster(n, d);
-  const int row_tiles = ((n + kTileM - 1) / kTileM + cl - 1) / cl * cl;
+  const int row_tiles = ((n + kTileM - 1) / kTileM + cl - 1) / cl * cl * tc_dv_chunks(d);
   const int nt_total = padded_patterns(p) / kTileP;
   const int max_splits = nt_total < 32 ? nt_total : 32;
   int best = 1;
@@ -910,32 +928,55 @@ size_t tc_forward_workspace(int n, int p, int d, int update_steps) {
   return round_up_sz(rows * d * sizeof(float), 256) + 3 * round_up_sz(rows * sizeof(float), 256);
 }
 
-int launch_tc_forward(const TcPassArgs& a, cudaStream_t st) {
-  if (!tc_supported(a.h, a.dv)) HOP_FAIL(HOP_ERR_UNSUPPORTED, "tensor-core path needs H == Dv in {64,128,256}");
-  if (!a.retrieved) HOP_FAIL(HOP_ERR_BAD_ARG, "tensor-core forward: retrieved is NULL");
+static int launch_tc_one(const TcPassArgs& a, cudaStream_t st) {
   const int splits = tc_choose_splits(a.n, a.p, a.h, a.update_steps);
   const int cl = tc_choose_cluster(a.n, a.h);
   const bool pair = tc_use_pair(a.n, a.h);
-#define HOP_TC_DISPATCH(DD, BF)                                            \
-  do {                                                                     \
-    if (pair) return launch_d<DD, BF, 2, true>(a, splits, st);             \
-    if (cl == 4) return launch_d<DD, BF, 4, false>(a, splits, st);         \
-    if (cl == 2) return launch_d<DD, BF, 2, false>(a, splits, st);         \
-    return launch_d<DD, BF, 1, false>(a, splits, st);                      \
+#define HOP_TC_DISPATCH(HH, DVC, BF)                                            \
+  do {                                                                          \
+    if (pair) return launch_d<HH, DVC, BF, 2, true>(a, splits, st);             \
+    if (cl == 4) return launch_d<HH, DVC, BF, 4, false>(a, splits, st);         \
+    if (cl == 2) return launch_d<HH, DVC, BF, 2, false>(a, splits, st);         \
+    return launch_d<HH, DVC, BF, 1, false>(a, splits, st);                      \
   } while (0)
   if (a.bf16) {
     switch (a.h) {
-      case 64: HOP_TC_DISPATCH(64, true);
-      case 128: HOP_TC_DISPATCH(128, true);
-      default: HOP_TC_DISPATCH(256, true);
+      case 64: HOP_TC_DISPATCH(64, 64, true);
+      case 128: HOP_TC_DISPATCH(128, 128, true);
+      case 256: HOP_TC_DISPATCH(256, 256, true);
+      default: HOP_TC_DISPATCH(512, 256, true);
     }
   }
   switch (a.h) {
-    case 64: HOP_TC_DISPATCH(64, false);
-    case 128: HOP_TC_DISPATCH(128, false);
-    default: HOP_TC_DISPATCH(256, false);
+    case 64: HOP_TC_DISPATCH(64, 64, false);
+    case 128: HOP_TC_DISPATCH(128, 128, false);
+    case 256: HOP_TC_DISPATCH(256, 256, false);
+    default: HOP_TC_DISPATCH(512, 256, false);
   }
 #undef HOP_TC_DISPATCH
+}
+
+int launch_tc_forward(const TcPassArgs& a, cudaStream_t st) {
+  if (!tc_supported(a.h, a.dv)) HOP_FAIL(HOP_ERR_UNSUPPORTED, "tensor-core path needs H == Dv in {64,128,256,512}");
+  if (!a.retrieved) HOP_FAIL(HOP_ERR_BAD_ARG, "tensor-core forward: retrieved is NULL");
+  if (tc_dv_chunks(a.h) == 1 || a.update_steps == 0) return launch_tc_one(a, st);
+  // D = 512: the state of a retrieve update is 512 columns wide but one CTA accumulates 256 of them, so every
+  // update is its own launch (read-out operand = K^T, result beta * A K^ = the next launch's prepared state)
+  if (!a.kt16 || !a.qtmp[0] || !a.qtmp[1])
+    HOP_FAIL(HOP_ERR_WORKSPACE, "tensor-core forward with T > 0 at D = 512 needs kt16 and the two state buffers");
+  const float* qs = a.qs;
+  const float* x_raw = a.x_raw;
+  for (int t = 0; t < a.update_steps; ++t) {
+    TcPassArgs b = a;
+    b.x_raw = x_raw; b.qs = qs; b.update_steps = 0; b.vt16 = a.kt16; b.bias = nullptr; b.out_scale = a.beta;
+    b.retrieved = (qs == a.qtmp[0]) ? a.qtmp[1] : a.qtmp[0];
+    b.qsave = nullptr; b.lse = nullptr; b.argmax = nullptr; b.rowmax = nullptr;
+    HOP_TRY(launch_tc_one(b, st));
+    qs = b.retrieved; x_raw = nullptr;
+  }
+  TcPassArgs b = a;
+  b.x_raw = nullptr; b.qs = qs; b.update_steps = 0;
+  return launch_tc_one(b, st);
 }
 
 }  // namespace hop

@@ -314,6 +314,11 @@ TC_CASES = {
     "d64_T1": (64, 640, 384, 1),
     "d128_T3": (128, 512, 256, 3),
     "d256_T1": (256, 1024, 256, 1),
+    # D = 512: the read-out is cut into two 256-column chunks (gridDim.z), updates run as separate launches
+    "d512_p2k": (512, 2048, 512, 0),
+    "d512_ragged": (512, 1100, 257, 0),
+    "d512_single_tile": (512, 640, 100, 0),
+    "d512_T2": (512, 1024, 384, 2),
 }
 
 
@@ -335,8 +340,8 @@ def test_forward_parity_tensor_core(hf, name, splits, monkeypatch):
     """tcgen05 fp16-operand / fp32-accumulate path against the fp32 oracle: rel-L2 <= 1e-3 (north-star bar),
     nearest-pattern index identical wherever the oracle's top-1/top-2 gap exceeds the 16-bit operand noise."""
     D, P, N, T = TC_CASES[name]
-    if splits and T > 0:
-        pytest.skip("retrieve updates never split the pattern axis")
+    if splits and T > 0 and D <= 256:
+        pytest.skip("on-chip retrieve updates never split the pattern axis")
     if splits:
         monkeypatch.setenv("HOP_TC_SPLITS", str(splits))
     ref, dut, g = _sweep_layer(hf, D, P, T)
