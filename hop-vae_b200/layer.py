@@ -27,8 +27,8 @@ import torch.nn as nn
 from torch import Tensor
 
 from . import cabi
-from .ops import (LayerSpec, HopfieldAssociation, prepare_patterns_op, retrieve_op, resolve_path, _PATTERN_SIDE,
-                  _QUERY_SIDE, _PARAM_ORDER)
+from .ops import (LayerSpec, HopfieldAssociation, prepare_patterns, prepare_patterns_op, retrieve, retrieve_op,
+                  resolve_path, _eager, _PATTERN_SIDE, _QUERY_SIDE, _PARAM_ORDER)
 
 _NOT_BUILT = dict(num_heads=1, normalize_hopfield_space=False, normalize_hopfield_space_affine=False,
                   pattern_projection_as_connected=False, association_activation=None, dropout=0.0,
@@ -171,6 +171,7 @@ class HopfieldLayer(nn.Module):
         self.last_lse: Optional[Tensor] = None
         self._cache_key = None
         self._cache = None
+        self._paths: Dict[tuple, int] = {}
         self.reset_parameters()
 
     # ---------------------------------------------------------------- parameters
@@ -215,10 +216,9 @@ class HopfieldLayer(nn.Module):
             for k in _PATTERN_SIDE)
         if key != self._cache_key:
             with torch.no_grad():
-                self._cache = prepare_patterns_op(*[None if pack[k] is None else pack[k].detach().contiguous()
-                                                    for k in _PATTERN_SIDE],
-                                                  spec.flags, path, spec.d_assoc, spec.d_v, spec.update_steps,
-                                                  spec.ln_eps)
+                self._cache = (prepare_patterns if _eager() else prepare_patterns_op)(
+                    *[None if pack[k] is None else pack[k].detach().contiguous() for k in _PATTERN_SIDE],
+                    spec.flags, path, spec.d_assoc, spec.d_v, spec.update_steps, spec.ln_eps)
             self._cache_key = key
         return self._cache
 
@@ -245,12 +245,18 @@ class HopfieldLayer(nn.Module):
             out, argmax = HopfieldAssociation.apply(spec, x, *[None if pack[k] is None else pack[k].contiguous()
                                                                for k in _PARAM_ORDER])
         else:
-            path = resolve_path(spec, x.shape[0], self.quantity)
+            pkey = (spec, x.shape[0], self.quantity)
+            path = self._paths.get(pkey)
+            if path is None:
+                path = self._paths[pkey] = resolve_path(spec, x.shape[0], self.quantity)
             pats = self._prepared(pack, spec, path)
-            res = retrieve_op(x.detach(), *pats, *[None if pack[k] is None else pack[k].detach().contiguous()
-                                                   for k in _QUERY_SIDE],
-                              spec.flags, path, spec.d_in, spec.d_out, spec.update_steps, spec.beta, spec.ln_eps, 0,
-                              False)
+            q = [None if pack[k] is None else pack[k].detach().contiguous() for k in _QUERY_SIDE]
+            if _eager():
+                res = retrieve(x.detach(), *pats, *q, spec.flags, path, spec.d_in, spec.d_out, spec.update_steps,
+                               spec.beta, spec.ln_eps, 0, False, False)
+            else:
+                res = retrieve_op(x.detach(), *pats, *q, spec.flags, path, spec.d_in, spec.d_out, spec.update_steps,
+                                  spec.beta, spec.ln_eps, 0, False)
             out, argmax = res[0], res[4]
             self.last_lse = res[3]
         self.last_argmax = argmax

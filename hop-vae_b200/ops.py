@@ -7,6 +7,7 @@ runs in `libhop_sm100.so`.  CUDA tensors only -- there is no CPU path.
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass
 from typing import List, Optional, Tuple
 
@@ -34,8 +35,48 @@ class LayerSpec:
     ln_eps: float = 1e-5
 
 
-def _stream() -> int:
-    return torch.cuda.current_stream().cuda_stream
+def _stream(dev: Optional[torch.device] = None) -> int:
+    """Raw handle of the current CUDA stream (the launch-bound reference shapes feel every microsecond here)."""
+    idx = torch.cuda.current_device() if dev is None or dev.index is None else dev.index
+    return torch._C._cuda_getCurrentRawStream(idx)
+
+
+class _on_device:
+    """`with torch.cuda.device(dev)` only when `dev` is not already current (the common case costs nothing)."""
+    __slots__ = ("guard",)
+
+    def __init__(self, dev: torch.device):
+        self.guard = None if dev.index is None or dev.index == torch.cuda.current_device() else torch.cuda.device(dev)
+
+    def __enter__(self):
+        if self.guard is not None:
+            self.guard.__enter__()
+
+    def __exit__(self, *exc):
+        if self.guard is not None:
+            self.guard.__exit__(*exc)
+        return False
+
+
+def _eager() -> bool:
+    """Outside torch.compile the plain Python bodies are called directly: the custom-op dispatcher costs ~50 us
+    per call, more than the kernels at the reference's own sizes (N ~ 2k-9k rows, P = 512)."""
+    return not torch.compiler.is_compiling()
+
+
+_WS_BYTES = {}
+
+
+def _workspace_bytes(d: "cabi.HopDesc", key, for_backward: int) -> int:
+    k = (key, for_backward, os.environ.get("HOP_TC_SPLITS"))   # (test knob that changes the split workspace)
+    v = _WS_BYTES.get(k)
+    if v is None:
+        import ctypes as C
+        need = C.c_size_t(0)
+        cabi.check(cabi.load().hop_sm100_workspace_bytes(C.byref(d), for_backward, C.byref(need)),
+                   "hop_sm100_workspace_bytes")
+        v = _WS_BYTES[k] = int(need.value)
+    return v
 
 
 def _req_cuda_f32(t: Optional[Tensor], name: str) -> None:
@@ -66,8 +107,7 @@ def resolve_path(spec: LayerSpec, n_rows: int, n_patterns: int) -> int:
 
 
 # --------------------------------------------------------------------------- prepare_patterns
-@torch.library.custom_op("hop_sm100::prepare_patterns", mutates_args=(), device_types="cuda")
-def prepare_patterns_op(lookup: Tensor, lookup_targets: Optional[Tensor], ln_stored_w: Optional[Tensor],
+def prepare_patterns(lookup: Tensor, lookup_targets: Optional[Tensor], ln_stored_w: Optional[Tensor],
                         ln_stored_b: Optional[Tensor], ln_proj_w: Optional[Tensor], ln_proj_b: Optional[Tensor],
                         wk: Optional[Tensor], bk: Optional[Tensor], wv: Optional[Tensor], bv: Optional[Tensor],
                         wo: Optional[Tensor], flags: int, path: int, d_assoc: int, d_v: int, update_steps: int,
@@ -84,12 +124,16 @@ def prepare_patterns_op(lookup: Tensor, lookup_targets: Optional[Tensor], ln_sto
     P, d_in = lookup.shape
     d_out = wo.shape[0] if (wo is not None and (flags & cabi.F_OUT_PROJ)) else 1
     d = _desc(flags, path, 1, P, d_in, d_assoc, d_v, d_out, update_steps, 1.0, ln_eps)
-    sizes = [C.c_size_t(0) for _ in range(6)]
-    cabi.check(lib.hop_sm100_pattern_bytes(C.byref(d), *[C.byref(s) for s in sizes]), "hop_sm100_pattern_bytes")
     dev = lookup.device
     khat = torch.empty((P, d_assoc), device=dev, dtype=torch.float32)
     vhat = torch.empty((P, d_v), device=dev, dtype=torch.float32)
-    packs = [torch.empty((int(s.value) // 2,), device=dev, dtype=torch.int16) for s in sizes[2:]]
+    if path == cabi.PATH_FP32_SIMT:
+        none16 = torch.empty((0,), device=dev, dtype=torch.int16)
+        packs = [none16, none16, none16, none16]
+    else:
+        sizes = [C.c_size_t(0) for _ in range(6)]
+        cabi.check(lib.hop_sm100_pattern_bytes(C.byref(d), *[C.byref(s) for s in sizes]), "hop_sm100_pattern_bytes")
+        packs = [torch.empty((int(s.value) // 2,), device=dev, dtype=torch.int16) for s in sizes[2:]]
     params = cabi.HopParams(lookup=cabi.ptr(lookup), lookup_targets=cabi.ptr(lookup_targets),
                             ln_stored_w=cabi.ptr(ln_stored_w), ln_stored_b=cabi.ptr(ln_stored_b),
                             ln_proj_w=cabi.ptr(ln_proj_w), ln_proj_b=cabi.ptr(ln_proj_b), wk=cabi.ptr(wk),
@@ -99,10 +143,23 @@ def prepare_patterns_op(lookup: Tensor, lookup_targets: Optional[Tensor], ln_sto
                             kt16=cabi.ptr(packs[1]) if packs[1].numel() else None,
                             vt16=cabi.ptr(packs[2]) if packs[2].numel() else None,
                             vot16=cabi.ptr(packs[3]) if packs[3].numel() else None)
-    with torch.cuda.device(dev):
-        cabi.check(lib.hop_sm100_prepare_patterns(C.byref(d), C.byref(params), C.byref(pats), _stream()),
+    with _on_device(dev):
+        cabi.check(lib.hop_sm100_prepare_patterns(C.byref(d), C.byref(params), C.byref(pats), _stream(dev)),
                    "hop_sm100_prepare_patterns")
     return [khat, vhat] + packs
+
+
+@torch.library.custom_op("hop_sm100::prepare_patterns", mutates_args=(), device_types="cuda")
+def prepare_patterns_op(lookup: Tensor, lookup_targets: Optional[Tensor], ln_stored_w: Optional[Tensor],
+                        ln_stored_b: Optional[Tensor], ln_proj_w: Optional[Tensor], ln_proj_b: Optional[Tensor],
+                        wk: Optional[Tensor], bk: Optional[Tensor], wv: Optional[Tensor], bv: Optional[Tensor],
+                        wo: Optional[Tensor], flags: int, path: int, d_assoc: int, d_v: int, update_steps: int,
+                        ln_eps: float) -> List[Tensor]:
+    """torch.compile-visible wrapper of `prepare_patterns`."""
+    res = prepare_patterns(lookup, lookup_targets, ln_stored_w, ln_stored_b, ln_proj_w, ln_proj_b, wk, bk, wv, bv,
+                           wo, flags, path, d_assoc, d_v, update_steps, ln_eps)
+    # custom-op outputs may not alias each other (the fp32 path shares one empty pack)
+    return res[:2] + [r if r.numel() else torch.empty_like(r) for r in res[2:]]
 
 
 @prepare_patterns_op.register_fake
@@ -120,15 +177,15 @@ def _(lookup, lookup_targets, ln_stored_w, ln_stored_b, ln_proj_w, ln_proj_b, wk
 
 
 # --------------------------------------------------------------------------- retrieve (forward)
-@torch.library.custom_op("hop_sm100::retrieve", mutates_args=(), device_types="cuda")
-def retrieve_op(x: Tensor, khat: Tensor, vhat: Tensor, k16: Tensor, kt16: Tensor, vt16: Tensor, vot16: Tensor,
-                ln_state_w: Optional[Tensor], ln_state_b: Optional[Tensor], wq: Optional[Tensor],
-                bq: Optional[Tensor], wo: Optional[Tensor], bo: Optional[Tensor], flags: int, path: int,
-                d_in: int, d_out: int, update_steps: int, beta: float, ln_eps: float,
-                pattern_offset: int, want_retrieved: bool = True) -> List[Tensor]:
+def retrieve(x: Tensor, khat: Tensor, vhat: Tensor, k16: Tensor, kt16: Tensor, vt16: Tensor, vot16: Tensor,
+             ln_state_w: Optional[Tensor], ln_state_b: Optional[Tensor], wq: Optional[Tensor],
+             bq: Optional[Tensor], wo: Optional[Tensor], bo: Optional[Tensor], flags: int, path: int,
+             d_in: int, d_out: int, update_steps: int, beta: float, ln_eps: float,
+             pattern_offset: int, want_retrieved: bool = True, want_saved: bool = True) -> List[Tensor]:
     """x (N, Din) -> [out (N,Dout|Dv), retrieved (N,Dv), qhat (N,H), lse (N), argmax (N) int32, rowmax (N)].
     With want_retrieved=False and a folded read-out operand (vot16) the tensor-core kernel writes `out`
-    directly and `retrieved` is returned empty."""
+    directly and `retrieved` is returned empty.  want_saved=False (inference) additionally skips everything only
+    the backward needs: `qhat` is returned empty and, with an out-projection, so is `retrieved`."""
     import ctypes as C
     lib = cabi.load()
     for name, t in (("x", x), ("khat", khat), ("vhat", vhat), ("ln_state_w", ln_state_w), ("ln_state_b", ln_state_b),
@@ -138,22 +195,27 @@ def retrieve_op(x: Tensor, khat: Tensor, vhat: Tensor, k16: Tensor, kt16: Tensor
     P, H = khat.shape
     Dv = vhat.shape[1]
     out_proj = bool(flags & cabi.F_OUT_PROJ)
-    d = _desc(flags, path, N, P, d_in, H, Dv, d_out if out_proj else 1, update_steps, beta, ln_eps, pattern_offset)
+    key = (flags, path, N, P, d_in, H, Dv, d_out if out_proj else 1, update_steps, beta, ln_eps, pattern_offset)
+    d = cabi.make_desc(flags=flags, path=path, n_rows=N, n_patterns=P, d_in=d_in, d_assoc=H, d_v=Dv,
+                       d_out=d_out if out_proj else 1, update_steps=update_steps, beta=beta, ln_eps=ln_eps,
+                       pattern_offset=pattern_offset)
     dev = x.device
     out = torch.empty((N, d_out if out_proj else Dv), device=dev, dtype=torch.float32)
-    folded = out_proj and not want_retrieved and vot16.numel() > 0 and path != cabi.PATH_FP32_SIMT
-    if folded:
+    tc = path != cabi.PATH_FP32_SIMT
+    folded = out_proj and not want_retrieved and vot16.numel() > 0 and tc
+    if not want_saved and not tc:
+        want_retrieved = False              # the fp32 kernel's read-out only feeds its fused out-projection
+    if folded or (out_proj and not want_retrieved and not tc):
         retrieved = None
     else:
         retrieved = torch.empty((N, Dv), device=dev, dtype=torch.float32) if out_proj else out
-    qhat = torch.empty((N, H), device=dev, dtype=torch.float32)
-    lse = torch.empty((N,), device=dev, dtype=torch.float32)
-    rowmax = torch.empty((N,), device=dev, dtype=torch.float32)
+    qhat = torch.empty((N, H), device=dev, dtype=torch.float32) if want_saved else None
+    stats = torch.empty((2, N), device=dev, dtype=torch.float32)      # lse, rowmax
+    lse, rowmax = stats[0], stats[1]
     argmax = torch.empty((N,), device=dev, dtype=torch.int32)
-    need = C.c_size_t(0)
-    cabi.check(lib.hop_sm100_workspace_bytes(C.byref(d), 0, C.byref(need)), "hop_sm100_workspace_bytes")
-    use_ws = bool(flags & cabi.F_PROJ_STATE) or update_steps > 0 or path != cabi.PATH_FP32_SIMT
-    ws = torch.empty((int(need.value),), device=dev, dtype=torch.uint8) if use_ws else None
+    use_ws = bool(flags & cabi.F_PROJ_STATE) or update_steps > 0 or tc
+    need = _workspace_bytes(d, key, 0) if use_ws else 0
+    ws = torch.empty((need,), device=dev, dtype=torch.uint8) if use_ws else None
     params = cabi.HopParams(ln_state_w=cabi.ptr(ln_state_w), ln_state_b=cabi.ptr(ln_state_b), wq=cabi.ptr(wq),
                             bq=cabi.ptr(bq), wo=cabi.ptr(wo), bo=cabi.ptr(bo))
     pats = cabi.HopPatterns(khat=cabi.ptr(khat), vhat=cabi.ptr(vhat),
@@ -161,14 +223,30 @@ def retrieve_op(x: Tensor, khat: Tensor, vhat: Tensor, k16: Tensor, kt16: Tensor
                             kt16=cabi.ptr(kt16) if kt16.numel() else None,
                             vt16=cabi.ptr(vt16) if vt16.numel() else None,
                             vot16=cabi.ptr(vot16) if vot16.numel() else None)
-    with torch.cuda.device(dev):
+    with _on_device(dev):
         cabi.check(lib.hop_sm100_forward(C.byref(d), C.byref(params), C.byref(pats), cabi.ptr(x), cabi.ptr(out),
                                          cabi.ptr(retrieved), cabi.ptr(qhat), cabi.ptr(lse), cabi.ptr(argmax),
-                                         cabi.ptr(rowmax), cabi.ptr(ws), int(need.value) if use_ws else 0,
-                                         _stream()), "hop_sm100_forward")
-    if folded:
-        return [out, torch.empty((0, Dv), device=dev, dtype=torch.float32), qhat, lse, argmax, rowmax]
-    return [out, retrieved if out_proj else out.clone(), qhat, lse, argmax, rowmax]
+                                         cabi.ptr(rowmax), cabi.ptr(ws), need, _stream(dev)), "hop_sm100_forward")
+    if qhat is None:
+        qhat = torch.empty((0, H), device=dev, dtype=torch.float32)
+    if retrieved is None:
+        retrieved = torch.empty((0, Dv), device=dev, dtype=torch.float32)
+    elif not out_proj:
+        retrieved = out.clone() if want_saved else out
+    return [out, retrieved, qhat, lse, argmax, rowmax]
+
+
+@torch.library.custom_op("hop_sm100::retrieve", mutates_args=(), device_types="cuda")
+def retrieve_op(x: Tensor, khat: Tensor, vhat: Tensor, k16: Tensor, kt16: Tensor, vt16: Tensor, vot16: Tensor,
+                ln_state_w: Optional[Tensor], ln_state_b: Optional[Tensor], wq: Optional[Tensor],
+                bq: Optional[Tensor], wo: Optional[Tensor], bo: Optional[Tensor], flags: int, path: int,
+                d_in: int, d_out: int, update_steps: int, beta: float, ln_eps: float,
+                pattern_offset: int, want_retrieved: bool = True) -> List[Tensor]:
+    """torch.compile-visible wrapper of `retrieve` (always returns what the backward needs)."""
+    res = retrieve(x, khat, vhat, k16, kt16, vt16, vot16, ln_state_w, ln_state_b, wq, bq, wo, bo, flags, path, d_in,
+                   d_out, update_steps, beta, ln_eps, pattern_offset, want_retrieved, True)
+    # custom-op outputs may not alias each other
+    return [res[0], res[1], res[2], res[3].clone(), res[4], res[5].clone()]
 
 
 @retrieve_op.register_fake
@@ -187,6 +265,50 @@ def _(x, khat, vhat, k16, kt16, vt16, vot16, ln_state_w, ln_state_b, wq, bq, wo,
 _GRAD_ORDER = cabi._GRAD_FIELDS  # order of the returned list
 
 
+def retrieve_backward(grad_out: Tensor, x: Tensor, qhat: Tensor, retrieved: Tensor, lse: Tensor, khat: Tensor,
+                      vhat: Tensor, lookup: Tensor, lookup_targets: Optional[Tensor],
+                      ln_state_w: Optional[Tensor], ln_state_b: Optional[Tensor], ln_stored_w: Optional[Tensor],
+                      ln_stored_b: Optional[Tensor], ln_proj_w: Optional[Tensor], ln_proj_b: Optional[Tensor],
+                      wq: Optional[Tensor], bq: Optional[Tensor], wk: Optional[Tensor], bk: Optional[Tensor],
+                      wv: Optional[Tensor], bv: Optional[Tensor], wo: Optional[Tensor], bo: Optional[Tensor],
+                      flags: int, d_out: int, beta: float, ln_eps: float) -> List[Optional[Tensor]]:
+    """Gradients in the order of hop_grads (None where the parameter is absent)."""
+    import ctypes as C
+    lib = cabi.load()
+    _req_cuda_f32(grad_out, "grad_out")
+    N, d_in = x.shape
+    P, H = khat.shape
+    Dv = vhat.shape[1]
+    out_proj = bool(flags & cabi.F_OUT_PROJ)
+    key = (flags, cabi.PATH_FP32_SIMT, N, P, d_in, H, Dv, d_out if out_proj else 1, 0, beta, ln_eps, 0)
+    d = _desc(flags, cabi.PATH_FP32_SIMT, N, P, d_in, H, Dv, d_out if out_proj else 1, 0, beta, ln_eps)
+    dev = x.device
+    like = lambda t: None if t is None else torch.empty_like(t)
+    g = {
+        "d_x": torch.empty_like(x), "d_lookup": torch.empty_like(lookup), "d_lookup_targets": like(lookup_targets),
+        "d_ln_state_w": like(ln_state_w), "d_ln_state_b": like(ln_state_b), "d_ln_stored_w": like(ln_stored_w),
+        "d_ln_stored_b": like(ln_stored_b), "d_ln_proj_w": like(ln_proj_w), "d_ln_proj_b": like(ln_proj_b),
+        "d_wq": like(wq), "d_bq": like(bq), "d_wk": like(wk), "d_bk": like(bk), "d_wv": like(wv), "d_bv": like(bv),
+        "d_wo": like(wo), "d_bo": like(bo),
+    }
+    need = _workspace_bytes(d, key, 1)
+    ws = torch.empty((need,), device=dev, dtype=torch.uint8)
+    params = cabi.HopParams(lookup=cabi.ptr(lookup), lookup_targets=cabi.ptr(lookup_targets),
+                            ln_state_w=cabi.ptr(ln_state_w), ln_state_b=cabi.ptr(ln_state_b),
+                            ln_stored_w=cabi.ptr(ln_stored_w), ln_stored_b=cabi.ptr(ln_stored_b),
+                            ln_proj_w=cabi.ptr(ln_proj_w), ln_proj_b=cabi.ptr(ln_proj_b), wq=cabi.ptr(wq),
+                            bq=cabi.ptr(bq), wk=cabi.ptr(wk), bk=cabi.ptr(bk), wv=cabi.ptr(wv), bv=cabi.ptr(bv),
+                            wo=cabi.ptr(wo), bo=cabi.ptr(bo))
+    pats = cabi.HopPatterns(khat=cabi.ptr(khat), vhat=cabi.ptr(vhat))
+    grads = cabi.HopGrads(**{k: (cabi.ptr(v) if v is not None and v.numel() else None) for k, v in g.items()})
+    go = grad_out.contiguous()
+    with _on_device(dev):
+        cabi.check(lib.hop_sm100_backward(C.byref(d), C.byref(params), C.byref(pats), cabi.ptr(x), cabi.ptr(qhat),
+                                          cabi.ptr(retrieved), cabi.ptr(lse), cabi.ptr(go), C.byref(grads),
+                                          cabi.ptr(ws), need, _stream(dev)), "hop_sm100_backward")
+    return [g[k] for k in _GRAD_ORDER]
+
+
 @torch.library.custom_op("hop_sm100::retrieve_backward", mutates_args=(), device_types="cuda")
 def retrieve_backward_op(grad_out: Tensor, x: Tensor, qhat: Tensor, retrieved: Tensor, lse: Tensor, khat: Tensor,
                          vhat: Tensor, lookup: Tensor, lookup_targets: Optional[Tensor],
@@ -195,41 +317,11 @@ def retrieve_backward_op(grad_out: Tensor, x: Tensor, qhat: Tensor, retrieved: T
                          wq: Optional[Tensor], bq: Optional[Tensor], wk: Optional[Tensor], bk: Optional[Tensor],
                          wv: Optional[Tensor], bv: Optional[Tensor], wo: Optional[Tensor], bo: Optional[Tensor],
                          flags: int, d_out: int, beta: float, ln_eps: float) -> List[Tensor]:
-    """Gradients in the order of hop_grads (empty tensors where the parameter is absent)."""
-    import ctypes as C
-    lib = cabi.load()
-    _req_cuda_f32(grad_out, "grad_out")
-    N, d_in = x.shape
-    P, H = khat.shape
-    Dv = vhat.shape[1]
-    out_proj = bool(flags & cabi.F_OUT_PROJ)
-    d = _desc(flags, cabi.PATH_FP32_SIMT, N, P, d_in, H, Dv, d_out if out_proj else 1, 0, beta, ln_eps)
-    dev = x.device
-    like = lambda t: torch.empty_like(t) if t is not None else torch.empty((0,), device=dev)
-    g = {
-        "d_x": torch.empty_like(x), "d_lookup": torch.empty_like(lookup), "d_lookup_targets": like(lookup_targets),
-        "d_ln_state_w": like(ln_state_w), "d_ln_state_b": like(ln_state_b), "d_ln_stored_w": like(ln_stored_w),
-        "d_ln_stored_b": like(ln_stored_b), "d_ln_proj_w": like(ln_proj_w), "d_ln_proj_b": like(ln_proj_b),
-        "d_wq": like(wq), "d_bq": like(bq), "d_wk": like(wk), "d_bk": like(bk), "d_wv": like(wv), "d_bv": like(bv),
-        "d_wo": like(wo), "d_bo": like(bo),
-    }
-    need = C.c_size_t(0)
-    cabi.check(lib.hop_sm100_workspace_bytes(C.byref(d), 1, C.byref(need)), "hop_sm100_workspace_bytes")
-    ws = torch.empty((int(need.value),), device=dev, dtype=torch.uint8)
-    params = cabi.HopParams(lookup=cabi.ptr(lookup), lookup_targets=cabi.ptr(lookup_targets),
-                            ln_state_w=cabi.ptr(ln_state_w), ln_state_b=cabi.ptr(ln_state_b),
-                            ln_stored_w=cabi.ptr(ln_stored_w), ln_stored_b=cabi.ptr(ln_stored_b),
-                            ln_proj_w=cabi.ptr(ln_proj_w), ln_proj_b=cabi.ptr(ln_proj_b), wq=cabi.ptr(wq),
-                            bq=cabi.ptr(bq), wk=cabi.ptr(wk), bk=cabi.ptr(bk), wv=cabi.ptr(wv), bv=cabi.ptr(bv),
-                            wo=cabi.ptr(wo), bo=cabi.ptr(bo))
-    pats = cabi.HopPatterns(khat=cabi.ptr(khat), vhat=cabi.ptr(vhat))
-    grads = cabi.HopGrads(**{k: (cabi.ptr(v) if v.numel() else None) for k, v in g.items()})
-    go = grad_out.contiguous()
-    with torch.cuda.device(dev):
-        cabi.check(lib.hop_sm100_backward(C.byref(d), C.byref(params), C.byref(pats), cabi.ptr(x), cabi.ptr(qhat),
-                                          cabi.ptr(retrieved), cabi.ptr(lse), cabi.ptr(go), C.byref(grads),
-                                          cabi.ptr(ws), int(need.value), _stream()), "hop_sm100_backward")
-    return [g[k] for k in _GRAD_ORDER]
+    """torch.compile-visible wrapper of `retrieve_backward` (empty tensors where the parameter is absent)."""
+    res = retrieve_backward(grad_out, x, qhat, retrieved, lse, khat, vhat, lookup, lookup_targets, ln_state_w,
+                            ln_state_b, ln_stored_w, ln_stored_b, ln_proj_w, ln_proj_b, wq, bq, wk, bk, wv, bv, wo,
+                            bo, flags, d_out, beta, ln_eps)
+    return [r if r is not None else torch.empty((0,), device=x.device) for r in res]
 
 
 @retrieve_backward_op.register_fake
@@ -260,11 +352,14 @@ class HopfieldAssociation(torch.autograd.Function):
         N, P = x.shape[0], pd["lookup"].shape[0]
         # the backward kernels are fp32: keep forward and backward on the same (exact) path
         path = cabi.PATH_FP32_SIMT
-        pats = prepare_patterns_op(*[pd[k] for k in _PATTERN_SIDE], spec.flags, path, spec.d_assoc, spec.d_v,
-                                   spec.update_steps, spec.ln_eps)
-        res = retrieve_op(x, *pats, *[pd[k] for k in _QUERY_SIDE], spec.flags, path, spec.d_in, spec.d_out,
-                          spec.update_steps, spec.beta, spec.ln_eps, 0)
+        eager = _eager()
+        pats = (prepare_patterns if eager else prepare_patterns_op)(
+            *[pd[k] for k in _PATTERN_SIDE], spec.flags, path, spec.d_assoc, spec.d_v, spec.update_steps, spec.ln_eps)
+        res = (retrieve if eager else retrieve_op)(
+            x, *pats, *[pd[k] for k in _QUERY_SIDE], spec.flags, path, spec.d_in, spec.d_out, spec.update_steps,
+            spec.beta, spec.ln_eps, 0)
         out, retrieved, qhat, lse, argmax, _ = res
+        ctx.set_materialize_grads(False)
         ctx.spec = spec
         ctx.present = [p is not None for p in params]
         ctx.save_for_backward(x, qhat, retrieved, lse, pats[0], pats[1], *[p for p in params if p is not None])
@@ -274,6 +369,8 @@ class HopfieldAssociation(torch.autograd.Function):
     @staticmethod
     def backward(ctx, grad_out, _grad_argmax):
         spec = ctx.spec
+        if grad_out is None:
+            return (None,) * (2 + len(ctx.present))
         if spec.update_steps != 0:
             raise NotImplementedError("hop_sm100: backward is implemented for update_steps_max == 0 "
                                       "(the setting every Hop-VAE config trains with)")
@@ -281,13 +378,15 @@ class HopfieldAssociation(torch.autograd.Function):
         x, qhat, retrieved, lse, khat, vhat = saved[:6]
         it = iter(saved[6:])
         pd = {k: (next(it) if present else None) for k, present in zip(_PARAM_ORDER, ctx.present)}
-        grads = retrieve_backward_op(grad_out.contiguous(), x, qhat, retrieved, lse, khat, vhat,
-                                     *[pd[k] for k in _PARAM_ORDER], spec.flags, spec.d_out, spec.beta, spec.ln_eps)
+        grads = (retrieve_backward if _eager() else retrieve_backward_op)(
+            grad_out.contiguous(), x, qhat, retrieved, lse, khat, vhat, *[pd[k] for k in _PARAM_ORDER], spec.flags,
+            spec.d_out, spec.beta, spec.ln_eps)
         gd = dict(zip(_GRAD_ORDER, grads))
         outs = [None, gd["d_x"] if ctx.needs_input_grad[1] else None]
         for i, k in enumerate(_PARAM_ORDER):
             gk = gd[_GRAD_OF_PARAM[k]]
-            outs.append(gk if (pd[k] is not None and ctx.needs_input_grad[2 + i] and gk.numel()) else None)
+            outs.append(gk if (pd[k] is not None and ctx.needs_input_grad[2 + i] and gk is not None
+                               and gk.numel()) else None)
         return tuple(outs)
 
 
