@@ -543,6 +543,20 @@ int launch_core(const CoreArgs& a, cudaStream_t st) {
   return launch_core_kv<HC, DVC>(a, st);
 }
 
+// One launch zeroes every accumulation target of a backward call (the RED / atomicAdd destinations): at the
+// reference's sizes a dozen cudaMemsetAsync calls cost more host time than the arithmetic.
+struct ZeroBatch {
+  static constexpr int kMax = 20;
+  float* ptr[kMax]; unsigned long long elems[kMax]; int count;
+};
+
+__global__ void __launch_bounds__(NT) multi_zero_kernel(ZeroBatch z) {
+  float* p = z.ptr[blockIdx.y];
+  const unsigned long long n = z.elems[blockIdx.y];
+  for (unsigned long long i = (unsigned long long)blockIdx.x * NT + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * NT)
+    p[i] = 0.f;
+}
+
 struct BwdWs {
   float *dr, *dqs, *delta, *dkhat, *dvhat, *dvn, *dkn, *dqn;
   size_t total;
@@ -585,10 +599,35 @@ int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patte
   const bool k_proj = d.flags & HOP_F_PROJ_STORED, v_proj = d.flags & HOP_F_PROJ_PATTERN;
   const bool sep_targets = p.lookup_targets != nullptr;
 
+  // every accumulation target is known up front: collect them, zero them with one launch
+  ZeroBatch zb{};
+  size_t zmax = 0;
   auto zero = [&](float* ptr, size_t elems) -> int {
-    if (ptr) HOP_CUDA(cudaMemsetAsync(ptr, 0, elems * sizeof(float), st));
+    if (ptr && elems) {
+      if (zb.count >= ZeroBatch::kMax) HOP_FAIL(HOP_ERR_BAD_ARG, "backward: too many accumulation targets");
+      zb.ptr[zb.count] = ptr; zb.elems[zb.count] = elems; ++zb.count;
+      if (elems > zmax) zmax = elems;
+    }
     return HOP_OK;
   };
+  {
+    const bool has_wt = (sep_targets ? g.d_lookup_targets : g.d_lookup) != nullptr;
+    if (out_proj && g.d_wo) { HOP_TRY(zero(g.d_wo, (size_t)d.d_out * Dv)); HOP_TRY(zero(g.d_bo, d.d_out)); }
+    HOP_TRY(zero(w.dkhat, (size_t)P * H));
+    HOP_TRY(zero(w.dvhat, (size_t)P * Dv));
+    if (q_proj && g.d_wq) { HOP_TRY(zero(g.d_wq, (size_t)H * Din)); HOP_TRY(zero(g.d_bq, H)); }
+    if (g.d_x) { HOP_TRY(zero(g.d_ln_state_w, Din)); HOP_TRY(zero(g.d_ln_state_b, Din)); }
+    if (v_proj && g.d_wv) { HOP_TRY(zero(g.d_wv, (size_t)Dv * Din)); HOP_TRY(zero(g.d_bv, Dv)); }
+    if (has_wt) { HOP_TRY(zero(g.d_ln_proj_w, Din)); HOP_TRY(zero(g.d_ln_proj_b, Din)); }
+    if (k_proj && g.d_wk) { HOP_TRY(zero(g.d_wk, (size_t)H * Din)); HOP_TRY(zero(g.d_bk, H)); }
+    if (g.d_lookup) { HOP_TRY(zero(g.d_ln_stored_w, Din)); HOP_TRY(zero(g.d_ln_stored_b, Din)); }
+    if (zb.count) {
+      int bx = (int)((zmax + NT * 4 - 1) / (NT * 4));
+      if (bx > 64) bx = 64;
+      multi_zero_kernel<<<dim3(bx < 1 ? 1 : bx, zb.count), NT, 0, st>>>(zb);
+      HOP_LAUNCH_CHECK("multi_zero_kernel");
+    }
+  }
 
   // 1. out-projection backward
   const float* dR = grad_out;
@@ -596,16 +635,12 @@ int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patte
     HOP_TRY(launch_linear_nn(grad_out, p.wo, w.dr, N, d.d_out, Dv, st));
     dR = w.dr;
     if (g.d_wo) {
-      HOP_TRY(zero(g.d_wo, (size_t)d.d_out * Dv));
-      HOP_TRY(zero(g.d_bo, d.d_out));
       WgradArgs wa{grad_out, retrieved, N, d.d_out, Dv, 0, nullptr, nullptr, 0.f, g.d_wo, g.d_bo, 0, 1.f};
       HOP_TRY(launch_wgrad(wa, st));
     }
   }
 
   // 2. association core
-  HOP_TRY(zero(w.dkhat, (size_t)P * H));
-  HOP_TRY(zero(w.dvhat, (size_t)P * Dv));
   CoreArgs ca{qhat, pt.khat, pt.vhat, lse, dR, retrieved, w.delta, w.dqs, w.dkhat, w.dvhat, N, P, H, Dv, 0};
   const int hc = (H + 63) / 64, dvc = (Dv + 63) / 64;
   if (hc == 1 && dvc == 1) HOP_TRY((launch_core<1, 1>(ca, st)));
@@ -620,8 +655,6 @@ int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patte
     if (q_proj) {
       // dWq = (beta dqs)^T LN(x), dbq = sum beta dqs ; dqn = beta dqs . Wq
       if (g.d_wq) {
-        HOP_TRY(zero(g.d_wq, (size_t)H * Din));
-        HOP_TRY(zero(g.d_bq, H));
         WgradArgs wa{w.dqs, x, N, H, Din, (d.flags & HOP_F_NORM_STATE) ? 1 : 0, p.ln_state_w, p.ln_state_b, d.ln_eps,
                      g.d_wq, g.d_bq, 0, d.beta};
         HOP_TRY(launch_wgrad(wa, st));
@@ -630,8 +663,6 @@ int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patte
       gq = w.dqn;
     }
     if (g.d_x) {
-      HOP_TRY(zero(g.d_ln_state_w, Din));
-      HOP_TRY(zero(g.d_ln_state_b, Din));
       LnBwdArgs la{x, gq, N, Din, (d.flags & HOP_F_NORM_STATE) ? 1 : 0, p.ln_state_w, d.ln_eps, scale,
                    g.d_x, 0, g.d_ln_state_w, g.d_ln_state_b};
       HOP_TRY(launch_ln_bwd(la, st));
@@ -645,8 +676,6 @@ int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patte
     const float* gv = w.dvhat;
     if (v_proj) {
       if (g.d_wv) {
-        HOP_TRY(zero(g.d_wv, (size_t)Dv * Din));
-        HOP_TRY(zero(g.d_bv, Dv));
         WgradArgs wa{w.dvhat, Wt, P, Dv, Din, (d.flags & HOP_F_NORM_PROJ) ? 1 : 0, p.ln_proj_w, p.ln_proj_b, d.ln_eps,
                      g.d_wv, g.d_bv, 0, 1.f};
         HOP_TRY(launch_wgrad(wa, st));
@@ -655,8 +684,6 @@ int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patte
       gv = w.dvn;
     }
     if (d_wt) {
-      HOP_TRY(zero(g.d_ln_proj_w, Din));
-      HOP_TRY(zero(g.d_ln_proj_b, Din));
       LnBwdArgs la{Wt, gv, P, Din, (d.flags & HOP_F_NORM_PROJ) ? 1 : 0, p.ln_proj_w, d.ln_eps, 1.f,
                    d_wt, 0, g.d_ln_proj_w, g.d_ln_proj_b};
       HOP_TRY(launch_ln_bwd(la, st));
@@ -667,8 +694,6 @@ int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patte
     const float* gk = w.dkhat;
     if (k_proj) {
       if (g.d_wk) {
-        HOP_TRY(zero(g.d_wk, (size_t)H * Din));
-        HOP_TRY(zero(g.d_bk, H));
         WgradArgs wa{w.dkhat, p.lookup, P, H, Din, (d.flags & HOP_F_NORM_STORED) ? 1 : 0, p.ln_stored_w, p.ln_stored_b,
                      d.ln_eps, g.d_wk, g.d_bk, 0, 1.f};
         HOP_TRY(launch_wgrad(wa, st));
@@ -677,8 +702,6 @@ int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patte
       gk = w.dkn;
     }
     if (g.d_lookup) {
-      HOP_TRY(zero(g.d_ln_stored_w, Din));
-      HOP_TRY(zero(g.d_ln_stored_b, Din));
       const int accumulate = (!sep_targets && d_wt != nullptr) ? 1 : 0;
       LnBwdArgs la{p.lookup, gk, P, Din, (d.flags & HOP_F_NORM_STORED) ? 1 : 0, p.ln_stored_w, d.ln_eps, 1.f,
                    g.d_lookup, accumulate, g.d_ln_stored_w, g.d_ln_stored_b};

@@ -13,7 +13,20 @@
 // owns 4 score columns (tx + 16 b) and 4*DVC read-out columns (4 tx + 64 c).
 // The 16 threads of a row group keep the running (max, sum, argmax) replicated
 // via half-warp butterfly shuffles.
+//
+// Small problems (the reference's N = 2k..9k rows against P = 512 patterns) do not fill 148 SMs with row tiles
+// alone: the pattern axis is then cut into `splits` ranges, one CTA each, and the CTAs of one row tile form a
+// thread-block cluster (1 x splits x 1).  Every CTA leaves its un-normalised partial (O, max, sum, argmax) in
+// its own shared memory; after a cluster barrier CTA r merges rows [r BM/splits, (r+1) BM/splits) straight out
+// of its peers' shared memory (DSMEM), runs the fused out-projection on them and writes the result -- still
+// one launch, and no partials in HBM.
+#include <cooperative_groups.h>
+
+#include <cstdlib>
+
 #include "hop_common.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace hop {
 
@@ -26,7 +39,7 @@ constexpr int PS = BP + 4;  // stride of the probability tile
 struct SimtSmemLayout {
   int hs;      // stride of Q / K tiles (floats)
   int ds;      // stride of read-out tile (floats) = 64*DVC
-  int q_off, k_off, b_off, p_off, total;  // float offsets
+  int q_off, k_off, b_off, p_off, st_off, total;  // float offsets
 };
 
 __host__ __device__ inline SimtSmemLayout simt_layout(int bm, int h, int dvc) {
@@ -39,7 +52,8 @@ __host__ __device__ inline SimtSmemLayout simt_layout(int bm, int h, int dvc) {
   L.b_off = L.k_off + BP * L.hs;
   const int b_elems = (BP > bm ? BP : bm) * L.ds;  // reused as the O tile in the epilogue
   L.p_off = L.b_off + b_elems;
-  L.total = L.p_off + bm * PS;
+  L.st_off = L.p_off + bm * PS;      // per-row (max, sum, argmax) of this CTA's pattern range
+  L.total = L.st_off + 3 * bm;
   return L;
 }
 
@@ -66,7 +80,7 @@ __device__ __forceinline__ void load_tile(float* __restrict__ dst, const float* 
 }
 
 template <int RM, int DVC>
-__global__ void __launch_bounds__(NT) hop_fwd_simt_kernel(SimtPassArgs a) {
+__global__ void __launch_bounds__(NT) hop_fwd_simt_kernel(SimtPassArgs a, int splits) {
   extern __shared__ __align__(16) float smem[];
   constexpr int BM = 16 * RM;
   const SimtSmemLayout L = simt_layout(BM, a.h, DVC);
@@ -99,7 +113,7 @@ __global__ void __launch_bounds__(NT) hop_fwd_simt_kernel(SimtPassArgs a) {
               if (a.lnq_b) v += __ldg(a.lnq_b + i);
             }
             v *= a.beta;
-            if (a.qsave) a.qsave[(size_t)gr * a.h + i] = v;
+            if (a.qsave && blockIdx.y == 0) a.qsave[(size_t)gr * a.h + i] = v;
           }
           Qs[r * L.hs + i] = v;
         }
@@ -109,7 +123,7 @@ __global__ void __launch_bounds__(NT) hop_fwd_simt_kernel(SimtPassArgs a) {
     }
   } else {
     load_tile(Qs, a.qs, row0, BM, a.n, a.h, h4, L.hs);
-    if (a.qsave) {
+    if (a.qsave && blockIdx.y == 0) {
       for (int idx = tid; idx < BM * a.h; idx += NT) {
         const int r = idx / a.h, c = idx - r * a.h;
         if (row0 + r < a.n) a.qsave[(size_t)(row0 + r) * a.h + c] = a.qs[(size_t)(row0 + r) * a.h + c];
@@ -132,7 +146,10 @@ __global__ void __launch_bounds__(NT) hop_fwd_simt_kernel(SimtPassArgs a) {
   }
 
   const int n_tiles = (a.p + BP - 1) / BP;
-  for (int t = 0; t < n_tiles; ++t) {
+  const int tiles_per_split = (n_tiles + splits - 1) / splits;
+  const int t_begin = (int)blockIdx.y * tiles_per_split;
+  const int t_end = min(n_tiles, t_begin + tiles_per_split);
+  for (int t = t_begin; t < t_end; ++t) {
     const int p0 = t * BP;
     __syncthreads();  // previous tile's consumers are done with Ks / Bs / Ps (and Qs is written)
     load_tile(Ks, a.khat, p0, BP, a.p, a.h, h4, L.hs);
@@ -231,64 +248,191 @@ __global__ void __launch_bounds__(NT) hop_fwd_simt_kernel(SimtPassArgs a) {
 
   // ---- epilogue ----
   __syncthreads();
-  float* Os = Bs;  // [BM][ds], normalised read-out rows for the fused out-projection
+  float* Os = Bs;  // [BM][ds]: read-out rows for the merge / the fused out-projection
+  int rows_lo = 0, rows_n = BM;   // rows of the tile this CTA finishes
+  if (splits > 1) {
+    // un-normalised partials -> own shared memory, then merge this CTA's share of the rows across the cluster
+    float* St = smem + L.st_off;
 #pragma unroll
-  for (int i = 0; i < RM; ++i) {
-    const int r = ty * RM + i, gr = row0 + r;
-    const float inv = 1.f / l_run[i];
+    for (int i = 0; i < RM; ++i) {
+      const int r = ty * RM + i;
 #pragma unroll
-    for (int c = 0; c < DVC; ++c) {
-      float4 v = make_float4(o[i][c][0] * inv, o[i][c][1] * inv, o[i][c][2] * inv, o[i][c][3] * inv);
-      *reinterpret_cast<float4*>(Os + r * L.ds + 4 * tx + 64 * c) = v;
-      if (a.res != nullptr && gr < a.n) {
-        const int col = 4 * tx + 64 * c;
-        const float vv[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-        for (int e = 0; e < 4; ++e)
-          if (col + e < a.dr) a.res[(size_t)gr * a.dr + col + e] = vv[e] * a.out_scale;
+      for (int c = 0; c < DVC; ++c)
+        *reinterpret_cast<float4*>(Os + r * L.ds + 4 * tx + 64 * c) =
+            make_float4(o[i][c][0], o[i][c][1], o[i][c][2], o[i][c][3]);
+      if (tx == 0) {
+        St[r] = m_run[i];
+        St[BM + r] = l_run[i];
+        St[2 * BM + r] = __int_as_float(arg_run[i]);
       }
     }
-    if (tx == 0 && gr < a.n) {
-      if (a.lse) a.lse[gr] = m_run[i] + __logf(l_run[i]);
-      if (a.argmax) a.argmax[gr] = arg_run[i] + a.pattern_offset;
-      if (a.rowmax) a.rowmax[gr] = m_run[i];
+    cg::cluster_group cluster = cg::this_cluster();
+    cluster.sync();
+    rows_n = BM / splits;
+    rows_lo = (int)blockIdx.y * rows_n;
+    float* Ms = Ps;   // merged rows [rows_n][ds] (the probability tile is free now)
+    float* Mst = Ps + rows_n * L.ds;   // merged (scale per split ..., lse, max, arg) scratch: [rows_n][splits + 3]
+    const int sw = splits + 3;
+    for (int r = tid; r < rows_n; r += NT) {
+      float M = -INFINITY;
+      int arg = 0;
+      for (int sp = 0; sp < splits; ++sp) {
+        const float* pst = cluster.map_shared_rank(St, sp);
+        const float ms = pst[rows_lo + r];
+        if (ms > M) { M = ms; arg = __float_as_int(pst[2 * BM + rows_lo + r]); }   // strict: lower range keeps ties
+      }
+      float Lsum = 0.f;
+      for (int sp = 0; sp < splits; ++sp) {
+        const float* pst = cluster.map_shared_rank(St, sp);
+        const float w = __expf(pst[rows_lo + r] - M);     // exp(-inf) = 0 for an empty range
+        Mst[r * sw + sp] = w;
+        Lsum += w * pst[BM + rows_lo + r];
+      }
+      const float inv = 1.f / Lsum;
+      for (int sp = 0; sp < splits; ++sp) Mst[r * sw + sp] *= inv;
+      Mst[r * sw + splits] = M + __logf(Lsum);
+      Mst[r * sw + splits + 1] = M;
+      Mst[r * sw + splits + 2] = __int_as_float(arg);
     }
+    __syncthreads();
+    for (int idx = tid; idx < rows_n * (L.ds / 4); idx += NT) {
+      const int r = idx / (L.ds / 4), c4 = (idx - r * (L.ds / 4)) * 4;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int sp = 0; sp < splits; ++sp) {
+        const float* pos = cluster.map_shared_rank(Os, sp);
+        const float4 v = *reinterpret_cast<const float4*>(pos + (rows_lo + r) * L.ds + c4);
+        const float w = Mst[r * sw + sp];
+        acc.x = fmaf(w, v.x, acc.x); acc.y = fmaf(w, v.y, acc.y); acc.z = fmaf(w, v.z, acc.z); acc.w = fmaf(w, v.w, acc.w);
+      }
+      *reinterpret_cast<float4*>(Ms + r * L.ds + c4) = acc;
+      const int gr = row0 + rows_lo + r;
+      if (a.res != nullptr && gr < a.n) {
+        const float vv[4] = {acc.x, acc.y, acc.z, acc.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+          if (c4 + e < a.dr) a.res[(size_t)gr * a.dr + c4 + e] = vv[e] * a.out_scale;
+      }
+    }
+    for (int r = tid; r < rows_n; r += NT) {
+      const int gr = row0 + rows_lo + r;
+      if (gr < a.n) {
+        if (a.lse) a.lse[gr] = Mst[r * sw + splits];
+        if (a.rowmax) a.rowmax[gr] = Mst[r * sw + splits + 1];
+        if (a.argmax) a.argmax[gr] = __float_as_int(Mst[r * sw + splits + 2]) + a.pattern_offset;
+      }
+    }
+    cluster.sync();   // peers are done reading this CTA's partials (and Ms is complete for the out-projection)
+    Os = Ms;
+  } else {
+#pragma unroll
+    for (int i = 0; i < RM; ++i) {
+      const int r = ty * RM + i, gr = row0 + r;
+      const float inv = 1.f / l_run[i];
+#pragma unroll
+      for (int c = 0; c < DVC; ++c) {
+        float4 v = make_float4(o[i][c][0] * inv, o[i][c][1] * inv, o[i][c][2] * inv, o[i][c][3] * inv);
+        *reinterpret_cast<float4*>(Os + r * L.ds + 4 * tx + 64 * c) = v;
+        if (a.res != nullptr && gr < a.n) {
+          const int col = 4 * tx + 64 * c;
+          const float vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            if (col + e < a.dr) a.res[(size_t)gr * a.dr + col + e] = vv[e] * a.out_scale;
+        }
+      }
+      if (tx == 0 && gr < a.n) {
+        if (a.lse) a.lse[gr] = m_run[i] + __logf(l_run[i]);
+        if (a.argmax) a.argmax[gr] = arg_run[i] + a.pattern_offset;
+        if (a.rowmax) a.rowmax[gr] = m_run[i];
+      }
+    }
+    __syncthreads();
   }
   if (a.wo != nullptr) {
-    __syncthreads();
-    for (int idx = tid; idx < BM * a.dout; idx += NT) {
-      const int r = idx / a.dout, oc = idx - r * a.dout;
-      if (row0 + r >= a.n) continue;
-      const float* w = a.wo + (size_t)oc * a.dr;
-      float acc = a.bo ? __ldg(a.bo + oc) : 0.f;
-      for (int j = 0; j < a.dr; ++j) acc = fmaf(Os[r * L.ds + j], __ldg(w + j), acc);
-      a.out[(size_t)(row0 + r) * a.dout + oc] = acc;
+    // fused out-projection of the rows this CTA finished (Os row r <-> tile row rows_lo + r):
+    // out = Os . Wo^T is the score contraction again, with 64-row chunks of Wo staged in the K tile
+    const int kc = h4 < L.ds ? h4 : L.ds;          // contraction chunk that fits a K-tile row
+    for (int oc0 = 0; oc0 < a.dout; oc0 += BP) {
+      float acc[RM][4];
+#pragma unroll
+      for (int i = 0; i < RM; ++i)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[i][b] = 0.f;
+      for (int j0 = 0; j0 < a.dr; j0 += kc) {
+        __syncthreads();
+        for (int idx = tid; idx < BP * kc; idx += NT) {
+          const int oc = idx / kc, j = idx - oc * kc;
+          float v = 0.f;
+          if (oc0 + oc < a.dout && j0 + j < a.dr) v = __ldg(a.wo + (size_t)(oc0 + oc) * a.dr + j0 + j);
+          Ks[oc * L.hs + j] = v;
+        }
+        __syncthreads();
+        if (ty * RM < rows_n) {
+          for (int k = 0; k < kc; k += 4) {
+            float4 ov[RM];
+#pragma unroll
+            for (int i = 0; i < RM; ++i) ov[i] = *reinterpret_cast<const float4*>(Os + (ty * RM + i) * L.ds + j0 + k);
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+              const float4 ww = *reinterpret_cast<const float4*>(Ks + (tx + 16 * b) * L.hs + k);
+#pragma unroll
+              for (int i = 0; i < RM; ++i) {
+                acc[i][b] = fmaf(ov[i].x, ww.x, acc[i][b]);
+                acc[i][b] = fmaf(ov[i].y, ww.y, acc[i][b]);
+                acc[i][b] = fmaf(ov[i].z, ww.z, acc[i][b]);
+                acc[i][b] = fmaf(ov[i].w, ww.w, acc[i][b]);
+              }
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < RM; ++i) {
+        const int r = ty * RM + i, gr = row0 + rows_lo + r;
+        if (r >= rows_n || gr >= a.n) continue;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          const int oc = oc0 + tx + 16 * b;
+          if (oc < a.dout) a.out[(size_t)gr * a.dout + oc] = acc[i][b] + (a.bo ? __ldg(a.bo + oc) : 0.f);
+        }
+      }
     }
   }
 }
 
 template <int RM, int DVC>
-int launch_inst(const SimtPassArgs& a, cudaStream_t st) {
+int launch_inst(const SimtPassArgs& a, int splits, cudaStream_t st) {
   constexpr int BM = 16 * RM;
   const SimtSmemLayout L = simt_layout(BM, a.h, DVC);
   const size_t smem = (size_t)L.total * sizeof(float);
   if (smem > 227 * 1024) HOP_FAIL(HOP_ERR_BAD_SHAPE, "fp32 path: tile for H=%d Dr=%d needs %zu B of shared memory", a.h, a.dr, smem);
+  // the merged rows + their scratch live in the probability tile: (BM/splits) * (ds + splits + 3) <= BM * PS
+  while (splits > 1 && (BM % splits != 0 || (BM / splits) * (L.ds + splits + 3) > BM * PS)) splits >>= 1;
   auto kern = hop_fwd_simt_kernel<RM, DVC>;
   if (smem > 48 * 1024) HOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int grid = (a.n + BM - 1) / BM;
-  kern<<<grid, NT, smem, st>>>(a);
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid, splits, 1);
+  cfg.blockDim = dim3(NT);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = splits; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = splits > 1 ? 1 : 0;
+  HOP_CUDA(cudaLaunchKernelEx(&cfg, kern, a, splits));
   HOP_LAUNCH_CHECK("hop_fwd_simt_kernel");
   return HOP_OK;
 }
 
 template <int RM>
-int launch_rm(const SimtPassArgs& a, cudaStream_t st) {
+int launch_rm(const SimtPassArgs& a, int splits, cudaStream_t st) {
   const int dvc = (a.dr + 63) / 64;
   switch (dvc) {
-    case 1: return launch_inst<RM, 1>(a, st);
-    case 2: return launch_inst<RM, 2>(a, st);
+    case 1: return launch_inst<RM, 1>(a, splits, st);
+    case 2: return launch_inst<RM, 2>(a, splits, st);
     case 3:
-    case 4: return launch_inst<RM, 4>(a, st);
+    case 4: return launch_inst<RM, 4>(a, splits, st);
     default: HOP_FAIL(HOP_ERR_UNSUPPORTED, "fp32 path supports read-out width <= 256 (got %d)", a.dr);
   }
 }
@@ -297,16 +441,27 @@ int launch_rm(const SimtPassArgs& a, cudaStream_t st) {
 
 int launch_simt_pass(const SimtPassArgs& a, cudaStream_t st) {
   if (a.h > 256) HOP_FAIL(HOP_ERR_UNSUPPORTED, "fp32 path supports association width <= 256 (got %d)", a.h);
-  // Rows per CTA: large tiles once there are enough rows to give every SM >= 2 CTAs.
+  // Rows per CTA: 64-row tiles keep the inner loops FMA-bound (4 x 4 register tile per thread); when the row
+  // tiles alone leave SMs idle the pattern axis is split across a cluster (see the header) while everything
+  // still fits one wave of resident CTAs and every CTA keeps at least two 64-pattern tiles.
   const int sms = num_sms();
-  int rm = 1;
-  if (a.n >= 64 * 2 * sms) rm = 4;
-  else if (a.n >= 32 * 2 * sms) rm = 2;
-  if (rm == 4 && (a.h > 128 || a.dr > 128)) rm = 2;  // keep the tile under the shared-memory limit
+  int rm = 4;
+  if (a.h > 128 || a.dr > 128) rm = 2;  // keep the tile under the shared-memory limit
+  if (const char* e = getenv("HOP_SIMT_RM")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4) rm = v; }
+  const int row_tiles = (a.n + 16 * rm - 1) / (16 * rm);
+  const int n_tiles = (a.p + BP - 1) / BP;
+  // one wave: at most ~3 CTAs of this kernel are resident per SM (registers / shared memory)
+  const size_t tile_bytes = (size_t)simt_layout(16 * rm, a.h, (a.dr + 63) / 64).total * sizeof(float);
+  int per_sm = (int)((227u * 1024u) / (tile_bytes ? tile_bytes : 1));
+  per_sm = per_sm > 3 ? 3 : (per_sm < 1 ? 1 : per_sm);
+  const int slots = sms * per_sm;
+  int splits = 1;
+  while (splits < 8 && n_tiles >= 4 * splits && row_tiles * splits * 2 <= slots) splits <<= 1;
+  if (const char* e = getenv("HOP_SIMT_SPLITS")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4 || v == 8) splits = v; }
   switch (rm) {
-    case 4: return launch_rm<4>(a, st);
-    case 2: return launch_rm<2>(a, st);
-    default: return launch_rm<1>(a, st);
+    case 4: return launch_rm<4>(a, splits, st);
+    case 2: return launch_rm<2>(a, splits, st);
+    default: return launch_rm<1>(a, splits, st);
   }
 }
 
