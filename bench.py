@@ -270,7 +270,7 @@ def gpu_run(args):
         x_host, _ = make_queries(w, n, seed=1267)
         x_host = x_host.contiguous().pin_memory()
         x_dev = x_host.to(dev)
-        runner = impl.PatternShardedHopfield(layer)
+        runner = impl.PatternShardedHopfield(layer, exchange=args.exchange)
         p_local = runner.count
         sub = build_layer(hflayers.HopfieldLayer, p_local, d, t, w[runner.start:runner.start + p_local], wv, wo).to(dev)
         sub.kernel_path = {1: "fp32", 2: "f16", 3: "bf16"}[path]
@@ -390,6 +390,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "collective"],
+                    help="--mode sharded: fused peer-memory exchange kernel (default on CUDA) or NCCL collectives")
     ap.add_argument("--path", default="auto", choices=["auto", "fp32", "f16", "bf16"])
     ap.add_argument("--mode", default="batch", choices=["batch", "sharded"],
                     help="multi-GPU mode: batch-parallel rows (default, weak scaling) or pattern-sharded with an "

@@ -56,7 +56,19 @@ class HopGrads(C.Structure):
     _fields_ = [(n, _fp) for n in _GRAD_FIELDS]
 
 
-EXPORTS = ["hop_sm100_version", "hop_sm100_last_error", "hop_sm100_select_path", "hop_sm100_pattern_bytes",
+MAX_PEERS = 16
+PEER_FLAG_WORDS = 64
+
+
+class HopPeerMerge(C.Structure):
+    _fields_ = ([("n_rows", C.c_int32), ("d_v", C.c_int32), ("n_ranks", C.c_int32), ("rank", C.c_int32),
+                 ("row_begin", C.c_int32), ("row_count", C.c_int32), ("push_all", C.c_int32), ("epoch", C.c_uint32)]
+                + [(n, _fp * MAX_PEERS) for n in ("o", "lse", "rowmax", "argmax", "out", "lse_out", "argmax_out",
+                                                  "flags")])
+
+
+EXPORTS = ["hop_sm100_peer_merge", "hop_sm100_enable_peer_access", "hop_sm100_ipc_export", "hop_sm100_ipc_import",
+           "hop_sm100_ipc_close", "hop_sm100_version", "hop_sm100_last_error", "hop_sm100_select_path", "hop_sm100_pattern_bytes",
            "hop_sm100_workspace_bytes", "hop_sm100_prepare_patterns", "hop_sm100_forward", "hop_sm100_backward",
            "hop_sm100_merge_shards", "hop_sm100_out_projection", "hop_sm100_launch_count"]
 
@@ -99,6 +111,16 @@ def load() -> C.CDLL:
                                            _fp]
     lib.hop_sm100_out_projection.restype = C.c_int
     lib.hop_sm100_out_projection.argtypes = [C.c_int32, C.c_int32, C.c_int32, _fp, _fp, _fp, _fp, _fp]
+    lib.hop_sm100_peer_merge.restype = C.c_int
+    lib.hop_sm100_peer_merge.argtypes = [P(HopPeerMerge), _fp]
+    lib.hop_sm100_enable_peer_access.restype = C.c_int
+    lib.hop_sm100_enable_peer_access.argtypes = [C.c_int32]
+    lib.hop_sm100_ipc_export.restype = C.c_int
+    lib.hop_sm100_ipc_export.argtypes = [_fp, C.c_char_p, P(C.c_uint64)]
+    lib.hop_sm100_ipc_import.restype = C.c_int
+    lib.hop_sm100_ipc_import.argtypes = [C.c_char_p, C.c_uint64, P(_fp)]
+    lib.hop_sm100_ipc_close.restype = C.c_int
+    lib.hop_sm100_ipc_close.argtypes = [_fp, C.c_uint64]
     got = lib.hop_sm100_version()
     if got != ABI_VERSION:
         raise RuntimeError(f"libhop_sm100.so ABI version {got} != binding {ABI_VERSION}; rebuild the library")

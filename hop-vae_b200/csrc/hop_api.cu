@@ -1,5 +1,7 @@
 // C-ABI entry points (include/hop_sm100.h): argument checking, path selection
 // and orchestration of the kernels.  No device allocation, no host sync.
+#include <cuda.h>
+
 #include <atomic>
 #include <cstdarg>
 #include <cstring>
@@ -295,6 +297,72 @@ int hop_sm100_out_projection(int32_t n_rows, int32_t d_v, int32_t d_out, const f
   if (n_rows <= 0 || d_v <= 0 || d_out <= 0) HOP_FAIL(HOP_ERR_BAD_SHAPE, "out_projection: bad sizes");
   if (!retrieved || !wo || !out) HOP_FAIL(HOP_ERR_BAD_ARG, "out_projection: NULL argument");
   return launch_linear(n_rows, d_v, d_out, retrieved, wo, bo, out, (cudaStream_t)stream);
+}
+
+int hop_sm100_peer_merge(const hop_peer_merge* m, void* stream) {
+  HOP_TRY(device_info(nullptr));
+  if (!m) HOP_FAIL(HOP_ERR_BAD_ARG, "peer_merge: descriptor is NULL");
+  if (m->n_ranks < 1 || m->n_ranks > HOP_MAX_PEERS || m->rank < 0 || m->rank >= m->n_ranks)
+    HOP_FAIL(HOP_ERR_BAD_SHAPE, "peer_merge: rank %d of %d (at most %d peers)", m->rank, m->n_ranks, HOP_MAX_PEERS);
+  if (m->n_rows <= 0 || m->d_v <= 0 || (m->d_v & 3) || m->row_begin < 0 || m->row_count < 0 ||
+      m->row_begin + m->row_count > m->n_rows)
+    HOP_FAIL(HOP_ERR_BAD_SHAPE, "peer_merge: bad sizes (N=%d Dv=%d rows [%d, +%d))", m->n_rows, m->d_v, m->row_begin,
+             m->row_count);
+  if (m->epoch == 0) HOP_FAIL(HOP_ERR_BAD_ARG, "peer_merge: epoch must be non-zero");
+  for (int g = 0; g < m->n_ranks; ++g) {
+    if (!m->o[g] || !m->lse[g] || !m->rowmax[g] || !m->argmax[g] || !m->out[g] || !m->flags[g])
+      HOP_FAIL(HOP_ERR_BAD_ARG, "peer_merge: a buffer of rank %d is NULL", g);
+    if (!aligned16(m->o[g]) || !aligned16(m->out[g])) HOP_FAIL(HOP_ERR_BAD_ALIGN, "peer_merge: o / out must be 16-byte aligned");
+  }
+  return launch_peer_merge(*m, (cudaStream_t)stream);
+}
+
+int hop_sm100_enable_peer_access(int32_t peer_device) {
+  int dev = 0;
+  HOP_CUDA(cudaGetDevice(&dev));
+  if (peer_device == dev) return HOP_OK;
+  int can = 0;
+  HOP_CUDA(cudaDeviceCanAccessPeer(&can, dev, peer_device));
+  if (!can) HOP_FAIL(HOP_ERR_UNSUPPORTED, "device %d cannot access device %d's memory (no P2P path)", dev, peer_device);
+  const cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+  if (e == cudaErrorPeerAccessAlreadyEnabled) { (void)cudaGetLastError(); return HOP_OK; }
+  HOP_CUDA(e);
+  return HOP_OK;
+}
+
+int hop_sm100_ipc_export(const void* ptr, unsigned char handle[HOP_IPC_HANDLE_BYTES], uint64_t* offset) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == HOP_IPC_HANDLE_BYTES, "CUDA IPC handle size");
+  if (!ptr || !handle || !offset) HOP_FAIL(HOP_ERR_BAD_ARG, "ipc_export: NULL argument");
+  using RangeFn = CUresult (*)(CUdeviceptr*, size_t*, CUdeviceptr);
+  void* fp = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &fp, cudaEnableDefault, &q) != cudaSuccess || !fp)
+    HOP_FAIL(HOP_ERR_CUDA, "cuMemGetAddressRange is not available from the driver");
+  CUdeviceptr base = 0;
+  size_t size = 0;
+  const CUresult r = reinterpret_cast<RangeFn>(fp)(&base, &size, (CUdeviceptr)(uintptr_t)ptr);
+  if (r != CUDA_SUCCESS) HOP_FAIL(HOP_ERR_CUDA, "cuMemGetAddressRange failed (%d)", (int)r);
+  cudaIpcMemHandle_t h;
+  HOP_CUDA(cudaIpcGetMemHandle(&h, reinterpret_cast<void*>((uintptr_t)base)));
+  memcpy(handle, &h, sizeof(h));
+  *offset = (uint64_t)((uintptr_t)ptr - (uintptr_t)base);
+  return HOP_OK;
+}
+
+int hop_sm100_ipc_import(const unsigned char handle[HOP_IPC_HANDLE_BYTES], uint64_t offset, void** ptr) {
+  if (!handle || !ptr) HOP_FAIL(HOP_ERR_BAD_ARG, "ipc_import: NULL argument");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof(h));
+  void* base = nullptr;
+  HOP_CUDA(cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess));
+  *ptr = static_cast<char*>(base) + offset;
+  return HOP_OK;
+}
+
+int hop_sm100_ipc_close(void* ptr, uint64_t offset) {
+  if (!ptr) return HOP_OK;
+  HOP_CUDA(cudaIpcCloseMemHandle(static_cast<char*>(ptr) - offset));
+  return HOP_OK;
 }
 
 }  // extern "C"

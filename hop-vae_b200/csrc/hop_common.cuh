@@ -113,6 +113,8 @@ int launch_merge(int n, int dv, int g, int shard, const float* lse_all, const fl
                  const int32_t* argmax_all, float* retrieved, float* lse_out, int32_t* argmax_out,
                  cudaStream_t st);
 
+int launch_peer_merge(const hop_peer_merge& m, cudaStream_t st);
+
 // -------------------------------------------------------------- device side
 #ifdef __CUDACC__
 

@@ -7,6 +7,8 @@
 // lse = log sum_g exp(lse_g).  This kernel rescales the local O_g by w_g in
 // place (so one SUM all-reduce over NVLink finishes the job) and resolves the
 // global lse / nearest pattern.  HBM-bound: reads and writes N*Dv*4 bytes.
+#include <cstdlib>
+
 #include "hop_common.cuh"
 
 namespace hop {
@@ -54,6 +56,147 @@ __global__ void __launch_bounds__(256) merge_kernel(int n, int dv, int g, int sh
   }
 }
 
+// ------------------------------------------------------------------ peer-memory merge (hop_sm100_peer_merge)
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+// flag block of one rank: [0,16) ready[src], [16,32) done[src], [32] block counter, [33] local "go" flag
+constexpr int kFlagDone = HOP_MAX_PEERS, kFlagCounter = 2 * HOP_MAX_PEERS, kFlagGo = 2 * HOP_MAX_PEERS + 1;
+
+// One work item = (row, 32-lane column chunk): a lane pulls one float4 from each of the G ranks.  R items are in
+// flight per warp so that enough bytes are outstanding to cover the NVLink round trip.
+template <int GMAX, int R>
+__global__ void __launch_bounds__(256) peer_merge_kernel(const hop_peer_merge m) {
+  const int G = m.n_ranks, me = m.rank;
+  // ---- opening barrier.  Block 0 talks to the peers (system scope): "my partials are complete" (stream order),
+  // then waits for the same from everyone; the other blocks (all co-resident: grid <= 2 per SM) wait on a local
+  // device-scope flag -- hundreds of blocks polling system-scope flags cost more than the merge itself.
+  if (blockIdx.x == 0) {
+    if (threadIdx.x < G) {
+      __threadfence_system();
+      st_release_sys(m.flags[threadIdx.x] + me, m.epoch);
+      const uint32_t* mine = m.flags[me] + threadIdx.x;
+      while ((int32_t)(ld_acquire_sys(mine) - m.epoch) < 0) __nanosleep(32);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) st_release_gpu(m.flags[me] + kFlagGo, m.epoch);
+  } else {
+    if (threadIdx.x == 0) {
+      const uint32_t* go = m.flags[me] + kFlagGo;
+      while ((int32_t)(ld_acquire_gpu(go) - m.epoch) < 0) __nanosleep(32);
+    }
+    __syncthreads();
+  }
+
+  const int dv4 = m.d_v >> 2;
+  const int chunks = (dv4 + 31) >> 5;
+  const long long items = (long long)m.row_count * chunks;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
+  for (long long base = ((long long)blockIdx.x * wpb + warp) * R; base < items; base += (long long)gridDim.x * wpb * R) {
+    float4 v[R][GMAX];
+    float l[R][GMAX], rm[R][GMAX];
+    int32_t am[R][GMAX];
+    size_t row[R];
+    int c4[R];
+    bool valid[R], first[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const long long it = base + r;
+      valid[r] = it < items;
+      const long long ri = valid[r] ? it / chunks : 0;
+      row[r] = (size_t)m.row_begin + (size_t)ri;
+      const int ch = valid[r] ? (int)(it - ri * chunks) : 0;
+      first[r] = ch == 0;
+      c4[r] = ch * 32 + lane;
+#pragma unroll
+      for (int g = 0; g < GMAX; ++g) {
+        l[r][g] = -INFINITY; rm[r][g] = -INFINITY; am[r][g] = 0x7fffffff;
+        v[r][g] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (g < G && valid[r]) {
+          l[r][g] = __ldcg(m.lse[g] + row[r]);
+          if (first[r]) { rm[r][g] = __ldcg(m.rowmax[g] + row[r]); am[r][g] = __ldcg(m.argmax[g] + row[r]); }
+          if (c4[r] < dv4) v[r][g] = __ldcg(reinterpret_cast<const float4*>(m.o[g] + row[r] * m.d_v) + c4[r]);
+        }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      if (!valid[r]) continue;
+      float mx = -INFINITY;
+#pragma unroll
+      for (int g = 0; g < GMAX; ++g) mx = fmaxf(mx, l[r][g]);
+      float sum = 0.f;
+#pragma unroll
+      for (int g = 0; g < GMAX; ++g) { l[r][g] = (g < G) ? __expf(l[r][g] - mx) : 0.f; sum += l[r][g]; }
+      const float inv = 1.f / sum;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int g = 0; g < GMAX; ++g) {
+        const float w = l[r][g] * inv;
+        acc.x = fmaf(w, v[r][g].x, acc.x); acc.y = fmaf(w, v[r][g].y, acc.y);
+        acc.z = fmaf(w, v[r][g].z, acc.z); acc.w = fmaf(w, v[r][g].w, acc.w);
+      }
+      if (c4[r] < dv4) {
+        if (m.push_all) {
+#pragma unroll
+          for (int g = 0; g < GMAX; ++g)
+            if (g < G) reinterpret_cast<float4*>(m.out[g] + row[r] * m.d_v)[c4[r]] = acc;
+        } else {
+          reinterpret_cast<float4*>(m.out[me] + row[r] * m.d_v)[c4[r]] = acc;
+        }
+      }
+      if (first[r] && lane == 0) {
+        float best = -INFINITY;
+        int32_t arg = 0x7fffffff;
+#pragma unroll
+        for (int g = 0; g < GMAX; ++g)
+          if (rm[r][g] > best || (rm[r][g] == best && am[r][g] < arg)) { best = rm[r][g]; arg = am[r][g]; }
+        const float lse = mx + __logf(sum);
+        if (m.push_all) {
+          for (int g = 0; g < G; ++g) {
+            if (m.lse_out[g]) m.lse_out[g][row[r]] = lse;
+            if (m.argmax_out[g]) m.argmax_out[g][row[r]] = arg;
+          }
+        } else {
+          if (m.lse_out[me]) m.lse_out[me][row[r]] = lse;
+          if (m.argmax_out[me]) m.argmax_out[me][row[r]] = arg;
+        }
+      }
+    }
+  }
+
+  // ---- closing barrier: the last block of this rank tells every peer "my reads of your partials and my stores
+  // into your buffers are done", then waits for the same from all of them before the kernel may complete.
+  __syncthreads();
+  __shared__ int s_last;
+  if (threadIdx.x == 0) {
+    __threadfence_system();     // cumulative over the CTA's stores ordered before it by the barrier
+    uint32_t* counter = m.flags[me] + kFlagCounter;
+    s_last = (atomicAdd(counter, 1u) == gridDim.x - 1) ? 1 : 0;
+    if (s_last) *counter = 0u;
+  }
+  __syncthreads();
+  if (s_last && threadIdx.x < G) {
+    __threadfence_system();
+    st_release_sys(m.flags[threadIdx.x] + kFlagDone + me, m.epoch);
+    const uint32_t* mine = m.flags[me] + kFlagDone + threadIdx.x;
+    while ((int32_t)(ld_acquire_sys(mine) - m.epoch) < 0) __nanosleep(32);
+  }
+}
+
 }  // namespace
 
 int launch_merge(int n, int dv, int g, int shard, const float* lse_all, const float* rowmax_all,
@@ -68,6 +211,23 @@ int launch_merge(int n, int dv, int g, int shard, const float* lse_all, const fl
   merge_kernel<<<(int)blocks, 256, 0, st>>>(n, dv, g, shard, lse_all, rowmax_all, argmax_all, retrieved,
                                             lse_out, argmax_out);
   HOP_LAUNCH_CHECK("merge_kernel");
+  return HOP_OK;
+}
+
+int launch_peer_merge(const hop_peer_merge& m, cudaStream_t st) {
+  const int sms = num_sms();
+  const int chunks = ((m.d_v >> 2) + 31) >> 5;
+  const long long items = (long long)m.row_count * chunks;
+  const int r = m.n_ranks <= 2 ? 4 : (m.n_ranks <= 4 ? 2 : 1);
+  long long want = (items + 8 * r - 1) / (8 * r);      // 8 warps per block, r items per warp per trip
+  const int cap = (m.n_ranks > 8 ? 1 : 2) * sms;       // all blocks co-resident (see the barrier): <= 128 / 147 registers
+  int blocks = (int)(want < 1 ? 1 : (want > cap ? cap : want));
+  if (const char* e = getenv("HOP_PEER_BLOCKS")) { const int v = atoi(e); if (v > 0 && v <= cap) blocks = v; }   // tuning knob
+  if (m.n_ranks <= 2) peer_merge_kernel<2, 4><<<blocks, 256, 0, st>>>(m);
+  else if (m.n_ranks <= 4) peer_merge_kernel<4, 2><<<blocks, 256, 0, st>>>(m);
+  else if (m.n_ranks <= 8) peer_merge_kernel<8, 1><<<blocks, 256, 0, st>>>(m);
+  else peer_merge_kernel<16, 1><<<blocks, 256, 0, st>>>(m);
+  HOP_LAUNCH_CHECK("peer_merge_kernel");
   return HOP_OK;
 }
 

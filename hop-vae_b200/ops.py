@@ -181,11 +181,14 @@ def retrieve(x: Tensor, khat: Tensor, vhat: Tensor, k16: Tensor, kt16: Tensor, v
              ln_state_w: Optional[Tensor], ln_state_b: Optional[Tensor], wq: Optional[Tensor],
              bq: Optional[Tensor], wo: Optional[Tensor], bo: Optional[Tensor], flags: int, path: int,
              d_in: int, d_out: int, update_steps: int, beta: float, ln_eps: float,
-             pattern_offset: int, want_retrieved: bool = True, want_saved: bool = True) -> List[Tensor]:
+             pattern_offset: int, want_retrieved: bool = True, want_saved: bool = True,
+             into: Optional[Tuple[Tensor, Tensor, Tensor]] = None) -> List[Tensor]:
     """x (N, Din) -> [out (N,Dout|Dv), retrieved (N,Dv), qhat (N,H), lse (N), argmax (N) int32, rowmax (N)].
     With want_retrieved=False and a folded read-out operand (vot16) the tensor-core kernel writes `out`
     directly and `retrieved` is returned empty.  want_saved=False (inference) additionally skips everything only
-    the backward needs: `qhat` is returned empty and, with an out-projection, so is `retrieved`."""
+    the backward needs: `qhat` is returned empty and, with an out-projection, so is `retrieved`.
+    `into=(out (N,W), stats (2,N) f32, argmax (N) i32)` writes the results into caller-owned buffers (the
+    peer-mapped exchange buffers of the pattern-sharded mode) instead of fresh tensors."""
     import ctypes as C
     lib = cabi.load()
     for name, t in (("x", x), ("khat", khat), ("vhat", vhat), ("ln_state_w", ln_state_w), ("ln_state_b", ln_state_b),
@@ -200,7 +203,12 @@ def retrieve(x: Tensor, khat: Tensor, vhat: Tensor, k16: Tensor, kt16: Tensor, v
                        d_out=d_out if out_proj else 1, update_steps=update_steps, beta=beta, ln_eps=ln_eps,
                        pattern_offset=pattern_offset)
     dev = x.device
-    out = torch.empty((N, d_out if out_proj else Dv), device=dev, dtype=torch.float32)
+    if into is not None:
+        out = into[0]
+        if out.shape != (N, d_out if out_proj else Dv) or not out.is_contiguous() or out.dtype != torch.float32:
+            raise ValueError("hop_sm100: `into[0]` must be a contiguous float32 (N, out width) tensor")
+    else:
+        out = torch.empty((N, d_out if out_proj else Dv), device=dev, dtype=torch.float32)
     tc = path != cabi.PATH_FP32_SIMT
     folded = out_proj and not want_retrieved and vot16.numel() > 0 and tc
     if not want_saved and not tc:
@@ -210,9 +218,9 @@ def retrieve(x: Tensor, khat: Tensor, vhat: Tensor, k16: Tensor, kt16: Tensor, v
     else:
         retrieved = torch.empty((N, Dv), device=dev, dtype=torch.float32) if out_proj else out
     qhat = torch.empty((N, H), device=dev, dtype=torch.float32) if want_saved else None
-    stats = torch.empty((2, N), device=dev, dtype=torch.float32)      # lse, rowmax
+    stats = into[1] if into is not None else torch.empty((2, N), device=dev, dtype=torch.float32)   # lse, rowmax
     lse, rowmax = stats[0], stats[1]
-    argmax = torch.empty((N,), device=dev, dtype=torch.int32)
+    argmax = into[2] if into is not None else torch.empty((N,), device=dev, dtype=torch.int32)
     use_ws = bool(flags & cabi.F_PROJ_STATE) or update_steps > 0 or tc
     need = _workspace_bytes(d, key, 0) if use_ws else 0
     ws = torch.empty((need,), device=dev, dtype=torch.uint8) if use_ws else None

@@ -205,6 +205,59 @@ int hop_sm100_merge_shards(int32_t n_rows, int32_t d_v, int32_t n_shards, int32_
                            const int32_t* argmax_all, float* retrieved,
                            float* lse_out, int32_t* argmax_out, void* stream);
 
+/* Pattern-sharded mode, exchange fused over NVLink / NVSwitch peer memory (new;
+ * replaces all_gather + merge + all_reduce by ONE kernel per rank):
+ * every rank g keeps its shard-local (O_g, lse_g, rowmax_g, argmax_g) in a
+ * peer-mapped buffer; rank r finishes rows [row_begin, row_begin+row_count):
+ * it waits (flag barrier in peer memory) until every rank's partials of this
+ * `epoch` are complete, pulls the G partial rows with P2P loads, merges them
+ * with the log-sum-exp monoid and stores the result into its own `out` buffer
+ * (push_all = 0, reduce-scatter semantics) or into every rank's (push_all = 1,
+ * all-reduce semantics; P2P stores).  A closing flag barrier makes the kernel's
+ * completion on rank r imply that every peer's rows have landed in r's buffers
+ * and that nobody still reads r's partials.
+ *   o[g] (N,Dv), lse[g] (N), rowmax[g] (N), argmax[g] (N): rank g's partials
+ *   out[g] (N,Dv), lse_out[g] (N), argmax_out[g] (N): rank g's result buffers
+ *   flags[g]: rank g's flag block, HOP_PEER_FLAG_WORDS uint32, zeroed once at
+ *             set-up and owned by the library afterwards
+ *   epoch: the same strictly increasing non-zero number on every rank per call
+ * All pointers must be dereferenceable from the calling rank's device
+ * (cudaIpcOpenMemHandle / cuMem mappings + hop_sm100_enable_peer_access).      */
+#define HOP_MAX_PEERS 16
+#define HOP_PEER_FLAG_WORDS 64
+typedef struct hop_peer_merge {
+  int32_t n_rows, d_v, n_ranks, rank;
+  int32_t row_begin, row_count;
+  int32_t push_all;
+  uint32_t epoch;
+  const float* o[HOP_MAX_PEERS];
+  const float* lse[HOP_MAX_PEERS];
+  const float* rowmax[HOP_MAX_PEERS];
+  const int32_t* argmax[HOP_MAX_PEERS];
+  float* out[HOP_MAX_PEERS];
+  float* lse_out[HOP_MAX_PEERS];
+  int32_t* argmax_out[HOP_MAX_PEERS];
+  uint32_t* flags[HOP_MAX_PEERS];
+} hop_peer_merge;
+int hop_sm100_peer_merge(const hop_peer_merge* m, void* stream);
+
+/* cudaDeviceEnablePeerAccess(peer_device) from the current device (already
+ * enabled is not an error).                                                   */
+int hop_sm100_enable_peer_access(int32_t peer_device);
+
+/* Sharing the exchange block between the ranks of one node (one process per
+ * GPU).  export: CUDA IPC handle of the cudaMalloc allocation that contains
+ * `ptr` plus ptr's offset inside it.  import: maps that allocation into the
+ * calling process on the CURRENT device (cudaIpcMemLazyEnablePeerAccess, so the
+ * calling rank's kernels may load/store it over NVLink) and returns the
+ * address that corresponds to the exporter's `ptr`; the mapping lives until
+ * hop_sm100_ipc_close(ptr, offset) or process exit.  The library allocates
+ * nothing: the block itself belongs to the caller (a torch tensor).           */
+#define HOP_IPC_HANDLE_BYTES 64
+int hop_sm100_ipc_export(const void* ptr, unsigned char handle[HOP_IPC_HANDLE_BYTES], uint64_t* offset);
+int hop_sm100_ipc_import(const unsigned char handle[HOP_IPC_HANDLE_BYTES], uint64_t offset, void** ptr);
+int hop_sm100_ipc_close(void* ptr, uint64_t offset);
+
 /* out = retrieved . Wo^T + bo on (N, Dv) -> (N, Dout); used after a shard
  * merge (upstream `out_proj`, ckpt keys ...association_core.out_proj.*).     */
 int hop_sm100_out_projection(int32_t n_rows, int32_t d_v, int32_t d_out,

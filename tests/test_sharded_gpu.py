@@ -32,17 +32,33 @@ for (D, P, N, T, path, bar) in [(64, 512, 300, 0, "fp32", 1e-5), (64, 515, 77, 2
     full = impl.HopfieldLayer(**kw); full.load_state_dict(ref.state_dict()); full = full.cuda(); full.kernel_path = path
     idx = torch.randint(0, P, (N,), generator=g)
     x = ref.lookup_weights[0, idx].detach() + 0.5 * torch.randn(N, D, generator=g)
-    sh = impl.PatternShardedHopfield(full)
     with torch.no_grad():
         want, _, scores, _ = ref(x[None], return_details=True)
-        got = sh(x.cuda())
-    r = rel_l2(got, want[0])
     s = scores.reshape(N, P); top2 = s.topk(2, -1).values
     decided = (top2[:, 0] - top2[:, 1]) > (2e-2 if path == "f16" else 1e-5)
-    if T == 0:
-        assert torch.equal(sh.last_argmax.cpu().long()[decided], s.argmax(-1)[decided])
-    print(f"rank {rank}: D={D} P={P} T={T} {path}: rel-L2 {r:.3e}", flush=True)
-    assert r < bar, r
+    outs = {}
+    # "peer": one fused kernel per rank over NVLink peer memory; "collective": all_gather + merge + all_reduce
+    for exchange in ("peer", "collective"):
+        sh = impl.PatternShardedHopfield(full, exchange=exchange)
+        assert sh.use_peer == (exchange == "peer")
+        with torch.no_grad():
+            for rep in range(3):                       # repeated calls: flag epochs and buffer parity
+                got = sh(x.cuda()).clone()
+        r = rel_l2(got, want[0])
+        if T == 0:
+            assert torch.equal(sh.last_argmax.cpu().long()[decided], s.argmax(-1)[decided])
+        if T == 0:
+            assert rel_l2(sh.last_lse, torch.logsumexp(s, -1)) < (1e-3 if path == "f16" else 1e-5)
+        print(f"rank {rank}: D={D} P={P} T={T} {path} {exchange}: rel-L2 {r:.3e}", flush=True)
+        assert r < bar, r
+        outs[exchange] = got
+    assert rel_l2(outs["peer"], outs["collective"]) < 1e-5
+    if T == 0 and N % world == 0:
+        sh = impl.PatternShardedHopfield(full, exchange="peer", scatter_rows=True)
+        with torch.no_grad():
+            mine = sh(x.cuda())
+        rows = N // world
+        assert rel_l2(mine, want[0][rank * rows:(rank + 1) * rows]) < bar
 dist.destroy_process_group()
 '''
 
