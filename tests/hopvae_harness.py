@@ -129,6 +129,15 @@ class HopVAEHarness(nn.Module):
         e = emb.view(-1, r, r, self.cfg.embedding_dim).permute(0, 3, 1, 2).contiguous()
         return self.decoder(e)
 
+    def sample_from_indices(self, idx):
+        """`HopVAE.sample()` after the prior (HopVAE.py:188-200): idx (S, index_dim, R, R) integer levels ->
+        (z_embeddings (S, R*R, D), x_sample)."""
+        r = self.cfg.representation_dim
+        z = idx.type(torch.int64) / (self.cfg.num_levels - 1)
+        z = z.permute(0, 2, 3, 1).contiguous().view(-1, r * r, self.cfg.index_dim)
+        emb = self.index_to_embedding(z)
+        return emb, self.decode(emb)
+
     def forward(self, x):
         b = self.bottleneck(self.encode(x))
         return self.decode(b["emb"]), b["emb_recon_loss"]
