@@ -10,7 +10,7 @@ import torch.nn.functional as F
 import hopvae_harness as H
 from oracle import hflayers_oracle as O
 from oracle.hopfield_f64 import hopfield_forward_f64
-from util import layer_state, load_ckpt, load_golden, rel_l2, randomize_
+from util import layer_state, load_ckpt, load_golden, load_sample_golden, rel_l2, randomize_
 
 
 @pytest.fixture(scope="module")
@@ -148,3 +148,15 @@ def test_projected_patterns_shapes():
     layer = O.HopfieldLayer(input_size=12, hidden_size=20, pattern_size=24, output_size=5, quantity=30)
     assert layer.hopfield.association_core.in_proj_weight.shape == (20 + 20 + 24, 12)
     assert layer(torch.randn(2, 3, 12)).shape == (2, 3, 5)
+
+
+@pytest.mark.parametrize("tag", ["prior", "batch"])
+def test_golden_sample_path(model, tag):
+    """BASELINE config 4 (HopVAE.sample, HopVAE.py:187-200): prior indices -> index_to_embedding -> decoder,
+    against the outputs of the reference itself (fixture generated by tests/golden/make_golden_sample.py)."""
+    g = load_sample_golden()
+    idx = torch.from_numpy(g[f"idx_{tag}"])
+    with torch.no_grad():
+        emb, x = model.sample_from_indices(idx)
+    assert torch.equal(emb, torch.from_numpy(g[f"emb_{tag}"]))
+    assert torch.equal(x, torch.from_numpy(g[f"x_{tag}"]))

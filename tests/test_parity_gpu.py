@@ -13,7 +13,7 @@ import torch.nn.functional as F
 
 import hopvae_harness as H
 from oracle import hflayers_oracle as O
-from util import REL_L2_BAR, RECON_MSE_REL_BAR, load_ckpt, load_golden, rel_l2, randomize_
+from util import REL_L2_BAR, RECON_MSE_REL_BAR, load_ckpt, load_golden, load_sample_golden, rel_l2, randomize_
 
 pytestmark = pytest.mark.gpu
 
@@ -180,6 +180,22 @@ def test_checkpoint_golden_parity(ckpt_models, tag):
     print(f"{tag} recon MSE {mse:.6e} vs {want_mse:.6e}")
     assert abs(mse - want_mse) <= RECON_MSE_REL_BAR * want_mse
     assert abs(float(b["emb_recon_loss"]) - float(g[f"{tag}_emb_recon_loss"])) <= 5e-3 * float(g[f"{tag}_emb_recon_loss"])
+
+
+@pytest.mark.parametrize("tag", ["prior", "batch"])
+def test_sample_path_golden_parity(ckpt_models, tag):
+    """BASELINE config 4: prior indices -> `index_to_embedding` (D = 3 Hopfield layer, sm_100a kernels) -> decoder,
+    against the reference's own HopVAE.sample() outputs (committed fixture)."""
+    _, dut = ckpt_models
+    g = load_sample_golden()
+    idx = torch.from_numpy(g[f"idx_{tag}"]).cuda()
+    with torch.no_grad():
+        emb, x = dut.sample_from_indices(idx)
+    assert dut.index_to_embedding.last_argmax.shape == (idx.shape[0] * 64,)
+    r_emb, r_x = rel_l2(emb, g[f"emb_{tag}"]), rel_l2(x, g[f"x_{tag}"])
+    print(f"sample[{tag}]: embeddings rel-L2 {r_emb:.3e}, decoded image rel-L2 {r_x:.3e}")
+    assert r_emb < FP32_BAR
+    assert r_x < 1e-4                      # cuDNN vs CPU convolutions downstream of identical embeddings
 
 
 def test_checkpoint_full_forward(ckpt_models):

@@ -22,6 +22,12 @@ def load_golden():
     return np.load(os.path.join(GOLDEN, "mnist28_golden.npz"))
 
 
+def load_sample_golden():
+    """BASELINE config 4: the reference's own HopVAE.sample() run in the build container
+    (tests/golden/make_golden_sample.py)."""
+    return np.load(os.path.join(GOLDEN, "pixelcnn_sample_golden.npz"))
+
+
 def load_ckpt():
     return torch.load(os.path.join(GOLDEN, "MNIST-28.ckpt"), map_location="cpu", weights_only=True)
 
