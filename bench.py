@@ -237,6 +237,26 @@ def timed_steps(fn, steps, flush, torch):
     return [a.elapsed_time(b) for a, b in evs]
 
 
+def bind_to_gpu_numa_node(index):
+    """Multi-rank runs: pin this process to the CPUs next to its GPU (NVML's ideal affinity) BEFORE the pinned
+    host buffers are allocated, so that they land on that NUMA node and 8 ranks do not all pull their host-side
+    copies through one socket.  Best effort: returns the CPU count bound to, or None."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        n_cpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (n_cpu + 63) // 64)
+        cpus = {64 * w + b for w, m in enumerate(words) for b in range(64) if (m >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return len(cpus)
+    except Exception:  # noqa: BLE001  (no NVML / not permitted: keep the default placement)
+        pass
+    return None
+
+
 def gpu_run(args):
     import torch
     import torch.distributed as dist
@@ -247,6 +267,7 @@ def gpu_run(args):
         raise SystemExit("bench.py: no CUDA device (the Hopfield retrieval op is sm_100a only; no CPU fallback)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa = bind_to_gpu_numa_node(local) if world > 1 else None
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     import hflayers
@@ -279,6 +300,10 @@ def gpu_run(args):
         runner = layer
         raw = RawForward(impl, layer, x_dev, path)
 
+    e2e_chunks = args.e2e_chunks
+    if isinstance(e2e_chunks, str):
+        e2e_chunks = tuple(float(v) for v in e2e_chunks.split(",")) if "," in e2e_chunks else int(e2e_chunks)
+
     def step_dev():
         with torch.no_grad():
             return runner(x_dev)
@@ -291,7 +316,7 @@ def gpu_run(args):
                 y = runner(x_stage)
                 out_host.copy_(y.reshape(n, d), non_blocking=True)
             else:
-                layer.forward_host(x_host, out_host, chunks=args.e2e_chunks)
+                layer.forward_host(x_host, out_host, chunks=e2e_chunks)
 
     def barrier():
         torch.cuda.synchronize()
@@ -343,7 +368,7 @@ def gpu_run(args):
                        "parallelism": (f"pattern-sharded{world} (P/{world} per GPU, NCCL LSE merge)" if sharded
                                        else f"batch-dp{world}"), "kernel_path":
                        {1: "fp32_simt", 2: "tc_f16", 3: "tc_bf16"}[path],
-                       "l2": "flushed between timed steps (256 MiB memset outside the events)"},
+                       "host_numa_cpus": numa, "l2": "flushed between timed steps (256 MiB memset outside the events)"},
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": x_host.numel() * 4,
                     "d2h_bytes_per_step": out_host.numel() * 4,
                     "api": ("PatternShardedHopfield.forward on a staged copy" if sharded else
@@ -396,7 +421,8 @@ def main():
     ap.add_argument("--mode", default="batch", choices=["batch", "sharded"],
                     help="multi-GPU mode: batch-parallel rows (default, weak scaling) or pattern-sharded with an "
                          "NCCL log-sum-exp merge (strong scaling in P)")
-    ap.add_argument("--e2e-chunks", type=int, default=None, help="row chunks of the pipelined host-buffer call")
+    ap.add_argument("--e2e-chunks", default=None,
+                    help="row chunks of the pipelined host-buffer call: a count (equal pieces) or weights like 1,3,3,1")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")

@@ -263,10 +263,11 @@ class HopfieldLayer(nn.Module):
         return out.reshape(*lead, out.shape[-1])
 
     # ------------------------------------------------------- host-buffer entry point
-    def forward_host(self, x_host: Tensor, out_host: Optional[Tensor] = None, chunks: Optional[int] = None) -> Tensor:
+    def forward_host(self, x_host: Tensor, out_host: Optional[Tensor] = None, chunks=None) -> Tensor:
         """Host-buffer call: `x_host` (N, input_size) pinned fp32 -> `out_host` (N, output_size) pinned fp32.
 
-        The rows are cut into `chunks` pieces (multiples of 128 rows); the host->device copy of piece i+1, the
+        The rows are cut into `chunks` pieces (an int: equal pieces; a sequence of weights: proportional pieces;
+        multiples of 128 rows); the host->device copy of piece i+1, the
         fused retrieval of piece i and the device->host copy of piece i-1 run on three streams, so the PCIe
         transfers hide behind the kernels.  Returns once all work is *enqueued*; the current stream waits for
         the last device->host copy, so a synchronize / event on the current stream covers everything.
@@ -283,9 +284,19 @@ class HopfieldLayer(nn.Module):
             out_host = torch.empty((n, self.output_size if (self._flags & cabi.F_OUT_PROJ) else self.pattern_size),
                                    dtype=torch.float32).pin_memory()
         if chunks is None:
-            chunks = 4 if n >= 8192 else (2 if n >= 2048 else 1)
-        rows = max(128, (-(-n // max(chunks, 1)) + 127) // 128 * 128)
-        bounds = [(a, min(a + rows, n)) for a in range(0, n, rows)]
+            # ramp: small first / last pieces keep the un-overlapped lead-in copy and lead-out copy short
+            chunks = (1, 3, 3, 1) if n >= 8192 else (2 if n >= 2048 else 1)
+        if isinstance(chunks, int):
+            rows = max(128, (-(-n // max(chunks, 1)) + 127) // 128 * 128)
+            bounds = [(a, min(a + rows, n)) for a in range(0, n, rows)]
+        else:
+            total = float(sum(chunks))
+            cuts, acc = [0], 0.0
+            for w in chunks:
+                acc += w
+                cuts.append(min(n, int(round(n * acc / total / 128.0)) * 128))
+            cuts[-1] = n
+            bounds = [(a, b) for a, b in zip(cuts[:-1], cuts[1:]) if b > a]
         if getattr(self, "_host_streams", None) is None or self._host_streams[0].device != dev:
             self._host_streams = tuple(torch.cuda.Stream(device=dev) for _ in range(3))
         if getattr(self, "_x_stage", None) is None or self._x_stage.shape[0] < n or self._x_stage.device != dev:
