@@ -13,7 +13,11 @@
 //   dK^  = dS^T qs          (P,H),  dV^ = A^T dR  (P,Dv)   [core_kv, split over N, fp32 RED]
 //   then LayerNorm / projection backward on the query side and (twice) on the
 //   pattern side, both paths summing into d_lookup.
+#include <cooperative_groups.h>
+
 #include "hop_common.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace hop {
 
@@ -76,8 +80,11 @@ struct CoreArgs {
 };
 
 // ------------------------------------------------------------------ core_q
+// Like the forward (hop_fwd_simt.cu): 16*RM query rows per CTA; when the row tiles alone do not fill the SMs the
+// pattern axis is cut into `splits` ranges across a thread-block cluster (1 x splits x 1) and the partial dq tiles
+// are summed through distributed shared memory -- no atomics, no partials in HBM.
 template <int RM, int HC, int DVC>
-__global__ void __launch_bounds__(NT) bwd_core_q_kernel(CoreArgs a) {
+__global__ void __launch_bounds__(NT) bwd_core_q_kernel(CoreArgs a, int splits) {
   extern __shared__ __align__(16) float smem[];
   constexpr int BM = 16 * RM;
   constexpr int HS = 64 * HC + 4, VS = 64 * DVC + 4;
@@ -104,7 +111,7 @@ __global__ void __launch_bounds__(NT) bwd_core_q_kernel(CoreArgs a) {
     for (int off = 8; off > 0; off >>= 1) part += __shfl_xor_sync(0xffffffffu, part, off);
     delta_r[i] = part;
     lse_r[i] = gr < a.n ? __ldg(a.lse + gr) : 0.f;
-    if (tx == 0 && gr < a.n) a.delta[gr] = part;
+    if (tx == 0 && gr < a.n && blockIdx.y == 0) a.delta[gr] = part;
   }
 
   float dq[RM][HC][4];
@@ -116,7 +123,10 @@ __global__ void __launch_bounds__(NT) bwd_core_q_kernel(CoreArgs a) {
       for (int e = 0; e < 4; ++e) dq[i][c][e] = 0.f;
 
   const int n_tiles = (a.p + BP - 1) / BP;
-  for (int t = 0; t < n_tiles; ++t) {
+  const int tiles_per_split = (n_tiles + splits - 1) / splits;
+  const int t_begin = (int)blockIdx.y * tiles_per_split;
+  const int t_end = min(n_tiles, t_begin + tiles_per_split);
+  for (int t = t_begin; t < t_end; ++t) {
     const int p0 = t * BP;
     __syncthreads();
     load_tile_pad(Ks, a.khat, p0, BP, a.p, a.h, 64 * HC, HS);
@@ -158,6 +168,38 @@ __global__ void __launch_bounds__(NT) bwd_core_q_kernel(CoreArgs a) {
         }
     }
   }
+  if (splits > 1) {
+    // partial dq tile -> own shared memory (the Q tile is no longer needed), summed across the cluster
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < RM; ++i)
+#pragma unroll
+      for (int c = 0; c < HC; ++c)
+        *reinterpret_cast<float4*>(Qs + (ty * RM + i) * HS + 4 * tx + 64 * c) =
+            make_float4(dq[i][c][0], dq[i][c][1], dq[i][c][2], dq[i][c][3]);
+    cg::cluster_group cluster = cg::this_cluster();
+    cluster.sync();
+    const int rows_n = BM / splits, rows_lo = (int)blockIdx.y * rows_n;
+    constexpr int W4 = 16 * HC;    // float4 per row
+    for (int idx = tid; idx < rows_n * W4; idx += NT) {
+      const int r = rows_lo + idx / W4, c4 = (idx % W4) * 4;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int sp = 0; sp < splits; ++sp) {
+        const float* peer = cluster.map_shared_rank(Qs, sp);
+        const float4 v = *reinterpret_cast<const float4*>(peer + r * HS + c4);
+        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      }
+      const int gr = row0 + r;
+      if (gr < a.n) {
+        const float vv[4] = {acc.x, acc.y, acc.z, acc.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+          if (c4 + e < a.h) a.dqs[(size_t)gr * a.h + c4 + e] = vv[e];
+      }
+    }
+    cluster.sync();   // peers are done reading this CTA's partial
+    return;
+  }
 #pragma unroll
   for (int i = 0; i < RM; ++i) {
     const int gr = row0 + ty * RM + i;
@@ -173,10 +215,10 @@ __global__ void __launch_bounds__(NT) bwd_core_q_kernel(CoreArgs a) {
 }
 
 // ----------------------------------------------------------------- core_kv
-template <int HC, int DVC>
+template <int HC, int DVC, int RQ>
 __global__ void __launch_bounds__(NT) bwd_core_kv_kernel(CoreArgs a) {
   extern __shared__ __align__(16) float smem[];
-  constexpr int RQ = 2, BQ = 16 * RQ;
+  constexpr int BQ = 16 * RQ;      // query rows per step (4 x 4 register tile for the score recompute when RQ = 4)
   constexpr int HS = 64 * HC + 4, VS = 64 * DVC + 4;
   float* Ks = smem;
   float* Vs = Ks + BP * HS;
@@ -511,16 +553,33 @@ int launch_core_q(const CoreArgs& a, cudaStream_t st) {
   const size_t smem = sizeof(float) * (size_t)(BM * HS + BM * VS + BP * HS + BP * VS + BM * PS);
   auto kern = bwd_core_q_kernel<RM, HC, DVC>;
   if (smem > 48 * 1024) HOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kern<<<(a.n + BM - 1) / BM, NT, smem, st>>>(a);
+  // pattern splits across a cluster while everything stays in one wave and every CTA keeps >= 2 tiles
+  const int sms = num_sms();
+  int per_sm = (int)((227u * 1024u) / smem);
+  per_sm = per_sm > 2 ? 2 : (per_sm < 1 ? 1 : per_sm);
+  const int row_tiles = (a.n + BM - 1) / BM, n_tiles = (a.p + BP - 1) / BP;
+  int splits = 1;
+  while (splits < 8 && splits * 2 <= BM && n_tiles >= 4 * splits && row_tiles * splits * 2 <= sms * per_sm) splits <<= 1;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(row_tiles, splits, 1);
+  cfg.blockDim = dim3(NT);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = splits; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = splits > 1 ? 1 : 0;
+  HOP_CUDA(cudaLaunchKernelEx(&cfg, kern, a, splits));
   HOP_LAUNCH_CHECK("bwd_core_q_kernel");
   return HOP_OK;
 }
 
 template <int HC, int DVC>
 int launch_core_kv(CoreArgs a, cudaStream_t st) {
-  constexpr int BQ = 32, HS = 64 * HC + 4, VS = 64 * DVC + 4;
+  constexpr int RQ = (HC == 1 && DVC == 1) ? 4 : 2;
+  constexpr int BQ = 16 * RQ, HS = 64 * HC + 4, VS = 64 * DVC + 4;
   const size_t smem = sizeof(float) * (size_t)(BP * HS + BP * VS + BQ * HS + BQ * VS + 2 * BQ * PS);
-  auto kern = bwd_core_kv_kernel<HC, DVC>;
+  auto kern = bwd_core_kv_kernel<HC, DVC, RQ>;
   if (smem > 48 * 1024) HOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int sms = num_sms();
   const int ptiles = (a.p + BP - 1) / BP;
@@ -537,9 +596,9 @@ int launch_core_kv(CoreArgs a, cudaStream_t st) {
 
 template <int HC, int DVC>
 int launch_core(const CoreArgs& a, cudaStream_t st) {
-  const int sms = num_sms();
-  if (a.n >= 32 * 2 * sms) HOP_TRY((launch_core_q<2, HC, DVC>(a, st)));
-  else HOP_TRY((launch_core_q<1, HC, DVC>(a, st)));
+  // 64-row tiles (4 x 4 register tile) where the shared-memory budget allows, else 32
+  if constexpr (HC == 1 && DVC == 1) HOP_TRY((launch_core_q<4, HC, DVC>(a, st)));
+  else HOP_TRY((launch_core_q<2, HC, DVC>(a, st)));
   return launch_core_kv<HC, DVC>(a, st);
 }
 
