@@ -187,7 +187,7 @@ int hop_sm100_forward(const hop_desc* desc, const hop_params* params, const hop_
   const bool q_proj = (d.flags & HOP_F_PROJ_STATE) != 0;
   const size_t tc_ws = (path != HOP_PATH_FP32_SIMT) ? tc_forward_workspace(d.n_rows, d.n_patterns, d.d_assoc, d.update_steps) : 0;
   const bool need_ws = q_proj || (path == HOP_PATH_FP32_SIMT && d.update_steps > 0) || tc_ws > 0 ||
-                       (path != HOP_PATH_FP32_SIMT && d.update_steps > 0 && d.d_assoc > 256) ||
+                       (path != HOP_PATH_FP32_SIMT && d.update_steps > 0) ||
                        (path != HOP_PATH_FP32_SIMT && out_proj && !retrieved &&
                         !(patterns->vot16 && out_proj_foldable(d)));
   if (need_ws && (!workspace || workspace_bytes < need))

@@ -85,6 +85,8 @@ struct TcCfg {
   static_assert(DV <= 256 && DV <= H && H % DV == 0 && kSmemBytes <= 232448, "TMEM / shared-memory budget");
 };
 
+size_t ws_for_splits_fwd(int splits, int n, int d);   // defined with the host-side heuristics below
+
 struct TcKernelArgs {
   const float* x_raw; const float* lnq_w; const float* lnq_b; float ln_eps; int has_ln; float beta;
   const float* qs; const float* bias;
@@ -818,7 +820,7 @@ int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
   k.retrieved = a.retrieved; k.qsave = a.qsave; k.lse = a.lse; k.argmax = a.argmax; k.rowmax = a.rowmax;
   k.pattern_offset = a.pattern_offset;
   if (k.splits > 1) {
-    const size_t need = tc_forward_workspace(a.n, a.p, a.dv, a.update_steps);
+    const size_t need = ws_for_splits_fwd(splits, a.n, a.dv);
     if (!a.ws || a.ws_bytes < need)
       HOP_FAIL(HOP_ERR_WORKSPACE, "tensor-core forward needs %zu workspace bytes for %d pattern splits, %zu given", need,
                k.splits, a.ws_bytes);
@@ -870,11 +872,30 @@ bool tc_supported(int h, int dv) { return h == dv && (h == 64 || h == 128 || h =
 // read-out column chunks (gridDim.z): the O accumulator of one CTA holds at most 256 fp32 TMEM columns
 static inline int tc_dv_chunks(int d) { return d > 256 ? d / 256 : 1; }
 
+// Retrieve updates run as one launch per pass (state through the fp32 workspace buffers, every pass free to
+// split the pattern axis) instead of on-chip in one persistent launch.  Always at D = 512 (a CTA holds 256 of
+// the 512 state columns).  Knob for experiments: HOP_TC_MULTI = 0 | 1.
+//
+// Also for D <= 256 once one CTA would sweep more than 512 pattern tiles (P > 64k): the tensor core adds into its
+// fp32 accumulator with truncation, a bias that grows with the length of the accumulation chain (measured: the
+// state shrinks by ~1e-3 over 2,048 tiles) and that the retrieve iteration amplifies near its bifurcation
+// (P = 256k, D = 256: rel-L2 2.1e-3 / 9.3e-3 at T = 1 / 3 on-chip).  Short per-split chains, merged in fp32 by
+// the combine kernel, keep it at the operand-rounding level.
+constexpr int kMaxTilesOnChipUpdates = 512;
+constexpr int kMaxChainTilesUpdate = 256;    // pattern tiles one CTA accumulates when T > 0 (multi-launch form)
+constexpr int kMaxChainTilesReadout = 512;   // ... when T = 0 (errors are not amplified)
+static inline bool tc_multi_launch(int p, int d, int update_steps) {
+  if (update_steps <= 0) return false;
+  if (tc_dv_chunks(d) > 1) return true;
+  if (const char* e = getenv("HOP_TC_MULTI")) return atoi(e) != 0;
+  return padded_patterns(p) / kTileP > kMaxTilesOnChipUpdates;
+}
+
 // Pattern splits per 128-row tile: the smallest count that fills >= 95 % of the last wave of SMs
 // (on-chip retrieve updates need the full softmax per pass, so T > 0 never splits; D = 512 runs its updates as
 // separate launches and may split every one of them).
 int tc_choose_splits(int n, int p, int d, int update_steps) {
-  if (update_steps > 0 && tc_dv_chunks(d) == 1) return 1;
+  if (update_steps > 0 && !tc_multi_launch(p, d, update_steps)) return 1;
   const int nt_all = padded_patterns(p) / kTileP;
   if (const char* e = getenv("HOP_TC_SPLITS")) {          // test knob: force a split count
     const int s = atoi(e);
@@ -884,11 +905,14 @@ int tc_choose_splits(int n, int p, int d, int update_steps) {
   const int cl = tc_choose_cluster(n, d);
   const int row_tiles = ((n + kTileM - 1) / kTileM + cl - 1) / cl * cl * tc_dv_chunks(d);
   const int nt_total = padded_patterns(p) / kTileP;
-  const int max_splits = nt_total < 32 ? nt_total : 32;
-  int best = 1;
+  const int chain = update_steps > 0 ? kMaxChainTilesUpdate : kMaxChainTilesReadout;
+  const int min_splits = (nt_total + chain - 1) / chain;            // accuracy: bound the accumulation chain
+  int max_splits = nt_total < 32 ? nt_total : 32;
+  if (max_splits < min_splits + 8) max_splits = min_splits + 8 < nt_total ? min_splits + 8 : nt_total;
+  int best = min_splits;
   double best_eff = 0.0;
-  for (int s = 1; s <= max_splits; ++s) {
-    if (nt_total / s < 4 && s > 1) break;                 // keep >= 4 tiles per CTA
+  for (int s = min_splits; s <= max_splits; ++s) {
+    if (nt_total / s < 4 && s > min_splits) break;        // keep >= 4 tiles per CTA
     const long long items = (long long)row_tiles * s;
     const long long waves = (items + sms - 1) / sms;
     const double eff = (double)items / (double)(waves * sms);
@@ -921,15 +945,19 @@ int tc_choose_cluster(int n, int d) {
   return want;
 }
 
-size_t tc_forward_workspace(int n, int p, int d, int update_steps) {
-  const int splits = tc_choose_splits(n, p, d, update_steps);
+static size_t ws_for_splits(int splits, int n, int d);
+namespace { size_t ws_for_splits_fwd(int splits, int n, int d) { return ws_for_splits(splits, n, d); } }
+static size_t ws_for_splits(int splits, int n, int d) {
   if (splits <= 1) return 0;
   const size_t rows = (size_t)splits * n;
   return round_up_sz(rows * d * sizeof(float), 256) + 3 * round_up_sz(rows * sizeof(float), 256);
 }
 
-static int launch_tc_one(const TcPassArgs& a, cudaStream_t st) {
-  const int splits = tc_choose_splits(a.n, a.p, a.h, a.update_steps);
+size_t tc_forward_workspace(int n, int p, int d, int update_steps) {
+  return ws_for_splits(tc_choose_splits(n, p, d, update_steps), n, d);
+}
+
+static int launch_tc_one(const TcPassArgs& a, int splits, cudaStream_t st) {
   const int cl = tc_choose_cluster(a.n, a.h);
   const bool pair = tc_use_pair(a.n, a.h);
 #define HOP_TC_DISPATCH(HH, DVC, BF)                                            \
@@ -959,11 +987,12 @@ static int launch_tc_one(const TcPassArgs& a, cudaStream_t st) {
 int launch_tc_forward(const TcPassArgs& a, cudaStream_t st) {
   if (!tc_supported(a.h, a.dv)) HOP_FAIL(HOP_ERR_UNSUPPORTED, "tensor-core path needs H == Dv in {64,128,256,512}");
   if (!a.retrieved) HOP_FAIL(HOP_ERR_BAD_ARG, "tensor-core forward: retrieved is NULL");
-  if (tc_dv_chunks(a.h) == 1 || a.update_steps == 0) return launch_tc_one(a, st);
+  const int splits = tc_choose_splits(a.n, a.p, a.h, a.update_steps);   // one count for every pass of this call
+  if (!tc_multi_launch(a.p, a.h, a.update_steps)) return launch_tc_one(a, splits, st);
   // D = 512: the state of a retrieve update is 512 columns wide but one CTA accumulates 256 of them, so every
   // update is its own launch (read-out operand = K^T, result beta * A K^ = the next launch's prepared state)
   if (!a.kt16 || !a.qtmp[0] || !a.qtmp[1])
-    HOP_FAIL(HOP_ERR_WORKSPACE, "tensor-core forward with T > 0 at D = 512 needs kt16 and the two state buffers");
+    HOP_FAIL(HOP_ERR_WORKSPACE, "tensor-core forward with one launch per retrieve update needs kt16 and the two state buffers");
   const float* qs = a.qs;
   const float* x_raw = a.x_raw;
   for (int t = 0; t < a.update_steps; ++t) {
@@ -971,12 +1000,12 @@ int launch_tc_forward(const TcPassArgs& a, cudaStream_t st) {
     b.x_raw = x_raw; b.qs = qs; b.update_steps = 0; b.vt16 = a.kt16; b.bias = nullptr; b.out_scale = a.beta;
     b.retrieved = (qs == a.qtmp[0]) ? a.qtmp[1] : a.qtmp[0];
     b.qsave = nullptr; b.lse = nullptr; b.argmax = nullptr; b.rowmax = nullptr;
-    HOP_TRY(launch_tc_one(b, st));
+    HOP_TRY(launch_tc_one(b, splits, st));
     qs = b.retrieved; x_raw = nullptr;
   }
   TcPassArgs b = a;
   b.x_raw = nullptr; b.qs = qs; b.update_steps = 0;
-  return launch_tc_one(b, st);
+  return launch_tc_one(b, splits, st);
 }
 
 }  // namespace hop

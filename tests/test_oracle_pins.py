@@ -10,7 +10,7 @@ import torch.nn.functional as F
 import hopvae_harness as H
 from oracle import hflayers_oracle as O
 from oracle.hopfield_f64 import hopfield_forward_f64
-from util import layer_state, load_ckpt, load_golden, load_sample_golden, rel_l2, randomize_
+from util import layer_state, load_ckpt, load_golden, load_sample_golden, rel_l2, randomize_, chunked_oracle
 
 
 @pytest.fixture(scope="module")
@@ -160,3 +160,21 @@ def test_golden_sample_path(model, tag):
         emb, x = model.sample_from_indices(idx)
     assert torch.equal(emb, torch.from_numpy(g[f"emb_{tag}"]))
     assert torch.equal(x, torch.from_numpy(g[f"x_{tag}"]))
+
+
+@pytest.mark.parametrize("T", [0, 2])
+def test_chunked_checker_equals_oracle(T):
+    """The P-chunked full-size checker of the config-5 sweep (util.chunked_oracle) is the same function as the
+    restated layer (small size, several chunks)."""
+    import bench
+    w, wv, wo = bench.make_state(2048, 64, T)
+    x, _ = bench.make_queries(w, 24)
+    layer = bench.build_layer(O.HopfieldLayer, 2048, 64, T, w, wv, wo)
+    with torch.no_grad():
+        want, _, scores, _ = layer(x[None], return_details=True)
+    got, arg, gap = chunked_oracle(x, w, wv, wo, T, 1.0 / 8.0, chunk=512)
+    assert rel_l2(got, want[0]) < 2e-6
+    s = scores.reshape(24, 2048)
+    assert torch.equal(arg, s.argmax(-1))
+    top2 = s.topk(2, -1).values
+    assert torch.allclose(gap, top2[:, 0] - top2[:, 1], atol=1e-5)
