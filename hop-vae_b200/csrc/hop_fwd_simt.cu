@@ -400,6 +400,129 @@ __global__ void __launch_bounds__(NT) hop_fwd_simt_kernel(SimtPassArgs a, int sp
   }
 }
 
+// ------------------------------------------------------------------ tiny-width path (H, Dr <= 4)
+// Hop-VAE's `index_to_embedding` layer retrieves over 3-dimensional patterns (HopVAE.py:164-170; all of BASELINE
+// config 4 is this layer): a 64 x 64 tile wastes 15/16 of its read-out lanes on padding.  Here all P patterns
+// (K^ and the read-out matrix, padded to float4) sit in shared memory, four lanes share a query row -- lane q
+// scans patterns q, q+4, ... -- and combine with quad shuffles.  Two passes over the scores (max, then exp /
+// sum / read-out) instead of an online rescale: with H <= 4 recomputing a score costs less than the dependent
+// rescale chain.  LN_q + beta in the prologue, out-projection in the epilogue, like the tiled kernel.
+constexpr int kTinyThreads = 128;
+constexpr int kTinyRows = kTinyThreads / 4;
+
+__global__ void __launch_bounds__(kTinyThreads) hop_fwd_tiny_kernel(SimtPassArgs a) {
+  extern __shared__ __align__(16) float smem[];
+  float4* Ks = reinterpret_cast<float4*>(smem);                 // [P]
+  float4* Bs = Ks + a.p;                                        // [P]
+  float4* Ws = Bs + a.p;                                        // [dout] rows of Wo (dr <= 4 columns), if any
+  float* bs = reinterpret_cast<float*>(Ws + (a.wo ? a.dout : 0));   // [dout] bias
+  const int tid = threadIdx.x;
+  for (int j = tid; j < a.p; j += kTinyThreads) {
+    float kv[4] = {0.f, 0.f, 0.f, 0.f}, bv[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int c = 0; c < a.h; ++c) kv[c] = __ldg(a.khat + (size_t)j * a.h + c);
+    for (int c = 0; c < a.dr; ++c) bv[c] = __ldg(a.bmat + (size_t)j * a.dr + c);
+    Ks[j] = make_float4(kv[0], kv[1], kv[2], kv[3]);
+    Bs[j] = make_float4(bv[0], bv[1], bv[2], bv[3]);
+  }
+  if (a.wo) {
+    for (int oc = tid; oc < a.dout; oc += kTinyThreads) {
+      float wv[4] = {0.f, 0.f, 0.f, 0.f};
+      for (int c = 0; c < a.dr; ++c) wv[c] = __ldg(a.wo + (size_t)oc * a.dr + c);
+      Ws[oc] = make_float4(wv[0], wv[1], wv[2], wv[3]);
+      bs[oc] = a.bo ? __ldg(a.bo + oc) : 0.f;
+    }
+  }
+  __syncthreads();
+
+  const int quad = tid & 3;
+  const long long gr = (long long)blockIdx.x * kTinyRows + (tid >> 2);
+  const bool ok = gr < a.n;
+  // ---- query row: LN_q + beta (every lane of the quad redundantly; H <= 4)
+  float q[4] = {0.f, 0.f, 0.f, 0.f};
+  if (ok) {
+    const float* src = (a.x_raw ? a.x_raw : a.qs) + gr * a.h;
+    for (int c = 0; c < a.h; ++c) q[c] = __ldg(src + c);
+    if (a.x_raw) {
+      if (a.has_ln) {
+        float mean = 0.f;
+        for (int c = 0; c < a.h; ++c) mean += q[c];
+        mean /= (float)a.h;
+        float var = 0.f;
+        for (int c = 0; c < a.h; ++c) { const float d0 = q[c] - mean; var += d0 * d0; }
+        const float rstd = rsqrtf(var / (float)a.h + a.ln_eps);
+        for (int c = 0; c < a.h; ++c) {
+          q[c] = (q[c] - mean) * rstd;
+          if (a.lnq_w) q[c] *= __ldg(a.lnq_w + c);
+          if (a.lnq_b) q[c] += __ldg(a.lnq_b + c);
+        }
+      }
+      for (int c = 0; c < a.h; ++c) q[c] *= a.beta;
+    }
+    if (a.qsave && quad == 0)
+      for (int c = 0; c < a.h; ++c) a.qsave[gr * a.h + c] = q[c];
+  }
+  // ---- pass 1: row maximum and nearest pattern (strict >: the lowest index wins ties inside a lane)
+  float m = -INFINITY;
+  int arg = 0x7fffffff;
+  for (int j = quad; j < a.p; j += 4) {
+    const float4 k = Ks[j];
+    const float s = fmaf(q[3], k.w, fmaf(q[2], k.z, fmaf(q[1], k.y, q[0] * k.x)));
+    if (s > m) { m = s; arg = j; }
+  }
+#pragma unroll
+  for (int off = 1; off <= 2; off <<= 1) {
+    const float om = __shfl_xor_sync(0xffffffffu, m, off);
+    const int oa = __shfl_xor_sync(0xffffffffu, arg, off);
+    if (om > m || (om == m && oa < arg)) { m = om; arg = oa; }
+  }
+  // ---- pass 2: exp, sum, read-out
+  float l = 0.f, acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int j = quad; j < a.p; j += 4) {
+    const float4 k = Ks[j];
+    const float s = fmaf(q[3], k.w, fmaf(q[2], k.z, fmaf(q[1], k.y, q[0] * k.x)));
+    const float pexp = __expf(s - m);
+    const float4 b = Bs[j];
+    l += pexp;
+    acc[0] = fmaf(pexp, b.x, acc[0]); acc[1] = fmaf(pexp, b.y, acc[1]);
+    acc[2] = fmaf(pexp, b.z, acc[2]); acc[3] = fmaf(pexp, b.w, acc[3]);
+  }
+#pragma unroll
+  for (int off = 1; off <= 2; off <<= 1) {
+    l += __shfl_xor_sync(0xffffffffu, l, off);
+#pragma unroll
+    for (int c = 0; c < 4; ++c) acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], off);
+  }
+  if (!ok) return;
+  const float inv = 1.f / l;
+  float r[4];
+#pragma unroll
+  for (int c = 0; c < 4; ++c) r[c] = acc[c] * inv;
+  if (quad == 0) {
+    if (a.res)
+      for (int c = 0; c < a.dr; ++c) a.res[gr * a.dr + c] = r[c] * a.out_scale;
+    if (a.lse) a.lse[gr] = m + __logf(l);
+    if (a.argmax) a.argmax[gr] = arg + a.pattern_offset;
+    if (a.rowmax) a.rowmax[gr] = m;
+  }
+  if (a.wo) {
+    // out-projection: lane `quad` writes output columns quad, quad + 4, ... (a quad covers 16 consecutive bytes)
+    float* dst = a.out + gr * a.dout;
+    for (int oc = quad; oc < a.dout; oc += 4) {
+      const float4 w = Ws[oc];
+      dst[oc] = fmaf(r[3], w.w, fmaf(r[2], w.z, fmaf(r[1], w.y, fmaf(r[0], w.x, bs[oc]))));
+    }
+  }
+}
+
+int launch_tiny(const SimtPassArgs& a, cudaStream_t st) {
+  const size_t smem = sizeof(float4) * (2 * (size_t)a.p + (a.wo ? a.dout : 0)) + sizeof(float) * (a.wo ? a.dout : 0);
+  if (smem > 48 * 1024)
+    HOP_CUDA(cudaFuncSetAttribute(hop_fwd_tiny_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  hop_fwd_tiny_kernel<<<(a.n + kTinyRows - 1) / kTinyRows, kTinyThreads, smem, st>>>(a);
+  HOP_LAUNCH_CHECK("hop_fwd_tiny_kernel");
+  return HOP_OK;
+}
+
 template <int RM, int DVC>
 int launch_inst(const SimtPassArgs& a, int splits, cudaStream_t st) {
   constexpr int BM = 16 * RM;
@@ -441,6 +564,8 @@ int launch_rm(const SimtPassArgs& a, int splits, cudaStream_t st) {
 
 int launch_simt_pass(const SimtPassArgs& a, cudaStream_t st) {
   if (a.h > 256) HOP_FAIL(HOP_ERR_UNSUPPORTED, "fp32 path supports association width <= 256 (got %d)", a.h);
+  if (a.h <= 4 && a.dr <= 4 && a.p <= 4096 && (!a.wo || a.dout <= 1024) && !getenv("HOP_SIMT_NO_TINY"))
+    return launch_tiny(a, st);
   // Rows per CTA: 64-row tiles keep the inner loops FMA-bound (4 x 4 register tile per thread); when the row
   // tiles alone leave SMs idle the pattern axis is split across a cluster (see the header) while everything
   // still fits one wave of resident CTAs and every CTA keeps at least two 64-pattern tiles.

@@ -110,3 +110,46 @@ for name, cfg in (("mnist28", H.MNIST_28), ("ffhq32", H.FFHQ_32), ("ffhq64", H.F
     res["latents_per_s_fwd_eager"] = n / (res["us_fwd_eager"] * 1e-6)
     rows.append(res)
     print(json.dumps(res), flush=True)
+
+
+# BASELINE config 4 (HopVAE.sample after the prior, HopVAE.py:188-200): index tensor -> index_to_embedding (D = 3
+# Hopfield layer) -> decoder.  S = 1 as the reference samples, S = 1024 as the synthetic batch of SURVEY.md 8d.
+torch.manual_seed(1265)
+ref = H.HopVAEHarness(H.MNIST_28, O.HopfieldLayer).to(dev).eval()
+dut = H.HopVAEHarness(H.MNIST_28, hflayers.HopfieldLayer)
+dut.load_state_dict(ref.state_dict())
+dut = dut.to(dev).eval()
+for S in (1, 1024):
+    idx = torch.randint(0, 512, (S, 3, 8, 8), generator=torch.Generator().manual_seed(1265)).to(dev)
+    with torch.no_grad():
+        ea, xa = dut.sample_from_indices(idx)
+        eb, xb = ref.sample_from_indices(idx)
+    res = {"config": f"pixelcnn_sample_S{S}", "rows": 64 * S,
+           "parity_rel_l2_embeddings": float((ea - eb).norm() / eb.norm()),
+           "parity_rel_l2_image": float((xa - xb).norm() / xb.norm())}
+
+    def lookup(m):
+        r = m.cfg.representation_dim
+        z = (idx.type(torch.int64) / (m.cfg.num_levels - 1)).permute(0, 2, 3, 1).contiguous().view(-1, r * r, 3)
+
+        def f():
+            with torch.no_grad():
+                m.index_to_embedding(z)
+        return f
+
+    def whole(m):
+        def f():
+            with torch.no_grad():
+                m.sample_from_indices(idx)
+        return f
+
+    for layer in (ref.index_to_embedding,):
+        layer.faithful = True
+    res["us_index_to_embedding_ours"] = timed(lookup(dut))
+    res["us_index_to_embedding_eager_upstream_shape"] = timed(lookup(ref))
+    res["us_lookup_plus_decoder_ours"] = timed(whole(dut))
+    res["us_lookup_plus_decoder_eager_upstream_shape"] = timed(whole(ref))
+    res["us_index_to_embedding_ours_graph"] = timed(graphed(lookup(dut)))
+    res["latents_per_s_ours"] = 64 * S / (res["us_index_to_embedding_ours"] * 1e-6)
+    print(json.dumps(res), flush=True)
+
