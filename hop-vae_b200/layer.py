@@ -169,6 +169,7 @@ class HopfieldLayer(nn.Module):
         self.kernel_path = os.environ.get("HOP_SM100_PATH", "auto")
         self.last_argmax: Optional[Tensor] = None
         self.last_lse: Optional[Tensor] = None
+        self._pack_cache = None
         self._cache_key = None
         self._cache = None
         self._paths: Dict[tuple, int] = {}
@@ -193,7 +194,23 @@ class HopfieldLayer(nn.Module):
                          beta=self.beta, ln_eps=1e-5)
 
     def param_pack(self) -> Dict[str, Optional[Tensor]]:
-        """The module's tensors under the hop_params names."""
+        """The module's tensors under the hop_params names.  Under no_grad the dict is cached (rebuilt when a
+        parameter's storage moved, e.g. after `.to(device)` -- the q/k/v entries are views of `in_proj_*`); with
+        autograd on it is rebuilt every call so that the views belong to the current graph."""
+        if torch.is_grad_enabled():
+            return self._build_pack()
+        core0 = self.hopfield.association_core
+        stamp = (self.lookup_weights.data_ptr(),
+                 0 if core0.in_proj_weight is None else core0.in_proj_weight.data_ptr(),
+                 0 if core0.in_proj_bias is None else core0.in_proj_bias.data_ptr(),
+                 0 if self.lookup_targets is None else self.lookup_targets.data_ptr())
+        if self._pack_cache is not None and self._pack_cache[0] == stamp:
+            return self._pack_cache[1]
+        pack = self._build_pack()
+        self.__dict__["_pack_cache"] = (stamp, pack)
+        return pack
+
+    def _build_pack(self) -> Dict[str, Optional[Tensor]]:
         h = self.hopfield
         core = h.association_core
         ln = lambda m: (None, None) if m is None else (m.weight, m.bias)
@@ -258,8 +275,8 @@ class HopfieldLayer(nn.Module):
                 res = retrieve_op(x.detach(), *pats, *q, spec.flags, path, spec.d_in, spec.d_out, spec.update_steps,
                                   spec.beta, spec.ln_eps, 0, False)
             out, argmax = res[0], res[4]
-            self.last_lse = res[3]
-        self.last_argmax = argmax
+            self.__dict__["last_lse"] = res[3]     # (plain attribute: nn.Module.__setattr__ costs ~5 us per set)
+        self.__dict__["last_argmax"] = argmax
         return out.reshape(*lead, out.shape[-1])
 
     # ------------------------------------------------------- host-buffer entry point

@@ -64,6 +64,17 @@ def _eager() -> bool:
     return not torch.compiler.is_compiling()
 
 
+_EMPTY_F32 = {}
+
+
+def _empty_f32(dev: torch.device) -> Tensor:
+    """Shared zero-element placeholder for outputs the inference call does not produce."""
+    t = _EMPTY_F32.get(dev)
+    if t is None:
+        t = _EMPTY_F32[dev] = torch.empty((0,), device=dev, dtype=torch.float32)
+    return t
+
+
 _WS_BYTES = {}
 
 
@@ -236,9 +247,9 @@ def retrieve(x: Tensor, khat: Tensor, vhat: Tensor, k16: Tensor, kt16: Tensor, v
                                          cabi.ptr(retrieved), cabi.ptr(qhat), cabi.ptr(lse), cabi.ptr(argmax),
                                          cabi.ptr(rowmax), cabi.ptr(ws), need, _stream(dev)), "hop_sm100_forward")
     if qhat is None:
-        qhat = torch.empty((0, H), device=dev, dtype=torch.float32)
+        qhat = _empty_f32(dev)
     if retrieved is None:
-        retrieved = torch.empty((0, Dv), device=dev, dtype=torch.float32)
+        retrieved = _empty_f32(dev) if not want_saved else torch.empty((0, Dv), device=dev, dtype=torch.float32)
     elif not out_proj:
         retrieved = out.clone() if want_saved else out
     return [out, retrieved, qhat, lse, argmax, rowmax]
