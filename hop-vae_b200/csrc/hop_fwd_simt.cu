@@ -40,22 +40,42 @@ struct SimtSmemLayout {
   int hs;      // stride of Q / K tiles (floats)
   int ds;      // stride of read-out tile (floats) = 64*DVC
   int q_off, k_off, b_off, p_off, st_off, total;  // float offsets
+  int k_elems, b_elems, nbuf;                     // per-buffer sizes of the K / read-out tiles, buffers (1 | 2)
 };
 
-__host__ __device__ inline SimtSmemLayout simt_layout(int bm, int h, int dvc) {
+__host__ __device__ inline SimtSmemLayout simt_layout_n(int bm, int h, int dvc, int nbuf) {
   SimtSmemLayout L;
   const int h4 = (h + 3) / 4 * 4;
   L.hs = h4 + 4;
   L.ds = 64 * dvc;
+  L.nbuf = nbuf;
   L.q_off = 0;
   L.k_off = L.q_off + bm * L.hs;
-  L.b_off = L.k_off + BP * L.hs;
-  const int b_elems = (BP > bm ? BP : bm) * L.ds;  // reused as the O tile in the epilogue
-  L.p_off = L.b_off + b_elems;
+  L.k_elems = BP * L.hs;
+  L.b_off = L.k_off + nbuf * L.k_elems;
+  L.b_elems = (BP > bm ? BP : bm) * L.ds;  // buffer 0 is reused as the O tile in the epilogue
+  L.p_off = L.b_off + nbuf * L.b_elems;
   L.st_off = L.p_off + bm * PS;      // per-row (max, sum, argmax) of this CTA's pattern range
   L.total = L.st_off + 3 * bm;
   return L;
 }
+
+// Two K^ / read-out tile buffers (cp.async prefetch of tile t+1 under the arithmetic of tile t) while two CTAs
+// still fit an SM, else one.
+__host__ __device__ inline SimtSmemLayout simt_layout(int bm, int h, int dvc) {
+  const SimtSmemLayout L2 = simt_layout_n(bm, h, dvc, 2);
+  if ((size_t)L2.total * sizeof(float) <= 110u * 1024u) return L2;
+  return simt_layout_n(bm, h, dvc, 1);
+}
+
+__device__ __forceinline__ void cp_async16(float* dst_smem, const float* src, bool valid) {
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst_smem);
+  const int bytes = valid ? 16 : 0;            // src-size 0: the 16 destination bytes are zero-filled
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(src), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 // Load rows [r0, r0+rows) x [0, w) of a (nrows_total, w) fp32 matrix into smem
 // with stride `stride`, zero-filling rows >= nrows_total and columns in [w, wpad).
@@ -79,6 +99,22 @@ __device__ __forceinline__ void load_tile(float* __restrict__ dst, const float* 
   }
 }
 
+// Same tile as load_tile, issued as 16-byte cp.async copies when the row width allows (multiple of 4 floats);
+// other widths fall back to the synchronous loader.  The caller commits / waits.
+__device__ __forceinline__ void load_tile_async(float* __restrict__ dst, const float* __restrict__ src, int r0,
+                                                int rows, int nrows_total, int w, int wpad, int stride) {
+  if ((w & 3) != 0) {
+    load_tile(dst, src, r0, rows, nrows_total, w, wpad, stride);
+    return;
+  }
+  const int w4 = wpad >> 2;
+  for (int idx = threadIdx.x; idx < rows * w4; idx += NT) {
+    const int r = idx / w4, c = (idx - r * w4) << 2;
+    const bool valid = r0 + r < nrows_total && c < w;
+    cp_async16(dst + r * stride + c, valid ? src + (size_t)(r0 + r) * w + c : src, valid);
+  }
+}
+
 template <int RM, int DVC>
 __global__ void __launch_bounds__(NT) hop_fwd_simt_kernel(SimtPassArgs a, int splits) {
   extern __shared__ __align__(16) float smem[];
@@ -94,6 +130,20 @@ __global__ void __launch_bounds__(NT) hop_fwd_simt_kernel(SimtPassArgs a, int sp
   const int warp = tid >> 5, lane = tid & 31;
   const int row0 = blockIdx.x * BM;
   const int h4 = (a.h + 3) / 4 * 4;
+
+  const int n_tiles = (a.p + BP - 1) / BP;
+  const int tiles_per_split = (n_tiles + splits - 1) / splits;
+  const int t_begin = (int)blockIdx.y * tiles_per_split;
+  const int t_end = min(n_tiles, t_begin + tiles_per_split);
+  float* const K0 = Ks;
+  float* const B0 = Bs;
+  auto issue = [&](int t) {            // tile t -> buffer (t - t_begin) & 1 (or the only buffer)
+    const int buf = L.nbuf == 2 ? ((t - t_begin) & 1) : 0;
+    load_tile_async(K0 + buf * L.k_elems, a.khat, t * BP, BP, a.p, a.h, h4, L.hs);
+    load_tile_async(B0 + buf * L.b_elems, a.bmat, t * BP, BP, a.p, a.dr, L.ds, L.ds);
+    cp_async_commit();
+  };
+  if (L.nbuf == 2 && t_begin < t_end) issue(t_begin);      // overlaps the query prologue below
 
   // ---- prologue: queries -> smem (fused LayerNorm + beta when x_raw given) ----
   if (a.x_raw != nullptr) {
@@ -145,15 +195,17 @@ __global__ void __launch_bounds__(NT) hop_fwd_simt_kernel(SimtPassArgs a, int sp
       for (int e = 0; e < 4; ++e) o[i][c][e] = 0.f;
   }
 
-  const int n_tiles = (a.p + BP - 1) / BP;
-  const int tiles_per_split = (n_tiles + splits - 1) / splits;
-  const int t_begin = (int)blockIdx.y * tiles_per_split;
-  const int t_end = min(n_tiles, t_begin + tiles_per_split);
   for (int t = t_begin; t < t_end; ++t) {
     const int p0 = t * BP;
-    __syncthreads();  // previous tile's consumers are done with Ks / Bs / Ps (and Qs is written)
-    load_tile(Ks, a.khat, p0, BP, a.p, a.h, h4, L.hs);
-    load_tile(Bs, a.bmat, p0, BP, a.p, a.dr, L.ds, L.ds);
+    __syncthreads();  // previous tile's consumers are done with their K / read-out / P tiles (and Qs is written)
+    if (L.nbuf == 2) {
+      if (t + 1 < t_end) { issue(t + 1); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
+      Ks = K0 + ((t - t_begin) & 1) * L.k_elems;
+      Bs = B0 + ((t - t_begin) & 1) * L.b_elems;
+    } else {
+      issue(t);
+      cp_async_wait<0>();
+    }
     __syncthreads();
 
     // ---- phase 1: scores  s[i][b] = <q_row, k_col> ----
@@ -248,6 +300,8 @@ __global__ void __launch_bounds__(NT) hop_fwd_simt_kernel(SimtPassArgs a, int sp
 
   // ---- epilogue ----
   __syncthreads();
+  Ks = K0;
+  Bs = B0;
   float* Os = Bs;  // [BM][ds]: read-out rows for the merge / the fused out-projection
   int rows_lo = 0, rows_n = BM;   // rows of the tile this CTA finishes
   if (splits > 1) {

@@ -123,6 +123,49 @@ def test_2d_input_and_dtype_errors(hf):
         dut(torch.randn(4, 63).cuda())
 
 
+def test_cabi_status_codes(hf):
+    """Error behaviour of the C-ABI (include/hop_sm100.h): status codes, never an exception / exit, message in
+    hop_sm100_last_error()."""
+    import ctypes as C
+    cabi = hf._impl.cabi
+    lib = cabi.load()
+    flags = cabi.F_NORM_STATE | cabi.F_NORM_STORED | cabi.F_NORM_PROJ
+    mk = lambda **kw: cabi.make_desc(**{**dict(flags=flags, path=cabi.PATH_FP32_SIMT, n_rows=64, n_patterns=128,
+                                               d_in=64, d_assoc=64, d_v=64, d_out=1, update_steps=0, beta=0.125), **kw})
+    need = C.c_size_t(0)
+    bad = mk()
+    bad.abi_version = 999
+    assert lib.hop_sm100_workspace_bytes(C.byref(bad), 0, C.byref(need)) == 1          # HOP_ERR_BAD_ARG
+    assert b"abi_version" in lib.hop_sm100_last_error()
+    assert lib.hop_sm100_workspace_bytes(C.byref(mk(n_rows=0)), 0, C.byref(need)) == 2  # HOP_ERR_BAD_SHAPE
+    assert lib.hop_sm100_workspace_bytes(C.byref(mk(d_assoc=32)), 0, C.byref(need)) == 2  # static state: H == Din
+    path = C.c_int32(0)
+    d = mk(path=cabi.PATH_TC_F16, d_in=96, d_assoc=96, d_v=96)
+    assert lib.hop_sm100_select_path(C.byref(d), C.byref(path)) == 7                    # HOP_ERR_UNSUPPORTED
+    # forward: misaligned x -> BAD_ALIGN; T > 0 without workspace -> WORKSPACE
+    x = torch.zeros(64 * 64 + 4, device="cuda")
+    out = torch.zeros(64, 64, device="cuda")
+    k = torch.zeros(128, 64, device="cuda")
+    params, pats = cabi.HopParams(), cabi.HopPatterns(khat=k.data_ptr(), vhat=k.data_ptr())
+    st = lib.hop_sm100_forward(C.byref(mk()), C.byref(params), C.byref(pats), x.data_ptr() + 4, out.data_ptr(), None,
+                               None, None, None, None, None, 0, None)
+    assert st == 3 and b"aligned" in lib.hop_sm100_last_error()
+    st = lib.hop_sm100_forward(C.byref(mk(update_steps=1)), C.byref(params), C.byref(pats), x.data_ptr(),
+                               out.data_ptr(), None, None, None, None, None, None, 0, None)
+    assert st == 6 and b"workspace" in lib.hop_sm100_last_error()
+    with pytest.raises(RuntimeError, match="HOP_ERR_WORKSPACE"):
+        cabi.check(st, "hop_sm100_forward")
+    # peer merge: argument checks come before any launch
+    m = cabi.HopPeerMerge()
+    m.n_rows, m.d_v, m.n_ranks, m.rank, m.row_count, m.epoch = 64, 64, 2, 5, 64, 1
+    assert lib.hop_sm100_peer_merge(C.byref(m), None) == 2
+    m.rank, m.epoch = 0, 0
+    assert lib.hop_sm100_peer_merge(C.byref(m), None) == 1
+    m.epoch = 1
+    assert lib.hop_sm100_peer_merge(C.byref(m), None) == 1 and b"NULL" in lib.hop_sm100_last_error()
+    torch.cuda.synchronize()
+
+
 def test_pattern_cache_invalidation(hf):
     """Prepared K^/V^ are cached across calls and refreshed when a parameter changes in place."""
     kw = dict(input_size=32, quantity=64, **STATIC)
