@@ -86,6 +86,7 @@ struct TcCfg {
 };
 
 size_t ws_for_splits_fwd(int splits, int n, int d);   // defined with the host-side heuristics below
+bool streamk_wanted(int n, int p, int d, int update_steps);
 
 struct TcKernelArgs {
   const float* x_raw; const float* lnq_w; const float* lnq_b; float ln_eps; int has_ln; float beta;
@@ -94,6 +95,9 @@ struct TcKernelArgs {
   int dv_total;                         // row pitch of the read-out (gridDim.z chunks of DV columns)
   float out_scale;                      // applied to the normalised read-out (beta when it is the next state)
   int splits, tiles_per_split;          // pattern tiles (of 128) handled by one CTA
+  // stream-K form (T = 0): the (row group x pattern tile) units are cut into one contiguous share per resident
+  // cluster; a cluster walks its share segment by segment (a segment = one row group, a contiguous tile range)
+  int streamk, sk_base, sk_rem, sk_max_seg;
   float* retrieved; float* qsave; float* lse; int32_t* argmax; float* rowmax; int pattern_offset;
   // partial outputs when splits > 1: (splits, N, D), (splits, N) x3
   float* part_o; float* part_lse; float* part_max; int32_t* part_arg;
@@ -125,6 +129,16 @@ __device__ __forceinline__ float ld_shared_f32(uint32_t addr) {
   float v;
   asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
   return v;
+}
+
+// Next segment of this cluster's unit range [u, end): row group `rg`, first tile `t0`, `nt` tiles.
+__device__ __forceinline__ bool seg_next(int& u, int end, int nt_total, int& rg, int& t0, int& nt) {
+  if (u >= end) return false;
+  rg = u / nt_total;
+  t0 = u - rg * nt_total;
+  nt = min(end - u, nt_total - t0);
+  u += nt;
+  return true;
 }
 
 // kCluster CTAs (consecutive row tiles, same pattern split) form a cluster and share every K^ / V^T stage:
@@ -165,8 +179,17 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
   const int split = blockIdx.y;
   const int zoff = (int)blockIdx.z * DV;       // first read-out column of this CTA
   const int nt_total = (a.p + kTileP - 1) / kTileP;
-  const int t0 = split * a.tiles_per_split;
-  const int nt = min(a.tiles_per_split, nt_total - t0);
+  const int cid = (int)blockIdx.x / kCluster;  // cluster index along x (row group in the plain form)
+  // unit range of this cluster: one segment in the plain form, a contiguous share in the stream-K form
+  int u_start, u_end;
+  if (a.streamk) {
+    u_start = cid * a.sk_base + min(cid, a.sk_rem);
+    u_end = u_start + a.sk_base + (cid < a.sk_rem ? 1 : 0);
+  } else {
+    const int ts = split * a.tiles_per_split;
+    u_start = cid * nt_total + ts;
+    u_end = u_start + min(a.tiles_per_split, nt_total - ts);
+  }
   const int passes = a.update_steps + 1;
 
   if (threadIdx.x == 0) {
@@ -208,6 +231,8 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
           if (crank == 0) ptx::mbar_arrive_expect_tx(full_bar(s), total_bytes);
           return s;
         };
+        int u = u_start, rg, t0, nt;
+        while (seg_next(u, u_end, nt_total, rg, t0, nt))
         for (int pass = 0; pass < passes; ++pass) {
           const CUtensorMap* bm = (pass < a.update_steps) ? &tm_kt : &tm_vt;
           auto load_k = [&](int tile) {
@@ -253,6 +278,8 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         }
         ++it;
       };
+      int u = u_start, rg, t0, nt;
+      while (seg_next(u, u_end, nt_total, rg, t0, nt))
       for (int pass = 0; pass < passes; ++pass) {
         const CUtensorMap* bm = (pass < a.update_steps) ? &tm_kt : &tm_vt;
         auto load_k = [&](int tile) {
@@ -280,9 +307,11 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         constexpr uint32_t idesc_pv = ptx::umma_idesc_f16(2 * kTileM, DV, fmt);
         constexpr int kKPerStage = Cfg::kKChunks >= 2 ? 2 : 1;
         constexpr int kKStages = Cfg::kKChunks / kKPerStage;
-        uint32_t it = 0, g = 0;
+        uint32_t it = 0, g = 0, qphase = 0;
+        int u = u_start, rg, t0, nt;
+        while (seg_next(u, u_end, nt_total, rg, t0, nt))
         for (int pass = 0; pass < passes; ++pass) {
-          ptx::mbar_wait_cluster(q_ready, pass & 1);           // both CTAs' Q tiles are in their shared memory
+          ptx::mbar_wait_cluster(q_ready, (qphase++) & 1);     // both CTAs' Q tiles are in their shared memory
           ptx::tc_fence_after();
           auto issue_qk = [&](uint32_t gg) {
             const int b = gg & 1;
@@ -342,8 +371,11 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         if constexpr (kCluster > 1) ptx::umma_commit_mc(bar, (uint16_t)((1u << kCluster) - 1u));
         else ptx::umma_commit(bar);
       };
+      uint32_t qphase = 0;
+      int u = u_start, rg, t0, nt;
+      while (seg_next(u, u_end, nt_total, rg, t0, nt))
       for (int pass = 0; pass < passes; ++pass) {
-        ptx::mbar_wait(q_ready, pass & 1);
+        ptx::mbar_wait(q_ready, (qphase++) & 1);
         ptx::tc_fence_after();
         auto issue_qk = [&](uint32_t gg) {
           // S buffer b also holds P~ of tile gg-2: its read-out MMA was issued before this point and
@@ -403,9 +435,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
     const int wq = warp & 3;                      // TMEM lane quarter this warp may access
     const int half = (warp - 2) >> 2;             // which 64 score columns / which half of the O columns
     const int row = wq * 32 + lane;               // row of the tile owned by this thread (shared with the partner warp)
-    const long long grow = (long long)blockIdx.x * kTileM + row;
     const uint32_t lane_base = tmem_base + ((uint32_t)(wq * 32) << 16);
-    const bool row_ok = grow < a.n;
     const float qscale = a.beta;                  // natural-units scale of the state pattern
     const uint32_t pair_bar = 1 + wq;             // named barrier of the warp pair (64 threads)
     constexpr int kOGroups = DV / 64;             // 32-column O groups per half
@@ -416,7 +446,19 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
       else ptx::mbar_arrive(bar);
     };
 
+    uint32_t g = 0;
+    int u = u_start, rg, t0, nt, seg_local = 0;
+    while (seg_next(u, u_end, nt_total, rg, t0, nt)) {
+    const long long row_tile = (long long)rg * kCluster + (long long)crank;   // (plain form: == blockIdx.x)
+    const long long grow = row_tile * kTileM + row;
+    const bool row_ok = grow < a.n;
+    // row of this thread inside the partial-result arrays
+    const long long part_row = a.streamk
+        ? ((long long)cid * a.sk_max_seg + seg_local) * (kCluster * kTileM) + (long long)crank * kTileM + row
+        : (long long)split * a.n + grow;
+    ++seg_local;
     // ---- pass-0 Q tile: one warp per row, 4 rows in flight; LN_q + beta, fp32 qsave, 16-bit swizzled smem
+    // (a later segment may overwrite the Q tile: its predecessor ended by waiting for its last MMA)
     {
       constexpr int kVec = (H + 127) / 128;       // float4 per lane
       constexpr int kRowsInFlight = H > 256 ? 2 : 4;
@@ -438,7 +480,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         float4 xv[kRowsInFlight][kVec];
 #pragma unroll
         for (int u = 0; u < kRowsInFlight; ++u) {
-          const long long gr = (long long)blockIdx.x * kTileM + sw * kRowsPerWarp + rr + u;
+          const long long gr = row_tile * kTileM + sw * kRowsPerWarp + rr + u;
 #pragma unroll
           for (int v = 0; v < kVec; ++v) {
             const int e = lane * 4 + v * 128;
@@ -449,7 +491,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
 #pragma unroll
         for (int u = 0; u < kRowsInFlight; ++u) {
           const int r = sw * kRowsPerWarp + rr + u;
-          const long long gr = (long long)blockIdx.x * kTileM + r;
+          const long long gr = row_tile * kTileM + r;
           if (a.x_raw) {
             if (a.has_ln) {
               float s = 0.f;
@@ -482,7 +524,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
           for (int v = 0; v < kVec; ++v) {
             const int e = lane * 4 + v * 128;
             if (e < H) {
-              if (a.qsave && a.update_steps == 0 && gr < a.n && split == 0 && blockIdx.z == 0)
+              if (a.qsave && a.update_steps == 0 && gr < a.n && t0 == 0 && blockIdx.z == 0)
                 *reinterpret_cast<float4*>(a.qsave + gr * H + e) = xv[u][v];
               const uint32_t lo = pack16<kBf16>(xv[u][v].x * kLog2e, xv[u][v].y * kLog2e);
               const uint32_t hi = pack16<kBf16>(xv[u][v].z * kLog2e, xv[u][v].w * kLog2e);
@@ -494,7 +536,6 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
       }
     }
 
-    uint32_t g = 0;
     for (int pass = 0; pass < passes; ++pass) {
       ptx::fence_proxy_async_smem();
       arrive_issuer(q_ready);
@@ -666,7 +707,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         }
         ptx::tc_fence_before();
       } else {
-        float* o_dst = ((a.splits > 1) ? a.part_o + ((long long)split * a.n + grow) * a.dv_total
+        float* o_dst = ((a.splits > 1) ? a.part_o + part_row * a.dv_total
                                        : a.retrieved + grow * a.dv_total) + zoff;
         const float osc = (a.splits > 1) ? inv : inv * a.out_scale;
 #pragma unroll 1
@@ -689,7 +730,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         if (row_ok && half == 0 && blockIdx.z == 0) {
           const float lse = kLn2 * (m_run + ptx::lg2(l_tot));
           if (a.splits > 1) {
-            const long long o = (long long)split * a.n + grow;
+            const long long o = part_row;
             a.part_lse[o] = lse; a.part_max[o] = tmax * kLn2; a.part_arg[o] = targ + a.pattern_offset;
           } else {
             if (a.lse) a.lse[grow] = lse;
@@ -701,6 +742,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
       }
       g += nt;
     }
+    }  // segments of this cluster
   }
 
   __syncthreads();
@@ -741,6 +783,73 @@ __global__ void tc_combine_kernel(int n, int splits, const float* __restrict__ p
     const float w = __expf(part_lse[o] - m) * inv * out_scale;
     const float pm = part_max[o];
     if (pm > best) { best = pm; arg = part_arg[o]; }   // splits are in pattern order: ties keep the lowest index
+#pragma unroll
+    for (int v = 0; v < kVec; ++v) {
+      const int e = lane * 4 + v * 128;
+      if (e < D) {
+        const float4 t = *reinterpret_cast<const float4*>(part_o + o * D + e);
+        acc[v].x += w * t.x; acc[v].y += w * t.y; acc[v].z += w * t.z; acc[v].w += w * t.w;
+      }
+    }
+  }
+#pragma unroll
+  for (int v = 0; v < kVec; ++v) {
+    const int e = lane * 4 + v * 128;
+    if (e < D) *reinterpret_cast<float4*>(retrieved + r * D + e) = acc[v];
+  }
+  if (lane == 0) {
+    if (lse) lse[r] = m + __logf(z);
+    if (rowmax) rowmax[r] = best;
+    if (argmax) argmax[r] = arg;
+  }
+}
+
+// Stream-K form of the merge: the partials of row group rg live in the slots of the clusters whose unit shares
+// intersect [rg * nt_total, (rg + 1) * nt_total) -- one segment each, in pattern order.
+struct StreamKPlan { int nt_total, base, rem, max_seg, cluster; };
+
+__device__ __forceinline__ int sk_cluster_of(const StreamKPlan& s, int u) {
+  const int big = s.rem * (s.base + 1);
+  return u < big ? u / (s.base + 1) : s.rem + (u - big) / s.base;
+}
+
+template <int D>
+__global__ void tc_combine_streamk_kernel(int n, StreamKPlan sk, const float* __restrict__ part_o,
+                                          const float* __restrict__ part_lse, const float* __restrict__ part_max,
+                                          const int32_t* __restrict__ part_arg, const float* __restrict__ bias,
+                                          float out_scale, float* __restrict__ retrieved, float* __restrict__ lse,
+                                          int32_t* __restrict__ argmax, float* __restrict__ rowmax) {
+  const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp_global >= n) return;
+  const long long r = warp_global;
+  const int row_tile = warp_global / kTileM;
+  const int rg = row_tile / sk.cluster;
+  const int in_rg = (row_tile - rg * sk.cluster) * kTileM + (warp_global - row_tile * kTileM);
+  const int c0 = sk_cluster_of(sk, rg * sk.nt_total), c1 = sk_cluster_of(sk, (rg + 1) * sk.nt_total - 1);
+  auto slot_row = [&](int c) -> long long {
+    const int start = c * sk.base + min(c, sk.rem);
+    const int local = rg - start / sk.nt_total;
+    return ((long long)c * sk.max_seg + local) * (sk.cluster * kTileM) + in_rg;
+  };
+  float m = -INFINITY;
+  for (int c = c0; c <= c1; ++c) m = fmaxf(m, part_lse[slot_row(c)]);
+  float z = 0.f;
+  for (int c = c0; c <= c1; ++c) z += __expf(part_lse[slot_row(c)] - m);
+  const float inv = 1.f / z;
+  constexpr int kVec = (D + 127) / 128;
+  float4 acc[kVec];
+#pragma unroll
+  for (int v = 0; v < kVec; ++v) {
+    const int e = lane * 4 + v * 128;
+    acc[v] = (bias && e < D) ? __ldg(reinterpret_cast<const float4*>(bias + e)) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  float best = -INFINITY;
+  int arg = 0;
+  for (int c = c0; c <= c1; ++c) {
+    const long long o = slot_row(c);
+    const float w = __expf(part_lse[o] - m) * inv * out_scale;
+    const float pm = part_max[o];
+    if (pm > best) { best = pm; arg = part_arg[o]; }   // segments are in pattern order: ties keep the lowest index
 #pragma unroll
     for (int v = 0; v < kVec; ++v) {
       const int e = lane * 4 + v * 128;
@@ -819,6 +928,64 @@ int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
   k.splits = (nt_total + k.tiles_per_split - 1) / k.tiles_per_split;   // every split owns >= 1 tile
   k.retrieved = a.retrieved; k.qsave = a.qsave; k.lse = a.lse; k.argmax = a.argmax; k.rowmax = a.rowmax;
   k.pattern_offset = a.pattern_offset;
+  auto* kern = hop_fwd_tc_kernel<H, DV, kBf16, kCluster, kPair>;
+  const int row_tiles = (a.n + kTileM - 1) / kTileM;
+  const int row_groups = (row_tiles + kCluster - 1) / kCluster;
+
+  // ---- stream-K form: one contiguous share of the (row group x tile) units per resident cluster
+  StreamKPlan sk{};
+  bool streamk = kCluster <= 2 && H == DV && a.update_steps == 0 && streamk_wanted(a.n, a.p, a.h, a.update_steps);
+  if (streamk) {
+    HOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    cudaLaunchConfig_t oc{};
+    oc.gridDim = dim3(num_sms() / kCluster * kCluster, 1, 1);
+    oc.blockDim = dim3(kThreads);
+    oc.dynamicSmemBytes = Cfg::kSmemBytes;
+    cudaLaunchAttribute oattr[1];
+    oattr[0].id = cudaLaunchAttributeClusterDimension;
+    oattr[0].val.clusterDim.x = kCluster; oattr[0].val.clusterDim.y = 1; oattr[0].val.clusterDim.z = 1;
+    oc.attrs = oattr; oc.numAttrs = 1;
+    // resident clusters of this kernel on this device: queried once (the query costs tens of microseconds)
+    static int resident_cache[64];
+    int dev = 0;
+    HOP_CUDA(cudaGetDevice(&dev));
+    int resident = (dev >= 0 && dev < 64) ? resident_cache[dev] : 0;
+    if (resident == 0) {
+      if (cudaOccupancyMaxActiveClusters(&resident, kern, &oc) != cudaSuccess) { (void)cudaGetLastError(); resident = 0; }
+      if (dev >= 0 && dev < 64) resident_cache[dev] = resident;
+    }
+    const int cap = num_sms() / kCluster;
+    int n_clusters = resident < cap ? resident : cap;
+    const long long units = (long long)row_groups * nt_total;
+    if (n_clusters > units) n_clusters = (int)units;
+    if (n_clusters < 1) streamk = false;
+    if (streamk) {
+      sk.nt_total = nt_total; sk.cluster = kCluster;
+      sk.base = (int)(units / n_clusters); sk.rem = (int)(units % n_clusters);
+      sk.max_seg = (sk.base + 1 + nt_total - 1) / nt_total + 1;
+      const size_t rows = (size_t)n_clusters * sk.max_seg * kCluster * kTileM;
+      const size_t need = round_up_sz(rows * a.dv * sizeof(float), 256) + 3 * round_up_sz(rows * sizeof(float), 256);
+      if (!a.ws || a.ws_bytes < need) HOP_FAIL(HOP_ERR_WORKSPACE, "stream-K forward needs %zu workspace bytes, %zu given", need, a.ws_bytes);
+      char* w = static_cast<char*>(a.ws);
+      k.part_o = reinterpret_cast<float*>(w); w += round_up_sz(rows * a.dv * sizeof(float), 256);
+      k.part_lse = reinterpret_cast<float*>(w); w += round_up_sz(rows * sizeof(float), 256);
+      k.part_max = reinterpret_cast<float*>(w); w += round_up_sz(rows * sizeof(float), 256);
+      k.part_arg = reinterpret_cast<int32_t*>(w);
+      k.streamk = 1; k.sk_base = sk.base; k.sk_rem = sk.rem; k.sk_max_seg = sk.max_seg;
+      k.splits = 2;                       // (> 1: every segment leaves a partial for the merge)
+      cudaLaunchConfig_t cfg = oc;
+      cfg.gridDim = dim3(n_clusters * kCluster, 1, 1);
+      cfg.stream = st;
+      HOP_CUDA(cudaLaunchKernelEx(&cfg, kern, tk, tkt, tvt, k));
+      HOP_LAUNCH_CHECK("hop_fwd_tc_kernel");
+      const int threads = 256, rows_per_block = threads / 32;
+      tc_combine_streamk_kernel<H><<<(a.n + rows_per_block - 1) / rows_per_block, threads, 0, st>>>(
+          a.n, sk, k.part_o, k.part_lse, k.part_max, k.part_arg, a.bias, a.out_scale, a.retrieved, a.lse, a.argmax,
+          a.rowmax);
+      HOP_LAUNCH_CHECK("tc_combine_streamk_kernel");
+      return HOP_OK;
+    }
+  }
   if (k.splits > 1) {
     const size_t need = ws_for_splits_fwd(splits, a.n, a.dv);
     if (!a.ws || a.ws_bytes < need)
@@ -833,9 +1000,7 @@ int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
   }
 
   // the attribute is per device and cheap to set: do it on every launch so that any current device works
-  auto* kern = hop_fwd_tc_kernel<H, DV, kBf16, kCluster, kPair>;
   HOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
-  const int row_tiles = (a.n + kTileM - 1) / kTileM;
   cudaLaunchConfig_t cfg{};
   // whole clusters (extra CTAs are masked) x pattern splits x read-out column chunks
   cfg.gridDim = dim3((row_tiles + kCluster - 1) / kCluster * kCluster, k.splits, a.dv / DV);
@@ -953,8 +1118,35 @@ static size_t ws_for_splits(int splits, int n, int d) {
   return round_up_sz(rows * d * sizeof(float), 256) + 3 * round_up_sz(rows * sizeof(float), 256);
 }
 
+// Stream-K scheduling of the T = 0 forward (knob: HOP_TC_STREAMK = 0 | 1): used when the plain grid would give
+// every CTA a short pattern range (fixed prologue / epilogue cost per CTA, P = 64k: 64 tiles each) and the share
+// of one cluster stays within the accumulation-chain cap.
+static bool streamk_ok(int n, int p, int d, int update_steps) {
+  if (update_steps != 0 || tc_dv_chunks(d) > 1 || getenv("HOP_TC_SPLITS")) return false;
+  const int cl = tc_choose_cluster(n, d);
+  if (cl > 2) return false;
+  const int sms = num_sms();
+  const long long nt_total = padded_patterns(p) / kTileP;
+  const long long row_groups = ((n + kTileM - 1) / kTileM + cl - 1) / cl;
+  const long long share = row_groups * nt_total / (sms / cl > 0 ? sms / cl : 1);
+  if (const char* e = getenv("HOP_TC_STREAMK")) return atoi(e) != 0;
+  return share >= 200 && share <= 2 * kMaxChainTilesReadout;   // (measured: below ~200 tiles per cluster the plain grid wins)
+}
+namespace { bool streamk_wanted(int n, int p, int d, int update_steps) { return streamk_ok(n, p, d, update_steps); } }
+
+// upper bound of the stream-K partial slots: sum of segments <= row groups + 3 x clusters
+static size_t streamk_ws(int n, int d) {
+  const int cl = tc_choose_cluster(n, d);
+  const size_t row_groups = ((size_t)(n + kTileM - 1) / kTileM + cl - 1) / cl;
+  const size_t rows = (row_groups + 3 * (size_t)(num_sms() / cl)) * cl * kTileM;
+  return round_up_sz(rows * d * sizeof(float), 256) + 3 * round_up_sz(rows * sizeof(float), 256);
+}
+
 size_t tc_forward_workspace(int n, int p, int d, int update_steps) {
-  return ws_for_splits(tc_choose_splits(n, p, d, update_steps), n, d);
+  const size_t plain = ws_for_splits(tc_choose_splits(n, p, d, update_steps), n, d);
+  if (!streamk_ok(n, p, d, update_steps)) return plain;
+  const size_t sk = streamk_ws(n, d);
+  return sk > plain ? sk : plain;
 }
 
 static int launch_tc_one(const TcPassArgs& a, int splits, cudaStream_t st) {

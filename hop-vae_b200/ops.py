@@ -79,7 +79,8 @@ _WS_BYTES = {}
 
 
 def _workspace_bytes(d: "cabi.HopDesc", key, for_backward: int) -> int:
-    k = (key, for_backward, os.environ.get("HOP_TC_SPLITS"))   # (test knob that changes the split workspace)
+    # (the two test / tuning knobs that change the forward workspace are part of the key)
+    k = (key, for_backward, os.environ.get("HOP_TC_SPLITS"), os.environ.get("HOP_TC_STREAMK"))
     v = _WS_BYTES.get(k)
     if v is None:
         import ctypes as C

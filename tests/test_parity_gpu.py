@@ -393,7 +393,7 @@ def _sweep_layer(hf, D, P, T, seed=31):
     return ref, dut.cuda(), g
 
 
-@pytest.mark.parametrize("splits", [0, 3])
+@pytest.mark.parametrize("splits", [0, 3, "streamk"])
 @pytest.mark.parametrize("name", list(TC_CASES))
 def test_forward_parity_tensor_core(hf, name, splits, monkeypatch):
     """tcgen05 fp16-operand / fp32-accumulate path against the fp32 oracle: rel-L2 <= 1e-3 (north-star bar),
@@ -401,7 +401,11 @@ def test_forward_parity_tensor_core(hf, name, splits, monkeypatch):
     D, P, N, T = TC_CASES[name]
     if splits and T > 0 and D <= 256:
         pytest.skip("on-chip retrieve updates never split the pattern axis")
-    if splits:
+    if splits == "streamk":
+        if T > 0 or D > 256:
+            pytest.skip("stream-K scheduling is the T = 0, D <= 256 form")
+        monkeypatch.setenv("HOP_TC_STREAMK", "1")      # force it at sizes where the heuristic keeps the plain grid
+    elif splits:
         monkeypatch.setenv("HOP_TC_SPLITS", str(splits))
     ref, dut, g = _sweep_layer(hf, D, P, T)
     idx = torch.randint(0, P, (N,), generator=g)
