@@ -934,7 +934,8 @@ int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
 
   // ---- stream-K form: one contiguous share of the (row group x tile) units per resident cluster
   StreamKPlan sk{};
-  bool streamk = kCluster <= 2 && H == DV && a.update_steps == 0 && streamk_wanted(a.n, a.p, a.h, a.update_steps);
+  constexpr int kZ = H / DV;           // read-out column chunks: every z-plane walks the same partition
+  bool streamk = kCluster <= 2 && a.update_steps == 0 && streamk_wanted(a.n, a.p, a.h, a.update_steps);
   if (streamk) {
     HOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     cudaLaunchConfig_t oc{};
@@ -955,7 +956,7 @@ int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
       if (dev >= 0 && dev < 64) resident_cache[dev] = resident;
     }
     const int cap = num_sms() / kCluster;
-    int n_clusters = resident < cap ? resident : cap;
+    int n_clusters = (resident < cap ? resident : cap) / kZ;
     const long long units = (long long)row_groups * nt_total;
     if (n_clusters > units) n_clusters = (int)units;
     if (n_clusters < 1) streamk = false;
@@ -974,7 +975,7 @@ int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
       k.streamk = 1; k.sk_base = sk.base; k.sk_rem = sk.rem; k.sk_max_seg = sk.max_seg;
       k.splits = 2;                       // (> 1: every segment leaves a partial for the merge)
       cudaLaunchConfig_t cfg = oc;
-      cfg.gridDim = dim3(n_clusters * kCluster, 1, 1);
+      cfg.gridDim = dim3(n_clusters * kCluster, 1, kZ);
       cfg.stream = st;
       HOP_CUDA(cudaLaunchKernelEx(&cfg, kern, tk, tkt, tvt, k));
       HOP_LAUNCH_CHECK("hop_fwd_tc_kernel");
@@ -1122,14 +1123,19 @@ static size_t ws_for_splits(int splits, int n, int d) {
 // every CTA a short pattern range (fixed prologue / epilogue cost per CTA, P = 64k: 64 tiles each) and the share
 // of one cluster stays within the accumulation-chain cap.
 static bool streamk_ok(int n, int p, int d, int update_steps) {
-  if (update_steps != 0 || tc_dv_chunks(d) > 1 || getenv("HOP_TC_SPLITS")) return false;
+  if (update_steps != 0 || getenv("HOP_TC_SPLITS")) return false;
   const int cl = tc_choose_cluster(n, d);
   if (cl > 2) return false;
   const int sms = num_sms();
   const long long nt_total = padded_patterns(p) / kTileP;
   const long long row_groups = ((n + kTileM - 1) / kTileM + cl - 1) / cl;
-  const long long share = row_groups * nt_total / (sms / cl > 0 ? sms / cl : 1);
+  const int planes = sms / cl / tc_dv_chunks(d);     // clusters per read-out column chunk
+  const long long share = row_groups * nt_total / (planes > 0 ? planes : 1);
   if (const char* e = getenv("HOP_TC_STREAMK")) return atoi(e) != 0;
+  // The clusters of a static partition sit at different pattern positions, so together they stream ALL of K^ / V^
+  // at once: that only works out of the L2 (126 MB).  Measured at D = 512, P = 64k (128 MB of packs): 0.61 -> 0.55.
+  const long long pack_bytes = (long long)padded_patterns(p) * 2 * d * 2;
+  if (pack_bytes > (96ll << 20)) return false;
   return share >= 200 && share <= 2 * kMaxChainTilesReadout;   // (measured: below ~200 tiles per cluster the plain grid wins)
 }
 namespace { bool streamk_wanted(int n, int p, int d, int update_steps) { return streamk_ok(n, p, d, update_steps); } }
