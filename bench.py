@@ -237,6 +237,20 @@ def timed_steps(fn, steps, flush, torch):
     return [a.elapsed_time(b) for a, b in evs]
 
 
+def traffic_of(workload, world, sharded):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture of this workload
+    (profiles/traffic.json names the capture), or None when none was taken (other workloads, sharded runs)."""
+    if sharded:
+        return None
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            e = json.load(f).get(workload)
+        return None if e is None else {"dram_bytes_per_launch": int(e["bytes_per_launch"]), "unit": "B",
+                                       "source": e["source"]}
+    except (OSError, ValueError, KeyError):
+        return None
+
+
 def bind_to_gpu_numa_node(index):
     """Multi-rank runs: pin this process to the CPUs next to its GPU (NVML's ideal affinity) BEFORE the pinned
     host buffers are allocated, so that they land on that NUMA node and 8 ranks do not all pull their host-side
@@ -375,7 +389,7 @@ def gpu_run(args):
                             "HopfieldLayer.forward_host (pinned host in/out, H2D / kernel / D2H pipelined in row chunks)")},
             "gpu_launches": int(launches),
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
-                         "frac": achieved / pk["bf16_tflops"], "traffic": None,
+                         "frac": achieved / pk["bf16_tflops"], "traffic": traffic_of(args.workload, world, sharded),
                          "kernel_ms": k_ms, "algorithmic_flops": fl, "peak_source": pk["source"],
                          "frac_of_sustained": (achieved / pk["bf16_tflops_sustained"]) if pk["bf16_tflops_sustained"] else None},
             "clocks": clocks,
