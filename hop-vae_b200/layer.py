@@ -262,33 +262,42 @@ class HopfieldLayer(nn.Module):
             out, argmax = HopfieldAssociation.apply(spec, x, *[None if pack[k] is None else pack[k].contiguous()
                                                                for k in _PARAM_ORDER])
         else:
-            pkey = (spec, x.shape[0], self.quantity)
-            path = self._paths.get(pkey)
-            if path is None:
-                path = self._paths[pkey] = resolve_path(spec, x.shape[0], self.quantity)
-            pats = self._prepared(pack, spec, path)
-            q = [None if pack[k] is None else pack[k].detach().contiguous() for k in _QUERY_SIDE]
-            if _eager():
-                res = retrieve(x.detach(), *pats, *q, spec.flags, path, spec.d_in, spec.d_out, spec.update_steps,
-                               spec.beta, spec.ln_eps, 0, False, False)
-            else:
-                res = retrieve_op(x.detach(), *pats, *q, spec.flags, path, spec.d_in, spec.d_out, spec.update_steps,
-                                  spec.beta, spec.ln_eps, 0, False)
-            out, argmax = res[0], res[4]
-            self.__dict__["last_lse"] = res[3]     # (plain attribute: nn.Module.__setattr__ costs ~5 us per set)
+            out, argmax, lse = self._infer(x, spec, pack)
+            self.__dict__["last_lse"] = lse        # (plain attribute: nn.Module.__setattr__ costs ~5 us per set)
         self.__dict__["last_argmax"] = argmax
         return out.reshape(*lead, out.shape[-1])
 
+    def _infer(self, x: Tensor, spec: LayerSpec, pack, into=None) -> Tuple[Tensor, Tensor, Tensor]:
+        """No-grad retrieval of x (N, Din) -> (out, nearest-pattern index, lse); `into` = caller-owned result
+        buffers (out (N,W), stats (2,N), argmax (N) i32)."""
+        pkey = (spec, x.shape[0], self.quantity)
+        path = self._paths.get(pkey)
+        if path is None:
+            path = self._paths[pkey] = resolve_path(spec, x.shape[0], self.quantity)
+        pats = self._prepared(pack, spec, path)
+        q = [None if pack[k] is None else pack[k].detach().contiguous() for k in _QUERY_SIDE]
+        if _eager():
+            res = retrieve(x.detach(), *pats, *q, spec.flags, path, spec.d_in, spec.d_out, spec.update_steps,
+                           spec.beta, spec.ln_eps, 0, False, False, into)
+        else:
+            res = retrieve_op(x.detach(), *pats, *q, spec.flags, path, spec.d_in, spec.d_out, spec.update_steps,
+                              spec.beta, spec.ln_eps, 0, False)
+        return res[0], res[4], res[3]
+
     # ------------------------------------------------------- host-buffer entry point
-    def forward_host(self, x_host: Tensor, out_host: Optional[Tensor] = None, chunks=None) -> Tensor:
+    def forward_host(self, x_host: Tensor, out_host: Optional[Tensor] = None, chunks=None,
+                     graph: Optional[bool] = None) -> Tensor:
         """Host-buffer call: `x_host` (N, input_size) pinned fp32 -> `out_host` (N, output_size) pinned fp32.
 
         The rows are cut into `chunks` pieces (an int: equal pieces; a sequence of weights: proportional pieces;
-        multiples of 128 rows); the host->device copy of piece i+1, the
-        fused retrieval of piece i and the device->host copy of piece i-1 run on three streams, so the PCIe
-        transfers hide behind the kernels.  Returns once all work is *enqueued*; the current stream waits for
-        the last device->host copy, so a synchronize / event on the current stream covers everything.
-        Inference only (no autograd)."""
+        multiples of 128 rows); the host->device copy of piece i+1, the fused retrieval of piece i and the
+        device->host copy of piece i-1 run on three streams, so the PCIe transfers hide behind the kernels.
+        The whole pipeline (copies, kernels, cross-stream dependencies) is captured ONCE per (buffers, N, schedule,
+        parameter version) into a CUDA graph and replayed afterwards: one host call per step instead of ~40, so a
+        busy host cannot starve the GPU (`graph=False`, or HOP_SM100_HOST_GRAPH=0, keeps the eager enqueue).
+        Returns once all work is *enqueued*; the current stream waits for the last device->host copy, so a
+        synchronize / event on the current stream covers everything.  Inference only (no autograd).
+        `last_argmax` / `last_lse` are views of per-layer staging buffers, valid until the next call."""
         dev = self.lookup_weights.device
         if dev.type != "cuda":
             raise RuntimeError("hflayers.HopfieldLayer (hop_sm100): the layer is on the CPU; no CPU fallback")
@@ -297,9 +306,12 @@ class HopfieldLayer(nn.Module):
         if not x_host.is_pinned():
             raise ValueError("forward_host needs pinned host memory (asynchronous copies)")
         n = x_host.shape[0]
-        if out_host is None:
-            out_host = torch.empty((n, self.output_size if (self._flags & cabi.F_OUT_PROJ) else self.pattern_size),
-                                   dtype=torch.float32).pin_memory()
+        width = self.output_size if (self._flags & cabi.F_OUT_PROJ) else self.pattern_size
+        own_out = out_host is None
+        if own_out:
+            out_host = torch.empty((n, width), dtype=torch.float32).pin_memory()
+        elif out_host.shape != (n, width) or out_host.dtype != torch.float32 or not out_host.is_pinned():
+            raise ValueError("forward_host: out_host must be a pinned float32 (N, output width) tensor")
         if chunks is None:
             # ramp: small first / last pieces keep the un-overlapped lead-in copy and lead-out copy short
             chunks = (1, 3, 3, 1) if n >= 8192 else (2 if n >= 2048 else 1)
@@ -314,35 +326,64 @@ class HopfieldLayer(nn.Module):
                 cuts.append(min(n, int(round(n * acc / total / 128.0)) * 128))
             cuts[-1] = n
             bounds = [(a, b) for a, b in zip(cuts[:-1], cuts[1:]) if b > a]
-        if getattr(self, "_host_streams", None) is None or self._host_streams[0].device != dev:
-            self._host_streams = tuple(torch.cuda.Stream(device=dev) for _ in range(3))
-        if getattr(self, "_x_stage", None) is None or self._x_stage.shape[0] < n or self._x_stage.device != dev:
-            self._x_stage = torch.empty((n, self.input_size), device=dev, dtype=torch.float32)
-        h2d, comp, d2h = self._host_streams
-        cur = torch.cuda.current_stream(dev)
-        for st in self._host_streams:
-            st.wait_stream(cur)
-        args = []
+        st = self.__dict__.get("_host_state")
+        if st is None or st["dev"] != dev or st["rows"] < n or st["width"] != width:
+            st = dict(dev=dev, rows=n, width=width, streams=tuple(torch.cuda.Stream(device=dev) for _ in range(3)),
+                      x=torch.empty((n, self.input_size), device=dev, dtype=torch.float32),
+                      y=torch.empty((n, width), device=dev, dtype=torch.float32),
+                      stats=torch.empty((2, n), device=dev, dtype=torch.float32),
+                      arg=torch.empty((n,), device=dev, dtype=torch.int32), graphs={})
+            self.__dict__["_host_state"] = st
+        # (a fresh result buffer per call would mean a fresh capture per call: graphs need caller-owned buffers)
+        use_graph = graph if graph is not None else (not own_out and os.environ.get("HOP_SM100_HOST_GRAPH", "1") != "0")
         with torch.no_grad():
-            for a, b in bounds:
-                xs = self._x_stage[a:b]
-                with torch.cuda.stream(h2d):
-                    xs.copy_(x_host[a:b], non_blocking=True)
-                    e1 = h2d.record_event()
-                with torch.cuda.stream(comp):
-                    comp.wait_event(e1)
-                    y = self.forward(xs)
-                    args.append(self.last_argmax)
-                    e2 = comp.record_event()
-                with torch.cuda.stream(d2h):
-                    d2h.wait_event(e2)
-                    out_host[a:b].copy_(y, non_blocking=True)
-                    y.record_stream(d2h)
+            spec, pack = self.spec(), self.param_pack()
+            if use_graph and _eager():
+                # the prepared pattern operands are baked into the captured launches: their cache key is part of ours
+                path = self._paths.get((spec, bounds[0][1] - bounds[0][0], self.quantity))
+                self._prepared(pack, spec, path if path is not None else
+                               resolve_path(spec, bounds[0][1] - bounds[0][0], self.quantity))
+                key = (x_host.data_ptr(), out_host.data_ptr(), n, tuple(bounds), self._cache_key, self.kernel_path)
+                g = st["graphs"].get(key)
+                if g is None:
+                    self._host_pipeline(x_host, out_host, bounds, st, spec, pack)      # warm-up: lazy caches, allocator
+                    torch.cuda.current_stream(dev).synchronize()
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g):
+                        self._host_pipeline(x_host, out_host, bounds, st, spec, pack)
+                    if len(st["graphs"]) >= 4:
+                        st["graphs"].pop(next(iter(st["graphs"])))
+                    st["graphs"][key] = g
+                g.replay()
+            else:
+                self._host_pipeline(x_host, out_host, bounds, st, spec, pack)
+        self.__dict__["last_argmax"] = st["arg"][:n]
+        self.__dict__["last_lse"] = st["stats"][0, :n]
+        return out_host
+
+    def _host_pipeline(self, x_host: Tensor, out_host: Tensor, bounds, st, spec: LayerSpec, pack) -> None:
+        """Enqueue H2D / retrieval / D2H of every piece on the three side streams (fork from and join to the current
+        stream, so the same code runs eagerly and under CUDA-graph capture); results go through staging buffers."""
+        dev = st["dev"]
+        h2d, comp, d2h = st["streams"]
+        cur = torch.cuda.current_stream(dev)
+        for s_ in st["streams"]:
+            s_.wait_stream(cur)
+        for a, b in bounds:
+            xs = st["x"][a:b]
+            with torch.cuda.stream(h2d):
+                xs.copy_(x_host[a:b], non_blocking=True)
+                e1 = h2d.record_event()
             with torch.cuda.stream(comp):
-                self.last_argmax = torch.cat(args) if len(args) > 1 else args[0]
+                comp.wait_event(e1)
+                self._infer(xs, spec, pack, into=(st["y"][a:b], st["stats"][:, a:b], st["arg"][a:b]))
+                e2 = comp.record_event()
+            with torch.cuda.stream(d2h):
+                d2h.wait_event(e2)
+                out_host[a:b].copy_(st["y"][a:b], non_blocking=True)
+        cur.wait_stream(h2d)
         cur.wait_stream(comp)
         cur.wait_stream(d2h)
-        return out_host
 
     def extra_repr(self) -> str:
         return (f"input_size={self.input_size}, hidden_size={self.hidden_size}, pattern_size={self.pattern_size}, "

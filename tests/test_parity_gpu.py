@@ -475,11 +475,25 @@ def test_forward_host_pipelined_matches_forward(hf):
     with torch.no_grad():
         want = dut(x.cuda()).cpu()
         arg = dut.last_argmax.cpu()
-        for chunks in (1, 3, 8):
+        for chunks in (1, 3, 8, (1, 3, 3, 1), (5, 1), None):     # equal pieces, weighted pieces, default schedule
             got = dut.forward_host(xh, chunks=chunks)
             torch.cuda.synchronize()
             assert torch.equal(got, want), chunks
             assert torch.equal(dut.last_argmax.cpu(), arg)
+        # caller-owned result buffer: the pipeline is captured into a CUDA graph once and replayed
+        out = torch.empty_like(want).pin_memory()
+        for rep in range(3):
+            out.zero_()
+            xh.copy_(x if rep != 1 else x.flip(0))          # replays read the buffer's CURRENT contents
+            r = dut.forward_host(xh, out, chunks=(1, 3, 3, 1))
+            torch.cuda.synchronize()
+            assert r is out
+            assert torch.equal(out, want if rep != 1 else want.flip(0)), rep
+            assert torch.equal(dut.last_argmax.cpu(), arg if rep != 1 else arg.flip(0))
+        assert len(dut._host_state["graphs"]) == 1
+        eager = dut.forward_host(xh, torch.empty_like(want).pin_memory(), chunks=(1, 3, 3, 1), graph=False)
+        torch.cuda.synchronize()
+        assert torch.equal(eager, want)
     with pytest.raises(ValueError, match="pinned"):
         dut.forward_host(x)
 
