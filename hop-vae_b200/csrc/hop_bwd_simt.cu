@@ -15,6 +15,7 @@
 //   pattern side, both paths summing into d_lookup.
 #include <cooperative_groups.h>
 
+#include <cstdlib>
 #include "hop_common.cuh"
 
 namespace cg = cooperative_groups;
@@ -214,6 +215,18 @@ __global__ void __launch_bounds__(NT) bwd_core_q_kernel(CoreArgs a, int splits) 
   }
 }
 
+// v[0..3] += into row[col..col+3]: one 16-byte RED (sm_90+ float4 atomicAdd) when the four columns exist and the
+// address is 16-byte aligned (width % 4 == 0), scalar REDs at a ragged edge.
+__device__ __forceinline__ void red_add4(float* row, int col, int width, const float (&v)[4]) {
+  if (col + 3 < width && (width & 3) == 0) {
+    atomicAdd(reinterpret_cast<float4*>(row + col), make_float4(v[0], v[1], v[2], v[3]));
+  } else {
+#pragma unroll
+    for (int e = 0; e < 4; ++e)
+      if (col + e < width) atomicAdd(row + col + e, v[e]);
+  }
+}
+
 // ----------------------------------------------------------------- core_kv
 template <int HC, int DVC, int RQ>
 __global__ void __launch_bounds__(NT) bwd_core_kv_kernel(CoreArgs a) {
@@ -309,19 +322,9 @@ __global__ void __launch_bounds__(NT) bwd_core_kv_kernel(CoreArgs a) {
     const int gp = p0 + ty * 4 + i;
     if (gp >= a.p) continue;
 #pragma unroll
-    for (int c = 0; c < HC; ++c)
+    for (int c = 0; c < HC; ++c) red_add4(a.dkhat + (size_t)gp * a.h, 4 * tx + 64 * c, a.h, dk[i][c]);
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const int col = 4 * tx + 64 * c + e;
-        if (col < a.h) atomicAdd(a.dkhat + (size_t)gp * a.h + col, dk[i][c][e]);
-      }
-#pragma unroll
-    for (int c = 0; c < DVC; ++c)
-#pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const int col = 4 * tx + 64 * c + e;
-        if (col < a.dv) atomicAdd(a.dvhat + (size_t)gp * a.dv + col, dvv[i][c][e]);
-      }
+    for (int c = 0; c < DVC; ++c) red_add4(a.dvhat + (size_t)gp * a.dv, 4 * tx + 64 * c, a.dv, dvv[i][c]);
   }
 }
 
@@ -583,7 +586,8 @@ int launch_core_kv(CoreArgs a, cudaStream_t st) {
   if (smem > 48 * 1024) HOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int sms = num_sms();
   const int ptiles = (a.p + BP - 1) / BP;
-  int splits = (3 * sms + ptiles - 1) / ptiles;
+  static const int waves = [] { const char* e = getenv("HOP_BWD_KV_WAVES"); return e ? atoi(e) : 3; }();
+  int splits = ((waves > 0 ? waves : 3) * sms + ptiles - 1) / ptiles;
   const int max_splits = (a.n + BQ - 1) / BQ;
   if (splits > max_splits) splits = max_splits;
   if (splits < 1) splits = 1;

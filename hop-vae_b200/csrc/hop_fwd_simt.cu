@@ -143,33 +143,38 @@ __global__ void __launch_bounds__(NT) hop_fwd_simt_kernel(SimtPassArgs a, int sp
     load_tile_async(B0 + buf * L.b_elems, a.bmat, t * BP, BP, a.p, a.dr, L.ds, L.ds);
     cp_async_commit();
   };
-  if (L.nbuf == 2 && t_begin < t_end) issue(t_begin);      // overlaps the query prologue below
-
   // ---- prologue: queries -> smem (fused LayerNorm + beta when x_raw given) ----
+  // The raw rows are staged with one batch of copies (all in flight at once) and normalised in place: a warp that
+  // reads its rows from global memory one after another exposes the full memory latency once per row (ncu: 29 %
+  // of this kernel's stall samples at N = 2,048).
   if (a.x_raw != nullptr) {
+    load_tile_async(Qs, a.x_raw, row0, BM, a.n, a.h, h4, L.hs);
+    cp_async_commit();
+  }
+  const bool prefetch0 = L.nbuf == 2 && t_begin < t_end;
+  if (prefetch0) issue(t_begin);                            // first pattern tile: overlaps the LayerNorm below
+  if (a.x_raw != nullptr) {
+    if (prefetch0) cp_async_wait<1>(); else cp_async_wait<0>();
+    __syncthreads();
     for (int r = warp; r < BM; r += NT / 32) {
       const int gr = row0 + r;
+      float* qr = Qs + r * L.hs;
       if (gr < a.n) {
-        const float* xr = a.x_raw + (size_t)gr * a.h;
         float mean = 0.f, rstd = 1.f;
-        if (a.has_ln) warp_row_stats(xr, a.h, a.ln_eps, mean, rstd);
-        for (int i = lane; i < L.hs; i += 32) {
-          float v = 0.f;
-          if (i < a.h) {
-            v = xr[i];
-            if (a.has_ln) {
-              v = (v - mean) * rstd;
-              if (a.lnq_w) v *= __ldg(a.lnq_w + i);
-              if (a.lnq_b) v += __ldg(a.lnq_b + i);
-            }
-            v *= a.beta;
-            if (a.qsave && blockIdx.y == 0) a.qsave[(size_t)gr * a.h + i] = v;
+        if (a.has_ln) warp_row_stats(qr, a.h, a.ln_eps, mean, rstd);
+        for (int i = lane; i < a.h; i += 32) {
+          float v = qr[i];
+          if (a.has_ln) {
+            v = (v - mean) * rstd;
+            if (a.lnq_w) v *= __ldg(a.lnq_w + i);
+            if (a.lnq_b) v += __ldg(a.lnq_b + i);
           }
-          Qs[r * L.hs + i] = v;
+          v *= a.beta;
+          if (a.qsave && blockIdx.y == 0) a.qsave[(size_t)gr * a.h + i] = v;
+          qr[i] = v;
         }
-      } else {
-        for (int i = lane; i < L.hs; i += 32) Qs[r * L.hs + i] = 0.f;
       }
+      for (int i = h4 + lane; i < L.hs; i += 32) qr[i] = 0.f;    // stride padding
     }
   } else {
     load_tile(Qs, a.qs, row0, BM, a.n, a.h, h4, L.hs);
@@ -302,6 +307,14 @@ __global__ void __launch_bounds__(NT) hop_fwd_simt_kernel(SimtPassArgs a, int sp
   __syncthreads();
   Ks = K0;
   Bs = B0;
+  // out-projection operand: when one K-tile row holds a whole Wo row, the first 64 rows of Wo start loading now
+  // (the K tiles are free) and arrive under the merge below
+  const int kc = h4 < L.ds ? h4 : L.ds;          // contraction chunk that fits a K-tile row
+  const bool wo_async = a.wo != nullptr && kc == a.dr && (a.dr & 3) == 0;
+  if (wo_async) {
+    load_tile_async(Ks, a.wo, 0, BP, a.dout, a.dr, kc, L.hs);
+    cp_async_commit();
+  }
   float* Os = Bs;  // [BM][ds]: read-out rows for the merge / the fused out-projection
   int rows_lo = 0, rows_n = BM;   // rows of the tile this CTA finishes
   if (splits > 1) {
@@ -405,7 +418,6 @@ __global__ void __launch_bounds__(NT) hop_fwd_simt_kernel(SimtPassArgs a, int sp
   if (a.wo != nullptr) {
     // fused out-projection of the rows this CTA finished (Os row r <-> tile row rows_lo + r):
     // out = Os . Wo^T is the score contraction again, with 64-row chunks of Wo staged in the K tile
-    const int kc = h4 < L.ds ? h4 : L.ds;          // contraction chunk that fits a K-tile row
     for (int oc0 = 0; oc0 < a.dout; oc0 += BP) {
       float acc[RM][4];
 #pragma unroll
@@ -414,11 +426,19 @@ __global__ void __launch_bounds__(NT) hop_fwd_simt_kernel(SimtPassArgs a, int sp
         for (int b = 0; b < 4; ++b) acc[i][b] = 0.f;
       for (int j0 = 0; j0 < a.dr; j0 += kc) {
         __syncthreads();
-        for (int idx = tid; idx < BP * kc; idx += NT) {
-          const int oc = idx / kc, j = idx - oc * kc;
-          float v = 0.f;
-          if (oc0 + oc < a.dout && j0 + j < a.dr) v = __ldg(a.wo + (size_t)(oc0 + oc) * a.dr + j0 + j);
-          Ks[oc * L.hs + j] = v;
+        if (wo_async) {
+          if (oc0 > 0) {
+            load_tile_async(Ks, a.wo, oc0, BP, a.dout, a.dr, kc, L.hs);
+            cp_async_commit();
+          }
+          cp_async_wait<0>();
+        } else {
+          for (int idx = tid; idx < BP * kc; idx += NT) {
+            const int oc = idx / kc, j = idx - oc * kc;
+            float v = 0.f;
+            if (oc0 + oc < a.dout && j0 + j < a.dr) v = __ldg(a.wo + (size_t)(oc0 + oc) * a.dr + j0 + j);
+            Ks[oc * L.hs + j] = v;
+          }
         }
         __syncthreads();
         if (ty * RM < rows_n) {
@@ -461,10 +481,15 @@ __global__ void __launch_bounds__(NT) hop_fwd_simt_kernel(SimtPassArgs a, int sp
 // scans patterns q, q+4, ... -- and combine with quad shuffles.  Two passes over the scores (max, then exp /
 // sum / read-out) instead of an online rescale: with H <= 4 recomputing a score costs less than the dependent
 // rescale chain.  LN_q + beta in the prologue, out-projection in the epilogue, like the tiled kernel.
+//
+// LPR lanes share a query row (4 | 8 | 16 | 32): at N = 2,048 a quad per row gives 64 CTAs of four warps, each
+// lane walking 128 patterns twice -- one warp per scheduler on 64 of 148 SMs, pure latency.  More lanes per row
+// shorten the serial scan and multiply the CTA count; the launcher picks the smallest LPR that fills the GPU.
 constexpr int kTinyThreads = 128;
-constexpr int kTinyRows = kTinyThreads / 4;
 
+template <int LPR>
 __global__ void __launch_bounds__(kTinyThreads) hop_fwd_tiny_kernel(SimtPassArgs a) {
+  constexpr int kTinyRows = kTinyThreads / LPR;
   extern __shared__ __align__(16) float smem[];
   float4* Ks = reinterpret_cast<float4*>(smem);                 // [P]
   float4* Bs = Ks + a.p;                                        // [P]
@@ -488,10 +513,10 @@ __global__ void __launch_bounds__(kTinyThreads) hop_fwd_tiny_kernel(SimtPassArgs
   }
   __syncthreads();
 
-  const int quad = tid & 3;
-  const long long gr = (long long)blockIdx.x * kTinyRows + (tid >> 2);
+  const int quad = tid & (LPR - 1);           // lane of the row group
+  const long long gr = (long long)blockIdx.x * kTinyRows + tid / LPR;
   const bool ok = gr < a.n;
-  // ---- query row: LN_q + beta (every lane of the quad redundantly; H <= 4)
+  // ---- query row: LN_q + beta (every lane of the row group redundantly; H <= 4)
   float q[4] = {0.f, 0.f, 0.f, 0.f};
   if (ok) {
     const float* src = (a.x_raw ? a.x_raw : a.qs) + gr * a.h;
@@ -518,20 +543,20 @@ __global__ void __launch_bounds__(kTinyThreads) hop_fwd_tiny_kernel(SimtPassArgs
   // ---- pass 1: row maximum and nearest pattern (strict >: the lowest index wins ties inside a lane)
   float m = -INFINITY;
   int arg = 0x7fffffff;
-  for (int j = quad; j < a.p; j += 4) {
+  for (int j = quad; j < a.p; j += LPR) {
     const float4 k = Ks[j];
     const float s = fmaf(q[3], k.w, fmaf(q[2], k.z, fmaf(q[1], k.y, q[0] * k.x)));
     if (s > m) { m = s; arg = j; }
   }
 #pragma unroll
-  for (int off = 1; off <= 2; off <<= 1) {
+  for (int off = 1; off < LPR; off <<= 1) {
     const float om = __shfl_xor_sync(0xffffffffu, m, off);
     const int oa = __shfl_xor_sync(0xffffffffu, arg, off);
     if (om > m || (om == m && oa < arg)) { m = om; arg = oa; }
   }
   // ---- pass 2: exp, sum, read-out
   float l = 0.f, acc[4] = {0.f, 0.f, 0.f, 0.f};
-  for (int j = quad; j < a.p; j += 4) {
+  for (int j = quad; j < a.p; j += LPR) {
     const float4 k = Ks[j];
     const float s = fmaf(q[3], k.w, fmaf(q[2], k.z, fmaf(q[1], k.y, q[0] * k.x)));
     const float pexp = __expf(s - m);
@@ -541,7 +566,7 @@ __global__ void __launch_bounds__(kTinyThreads) hop_fwd_tiny_kernel(SimtPassArgs
     acc[2] = fmaf(pexp, b.z, acc[2]); acc[3] = fmaf(pexp, b.w, acc[3]);
   }
 #pragma unroll
-  for (int off = 1; off <= 2; off <<= 1) {
+  for (int off = 1; off < LPR; off <<= 1) {
     l += __shfl_xor_sync(0xffffffffu, l, off);
 #pragma unroll
     for (int c = 0; c < 4; ++c) acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], off);
@@ -559,22 +584,39 @@ __global__ void __launch_bounds__(kTinyThreads) hop_fwd_tiny_kernel(SimtPassArgs
     if (a.rowmax) a.rowmax[gr] = m;
   }
   if (a.wo) {
-    // out-projection: lane `quad` writes output columns quad, quad + 4, ... (a quad covers 16 consecutive bytes)
+    // out-projection: lane `quad` writes output columns quad, quad + LPR, ... (a row group covers 4 LPR consecutive bytes)
     float* dst = a.out + gr * a.dout;
-    for (int oc = quad; oc < a.dout; oc += 4) {
+    for (int oc = quad; oc < a.dout; oc += LPR) {
       const float4 w = Ws[oc];
       dst[oc] = fmaf(r[3], w.w, fmaf(r[2], w.z, fmaf(r[1], w.y, fmaf(r[0], w.x, bs[oc]))));
     }
   }
 }
 
-int launch_tiny(const SimtPassArgs& a, cudaStream_t st) {
-  const size_t smem = sizeof(float4) * (2 * (size_t)a.p + (a.wo ? a.dout : 0)) + sizeof(float) * (a.wo ? a.dout : 0);
+template <int LPR>
+int launch_tiny_lpr(const SimtPassArgs& a, size_t smem, cudaStream_t st) {
+  constexpr int rows = kTinyThreads / LPR;
   if (smem > 48 * 1024)
-    HOP_CUDA(cudaFuncSetAttribute(hop_fwd_tiny_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  hop_fwd_tiny_kernel<<<(a.n + kTinyRows - 1) / kTinyRows, kTinyThreads, smem, st>>>(a);
+    HOP_CUDA(cudaFuncSetAttribute(hop_fwd_tiny_kernel<LPR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  hop_fwd_tiny_kernel<LPR><<<(a.n + rows - 1) / rows, kTinyThreads, smem, st>>>(a);
   HOP_LAUNCH_CHECK("hop_fwd_tiny_kernel");
   return HOP_OK;
+}
+
+int launch_tiny(const SimtPassArgs& a, cudaStream_t st) {
+  const size_t smem = sizeof(float4) * (2 * (size_t)a.p + (a.wo ? a.dout : 0)) + sizeof(float) * (a.wo ? a.dout : 0);
+  // smallest row group that still gives every SM two CTAs (each CTA stages all patterns: keep the groups small
+  // when there are rows enough).  Measured (B200, P = 512): N = 64: 16.5 / 10.4 / 8.3 us with 4 / 8 / 32 lanes per
+  // row; N = 65,536: 81 / 66 / 87 / 135 us with 4 / 8 / 16 / 32.
+  int lpr = 8;
+  while (lpr < 32 && (long long)a.n * lpr < 2LL * num_sms() * kTinyThreads) lpr <<= 1;
+  if (const char* e = getenv("HOP_TINY_LPR")) { const int v = atoi(e); if (v == 4 || v == 8 || v == 16 || v == 32) lpr = v; }
+  switch (lpr) {
+    case 4: return launch_tiny_lpr<4>(a, smem, st);
+    case 8: return launch_tiny_lpr<8>(a, smem, st);
+    case 16: return launch_tiny_lpr<16>(a, smem, st);
+    default: return launch_tiny_lpr<32>(a, smem, st);
+  }
 }
 
 template <int RM, int DVC>

@@ -11,9 +11,12 @@ These sizes are launch-latency bound (<= 2.5 GFLOP): the numbers reported are mi
 
     python scripts/bench_model_configs.py            # on the GPU box
 """
+import copy
 import json
 import os
+import statistics
 import sys
+import time
 
 import torch
 import torch.nn.functional as F
@@ -42,6 +45,21 @@ def timed(fn, iters=50, warm=10):
     e1.record()
     torch.cuda.synchronize()
     return e0.elapsed_time(e1) / iters * 1e3   # microseconds
+
+
+def timed_cpu(fn, iters=10, warm=3):
+    """Median wall time (us) of a CPU callable: the reference's CPU path timed beside the GPU numbers."""
+    for _ in range(warm):
+        fn()
+    ts = []
+    for _ in range(iters):
+        t0 = time.perf_counter()
+        fn()
+        ts.append(time.perf_counter() - t0)
+    return statistics.median(ts) * 1e6
+
+
+torch.set_num_threads(os.cpu_count() or 1)
 
 
 def graphed(fn):
@@ -93,6 +111,14 @@ for name, cfg in (("mnist28", H.MNIST_28), ("ffhq32", H.FFHQ_32), ("ffhq64", H.F
     for layer in (ref.hopfield, ref.embedding_to_index, ref.index_to_embedding):
         layer.faithful = True
     res["us_fwd_eager_upstream_shape"] = timed(fwd(ref))
+    ref_cpu, z_cpu = copy.deepcopy(ref).cpu(), z.cpu()
+
+    def fwd_cpu():
+        with torch.no_grad():
+            ref_cpu.bottleneck(z_cpu)
+    res["us_fwd_cpu_upstream_shape"] = timed_cpu(fwd_cpu)
+    res["cpu_threads"] = torch.get_num_threads()
+    del ref_cpu
 
     def fb(m):
         zz = z.clone().requires_grad_(True)
@@ -106,6 +132,12 @@ for name, cfg in (("mnist28", H.MNIST_28), ("ffhq32", H.FFHQ_32), ("ffhq64", H.F
     dut.train(); ref.train()
     res["us_fwdbwd_ours"] = timed(fb(dut), iters=30)
     res["us_fwdbwd_eager_upstream_shape"] = timed(fb(ref), iters=30)
+    # the same training step with the host out of the way (whole fwd+bwd captured into a CUDA graph, both arms)
+    for key, m in (("us_fwdbwd_ours_graph", dut), ("us_fwdbwd_eager_upstream_shape_graph", ref)):
+        try:
+            res[key] = timed(graphed(fb(m)), iters=30)
+        except Exception as e:  # noqa: BLE001
+            res[key] = f"capture failed: {type(e).__name__}: {str(e)[:120]}"
     res["latents_per_s_fwd_ours"] = n / (res["us_fwd_ours"] * 1e-6)
     res["latents_per_s_fwd_eager"] = n / (res["us_fwd_eager"] * 1e-6)
     rows.append(res)
@@ -150,6 +182,13 @@ for S in (1, 1024):
     res["us_lookup_plus_decoder_ours"] = timed(whole(dut))
     res["us_lookup_plus_decoder_eager_upstream_shape"] = timed(whole(ref))
     res["us_index_to_embedding_ours_graph"] = timed(graphed(lookup(dut)))
+    ref_cpu, idx_cpu = copy.deepcopy(ref).cpu(), idx.cpu()
+
+    def whole_cpu():
+        with torch.no_grad():
+            ref_cpu.sample_from_indices(idx_cpu)
+    res["us_lookup_plus_decoder_cpu_upstream_shape"] = timed_cpu(whole_cpu, iters=5 if S > 1 else 10, warm=1 if S > 1 else 3)
+    res["cpu_threads"] = torch.get_num_threads()
     res["latents_per_s_ours"] = 64 * S / (res["us_index_to_embedding_ours"] * 1e-6)
     print(json.dumps(res), flush=True)
 

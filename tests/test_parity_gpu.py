@@ -324,6 +324,46 @@ def test_training_step_matches_oracle(ckpt_models):
         ref.eval(); dut.eval()
 
 
+def test_training_step_under_cuda_graph(hf):
+    """forward + backward of a layer captured into a CUDA graph (no host sync, no allocation outside torch's
+    pool, every launch on the capturing stream): replays on new inputs give the gradients of an eager step."""
+    kw = dict(input_size=64, output_size=3, quantity=512, **STATIC)
+    ref, dut = make_pair(hf, seed=77, **kw)
+    g = torch.Generator().manual_seed(78)
+    xs = [torch.randn(4, 50, 64, generator=g) for _ in range(3)]
+    w = torch.randn(4, 50, 3, generator=g).cuda()
+    x_static = xs[0].cuda().requires_grad_(True)
+
+    def step():
+        dut.zero_grad(set_to_none=True)
+        x_static.grad = None
+        (dut(x_static) * w).sum().backward()
+
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for _ in range(3):
+            step()
+    torch.cuda.current_stream().wait_stream(side)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        step()
+    x_grad, p_grads = x_static.grad, {k: p.grad for k, p in dut.named_parameters()}
+    for x in xs[1:]:
+        with torch.no_grad():
+            x_static.copy_(x.cuda())
+        graph.replay()
+        torch.cuda.synchronize()
+        xr = x.clone().requires_grad_(True)
+        ref.zero_grad(set_to_none=True)
+        (ref(xr) * w.cpu()).sum().backward()
+        assert rel_l2(x_grad, xr.grad) < 1e-4
+        for k, p in ref.named_parameters():
+            if k.endswith("norm_stored_pattern.bias"):
+                continue                      # exactly 0 in exact arithmetic (see test_backward_parity)
+            assert rel_l2(p_grads[k], p.grad) < 1e-4, k
+
+
 # ----------------------------------------------------------------------------- sharded merge on one GPU
 @pytest.mark.parametrize("G", [2, 8])
 def test_pattern_sharded_merge_single_gpu(hf, G):
