@@ -328,6 +328,154 @@ __global__ void __launch_bounds__(NT) bwd_core_kv_kernel(CoreArgs a) {
   }
 }
 
+// ------------------------------------------------------- tiny-width core (H, Dv <= 4)
+// Hop-VAE's `index_to_embedding` layer has 3-wide patterns (HopVAE.py:164-170): the 64-column tiles above spend
+// 95 % of their arithmetic on padding there (core_q + core_kv: 42 us at N = 2,048, as much as a 64-wide layer).
+// Here all P patterns sit in shared memory as float4 and one launch does both halves of the core backward:
+//   phase A (row-major)      8 lanes share a query row, lane s scans patterns s, s+8, ...: dq = sum_j dS_j k_j,
+//                            combined with shuffles;
+//   phase B (pattern-major)  thread t owns patterns t, t+128, ... of a 512-pattern chunk and walks the CTA's rows
+//                            (broadcast reads): dK_j += dS_rj q_r, dV_j += A_rj dR_r in registers, one RED per
+//                            element at the end.
+// A score costs four FMAs, so computing it once per phase is cheaper than exchanging it.
+constexpr int kTinyBwdThreads = 128;
+constexpr int kTinyBwdLanes = 8;
+constexpr int kTinyBwdRows = kTinyBwdThreads / kTinyBwdLanes;   // 16 query rows per step
+constexpr int kTinyBwdPat = 4;                                   // patterns per thread and chunk
+
+__device__ __forceinline__ float dot4(const float4& a, const float4& b) {
+  return fmaf(a.w, b.w, fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x)));
+}
+
+__global__ void __launch_bounds__(kTinyBwdThreads) bwd_core_tiny_kernel(CoreArgs a) {
+  extern __shared__ __align__(16) float smem[];
+  float4* Ks = reinterpret_cast<float4*>(smem);   // [P]
+  float4* Vs = Ks + a.p;                          // [P]
+  float4* Qr = Vs + a.p;                          // [rows] query rows of the current step
+  float4* Gr = Qr + kTinyBwdRows;                 // [rows] dR rows
+  float* Lr = reinterpret_cast<float*>(Gr + kTinyBwdRows);   // [rows] lse
+  float* Dr = Lr + kTinyBwdRows;                  // [rows] delta
+  const int tid = threadIdx.x;
+  for (int j = tid; j < a.p; j += kTinyBwdThreads) {
+    float kv[4] = {0.f, 0.f, 0.f, 0.f}, vv[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {                 // (constant indices: the arrays stay in registers)
+      if (c < a.h) kv[c] = __ldg(a.khat + (size_t)j * a.h + c);
+      if (c < a.dv) vv[c] = __ldg(a.vhat + (size_t)j * a.dv + c);
+    }
+    Ks[j] = make_float4(kv[0], kv[1], kv[2], kv[3]);
+    Vs[j] = make_float4(vv[0], vv[1], vv[2], vv[3]);
+  }
+  const int sub = tid & (kTinyBwdLanes - 1), rloc = tid / kTinyBwdLanes;
+  const int chunk = kTinyBwdThreads * kTinyBwdPat;
+  const int n_chunks = (a.p + chunk - 1) / chunk;
+  const int n_groups = (a.n + kTinyBwdRows - 1) / kTinyBwdRows;
+  float dk[kTinyBwdPat][4], dv[kTinyBwdPat][4];
+#pragma unroll
+  for (int m = 0; m < kTinyBwdPat; ++m)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) dk[m][e] = dv[m][e] = 0.f;
+
+  auto flush = [&](int c0) {
+#pragma unroll
+    for (int m = 0; m < kTinyBwdPat; ++m) {
+      const int j = c0 + tid + kTinyBwdThreads * m;
+      if (j < a.p) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          if (c < a.h) atomicAdd(a.dkhat + (size_t)j * a.h + c, dk[m][c]);
+          if (c < a.dv) atomicAdd(a.dvhat + (size_t)j * a.dv + c, dv[m][c]);
+        }
+      }
+#pragma unroll
+      for (int e = 0; e < 4; ++e) dk[m][e] = dv[m][e] = 0.f;
+    }
+  };
+
+  for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
+    const long long gr = (long long)grp * kTinyBwdRows + rloc;
+    const bool ok = gr < a.n;
+    // ---- the row: q, dR, lse, delta = <dR, R>
+    float qv[4] = {0.f, 0.f, 0.f, 0.f}, gv[4] = {0.f, 0.f, 0.f, 0.f};
+    float lse = INFINITY, delta = 0.f;            // exp(s - inf) = 0: rows past N contribute nothing
+    if (ok) {
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        if (c < a.h) qv[c] = __ldg(a.qs + gr * a.h + c);
+        if (c < a.dv) {
+          gv[c] = __ldg(a.dr + gr * a.dv + c);
+          delta = fmaf(gv[c], __ldg(a.r + gr * a.dv + c), delta);
+        }
+      }
+      lse = __ldg(a.lse + gr);
+    }
+    const float4 q = make_float4(qv[0], qv[1], qv[2], qv[3]);
+    const float4 g = make_float4(gv[0], gv[1], gv[2], gv[3]);
+    __syncthreads();                               // phase B of the previous step is done with Qr.. (and Ks/Vs are staged)
+    if (sub == 0) {
+      Qr[rloc] = q; Gr[rloc] = g; Lr[rloc] = lse; Dr[rloc] = delta;
+      if (ok) a.delta[gr] = delta;
+    }
+    // ---- phase A: dq of this row
+    float dq[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int j = sub; j < a.p; j += kTinyBwdLanes) {
+      const float4 k = Ks[j];
+      const float prob = __expf(dot4(q, k) - lse);
+      const float ds = prob * (dot4(g, Vs[j]) - delta);
+      dq[0] = fmaf(ds, k.x, dq[0]); dq[1] = fmaf(ds, k.y, dq[1]);
+      dq[2] = fmaf(ds, k.z, dq[2]); dq[3] = fmaf(ds, k.w, dq[3]);
+    }
+#pragma unroll
+    for (int off = 1; off < kTinyBwdLanes; off <<= 1)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) dq[c] += __shfl_xor_sync(0xffffffffu, dq[c], off);
+    if (ok && sub == 0) {
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+        if (c < a.h) a.dqs[gr * a.h + c] = dq[c];
+    }
+    __syncthreads();
+    // ---- phase B: dK^, dV^ of this thread's patterns over the step's rows
+    for (int ch = 0; ch < n_chunks; ++ch) {
+      float4 k[kTinyBwdPat], v[kTinyBwdPat];
+#pragma unroll
+      for (int m = 0; m < kTinyBwdPat; ++m) {
+        const int j = ch * chunk + tid + kTinyBwdThreads * m;
+        k[m] = j < a.p ? Ks[j] : make_float4(0.f, 0.f, 0.f, 0.f);
+        v[m] = j < a.p ? Vs[j] : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll 4
+      for (int r = 0; r < kTinyBwdRows; ++r) {
+        const float4 qr = Qr[r], gr4 = Gr[r];
+        const float lr = Lr[r], dr = Dr[r];
+#pragma unroll
+        for (int m = 0; m < kTinyBwdPat; ++m) {
+          const float prob = __expf(dot4(qr, k[m]) - lr);
+          const float ds = prob * (dot4(gr4, v[m]) - dr);
+          dk[m][0] = fmaf(ds, qr.x, dk[m][0]); dk[m][1] = fmaf(ds, qr.y, dk[m][1]);
+          dk[m][2] = fmaf(ds, qr.z, dk[m][2]); dk[m][3] = fmaf(ds, qr.w, dk[m][3]);
+          dv[m][0] = fmaf(prob, gr4.x, dv[m][0]); dv[m][1] = fmaf(prob, gr4.y, dv[m][1]);
+          dv[m][2] = fmaf(prob, gr4.z, dv[m][2]); dv[m][3] = fmaf(prob, gr4.w, dv[m][3]);
+        }
+      }
+      if (n_chunks > 1) flush(ch * chunk);         // several chunks share the registers: hand each over at once
+    }
+  }
+  if (n_chunks == 1) flush(0);                     // one chunk: the sums ran across all of this CTA's steps
+}
+
+int launch_core_tiny(const CoreArgs& a, cudaStream_t st) {
+  const size_t smem = sizeof(float4) * (2 * (size_t)a.p + 2 * kTinyBwdRows) + sizeof(float) * 2 * kTinyBwdRows;
+  if (smem > 48 * 1024)
+    HOP_CUDA(cudaFuncSetAttribute(bwd_core_tiny_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int n_groups = (a.n + kTinyBwdRows - 1) / kTinyBwdRows;
+  int grid = 2 * num_sms();
+  if (grid > n_groups) grid = n_groups;
+  bwd_core_tiny_kernel<<<grid < 1 ? 1 : grid, kTinyBwdThreads, smem, st>>>(a);
+  HOP_LAUNCH_CHECK("bwd_core_tiny_kernel");
+  return HOP_OK;
+}
+
 // ------------------------------------------------------- LayerNorm backward
 // For rows of y = LN(x) (or y = x when !has_ln):  dx (+)= d/dx <scale*g, y>, and the
 // affine grads dgamma += sum_rows scale*g*xhat, dbeta += sum_rows scale*g (fp32 RED).
@@ -706,7 +854,8 @@ int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patte
   // 2. association core
   CoreArgs ca{qhat, pt.khat, pt.vhat, lse, dR, retrieved, w.delta, w.dqs, w.dkhat, w.dvhat, N, P, H, Dv, 0};
   const int hc = (H + 63) / 64, dvc = (Dv + 63) / 64;
-  if (hc == 1 && dvc == 1) HOP_TRY((launch_core<1, 1>(ca, st)));
+  if (H <= 4 && Dv <= 4 && P <= 4096 && !getenv("HOP_BWD_NO_TINY")) HOP_TRY(launch_core_tiny(ca, st));
+  else if (hc == 1 && dvc == 1) HOP_TRY((launch_core<1, 1>(ca, st)));
   else if (hc == 1 && dvc == 2) HOP_TRY((launch_core<1, 2>(ca, st)));
   else if (hc == 2 && dvc == 1) HOP_TRY((launch_core<2, 1>(ca, st)));
   else HOP_TRY((launch_core<2, 2>(ca, st)));

@@ -68,8 +68,13 @@ class _AssociationCore(nn.Module):
         """Views of the q / k / v slices of in_proj (order q, k, v; static ones absent)."""
         out: Dict[str, Optional[Tensor]] = dict(wq=None, bq=None, wk=None, bk=None, wv=None, bv=None)
         o = 0
+        total = self.rows_q + self.rows_k + self.rows_v
         for tag, rows in (("q", self.rows_q), ("k", self.rows_k), ("v", self.rows_v)):
-            if rows:
+            if rows == total and rows:
+                # the only projection (Hop-VAE's layers: q and k static): hand out the parameter itself -- a slice
+                # would add a SliceBackward (zero-fill + copy of the full gradient) per parameter and step
+                out["w" + tag], out["b" + tag] = self.in_proj_weight, self.in_proj_bias
+            elif rows:
                 out["w" + tag] = self.in_proj_weight[o:o + rows]
                 out["b" + tag] = None if self.in_proj_bias is None else self.in_proj_bias[o:o + rows]
                 o += rows
@@ -215,8 +220,9 @@ class HopfieldLayer(nn.Module):
         core = h.association_core
         ln = lambda m: (None, None) if m is None else (m.weight, m.bias)
         pack: Dict[str, Optional[Tensor]] = dict(
-            lookup=self.lookup_weights[0],
-            lookup_targets=None if self.lookup_targets is None else self.lookup_targets[0])
+            # squeeze, not [0]: its backward is a view; SelectBackward zero-fills and copies the full gradient
+            lookup=self.lookup_weights.squeeze(0),
+            lookup_targets=None if self.lookup_targets is None else self.lookup_targets.squeeze(0))
         pack["ln_state_w"], pack["ln_state_b"] = ln(h.norm_state_pattern)
         pack["ln_stored_w"], pack["ln_stored_b"] = ln(h.norm_stored_pattern)
         pack["ln_proj_w"], pack["ln_proj_b"] = ln(h.norm_pattern_projection)
