@@ -39,7 +39,7 @@ __device__ __forceinline__ uint16_t to16(float v, int bf16) {
 }
 
 template <int RM>
-__global__ void __launch_bounds__(NT) ln_linear_kernel(LnLinearArgs a) {
+__device__ __forceinline__ void ln_linear_body(const LnLinearArgs& a) {
   constexpr int BR = 16 * RM;
   __shared__ __align__(16) float Xs[BR * XS];
   __shared__ __align__(16) float Ws[TN * XS];
@@ -154,6 +154,31 @@ __global__ void __launch_bounds__(NT) ln_linear_kernel(LnLinearArgs a) {
   }
 }
 
+template <int RM>
+__global__ void __launch_bounds__(NT) ln_linear_kernel(LnLinearArgs a) { ln_linear_body<RM>(a); }
+
+// Two independent jobs over the same number of rows in one launch (blockIdx.y picks the job): the K^ and V^ packs of
+// prepare_patterns -- at the reference's sizes each is a ~5 us launch-latency-bound kernel, once per training step.
+template <int RM>
+__global__ void __launch_bounds__(NT) ln_linear_pair_kernel(LnLinearArgs a0, LnLinearArgs a1) {
+  ln_linear_body<RM>(blockIdx.y == 0 ? a0 : a1);
+}
+
+int launch_ln_linear_pair(const LnLinearArgs& a0, const LnLinearArgs& a1, cudaStream_t st) {
+  const int total_rows = (a0.y16 || a0.yt16 || a1.y16 || a1.yt16) ? a0.rows_pad : a0.rows;
+  if (total_rows <= 0) return HOP_OK;
+  const int sms = num_sms();
+  if (total_rows >= 64 * sms) {
+    ln_linear_pair_kernel<4><<<dim3((total_rows + 63) / 64, 2), NT, 0, st>>>(a0, a1);
+  } else if (total_rows >= 32 * sms) {
+    ln_linear_pair_kernel<2><<<dim3((total_rows + 31) / 32, 2), NT, 0, st>>>(a0, a1);
+  } else {
+    ln_linear_pair_kernel<1><<<dim3((total_rows + 15) / 16, 2), NT, 0, st>>>(a0, a1);
+  }
+  HOP_LAUNCH_CHECK("ln_linear_pair_kernel");
+  return HOP_OK;
+}
+
 int launch_ln_linear(const LnLinearArgs& a, cudaStream_t st) {
   const int total_rows = (a.y16 || a.yt16) ? a.rows_pad : a.rows;
   if (total_rows <= 0) return HOP_OK;
@@ -183,7 +208,6 @@ int launch_prepare_patterns(const hop_desc& d, const hop_params& p, const hop_pa
   k.y16 = tc ? pt.k16 : nullptr; k.yt16 = (tc && d.update_steps > 0) ? pt.kt16 : nullptr;
   k.bf16 = (path == HOP_PATH_TC_BF16);
   if ((d.flags & HOP_F_PROJ_STORED) && !p.wk) HOP_FAIL(HOP_ERR_BAD_ARG, "HOP_F_PROJ_STORED set but params.wk is NULL");
-  HOP_TRY(launch_ln_linear(k, st));
 
   LnLinearArgs v{};
   v.x = p.lookup_targets ? p.lookup_targets : p.lookup; v.rows = d.n_patterns; v.rows_pad = ppad; v.din = d.d_in;
@@ -193,7 +217,7 @@ int launch_prepare_patterns(const hop_desc& d, const hop_params& p, const hop_pa
   v.y16 = nullptr; v.yt16 = tc ? pt.vt16 : nullptr;
   v.bf16 = (path == HOP_PATH_TC_BF16);
   if ((d.flags & HOP_F_PROJ_PATTERN) && !p.wv) HOP_FAIL(HOP_ERR_BAD_ARG, "HOP_F_PROJ_PATTERN set but params.wv is NULL");
-  HOP_TRY(launch_ln_linear(v, st));
+  HOP_TRY(launch_ln_linear_pair(k, v, st));     // K^ and V^ packs: same rows, one launch
 
   if (tc && pt.vot16) {
     // out_proj folded into the read-out operand: (V^ Wo^T)^T, 16-bit, from the fp32 V^ just written
