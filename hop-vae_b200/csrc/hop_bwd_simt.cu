@@ -486,9 +486,8 @@ struct LnBwdArgs {
   float* dgamma; float* dbeta;   // pre-zeroed; nullptr when no affine / not wanted
 };
 
-__global__ void __launch_bounds__(NT) ln_bwd_kernel(LnBwdArgs a) {
-  extern __shared__ float sh[];  // [2*d] column partials
-  float* sg = sh;
+__device__ __forceinline__ void ln_bwd_body(const LnBwdArgs& a, float* sh, int vbx, int vgx) {
+  float* sg = sh;                // [2*d] column partials
   float* sb = sh + a.d;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const bool want_affine = a.has_ln && (a.dgamma || a.dbeta);
@@ -496,7 +495,7 @@ __global__ void __launch_bounds__(NT) ln_bwd_kernel(LnBwdArgs a) {
     for (int i = threadIdx.x; i < 2 * a.d; i += NT) sh[i] = 0.f;
     __syncthreads();
   }
-  for (int r = blockIdx.x * (NT / 32) + warp; r < a.rows; r += gridDim.x * (NT / 32)) {
+  for (int r = vbx * (NT / 32) + warp; r < a.rows; r += vgx * (NT / 32)) {
     const float* xr = a.x + (size_t)r * a.d;
     const float* gr = a.g + (size_t)r * a.d;
     float* dxr = a.dx + (size_t)r * a.d;
@@ -539,14 +538,10 @@ __global__ void __launch_bounds__(NT) ln_bwd_kernel(LnBwdArgs a) {
   }
 }
 
-int launch_ln_bwd(const LnBwdArgs& a, cudaStream_t st) {
-  const int sms = num_sms();
+int ln_bwd_grid(const LnBwdArgs& a) {
   int grid = (a.rows + 7) / 8;
-  if (grid > 2 * sms) grid = 2 * sms;
-  if (grid < 1) grid = 1;
-  ln_bwd_kernel<<<grid, NT, 2 * a.d * sizeof(float), st>>>(a);
-  HOP_LAUNCH_CHECK("ln_bwd_kernel");
-  return HOP_OK;
+  if (grid > 2 * num_sms()) grid = 2 * num_sms();
+  return grid < 1 ? 1 : grid;
 }
 
 // ------------------------------------------------------------ weight grads
@@ -558,14 +553,14 @@ struct WgradArgs {
   float* dw; float* db; int rows_per_cta; float scale;
 };
 
-__global__ void __launch_bounds__(NT) wgrad_kernel(WgradArgs a) {
+__device__ __forceinline__ void wgrad_body(const WgradArgs& a, int vbx, int vby, int vbz) {
   constexpr int BR = 32, ST = 68;
   __shared__ __align__(16) float Ys[BR * ST];
   __shared__ __align__(16) float Xs[BR * ST];
   __shared__ float s_mean[BR], s_rstd[BR];
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4, warp = tid >> 5, lane = tid & 31;
-  const int o0 = blockIdx.x * 64, i0 = blockIdx.y * 64;
-  const int r_begin = blockIdx.z * a.rows_per_cta, r_end = min(a.rows, r_begin + a.rows_per_cta);
+  const int o0 = vbx * 64, i0 = vby * 64;
+  const int r_begin = vbz * a.rows_per_cta, r_end = min(a.rows, r_begin + a.rows_per_cta);
   float acc[4][4];
 #pragma unroll
   for (int i = 0; i < 4; ++i)
@@ -626,11 +621,12 @@ __global__ void __launch_bounds__(NT) wgrad_kernel(WgradArgs a) {
       const int c = i0 + tx * 4 + j;
       if (c < a.din) atomicAdd(a.dw + (size_t)o * a.din + c, acc[i][j] * a.scale);
     }
-    if (a.db && blockIdx.y == 0 && tx == 0) atomicAdd(a.db + o, bsum[i] * a.scale);
+    if (a.db && vby == 0 && tx == 0) atomicAdd(a.db + o, bsum[i] * a.scale);
   }
 }
 
-int launch_wgrad(WgradArgs a, cudaStream_t st) {
+// grid (dout/64, din/64, row splits); fills a.rows_per_cta
+dim3 wgrad_grid(WgradArgs& a) {
   const int sms = num_sms();
   const int tiles = ((a.dout + 63) / 64) * ((a.din + 63) / 64);
   int splits = (2 * sms + tiles - 1) / tiles;
@@ -639,21 +635,23 @@ int launch_wgrad(WgradArgs a, cudaStream_t st) {
   if (splits < 1) splits = 1;
   a.rows_per_cta = round_up((a.rows + splits - 1) / splits, 32);
   splits = (a.rows + a.rows_per_cta - 1) / a.rows_per_cta;
-  dim3 grid((a.dout + 63) / 64, (a.din + 63) / 64, splits);
-  wgrad_kernel<<<grid, NT, 0, st>>>(a);
-  HOP_LAUNCH_CHECK("wgrad_kernel");
-  return HOP_OK;
+  return dim3((a.dout + 63) / 64, (a.din + 63) / 64, splits);
 }
 
 // y[n][j] = sum_o g[n][o] * w[o][j]   (w row-major (dout_w, din_w); i.e. g . W, no transpose)
-__global__ void __launch_bounds__(NT) linear_nn_kernel(const float* __restrict__ g, const float* __restrict__ w,
-                                                       float* __restrict__ y, int n, int k, int m) {
+struct LinearNnArgs { const float* g; const float* w; float* y; int n, k, m; };
+
+__device__ __forceinline__ void linear_nn_body(const LinearNnArgs& a, int vbx, int vby) {
+  const float* __restrict__ g = a.g;
+  const float* __restrict__ w = a.w;
+  float* __restrict__ y = a.y;
+  const int n = a.n, k = a.k, m = a.m;
   // CTA: 32 rows x 64 output columns; contraction streamed in chunks of 32
   constexpr int BR = 32, KC = 32;
   __shared__ __align__(16) float Gs[BR * (KC + 4)];
   __shared__ __align__(16) float Ws[KC * 68];
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
-  const int row0 = blockIdx.x * BR, c0 = blockIdx.y * 64;
+  const int row0 = vbx * BR, c0 = vby * 64;
   float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
   for (int k0 = 0; k0 < k; k0 += KC) {
     __syncthreads();
@@ -691,10 +689,69 @@ __global__ void __launch_bounds__(NT) linear_nn_kernel(const float* __restrict__
   }
 }
 
-int launch_linear_nn(const float* g, const float* w, float* y, int n, int k, int m, cudaStream_t st) {
-  dim3 grid((n + 31) / 32, (m + 63) / 64);
-  linear_nn_kernel<<<grid, NT, 0, st>>>(g, w, y, n, k, m);
-  HOP_LAUNCH_CHECK("linear_nn_kernel");
+// ------------------------------------------------------------ batched small launches
+// The projections, weight gradients and LayerNorm backwards either side of the core are 3-10 us launch-latency-bound
+// kernels at the reference's sizes, ten per layer.  Jobs that are ready at the same time run as ONE launch: the
+// grid is the concatenation of the jobs' own grids, a block finds its job from the prefix sums.
+enum BwdJobKind { kJobLnBwd = 0, kJobWgrad = 1, kJobLinearNn = 2 };
+struct BwdJob {
+  int kind, block0, gx, gy;       // first block of the job in the merged grid; its own grid is (gx, gy, *)
+  LnBwdArgs ln; WgradArgs wg; LinearNnArgs lin;
+};
+struct BwdJobBatch {
+  static constexpr int kMax = 8;
+  BwdJob job[kMax];
+  int count, blocks;
+  size_t smem;
+};
+
+__global__ void __launch_bounds__(NT) bwd_job_batch_kernel(const __grid_constant__ BwdJobBatch b) {
+  extern __shared__ float sh[];
+  int j = 0;
+  while (j + 1 < b.count && (int)blockIdx.x >= b.job[j + 1].block0) ++j;
+  const BwdJob& job = b.job[j];
+  const int v = (int)blockIdx.x - job.block0;
+  if (job.kind == kJobLnBwd) {
+    ln_bwd_body(job.ln, sh, v, job.gx);
+  } else if (job.kind == kJobWgrad) {
+    const int per_z = job.gx * job.gy;
+    const int vz = v / per_z, rem = v - vz * per_z;
+    wgrad_body(job.wg, rem % job.gx, rem / job.gx, vz);
+  } else {
+    linear_nn_body(job.lin, v % job.gx, v / job.gx);
+  }
+}
+
+int batch_add_ln_bwd(BwdJobBatch& b, const LnBwdArgs& a) {
+  if (b.count >= BwdJobBatch::kMax) HOP_FAIL(HOP_ERR_BAD_ARG, "backward: job batch overflow");
+  BwdJob& j = b.job[b.count++];
+  j.kind = kJobLnBwd; j.block0 = b.blocks; j.gx = ln_bwd_grid(a); j.gy = 1; j.ln = a;
+  b.blocks += j.gx;
+  const size_t smem = 2 * (size_t)a.d * sizeof(float);
+  if (smem > b.smem) b.smem = smem;
+  return HOP_OK;
+}
+int batch_add_wgrad(BwdJobBatch& b, WgradArgs a) {
+  if (b.count >= BwdJobBatch::kMax) HOP_FAIL(HOP_ERR_BAD_ARG, "backward: job batch overflow");
+  const dim3 g = wgrad_grid(a);
+  BwdJob& j = b.job[b.count++];
+  j.kind = kJobWgrad; j.block0 = b.blocks; j.gx = (int)g.x; j.gy = (int)g.y; j.wg = a;
+  b.blocks += (int)(g.x * g.y * g.z);
+  return HOP_OK;
+}
+int batch_add_linear_nn(BwdJobBatch& b, const float* g, const float* w, float* y, int n, int k, int m) {
+  if (b.count >= BwdJobBatch::kMax) HOP_FAIL(HOP_ERR_BAD_ARG, "backward: job batch overflow");
+  BwdJob& j = b.job[b.count++];
+  j.kind = kJobLinearNn; j.block0 = b.blocks; j.gx = (n + 31) / 32; j.gy = (m + 63) / 64;
+  j.lin = LinearNnArgs{g, w, y, n, k, m};
+  b.blocks += j.gx * j.gy;
+  return HOP_OK;
+}
+int launch_job_batch(BwdJobBatch& b, cudaStream_t st) {
+  if (b.count == 0 || b.blocks == 0) return HOP_OK;
+  bwd_job_batch_kernel<<<b.blocks, NT, b.smem, st>>>(b);
+  HOP_LAUNCH_CHECK("bwd_job_batch_kernel");
+  b = BwdJobBatch{};
   return HOP_OK;
 }
 
@@ -840,16 +897,18 @@ int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patte
     }
   }
 
-  // 1. out-projection backward
+  // 1. out-projection backward: dR = G . Wo and dWo = G^T . R are independent -> one launch
+  BwdJobBatch stage[3] = {};
   const float* dR = grad_out;
   if (out_proj) {
-    HOP_TRY(launch_linear_nn(grad_out, p.wo, w.dr, N, d.d_out, Dv, st));
+    HOP_TRY(batch_add_linear_nn(stage[0], grad_out, p.wo, w.dr, N, d.d_out, Dv));
     dR = w.dr;
     if (g.d_wo) {
       WgradArgs wa{grad_out, retrieved, N, d.d_out, Dv, 0, nullptr, nullptr, 0.f, g.d_wo, g.d_bo, 0, 1.f};
-      HOP_TRY(launch_wgrad(wa, st));
+      HOP_TRY(batch_add_wgrad(stage[0], wa));
     }
   }
+  HOP_TRY(launch_job_batch(stage[0], st));
 
   // 2. association core
   CoreArgs ca{qhat, pt.khat, pt.vhat, lse, dR, retrieved, w.delta, w.dqs, w.dkhat, w.dvhat, N, P, H, Dv, 0};
@@ -860,66 +919,73 @@ int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patte
   else if (hc == 2 && dvc == 1) HOP_TRY((launch_core<2, 1>(ca, st)));
   else HOP_TRY((launch_core<2, 2>(ca, st)));
 
-  // 3. query side: dqs -> [Wq] -> LN_q -> dx
+  // 3-5. the three tails (query side, K^ path, V^ path) in stages: stage 0 = everything that needs only the core's
+  // outputs (weight gradients, the Linear backwards, LayerNorm backwards without a projection in front), stage 1 =
+  // LayerNorm backwards behind a projection, stage 2 = a second writer of d_lookup (the K^ and V^ paths share it
+  // unless lookup_targets exists; the later one accumulates, so they must not run in the same launch).
+  // query side: dqs -> [Wq] -> LN_q -> dx
   {
     const float* gq = w.dqs;     // gradient w.r.t. beta*Qproj
-    float scale = d.beta;
     if (q_proj) {
       // dWq = (beta dqs)^T LN(x), dbq = sum beta dqs ; dqn = beta dqs . Wq
       if (g.d_wq) {
         WgradArgs wa{w.dqs, x, N, H, Din, (d.flags & HOP_F_NORM_STATE) ? 1 : 0, p.ln_state_w, p.ln_state_b, d.ln_eps,
                      g.d_wq, g.d_bq, 0, d.beta};
-        HOP_TRY(launch_wgrad(wa, st));
+        HOP_TRY(batch_add_wgrad(stage[0], wa));
       }
-      HOP_TRY(launch_linear_nn(w.dqs, p.wq, w.dqn, N, H, Din, st));
+      HOP_TRY(batch_add_linear_nn(stage[0], w.dqs, p.wq, w.dqn, N, H, Din));
       gq = w.dqn;
     }
     if (g.d_x) {
-      LnBwdArgs la{x, gq, N, Din, (d.flags & HOP_F_NORM_STATE) ? 1 : 0, p.ln_state_w, d.ln_eps, scale,
+      LnBwdArgs la{x, gq, N, Din, (d.flags & HOP_F_NORM_STATE) ? 1 : 0, p.ln_state_w, d.ln_eps, d.beta,
                    g.d_x, 0, g.d_ln_state_w, g.d_ln_state_b};
-      HOP_TRY(launch_ln_bwd(la, st));
+      HOP_TRY(batch_add_ln_bwd(stage[q_proj ? 1 : 0], la));
     }
   }
-
-  // 4. pattern side, V^ path: dV^ -> [Wv] -> LN_v -> d_lookup(_targets)
-  const float* Wt = sep_targets ? p.lookup_targets : p.lookup;
-  float* d_wt = sep_targets ? g.d_lookup_targets : g.d_lookup;
-  {
-    const float* gv = w.dvhat;
-    if (v_proj) {
-      if (g.d_wv) {
-        WgradArgs wa{w.dvhat, Wt, P, Dv, Din, (d.flags & HOP_F_NORM_PROJ) ? 1 : 0, p.ln_proj_w, p.ln_proj_b, d.ln_eps,
-                     g.d_wv, g.d_bv, 0, 1.f};
-        HOP_TRY(launch_wgrad(wa, st));
-      }
-      HOP_TRY(launch_linear_nn(w.dvhat, p.wv, w.dvn, P, Dv, Din, st));
-      gv = w.dvn;
-    }
-    if (d_wt) {
-      LnBwdArgs la{Wt, gv, P, Din, (d.flags & HOP_F_NORM_PROJ) ? 1 : 0, p.ln_proj_w, d.ln_eps, 1.f,
-                   d_wt, 0, g.d_ln_proj_w, g.d_ln_proj_b};
-      HOP_TRY(launch_ln_bwd(la, st));
-    }
-  }
-  // 5. pattern side, K^ path (accumulates into d_lookup when it shares the V^ path's buffer)
+  // pattern side, K^ path: dK^ -> [Wk] -> LN_k -> d_lookup (first writer)
+  int k_stage = -1;
   {
     const float* gk = w.dkhat;
     if (k_proj) {
       if (g.d_wk) {
         WgradArgs wa{w.dkhat, p.lookup, P, H, Din, (d.flags & HOP_F_NORM_STORED) ? 1 : 0, p.ln_stored_w, p.ln_stored_b,
                      d.ln_eps, g.d_wk, g.d_bk, 0, 1.f};
-        HOP_TRY(launch_wgrad(wa, st));
+        HOP_TRY(batch_add_wgrad(stage[0], wa));
       }
-      HOP_TRY(launch_linear_nn(w.dkhat, p.wk, w.dkn, P, H, Din, st));
+      HOP_TRY(batch_add_linear_nn(stage[0], w.dkhat, p.wk, w.dkn, P, H, Din));
       gk = w.dkn;
     }
     if (g.d_lookup) {
-      const int accumulate = (!sep_targets && d_wt != nullptr) ? 1 : 0;
+      k_stage = k_proj ? 1 : 0;
       LnBwdArgs la{p.lookup, gk, P, Din, (d.flags & HOP_F_NORM_STORED) ? 1 : 0, p.ln_stored_w, d.ln_eps, 1.f,
-                   g.d_lookup, accumulate, g.d_ln_stored_w, g.d_ln_stored_b};
-      HOP_TRY(launch_ln_bwd(la, st));
+                   g.d_lookup, 0, g.d_ln_stored_w, g.d_ln_stored_b};
+      HOP_TRY(batch_add_ln_bwd(stage[k_stage], la));
     }
   }
+  // pattern side, V^ path: dV^ -> [Wv] -> LN_v -> d_lookup(_targets) (accumulates behind the K^ path when shared)
+  {
+    const float* Wt = sep_targets ? p.lookup_targets : p.lookup;
+    float* d_wt = sep_targets ? g.d_lookup_targets : g.d_lookup;
+    const float* gv = w.dvhat;
+    if (v_proj) {
+      if (g.d_wv) {
+        WgradArgs wa{w.dvhat, Wt, P, Dv, Din, (d.flags & HOP_F_NORM_PROJ) ? 1 : 0, p.ln_proj_w, p.ln_proj_b, d.ln_eps,
+                     g.d_wv, g.d_bv, 0, 1.f};
+        HOP_TRY(batch_add_wgrad(stage[0], wa));
+      }
+      HOP_TRY(batch_add_linear_nn(stage[0], w.dvhat, p.wv, w.dvn, P, Dv, Din));
+      gv = w.dvn;
+    }
+    if (d_wt) {
+      const int accumulate = (!sep_targets && k_stage >= 0) ? 1 : 0;
+      int v_stage = v_proj ? 1 : 0;
+      if (accumulate && v_stage <= k_stage) v_stage = k_stage + 1;
+      LnBwdArgs la{Wt, gv, P, Din, (d.flags & HOP_F_NORM_PROJ) ? 1 : 0, p.ln_proj_w, d.ln_eps, 1.f,
+                   d_wt, accumulate, g.d_ln_proj_w, g.d_ln_proj_b};
+      HOP_TRY(batch_add_ln_bwd(stage[v_stage], la));
+    }
+  }
+  for (int i = 0; i < 3; ++i) HOP_TRY(launch_job_batch(stage[i], st));
   return HOP_OK;
 }
 
