@@ -379,8 +379,9 @@ def gpu_run(args):
             "data": "synthetic (config-5 recipe, SURVEY.md 8d; seeds 1265/1266/1267+rank)",
             "config": {"workload": args.workload, "rows_per_gpu": n, "patterns": p, "dim": d, "update_steps": t,
                        "beta": 1.0 / math.sqrt(d),
-                       "parallelism": (f"pattern-sharded{world} (P/{world} per GPU, NCCL LSE merge)" if sharded
-                                       else f"batch-dp{world}"), "kernel_path":
+                       "parallelism": (f"pattern-sharded{world} (P/{world} per GPU, " +
+                                       ("fused peer-memory LSE merge over NVLink)" if getattr(runner, "use_peer", False)
+                                        else "NCCL LSE merge)") if sharded else f"batch-dp{world}"), "kernel_path":
                        {1: "fp32_simt", 2: "tc_f16", 3: "tc_bf16"}[path],
                        "host_numa_cpus": numa, "l2": "flushed between timed steps (256 MiB memset outside the events)"},
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": x_host.numel() * 4,
