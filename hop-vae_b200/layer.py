@@ -20,7 +20,7 @@ from __future__ import annotations
 
 import math
 import os
-from typing import Dict, Optional, Tuple
+from typing import Dict, List, Optional, Tuple
 
 import torch
 import torch.nn as nn
@@ -93,6 +93,30 @@ class _Hopfield(nn.Module):
         self.norm_stored_pattern = nn.LayerNorm(d_in, elementwise_affine=a_k) if n_k else None
         self.norm_state_pattern = nn.LayerNorm(d_in, elementwise_affine=a_q) if n_q else None
         self.norm_pattern_projection = nn.LayerNorm(d_in, elementwise_affine=a_v) if n_v else None
+
+
+def host_chunk_bounds(n: int, chunks=None) -> List[Tuple[int, int]]:
+    """Row pieces [(begin, end), ...] of `forward_host`'s copy / kernel pipeline: contiguous, covering [0, n), every
+    cut on a multiple of 128 rows (the fused kernel's row tile).  `chunks` = number of equal pieces, or a sequence
+    of weights (pieces proportional to them); default: a 1:3:3:1 ramp for n >= 8192 -- small first / last pieces
+    keep the un-overlapped lead-in copy and lead-out copy short -- two pieces for n >= 2048, else one."""
+    if n <= 0:
+        return []
+    if chunks is None:
+        chunks = (1, 3, 3, 1) if n >= 8192 else (2 if n >= 2048 else 1)
+    if isinstance(chunks, int):
+        rows = max(128, (-(-n // max(chunks, 1)) + 127) // 128 * 128)
+        return [(a, min(a + rows, n)) for a in range(0, n, rows)]
+    weights = [float(w) for w in chunks]
+    if not weights or min(weights) < 0 or sum(weights) <= 0:
+        raise ValueError("forward_host: chunk weights must be non-negative with a positive sum")
+    total = sum(weights)
+    cuts, acc = [0], 0.0
+    for w in weights:
+        acc += w
+        cuts.append(max(cuts[-1], min(n, int(round(n * acc / total / 128.0)) * 128)))
+    cuts[-1] = n
+    return [(a, b) for a, b in zip(cuts[:-1], cuts[1:]) if b > a]
 
 
 class HopfieldLayer(nn.Module):
@@ -318,20 +342,7 @@ class HopfieldLayer(nn.Module):
             out_host = torch.empty((n, width), dtype=torch.float32).pin_memory()
         elif out_host.shape != (n, width) or out_host.dtype != torch.float32 or not out_host.is_pinned():
             raise ValueError("forward_host: out_host must be a pinned float32 (N, output width) tensor")
-        if chunks is None:
-            # ramp: small first / last pieces keep the un-overlapped lead-in copy and lead-out copy short
-            chunks = (1, 3, 3, 1) if n >= 8192 else (2 if n >= 2048 else 1)
-        if isinstance(chunks, int):
-            rows = max(128, (-(-n // max(chunks, 1)) + 127) // 128 * 128)
-            bounds = [(a, min(a + rows, n)) for a in range(0, n, rows)]
-        else:
-            total = float(sum(chunks))
-            cuts, acc = [0], 0.0
-            for w in chunks:
-                acc += w
-                cuts.append(min(n, int(round(n * acc / total / 128.0)) * 128))
-            cuts[-1] = n
-            bounds = [(a, b) for a, b in zip(cuts[:-1], cuts[1:]) if b > a]
+        bounds = host_chunk_bounds(n, chunks)
         st = self.__dict__.get("_host_state")
         if st is None or st["dev"] != dev or st["rows"] < n or st["width"] != width:
             st = dict(dev=dev, rows=n, width=width, streams=tuple(torch.cuda.Stream(device=dev) for _ in range(3)),

@@ -132,3 +132,23 @@ def test_product_path_never_imports_oracle():
                 if f.endswith((".py", ".cu", ".cuh", ".h")):
                     text = open(os.path.join(dirpath, f)).read()
                     assert not re.search(r"^\s*(from|import)\s+oracle\b", text, re.M), (dirpath, f)
+
+
+def test_host_pipeline_pieces_cover_the_rows(impl):
+    """forward_host's row pieces: contiguous, cover [0, n), every inner cut on the fused kernel's 128-row tile."""
+    import random
+    bounds_of = impl.layer.host_chunk_bounds
+    rng = random.Random(5)
+    cases = [(n, c) for n in (1, 127, 128, 129, 2047, 2048, 8192, 16384, 16385, 100000)
+             for c in (None, 1, 2, 3, 7, (1, 3, 3, 1), (1, 2, 4, 1), (0, 1, 0), (5, 1))]
+    cases += [(rng.randrange(1, 70000), tuple(rng.random() for _ in range(rng.randrange(1, 9)))) for _ in range(200)]
+    for n, chunks in cases:
+        b = bounds_of(n, chunks)
+        assert b and b[0][0] == 0 and b[-1][1] == n, (n, chunks, b)
+        for (a0, a1), (b0, _) in zip(b[:-1], b[1:]):
+            assert a1 == b0 and a1 % 128 == 0
+        assert all(hi > lo for lo, hi in b)
+    assert bounds_of(16384, None) == [(0, 2048), (2048, 8192), (8192, 14336), (14336, 16384)]
+    assert bounds_of(0, 4) == []
+    with pytest.raises(ValueError):
+        bounds_of(1000, (0, 0))

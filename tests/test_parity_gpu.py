@@ -410,6 +410,9 @@ TC_CASES = {
     "d128_p4k": (128, 4096, 1024, 0),
     "d256_p2k": (256, 2048, 512, 0),
     "d256_ragged": (256, 1100, 257, 0),
+    # ragged rows AND patterns with enough (row group x pattern tile) units that a stream-K share spans row groups
+    "d256_multi_segment": (256, 20000, 1300, 0),
+    "d128_multi_segment": (128, 9000, 2100, 0),
     "d64_T1": (64, 640, 384, 1),
     "d128_T3": (128, 512, 256, 3),
     "d256_T1": (256, 1024, 256, 1),
