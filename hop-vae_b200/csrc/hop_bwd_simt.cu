@@ -791,8 +791,13 @@ int launch_core_kv(CoreArgs a, cudaStream_t st) {
   if (smem > 48 * 1024) HOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int sms = num_sms();
   const int ptiles = (a.p + BP - 1) / BP;
-  static const int waves = [] { const char* e = getenv("HOP_BWD_KV_WAVES"); return e ? atoi(e) : 3; }();
-  int splits = ((waves > 0 ? waves : 3) * sms + ptiles - 1) / ptiles;
+  // one full wave of resident CTAs (2 per SM at 104 KB of shared memory): with 3 x SMs CTAs the last half wave ran
+  // alone -- FFHQ-64 (N = 9,248): 895 -> 838 us per bottleneck training step
+  int per_sm = (int)((227u * 1024u) / smem);
+  per_sm = per_sm > 2 ? 2 : (per_sm < 1 ? 1 : per_sm);
+  static const int waves_env = [] { const char* e = getenv("HOP_BWD_KV_WAVES"); return e ? atoi(e) : 0; }();
+  const int waves = waves_env > 0 ? waves_env : per_sm;
+  int splits = (waves * sms + ptiles - 1) / ptiles;
   const int max_splits = (a.n + BQ - 1) / BQ;
   if (splits > max_splits) splits = max_splits;
   if (splits < 1) splits = 1;

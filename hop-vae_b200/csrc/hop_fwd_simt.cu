@@ -115,11 +115,15 @@ __device__ __forceinline__ void load_tile_async(float* __restrict__ dst, const f
   }
 }
 
-template <int RM, int DVC>
+// HF: association width known at compile time (64 -- Hop-VAE's `hopfield` and `embedding_to_index` layers) or 0.
+// With a runtime width 30 % of the issued instructions were address arithmetic and loop control of the two
+// contraction loops (IMAD / ISETP / BRA / LEA); the fixed width folds the strides and unrolls them.
+template <int RM, int DVC, int HF>
 __global__ void __launch_bounds__(NT) hop_fwd_simt_kernel(SimtPassArgs a, int splits) {
   extern __shared__ __align__(16) float smem[];
   constexpr int BM = 16 * RM;
-  const SimtSmemLayout L = simt_layout(BM, a.h, DVC);
+  const SimtSmemLayout L = simt_layout(BM, HF ? HF : a.h, DVC);
+  const int hs = HF ? HF + 4 : L.hs;            // stride of the Q / K tiles
   float* Qs = smem + L.q_off;
   float* Ks = smem + L.k_off;
   float* Bs = smem + L.b_off;
@@ -129,7 +133,7 @@ __global__ void __launch_bounds__(NT) hop_fwd_simt_kernel(SimtPassArgs a, int sp
   const int tx = tid & 15, ty = tid >> 4;
   const int warp = tid >> 5, lane = tid & 31;
   const int row0 = blockIdx.x * BM;
-  const int h4 = (a.h + 3) / 4 * 4;
+  const int h4 = HF ? HF : (a.h + 3) / 4 * 4;
 
   const int n_tiles = (a.p + BP - 1) / BP;
   const int tiles_per_split = (n_tiles + splits - 1) / splits;
@@ -219,13 +223,14 @@ __global__ void __launch_bounds__(NT) hop_fwd_simt_kernel(SimtPassArgs a, int sp
     for (int i = 0; i < RM; ++i)
 #pragma unroll
       for (int b = 0; b < 4; ++b) s[i][b] = 0.f;
+#pragma unroll(HF ? 4 : 1)
     for (int k = 0; k < h4; k += 4) {
       float4 q[RM];
 #pragma unroll
-      for (int i = 0; i < RM; ++i) q[i] = *reinterpret_cast<const float4*>(Qs + (ty * RM + i) * L.hs + k);
+      for (int i = 0; i < RM; ++i) q[i] = *reinterpret_cast<const float4*>(Qs + (ty * RM + i) * hs + k);
 #pragma unroll
       for (int b = 0; b < 4; ++b) {
-        const float4 kk = *reinterpret_cast<const float4*>(Ks + (tx + 16 * b) * L.hs + k);
+        const float4 kk = *reinterpret_cast<const float4*>(Ks + (tx + 16 * b) * hs + k);
 #pragma unroll
         for (int i = 0; i < RM; ++i) {
           s[i][b] = fmaf(q[i].x, kk.x, s[i][b]);
@@ -442,13 +447,14 @@ __global__ void __launch_bounds__(NT) hop_fwd_simt_kernel(SimtPassArgs a, int sp
         }
         __syncthreads();
         if (ty * RM < rows_n) {
+#pragma unroll(HF ? 4 : 1)
           for (int k = 0; k < kc; k += 4) {
             float4 ov[RM];
 #pragma unroll
             for (int i = 0; i < RM; ++i) ov[i] = *reinterpret_cast<const float4*>(Os + (ty * RM + i) * L.ds + j0 + k);
 #pragma unroll
             for (int b = 0; b < 4; ++b) {
-              const float4 ww = *reinterpret_cast<const float4*>(Ks + (tx + 16 * b) * L.hs + k);
+              const float4 ww = *reinterpret_cast<const float4*>(Ks + (tx + 16 * b) * hs + k);
 #pragma unroll
               for (int i = 0; i < RM; ++i) {
                 acc[i][b] = fmaf(ov[i].x, ww.x, acc[i][b]);
@@ -619,15 +625,15 @@ int launch_tiny(const SimtPassArgs& a, cudaStream_t st) {
   }
 }
 
-template <int RM, int DVC>
-int launch_inst(const SimtPassArgs& a, int splits, cudaStream_t st) {
+template <int RM, int DVC, int HF>
+int launch_inst_hf(const SimtPassArgs& a, int splits, cudaStream_t st) {
   constexpr int BM = 16 * RM;
   const SimtSmemLayout L = simt_layout(BM, a.h, DVC);
   const size_t smem = (size_t)L.total * sizeof(float);
   if (smem > 227 * 1024) HOP_FAIL(HOP_ERR_BAD_SHAPE, "fp32 path: tile for H=%d Dr=%d needs %zu B of shared memory", a.h, a.dr, smem);
   // the merged rows + their scratch live in the probability tile: (BM/splits) * (ds + splits + 3) <= BM * PS
   while (splits > 1 && (BM % splits != 0 || (BM / splits) * (L.ds + splits + 3) > BM * PS)) splits >>= 1;
-  auto kern = hop_fwd_simt_kernel<RM, DVC>;
+  auto kern = hop_fwd_simt_kernel<RM, DVC, HF>;
   if (smem > 48 * 1024) HOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int grid = (a.n + BM - 1) / BM;
   cudaLaunchConfig_t cfg{};
@@ -642,6 +648,14 @@ int launch_inst(const SimtPassArgs& a, int splits, cudaStream_t st) {
   HOP_CUDA(cudaLaunchKernelEx(&cfg, kern, a, splits));
   HOP_LAUNCH_CHECK("hop_fwd_simt_kernel");
   return HOP_OK;
+}
+
+template <int RM, int DVC>
+int launch_inst(const SimtPassArgs& a, int splits, cudaStream_t st) {
+  if constexpr (RM == 4 && DVC == 1) {
+    if (a.h == 64 && !getenv("HOP_SIMT_NO_HF")) return launch_inst_hf<RM, DVC, 64>(a, splits, st);
+  }
+  return launch_inst_hf<RM, DVC, 0>(a, splits, st);
 }
 
 template <int RM>
