@@ -12,7 +12,10 @@ layer.kernel_path = "f16"
 xh, _ = bench.make_queries(w, n)
 xh = xh.contiguous().pin_memory()
 out = torch.empty((n, d)).pin_memory()
-for sched in [(1, 3, 3, 1), (1, 2, 4, 1), (1, 6, 1), 4]:
+SCHEDS = [(1, 3, 3, 1), (1, 2, 4, 1), (1, 6, 1), 4]
+if len(sys.argv) > 1:
+    SCHEDS = [tuple(float(v) for v in a.split(',')) for a in sys.argv[1:]]
+for sched in SCHEDS:
     ts, hs = [], []
     for i in range(12):
         torch.cuda.synchronize()
@@ -22,4 +25,4 @@ for sched in [(1, 3, 3, 1), (1, 2, 4, 1), (1, 6, 1), 4]:
         t1 = time.perf_counter()
         torch.cuda.synchronize()
         ts.append(round(e0.elapsed_time(e1), 3)); hs.append(round((t1 - t0) * 1e3, 3))
-    print(json.dumps({"chunks": sched, "device_ms": ts, "host_enqueue_ms": hs}), flush=True)
+    print(json.dumps({"chunks": sched, "device_ms_median": sorted(ts[2:])[len(ts[2:]) // 2], "device_ms": ts, "host_enqueue_ms": hs}), flush=True)
