@@ -39,6 +39,8 @@ WORKLOADS = {
     "sweep_p64k_d512": (16384, 65536, 512, 0),
     "sweep_p64k_d512_t1": (16384, 65536, 512, 1),
     "sweep_p256k_d512": (16384, 262144, 512, 0),
+    "sweep_p64k_d1024": (16384, 65536, 1024, 0),
+    "sweep_p64k_d1024_t1": (16384, 65536, 1024, 1),
     "ffhq32_layer": (2592, 512, 64, 0),       # one `hopfield` layer of FFHQ-32 (launch-bound; context only)
     "tiny": (1024, 4096, 64, 0),              # plumbing check
 }

@@ -82,7 +82,7 @@ int resolve_path(const hop_desc* d) {
   const bool tc_ok = tc_supported(d->d_assoc, d->d_v);
   if (d->path == HOP_PATH_TC_F16 || d->path == HOP_PATH_TC_BF16) {
     if (!tc_ok) {
-      set_error("tensor-core path is not built for H=%d Dv=%d (needs H == Dv in {64,128,256,512})", d->d_assoc, d->d_v);
+      set_error("tensor-core path is not built for H=%d Dv=%d (needs H == Dv in {64,128,256,512,1024})", d->d_assoc, d->d_v);
       return -HOP_ERR_UNSUPPORTED;
     }
     return d->path;

@@ -76,7 +76,14 @@ struct TcCfg {
   static constexpr int kKChunks = H / 64;                 // 64-wide K chunks of the Q / K^ tiles
   static constexpr int kBStages = DV > 128 ? DV / 128 : 1;  // ring stages of one read-out chunk (DV rows x 64 patterns)
   static constexpr int kBRows = DV / kBStages;            // rows per TMA box of the read-out operand
-  static constexpr int kQBytes = kKChunks * kChunkBytes;  // Q tile
+  // Query rows a CTA really owns.  H = 1024: a 128-row fp16 Q tile (256 KiB) does not fit shared memory, so the
+  // tile keeps 64 rows (8 KiB per 64-column chunk).  The MMAs stay M = 128: the A descriptor of chunk kc reads
+  // 16 KiB from q_smem + kc * 8 KiB, i.e. TMEM lanes 64..127 accumulate rows that belong to nobody (their operand
+  // bytes are the next chunk's / the ring's) and are never read back; their softmax warps only keep the barrier
+  // counts.  Half of the issued tensor work is thrown away -- the functional first form of this width.
+  static constexpr int kRows = H > 512 ? 64 : kTileM;
+  static constexpr int kQChunkBytes = kRows * 128;        // one 64-column chunk of the Q tile
+  static constexpr int kQBytes = kKChunks * kQChunkBytes; // Q tile
   static constexpr int kStages = (H >= 512) ? 6 : (H >= 256) ? 10 : 12;   // even: a 2-stage read-out chunk never wraps
   static constexpr int kBarBytes = 512;                   // mbarriers + TMEM slot
   static constexpr int kXchBytes = 2 * 2 * kTileM * 4;    // [parity][half][row] floats exchanged by a warp pair
@@ -321,7 +328,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
               ptx::tc_fence_after();
 #pragma unroll
               for (int c = 0; c < kKPerStage; ++c) {
-                const uint64_t ad = ptx::umma_desc_sw128(q_smem + (ks * kKPerStage + c) * kChunkBytes);
+                const uint64_t ad = ptx::umma_desc_sw128(q_smem + (ks * kKPerStage + c) * Cfg::kQChunkBytes);
                 const uint64_t bd = ptx::umma_desc_sw128(ring + s * kChunkBytes + c * 8192);
 #pragma unroll
                 for (int k = 0; k < 4; ++k)
@@ -385,7 +392,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
             const int s = it % Cfg::kStages;
             ptx::mbar_wait(full_bar(s), (it / Cfg::kStages) & 1);
             ptx::tc_fence_after();
-            const uint64_t ad = ptx::umma_desc_sw128(q_smem + kc * kChunkBytes);
+            const uint64_t ad = ptx::umma_desc_sw128(q_smem + kc * Cfg::kQChunkBytes);
             const uint64_t bd = ptx::umma_desc_sw128(ring + s * kChunkBytes);
 #pragma unroll
             for (int k = 0; k < 4; ++k)
@@ -450,8 +457,9 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
     int u = u_start, rg, t0, nt, seg_local = 0;
     while (seg_next(u, u_end, nt_total, rg, t0, nt)) {
     const long long row_tile = (long long)rg * kCluster + (long long)crank;   // (plain form: == blockIdx.x)
-    const long long grow = row_tile * kTileM + row;
-    const bool row_ok = grow < a.n;
+    const long long grow = row_tile * Cfg::kRows + row;
+    const bool live = row < Cfg::kRows;            // (H = 1024: TMEM lanes 64..127 hold no query row)
+    const bool row_ok = live && grow < a.n;
     // row of this thread inside the partial-result arrays
     const long long part_row = a.streamk
         ? ((long long)cid * a.sk_max_seg + seg_local) * (kCluster * kTileM) + (long long)crank * kTileM + row
@@ -462,7 +470,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
     {
       constexpr int kVec = (H + 127) / 128;       // float4 per lane
       constexpr int kRowsInFlight = H > 256 ? 2 : 4;
-      constexpr int kRowsPerWarp = kTileM / kSoftmaxWarps;
+      constexpr int kRowsPerWarp = Cfg::kRows / kSoftmaxWarps;
       const int sw = warp - 2;
       float4 w4[kVec], b4[kVec];
 #pragma unroll
@@ -480,7 +488,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         float4 xv[kRowsInFlight][kVec];
 #pragma unroll
         for (int u = 0; u < kRowsInFlight; ++u) {
-          const long long gr = row_tile * kTileM + sw * kRowsPerWarp + rr + u;
+          const long long gr = row_tile * Cfg::kRows + sw * kRowsPerWarp + rr + u;
 #pragma unroll
           for (int v = 0; v < kVec; ++v) {
             const int e = lane * 4 + v * 128;
@@ -491,7 +499,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
 #pragma unroll
         for (int u = 0; u < kRowsInFlight; ++u) {
           const int r = sw * kRowsPerWarp + rr + u;
-          const long long gr = row_tile * kTileM + r;
+          const long long gr = row_tile * Cfg::kRows + r;
           if (a.x_raw) {
             if (a.has_ln) {
               float s = 0.f;
@@ -528,7 +536,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
                 *reinterpret_cast<float4*>(a.qsave + gr * H + e) = xv[u][v];
               const uint32_t lo = pack16<kBf16>(xv[u][v].x * kLog2e, xv[u][v].y * kLog2e);
               const uint32_t hi = pack16<kBf16>(xv[u][v].z * kLog2e, xv[u][v].w * kLog2e);
-              const uint32_t addr = q_smem + (e >> 6) * kChunkBytes + sw128_off(r, (e & 63) >> 3) + ((e & 4) << 1);
+              const uint32_t addr = q_smem + (e >> 6) * Cfg::kQChunkBytes + sw128_off(r, (e & 63) >> 3) + ((e & 4) << 1);
               asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr), "r"(lo), "r"(hi) : "memory");
             }
           }
@@ -558,6 +566,11 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         ptx::mbar_wait(s_full(b), (gg >> 1) & 1);
         ptx::tc_fence_after();
         HOP_STRACE(1);
+        if (!live) {                         // whole warps (lane quarters 2, 3): stay in step, feed the arrival count
+          ptx::tc_fence_before();
+          arrive_issuer(p_full(b));
+          continue;
+        }
         const uint32_t s_addr = lane_base + b * kTileP + half * kHalfP;
 
         // this thread's 64 scores into registers (one TMEM round trip), then free the S buffer at once
@@ -656,6 +669,14 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         HOP_STRACE(6);
       }
 
+      if (!live) {                           // the Q tile may be rewritten only after the last MMA that reads it
+        const uint32_t lastd = g + nt - 1;
+        ptx::mbar_wait(p_empty(lastd & 1), (lastd >> 1) & 1);
+        ptx::tc_fence_after();
+        ptx::tc_fence_before();
+        g += nt;
+        continue;
+      }
       // ---- end of the pass: the pair combines (l, tmax, targ); slots of the other parity are idle
       const int pl = (g + nt - 1) & 1;
       st_shared_f32(xch_at(pl ^ 1, half, row), l);
@@ -699,7 +720,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
               dst[q4] = make_float4(__uint_as_float(o[4 * q4]), __uint_as_float(o[4 * q4 + 1]),
                                     __uint_as_float(o[4 * q4 + 2]), __uint_as_float(o[4 * q4 + 3]));
           }
-          const uint32_t base = q_smem + (c >> 1) * kChunkBytes;
+          const uint32_t base = q_smem + (c >> 1) * Cfg::kQChunkBytes;
 #pragma unroll
           for (int q4 = 0; q4 < 4; ++q4)
             st_shared_v4(base + sw128_off(row, (c & 1) * 4 + q4), pk[4 * q4], pk[4 * q4 + 1], pk[4 * q4 + 2],
@@ -929,7 +950,7 @@ int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
   k.retrieved = a.retrieved; k.qsave = a.qsave; k.lse = a.lse; k.argmax = a.argmax; k.rowmax = a.rowmax;
   k.pattern_offset = a.pattern_offset;
   auto* kern = hop_fwd_tc_kernel<H, DV, kBf16, kCluster, kPair>;
-  const int row_tiles = (a.n + kTileM - 1) / kTileM;
+  const int row_tiles = (a.n + Cfg::kRows - 1) / Cfg::kRows;
   const int row_groups = (row_tiles + kCluster - 1) / kCluster;
 
   // ---- stream-K form: one contiguous share of the (row group x tile) units per resident cluster
@@ -1033,7 +1054,10 @@ extern "C" int hop_sm100_debug_trace(long long* dst_host, int n) {
 }
 #endif
 
-bool tc_supported(int h, int dv) { return h == dv && (h == 64 || h == 128 || h == 256 || h == 512); }
+bool tc_supported(int h, int dv) { return h == dv && (h == 64 || h == 128 || h == 256 || h == 512 || h == 1024); }
+
+// query rows per CTA (TcCfg::kRows): the 1024-wide Q tile holds 64
+static inline int tc_rows(int d) { return d > 512 ? 64 : kTileM; }
 
 // read-out column chunks (gridDim.z): the O accumulator of one CTA holds at most 256 fp32 TMEM columns
 static inline int tc_dv_chunks(int d) { return d > 256 ? d / 256 : 1; }
@@ -1069,7 +1093,7 @@ int tc_choose_splits(int n, int p, int d, int update_steps) {
   }
   const int sms = num_sms();
   const int cl = tc_choose_cluster(n, d);
-  const int row_tiles = ((n + kTileM - 1) / kTileM + cl - 1) / cl * cl * tc_dv_chunks(d);
+  const int row_tiles = ((n + tc_rows(d) - 1) / tc_rows(d) + cl - 1) / cl * cl * tc_dv_chunks(d);
   const int nt_total = padded_patterns(p) / kTileP;
   const int chain = update_steps > 0 ? kMaxChainTilesUpdate : kMaxChainTilesReadout;
   const int min_splits = (nt_total + chain - 1) / chain;            // accuracy: bound the accumulation chain
@@ -1092,8 +1116,8 @@ int tc_choose_splits(int n, int p, int d, int update_steps) {
 // 0 | 1 forces it off / on for every D).  Measured (r01, P = 64k / 256k): D = 256 1174 -> 1220 / 1226 -> 1367
 // TFLOP/s; D = 128 and 64 are MUFU-bound and do not gain (824 -> 798, 440 -> 438).
 bool tc_use_pair(int n, int d) {
-  if (const char* e = getenv("HOP_TC_PAIR")) return atoi(e) != 0 && n > kTileM;
-  return n > kTileM && d >= 256;
+  if (const char* e = getenv("HOP_TC_PAIR")) return atoi(e) != 0 && n > tc_rows(d);
+  return n > tc_rows(d) && d >= 256;
 }
 
 // CTAs per cluster sharing the streamed operands through TMA multicast (knob: HOP_TC_CLUSTER = 1 | 2 | 4).
@@ -1101,7 +1125,7 @@ bool tc_use_pair(int n, int d) {
 // TFLOP/s at cluster 1 / 2 / 4, P=64k D=256), so the default stays 1.
 int tc_choose_cluster(int n, int d) {
   if (tc_use_pair(n, d)) return 2;
-  const int row_tiles = (n + kTileM - 1) / kTileM;
+  const int row_tiles = (n + tc_rows(d) - 1) / tc_rows(d);
   int want = 1;
   if (const char* e = getenv("HOP_TC_CLUSTER")) {
     const int c = atoi(e);
@@ -1124,6 +1148,7 @@ static size_t ws_for_splits(int splits, int n, int d) {
 // of one cluster stays within the accumulation-chain cap.
 static bool streamk_ok(int n, int p, int d, int update_steps) {
   if (update_steps != 0 || getenv("HOP_TC_SPLITS")) return false;
+  if (d > 512) return false;                 // (the partial-slot arithmetic assumes 128-row tiles)
   const int cl = tc_choose_cluster(n, d);
   if (cl > 2) return false;
   const int sms = num_sms();
@@ -1170,20 +1195,22 @@ static int launch_tc_one(const TcPassArgs& a, int splits, cudaStream_t st) {
       case 64: HOP_TC_DISPATCH(64, 64, true);
       case 128: HOP_TC_DISPATCH(128, 128, true);
       case 256: HOP_TC_DISPATCH(256, 256, true);
-      default: HOP_TC_DISPATCH(512, 256, true);
+      case 512: HOP_TC_DISPATCH(512, 256, true);
+      default: HOP_TC_DISPATCH(1024, 256, true);
     }
   }
   switch (a.h) {
     case 64: HOP_TC_DISPATCH(64, 64, false);
     case 128: HOP_TC_DISPATCH(128, 128, false);
     case 256: HOP_TC_DISPATCH(256, 256, false);
-    default: HOP_TC_DISPATCH(512, 256, false);
+    case 512: HOP_TC_DISPATCH(512, 256, false);
+    default: HOP_TC_DISPATCH(1024, 256, false);
   }
 #undef HOP_TC_DISPATCH
 }
 
 int launch_tc_forward(const TcPassArgs& a, cudaStream_t st) {
-  if (!tc_supported(a.h, a.dv)) HOP_FAIL(HOP_ERR_UNSUPPORTED, "tensor-core path needs H == Dv in {64,128,256,512}");
+  if (!tc_supported(a.h, a.dv)) HOP_FAIL(HOP_ERR_UNSUPPORTED, "tensor-core path needs H == Dv in {64,128,256,512,1024}");
   if (!a.retrieved) HOP_FAIL(HOP_ERR_BAD_ARG, "tensor-core forward: retrieved is NULL");
   const int splits = tc_choose_splits(a.n, a.p, a.h, a.update_steps);   // one count for every pass of this call
   if (!tc_multi_launch(a.p, a.h, a.update_steps)) return launch_tc_one(a, splits, st);

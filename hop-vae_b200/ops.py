@@ -182,7 +182,7 @@ def _(lookup, lookup_targets, ln_stored_w, ln_stored_b, ln_proj_w, ln_proj_b, wk
     tc = path in (cabi.PATH_TC_F16, cabi.PATH_TC_BF16)
     mk = lambda n: lookup.new_empty((n,), dtype=torch.int16)
     fold = (tc and wo is not None and bool(flags & cabi.F_OUT_PROJ) and wo.shape[0] == d_assoc == d_v
-            and d_assoc in (64, 128, 256, 512))
+            and d_assoc in (64, 128, 256, 512, 1024))
     return [lookup.new_empty((P, d_assoc)), lookup.new_empty((P, d_v)), mk(ppad * d_assoc if tc else 0),
             mk(ppad * d_assoc if tc and update_steps > 0 else 0), mk(ppad * d_v if tc else 0),
             mk(ppad * d_assoc if fold else 0)]

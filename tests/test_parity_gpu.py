@@ -421,6 +421,11 @@ TC_CASES = {
     "d512_ragged": (512, 1100, 257, 0),
     "d512_single_tile": (512, 640, 100, 0),
     "d512_T2": (512, 1024, 384, 2),
+    # D = 1024: 64-row Q tiles (the fp16 tile of 128 rows exceeds shared memory), four read-out column chunks
+    "d1024_p2k": (1024, 2048, 512, 0),
+    "d1024_ragged": (1024, 1100, 257, 0),
+    "d1024_single_tile": (1024, 640, 40, 0),
+    "d1024_T1": (1024, 1024, 192, 1),
 }
 
 
@@ -550,6 +555,7 @@ FULL_CASES = {
     "p64k_d512_T1": (65536, 512, 1, 128),
     # long accumulation chains: one launch per pass with bounded per-CTA chains (was 2.1e-3 on-chip)
     "p256k_d256_T1": (262144, 256, 1, 128),
+    "p64k_d1024_T0": (65536, 1024, 0, 64),
 }
 
 
