@@ -1,5 +1,5 @@
 """BASELINE config 5 on one GPU: the synthetic retrieval sweep P in {64k, 256k, 1M} x D in {256, 512} x T in {0, 1, 3}
-(D = 1024 is not on the tensor path), N = 16,384 query rows, f16 operands / f32 accumulate.
+(D = 1024 points through --points=P,1024,T;...), N = 16,384 query rows, f16 operands / f32 accumulate.
 
 Per point: device time of `HopfieldLayer.forward` (CUDA events, L2 flushed between steps), algorithmic TFLOP/s
 (2 N P [(2T+1) D + Dv]) against the measured bf16 peak, and PARITY at full size against the
