@@ -775,6 +775,421 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
   }
 }
 
+// ------------------------------------------------------------------------------------------------------------
+// 64-rows-per-CTA form for the wide widths (H = 512, 1024).  A tcgen05 CTA pair with M = 128: each CTA supplies 64
+// query rows and half of every streamed operand tile.  Measured layout (scripts/probes/umma_layout_probe.cu): the
+// accumulator row r of a CTA sits in TMEM lane r for columns n < N/2 and in lane r + 64 for n >= N/2, both in TMEM
+// columns [0, N/2) -- an N-wide accumulator costs N/2 TMEM columns.  So one CTA holds two 128-pattern score tiles
+// (64 columns each) AND a 512-column read-out (256 columns, two N = 256 instructions): no score recompute at
+// D = 512, two column chunks at D = 1024, and a Q tile of 64 KiB / 128 KiB.
+//   TMEM   S0 [0,64)  S1 [64,128)  O [128, 128 + DV/2);  P~ (16-bit pairs, 64 columns) over the score tile
+//   lane L = 32 (warp % 4) + lane: row L & 63, pattern half h = L >> 6; two threads per lane (sub = 0 | 1), 32
+//   score columns each.  The four threads of a row agree on the row maximum through shared memory; the read-out
+//   MMA takes P~ from TMEM and every lane reads ITS OWN lane's data (measured), so the 16 packed words of a thread
+//   are swapped with the partner lane (L ^ 64) through shared memory and stored into both lanes.
+template <int H, int DV>
+struct Tc64Cfg {
+  static constexpr int kPolyPeriod = HOP_POLY_D256;
+  static constexpr int kRows = 64;
+  static constexpr int kKChunks = H / 64;
+  static constexpr int kKStages = kKChunks / 2;             // ring stages of one K^ tile (2 x 8 KiB chunks per stage)
+  static constexpr int kQChunkBytes = kRows * 128;
+  static constexpr int kQBytes = kKChunks * kQChunkBytes;
+  static constexpr int kNH = DV / 256;                      // N = 256 read-out instructions per K step
+  static constexpr int kStages = H >= 1024 ? 5 : 8;
+  static constexpr int kBarBytes = 512;
+  static constexpr int kXmaxBytes = 2 * 2 * 128 * 4;        // [parity][sub][lane]
+  static constexpr int kXpBytes = 4 * 2 * 128 * 16;         // [16-byte chunk][sub][lane]
+  static constexpr int kSmemBytes = kQBytes + kStages * kChunkBytes + kBarBytes + kXmaxBytes + kXpBytes;
+  static constexpr uint32_t kTmemO = 128;
+  static_assert(DV % 256 == 0 && DV <= 512 && H % DV == 0 && kSmemBytes <= 232448, "TMEM / shared-memory budget");
+};
+
+__device__ __forceinline__ void ld_shared_v4(uint32_t addr, uint32_t& a, uint32_t& b, uint32_t& c, uint32_t& d) {
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "r"(addr) : "memory");
+}
+
+template <int H, int DV, bool kBf16>
+__global__ void __launch_bounds__(kThreads, 1)
+hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_vt,
+                    const TcKernelArgs a) {
+  using Cfg = Tc64Cfg<H, DV>;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t smem_base = ptx::smem_u32(smem_raw);
+  if ((smem_base & 1023u) != 0) __trap();
+  const uint32_t q_smem = smem_base;
+  const uint32_t ring = q_smem + Cfg::kQBytes;
+  const uint32_t bars = ring + Cfg::kStages * kChunkBytes;
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (Cfg::kStages + s); };
+  const uint32_t misc = bars + 16u * Cfg::kStages;
+  auto s_full = [&](int b) { return misc + 8u * b; };
+  auto p_full = [&](int b) { return misc + 32u + 8u * b; };
+  auto p_empty = [&](int b) { return misc + 48u + 8u * b; };
+  const uint32_t q_ready = misc + 64u;
+  const uint32_t tmem_slot = misc + 72u;
+  const uint32_t xmax = bars + Cfg::kBarBytes;
+  const uint32_t xp = xmax + Cfg::kXmaxBytes;
+  auto xmax_at = [&](int parity, int sub, int L) { return xmax + (uint32_t)((((parity * 2 + sub) * 128) + L) * 4); };
+  auto xp_at = [&](int c, int sub, int L) { return xp + (uint32_t)((((c * 2 + sub) * 128) + L) * 16); };
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t crank = ptx::cluster_ctarank();
+  constexpr uint32_t kArrivers = kSoftmaxThreads * 2;
+  const int split = blockIdx.y;
+  const int zoff = (int)blockIdx.z * DV;
+  const int nt_total = (a.p + kTileP - 1) / kTileP;
+  const int cid = (int)blockIdx.x / 2;
+  const int t0 = split * a.tiles_per_split;
+  const int nt = min(a.tiles_per_split, nt_total - t0);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < Cfg::kStages; ++s) { ptx::mbar_init(full_bar(s), 1); ptx::mbar_init(empty_bar(s), 1); }
+    for (int b = 0; b < 2; ++b) {
+      ptx::mbar_init(s_full(b), 1);
+      ptx::mbar_init(p_full(b), kArrivers); ptx::mbar_init(p_empty(b), 1);
+    }
+    ptx::mbar_init(q_ready, kArrivers);
+    ptx::fence_barrier_init();
+    ptx::prefetch_tmap(&tm_k); ptx::prefetch_tmap(&tm_vt);
+  }
+  if (warp == 0) {
+    __syncwarp();
+    ptx::tmem_alloc_pair(tmem_slot, kTmemCols); ptx::tmem_relinquish_pair();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::cluster_sync();
+  ptx::tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer (each CTA: its half of every tile)
+    if (ptx::elect_one()) {
+      uint32_t it = 0;
+      auto acquire = [&](uint32_t total_bytes) {
+        const int s = it % Cfg::kStages;
+        ptx::mbar_wait(empty_bar(s), ((it / Cfg::kStages) & 1) ^ 1);
+        if (crank == 0) ptx::mbar_arrive_expect_tx(full_bar(s), total_bytes);
+        return s;
+      };
+      auto load_k = [&](int tile) {
+        for (int ks = 0; ks < Cfg::kKStages; ++ks) {
+          const int s = acquire(2u * 2u * 8192u);
+          const uint32_t fb = ptx::map_to_cta(full_bar(s), 0);
+          for (int c = 0; c < 2; ++c)
+            ptx::tma_load_2d_pair(ring + s * kChunkBytes + c * 8192, &tm_k, fb, (ks * 2 + c) * 64,
+                                  tile * kTileP + (int)crank * 64);
+          ++it;
+        }
+      };
+      auto load_b = [&](int tile) {
+        for (int kc = 0; kc < 2; ++kc)
+          for (int nh = 0; nh < Cfg::kNH; ++nh) {
+            const int s = acquire(2u * 128u * 128u);
+            ptx::tma_load_2d_pair(ring + s * kChunkBytes, &tm_vt, ptx::map_to_cta(full_bar(s), 0),
+                                  tile * kTileP + kc * 64, zoff + nh * 256 + (int)crank * 128);
+            ++it;
+          }
+      };
+      load_k(t0);
+      for (int j = 0; j < nt; ++j) {
+        if (j + 1 < nt) load_k(t0 + j + 1);
+        load_b(t0 + j);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // -------------------------------------------------------------- MMA issuer (leader CTA, one thread)
+    if (crank == 0 && ptx::elect_one()) {
+      constexpr int fmt = kBf16 ? 1 : 0;
+      constexpr uint32_t idesc_qk = ptx::umma_idesc_f16(128, kTileP, fmt);
+      constexpr uint32_t idesc_pv = ptx::umma_idesc_f16(128, 256, fmt);
+      uint32_t it = 0;
+      ptx::mbar_wait_cluster(q_ready, 0);
+      ptx::tc_fence_after();
+      auto issue_qk = [&](uint32_t gg) {
+        const int b = gg & 1;
+        for (int ks = 0; ks < Cfg::kKStages; ++ks) {
+          const int s = it % Cfg::kStages;
+          ptx::mbar_wait_cluster(full_bar(s), (it / Cfg::kStages) & 1);
+          ptx::tc_fence_after();
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            const uint64_t ad = ptx::umma_desc_sw128(q_smem + (ks * 2 + c) * Cfg::kQChunkBytes);
+            const uint64_t bd = ptx::umma_desc_sw128(ring + s * kChunkBytes + c * 8192);
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              ptx::umma2_f16_ss(tmem_base + b * 64, ad + 2 * k, bd + 2 * k, idesc_qk, (ks | c | k) != 0);
+          }
+          ptx::umma2_commit_both(empty_bar(s));
+          ++it;
+        }
+        ptx::umma2_commit_both(s_full(b));
+      };
+      issue_qk(0);
+      for (int j = 0; j < nt; ++j) {
+        if (j + 1 < nt) issue_qk(j + 1);
+        const int b = j & 1;
+        ptx::mbar_wait_cluster(p_full(b), (j >> 1) & 1);
+        ptx::tc_fence_after();
+        for (int kc = 0; kc < 2; ++kc)
+          for (int nh = 0; nh < Cfg::kNH; ++nh) {
+            const int s = it % Cfg::kStages;
+            ptx::mbar_wait_cluster(full_bar(s), (it / Cfg::kStages) & 1);
+            ptx::tc_fence_after();
+            const uint32_t at = tmem_base + b * 64 + kc * 32;
+            const uint64_t bd = ptx::umma_desc_sw128(ring + s * kChunkBytes);
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              ptx::umma2_f16_ts(tmem_base + Cfg::kTmemO + nh * 128, at + 8 * k, bd + 2 * k, idesc_pv, (j | kc | k) != 0);
+            ptx::umma2_commit_both(empty_bar(s));
+            ++it;
+          }
+        ptx::umma2_commit_both(p_empty(b));
+      }
+    }
+    __syncwarp();
+  } else {
+    // ------------------------------------------------------ softmax / epilogue
+    const int wq = warp & 3;                      // TMEM lane quarter
+    const int sub = (warp - 2) >> 2;              // which 32 of the lane's 64 score columns
+    const int L = wq * 32 + lane;                 // TMEM lane
+    const int h = L >> 6, row = L & 63;           // pattern half of the tile, query row of the CTA
+    const uint32_t lane_base = tmem_base + ((uint32_t)(wq * 32) << 16);
+    const uint32_t grp_bar = 1 + (wq & 1);        // the four warps that share 32 rows (128 threads)
+    const float qscale = a.beta;
+    const long long row_tile = (long long)cid * 2 + (long long)crank;
+    const long long grow = row_tile * Cfg::kRows + row;
+    const bool row_ok = grow < a.n;
+    const long long part_row = (long long)split * a.n + grow;
+    auto arrive_issuer = [&](uint32_t bar) { ptx::mbar_arrive_cluster(ptx::map_to_cta(bar, 0)); };
+
+    // ---- Q tile: one warp per row, 2 rows in flight; LN_q + beta, fp32 qsave, 16-bit swizzled smem
+    {
+      constexpr int kVec = (H + 127) / 128;
+      constexpr int kRowsInFlight = 2;
+      constexpr int kRowsPerWarp = Cfg::kRows / kSoftmaxWarps;
+      const int sw = warp - 2;
+      float4 w4[kVec], b4[kVec];
+#pragma unroll
+      for (int v = 0; v < kVec; ++v) {
+        const int e = lane * 4 + v * 128;
+        w4[v] = make_float4(1.f, 1.f, 1.f, 1.f);
+        b4[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (a.x_raw && a.has_ln) {
+          if (a.lnq_w) w4[v] = *reinterpret_cast<const float4*>(a.lnq_w + e);
+          if (a.lnq_b) b4[v] = *reinterpret_cast<const float4*>(a.lnq_b + e);
+        }
+      }
+      const float* src = a.x_raw ? a.x_raw : a.qs;
+      for (int rr = 0; rr < kRowsPerWarp; rr += kRowsInFlight) {
+        float4 xv[kRowsInFlight][kVec];
+#pragma unroll
+        for (int u = 0; u < kRowsInFlight; ++u) {
+          const long long gr = row_tile * Cfg::kRows + sw * kRowsPerWarp + rr + u;
+#pragma unroll
+          for (int v = 0; v < kVec; ++v) {
+            const int e = lane * 4 + v * 128;
+            xv[u][v] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (gr < a.n) xv[u][v] = __ldg(reinterpret_cast<const float4*>(src + gr * H + e));
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < kRowsInFlight; ++u) {
+          const int r = sw * kRowsPerWarp + rr + u;
+          const long long gr = row_tile * Cfg::kRows + r;
+          if (a.x_raw) {
+            if (a.has_ln) {
+              float s = 0.f;
+#pragma unroll
+              for (int v = 0; v < kVec; ++v) s += (xv[u][v].x + xv[u][v].y) + (xv[u][v].z + xv[u][v].w);
+              const float mean = warp_sum(s) * (1.f / H);
+              float q = 0.f;
+#pragma unroll
+              for (int v = 0; v < kVec; ++v) {
+                xv[u][v].x -= mean; xv[u][v].y -= mean; xv[u][v].z -= mean; xv[u][v].w -= mean;
+                q += xv[u][v].x * xv[u][v].x + xv[u][v].y * xv[u][v].y + xv[u][v].z * xv[u][v].z +
+                     xv[u][v].w * xv[u][v].w;
+              }
+              const float rstd = rsqrtf(warp_sum(q) * (1.f / H) + a.ln_eps);
+#pragma unroll
+              for (int v = 0; v < kVec; ++v) {
+                xv[u][v].x = xv[u][v].x * rstd * w4[v].x + b4[v].x; xv[u][v].y = xv[u][v].y * rstd * w4[v].y + b4[v].y;
+                xv[u][v].z = xv[u][v].z * rstd * w4[v].z + b4[v].z; xv[u][v].w = xv[u][v].w * rstd * w4[v].w + b4[v].w;
+              }
+            }
+#pragma unroll
+            for (int v = 0; v < kVec; ++v) {
+              xv[u][v].x *= qscale; xv[u][v].y *= qscale; xv[u][v].z *= qscale; xv[u][v].w *= qscale;
+            }
+          }
+#pragma unroll
+          for (int v = 0; v < kVec; ++v) {
+            const int e = lane * 4 + v * 128;
+            if (a.qsave && gr < a.n && t0 == 0 && blockIdx.z == 0)
+              *reinterpret_cast<float4*>(a.qsave + gr * H + e) = xv[u][v];
+            const uint32_t lo = pack16<kBf16>(xv[u][v].x * kLog2e, xv[u][v].y * kLog2e);
+            const uint32_t hi = pack16<kBf16>(xv[u][v].z * kLog2e, xv[u][v].w * kLog2e);
+            const uint32_t addr = q_smem + (e >> 6) * Cfg::kQChunkBytes + sw128_off(r, (e & 63) >> 3) + ((e & 4) << 1);
+            asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr), "r"(lo), "r"(hi) : "memory");
+          }
+        }
+      }
+    }
+    ptx::fence_proxy_async_smem();
+    arrive_issuer(q_ready);
+
+    float m_run = -INFINITY, l = 0.f, tmax = -INFINITY;
+    int targ = 0;
+    constexpr int kOGroups = DV / 4 / 32;          // 32-column TMEM groups of O handled by this thread
+    const int og0 = sub * kOGroups;
+    for (int j = 0; j < nt; ++j) {
+      const int b = j & 1;
+      const int col0 = (t0 + j) * kTileP + h * 64 + sub * 32;   // global pattern index of this thread's column 0
+      const int valid = a.p - col0;
+      ptx::mbar_wait(s_full(b), (j >> 1) & 1);
+      ptx::tc_fence_after();
+      uint32_t v[32];
+      ptx::tmem_ld_x32(lane_base + b * 64 + sub * 32, v);
+      ptx::tmem_wait_ld();
+      if (valid < 32) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i)
+          if (i >= valid) v[i] = __float_as_uint(-INFINITY);
+      }
+      float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+      for (int i = 0; i < 32; i += 8) {
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          mx[u] = fmaxf(mx[u], fmaxf(__uint_as_float(v[i + 2 * u]), __uint_as_float(v[i + 2 * u + 1])));
+      }
+      const float hmax = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+      st_shared_f32(xmax_at(b, sub, L), hmax);
+      if (hmax > tmax) {
+        int idx = 31;
+#pragma unroll
+        for (int i = 31; i >= 0; --i) idx = (__uint_as_float(v[i]) == hmax) ? i : idx;
+        tmax = hmax;
+        targ = col0 + idx;
+      }
+      ptx::named_bar_sync(grp_bar, 128);
+      const float cmax = fmaxf(fmaxf(ld_shared_f32(xmax_at(b, 0, row)), ld_shared_f32(xmax_at(b, 1, row))),
+                               fmaxf(ld_shared_f32(xmax_at(b, 0, row + 64)), ld_shared_f32(xmax_at(b, 1, row + 64))));
+      const bool need = cmax > m_run + kRescaleThreshold;
+      const bool any_need = __any_sync(0xffffffffu, need);
+      const float m_old = m_run;
+      if (any_need) m_run = fmaxf(m_run, cmax);
+
+      float ls[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        const float xs = __uint_as_float(v[i]) - m_run;
+        const bool poly = Cfg::kPolyPeriod > 0 && (i % (Cfg::kPolyPeriod > 0 ? Cfg::kPolyPeriod : 1)) == 0;
+        v[i] = __float_as_uint(poly ? ptx::ex2_poly(xs) : ptx::ex2(xs));
+      }
+      uint32_t pk[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const float p0 = __uint_as_float(v[2 * i]), p1 = __uint_as_float(v[2 * i + 1]);
+        ls[i & 3] += p0 + p1;
+        pk[i] = pack16<kBf16>(p0, p1);
+      }
+#pragma unroll
+      for (int c = 0; c < 4; ++c) st_shared_v4(xp_at(c, sub, L), pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+      if (any_need && j > 0) {
+        const uint32_t pg = j - 1;
+        ptx::mbar_wait(p_empty(pg & 1), (pg >> 1) & 1);   // read-out MMA of the previous tile done
+        ptx::tc_fence_after();
+        const float f = ptx::ex2(m_old - m_run);
+        l *= f;
+#pragma unroll 1
+        for (int c = og0; c < og0 + kOGroups; ++c) {
+          uint32_t o[32];
+          ptx::tmem_ld_x32(lane_base + Cfg::kTmemO + c * 32, o);
+          ptx::tmem_wait_ld();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * f);
+          ptx::tmem_st_x32(lane_base + Cfg::kTmemO + c * 32, o);
+        }
+      }
+      ptx::named_bar_sync(grp_bar, 128);
+      uint32_t pw[16];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) ld_shared_v4(xp_at(c, sub, L ^ 64), pw[4 * c], pw[4 * c + 1], pw[4 * c + 2], pw[4 * c + 3]);
+      // P~ row of this lane: patterns 64 h' + 32 sub' + i -> column 32 h' + 16 sub' + i / 2
+      ptx::tmem_st_x16(lane_base + b * 64 + h * 32 + sub * 16, pk);
+      ptx::tmem_st_x16(lane_base + b * 64 + (h ^ 1) * 32 + sub * 16, pw);
+      l += (ls[0] + ls[1]) + (ls[2] + ls[3]);
+      ptx::tmem_wait_st();
+      ptx::tc_fence_before();
+      arrive_issuer(p_full(b));
+    }
+
+    // ---- end of the pass: the four threads of a row combine (l, tmax, targ) in pattern order
+    ptx::named_bar_sync(grp_bar, 128);             // every P~ word of the last tile has been read
+    st_shared_v4(xp_at(0, sub, L), __float_as_uint(l), __float_as_uint(tmax), (uint32_t)targ, 0u);
+    ptx::named_bar_sync(grp_bar, 128);
+    float l_tot = 0.f, best = -INFINITY;
+    int best_arg = 0;
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh)
+#pragma unroll
+      for (int ss = 0; ss < 2; ++ss) {
+        uint32_t w0, w1, w2, w3;
+        ld_shared_v4(xp_at(0, ss, row + 64 * hh), w0, w1, w2, w3);
+        l_tot += __uint_as_float(w0);
+        const float om = __uint_as_float(w1);
+        if (om > best) { best = om; best_arg = (int)w2; }    // pattern order: ties keep the lowest index
+      }
+    const uint32_t last = nt - 1;
+    ptx::mbar_wait(p_empty(last & 1), (last >> 1) & 1);
+    ptx::tc_fence_after();
+    const float inv = 1.f / l_tot;
+    float* o_row = (a.splits > 1) ? a.part_o + part_row * a.dv_total : a.retrieved + grow * a.dv_total;
+    const float osc = (a.splits > 1) ? inv : inv * a.out_scale;
+#pragma unroll 1
+    for (int c = og0; c < og0 + kOGroups; ++c) {
+      uint32_t o[32];
+      ptx::tmem_ld_x32(lane_base + Cfg::kTmemO + c * 32, o);
+      ptx::tmem_wait_ld();
+      if (row_ok) {
+        const int tcol = c * 32;                               // TMEM column of O: instruction nh, column jj of its half
+        const int ocol = zoff + (tcol >> 7) * 256 + h * 128 + (tcol & 127);
+        float4* dst = reinterpret_cast<float4*>(o_row + ocol);
+        const float4* bia = (a.bias && a.splits == 1) ? reinterpret_cast<const float4*>(a.bias + ocol) : nullptr;
+#pragma unroll
+        for (int q4 = 0; q4 < 8; ++q4) {
+          float4 r = make_float4(__uint_as_float(o[4 * q4]) * osc, __uint_as_float(o[4 * q4 + 1]) * osc,
+                                 __uint_as_float(o[4 * q4 + 2]) * osc, __uint_as_float(o[4 * q4 + 3]) * osc);
+          if (bia) { const float4 bb = __ldg(bia + q4); r.x += bb.x; r.y += bb.y; r.z += bb.z; r.w += bb.w; }
+          dst[q4] = r;
+        }
+      }
+    }
+    if (row_ok && h == 0 && sub == 0 && blockIdx.z == 0) {
+      const float lse = kLn2 * (m_run + ptx::lg2(l_tot));
+      if (a.splits > 1) {
+        a.part_lse[part_row] = lse; a.part_max[part_row] = best * kLn2; a.part_arg[part_row] = best_arg + a.pattern_offset;
+      } else {
+        if (a.lse) a.lse[grow] = lse;
+        if (a.rowmax) a.rowmax[grow] = best * kLn2;
+        if (a.argmax) a.argmax[grow] = best_arg + a.pattern_offset;
+      }
+    }
+    ptx::tc_fence_before();
+  }
+
+  __syncthreads();
+  ptx::cluster_sync();
+  if (warp == 0) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc_pair(tmem_base, kTmemCols);
+  }
+}
+
 // Combine `splits` partial results of one row (flash-decoding merge): weights exp(lse_s - lse).
 template <int D>
 __global__ void tc_combine_kernel(int n, int splits, const float* __restrict__ part_o,
@@ -1045,6 +1460,60 @@ int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
   return HOP_OK;
 }
 
+// 64-rows-per-CTA pair form (hop_fwd_tc64_kernel): plain grid (row pairs x pattern splits x column chunks), T = 0
+template <int H, int DV, bool kBf16>
+int launch_h64(const TcPassArgs& a, int splits, cudaStream_t st) {
+  using Cfg = Tc64Cfg<H, DV>;
+  const int ppad = padded_patterns(a.p);
+  if (a.update_steps > 0) HOP_FAIL(HOP_ERR_UNSUPPORTED, "the 64-row form runs retrieve updates as separate launches (internal)");
+  CUtensorMap tk, tvt;
+  HOP_TRY(make_map(&tk, a.k16, ppad, H, kTileP / 2, a.bf16));     // this CTA's 64 patterns of a K^ chunk
+  HOP_TRY(make_map(&tvt, a.vt16, a.dv, ppad, 128, a.bf16));       // this CTA's 128 rows of an N = 256 read-out chunk
+  TcKernelArgs k{};
+  k.x_raw = a.x_raw; k.lnq_w = a.lnq_w; k.lnq_b = a.lnq_b; k.ln_eps = a.ln_eps; k.has_ln = a.has_ln; k.beta = a.beta;
+  k.qs = a.qs; k.bias = a.bias; k.n = a.n; k.p = a.p; k.update_steps = 0;
+  k.dv_total = a.dv; k.out_scale = a.out_scale;
+  const int nt_total = ppad / kTileP;
+  k.tiles_per_split = (nt_total + splits - 1) / splits;
+  k.splits = (nt_total + k.tiles_per_split - 1) / k.tiles_per_split;
+  k.retrieved = a.retrieved; k.qsave = a.qsave; k.lse = a.lse; k.argmax = a.argmax; k.rowmax = a.rowmax;
+  k.pattern_offset = a.pattern_offset;
+  if (k.splits > 1) {
+    const size_t need = ws_for_splits_fwd(splits, a.n, a.dv);
+    if (!a.ws || a.ws_bytes < need)
+      HOP_FAIL(HOP_ERR_WORKSPACE, "tensor-core forward needs %zu workspace bytes for %d pattern splits, %zu given", need,
+               k.splits, a.ws_bytes);
+    char* w = static_cast<char*>(a.ws);
+    const size_t rows = (size_t)splits * a.n;
+    k.part_o = reinterpret_cast<float*>(w); w += round_up_sz(rows * a.dv * sizeof(float), 256);
+    k.part_lse = reinterpret_cast<float*>(w); w += round_up_sz(rows * sizeof(float), 256);
+    k.part_max = reinterpret_cast<float*>(w); w += round_up_sz(rows * sizeof(float), 256);
+    k.part_arg = reinterpret_cast<int32_t*>(w);
+  }
+  auto* kern = hop_fwd_tc64_kernel<H, DV, kBf16>;
+  HOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+  const int row_tiles = (a.n + Cfg::kRows - 1) / Cfg::kRows;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((row_tiles + 1) / 2 * 2, k.splits, a.dv / DV);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  HOP_CUDA(cudaLaunchKernelEx(&cfg, kern, tk, tvt, k));
+  HOP_LAUNCH_CHECK("hop_fwd_tc64_kernel");
+  if (k.splits > 1) {
+    const int threads = 256, rows_per_block = threads / 32;
+    tc_combine_kernel<H><<<(a.n + rows_per_block - 1) / rows_per_block, threads, 0, st>>>(
+        a.n, k.splits, k.part_o, k.part_lse, k.part_max, k.part_arg, a.bias, a.out_scale, a.retrieved, a.lse, a.argmax,
+        a.rowmax);
+    HOP_LAUNCH_CHECK("tc_combine_kernel");
+  }
+  return HOP_OK;
+}
+
 }  // namespace
 
 #ifdef HOP_TC_TRACE
@@ -1056,11 +1525,20 @@ extern "C" int hop_sm100_debug_trace(long long* dst_host, int n) {
 
 bool tc_supported(int h, int dv) { return h == dv && (h == 64 || h == 128 || h == 256 || h == 512 || h == 1024); }
 
-// query rows per CTA (TcCfg::kRows): the 1024-wide Q tile holds 64
-static inline int tc_rows(int d) { return d > 512 ? 64 : kTileM; }
+// D >= 512 runs the 64-rows-per-CTA pair form (hop_fwd_tc64_kernel); knob HOP_TC_HALFM = 0 keeps the 128-row
+// kernel with its recomputed score tiles (D = 512) / discarded half-MMAs (D = 1024) for comparison.
+static inline bool tc_halfm(int d) {
+  if (d < 512) return false;
+  const char* e = getenv("HOP_TC_HALFM");
+  return !(e && atoi(e) == 0);
+}
 
-// read-out column chunks (gridDim.z): the O accumulator of one CTA holds at most 256 fp32 TMEM columns
-static inline int tc_dv_chunks(int d) { return d > 256 ? d / 256 : 1; }
+// query rows per CTA: 64 in the pair form above and under the 1024-wide Q tile of the 128-row kernel (TcCfg::kRows)
+static inline int tc_rows(int d) { return (tc_halfm(d) || d > 512) ? 64 : kTileM; }
+
+// read-out column chunks (gridDim.z): the O accumulator of one CTA holds at most 256 fp32 TMEM columns -- 256
+// read-out columns in the 128-row kernel, 512 in the 64-row pair form
+static inline int tc_dv_chunks(int d) { return tc_halfm(d) ? d / 512 : (d > 256 ? d / 256 : 1); }
 
 // Retrieve updates run as one launch per pass (state through the fp32 workspace buffers, every pass free to
 // split the pattern axis) instead of on-chip in one persistent launch.  Always at D = 512 (a CTA holds 256 of
@@ -1076,7 +1554,7 @@ constexpr int kMaxChainTilesUpdate = 256;    // pattern tiles one CTA accumulate
 constexpr int kMaxChainTilesReadout = 512;   // ... when T = 0 (errors are not amplified)
 static inline bool tc_multi_launch(int p, int d, int update_steps) {
   if (update_steps <= 0) return false;
-  if (tc_dv_chunks(d) > 1) return true;
+  if (d >= 512) return true;
   if (const char* e = getenv("HOP_TC_MULTI")) return atoi(e) != 0;
   return padded_patterns(p) / kTileP > kMaxTilesOnChipUpdates;
 }
@@ -1116,6 +1594,7 @@ int tc_choose_splits(int n, int p, int d, int update_steps) {
 // 0 | 1 forces it off / on for every D).  Measured (r01, P = 64k / 256k): D = 256 1174 -> 1220 / 1226 -> 1367
 // TFLOP/s; D = 128 and 64 are MUFU-bound and do not gain (824 -> 798, 440 -> 438).
 bool tc_use_pair(int n, int d) {
+  if (tc_halfm(d)) return true;
   if (const char* e = getenv("HOP_TC_PAIR")) return atoi(e) != 0 && n > tc_rows(d);
   return n > tc_rows(d) && d >= 256;
 }
@@ -1148,7 +1627,7 @@ static size_t ws_for_splits(int splits, int n, int d) {
 // of one cluster stays within the accumulation-chain cap.
 static bool streamk_ok(int n, int p, int d, int update_steps) {
   if (update_steps != 0 || getenv("HOP_TC_SPLITS")) return false;
-  if (d > 512) return false;                 // (the partial-slot arithmetic assumes 128-row tiles)
+  if (d > 512 || tc_halfm(d)) return false;  // (the partial-slot arithmetic assumes 128-row tiles)
   const int cl = tc_choose_cluster(n, d);
   if (cl > 2) return false;
   const int sms = num_sms();
@@ -1181,6 +1660,10 @@ size_t tc_forward_workspace(int n, int p, int d, int update_steps) {
 }
 
 static int launch_tc_one(const TcPassArgs& a, int splits, cudaStream_t st) {
+  if (tc_halfm(a.h)) {
+    if (a.h == 512) return a.bf16 ? launch_h64<512, 512, true>(a, splits, st) : launch_h64<512, 512, false>(a, splits, st);
+    return a.bf16 ? launch_h64<1024, 512, true>(a, splits, st) : launch_h64<1024, 512, false>(a, splits, st);
+  }
   const int cl = tc_choose_cluster(a.n, a.h);
   const bool pair = tc_use_pair(a.n, a.h);
 #define HOP_TC_DISPATCH(HH, DVC, BF)                                            \
