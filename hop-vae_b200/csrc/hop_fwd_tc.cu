@@ -62,6 +62,9 @@ __device__ long long g_trace[kTraceRoles * kTraceTiles * kTraceEvents];
 #ifndef HOP_POLY_D128
 #define HOP_POLY_D128 4
 #endif
+#ifndef HOP_TC64_STAGES_512
+#define HOP_TC64_STAGES_512 8   // ring stages of the 64-row pair kernel at H = 512 (9 still fits)
+#endif
 #ifndef HOP_POLY_D64
 #define HOP_POLY_D64 4
 #endif
@@ -796,7 +799,7 @@ struct Tc64Cfg {
   static constexpr int kQChunkBytes = kRows * 128;
   static constexpr int kQBytes = kKChunks * kQChunkBytes;
   static constexpr int kNH = DV / 256;                      // N = 256 read-out instructions per K step
-  static constexpr int kStages = H >= 1024 ? 5 : 8;
+  static constexpr int kStages = H >= 1024 ? 5 : HOP_TC64_STAGES_512;
   static constexpr int kBarBytes = 512;
   static constexpr int kXmaxBytes = 2 * 2 * 128 * 4;        // [parity][sub][lane]
   static constexpr int kXpBytes = 4 * 2 * 128 * 16;         // [16-byte chunk][sub][lane]
