@@ -402,6 +402,54 @@ def test_pattern_sharded_merge_single_gpu(hf, G):
     assert rel_l2(lse, torch.logsumexp(s, -1)) < 1e-5
 
 
+@pytest.mark.parametrize("D", [256, 512])
+def test_pattern_sharded_merge_single_gpu_tensor_core(hf, D):
+    """Same on the tcgen05 path (D = 512: the 64-rows-per-CTA pair kernel): per-shard (retrieved, lse, row max,
+    offset nearest-pattern index) from the fused forward + the library's LSE merge == unsharded oracle."""
+    impl = hf._impl
+    G, P, N = 2, 2048, 300
+    kw = dict(input_size=D, quantity=P, disable_out_projection=True, **STATIC)
+    ref = randomize_(O.HopfieldLayer(**kw), 71, 1.0)
+    g = torch.Generator().manual_seed(72)
+    with torch.no_grad():
+        ref.lookup_weights.copy_(torch.randn(1, P, D, generator=g))
+    dut = hf.HopfieldLayer(**kw)
+    dut.load_state_dict(ref.state_dict())
+    dut = dut.cuda()
+    idx = torch.randint(0, P, (N,), generator=g)
+    x = ref.lookup_weights[0, idx].detach() + 0.5 * torch.randn(N, D, generator=g)
+    with torch.no_grad():
+        want, _, scores, _ = ref(x[None], return_details=True)
+    spec = dut.spec()
+    pack = dut.param_pack()
+    per = P // G
+    path = impl.cabi.PATH_TC_F16
+    outs, lses, maxs, args = [], [], [], []
+    with torch.no_grad():
+        for gidx in range(G):
+            sl = slice(gidx * per, (gidx + 1) * per)
+            pats = impl.prepare_patterns_op(pack["lookup"][sl].contiguous(), None, pack["ln_stored_w"],
+                                            pack["ln_stored_b"], pack["ln_proj_w"], pack["ln_proj_b"], None, None,
+                                            pack["wv"], pack["bv"], None, spec.flags, path,
+                                            spec.d_assoc, spec.d_v, 0, spec.ln_eps)
+            res = impl.retrieve_op(x.cuda(), *pats, pack["ln_state_w"], pack["ln_state_b"], None, None, None, None,
+                                   spec.flags, path, spec.d_in, spec.d_out, 0, spec.beta, spec.ln_eps, gidx * per)
+            outs.append(res[1]); lses.append(res[3]); args.append(res[4]); maxs.append(res[5])
+        lse_all, max_all, arg_all = torch.stack(lses), torch.stack(maxs), torch.stack(args)
+        total = torch.zeros_like(outs[0])
+        for gidx in range(G):
+            from hop_vae_b200.ops import merge_shards
+            lse, arg = merge_shards(outs[gidx], lse_all, max_all, arg_all, gidx)
+            total += outs[gidx]
+    assert rel_l2(total, want[0]) < REL_L2_BAR
+    s = scores.reshape(N, P)
+    top2 = s.topk(2, dim=-1).values
+    decided = (top2[:, 0] - top2[:, 1]) > 2e-2
+    assert decided.float().mean() > 0.5
+    assert torch.equal(arg.cpu().long()[decided], s.argmax(-1)[decided])
+    assert (lse.cpu() - torch.logsumexp(s, -1)).abs().max() < 2e-2
+
+
 # --------------------------------------------------------------------------- tensor-core (tcgen05) path
 TC_CASES = {
     # name: (D, P, rows, T)
