@@ -17,6 +17,10 @@
 //               shared memory + a 64-thread named barrier, then each half does ex2, the 16-bit P~
 //               pack into swizzled shared memory and half of every O-column job (lazy rescale,
 //               epilogue, next pass' Q tile).
+//
+// Two kernels: hop_fwd_tc_kernel (128 query rows per CTA; D <= 256, and D >= 512 under HOP_TC_HALFM=0) and
+// hop_fwd_tc64_kernel (64 rows per CTA under M = 128 pair MMAs, whose accumulator layout fits a 512-column
+// read-out next to the score tiles; D = 512 and 1024).
 #include <cuda.h>
 
 #include <cstdlib>

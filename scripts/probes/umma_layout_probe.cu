@@ -129,7 +129,7 @@ __global__ void __launch_bounds__(128, 1) probe_layout(int mode, uint32_t* out /
 }
 
 // issue rate: `reps` x 4 MMAs (N = 256, K = 16 each) on resident operands, clock64 around them
-__global__ void __launch_bounds__(128, 1) probe_rate(int pair, int m, int reps, long long* cycles) {
+__global__ void __launch_bounds__(128, 1) probe_rate(int pair, int m, int n, int reps, long long* cycles) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const uint32_t bar = ptx::smem_u32(smem + 49152), slot = bar + 16;
   const uint32_t crank = ptx::cluster_ctarank();
@@ -149,7 +149,7 @@ __global__ void __launch_bounds__(128, 1) probe_rate(int pair, int m, int reps, 
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(slot));
   if (warp == 1 && ptx::elect_one() && (!pair || crank == 0)) {
-    const uint32_t idesc = ptx::umma_idesc_f16(m, 256, 0);
+    const uint32_t idesc = ptx::umma_idesc_f16(m, n, 0);
     const uint64_t ad = ptx::umma_desc_sw128(ptx::smem_u32(smem)), bd = ptx::umma_desc_sw128(ptx::smem_u32(smem + 16384));
     const long long t0 = clock64();
     for (int r = 0; r < reps; ++r) {
@@ -242,9 +242,10 @@ int main() {
   }
   // rates
   struct R { int pair, m; const char* name; } rs[4] = {{1, 256, "pair M=256"}, {1, 128, "pair M=128"}, {0, 128, "single M=128"}, {0, 64, "single M=64"}};
+  for (int n : {256, 128})
   for (auto& r : rs) {
     int reps = 4000;
-    void* args[] = {&r.pair, &r.m, &reps, &d_cyc};
+    void* args[] = {&r.pair, &r.m, &n, &reps, &d_cyc};
     CK(cudaMemset(d_cyc, 0, 2 * sizeof(long long)));
     int rc = launch((void*)probe_rate, 2, smem, args);
     cudaError_t e = cudaDeviceSynchronize();
@@ -252,8 +253,8 @@ int main() {
     long long c[2];
     CK(cudaMemcpy(c, d_cyc, sizeof(c), cudaMemcpyDeviceToHost));
     const double per_mma = (double)c[0] / (reps * 4.0);
-    const double flops_per_sm = 2.0 * r.m * 256 * 16 / (r.pair ? 2.0 : 1.0);   // per MMA, per SM involved
-    printf("rate %-13s N=256 K=16: %.1f cycles / MMA, %.0f FLOP / cycle / SM\n", r.name, per_mma, flops_per_sm / per_mma);
+    const double flops_per_sm = 2.0 * r.m * n * 16 / (r.pair ? 2.0 : 1.0);   // per MMA, per SM involved
+    printf("rate %-13s N=%d K=16: %.1f cycles / MMA, %.0f FLOP / cycle / SM\n", r.name, n, per_mma, flops_per_sm / per_mma);
   }
   return 0;
 }

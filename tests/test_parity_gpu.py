@@ -464,12 +464,12 @@ TC_CASES = {
     "d64_T1": (64, 640, 384, 1),
     "d128_T3": (128, 512, 256, 3),
     "d256_T1": (256, 1024, 256, 1),
-    # D = 512: the read-out is cut into two 256-column chunks (gridDim.z), updates run as separate launches
+    # D = 512: the 64-rows-per-CTA pair kernel (one 512-column read-out), updates run as separate launches
     "d512_p2k": (512, 2048, 512, 0),
     "d512_ragged": (512, 1100, 257, 0),
     "d512_single_tile": (512, 640, 100, 0),
     "d512_T2": (512, 1024, 384, 2),
-    # D = 1024: 64-row Q tiles (the fp16 tile of 128 rows exceeds shared memory), four read-out column chunks
+    # D = 1024: 64-row Q tiles (the fp16 tile of 128 rows exceeds shared memory), two 512-column read-out chunks
     "d1024_p2k": (1024, 2048, 512, 0),
     "d1024_ragged": (1024, 1100, 257, 0),
     "d1024_single_tile": (1024, 640, 40, 0),
