@@ -794,33 +794,45 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
 //   score columns each.  The four threads of a row agree on the row maximum through shared memory; the read-out
 //   MMA takes P~ from TMEM and every lane reads ITS OWN lane's data (measured), so the 16 packed words of a thread
 //   are swapped with the partner lane (L ^ 64) through shared memory and stored into both lanes.
-template <int H, int DV>
+// TP = patterns per score tile: 256 at H = 512 (the M = 128 pair instruction issues at 3,640 FLOP/clk/SM with N = 128
+// but 5,040 with N = 256, profiles/r01_umma_layout_probe.txt), 128 at H = 1024 (the 32 KiB exchange buffer of the
+// wide tile does not fit next to the 128 KiB Q tile).
+template <int H, int DV, int TP>
 struct Tc64Cfg {
   static constexpr int kPolyPeriod = HOP_POLY_D256;
   static constexpr int kRows = 64;
+  static constexpr int kTP = TP;
+  static constexpr int kSCols = TP / 2;                     // TMEM columns of one score tile (and of its P~)
+  static constexpr int kC = TP / 4;                         // score columns per softmax thread
+  static constexpr int kW = kC / 2;                         // packed P~ words per softmax thread
+  static constexpr int kPC = TP / 64;                       // 64-pattern K steps of the read-out per tile
   static constexpr int kKChunks = H / 64;
-  static constexpr int kKStages = kKChunks / 2;             // ring stages of one K^ tile (2 x 8 KiB chunks per stage)
+  static constexpr int kKPerStage = TP == 128 ? 2 : 1;      // K^ chunks (TP/2 patterns x 64) per 16 KiB ring stage
+  static constexpr int kKChunkBytes = (TP / 2) * 128;       // this CTA's half of one K^ chunk
+  static constexpr int kKStages = kKChunks / kKPerStage;    // ring stages of one K^ tile
   static constexpr int kQChunkBytes = kRows * 128;
   static constexpr int kQBytes = kKChunks * kQChunkBytes;
   static constexpr int kNH = DV / 256;                      // N = 256 read-out instructions per K step
-  static constexpr int kStages = H >= 1024 ? 5 : HOP_TC64_STAGES_512;
+  static constexpr int kStages = H >= 1024 ? 5 : (TP == 256 ? 8 : HOP_TC64_STAGES_512);
   static constexpr int kBarBytes = 512;
   static constexpr int kXmaxBytes = 2 * 2 * 128 * 4;        // [parity][sub][lane]
-  static constexpr int kXpBytes = 4 * 2 * 128 * 16;         // [16-byte chunk][sub][lane]
+  static constexpr int kXpBytes = (kW / 4) * 2 * 128 * 16;  // [16-byte chunk][sub][lane]
   static constexpr int kSmemBytes = kQBytes + kStages * kChunkBytes + kBarBytes + kXmaxBytes + kXpBytes;
-  static constexpr uint32_t kTmemO = 128;
-  static_assert(DV % 256 == 0 && DV <= 512 && H % DV == 0 && kSmemBytes <= 232448, "TMEM / shared-memory budget");
+  static constexpr uint32_t kTmemO = 2 * kSCols;
+  static_assert(TP == 128 || TP == 256, "score tile");
+  static_assert(DV % 256 == 0 && DV <= 512 && H % DV == 0 && kSmemBytes <= 232448 && 2 * kSCols + DV / 2 <= 512,
+                "TMEM / shared-memory budget");
 };
 
 __device__ __forceinline__ void ld_shared_v4(uint32_t addr, uint32_t& a, uint32_t& b, uint32_t& c, uint32_t& d) {
   asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "r"(addr) : "memory");
 }
 
-template <int H, int DV, bool kBf16>
+template <int H, int DV, int TP, bool kBf16>
 __global__ void __launch_bounds__(kThreads, 1)
 hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_vt,
                     const TcKernelArgs a) {
-  using Cfg = Tc64Cfg<H, DV>;
+  using Cfg = Tc64Cfg<H, DV, TP>;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t smem_base = ptx::smem_u32(smem_raw);
   if ((smem_base & 1023u) != 0) __trap();
@@ -845,7 +857,7 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
   constexpr uint32_t kArrivers = kSoftmaxThreads * 2;
   const int split = blockIdx.y;
   const int zoff = (int)blockIdx.z * DV;
-  const int nt_total = (a.p + kTileP - 1) / kTileP;
+  const int nt_total = (a.p + TP - 1) / TP;
   const int cid = (int)blockIdx.x / 2;
   const int t0 = split * a.tiles_per_split;
   const int nt = min(a.tiles_per_split, nt_total - t0);
@@ -883,20 +895,20 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
       };
       auto load_k = [&](int tile) {
         for (int ks = 0; ks < Cfg::kKStages; ++ks) {
-          const int s = acquire(2u * 2u * 8192u);
+          const int s = acquire(2u * Cfg::kKPerStage * Cfg::kKChunkBytes);
           const uint32_t fb = ptx::map_to_cta(full_bar(s), 0);
-          for (int c = 0; c < 2; ++c)
-            ptx::tma_load_2d_pair(ring + s * kChunkBytes + c * 8192, &tm_k, fb, (ks * 2 + c) * 64,
-                                  tile * kTileP + (int)crank * 64);
+          for (int c = 0; c < Cfg::kKPerStage; ++c)
+            ptx::tma_load_2d_pair(ring + s * kChunkBytes + c * Cfg::kKChunkBytes, &tm_k, fb,
+                                  (ks * Cfg::kKPerStage + c) * 64, tile * TP + (int)crank * (TP / 2));
           ++it;
         }
       };
       auto load_b = [&](int tile) {
-        for (int kc = 0; kc < 2; ++kc)
+        for (int kc = 0; kc < Cfg::kPC; ++kc)
           for (int nh = 0; nh < Cfg::kNH; ++nh) {
             const int s = acquire(2u * 128u * 128u);
             ptx::tma_load_2d_pair(ring + s * kChunkBytes, &tm_vt, ptx::map_to_cta(full_bar(s), 0),
-                                  tile * kTileP + kc * 64, zoff + nh * 256 + (int)crank * 128);
+                                  tile * TP + kc * 64, zoff + nh * 256 + (int)crank * 128);
             ++it;
           }
       };
@@ -911,7 +923,7 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
     // -------------------------------------------------------------- MMA issuer (leader CTA, one thread)
     if (crank == 0 && ptx::elect_one()) {
       constexpr int fmt = kBf16 ? 1 : 0;
-      constexpr uint32_t idesc_qk = ptx::umma_idesc_f16(128, kTileP, fmt);
+      constexpr uint32_t idesc_qk = ptx::umma_idesc_f16(128, TP, fmt);
       constexpr uint32_t idesc_pv = ptx::umma_idesc_f16(128, 256, fmt);
       uint32_t it = 0;
       ptx::mbar_wait_cluster(q_ready, 0);
@@ -923,12 +935,12 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
           ptx::mbar_wait_cluster(full_bar(s), (it / Cfg::kStages) & 1);
           ptx::tc_fence_after();
 #pragma unroll
-          for (int c = 0; c < 2; ++c) {
-            const uint64_t ad = ptx::umma_desc_sw128(q_smem + (ks * 2 + c) * Cfg::kQChunkBytes);
-            const uint64_t bd = ptx::umma_desc_sw128(ring + s * kChunkBytes + c * 8192);
+          for (int c = 0; c < Cfg::kKPerStage; ++c) {
+            const uint64_t ad = ptx::umma_desc_sw128(q_smem + (ks * Cfg::kKPerStage + c) * Cfg::kQChunkBytes);
+            const uint64_t bd = ptx::umma_desc_sw128(ring + s * kChunkBytes + c * Cfg::kKChunkBytes);
 #pragma unroll
             for (int k = 0; k < 4; ++k)
-              ptx::umma2_f16_ss(tmem_base + b * 64, ad + 2 * k, bd + 2 * k, idesc_qk, (ks | c | k) != 0);
+              ptx::umma2_f16_ss(tmem_base + b * Cfg::kSCols, ad + 2 * k, bd + 2 * k, idesc_qk, (ks | c | k) != 0);
           }
           ptx::umma2_commit_both(empty_bar(s));
           ++it;
@@ -941,12 +953,12 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
         const int b = j & 1;
         ptx::mbar_wait_cluster(p_full(b), (j >> 1) & 1);
         ptx::tc_fence_after();
-        for (int kc = 0; kc < 2; ++kc)
+        for (int kc = 0; kc < Cfg::kPC; ++kc)
           for (int nh = 0; nh < Cfg::kNH; ++nh) {
             const int s = it % Cfg::kStages;
             ptx::mbar_wait_cluster(full_bar(s), (it / Cfg::kStages) & 1);
             ptx::tc_fence_after();
-            const uint32_t at = tmem_base + b * 64 + kc * 32;
+            const uint32_t at = tmem_base + b * Cfg::kSCols + kc * 32;
             const uint64_t bd = ptx::umma_desc_sw128(ring + s * kChunkBytes);
 #pragma unroll
             for (int k = 0; k < 4; ++k)
@@ -961,7 +973,7 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
   } else {
     // ------------------------------------------------------ softmax / epilogue
     const int wq = warp & 3;                      // TMEM lane quarter
-    const int sub = (warp - 2) >> 2;              // which 32 of the lane's 64 score columns
+    const int sub = (warp - 2) >> 2;              // which half of the lane's TP/2 score columns
     const int L = wq * 32 + lane;                 // TMEM lane
     const int h = L >> 6, row = L & 63;           // pattern half of the tile, query row of the CTA
     const uint32_t lane_base = tmem_base + ((uint32_t)(wq * 32) << 16);
@@ -1054,21 +1066,23 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
     const int og0 = sub * kOGroups;
     for (int j = 0; j < nt; ++j) {
       const int b = j & 1;
-      const int col0 = (t0 + j) * kTileP + h * 64 + sub * 32;   // global pattern index of this thread's column 0
+      constexpr int kC = Cfg::kC, kW = Cfg::kW;
+      const int col0 = (t0 + j) * TP + h * (TP / 2) + sub * kC;  // global pattern index of this thread's column 0
       const int valid = a.p - col0;
       ptx::mbar_wait(s_full(b), (j >> 1) & 1);
       ptx::tc_fence_after();
-      uint32_t v[32];
-      ptx::tmem_ld_x32(lane_base + b * 64 + sub * 32, v);
-      ptx::tmem_wait_ld();
-      if (valid < 32) {
+      uint32_t v[kC];
 #pragma unroll
-        for (int i = 0; i < 32; ++i)
+      for (int c = 0; c < kC; c += 32) ptx::tmem_ld_x32p(lane_base + b * Cfg::kSCols + sub * kC + c, v + c);
+      ptx::tmem_wait_ld();
+      if (valid < kC) {
+#pragma unroll
+        for (int i = 0; i < kC; ++i)
           if (i >= valid) v[i] = __float_as_uint(-INFINITY);
       }
       float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-      for (int i = 0; i < 32; i += 8) {
+      for (int i = 0; i < kC; i += 8) {
 #pragma unroll
         for (int u = 0; u < 4; ++u)
           mx[u] = fmaxf(mx[u], fmaxf(__uint_as_float(v[i + 2 * u]), __uint_as_float(v[i + 2 * u + 1])));
@@ -1076,9 +1090,9 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
       const float hmax = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
       st_shared_f32(xmax_at(b, sub, L), hmax);
       if (hmax > tmax) {
-        int idx = 31;
+        int idx = kC - 1;
 #pragma unroll
-        for (int i = 31; i >= 0; --i) idx = (__uint_as_float(v[i]) == hmax) ? i : idx;
+        for (int i = kC - 1; i >= 0; --i) idx = (__uint_as_float(v[i]) == hmax) ? i : idx;
         tmax = hmax;
         targ = col0 + idx;
       }
@@ -1092,20 +1106,20 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
 
       float ls[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-      for (int i = 0; i < 32; ++i) {
+      for (int i = 0; i < kC; ++i) {
         const float xs = __uint_as_float(v[i]) - m_run;
         const bool poly = Cfg::kPolyPeriod > 0 && (i % (Cfg::kPolyPeriod > 0 ? Cfg::kPolyPeriod : 1)) == 0;
         v[i] = __float_as_uint(poly ? ptx::ex2_poly(xs) : ptx::ex2(xs));
       }
-      uint32_t pk[16];
+      uint32_t pk[kW];
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
+      for (int i = 0; i < kW; ++i) {
         const float p0 = __uint_as_float(v[2 * i]), p1 = __uint_as_float(v[2 * i + 1]);
         ls[i & 3] += p0 + p1;
         pk[i] = pack16<kBf16>(p0, p1);
       }
 #pragma unroll
-      for (int c = 0; c < 4; ++c) st_shared_v4(xp_at(c, sub, L), pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+      for (int c = 0; c < kW / 4; ++c) st_shared_v4(xp_at(c, sub, L), pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
       if (any_need && j > 0) {
         const uint32_t pg = j - 1;
         ptx::mbar_wait(p_empty(pg & 1), (pg >> 1) & 1);   // read-out MMA of the previous tile done
@@ -1123,12 +1137,14 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
         }
       }
       ptx::named_bar_sync(grp_bar, 128);
-      uint32_t pw[16];
+      uint32_t pw[kW];
 #pragma unroll
-      for (int c = 0; c < 4; ++c) ld_shared_v4(xp_at(c, sub, L ^ 64), pw[4 * c], pw[4 * c + 1], pw[4 * c + 2], pw[4 * c + 3]);
-      // P~ row of this lane: patterns 64 h' + 32 sub' + i -> column 32 h' + 16 sub' + i / 2
-      ptx::tmem_st_x16(lane_base + b * 64 + h * 32 + sub * 16, pk);
-      ptx::tmem_st_x16(lane_base + b * 64 + (h ^ 1) * 32 + sub * 16, pw);
+      for (int c = 0; c < kW / 4; ++c) ld_shared_v4(xp_at(c, sub, L ^ 64), pw[4 * c], pw[4 * c + 1], pw[4 * c + 2], pw[4 * c + 3]);
+      // P~ row of this lane: patterns (TP/2) h' + kC sub' + i -> column (TP/4) h' + kW sub' + i / 2
+      const uint32_t p_own = lane_base + b * Cfg::kSCols + h * (TP / 4) + sub * kW;
+      const uint32_t p_oth = lane_base + b * Cfg::kSCols + (h ^ 1) * (TP / 4) + sub * kW;
+      if constexpr (kW == 16) { ptx::tmem_st_x16(p_own, pk); ptx::tmem_st_x16(p_oth, pw); }
+      else { ptx::tmem_st_x32(p_own, pk); ptx::tmem_st_x32(p_oth, pw); }
       l += (ls[0] + ls[1]) + (ls[2] + ls[3]);
       ptx::tmem_wait_st();
       ptx::tc_fence_before();
@@ -1468,19 +1484,19 @@ int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
 }
 
 // 64-rows-per-CTA pair form (hop_fwd_tc64_kernel): plain grid (row pairs x pattern splits x column chunks), T = 0
-template <int H, int DV, bool kBf16>
+template <int H, int DV, int TP, bool kBf16>
 int launch_h64(const TcPassArgs& a, int splits, cudaStream_t st) {
-  using Cfg = Tc64Cfg<H, DV>;
+  using Cfg = Tc64Cfg<H, DV, TP>;
   const int ppad = padded_patterns(a.p);
   if (a.update_steps > 0) HOP_FAIL(HOP_ERR_UNSUPPORTED, "the 64-row form runs retrieve updates as separate launches (internal)");
   CUtensorMap tk, tvt;
-  HOP_TRY(make_map(&tk, a.k16, ppad, H, kTileP / 2, a.bf16));     // this CTA's 64 patterns of a K^ chunk
+  HOP_TRY(make_map(&tk, a.k16, ppad, H, TP / 2, a.bf16));         // this CTA's TP/2 patterns of a K^ chunk
   HOP_TRY(make_map(&tvt, a.vt16, a.dv, ppad, 128, a.bf16));       // this CTA's 128 rows of an N = 256 read-out chunk
   TcKernelArgs k{};
   k.x_raw = a.x_raw; k.lnq_w = a.lnq_w; k.lnq_b = a.lnq_b; k.ln_eps = a.ln_eps; k.has_ln = a.has_ln; k.beta = a.beta;
   k.qs = a.qs; k.bias = a.bias; k.n = a.n; k.p = a.p; k.update_steps = 0;
   k.dv_total = a.dv; k.out_scale = a.out_scale;
-  const int nt_total = ppad / kTileP;
+  const int nt_total = (ppad + TP - 1) / TP;          // (rows past ppad read as zeros and are masked)
   k.tiles_per_split = (nt_total + splits - 1) / splits;
   k.splits = (nt_total + k.tiles_per_split - 1) / k.tiles_per_split;
   k.retrieved = a.retrieved; k.qsave = a.qsave; k.lse = a.lse; k.argmax = a.argmax; k.rowmax = a.rowmax;
@@ -1497,7 +1513,7 @@ int launch_h64(const TcPassArgs& a, int splits, cudaStream_t st) {
     k.part_max = reinterpret_cast<float*>(w); w += round_up_sz(rows * sizeof(float), 256);
     k.part_arg = reinterpret_cast<int32_t*>(w);
   }
-  auto* kern = hop_fwd_tc64_kernel<H, DV, kBf16>;
+  auto* kern = hop_fwd_tc64_kernel<H, DV, TP, kBf16>;
   HOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
   const int row_tiles = (a.n + Cfg::kRows - 1) / Cfg::kRows;
   cudaLaunchConfig_t cfg{};
@@ -1668,8 +1684,13 @@ size_t tc_forward_workspace(int n, int p, int d, int update_steps) {
 
 static int launch_tc_one(const TcPassArgs& a, int splits, cudaStream_t st) {
   if (tc_halfm(a.h)) {
-    if (a.h == 512) return a.bf16 ? launch_h64<512, 512, true>(a, splits, st) : launch_h64<512, 512, false>(a, splits, st);
-    return a.bf16 ? launch_h64<1024, 512, true>(a, splits, st) : launch_h64<1024, 512, false>(a, splits, st);
+    if (a.h == 512) {
+      const char* e = getenv("HOP_TC64_TILE");           // experiment knob: 128-pattern score tiles at D = 512
+      if (e && atoi(e) == 128)
+        return a.bf16 ? launch_h64<512, 512, 128, true>(a, splits, st) : launch_h64<512, 512, 128, false>(a, splits, st);
+      return a.bf16 ? launch_h64<512, 512, 256, true>(a, splits, st) : launch_h64<512, 512, 256, false>(a, splits, st);
+    }
+    return a.bf16 ? launch_h64<1024, 512, 128, true>(a, splits, st) : launch_h64<1024, 512, 128, false>(a, splits, st);
   }
   const int cl = tc_choose_cluster(a.n, a.h);
   const bool pair = tc_use_pair(a.n, a.h);
