@@ -813,7 +813,7 @@ struct Tc64Cfg {
   static constexpr int kQChunkBytes = kRows * 128;
   static constexpr int kQBytes = kKChunks * kQChunkBytes;
   static constexpr int kNH = DV / 256;                      // N = 256 read-out instructions per K step
-  static constexpr int kStages = H >= 1024 ? 5 : (TP == 256 ? 8 : HOP_TC64_STAGES_512);
+  static constexpr int kStages = H >= 1024 ? (TP == 256 ? 4 : 5) : (TP == 256 ? 8 : HOP_TC64_STAGES_512);
   static constexpr int kBarBytes = 512;
   static constexpr int kXmaxBytes = 2 * 2 * 128 * 4;        // [parity][sub][lane]
   static constexpr int kXpBytes = (kW / 4) * 2 * 128 * 16;  // [16-byte chunk][sub][lane]
@@ -1689,6 +1689,10 @@ static int launch_tc_one(const TcPassArgs& a, int splits, cudaStream_t st) {
       if (e && atoi(e) == 128)
         return a.bf16 ? launch_h64<512, 512, 128, true>(a, splits, st) : launch_h64<512, 512, 128, false>(a, splits, st);
       return a.bf16 ? launch_h64<512, 512, 256, true>(a, splits, st) : launch_h64<512, 512, 256, false>(a, splits, st);
+    }
+    {
+      const char* e = getenv("HOP_TC64_TILE");           // experiment knob: 256-pattern score tiles at D = 1024 (4-stage ring)
+      if (e && atoi(e) == 256 && !a.bf16) return launch_h64<1024, 512, 256, false>(a, splits, st);
     }
     return a.bf16 ? launch_h64<1024, 512, 128, true>(a, splits, st) : launch_h64<1024, 512, 128, false>(a, splits, st);
   }
