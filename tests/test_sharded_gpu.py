@@ -22,7 +22,8 @@ from oracle import hflayers_oracle as O
 from util import randomize_, rel_l2
 impl = hflayers._impl
 for (D, P, N, T, path, bar) in [(64, 512, 300, 0, "fp32", 1e-5), (64, 515, 77, 2, "fp32", 1e-4),
-                                (128, 4096, 1024, 0, "f16", 1e-3), (256, 2048, 512, 1, "f16", 1e-3)]:
+                                (128, 4096, 1024, 0, "f16", 1e-3), (256, 2048, 512, 1, "f16", 1e-3),
+                                (512, 4096, 256, 0, "f16", 1e-3)]:     # the 64-rows-per-CTA pair kernel per shard
     kw = dict(input_size=D, quantity=P, update_steps_max=T, update_steps_eps=0.0,
               stored_pattern_as_static=True, state_pattern_as_static=True)
     ref = randomize_(O.HopfieldLayer(**kw), 5, 1.0)
