@@ -82,6 +82,39 @@ def test_error_reporting_without_gpu(impl):
     assert sizes[5].value == (65536 * 256 * 2 if out.value == cb.PATH_TC_F16 else 0)
 
 
+def test_wide_widths_select_the_tensor_path_and_size_their_workspace(impl, monkeypatch):
+    """Host logic of BASELINE config 5's wide widths, no GPU needed (the SM count falls back to 148): D = 512 and
+    1024 resolve to the tcgen05 path (the fp32 kernels stop at 256), unsupported widths are refused there, and the
+    forward workspace covers the state buffers plus the split partials under both kernel forms."""
+    cb = impl.cabi
+    lib = cb.load()
+    out = C.c_int32(0)
+    for d_ in (512, 1024):
+        d = cb.make_desc(flags=0, path=0, n_rows=300, n_patterns=2048, d_in=d_, d_assoc=d_, d_v=d_, d_out=d_,
+                         update_steps=0, beta=d_ ** -0.5)
+        assert lib.hop_sm100_select_path(C.byref(d), C.byref(out)) == 0 and out.value == cb.PATH_TC_F16
+        sizes = [C.c_size_t(0) for _ in range(6)]
+        assert lib.hop_sm100_pattern_bytes(C.byref(d), *[C.byref(s) for s in sizes]) == 0
+        assert sizes[2].value == 2048 * d_ * 2 and sizes[4].value == 2048 * d_ * 2 and sizes[3].value == 0
+        state = 3 * ((300 * d_ * 4 + 255) // 256 * 256)          # two state buffers + one read-out buffer
+        got = {}
+        for halfm in ("1", "0"):
+            monkeypatch.setenv("HOP_TC_HALFM", halfm)
+            ws = C.c_size_t(0)
+            assert lib.hop_sm100_workspace_bytes(C.byref(d), 0, C.byref(ws)) == 0
+            assert ws.value >= state and (ws.value - state) % 256 == 0
+            got[halfm] = ws.value - state
+        # split partials: (splits x N) rows of D floats + three per-row vectors, for some split count >= 1
+        for extra in got.values():
+            if extra:
+                per_split = (300 * d_ * 4 + 255) // 256 * 256
+                assert extra >= 2 * per_split
+    bad = cb.make_desc(flags=0, path=cb.PATH_TC_F16, n_rows=300, n_patterns=2048, d_in=768, d_assoc=768, d_v=768,
+                       d_out=768, update_steps=0, beta=0.05)
+    assert lib.hop_sm100_select_path(C.byref(bad), C.byref(out)) != 0
+    assert b"1024" in lib.hop_sm100_last_error()
+
+
 def test_constructor_signature_mirrors_upstream(impl):
     from oracle import hflayers_oracle as O
     ours = inspect.signature(impl.HopfieldLayer.__init__)
