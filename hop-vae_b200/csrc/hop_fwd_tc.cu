@@ -786,17 +786,17 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
 // 64-rows-per-CTA form for the wide widths (H = 512, 1024).  A tcgen05 CTA pair with M = 128: each CTA supplies 64
 // query rows and half of every streamed operand tile.  Measured layout (scripts/probes/umma_layout_probe.cu): the
 // accumulator row r of a CTA sits in TMEM lane r for columns n < N/2 and in lane r + 64 for n >= N/2, both in TMEM
-// columns [0, N/2) -- an N-wide accumulator costs N/2 TMEM columns.  So one CTA holds two 128-pattern score tiles
-// (64 columns each) AND a 512-column read-out (256 columns, two N = 256 instructions): no score recompute at
+// columns [0, N/2) -- an N-wide accumulator costs N/2 TMEM columns.  So one CTA holds two TP-pattern score tiles
+// (TP/2 columns each) AND a 512-column read-out (256 columns, two N = 256 instructions): no score recompute at
 // D = 512, two column chunks at D = 1024, and a Q tile of 64 KiB / 128 KiB.
-//   TMEM   S0 [0,64)  S1 [64,128)  O [128, 128 + DV/2);  P~ (16-bit pairs, 64 columns) over the score tile
-//   lane L = 32 (warp % 4) + lane: row L & 63, pattern half h = L >> 6; two threads per lane (sub = 0 | 1), 32
+//   TMEM   S0 [0,TP/2)  S1 [TP/2,TP)  O [TP, TP + DV/2);  P~ (16-bit pairs, TP/2 columns) over the score tile
+//   lane L = 32 (warp % 4) + lane: row L & 63, pattern half h = L >> 6; two threads per lane (sub = 0 | 1), TP/4
 //   score columns each.  The four threads of a row agree on the row maximum through shared memory; the read-out
-//   MMA takes P~ from TMEM and every lane reads ITS OWN lane's data (measured), so the 16 packed words of a thread
-//   are swapped with the partner lane (L ^ 64) through shared memory and stored into both lanes.
+//   MMA takes P~ from TMEM and every lane reads ITS OWN lane's data (measured), so the TP/8 packed words of a
+//   thread are swapped with the partner lane (L ^ 64) through shared memory and stored into both lanes.
 // TP = patterns per score tile: 256 at H = 512 (the M = 128 pair instruction issues at 3,640 FLOP/clk/SM with N = 128
 // but 5,040 with N = 256, profiles/r01_umma_layout_probe.txt), 128 at H = 1024 (the 32 KiB exchange buffer of the
-// wide tile does not fit next to the 128 KiB Q tile).
+// wide tile leaves room for four ring stages only next to the 128 KiB Q tile: measured slower, HOP_TC64_TILE=256).
 template <int H, int DV, int TP>
 struct Tc64Cfg {
   static constexpr int kPolyPeriod = HOP_POLY_D256;
