@@ -65,7 +65,8 @@ enum {
 enum {
   HOP_PATH_AUTO      = 0,  /* library picks (see hop_sm100_select_path)                         */
   HOP_PATH_FP32_SIMT = 1,  /* exact fp32 CUDA-core kernels (small / argmax-tight problems, D<16) */
-  HOP_PATH_TC_F16    = 2,  /* tcgen05 kind::f16 MMAs, fp16-encoded operands, fp32 accumulate    */
+  HOP_PATH_TC_F16    = 2,  /* tcgen05 kind::f16 MMAs, fp16-encoded operands, fp32 accumulate;
+                              H == Dv in {64, 128, 256, 512, 1024}, else HOP_ERR_UNSUPPORTED    */
   HOP_PATH_TC_BF16   = 3   /* same kernels, bf16-encoded operands (fails the 1e-3 parity bar;
                               kept for throughput comparison)                                    */
 };
