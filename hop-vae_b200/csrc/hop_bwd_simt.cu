@@ -15,7 +15,6 @@
 //   pattern side, both paths summing into d_lookup.
 #include <cooperative_groups.h>
 
-#include <cstdlib>
 #include "hop_common.cuh"
 
 namespace cg = cooperative_groups;
@@ -795,8 +794,7 @@ int launch_core_kv(CoreArgs a, cudaStream_t st) {
   // alone -- FFHQ-64 (N = 9,248): 895 -> 838 us per bottleneck training step
   int per_sm = (int)((227u * 1024u) / smem);
   per_sm = per_sm > 2 ? 2 : (per_sm < 1 ? 1 : per_sm);
-  static const int waves_env = [] { const char* e = getenv("HOP_BWD_KV_WAVES"); return e ? atoi(e) : 0; }();
-  const int waves = waves_env > 0 ? waves_env : per_sm;
+  const int waves = per_sm;
   int splits = (waves * sms + ptiles - 1) / ptiles;
   const int max_splits = (a.n + BQ - 1) / BQ;
   if (splits > max_splits) splits = max_splits;
@@ -918,7 +916,7 @@ int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patte
   // 2. association core
   CoreArgs ca{qhat, pt.khat, pt.vhat, lse, dR, retrieved, w.delta, w.dqs, w.dkhat, w.dvhat, N, P, H, Dv, 0};
   const int hc = (H + 63) / 64, dvc = (Dv + 63) / 64;
-  if (H <= 4 && Dv <= 4 && P <= 4096 && !getenv("HOP_BWD_NO_TINY")) HOP_TRY(launch_core_tiny(ca, st));
+  if (H <= 4 && Dv <= 4 && P <= 4096) HOP_TRY(launch_core_tiny(ca, st));
   else if (hc == 1 && dvc == 1) HOP_TRY((launch_core<1, 1>(ca, st)));
   else if (hc == 1 && dvc == 2) HOP_TRY((launch_core<1, 2>(ca, st)));
   else if (hc == 2 && dvc == 1) HOP_TRY((launch_core<2, 1>(ca, st)));

@@ -45,6 +45,9 @@ void count_launch(int n = 1);
 
 static inline int round_up(int x, int m) { return (x + m - 1) / m * m; }
 static inline size_t round_up_sz(size_t x, size_t m) { return (x + m - 1) / m * m; }
+// scheduling overrides of the tensor-core forward (hop_desc.tune_splits / tune_flags)
+struct TcTune { int splits; uint32_t flags; };
+static inline TcTune tune_of(const hop_desc& d) { return TcTune{d.tune_splits, d.tune_flags}; }
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 // Pattern count padded for the 16-bit transposed packs (TMA row pitch must be a
@@ -80,6 +83,7 @@ struct SimtPassArgs {
   float* qsave;     // (N, H)  or nullptr
   float* lse; int32_t* argmax; float* rowmax; int pattern_offset;
   const float* wo; const float* bo; int dout; float* out;   // fused out-proj (optional)
+  const uint32_t* stopped;   // device flag of the stop rule or nullptr: when set, an update pass copies qs -> res
 };
 int launch_simt_pass(const SimtPassArgs& a, cudaStream_t st);
 // hop_bwd_simt.cu
@@ -88,11 +92,31 @@ int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patte
                          const float* grad_out, const hop_grads& g, void* ws, size_t ws_bytes,
                          cudaStream_t st);
 size_t simt_backward_workspace(const hop_desc& d);
+// hop_repair.cu -- exact nearest-pattern index behind the 16-bit tensor-core scores (HOP_F_EXACT_ARGMAX) and the
+// fp32 path's stop rule of the retrieve updates (update_eps)
+struct RepairArgs {
+  // query rows in the arithmetic of the last pass: raw x + LN_q + beta (x_raw) or a prepared fp32 state (qs)
+  const float* x_raw; const float* lnq_w; const float* lnq_b; float ln_eps; int has_ln; float beta;
+  const float* qs;
+  const float* khat;          // (P, H) fp32
+  const float* kstats;        // [0] = max_j ||K^_j||
+  int n, p, h, pattern_offset;
+  const float* lse; float* rowmax; int32_t* argmax;   // results of the 16-bit pass; argmax / rowmax are corrected in place
+  void* ws; size_t ws_bytes;  // repair_workspace_bytes(n, h); its first 16 bytes are the control words, which the
+                              // forward kernel of the same call clears (TcPassArgs::zero_words)
+};
+size_t repair_workspace_bytes(int n, int h);
+int launch_argmax_repair(const RepairArgs& a, cudaStream_t st);
+// ||A_t - A_(t-1)||_F per batch item, max over items, compared with eps: sets *stopped (device) to 1 when the
+// retrieve updates have converged (upstream's rule).  fp32, CUDA cores.
+int launch_update_delta(const float* q_new, const float* q_old, const float* khat, int n, int p, int h,
+                        int rows_per_item, float eps, float* row_scratch, uint32_t* stopped, cudaStream_t st);
 // hop_fwd_tc.cu
 struct TcPassArgs {
   const float* x_raw; const float* lnq_w; const float* lnq_b; float ln_eps; int has_ln; float beta;
   const float* qs;          // prepared beta*Q^ (N,H) fp32 if x_raw == nullptr
   const void* k16; const void* kt16; const void* vt16;
+  const void* k16lo; const void* kt16lo;   // low halves (update passes of T >= 2 with hi + lo operand pairs) or nullptr
   const float* bias;        // (Dv) added to the read-out (folded out_proj bias) or nullptr
   float out_scale;          // scale of the normalised read-out (1 except for an update pass run as its own launch)
   float* qtmp[2];           // two (N,H) fp32 state buffers, needed when T > 0 and H > 256 (one launch per pass)
@@ -101,13 +125,26 @@ struct TcPassArgs {
   float* qsave;             // (N,H) or nullptr
   float* lse; int32_t* argmax; float* rowmax; int pattern_offset;
   void* ws; size_t ws_bytes;   // partial results of the pattern splits (tc_forward_workspace bytes)
+  TcTune tune;
+  uint32_t* zero_words;        // 4 control words the first launch clears (repair counters) or nullptr
 };
-int tc_choose_splits(int n, int p, int d, int update_steps);
-int tc_choose_cluster(int n, int d);
-bool tc_use_pair(int n, int d);
-size_t tc_forward_workspace(int n, int p, int d, int update_steps);
+int tc_choose_splits(int n, int p, int d, int update_steps, const TcTune& tune);
+bool tc_use_pair(int n, int d, const TcTune& tune);
+bool tc_precise_updates(int d, int update_steps, const TcTune& tune);
+size_t tc_forward_workspace(int n, int p, int d, int update_steps, const TcTune& tune);
 int launch_tc_forward(const TcPassArgs& a, cudaStream_t st);
 bool tc_supported(int h, int dv);
+// hop_bwd_tc.cu -- association core of the backward on the tensor pipe (dq, dK^, dV^)
+struct TcBwdArgs {
+  const float* qs; const float* lse; const float* dr; const float* delta;   // (N,H), (N), (N,Dv), (N)
+  const void* k16; const void* v16; const void* kt16;                        // pattern packs
+  float* dqs; float* dkhat; float* dvhat;                                    // (N,H), (P,H), (P,Dv)
+  int n, p, h, dv;
+  void* ws; size_t ws_bytes;
+};
+bool tc_backward_supported(int n, int p, int h, int dv);
+size_t tc_backward_workspace(int n, int p, int h, int dv);
+int launch_tc_backward(const TcBwdArgs& a, cudaStream_t st);
 // hop_merge.cu
 int launch_merge(int n, int dv, int g, int shard, const float* lse_all, const float* rowmax_all,
                  const int32_t* argmax_all, float* retrieved, float* lse_out, int32_t* argmax_out,

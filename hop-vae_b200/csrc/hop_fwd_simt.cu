@@ -22,8 +22,6 @@
 // one launch, and no partials in HBM.
 #include <cooperative_groups.h>
 
-#include <cstdlib>
-
 #include "hop_common.cuh"
 
 namespace cg = cooperative_groups;
@@ -134,6 +132,17 @@ __global__ void __launch_bounds__(NT) hop_fwd_simt_kernel(SimtPassArgs a, int sp
   const int warp = tid >> 5, lane = tid & 31;
   const int row0 = blockIdx.x * BM;
   const int h4 = HF ? HF : (a.h + 3) / 4 * 4;
+
+  if (a.stopped != nullptr && *a.stopped != 0u) {
+    // the stop rule has fired (hop_repair.cu): this update pass carries the state through unchanged.  Every CTA of a
+    // cluster reads the same flag, so all of them leave before the first cluster barrier.
+    if (blockIdx.y == 0 && a.res != nullptr && a.qs != nullptr)
+      for (int idx = tid; idx < BM * a.h; idx += NT) {
+        const int r = idx / a.h, c = idx - r * a.h;
+        if (row0 + r < a.n) a.res[(size_t)(row0 + r) * a.dr + c] = a.qs[(size_t)(row0 + r) * a.h + c];
+      }
+    return;
+  }
 
   const int n_tiles = (a.p + BP - 1) / BP;
   const int tiles_per_split = (n_tiles + splits - 1) / splits;
@@ -502,6 +511,12 @@ __global__ void __launch_bounds__(kTinyThreads) hop_fwd_tiny_kernel(SimtPassArgs
   float4* Ws = Bs + a.p;                                        // [dout] rows of Wo (dr <= 4 columns), if any
   float* bs = reinterpret_cast<float*>(Ws + (a.wo ? a.dout : 0));   // [dout] bias
   const int tid = threadIdx.x;
+  if (a.stopped != nullptr && *a.stopped != 0u) {      // stop rule fired: identity pass (see hop_fwd_simt_kernel)
+    const long long r = (long long)blockIdx.x * kTinyRows + tid / LPR;
+    if (r < a.n && (tid & (LPR - 1)) == 0 && a.res != nullptr && a.qs != nullptr)
+      for (int c = 0; c < a.h; ++c) a.res[r * a.dr + c] = a.qs[r * a.h + c];
+    return;
+  }
   for (int j = tid; j < a.p; j += kTinyThreads) {
     float kv[4] = {0.f, 0.f, 0.f, 0.f}, bv[4] = {0.f, 0.f, 0.f, 0.f};
     for (int c = 0; c < a.h; ++c) kv[c] = __ldg(a.khat + (size_t)j * a.h + c);
@@ -616,7 +631,6 @@ int launch_tiny(const SimtPassArgs& a, cudaStream_t st) {
   // row; N = 65,536: 81 / 66 / 87 / 135 us with 4 / 8 / 16 / 32.
   int lpr = 8;
   while (lpr < 32 && (long long)a.n * lpr < 2LL * num_sms() * kTinyThreads) lpr <<= 1;
-  if (const char* e = getenv("HOP_TINY_LPR")) { const int v = atoi(e); if (v == 4 || v == 8 || v == 16 || v == 32) lpr = v; }
   switch (lpr) {
     case 4: return launch_tiny_lpr<4>(a, smem, st);
     case 8: return launch_tiny_lpr<8>(a, smem, st);
@@ -653,7 +667,7 @@ int launch_inst_hf(const SimtPassArgs& a, int splits, cudaStream_t st) {
 template <int RM, int DVC>
 int launch_inst(const SimtPassArgs& a, int splits, cudaStream_t st) {
   if constexpr (RM == 4 && DVC == 1) {
-    if (a.h == 64 && !getenv("HOP_SIMT_NO_HF")) return launch_inst_hf<RM, DVC, 64>(a, splits, st);
+    if (a.h == 64) return launch_inst_hf<RM, DVC, 64>(a, splits, st);
   }
   return launch_inst_hf<RM, DVC, 0>(a, splits, st);
 }
@@ -674,7 +688,7 @@ int launch_rm(const SimtPassArgs& a, int splits, cudaStream_t st) {
 
 int launch_simt_pass(const SimtPassArgs& a, cudaStream_t st) {
   if (a.h > 256) HOP_FAIL(HOP_ERR_UNSUPPORTED, "fp32 path supports association width <= 256 (got %d)", a.h);
-  if (a.h <= 4 && a.dr <= 4 && a.p <= 4096 && (!a.wo || a.dout <= 1024) && !getenv("HOP_SIMT_NO_TINY"))
+  if (a.h <= 4 && a.dr <= 4 && a.p <= 4096 && (!a.wo || a.dout <= 1024))
     return launch_tiny(a, st);
   // Rows per CTA: 64-row tiles keep the inner loops FMA-bound (4 x 4 register tile per thread); when the row
   // tiles alone leave SMs idle the pattern axis is split across a cluster (see the header) while everything
@@ -682,7 +696,6 @@ int launch_simt_pass(const SimtPassArgs& a, cudaStream_t st) {
   const int sms = num_sms();
   int rm = 4;
   if (a.h > 128 || a.dr > 128) rm = 2;  // keep the tile under the shared-memory limit
-  if (const char* e = getenv("HOP_SIMT_RM")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4) rm = v; }
   const int row_tiles = (a.n + 16 * rm - 1) / (16 * rm);
   const int n_tiles = (a.p + BP - 1) / BP;
   // one wave: at most ~3 CTAs of this kernel are resident per SM (registers / shared memory)
@@ -692,7 +705,6 @@ int launch_simt_pass(const SimtPassArgs& a, cudaStream_t st) {
   const int slots = sms * per_sm;
   int splits = 1;
   while (splits < 8 && n_tiles >= 4 * splits && row_tiles * splits * 2 <= slots) splits <<= 1;
-  if (const char* e = getenv("HOP_SIMT_SPLITS")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4 || v == 8) splits = v; }
   switch (rm) {
     case 4: return launch_rm<4>(a, splits, st);
     case 2: return launch_rm<2>(a, splits, st);

@@ -7,8 +7,6 @@
 // lse = log sum_g exp(lse_g).  This kernel rescales the local O_g by w_g in
 // place (so one SUM all-reduce over NVLink finishes the job) and resolves the
 // global lse / nearest pattern.  HBM-bound: reads and writes N*Dv*4 bytes.
-#include <cstdlib>
-
 #include "hop_common.cuh"
 
 namespace hop {
@@ -73,6 +71,28 @@ __device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
+// Bounded flag wait: a peer that never arrives (dead rank, mismatched epoch) becomes a trap ("unspecified launch
+// failure" on this rank) after kPeerWaitNs of wall time instead of a hung GPU.  The bound is wall time, not a spin
+// count: ranks legitimately start seconds apart (host-side skew of a first call).
+constexpr unsigned long long kPeerWaitNs = 30ull * 1000ull * 1000ull * 1000ull;
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+template <bool kSys>
+__device__ __forceinline__ void wait_flag(const uint32_t* p, uint32_t epoch) {
+  unsigned long long t0 = 0;
+  uint32_t spins = 0;
+  while ((int32_t)((kSys ? ld_acquire_sys(p) : ld_acquire_gpu(p)) - epoch) < 0) {
+    __nanosleep(32);
+    if ((++spins & 0x3fffu) == 0) {
+      const unsigned long long now = global_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > kPeerWaitNs) __trap();
+    }
+  }
+}
 // flag block of one rank: [0,16) ready[src], [16,32) done[src], [32] block counter, [33] local "go" flag
 constexpr int kFlagDone = HOP_MAX_PEERS, kFlagCounter = 2 * HOP_MAX_PEERS, kFlagGo = 2 * HOP_MAX_PEERS + 1;
 
@@ -82,22 +102,18 @@ template <int GMAX, int R>
 __global__ void __launch_bounds__(256) peer_merge_kernel(const hop_peer_merge m) {
   const int G = m.n_ranks, me = m.rank;
   // ---- opening barrier.  Block 0 talks to the peers (system scope): "my partials are complete" (stream order),
-  // then waits for the same from everyone; the other blocks (all co-resident: grid <= 2 per SM) wait on a local
-  // device-scope flag -- hundreds of blocks polling system-scope flags cost more than the merge itself.
+  // then waits for the same from everyone; the other blocks (all co-resident: a cooperative launch whose grid is
+  // capped by the occupancy query, see launch_peer_merge) wait on a local device-scope flag -- hundreds of blocks polling system-scope flags cost more than the merge itself.
   if (blockIdx.x == 0) {
     if (threadIdx.x < G) {
       __threadfence_system();
       st_release_sys(m.flags[threadIdx.x] + me, m.epoch);
-      const uint32_t* mine = m.flags[me] + threadIdx.x;
-      while ((int32_t)(ld_acquire_sys(mine) - m.epoch) < 0) __nanosleep(32);
+      wait_flag<true>(m.flags[me] + threadIdx.x, m.epoch);
     }
     __syncthreads();
     if (threadIdx.x == 0) st_release_gpu(m.flags[me] + kFlagGo, m.epoch);
   } else {
-    if (threadIdx.x == 0) {
-      const uint32_t* go = m.flags[me] + kFlagGo;
-      while ((int32_t)(ld_acquire_gpu(go) - m.epoch) < 0) __nanosleep(32);
-    }
+    if (threadIdx.x == 0) wait_flag<false>(m.flags[me] + kFlagGo, m.epoch);
     __syncthreads();
   }
 
@@ -192,8 +208,7 @@ __global__ void __launch_bounds__(256) peer_merge_kernel(const hop_peer_merge m)
   if (s_last && threadIdx.x < G) {
     __threadfence_system();
     st_release_sys(m.flags[threadIdx.x] + kFlagDone + me, m.epoch);
-    const uint32_t* mine = m.flags[me] + kFlagDone + threadIdx.x;
-    while ((int32_t)(ld_acquire_sys(mine) - m.epoch) < 0) __nanosleep(32);
+    wait_flag<true>(m.flags[me] + kFlagDone + threadIdx.x, m.epoch);
   }
 }
 
@@ -214,21 +229,45 @@ int launch_merge(int n, int dv, int g, int shard, const float* lse_all, const fl
   return HOP_OK;
 }
 
+template <int GMAX, int R>
+static int launch_peer_merge_inst(const hop_peer_merge& m, long long want, cudaStream_t st) {
+  auto* kern = peer_merge_kernel<GMAX, R>;
+  // every block must be resident at once (blocks != 0 wait for block 0's flag): cap the grid by the occupancy of
+  // THIS kernel on THIS device and launch cooperatively, so that the driver refuses a grid it cannot co-schedule
+  // instead of letting it deadlock
+  static int per_sm_cache[64];
+  int dev = 0;
+  HOP_CUDA(cudaGetDevice(&dev));
+  int per_sm = (dev >= 0 && dev < 64) ? per_sm_cache[dev] : 0;
+  if (per_sm == 0) {
+    HOP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, 0));
+    if (per_sm < 1) HOP_FAIL(HOP_ERR_CUDA, "peer_merge_kernel cannot be resident on this device");
+    if (dev >= 0 && dev < 64) per_sm_cache[dev] = per_sm;
+  }
+  const long long cap = (long long)(per_sm > 2 ? 2 : per_sm) * num_sms();
+  const int blocks = (int)(want < 1 ? 1 : (want > cap ? cap : want));
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(blocks);
+  cfg.blockDim = dim3(256);
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  HOP_CUDA(cudaLaunchKernelEx(&cfg, kern, m));
+  HOP_LAUNCH_CHECK("peer_merge_kernel");
+  return HOP_OK;
+}
+
 int launch_peer_merge(const hop_peer_merge& m, cudaStream_t st) {
-  const int sms = num_sms();
   const int chunks = ((m.d_v >> 2) + 31) >> 5;
   const long long items = (long long)m.row_count * chunks;
   const int r = m.n_ranks <= 2 ? 4 : (m.n_ranks <= 4 ? 2 : 1);
-  long long want = (items + 8 * r - 1) / (8 * r);      // 8 warps per block, r items per warp per trip
-  const int cap = (m.n_ranks > 8 ? 1 : 2) * sms;       // all blocks co-resident (see the barrier): <= 128 / 147 registers
-  int blocks = (int)(want < 1 ? 1 : (want > cap ? cap : want));
-  if (const char* e = getenv("HOP_PEER_BLOCKS")) { const int v = atoi(e); if (v > 0 && v <= cap) blocks = v; }   // tuning knob
-  if (m.n_ranks <= 2) peer_merge_kernel<2, 4><<<blocks, 256, 0, st>>>(m);
-  else if (m.n_ranks <= 4) peer_merge_kernel<4, 2><<<blocks, 256, 0, st>>>(m);
-  else if (m.n_ranks <= 8) peer_merge_kernel<8, 1><<<blocks, 256, 0, st>>>(m);
-  else peer_merge_kernel<16, 1><<<blocks, 256, 0, st>>>(m);
-  HOP_LAUNCH_CHECK("peer_merge_kernel");
-  return HOP_OK;
+  const long long want = (items + 8 * r - 1) / (8 * r);      // 8 warps per block, r items per warp per trip
+  if (m.n_ranks <= 2) return launch_peer_merge_inst<2, 4>(m, want, st);
+  if (m.n_ranks <= 4) return launch_peer_merge_inst<4, 2>(m, want, st);
+  if (m.n_ranks <= 8) return launch_peer_merge_inst<8, 1>(m, want, st);
+  return launch_peer_merge_inst<16, 1>(m, want, st);
 }
 
 }  // namespace hop

@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define HOP_SM100_ABI_VERSION 2u
+#define HOP_SM100_ABI_VERSION 3u
 
 typedef enum hop_status {
   HOP_OK = 0,
@@ -58,7 +58,27 @@ enum {
   HOP_F_PROJ_STATE   = 1u << 3,  /* Q projection present   (state_pattern_as_static=False)  */
   HOP_F_PROJ_STORED  = 1u << 4,  /* K projection present   (stored_pattern_as_static=False) */
   HOP_F_PROJ_PATTERN = 1u << 5,  /* V projection present   (pattern_projection_as_static=False) */
-  HOP_F_OUT_PROJ     = 1u << 6   /* out_proj present       (disable_out_projection=False)  */
+  HOP_F_OUT_PROJ     = 1u << 6,  /* out_proj present       (disable_out_projection=False)  */
+  /* behaviour switches of this library (no upstream counterpart) */
+  HOP_F_EXACT_ARGMAX = 1u << 7,  /* tensor-core paths: rows whose nearest pattern the 16-bit score arithmetic cannot
+                                    decide (log-sum-exp certificate, see hop_sm100_forward) are re-scored in fp32 */
+  HOP_F_TRAIN        = 1u << 8   /* prepare_patterns also writes the packs only the tensor-core backward reads
+                                    (kt16, v16) */
+};
+
+/* hop_desc.tune_flags -- scheduling overrides for tests and experiments; 0 = the library's own heuristics.
+ * They travel in the descriptor (not in environment variables): the library keeps no process-wide state. */
+enum {
+  HOP_TUNE_STREAMK_ON   = 1u << 0,  /* force / forbid the stream-K schedule of the T = 0 forward             */
+  HOP_TUNE_STREAMK_OFF  = 1u << 1,
+  HOP_TUNE_ROWS128      = 1u << 2,  /* D >= 512 on the 128-row kernel (score tile recomputed per column chunk) */
+  HOP_TUNE_MULTI_ON     = 1u << 3,  /* retrieve updates as one launch per pass / on chip in one launch         */
+  HOP_TUNE_MULTI_OFF    = 1u << 4,
+  HOP_TUNE_PAIR_ON      = 1u << 5,  /* tcgen05 CTA pairs (cta_group::2) forced on / off                        */
+  HOP_TUNE_PAIR_OFF     = 1u << 6,
+  HOP_TUNE_PLAIN_UPDATES = 1u << 7, /* retrieve updates with plain 16-bit operands even when T >= 2 (default: the
+                                       update passes of T >= 2 use hi + lo operand pairs)   */
+  HOP_TUNE_BWD_SIMT     = 1u << 8   /* backward on the fp32 CUDA-core kernels even where the tcgen05 one applies */
 };
 
 /* hop_desc.path -- which kernel family evaluates the association.            */
@@ -67,8 +87,8 @@ enum {
   HOP_PATH_FP32_SIMT = 1,  /* exact fp32 CUDA-core kernels (small / argmax-tight problems, D<16) */
   HOP_PATH_TC_F16    = 2,  /* tcgen05 kind::f16 MMAs, fp16-encoded operands, fp32 accumulate;
                               H == Dv in {64, 128, 256, 512, 1024}, else HOP_ERR_UNSUPPORTED    */
-  HOP_PATH_TC_BF16   = 3   /* same kernels, bf16-encoded operands (fails the 1e-3 parity bar;
-                              kept for throughput comparison)                                    */
+  HOP_PATH_TC_BF16   = 3   /* same kernels, bf16-encoded operands (8 significand bits: fails the 1e-3
+                              parity bar on tight problems; kept for comparison, never picked by AUTO) */
 };
 
 typedef struct hop_desc {
@@ -81,10 +101,19 @@ typedef struct hop_desc {
   int32_t  d_assoc;         /* H  (`hidden_size`, = Din when Q/K are static)           */
   int32_t  d_v;             /* Dv (`pattern_size`, = H by default)                     */
   int32_t  d_out;           /* Dout (`output_size`), ignored without HOP_F_OUT_PROJ    */
-  int32_t  update_steps;    /* T  (`update_steps_max`, >= 0; fixed-count semantics)    */
+  int32_t  update_steps;    /* T  (`update_steps_max`): at most T retrieve updates; < 0 = until the stop rule
+                               fires (fp32 path, at most 64 updates)                     */
   int32_t  pattern_offset;  /* global index of this shard's first pattern (argmax)     */
   float    beta;            /* `scaling` (1/sqrt(H) when upstream's is None)           */
   float    ln_eps;          /* LayerNorm eps (1e-5)                                    */
+  float    update_eps;      /* `update_steps_eps`: upstream's stop rule -- after pass t >= 1 the updates end
+                               when max over the batch of ||A_t - A_(t-1)||_F <= update_eps; 0 = exactly T
+                               updates.  Honoured by the fp32 path; the 16-bit tensor-core paths cannot resolve
+                               1e-4 changes of A and always run exactly T updates                              */
+  int32_t  rows_per_item;   /* query rows per batch item (`L` of a (B, L, D) input) for the stop rule's
+                               per-item Frobenius norm; 0 = all N rows are one item                           */
+  int32_t  tune_splits;     /* pattern splits per row tile of the tensor-core forward, 0 = heuristic          */
+  uint32_t tune_flags;      /* HOP_TUNE_*, 0 = heuristics                                                     */
 } hop_desc;
 
 /* Module parameters, exactly the tensors of the reference's state-dict
@@ -118,7 +147,18 @@ typedef struct hop_patterns {
                     the read-out operand, A.(V^ Wo^T) + bo == (A.V^) Wo^T + bo; written and
                     used on the tensor-core paths when HOP_F_OUT_PROJ and Dout == H == Dv,
                     so that inference needs no separate out-projection launch            */
+  void*  k16lo;  /* K^ - fp16(K^) as fp16 (Ppad, H): low halves of the score operand, used by the
+                    update passes of T >= 2 (hi + lo pairs, 3 MMAs per score tile)          */
+  void*  kt16lo; /* same, transposed (H, Ppad): low halves of the retrieve-update operand    */
+  void*  v16;    /* V^ 16-bit, row-major (Ppad, Dv): tensor-core backward (HOP_F_TRAIN)      */
+  float* kstats; /* 4 floats: [0] = max_j ||K^_j||_2 (bounds the 16-bit score noise for the
+                    HOP_F_EXACT_ARGMAX certificate); tensor-core paths                       */
 } hop_patterns;
+
+/* Byte sizes of the hop_patterns buffers (0 where a buffer is not needed).   */
+typedef struct hop_pattern_sizes {
+  size_t khat, vhat, k16, kt16, vt16, vot16, k16lo, kt16lo, v16, kstats;
+} hop_pattern_sizes;
 
 /* Gradients written (overwritten, not accumulated) by hop_sm100_backward.
  * Same shapes as the corresponding hop_params members; NULL = not wanted.    */
@@ -145,9 +185,14 @@ const char* hop_sm100_last_error(void);
  * fp32 kernels for small problems or H < 16, the tcgen05 kernels otherwise.  */
 int hop_sm100_select_path(const hop_desc* desc, int32_t* path_out);
 
-/* Byte sizes of the six hop_patterns buffers (0 where not needed).           */
-int hop_sm100_pattern_bytes(const hop_desc* desc, size_t* khat, size_t* vhat,
-                            size_t* k16, size_t* kt16, size_t* vt16, size_t* vot16);
+/* Path a TRAINING step (hop_sm100_forward + hop_sm100_backward) of `desc` runs on: the tcgen05 path where the
+ * tensor-core backward applies (T == 0, H == Dv in {128, 256, 512}, large N x P, LayerNorm'd operands), else the
+ * exact fp32 kernels (H, Dv <= 256); HOP_ERR_UNSUPPORTED where neither does.  The caller passes the result as
+ * desc.path (with HOP_F_TRAIN on a tensor-core path) to prepare_patterns, forward and backward of that step.   */
+int hop_sm100_select_train_path(const hop_desc* desc, int32_t* path_out);
+
+/* Byte sizes of the hop_patterns buffers for `desc` (0 where not needed).     */
+int hop_sm100_pattern_bytes(const hop_desc* desc, hop_pattern_sizes* sizes);
 
 /* Workspace bytes needed by forward (for_backward == 0) or backward (!= 0).  */
 int hop_sm100_workspace_bytes(const hop_desc* desc, int for_backward, size_t* bytes);
@@ -185,7 +230,11 @@ int hop_sm100_forward(const hop_desc* desc, const hop_params* params,
 /* Backward of hop_sm100_forward for T == 0 (what every reference config
  * trains with: update_steps_max defaults to 0, main.py:35 `loss.backward()`).
  * Flash-style: the N x P matrices are recomputed from (qhat, lse), never
- * stored.  `retrieved` is the forward's A.V^ (N, Dv).                        */
+ * stored.  `retrieved` is the forward's A.V^ (N, Dv).  desc.path = the path
+ * the forward of this step ran on (hop_sm100_select_train_path): on a
+ * tensor-core path the association core (dq, dK^, dV^: the five dense
+ * contractions) runs on tcgen05 from the kt16 / v16 packs (HOP_F_TRAIN);
+ * LayerNorm / projection backwards are fp32 CUDA-core kernels either way.    */
 int hop_sm100_backward(const hop_desc* desc, const hop_params* params,
                        const hop_patterns* patterns, const float* x,
                        const float* qhat, const float* retrieved, const float* lse,
