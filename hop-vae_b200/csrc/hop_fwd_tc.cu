@@ -23,7 +23,6 @@
 // read-out next to the score tiles; D = 512 and 1024).
 #include <cuda.h>
 
-#include <cstdlib>
 #include <mutex>
 
 #include "hop_common.cuh"
@@ -77,7 +76,11 @@ __device__ long long g_trace[kTraceRoles * kTraceTiles * kTraceEvents];
 // DV = read-out columns accumulated by ONE CTA.  The O accumulator owns TMEM columns [256, 256+DV), so DV <= 256:
 // a wider read-out (Dv = 512) is cut into Dv/DV column chunks along gridDim.z, each CTA recomputing the score
 // tile of its rows (the redundant score MMA is the price of the 512-column TMEM).
-template <int H, int DV>
+// kPrecise: hi + lo operand pairs (fp16(v) and fp16(v - fp16(v))) for the state, K^ and the read-out operand: the
+// score tile is three MMAs (Qh Kh + Ql Kh + Qh Kl, the lo x lo term is below 2^-22) and the read-out two (P~ Bh +
+// P~ Bl), ~2^-21 relative operand error instead of 2^-11.  Used for the update passes of T >= 2, where the retrieve
+// iteration amplifies operand rounding; the Q tile holds both halves, so the ring is shorter.
+template <int H, int DV, bool kPrecise = false>
 struct TcCfg {
   static constexpr int kPolyPeriod = H >= 256 ? HOP_POLY_D256 : (H >= 128 ? HOP_POLY_D128 : HOP_POLY_D64);
   static constexpr int kKChunks = H / 64;                 // 64-wide K chunks of the Q / K^ tiles
@@ -90,17 +93,21 @@ struct TcCfg {
   // counts.  Half of the issued tensor work is thrown away -- the functional first form of this width.
   static constexpr int kRows = H > 512 ? 64 : kTileM;
   static constexpr int kQChunkBytes = kRows * 128;        // one 64-column chunk of the Q tile
-  static constexpr int kQBytes = kKChunks * kQChunkBytes; // Q tile
-  static constexpr int kStages = (H >= 512) ? 6 : (H >= 256) ? 10 : 12;   // even: a 2-stage read-out chunk never wraps
+  static constexpr int kQTileBytes = kKChunks * kQChunkBytes;             // one 16-bit copy of the Q tile
+  static constexpr int kQBytes = (kPrecise ? 2 : 1) * kQTileBytes;        // hi [+ lo]
   static constexpr int kBarBytes = 512;                   // mbarriers + TMEM slot
   static constexpr int kXchBytes = 2 * 2 * kTileM * 4;    // [parity][half][row] floats exchanged by a warp pair
+  static constexpr int kRoom = (232448 - kBarBytes - kXchBytes - kQBytes) / kChunkBytes / 2 * 2;
+  // even: a 2-stage read-out chunk never wraps
+  static constexpr int kStages = !kPrecise ? ((H >= 512) ? 6 : (H >= 256) ? 10 : 12) : (kRoom > 12 ? 12 : kRoom);
   static constexpr int kSmemBytes = kQBytes + kStages * kChunkBytes + kBarBytes + kXchBytes;
   static_assert(kStages % 2 == 0 && (kKChunks % 2 == 0 || kBStages == 1), "2-stage chunks must stay pair-aligned");
   static_assert(DV <= 256 && DV <= H && H % DV == 0 && kSmemBytes <= 232448, "TMEM / shared-memory budget");
+  static_assert(!kPrecise || (H == DV && H <= 256 && kStages >= 6), "hi + lo operand pairs: D <= 256");
 };
 
 size_t ws_for_splits_fwd(int splits, int n, int d);   // defined with the host-side heuristics below
-bool streamk_wanted(int n, int p, int d, int update_steps);
+bool streamk_wanted(int n, int p, int d, int update_steps, const TcTune& tune);
 
 struct TcKernelArgs {
   const float* x_raw; const float* lnq_w; const float* lnq_b; float ln_eps; int has_ln; float beta;
@@ -113,6 +120,7 @@ struct TcKernelArgs {
   // cluster; a cluster walks its share segment by segment (a segment = one row group, a contiguous tile range)
   int streamk, sk_base, sk_rem, sk_max_seg;
   float* retrieved; float* qsave; float* lse; int32_t* argmax; float* rowmax; int pattern_offset;
+  uint32_t* zero_words;                 // 4 control words of the argmax repair, cleared by CTA (0,0,0) (or nullptr)
   // partial outputs when splits > 1: (splits, N, D), (splits, N) x3
   float* part_o; float* part_lse; float* part_max; int32_t* part_arg;
 };
@@ -126,6 +134,18 @@ __device__ __forceinline__ uint32_t pack16(float a, float b) {
     __half2 v = __floats2half2_rn(a, b);
     return *reinterpret_cast<uint32_t*>(&v);
   }
+}
+
+template <bool kBf16>
+__device__ __forceinline__ float2 unpack16(uint32_t w) {
+  if constexpr (kBf16) return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&w));
+  else return __half22float2(*reinterpret_cast<__half2*>(&w));
+}
+// low half of a hi + lo operand pair: the 16-bit encoding of what the hi word lost
+template <bool kBf16>
+__device__ __forceinline__ uint32_t pack16_lo(float a, float b, uint32_t hi) {
+  const float2 h = unpack16<kBf16>(hi);
+  return pack16<kBf16>(a - h.x, b - h.y);
 }
 
 // Byte offset of 16-byte chunk `c16` (0..7) of row `r` inside a 128B-swizzled [rows x 64] tile.
@@ -164,11 +184,12 @@ __device__ __forceinline__ bool seg_next(int& u, int end, int nt_total, int& rg,
 // tile in shared memory; one thread of the leader CTA issues the MMAs for both.  Per SM this halves the TMA
 // writes and the B-operand reads of shared memory -- the SS-mode score MMA alone needs 128 B/clk of operand
 // fetch in the single-CTA form, i.e. the whole shared-memory bandwidth (measured: 1400 instead of 1024 cycles).
-template <int H, int DV, bool kBf16, int kCluster, bool kPair>
+template <int H, int DV, bool kBf16, int kCluster, bool kPair, bool kPrecise>
 __global__ void __launch_bounds__(kThreads, 1)
 hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_kt,
-                  const __grid_constant__ CUtensorMap tm_vt, const TcKernelArgs a) {
-  using Cfg = TcCfg<H, DV>;
+                  const __grid_constant__ CUtensorMap tm_vt, const __grid_constant__ CUtensorMap tm_klo,
+                  const __grid_constant__ CUtensorMap tm_blo, const TcKernelArgs a) {
+  using Cfg = TcCfg<H, DV, kPrecise>;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t smem_base = ptx::smem_u32(smem_raw);
   if ((smem_base & 1023u) != 0) __trap();       // the 128B-swizzle atoms need a 1 KiB-aligned base
@@ -207,6 +228,8 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
   const int passes = a.update_steps + 1;
 
   if (threadIdx.x == 0) {
+    if (a.zero_words && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0)
+      *reinterpret_cast<uint4*>(a.zero_words) = make_uint4(0u, 0u, 0u, 0u);
     for (int s = 0; s < Cfg::kStages; ++s) {
       ptx::mbar_init(full_bar(s), 1);
       ptx::mbar_init(empty_bar(s), kPair ? 1 : kCluster);   // pair: one multicast commit of the leader's MMA thread
@@ -218,6 +241,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
     ptx::mbar_init(q_ready, kArrivers);
     ptx::fence_barrier_init();
     ptx::prefetch_tmap(&tm_k); ptx::prefetch_tmap(&tm_kt); ptx::prefetch_tmap(&tm_vt);
+    if constexpr (kPrecise) { ptx::prefetch_tmap(&tm_klo); ptx::prefetch_tmap(&tm_blo); }
   }
   if (warp == 0) {
     __syncwarp();
@@ -250,21 +274,27 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         for (int pass = 0; pass < passes; ++pass) {
           const CUtensorMap* bm = (pass < a.update_steps) ? &tm_kt : &tm_vt;
           auto load_k = [&](int tile) {
-            for (int ks = 0; ks < kKStages; ++ks) {
-              const int s = acquire(2u * kKPerStage * 8192u);
-              const uint32_t fb = ptx::map_to_cta(full_bar(s), 0);
-              for (int c = 0; c < kKPerStage; ++c)
-                ptx::tma_load_2d_pair(ring + s * kChunkBytes + c * 8192, &tm_k, fb, (ks * kKPerStage + c) * 64,
-                                      tile * kTileP + (int)crank * 64);
-              ++it;
+            for (int half = 0; half < (kPrecise ? 2 : 1); ++half) {       // hi chunks, then the lo chunks
+              const CUtensorMap* km = half ? &tm_klo : &tm_k;
+              for (int ks = 0; ks < kKStages; ++ks) {
+                const int s = acquire(2u * kKPerStage * 8192u);
+                const uint32_t fb = ptx::map_to_cta(full_bar(s), 0);
+                for (int c = 0; c < kKPerStage; ++c)
+                  ptx::tma_load_2d_pair(ring + s * kChunkBytes + c * 8192, km, fb, (ks * kKPerStage + c) * 64,
+                                        tile * kTileP + (int)crank * 64);
+                ++it;
+              }
             }
           };
           auto load_b = [&](int tile) {
-            for (int kc = 0; kc < 2; ++kc) {
-              const int s = acquire(2u * (DV / 2) * 128u);
-              ptx::tma_load_2d_pair(ring + s * kChunkBytes, bm, ptx::map_to_cta(full_bar(s), 0),
-                                    tile * kTileP + kc * 64, zoff + (int)crank * (DV / 2));
-              ++it;
+            for (int half = 0; half < (kPrecise ? 2 : 1); ++half) {
+              const CUtensorMap* m = half ? &tm_blo : bm;
+              for (int kc = 0; kc < 2; ++kc) {
+                const int s = acquire(2u * (DV / 2) * 128u);
+                ptx::tma_load_2d_pair(ring + s * kChunkBytes, m, ptx::map_to_cta(full_bar(s), 0),
+                                      tile * kTileP + kc * 64, zoff + (int)crank * (DV / 2));
+                ++it;
+              }
             }
           };
           load_k(t0);
@@ -298,11 +328,14 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         const CUtensorMap* bm = (pass < a.update_steps) ? &tm_kt : &tm_vt;
         auto load_k = [&](int tile) {
           for (int kc = 0; kc < Cfg::kKChunks; ++kc) produce(&tm_k, kc * 64, tile * kTileP, kTileP);
+          if constexpr (kPrecise)
+            for (int kc = 0; kc < Cfg::kKChunks; ++kc) produce(&tm_klo, kc * 64, tile * kTileP, kTileP);
         };
         auto load_b = [&](int tile) {
-          for (int kc = 0; kc < 2; ++kc)
-            for (int bs = 0; bs < Cfg::kBStages; ++bs)
-              produce(bm, tile * kTileP + kc * 64, zoff + bs * Cfg::kBRows, Cfg::kBRows);
+          for (int half = 0; half < (kPrecise ? 2 : 1); ++half)
+            for (int kc = 0; kc < 2; ++kc)
+              for (int bs = 0; bs < Cfg::kBStages; ++bs)
+                produce(half ? &tm_blo : bm, tile * kTileP + kc * 64, zoff + bs * Cfg::kBRows, Cfg::kBRows);
         };
         load_k(t0);
         for (int j = 0; j < nt; ++j) {
@@ -329,6 +362,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
           ptx::tc_fence_after();
           auto issue_qk = [&](uint32_t gg) {
             const int b = gg & 1;
+            for (int half = 0; half < (kPrecise ? 2 : 1); ++half)      // K^ hi stages (x Qh [, x Ql]), then K^ lo (x Qh)
             for (int ks = 0; ks < kKStages; ++ks) {
               const int s = it % Cfg::kStages;
               ptx::mbar_wait_cluster(full_bar(s), (it / Cfg::kStages) & 1);
@@ -339,7 +373,13 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
                 const uint64_t bd = ptx::umma_desc_sw128(ring + s * kChunkBytes + c * 8192);
 #pragma unroll
                 for (int k = 0; k < 4; ++k)
-                  ptx::umma2_f16_ss(tmem_base + b * kTileP, ad + 2 * k, bd + 2 * k, idesc_qk, (ks | c | k) != 0);
+                  ptx::umma2_f16_ss(tmem_base + b * kTileP, ad + 2 * k, bd + 2 * k, idesc_qk, (half | ks | c | k) != 0);
+                if (kPrecise && half == 0) {
+                  const uint64_t al = ptx::umma_desc_sw128(q_smem + Cfg::kQTileBytes + (ks * kKPerStage + c) * Cfg::kQChunkBytes);
+#pragma unroll
+                  for (int k = 0; k < 4; ++k)
+                    ptx::umma2_f16_ss(tmem_base + b * kTileP, al + 2 * k, bd + 2 * k, idesc_qk, 1u);
+                }
               }
               ptx::umma2_commit_both(empty_bar(s));
               ++it;
@@ -356,6 +396,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
             ptx::mbar_wait_cluster(p_full(b), (gg >> 1) & 1);  // P~ of both CTAs is in their TMEM
             ptx::tc_fence_after();
             HOP_TRACE(0, j, 2);
+            for (int half = 0; half < (kPrecise ? 2 : 1); ++half)      // read-out operand hi, then lo
             for (int kc = 0; kc < 2; ++kc) {
               const int s = it % Cfg::kStages;
               ptx::mbar_wait_cluster(full_bar(s), (it / Cfg::kStages) & 1);
@@ -364,7 +405,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
               const uint64_t bd = ptx::umma_desc_sw128(ring + s * kChunkBytes);
 #pragma unroll
               for (int k = 0; k < 4; ++k)
-                ptx::umma2_f16_ts(tmem_base + kTmemO, at + 8 * k, bd + 2 * k, idesc_pv, (j | kc | k) != 0);
+                ptx::umma2_f16_ts(tmem_base + kTmemO, at + 8 * k, bd + 2 * k, idesc_pv, (j | half | kc | k) != 0);
               ptx::umma2_commit_both(empty_bar(s));
               ++it;
             }
@@ -395,6 +436,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
           // S buffer b also holds P~ of tile gg-2: its read-out MMA was issued before this point and
           // tcgen05.mma instructions of one thread execute in issue order, so no barrier is needed
           const int b = gg & 1;
+          for (int half = 0; half < (kPrecise ? 2 : 1); ++half)      // K^ hi chunks (x Qh [, x Ql]), then K^ lo (x Qh)
           for (int kc = 0; kc < Cfg::kKChunks; ++kc) {
             const int s = it % Cfg::kStages;
             ptx::mbar_wait(full_bar(s), (it / Cfg::kStages) & 1);
@@ -403,7 +445,13 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
             const uint64_t bd = ptx::umma_desc_sw128(ring + s * kChunkBytes);
 #pragma unroll
             for (int k = 0; k < 4; ++k)
-              ptx::umma_f16_ss(tmem_base + b * kTileP, ad + 2 * k, bd + 2 * k, idesc_qk, (kc | k) != 0);
+              ptx::umma_f16_ss(tmem_base + b * kTileP, ad + 2 * k, bd + 2 * k, idesc_qk, (half | kc | k) != 0);
+            if (kPrecise && half == 0) {
+              const uint64_t al = ptx::umma_desc_sw128(q_smem + Cfg::kQTileBytes + kc * Cfg::kQChunkBytes);
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                ptx::umma_f16_ss(tmem_base + b * kTileP, al + 2 * k, bd + 2 * k, idesc_qk, 1u);
+            }
             release(empty_bar(s));
             ++it;
           }
@@ -419,6 +467,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
           ptx::mbar_wait(p_full(b), (gg >> 1) & 1);
           ptx::tc_fence_after();
           HOP_TRACE(0, j, 2);
+          for (int half = 0; half < (kPrecise ? 2 : 1); ++half)      // read-out operand hi, then lo
           for (int kc = 0; kc < 2; ++kc) {
             // one read-out chunk = D rows x 64 patterns = kBStages consecutive (pair-aligned) ring stages
             const int s = it % Cfg::kStages;
@@ -431,7 +480,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
             const uint64_t bd = ptx::umma_desc_sw128(ring + s * kChunkBytes);
 #pragma unroll
             for (int k = 0; k < 4; ++k)
-              ptx::umma_f16_ts(tmem_base + kTmemO, at + 8 * k, bd + 2 * k, idesc_pv, (j | kc | k) != 0);
+              ptx::umma_f16_ts(tmem_base + kTmemO, at + 8 * k, bd + 2 * k, idesc_pv, (j | half | kc | k) != 0);
             for (int bs = 0; bs < Cfg::kBStages; ++bs) {
               release(empty_bar(it % Cfg::kStages));
               ++it;
@@ -545,6 +594,11 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
               const uint32_t hi = pack16<kBf16>(xv[u][v].z * kLog2e, xv[u][v].w * kLog2e);
               const uint32_t addr = q_smem + (e >> 6) * Cfg::kQChunkBytes + sw128_off(r, (e & 63) >> 3) + ((e & 4) << 1);
               asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr), "r"(lo), "r"(hi) : "memory");
+              if constexpr (kPrecise) {         // second copy of the tile: what the 16-bit words above lost
+                const uint32_t rlo = pack16_lo<kBf16>(xv[u][v].x * kLog2e, xv[u][v].y * kLog2e, lo);
+                const uint32_t rhi = pack16_lo<kBf16>(xv[u][v].z * kLog2e, xv[u][v].w * kLog2e, hi);
+                asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr + Cfg::kQTileBytes), "r"(rlo), "r"(rhi) : "memory");
+              }
             }
           }
         }
@@ -863,6 +917,8 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
   const int nt = min(a.tiles_per_split, nt_total - t0);
 
   if (threadIdx.x == 0) {
+    if (a.zero_words && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0)
+      *reinterpret_cast<uint4*>(a.zero_words) = make_uint4(0u, 0u, 0u, 0u);
     for (int s = 0; s < Cfg::kStages; ++s) { ptx::mbar_init(full_bar(s), 1); ptx::mbar_init(empty_bar(s), 1); }
     for (int b = 0; b < 2; ++b) {
       ptx::mbar_init(s_full(b), 1);
@@ -1364,12 +1420,22 @@ int make_map(CUtensorMap* m, const void* base, int rows, int cols, int box_rows,
   return HOP_OK;
 }
 
-template <int H, int DV, bool kBf16, int kCluster, bool kPair>
-int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
-  using Cfg = TcCfg<H, DV>;
+// internal per-launch switches of launch_tc_one (not part of TcPassArgs: they belong to one launch of a call)
+struct TcLaunchOpt {
+  bool precise;       // hi + lo operand pairs (update passes of T >= 2)
+  bool allow_streamk; // false for every launch of the one-launch-per-pass form (its workspace is sized for the plain grid
+                      // and its accumulation chains are capped at kMaxChainTilesUpdate tiles)
+  uint32_t* zero_words;
+};
+
+template <int H, int DV, bool kBf16, int kCluster, bool kPair, bool kPrecise>
+int launch_d(const TcPassArgs& a, int splits, const TcLaunchOpt& opt, cudaStream_t st) {
+  using Cfg = TcCfg<H, DV, kPrecise>;
   const int ppad = padded_patterns(a.p);
   if (a.update_steps > 0 && H != DV) HOP_FAIL(HOP_ERR_UNSUPPORTED, "on-chip retrieve updates need H == DV (internal)");
-  CUtensorMap tk, tkt, tvt;
+  if (kPrecise && (a.update_steps > 0 || !a.k16lo || !a.kt16lo))
+    HOP_FAIL(HOP_ERR_BAD_ARG, "hi + lo update passes are separate launches and need the k16lo / kt16lo packs");
+  CUtensorMap tk, tkt, tvt, tklo, tblo;
   // TMA boxes: pair = this CTA's half of a tile (64 patterns of K^, DV/2 rows of V^T); else 1/kCluster of a stage
   const int k_rows = kPair ? kTileP / 2 : kTileP / kCluster;
   const int b_rows = kPair ? DV / 2 : Cfg::kBRows / kCluster;
@@ -1377,6 +1443,12 @@ int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
   HOP_TRY(make_map(&tvt, a.vt16, a.dv, ppad, b_rows, a.bf16));
   if (a.update_steps > 0) HOP_TRY(make_map(&tkt, a.kt16, H, ppad, b_rows, a.bf16));
   else tkt = tvt;
+  if (kPrecise) {
+    HOP_TRY(make_map(&tklo, a.k16lo, ppad, H, k_rows, a.bf16));
+    HOP_TRY(make_map(&tblo, a.kt16lo, a.dv, ppad, b_rows, a.bf16));   // (a precise launch reads out over K^: vt16 = kt16)
+  } else {
+    tklo = tk; tblo = tvt;
+  }
 
   TcKernelArgs k{};
   k.x_raw = a.x_raw; k.lnq_w = a.lnq_w; k.lnq_b = a.lnq_b; k.ln_eps = a.ln_eps; k.has_ln = a.has_ln; k.beta = a.beta;
@@ -1387,14 +1459,16 @@ int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
   k.splits = (nt_total + k.tiles_per_split - 1) / k.tiles_per_split;   // every split owns >= 1 tile
   k.retrieved = a.retrieved; k.qsave = a.qsave; k.lse = a.lse; k.argmax = a.argmax; k.rowmax = a.rowmax;
   k.pattern_offset = a.pattern_offset;
-  auto* kern = hop_fwd_tc_kernel<H, DV, kBf16, kCluster, kPair>;
+  k.zero_words = opt.zero_words;
+  auto* kern = hop_fwd_tc_kernel<H, DV, kBf16, kCluster, kPair, kPrecise>;
   const int row_tiles = (a.n + Cfg::kRows - 1) / Cfg::kRows;
   const int row_groups = (row_tiles + kCluster - 1) / kCluster;
 
   // ---- stream-K form: one contiguous share of the (row group x tile) units per resident cluster
   StreamKPlan sk{};
   constexpr int kZ = H / DV;           // read-out column chunks: every z-plane walks the same partition
-  bool streamk = kCluster <= 2 && a.update_steps == 0 && streamk_wanted(a.n, a.p, a.h, a.update_steps);
+  bool streamk = !kPrecise && opt.allow_streamk && a.update_steps == 0 &&
+                 streamk_wanted(a.n, a.p, a.h, a.update_steps, a.tune);
   if (streamk) {
     HOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     cudaLaunchConfig_t oc{};
@@ -1436,7 +1510,7 @@ int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
       cudaLaunchConfig_t cfg = oc;
       cfg.gridDim = dim3(n_clusters * kCluster, 1, kZ);
       cfg.stream = st;
-      HOP_CUDA(cudaLaunchKernelEx(&cfg, kern, tk, tkt, tvt, k));
+      HOP_CUDA(cudaLaunchKernelEx(&cfg, kern, tk, tkt, tvt, tklo, tblo, k));
       HOP_LAUNCH_CHECK("hop_fwd_tc_kernel");
       const int threads = 256, rows_per_block = threads / 32;
       tc_combine_streamk_kernel<H><<<(a.n + rows_per_block - 1) / rows_per_block, threads, 0, st>>>(
@@ -1471,7 +1545,7 @@ int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = kCluster; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr; cfg.numAttrs = 1;
-  HOP_CUDA(cudaLaunchKernelEx(&cfg, kern, tk, tkt, tvt, k));
+  HOP_CUDA(cudaLaunchKernelEx(&cfg, kern, tk, tkt, tvt, tklo, tblo, k));
   HOP_LAUNCH_CHECK("hop_fwd_tc_kernel");
   if (k.splits > 1) {
     const int threads = 256, rows_per_block = threads / 32;
@@ -1485,7 +1559,7 @@ int launch_d(const TcPassArgs& a, int splits, cudaStream_t st) {
 
 // 64-rows-per-CTA pair form (hop_fwd_tc64_kernel): plain grid (row pairs x pattern splits x column chunks), T = 0
 template <int H, int DV, int TP, bool kBf16>
-int launch_h64(const TcPassArgs& a, int splits, cudaStream_t st) {
+int launch_h64(const TcPassArgs& a, int splits, const TcLaunchOpt& opt, cudaStream_t st) {
   using Cfg = Tc64Cfg<H, DV, TP>;
   const int ppad = padded_patterns(a.p);
   if (a.update_steps > 0) HOP_FAIL(HOP_ERR_UNSUPPORTED, "the 64-row form runs retrieve updates as separate launches (internal)");
@@ -1501,6 +1575,7 @@ int launch_h64(const TcPassArgs& a, int splits, cudaStream_t st) {
   k.splits = (nt_total + k.tiles_per_split - 1) / k.tiles_per_split;
   k.retrieved = a.retrieved; k.qsave = a.qsave; k.lse = a.lse; k.argmax = a.argmax; k.rowmax = a.rowmax;
   k.pattern_offset = a.pattern_offset;
+  k.zero_words = opt.zero_words;
   if (k.splits > 1) {
     const size_t need = ws_for_splits_fwd(splits, a.n, a.dv);
     if (!a.ws || a.ws_bytes < need)
@@ -1548,24 +1623,29 @@ extern "C" int hop_sm100_debug_trace(long long* dst_host, int n) {
 
 bool tc_supported(int h, int dv) { return h == dv && (h == 64 || h == 128 || h == 256 || h == 512 || h == 1024); }
 
-// D >= 512 runs the 64-rows-per-CTA pair form (hop_fwd_tc64_kernel); knob HOP_TC_HALFM = 0 keeps the 128-row
-// kernel with its recomputed score tiles (D = 512) / discarded half-MMAs (D = 1024) for comparison.
-static inline bool tc_halfm(int d) {
-  if (d < 512) return false;
-  const char* e = getenv("HOP_TC_HALFM");
-  return !(e && atoi(e) == 0);
-}
+// D >= 512 runs the 64-rows-per-CTA pair form (hop_fwd_tc64_kernel); HOP_TUNE_ROWS128 keeps the 128-row kernel with its
+// recomputed score tiles (D = 512) / discarded half-MMAs (D = 1024) for comparison.
+static inline bool tc_halfm(int d, const TcTune& t) { return d >= 512 && !(t.flags & HOP_TUNE_ROWS128); }
 
 // query rows per CTA: 64 in the pair form above and under the 1024-wide Q tile of the 128-row kernel (TcCfg::kRows)
-static inline int tc_rows(int d) { return (tc_halfm(d) || d > 512) ? 64 : kTileM; }
+static inline int tc_rows(int d, const TcTune& t) { return (tc_halfm(d, t) || d > 512) ? 64 : kTileM; }
 
 // read-out column chunks (gridDim.z): the O accumulator of one CTA holds at most 256 fp32 TMEM columns -- 256
 // read-out columns in the 128-row kernel, 512 in the 64-row pair form
-static inline int tc_dv_chunks(int d) { return tc_halfm(d) ? d / 512 : (d > 256 ? d / 256 : 1); }
+static inline int tc_dv_chunks(int d, const TcTune& t) { return tc_halfm(d, t) ? d / 512 : (d > 256 ? d / 256 : 1); }
+
+// Update passes with hi + lo operand pairs (TcCfg<.., kPrecise>): default for T >= 2 at D <= 256.  The retrieve
+// iteration amplifies operand rounding by its gain beta w (1 - w) |k|^2 per pass (w = softmax weight of the nearest
+// pattern): at the bifurcation of BASELINE config 5's recipe (P = 256k, D = 256: w ~ 0.79, gain ~ 2.7) plain 16-bit
+// operands end at 3.3e-3 after three updates, the pairs at 2e-4 (CPU emulation of both: DESIGN.md 4.1).  D >= 512 is
+// contractive in that recipe (w ~ 0.997) and keeps plain operands.
+bool tc_precise_updates(int d, int update_steps, const TcTune& t) {
+  return update_steps >= 2 && d <= 256 && !(t.flags & HOP_TUNE_PLAIN_UPDATES);
+}
 
 // Retrieve updates run as one launch per pass (state through the fp32 workspace buffers, every pass free to
-// split the pattern axis) instead of on-chip in one persistent launch.  Always at D = 512 (a CTA holds 256 of
-// the 512 state columns).  Knob for experiments: HOP_TC_MULTI = 0 | 1.
+// split the pattern axis) instead of on-chip in one persistent launch.  Always at D >= 512 (a CTA holds part of the
+// state columns) and for the hi + lo update passes.  HOP_TUNE_MULTI_ON / _OFF force it for experiments.
 //
 // Also for D <= 256 once one CTA would sweep more than 512 pattern tiles (P > 64k): the tensor core adds into its
 // fp32 accumulator with truncation, a bias that grows with the length of the accumulation chain (measured: the
@@ -1575,26 +1655,35 @@ static inline int tc_dv_chunks(int d) { return tc_halfm(d) ? d / 512 : (d > 256 
 constexpr int kMaxTilesOnChipUpdates = 512;
 constexpr int kMaxChainTilesUpdate = 256;    // pattern tiles one CTA accumulates when T > 0 (multi-launch form)
 constexpr int kMaxChainTilesReadout = 512;   // ... when T = 0 (errors are not amplified)
-static inline bool tc_multi_launch(int p, int d, int update_steps) {
+static inline bool tc_multi_launch(int p, int d, int update_steps, const TcTune& t) {
   if (update_steps <= 0) return false;
-  if (d >= 512) return true;
-  if (const char* e = getenv("HOP_TC_MULTI")) return atoi(e) != 0;
+  if (d >= 512 || tc_precise_updates(d, update_steps, t)) return true;
+  if (t.flags & HOP_TUNE_MULTI_ON) return true;
+  if (t.flags & HOP_TUNE_MULTI_OFF) return false;
   return padded_patterns(p) / kTileP > kMaxTilesOnChipUpdates;
 }
 
+// tcgen05 CTA pairs (cta_group::2): on for D = 256 when there are at least two row tiles (HOP_TUNE_PAIR_ON / _OFF
+// force it for every D <= 256).  Measured (r01, P = 64k / 256k): D = 256 1174 -> 1220 / 1226 -> 1367 TFLOP/s; D = 128
+// and 64 are MUFU-bound and do not gain (824 -> 798, 440 -> 438).
+bool tc_use_pair(int n, int d, const TcTune& t) {
+  if (tc_halfm(d, t)) return true;
+  if (t.flags & HOP_TUNE_PAIR_ON) return n > tc_rows(d, t);
+  if (t.flags & HOP_TUNE_PAIR_OFF) return false;
+  return n > tc_rows(d, t) && d >= 256;
+}
+static inline int tc_cluster(int n, int d, const TcTune& t) { return tc_use_pair(n, d, t) ? 2 : 1; }
+
 // Pattern splits per 128-row tile: the smallest count that fills >= 95 % of the last wave of SMs
-// (on-chip retrieve updates need the full softmax per pass, so T > 0 never splits; D = 512 runs its updates as
-// separate launches and may split every one of them).
-int tc_choose_splits(int n, int p, int d, int update_steps) {
-  if (update_steps > 0 && !tc_multi_launch(p, d, update_steps)) return 1;
+// (on-chip retrieve updates need the full softmax per pass, so T > 0 never splits there; the one-launch-per-pass
+// form may split every launch).
+int tc_choose_splits(int n, int p, int d, int update_steps, const TcTune& t) {
+  if (update_steps > 0 && !tc_multi_launch(p, d, update_steps, t)) return 1;
   const int nt_all = padded_patterns(p) / kTileP;
-  if (const char* e = getenv("HOP_TC_SPLITS")) {          // test knob: force a split count
-    const int s = atoi(e);
-    if (s >= 1) return s < nt_all ? s : nt_all;
-  }
+  if (t.splits >= 1) return t.splits < nt_all ? t.splits : nt_all;      // forced (tests)
   const int sms = num_sms();
-  const int cl = tc_choose_cluster(n, d);
-  const int row_tiles = ((n + tc_rows(d) - 1) / tc_rows(d) + cl - 1) / cl * cl * tc_dv_chunks(d);
+  const int cl = tc_cluster(n, d, t);
+  const int row_tiles = ((n + tc_rows(d, t) - 1) / tc_rows(d, t) + cl - 1) / cl * cl * tc_dv_chunks(d, t);
   const int nt_total = padded_patterns(p) / kTileP;
   const int chain = update_steps > 0 ? kMaxChainTilesUpdate : kMaxChainTilesReadout;
   const int min_splits = (nt_total + chain - 1) / chain;            // accuracy: bound the accumulation chain
@@ -1613,30 +1702,6 @@ int tc_choose_splits(int n, int p, int d, int update_steps) {
   return best;
 }
 
-// tcgen05 CTA pairs (cta_group::2): on for D = 256 when there are at least two row tiles (knob: HOP_TC_PAIR =
-// 0 | 1 forces it off / on for every D).  Measured (r01, P = 64k / 256k): D = 256 1174 -> 1220 / 1226 -> 1367
-// TFLOP/s; D = 128 and 64 are MUFU-bound and do not gain (824 -> 798, 440 -> 438).
-bool tc_use_pair(int n, int d) {
-  if (tc_halfm(d)) return true;
-  if (const char* e = getenv("HOP_TC_PAIR")) return atoi(e) != 0 && n > tc_rows(d);
-  return n > tc_rows(d) && d >= 256;
-}
-
-// CTAs per cluster sharing the streamed operands through TMA multicast (knob: HOP_TC_CLUSTER = 1 | 2 | 4).
-// Measured on B200 (r01): no gain -- the L2 already de-duplicates the unicast streams (1169 / 1195 / 1099
-// TFLOP/s at cluster 1 / 2 / 4, P=64k D=256), so the default stays 1.
-int tc_choose_cluster(int n, int d) {
-  if (tc_use_pair(n, d)) return 2;
-  const int row_tiles = (n + tc_rows(d) - 1) / tc_rows(d);
-  int want = 1;
-  if (const char* e = getenv("HOP_TC_CLUSTER")) {
-    const int c = atoi(e);
-    if (c == 1 || c == 2 || c == 4) want = c;
-  }
-  while (want > 1 && row_tiles < want) want >>= 1;
-  return want;
-}
-
 static size_t ws_for_splits(int splits, int n, int d);
 namespace { size_t ws_for_splits_fwd(int splits, int n, int d) { return ws_for_splits(splits, n, d); } }
 static size_t ws_for_splits(int splits, int n, int d) {
@@ -1645,66 +1710,73 @@ static size_t ws_for_splits(int splits, int n, int d) {
   return round_up_sz(rows * d * sizeof(float), 256) + 3 * round_up_sz(rows * sizeof(float), 256);
 }
 
-// Stream-K scheduling of the T = 0 forward (knob: HOP_TC_STREAMK = 0 | 1): used when the plain grid would give
+// Stream-K scheduling of the T = 0 forward (HOP_TUNE_STREAMK_ON / _OFF force it): used when the plain grid would give
 // every CTA a short pattern range (fixed prologue / epilogue cost per CTA, P = 64k: 64 tiles each) and the share
-// of one cluster stays within the accumulation-chain cap.
-static bool streamk_ok(int n, int p, int d, int update_steps) {
-  if (update_steps != 0 || getenv("HOP_TC_SPLITS")) return false;
-  if (d > 512 || tc_halfm(d)) return false;  // (the partial-slot arithmetic assumes 128-row tiles)
-  const int cl = tc_choose_cluster(n, d);
-  if (cl > 2) return false;
+// of one cluster stays within the accumulation-chain cap.  Never for a launch of the one-launch-per-pass form.
+static bool streamk_ok(int n, int p, int d, int update_steps, const TcTune& t) {
+  if (update_steps != 0 || t.splits >= 1 || (t.flags & HOP_TUNE_STREAMK_OFF)) return false;
+  if (d > 512 || tc_halfm(d, t)) return false;  // (the partial-slot arithmetic assumes 128-row tiles)
+  const int cl = tc_cluster(n, d, t);
   const int sms = num_sms();
   const long long nt_total = padded_patterns(p) / kTileP;
   const long long row_groups = ((n + kTileM - 1) / kTileM + cl - 1) / cl;
-  const int planes = sms / cl / tc_dv_chunks(d);     // clusters per read-out column chunk
+  const int planes = sms / cl / tc_dv_chunks(d, t);     // clusters per read-out column chunk
   const long long share = row_groups * nt_total / (planes > 0 ? planes : 1);
-  if (const char* e = getenv("HOP_TC_STREAMK")) return atoi(e) != 0;
+  if (t.flags & HOP_TUNE_STREAMK_ON) return true;
   // The clusters of a static partition sit at different pattern positions, so together they stream ALL of K^ / V^
   // at once: that only works out of the L2 (126 MB).  Measured at D = 512, P = 64k (128 MB of packs): 0.61 -> 0.55.
   const long long pack_bytes = (long long)padded_patterns(p) * 2 * d * 2;
   if (pack_bytes > (96ll << 20)) return false;
   return share >= 200 && share <= 2 * kMaxChainTilesReadout;   // (measured: below ~200 tiles per cluster the plain grid wins)
 }
-namespace { bool streamk_wanted(int n, int p, int d, int update_steps) { return streamk_ok(n, p, d, update_steps); } }
+namespace {
+bool streamk_wanted(int n, int p, int d, int update_steps, const TcTune& t) { return streamk_ok(n, p, d, update_steps, t); }
+}
 
 // upper bound of the stream-K partial slots: sum of segments <= row groups + 3 x clusters
-static size_t streamk_ws(int n, int d) {
-  const int cl = tc_choose_cluster(n, d);
+static size_t streamk_ws(int n, int d, const TcTune& t) {
+  const int cl = tc_cluster(n, d, t);
   const size_t row_groups = ((size_t)(n + kTileM - 1) / kTileM + cl - 1) / cl;
   const size_t rows = (row_groups + 3 * (size_t)(num_sms() / cl)) * cl * kTileM;
   return round_up_sz(rows * d * sizeof(float), 256) + 3 * round_up_sz(rows * sizeof(float), 256);
 }
 
-size_t tc_forward_workspace(int n, int p, int d, int update_steps) {
-  const size_t plain = ws_for_splits(tc_choose_splits(n, p, d, update_steps), n, d);
-  if (!streamk_ok(n, p, d, update_steps)) return plain;
-  const size_t sk = streamk_ws(n, d);
+// Covers every launch form launch_tc_forward can choose for (n, p, d, T): the plain grid's split partials (all
+// launches of one call share one split count) and, for the single T = 0 launch only, the stream-K slots.
+size_t tc_forward_workspace(int n, int p, int d, int update_steps, const TcTune& t) {
+  const size_t plain = ws_for_splits(tc_choose_splits(n, p, d, update_steps, t), n, d);
+  if (!streamk_ok(n, p, d, update_steps, t)) return plain;
+  const size_t sk = streamk_ws(n, d, t);
   return sk > plain ? sk : plain;
 }
 
-static int launch_tc_one(const TcPassArgs& a, int splits, cudaStream_t st) {
-  if (tc_halfm(a.h)) {
-    if (a.h == 512) {
-      const char* e = getenv("HOP_TC64_TILE");           // experiment knob: 128-pattern score tiles at D = 512
-      if (e && atoi(e) == 128)
-        return a.bf16 ? launch_h64<512, 512, 128, true>(a, splits, st) : launch_h64<512, 512, 128, false>(a, splits, st);
-      return a.bf16 ? launch_h64<512, 512, 256, true>(a, splits, st) : launch_h64<512, 512, 256, false>(a, splits, st);
-    }
-    {
-      const char* e = getenv("HOP_TC64_TILE");           // experiment knob: 256-pattern score tiles at D = 1024 (4-stage ring)
-      if (e && atoi(e) == 256 && !a.bf16) return launch_h64<1024, 512, 256, false>(a, splits, st);
-    }
-    return a.bf16 ? launch_h64<1024, 512, 128, true>(a, splits, st) : launch_h64<1024, 512, 128, false>(a, splits, st);
+static int launch_tc_one(const TcPassArgs& a, int splits, const TcLaunchOpt& opt, cudaStream_t st) {
+  if (tc_halfm(a.h, a.tune)) {
+    // D = 512: 256-pattern score tiles, one 512-column read-out; D = 1024: 128-pattern tiles, two read-out chunks
+    if (a.h == 512)
+      return a.bf16 ? launch_h64<512, 512, 256, true>(a, splits, opt, st) : launch_h64<512, 512, 256, false>(a, splits, opt, st);
+    return a.bf16 ? launch_h64<1024, 512, 128, true>(a, splits, opt, st) : launch_h64<1024, 512, 128, false>(a, splits, opt, st);
   }
-  const int cl = tc_choose_cluster(a.n, a.h);
-  const bool pair = tc_use_pair(a.n, a.h);
-#define HOP_TC_DISPATCH(HH, DVC, BF)                                            \
-  do {                                                                          \
-    if (pair) return launch_d<HH, DVC, BF, 2, true>(a, splits, st);             \
-    if (cl == 4) return launch_d<HH, DVC, BF, 4, false>(a, splits, st);         \
-    if (cl == 2) return launch_d<HH, DVC, BF, 2, false>(a, splits, st);         \
-    return launch_d<HH, DVC, BF, 1, false>(a, splits, st);                      \
+  const bool pair = tc_use_pair(a.n, a.h, a.tune);
+#define HOP_TC_DISPATCH(HH, DVC, BF)                                                        \
+  do {                                                                                      \
+    if (pair) return launch_d<HH, DVC, BF, 2, true, false>(a, splits, opt, st);             \
+    return launch_d<HH, DVC, BF, 1, false, false>(a, splits, opt, st);                      \
   } while (0)
+#define HOP_TC_DISPATCH_PRECISE(HH)                                                         \
+  do {                                                                                      \
+    if (pair) return launch_d<HH, HH, false, 2, true, true>(a, splits, opt, st);            \
+    return launch_d<HH, HH, false, 1, false, true>(a, splits, opt, st);                     \
+  } while (0)
+  if (opt.precise) {
+    if (a.bf16) HOP_FAIL(HOP_ERR_UNSUPPORTED, "hi + lo update passes are built for fp16-encoded operands");
+    switch (a.h) {
+      case 64: HOP_TC_DISPATCH_PRECISE(64);
+      case 128: HOP_TC_DISPATCH_PRECISE(128);
+      case 256: HOP_TC_DISPATCH_PRECISE(256);
+      default: HOP_FAIL(HOP_ERR_UNSUPPORTED, "hi + lo update passes are built for D <= 256");
+    }
+  }
   if (a.bf16) {
     switch (a.h) {
       case 64: HOP_TC_DISPATCH(64, 64, true);
@@ -1722,17 +1794,22 @@ static int launch_tc_one(const TcPassArgs& a, int splits, cudaStream_t st) {
     default: HOP_TC_DISPATCH(1024, 256, false);
   }
 #undef HOP_TC_DISPATCH
+#undef HOP_TC_DISPATCH_PRECISE
 }
 
 int launch_tc_forward(const TcPassArgs& a, cudaStream_t st) {
   if (!tc_supported(a.h, a.dv)) HOP_FAIL(HOP_ERR_UNSUPPORTED, "tensor-core path needs H == Dv in {64,128,256,512,1024}");
   if (!a.retrieved) HOP_FAIL(HOP_ERR_BAD_ARG, "tensor-core forward: retrieved is NULL");
-  const int splits = tc_choose_splits(a.n, a.p, a.h, a.update_steps);   // one count for every pass of this call
-  if (!tc_multi_launch(a.p, a.h, a.update_steps)) return launch_tc_one(a, splits, st);
-  // D = 512: the state of a retrieve update is 512 columns wide but one CTA accumulates 256 of them, so every
-  // update is its own launch (read-out operand = K^T, result beta * A K^ = the next launch's prepared state)
+  const int splits = tc_choose_splits(a.n, a.p, a.h, a.update_steps, a.tune);   // one count for every pass of this call
+  if (!tc_multi_launch(a.p, a.h, a.update_steps, a.tune))
+    return launch_tc_one(a, splits, TcLaunchOpt{false, true, a.zero_words}, st);
+  // one launch per pass: read-out operand = K^T, result beta * A K^ = the next launch's prepared state (fp32).
+  // No stream-K here: the workspace is sized for `splits` partials and the chains stay within kMaxChainTilesUpdate.
   if (!a.kt16 || !a.qtmp[0] || !a.qtmp[1])
     HOP_FAIL(HOP_ERR_WORKSPACE, "tensor-core forward with one launch per retrieve update needs kt16 and the two state buffers");
+  const bool precise = tc_precise_updates(a.h, a.update_steps, a.tune) && !a.bf16;
+  if (precise && (!a.k16lo || !a.kt16lo))
+    HOP_FAIL(HOP_ERR_BAD_ARG, "T >= 2 at D <= 256 runs its update passes with hi + lo operand pairs: k16lo / kt16lo are NULL");
   const float* qs = a.qs;
   const float* x_raw = a.x_raw;
   for (int t = 0; t < a.update_steps; ++t) {
@@ -1740,12 +1817,12 @@ int launch_tc_forward(const TcPassArgs& a, cudaStream_t st) {
     b.x_raw = x_raw; b.qs = qs; b.update_steps = 0; b.vt16 = a.kt16; b.bias = nullptr; b.out_scale = a.beta;
     b.retrieved = (qs == a.qtmp[0]) ? a.qtmp[1] : a.qtmp[0];
     b.qsave = nullptr; b.lse = nullptr; b.argmax = nullptr; b.rowmax = nullptr;
-    HOP_TRY(launch_tc_one(b, splits, st));
+    HOP_TRY(launch_tc_one(b, splits, TcLaunchOpt{precise, false, t == 0 ? a.zero_words : nullptr}, st));
     qs = b.retrieved; x_raw = nullptr;
   }
   TcPassArgs b = a;
   b.x_raw = nullptr; b.qs = qs; b.update_steps = 0;
-  return launch_tc_one(b, splits, st);
+  return launch_tc_one(b, splits, TcLaunchOpt{false, false, nullptr}, st);
 }
 
 }  // namespace hop
