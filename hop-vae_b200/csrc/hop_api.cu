@@ -60,7 +60,12 @@ int validate_desc(const hop_desc* d) {
     HOP_FAIL(HOP_ERR_BAD_SHAPE, "non-positive dimension (N=%d P=%d Din=%d H=%d Dv=%d)", d->n_rows, d->n_patterns,
              d->d_in, d->d_assoc, d->d_v);
   if ((d->flags & HOP_F_OUT_PROJ) && d->d_out <= 0) HOP_FAIL(HOP_ERR_BAD_SHAPE, "HOP_F_OUT_PROJ with d_out=%d", d->d_out);
-  if (d->update_steps < 0) HOP_FAIL(HOP_ERR_BAD_ARG, "update_steps must be >= 0 (fixed-count semantics)");
+  if (!(d->update_eps >= 0.f)) HOP_FAIL(HOP_ERR_BAD_ARG, "update_eps must be >= 0");
+  if (d->update_steps < 0 && !(d->update_eps > 0.f))
+    HOP_FAIL(HOP_ERR_BAD_ARG, "update_steps < 0 (iterate until convergence) needs update_eps > 0");
+  if (d->rows_per_item < 0 || (d->rows_per_item > 0 && d->n_rows % d->rows_per_item != 0))
+    HOP_FAIL(HOP_ERR_BAD_SHAPE, "rows_per_item (%d) must divide n_rows (%d)", d->rows_per_item, d->n_rows);
+  if (d->tune_splits < 0) HOP_FAIL(HOP_ERR_BAD_ARG, "tune_splits must be >= 0");
   if (!(d->flags & HOP_F_PROJ_STATE) && d->d_assoc != d->d_in)
     HOP_FAIL(HOP_ERR_BAD_SHAPE, "static state pattern needs d_assoc == d_in (%d vs %d)", d->d_assoc, d->d_in);
   if (!(d->flags & HOP_F_PROJ_STORED) && d->d_assoc != d->d_in)
@@ -87,11 +92,27 @@ int resolve_path(const hop_desc* d) {
     }
     return d->path;
   }
-  // AUTO: exact fp32 kernels for the reference's own (launch-bound, argmax-tight) sizes and for
-  // widths the MMA cannot take; tcgen05 once the N x P score block is large.
+  // AUTO: exact fp32 kernels for the reference's own (launch-bound, argmax-tight) sizes, for widths the MMA cannot
+  // take, for update_steps < 0 and for layers whose score operands are not LayerNorm'd (fp16 encodes O(1) operands
+  // with 11 bits but saturates at 65504: without normalize_state_pattern / normalize_stored_pattern nothing bounds
+  // them, so AUTO keeps such layers in fp32 while the width allows); tcgen05 once the N x P score block is large.
   const long long np = (long long)d->n_rows * d->n_patterns;
-  if (tc_ok && (np >= (1ll << 25) || d->d_assoc > 256)) return HOP_PATH_TC_F16;   // the fp32 kernels stop at width 256
+  const bool normed = (d->flags & HOP_F_NORM_STATE) && (d->flags & HOP_F_NORM_STORED);
+  if (d->d_assoc > 256 && tc_ok) return HOP_PATH_TC_F16;          // the fp32 kernels stop at width 256
+  if (d->update_steps < 0 || !normed) return HOP_PATH_FP32_SIMT;
+  if (tc_ok && np >= (1ll << 25)) return HOP_PATH_TC_F16;
   return HOP_PATH_FP32_SIMT;
+}
+
+// maximum number of retrieve updates the fp32 path enqueues for update_steps < 0 ("until convergence"): upstream
+// loops on a host-side `.any()`; here the stop flag lives on the device and the passes behind it are identity passes
+constexpr int kMaxUpdatesUntilConverged = 64;
+static inline int simt_update_count(const hop_desc& d) { return d.update_steps < 0 ? kMaxUpdatesUntilConverged : d.update_steps; }
+static inline bool simt_stop_rule(const hop_desc& d) {
+  return d.update_eps > 0.f && (d.update_steps < 0 || d.update_steps >= 2);
+}
+static inline bool tc_exact_argmax(const hop_desc& d, const int32_t* argmax) {
+  return (d.flags & HOP_F_EXACT_ARGMAX) && argmax != nullptr;
 }
 
 }  // namespace hop
@@ -115,35 +136,84 @@ int hop_sm100_select_path(const hop_desc* desc, int32_t* path_out) {
   return HOP_OK;
 }
 
-int hop_sm100_pattern_bytes(const hop_desc* desc, size_t* khat, size_t* vhat, size_t* k16, size_t* kt16,
-                            size_t* vt16, size_t* vot16) {
+int hop_sm100_select_train_path(const hop_desc* desc, int32_t* path_out) {
   HOP_TRY(validate_desc(desc));
+  if (!path_out) HOP_FAIL(HOP_ERR_BAD_ARG, "path_out is NULL");
+  if (desc->update_steps != 0)
+    HOP_FAIL(HOP_ERR_UNSUPPORTED, "backward is implemented for update_steps == 0 (what the reference trains with)");
+  const int fwd = resolve_path(desc);
+  if (fwd < 0) return -fwd;
+  const bool tc_bwd = tc_backward_supported(desc->n_rows, desc->n_patterns, desc->d_assoc, desc->d_v) &&
+                      !(desc->tune_flags & HOP_TUNE_BWD_SIMT);
+  if (fwd != HOP_PATH_FP32_SIMT && tc_bwd) { *path_out = fwd; return HOP_OK; }
+  if (desc->d_assoc > 256 || desc->d_v > 256)
+    HOP_FAIL(HOP_ERR_UNSUPPORTED, "training at H=%d Dv=%d: the fp32 kernels stop at width 256 and the tensor-core "
+             "backward is built for H == Dv in {128, 256, 512}", desc->d_assoc, desc->d_v);
+  *path_out = HOP_PATH_FP32_SIMT;
+  return HOP_OK;
+}
+
+int hop_sm100_pattern_bytes(const hop_desc* desc, hop_pattern_sizes* sz) {
+  HOP_TRY(validate_desc(desc));
+  if (!sz) HOP_FAIL(HOP_ERR_BAD_ARG, "sizes is NULL");
   const int path = resolve_path(desc);
   if (path < 0) return -path;
   const bool tc = (path != HOP_PATH_FP32_SIMT);
   const size_t P = (size_t)desc->n_patterns, Pp = (size_t)padded_patterns(desc->n_patterns);
-  if (khat) *khat = P * desc->d_assoc * sizeof(float);
-  if (vhat) *vhat = P * desc->d_v * sizeof(float);
-  if (k16) *k16 = tc ? Pp * desc->d_assoc * 2 : 0;
-  if (kt16) *kt16 = (tc && desc->update_steps > 0) ? Pp * desc->d_assoc * 2 : 0;
-  if (vt16) *vt16 = tc ? Pp * desc->d_v * 2 : 0;
-  if (vot16) *vot16 = (tc && out_proj_foldable(*desc)) ? Pp * desc->d_out * 2 : 0;
+  const bool train = tc && (desc->flags & HOP_F_TRAIN);
+  const bool precise = tc && path == HOP_PATH_TC_F16 && tc_precise_updates(desc->d_assoc, desc->update_steps, tune_of(*desc));
+  *sz = hop_pattern_sizes{};
+  sz->khat = P * desc->d_assoc * sizeof(float);
+  sz->vhat = P * desc->d_v * sizeof(float);
+  sz->k16 = tc ? Pp * desc->d_assoc * 2 : 0;
+  sz->kt16 = (tc && (desc->update_steps > 0 || train)) ? Pp * desc->d_assoc * 2 : 0;
+  sz->vt16 = tc ? Pp * desc->d_v * 2 : 0;
+  sz->vot16 = (tc && out_proj_foldable(*desc)) ? Pp * desc->d_out * 2 : 0;
+  sz->k16lo = precise ? Pp * desc->d_assoc * 2 : 0;
+  sz->kt16lo = precise ? Pp * desc->d_assoc * 2 : 0;
+  sz->v16 = train ? Pp * desc->d_v * 2 : 0;
+  sz->kstats = tc ? 4 * sizeof(float) : 0;
   return HOP_OK;
 }
+
+namespace {
+// forward workspace: [q state 0][q state 1][read-out][tensor-core split partials][repair][final state][lse, rowmax]
+// (fp32 path with the stop rule: [q state 0][q state 1][read-out][row scratch (N)][flag])
+struct FwdWs {
+  size_t q, r, tc, repair, qfinal, stat, total;   // sizes of the regions (q: one state buffer)
+};
+FwdWs fwd_ws(const hop_desc& d, int path, bool exact) {
+  FwdWs w{};
+  const size_t N = (size_t)d.n_rows;
+  w.q = round_up_sz(N * d.d_assoc * sizeof(float), 256);
+  w.r = round_up_sz(N * d.d_v * sizeof(float), 256);
+  if (path != HOP_PATH_FP32_SIMT) {
+    w.tc = tc_forward_workspace(d.n_rows, d.n_patterns, d.d_assoc, d.update_steps, tune_of(d));
+    if (exact) {
+      w.repair = repair_workspace_bytes(d.n_rows, d.d_assoc);
+      w.qfinal = d.update_steps > 0 ? w.q : 0;
+      w.stat = round_up_sz(N * sizeof(float), 256);
+    }
+  } else if (simt_stop_rule(d)) {
+    w.stat = round_up_sz(N * sizeof(float), 256);
+  }
+  w.total = 2 * w.q + w.r + w.tc + w.repair + w.qfinal + 2 * w.stat + (w.stat ? 256 : 0);
+  return w;
+}
+}  // namespace
 
 int hop_sm100_workspace_bytes(const hop_desc* desc, int for_backward, size_t* bytes) {
   HOP_TRY(validate_desc(desc));
   if (!bytes) HOP_FAIL(HOP_ERR_BAD_ARG, "bytes is NULL");
-  const size_t N = (size_t)desc->n_rows;
   if (for_backward) {
     *bytes = simt_backward_workspace(*desc);
+    if (tc_backward_supported(desc->n_rows, desc->n_patterns, desc->d_assoc, desc->d_v) && !(desc->tune_flags & HOP_TUNE_BWD_SIMT))
+      *bytes += tc_backward_workspace(desc->n_rows, desc->n_patterns, desc->d_assoc, desc->d_v);
   } else {
-    // two ping-pong query-state buffers (N,H) + one read-out buffer (N,Dv), each 256-byte aligned
-    *bytes = 2 * round_up_sz(N * desc->d_assoc * sizeof(float), 256) + round_up_sz(N * desc->d_v * sizeof(float), 256);
     const int path = resolve_path(desc);
     if (path < 0) return -path;
-    if (path != HOP_PATH_FP32_SIMT)  // partial results of the intra-GPU pattern splits
-      *bytes += tc_forward_workspace(desc->n_rows, desc->n_patterns, desc->d_assoc, desc->update_steps);
+    // (sized as if the nearest-pattern index were requested: the caller asks before it knows)
+    *bytes = fwd_ws(*desc, path, (desc->flags & HOP_F_EXACT_ARGMAX) != 0).total;
   }
   return HOP_OK;
 }
@@ -159,7 +229,14 @@ int hop_sm100_prepare_patterns(const hop_desc* desc, const hop_params* params, c
   if (path != HOP_PATH_FP32_SIMT) {
     if (!patterns->k16 || !patterns->vt16 || (desc->update_steps > 0 && !patterns->kt16))
       HOP_FAIL(HOP_ERR_BAD_ARG, "tensor-core path needs the k16 / vt16 (/ kt16 when T > 0) buffers");
-    if (!aligned16(patterns->k16) || !aligned16(patterns->vt16) || !aligned16(patterns->kt16))
+    if (path == HOP_PATH_TC_F16 && tc_precise_updates(desc->d_assoc, desc->update_steps, tune_of(*desc)) &&
+        (!patterns->k16lo || !patterns->kt16lo))
+      HOP_FAIL(HOP_ERR_BAD_ARG, "T >= 2 at D <= 256 runs its update passes with hi + lo operand pairs: k16lo / kt16lo are NULL");
+    if ((desc->flags & HOP_F_TRAIN) && (!patterns->kt16 || !patterns->v16))
+      HOP_FAIL(HOP_ERR_BAD_ARG, "HOP_F_TRAIN: the tensor-core backward needs the kt16 / v16 buffers");
+    if (!aligned16(patterns->k16) || !aligned16(patterns->vt16) || !aligned16(patterns->kt16) ||
+        !aligned16(patterns->k16lo) || !aligned16(patterns->kt16lo) || !aligned16(patterns->v16) ||
+        !aligned16(patterns->kstats))
       HOP_FAIL(HOP_ERR_BAD_ALIGN, "16-bit pattern packs must be 16-byte aligned");
     if (patterns->vot16 && (!out_proj_foldable(*desc) || !params->wo || !aligned16(patterns->vot16)))
       HOP_FAIL(HOP_ERR_BAD_ARG, "vot16 given but out_proj cannot be folded (needs HOP_F_OUT_PROJ, Dout == H == Dv, wo, alignment)");
@@ -181,24 +258,28 @@ int hop_sm100_forward(const hop_desc* desc, const hop_params* params, const hop_
   const hop_params& p = *params;
   const int path = resolve_path(desc);
   if (path < 0) return -path;
-  size_t need = 0;
-  HOP_TRY(hop_sm100_workspace_bytes(desc, 0, &need));
+  const bool tc = path != HOP_PATH_FP32_SIMT;
+  if (tc && d.update_steps < 0)
+    HOP_FAIL(HOP_ERR_UNSUPPORTED, "update_steps < 0 (iterate until convergence) runs on the fp32 path only: the 16-bit "
+                                  "score arithmetic cannot resolve update_eps-sized changes of the association");
+  const bool exact = tc && tc_exact_argmax(d, argmax);
+  const bool stop_rule = !tc && simt_stop_rule(d);
+  const FwdWs W = fwd_ws(d, path, exact);
   const bool out_proj = (d.flags & HOP_F_OUT_PROJ) != 0;
   const bool q_proj = (d.flags & HOP_F_PROJ_STATE) != 0;
-  const size_t tc_ws = (path != HOP_PATH_FP32_SIMT) ? tc_forward_workspace(d.n_rows, d.n_patterns, d.d_assoc, d.update_steps) : 0;
-  const bool need_ws = q_proj || (path == HOP_PATH_FP32_SIMT && d.update_steps > 0) || tc_ws > 0 ||
-                       (path != HOP_PATH_FP32_SIMT && d.update_steps > 0) ||
-                       (path != HOP_PATH_FP32_SIMT && out_proj && !retrieved &&
-                        !(patterns->vot16 && out_proj_foldable(d)));
-  if (need_ws && (!workspace || workspace_bytes < need))
-    HOP_FAIL(HOP_ERR_WORKSPACE, "workspace of %zu bytes needed, %zu given", need, workspace_bytes);
+  const bool need_ws = q_proj || d.update_steps != 0 || W.tc > 0 || exact ||
+                       (tc && out_proj && !retrieved && !(patterns->vot16 && out_proj_foldable(d)));
+  if (need_ws && (!workspace || workspace_bytes < W.total))
+    HOP_FAIL(HOP_ERR_WORKSPACE, "workspace of %zu bytes needed, %zu given", W.total, workspace_bytes);
   if (out_proj && (!p.wo)) HOP_FAIL(HOP_ERR_BAD_ARG, "HOP_F_OUT_PROJ set but params.wo is NULL");
   cudaStream_t st = (cudaStream_t)stream;
 
-  const size_t qbytes = round_up_sz((size_t)d.n_rows * d.d_assoc * sizeof(float), 256);
-  float* qbuf[2] = {reinterpret_cast<float*>(workspace),
-                    workspace ? reinterpret_cast<float*>(static_cast<char*>(workspace) + qbytes) : nullptr};
-  float* rbuf = workspace ? reinterpret_cast<float*>(static_cast<char*>(workspace) + 2 * qbytes) : nullptr;
+  char* wsb = static_cast<char*>(workspace);
+  auto region = [&](size_t off) -> char* { return wsb ? wsb + off : nullptr; };
+  float* qbuf[2] = {reinterpret_cast<float*>(region(0)), reinterpret_cast<float*>(region(W.q))};
+  float* rbuf = reinterpret_cast<float*>(region(2 * W.q));
+  const size_t off_tc = 2 * W.q + W.r, off_repair = off_tc + W.tc, off_qfinal = off_repair + W.repair;
+  const size_t off_stat = off_qfinal + W.qfinal;
 
   const float* qs = nullptr;  // prepared beta*Q^ when not fused
   if (q_proj) {
@@ -206,23 +287,35 @@ int hop_sm100_forward(const hop_desc* desc, const hop_params* params, const hop_
     qs = qbuf[0];
   }
 
-  if (path == HOP_PATH_FP32_SIMT) {
-    int cur = 0;  // index of the buffer holding the current state when qs != nullptr
-    for (int t = 0; t < d.update_steps; ++t) {
+  if (!tc) {
+    // fp32 path: one launch per pass.  With the stop rule (update_eps > 0 and at least two possible updates) the
+    // passes behind a converged iteration become identity passes -- decided on the device, no host synchronisation.
+    const int T = simt_update_count(d);
+    float* row_scratch = stop_rule ? reinterpret_cast<float*>(region(off_stat)) : nullptr;
+    uint32_t* stopped = stop_rule ? reinterpret_cast<uint32_t*>(region(off_stat + 2 * W.stat)) : nullptr;
+    if (stop_rule) HOP_CUDA(cudaMemsetAsync(stopped, 0, sizeof(uint32_t), st));
+    float* cur = const_cast<float*>(qs);      // buffer holding the current state (nullptr: still the raw x, fused)
+    float* prev = nullptr;
+    for (int t = 0; t < T; ++t) {
+      if (stop_rule && t >= 1)
+        HOP_TRY(launch_update_delta(cur, prev, patterns->khat, d.n_rows, d.n_patterns, d.d_assoc, d.rows_per_item,
+                                    d.update_eps, row_scratch, stopped, st));
       SimtPassArgs a{};
-      a.x_raw = qs ? nullptr : x; a.lnq_w = p.ln_state_w; a.lnq_b = p.ln_state_b; a.ln_eps = d.ln_eps;
-      a.has_ln = (d.flags & HOP_F_NORM_STATE) ? 1 : 0; a.beta = d.beta; a.qs = qs;
+      a.x_raw = cur ? nullptr : x; a.lnq_w = p.ln_state_w; a.lnq_b = p.ln_state_b; a.ln_eps = d.ln_eps;
+      a.has_ln = (d.flags & HOP_F_NORM_STATE) ? 1 : 0; a.beta = d.beta; a.qs = cur;
       a.khat = patterns->khat; a.bmat = patterns->khat;
       a.n = d.n_rows; a.p = d.n_patterns; a.h = d.d_assoc; a.dr = d.d_assoc; a.out_scale = d.beta;
-      const int nxt = qs ? (cur ^ 1) : 0;
-      a.res = qbuf[nxt];
+      float* nxt = (cur == qbuf[0]) ? qbuf[1] : qbuf[0];
+      a.res = nxt;
+      if (stop_rule && !cur) a.qsave = qbuf[1];          // the first state, needed by the check behind update 1
+      a.stopped = (stop_rule && t >= 1) ? stopped : nullptr;
       HOP_TRY(launch_simt_pass(a, st));
-      qs = qbuf[nxt];
+      prev = cur ? cur : qbuf[1];
       cur = nxt;
     }
     SimtPassArgs a{};
-    a.x_raw = qs ? nullptr : x; a.lnq_w = p.ln_state_w; a.lnq_b = p.ln_state_b; a.ln_eps = d.ln_eps;
-    a.has_ln = (d.flags & HOP_F_NORM_STATE) ? 1 : 0; a.beta = d.beta; a.qs = qs;
+    a.x_raw = cur ? nullptr : x; a.lnq_w = p.ln_state_w; a.lnq_b = p.ln_state_b; a.ln_eps = d.ln_eps;
+    a.has_ln = (d.flags & HOP_F_NORM_STATE) ? 1 : 0; a.beta = d.beta; a.qs = cur;
     a.khat = patterns->khat; a.bmat = patterns->vhat;
     a.n = d.n_rows; a.p = d.n_patterns; a.h = d.d_assoc; a.dr = d.d_v; a.out_scale = 1.f;
     a.qsave = qhat; a.lse = lse; a.argmax = argmax; a.rowmax = rowmax; a.pattern_offset = d.pattern_offset;
@@ -237,22 +330,44 @@ int hop_sm100_forward(const hop_desc* desc, const hop_params* params, const hop_
     return HOP_OK;
   }
 
-  // tensor-core path: one persistent kernel runs all T+1 passes.  With the folded operand (V^ Wo^T)^T the
-  // kernel's read-out IS the layer output; otherwise out_proj is a second (HBM-bound) launch.
+  // tensor-core path: one persistent kernel runs all T+1 passes (or one launch per pass, see launch_tc_forward).  With
+  // the folded operand (V^ Wo^T)^T the kernel's read-out IS the layer output; otherwise out_proj is a second launch.
   const bool folded = out_proj && !retrieved && patterns->vot16 && out_proj_foldable(d);
+  if (exact && (!patterns->kstats || !patterns->khat))
+    HOP_FAIL(HOP_ERR_BAD_ARG, "HOP_F_EXACT_ARGMAX needs patterns.kstats and the fp32 K^");
+  float* lse_w = lse, *rowmax_w = rowmax;
+  if (exact) {      // the certificate needs both statistics even when the caller does not ask for them
+    if (!lse_w) lse_w = reinterpret_cast<float*>(region(off_stat));
+    if (!rowmax_w) rowmax_w = reinterpret_cast<float*>(region(off_stat + W.stat));
+  }
+  float* qfinal = (exact && d.update_steps > 0) ? reinterpret_cast<float*>(region(off_qfinal)) : nullptr;
   TcPassArgs a{};
   a.x_raw = qs ? nullptr : x; a.lnq_w = p.ln_state_w; a.lnq_b = p.ln_state_b; a.ln_eps = d.ln_eps;
   a.has_ln = (d.flags & HOP_F_NORM_STATE) ? 1 : 0; a.beta = d.beta; a.qs = qs;
   a.k16 = patterns->k16; a.kt16 = patterns->kt16; a.vt16 = folded ? patterns->vot16 : patterns->vt16;
+  a.k16lo = patterns->k16lo; a.kt16lo = patterns->kt16lo;
   a.bias = folded ? p.bo : nullptr; a.out_scale = 1.f; a.qtmp[0] = qbuf[0]; a.qtmp[1] = qbuf[1];
   a.n = d.n_rows; a.p = d.n_patterns; a.h = d.d_assoc; a.dv = d.d_v; a.update_steps = d.update_steps;
   a.bf16 = (path == HOP_PATH_TC_BF16);
   a.retrieved = folded ? out : (out_proj ? (retrieved ? retrieved : rbuf) : out);
-  a.qsave = qhat; a.lse = lse; a.argmax = argmax; a.rowmax = rowmax; a.pattern_offset = d.pattern_offset;
-  a.ws = workspace ? static_cast<char*>(workspace) + 2 * qbytes + round_up_sz((size_t)d.n_rows * d.d_v * sizeof(float), 256)
-                   : nullptr;
-  a.ws_bytes = tc_ws;
+  a.qsave = qhat ? qhat : qfinal; a.lse = lse_w; a.argmax = argmax; a.rowmax = rowmax_w; a.pattern_offset = d.pattern_offset;
+  a.ws = region(off_tc);
+  a.ws_bytes = W.tc;
+  a.tune = tune_of(d);
+  a.zero_words = exact ? reinterpret_cast<uint32_t*>(region(off_repair)) : nullptr;
   HOP_TRY(launch_tc_forward(a, st));
+  if (exact) {
+    RepairArgs r{};
+    if (d.update_steps > 0) { r.qs = a.qsave; }
+    else if (qs) { r.qs = qs; }
+    else { r.x_raw = x; r.lnq_w = p.ln_state_w; r.lnq_b = p.ln_state_b; r.ln_eps = d.ln_eps; r.has_ln = a.has_ln; }
+    r.beta = d.beta;
+    r.khat = patterns->khat; r.kstats = patterns->kstats;
+    r.n = d.n_rows; r.p = d.n_patterns; r.h = d.d_assoc; r.pattern_offset = d.pattern_offset;
+    r.lse = lse_w; r.rowmax = rowmax_w; r.argmax = argmax;
+    r.ws = region(off_repair); r.ws_bytes = W.repair;
+    HOP_TRY(launch_argmax_repair(r, st));
+  }
   if (folded) return HOP_OK;
   if (out_proj) HOP_TRY(launch_linear(d.n_rows, d.d_v, d.d_out, a.retrieved, p.wo, p.bo, out, st));
   else if (retrieved && retrieved != out)

@@ -29,6 +29,9 @@ struct LnLinearArgs {
   void* y16;           // (rows_pad, dout) 16-bit or nullptr
   void* yt16;          // (dout, rows_pad) 16-bit or nullptr
   int bf16;            // 16-bit encoding: 0 = fp16 (saturating), 1 = bf16
+  void* y16lo;         // (rows_pad, dout) 16-bit: y - decode(y16), the low half of a hi + lo operand pair, or nullptr
+  void* yt16lo;        // (dout, rows_pad) same, transposed, or nullptr
+  float* norm_max;     // [1]: max over rows of ||y_row||_2 (atomic max on the float's bits; zeroed by the caller) or nullptr
 };
 
 __device__ __forceinline__ uint16_t to16(float v, int bf16) {
@@ -38,12 +41,18 @@ __device__ __forceinline__ uint16_t to16(float v, int bf16) {
   return __half_as_ushort(__float2half_rn(v));
 }
 
+__device__ __forceinline__ float from16(uint16_t w, int bf16) {
+  return bf16 ? __bfloat162float(__ushort_as_bfloat16(w)) : __half2float(__ushort_as_half(w));
+}
+// low half of a hi + lo operand pair: what the 16-bit encoding of v lost, encoded again
+__device__ __forceinline__ uint16_t to16_lo(float v, int bf16) { return to16(v - from16(to16(v, bf16), bf16), bf16); }
+
 template <int RM>
 __device__ __forceinline__ void ln_linear_body(const LnLinearArgs& a) {
   constexpr int BR = 16 * RM;
   __shared__ __align__(16) float Xs[BR * XS];
   __shared__ __align__(16) float Ws[TN * XS];
-  __shared__ float s_mean[BR], s_rstd[BR];
+  __shared__ float s_mean[BR], s_rstd[BR], s_sq[BR];
   float* Ys = Xs;  // the staged output tile aliases the input chunk (BR*YS <= BR*XS), see the barriers below
   static_assert(YS <= XS, "output staging tile must fit in the input chunk");
 
@@ -58,6 +67,7 @@ __device__ __forceinline__ void ln_linear_body(const LnLinearArgs& a) {
     if (lane == 0) {
       s_mean[r] = mean;
       s_rstd[r] = rstd;
+      s_sq[r] = 0.f;
     }
   }
   __syncthreads();
@@ -141,6 +151,8 @@ __device__ __forceinline__ void ln_linear_body(const LnLinearArgs& a) {
       const float v = (gr < a.rows) ? Ys[r * YS + c] : 0.f;
       if (a.y && gr < a.rows) a.y[(size_t)gr * a.dout + gc] = v;
       if (a.y16 && gr < a.rows_pad) reinterpret_cast<uint16_t*>(a.y16)[(size_t)gr * a.dout + gc] = to16(v, a.bf16);
+      if (a.y16lo && gr < a.rows_pad) reinterpret_cast<uint16_t*>(a.y16lo)[(size_t)gr * a.dout + gc] = to16_lo(v, a.bf16);
+      if (a.norm_max) atomicAdd(&s_sq[r], v * v);
     }
     if (a.yt16) {
       for (int idx = tid; idx < BR * TN; idx += NT) {
@@ -149,8 +161,13 @@ __device__ __forceinline__ void ln_linear_body(const LnLinearArgs& a) {
         if (gc >= a.dout || gr >= a.rows_pad) continue;
         const float v = (gr < a.rows) ? Ys[r * YS + c] : 0.f;
         reinterpret_cast<uint16_t*>(a.yt16)[(size_t)gc * a.rows_pad + gr] = to16(v, a.bf16);
+        if (a.yt16lo) reinterpret_cast<uint16_t*>(a.yt16lo)[(size_t)gc * a.rows_pad + gr] = to16_lo(v, a.bf16);
       }
     }
+  }
+  if (a.norm_max) {
+    __syncthreads();
+    if (tid < BR) atomicMax(reinterpret_cast<int*>(a.norm_max), __float_as_int(sqrtf(s_sq[tid])));   // (>= 0: bit order = value order)
   }
 }
 
@@ -165,7 +182,7 @@ __global__ void __launch_bounds__(NT) ln_linear_pair_kernel(LnLinearArgs a0, LnL
 }
 
 int launch_ln_linear_pair(const LnLinearArgs& a0, const LnLinearArgs& a1, cudaStream_t st) {
-  const int total_rows = (a0.y16 || a0.yt16 || a1.y16 || a1.yt16) ? a0.rows_pad : a0.rows;
+  const int total_rows = (a0.y16 || a0.yt16 || a0.y16lo || a1.y16 || a1.yt16) ? a0.rows_pad : a0.rows;
   if (total_rows <= 0) return HOP_OK;
   const int sms = num_sms();
   if (total_rows >= 64 * sms) {
@@ -205,8 +222,13 @@ int launch_prepare_patterns(const hop_desc& d, const hop_params& p, const hop_pa
   k.has_ln = (d.flags & HOP_F_NORM_STORED) ? 1 : 0; k.ln_w = p.ln_stored_w; k.ln_b = p.ln_stored_b; k.ln_eps = d.ln_eps;
   k.w = (d.flags & HOP_F_PROJ_STORED) ? p.wk : nullptr; k.b = (d.flags & HOP_F_PROJ_STORED) ? p.bk : nullptr;
   k.dout = d.d_assoc; k.scale = 1.f; k.y = pt.khat;
-  k.y16 = tc ? pt.k16 : nullptr; k.yt16 = (tc && d.update_steps > 0) ? pt.kt16 : nullptr;
+  k.y16 = tc ? pt.k16 : nullptr; k.yt16 = tc ? pt.kt16 : nullptr;   // (kt16: only when T > 0 or HOP_F_TRAIN, else NULL)
+  k.y16lo = tc ? pt.k16lo : nullptr; k.yt16lo = (tc && pt.kt16) ? pt.kt16lo : nullptr;
   k.bf16 = (path == HOP_PATH_TC_BF16);
+  if (tc && pt.kstats) {
+    HOP_CUDA(cudaMemsetAsync(pt.kstats, 0, 4 * sizeof(float), st));
+    k.norm_max = pt.kstats;
+  }
   if ((d.flags & HOP_F_PROJ_STORED) && !p.wk) HOP_FAIL(HOP_ERR_BAD_ARG, "HOP_F_PROJ_STORED set but params.wk is NULL");
 
   LnLinearArgs v{};
@@ -214,7 +236,7 @@ int launch_prepare_patterns(const hop_desc& d, const hop_params& p, const hop_pa
   v.has_ln = (d.flags & HOP_F_NORM_PROJ) ? 1 : 0; v.ln_w = p.ln_proj_w; v.ln_b = p.ln_proj_b; v.ln_eps = d.ln_eps;
   v.w = (d.flags & HOP_F_PROJ_PATTERN) ? p.wv : nullptr; v.b = (d.flags & HOP_F_PROJ_PATTERN) ? p.bv : nullptr;
   v.dout = d.d_v; v.scale = 1.f; v.y = pt.vhat;
-  v.y16 = nullptr; v.yt16 = tc ? pt.vt16 : nullptr;
+  v.y16 = tc ? pt.v16 : nullptr; v.yt16 = tc ? pt.vt16 : nullptr;
   v.bf16 = (path == HOP_PATH_TC_BF16);
   if ((d.flags & HOP_F_PROJ_PATTERN) && !p.wv) HOP_FAIL(HOP_ERR_BAD_ARG, "HOP_F_PROJ_PATTERN set but params.wv is NULL");
   HOP_TRY(launch_ln_linear_pair(k, v, st));     // K^ and V^ packs: same rows, one launch
