@@ -13,11 +13,15 @@ from typing import Optional
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("HOP_SM100_LIB") or os.path.join(HERE, "libhop_sm100.so")   # env: debug builds only
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 # hop_desc.flags
 F_NORM_STATE, F_NORM_STORED, F_NORM_PROJ = 1 << 0, 1 << 1, 1 << 2
 F_PROJ_STATE, F_PROJ_STORED, F_PROJ_PATTERN, F_OUT_PROJ = 1 << 3, 1 << 4, 1 << 5, 1 << 6
+F_EXACT_ARGMAX, F_TRAIN = 1 << 7, 1 << 8
+# hop_desc.tune_flags (tests / experiments; 0 = the library's heuristics)
+TUNE_STREAMK_ON, TUNE_STREAMK_OFF, TUNE_ROWS128, TUNE_MULTI_ON, TUNE_MULTI_OFF = 1 << 0, 1 << 1, 1 << 2, 1 << 3, 1 << 4
+TUNE_PAIR_ON, TUNE_PAIR_OFF, TUNE_PLAIN_UPDATES, TUNE_BWD_SIMT = 1 << 5, 1 << 6, 1 << 7, 1 << 8
 # hop_desc.path
 PATH_AUTO, PATH_FP32_SIMT, PATH_TC_F16, PATH_TC_BF16 = 0, 1, 2, 3
 PATH_NAMES = {"auto": PATH_AUTO, "fp32": PATH_FP32_SIMT, "f16": PATH_TC_F16, "bf16": PATH_TC_BF16}
@@ -33,12 +37,13 @@ class HopDesc(C.Structure):
                 ("n_rows", C.c_int32), ("n_patterns", C.c_int32), ("d_in", C.c_int32),
                 ("d_assoc", C.c_int32), ("d_v", C.c_int32), ("d_out", C.c_int32),
                 ("update_steps", C.c_int32), ("pattern_offset", C.c_int32),
-                ("beta", C.c_float), ("ln_eps", C.c_float)]
+                ("beta", C.c_float), ("ln_eps", C.c_float), ("update_eps", C.c_float),
+                ("rows_per_item", C.c_int32), ("tune_splits", C.c_int32), ("tune_flags", C.c_uint32)]
 
 
 _PARAM_FIELDS = ["lookup", "lookup_targets", "ln_state_w", "ln_state_b", "ln_stored_w", "ln_stored_b",
                  "ln_proj_w", "ln_proj_b", "wq", "bq", "wk", "bk", "wv", "bv", "wo", "bo"]
-_PATTERN_FIELDS = ["khat", "vhat", "k16", "kt16", "vt16", "vot16"]
+_PATTERN_FIELDS = ["khat", "vhat", "k16", "kt16", "vt16", "vot16", "k16lo", "kt16lo", "v16", "kstats"]
 _GRAD_FIELDS = ["d_x", "d_lookup", "d_lookup_targets", "d_ln_state_w", "d_ln_state_b", "d_ln_stored_w",
                 "d_ln_stored_b", "d_ln_proj_w", "d_ln_proj_b", "d_wq", "d_bq", "d_wk", "d_bk", "d_wv", "d_bv",
                 "d_wo", "d_bo"]
@@ -50,6 +55,10 @@ class HopParams(C.Structure):
 
 class HopPatterns(C.Structure):
     _fields_ = [(n, _fp) for n in _PATTERN_FIELDS]
+
+
+class HopPatternSizes(C.Structure):
+    _fields_ = [(n, C.c_size_t) for n in _PATTERN_FIELDS]
 
 
 class HopGrads(C.Structure):
@@ -68,7 +77,7 @@ class HopPeerMerge(C.Structure):
 
 
 EXPORTS = ["hop_sm100_peer_merge", "hop_sm100_enable_peer_access", "hop_sm100_ipc_export", "hop_sm100_ipc_import",
-           "hop_sm100_ipc_close", "hop_sm100_version", "hop_sm100_last_error", "hop_sm100_select_path", "hop_sm100_pattern_bytes",
+           "hop_sm100_ipc_close", "hop_sm100_select_train_path", "hop_sm100_version", "hop_sm100_last_error", "hop_sm100_select_path", "hop_sm100_pattern_bytes",
            "hop_sm100_workspace_bytes", "hop_sm100_prepare_patterns", "hop_sm100_forward", "hop_sm100_backward",
            "hop_sm100_merge_shards", "hop_sm100_out_projection", "hop_sm100_launch_count"]
 
@@ -94,8 +103,10 @@ def load() -> C.CDLL:
     lib.hop_sm100_launch_count.argtypes = []
     lib.hop_sm100_select_path.restype = C.c_int
     lib.hop_sm100_select_path.argtypes = [P(HopDesc), P(C.c_int32)]
+    lib.hop_sm100_select_train_path.restype = C.c_int
+    lib.hop_sm100_select_train_path.argtypes = [P(HopDesc), P(C.c_int32)]
     lib.hop_sm100_pattern_bytes.restype = C.c_int
-    lib.hop_sm100_pattern_bytes.argtypes = [P(HopDesc)] + [P(C.c_size_t)] * 6
+    lib.hop_sm100_pattern_bytes.argtypes = [P(HopDesc), P(HopPatternSizes)]
     lib.hop_sm100_workspace_bytes.restype = C.c_int
     lib.hop_sm100_workspace_bytes.argtypes = [P(HopDesc), C.c_int, P(C.c_size_t)]
     lib.hop_sm100_prepare_patterns.restype = C.c_int
@@ -142,9 +153,16 @@ def launch_count() -> int:
 
 
 def make_desc(*, flags: int, path: int, n_rows: int, n_patterns: int, d_in: int, d_assoc: int, d_v: int,
-              d_out: int, update_steps: int, beta: float, ln_eps: float = 1e-5, pattern_offset: int = 0) -> HopDesc:
+              d_out: int, update_steps: int, beta: float, ln_eps: float = 1e-5, pattern_offset: int = 0,
+              update_eps: float = 0.0, rows_per_item: int = 0, tune_splits: int = 0, tune_flags: int = 0) -> HopDesc:
     return HopDesc(ABI_VERSION, flags, path, n_rows, n_patterns, d_in, d_assoc, d_v, d_out, update_steps,
-                   pattern_offset, beta, ln_eps)
+                   pattern_offset, beta, ln_eps, update_eps, rows_per_item, tune_splits, tune_flags)
+
+
+def patterns_struct(pats) -> "HopPatterns":
+    """hop_patterns from the tensors of `ops.prepare_patterns` (order of _PATTERN_FIELDS; empty tensor -> NULL)."""
+    return HopPatterns(**{n: (t.data_ptr() if t is not None and t.numel() else None)
+                          for n, t in zip(_PATTERN_FIELDS, pats)})
 
 
 def ptr(t) -> Optional[int]:

@@ -30,6 +30,10 @@ from . import cabi
 from .ops import (LayerSpec, HopfieldAssociation, prepare_patterns, prepare_patterns_op, retrieve, retrieve_op,
                   resolve_path, _eager, _PATTERN_SIDE, _QUERY_SIDE, _PARAM_ORDER)
 
+_TUNE_NAMES = {"streamk": (cabi.TUNE_STREAMK_ON, cabi.TUNE_STREAMK_OFF), "multi_launch": (cabi.TUNE_MULTI_ON, cabi.TUNE_MULTI_OFF),
+               "pair": (cabi.TUNE_PAIR_ON, cabi.TUNE_PAIR_OFF), "rows128": (cabi.TUNE_ROWS128, 0),
+               "plain_updates": (cabi.TUNE_PLAIN_UPDATES, 0), "bwd_simt": (cabi.TUNE_BWD_SIMT, 0)}
+
 _NOT_BUILT = dict(num_heads=1, normalize_hopfield_space=False, normalize_hopfield_space_affine=False,
                   pattern_projection_as_connected=False, association_activation=None, dropout=0.0,
                   concat_bias_pattern=False, add_zero_association=False, batch_first=True)
@@ -126,9 +130,21 @@ class HopfieldLayer(nn.Module):
     (B, L, output_size or input_size).  After a call, `last_argmax` holds the
     nearest-pattern index per query row (int32, flattened rows).
 
-    `kernel_path` ("auto" | "fp32" | "f16" | "bf16", or env HOP_SM100_PATH)
-    selects the kernel family for inference; training always uses the exact
-    fp32 kernels (forward and backward on the same arithmetic).
+    `kernel_path` ("auto" | "fp32" | "f16" | "bf16", or env HOP_SM100_PATH at construction) selects the kernel
+    family; "auto" keeps the reference's own sizes and every layer without LayerNorm'd score operands on the exact
+    fp32 kernels and sends large N x P problems to tcgen05 (fp16-encoded operands, fp32 accumulate).  A training
+    step runs forward and backward on one family (`hop_sm100_select_train_path`).
+
+    `update_steps_max` / `update_steps_eps` follow upstream: at most T retrieve updates, ending early when
+    max over the batch of ||A_t - A_(t-1)||_F <= eps (checked behind update t >= 1; `update_steps_max < 0` iterates
+    until then, at most 64 updates).  The stop rule is evaluated by the fp32 kernels; the 16-bit tensor-core paths
+    cannot resolve 1e-4 changes of the association and run exactly T updates.
+
+    `exact_argmax` (default True): on the tensor-core paths rows whose nearest pattern the 16-bit scores cannot
+    decide are re-scored in fp32, so `last_argmax` equals the fp32 reference's index.
+
+    `tune` (dict, tests / experiments): scheduling overrides that travel in the op descriptor, e.g.
+    `layer.tune = dict(splits=3)`, `dict(streamk=True)`, `dict(rows128=True)`.
     """
 
     def __init__(self, input_size: int, hidden_size: Optional[int] = None, output_size: Optional[int] = None,
@@ -158,9 +174,10 @@ class HopfieldLayer(nn.Module):
                                           f"(HopVAE.py:149-170) leaves it at {default!r}")
         if stored_pattern_size not in (None, input_size) or pattern_projection_size not in (None, input_size):
             raise NotImplementedError("stored_pattern_size / pattern_projection_size other than input_size")
-        if update_steps_max is None or update_steps_max < 0:
-            raise NotImplementedError("update_steps_max < 0 (iterate until convergence) is not built; "
-                                      "give a fixed number of update steps")
+        if update_steps_max is None:
+            raise ValueError("update_steps_max must be an integer (upstream: < 0 iterates until convergence)")
+        if update_steps_max < 0 and not update_steps_eps > 0:
+            raise ValueError("update_steps_max < 0 (iterate until convergence) needs update_steps_eps > 0")
         d_in = int(input_size)
         d_assoc = d_in if hidden_size is None else int(hidden_size)
         d_v = d_assoc if pattern_size is None else int(pattern_size)
@@ -196,6 +213,8 @@ class HopfieldLayer(nn.Module):
         flags |= 0 if disable_out_projection else cabi.F_OUT_PROJ
         self._flags = flags
         self.kernel_path = os.environ.get("HOP_SM100_PATH", "auto")
+        self.exact_argmax = True
+        self.tune: Dict[str, object] = {}
         self.last_argmax: Optional[Tensor] = None
         self.last_lse: Optional[Tensor] = None
         self._pack_cache = None
@@ -218,9 +237,19 @@ class HopfieldLayer(nn.Module):
         path = cabi.PATH_NAMES.get(self.kernel_path)
         if path is None:
             raise ValueError(f"kernel_path must be one of {sorted(cabi.PATH_NAMES)}, got {self.kernel_path!r}")
-        return LayerSpec(flags=self._flags, path=path, d_in=self.input_size, d_assoc=self.hidden_size,
-                         d_v=self.pattern_size, d_out=self.output_size, update_steps=self.update_steps_max,
-                         beta=self.beta, ln_eps=1e-5)
+        tune_flags = 0
+        for name, v in self.tune.items():
+            if name == "splits":
+                continue
+            if name not in _TUNE_NAMES:
+                raise ValueError(f"unknown tuning override {name!r} (one of {sorted(_TUNE_NAMES) + ['splits']})")
+            on, off = _TUNE_NAMES[name]
+            tune_flags |= on if v else off
+        return LayerSpec(flags=self._flags | (cabi.F_EXACT_ARGMAX if self.exact_argmax else 0), path=path,
+                         d_in=self.input_size, d_assoc=self.hidden_size, d_v=self.pattern_size,
+                         d_out=self.output_size, update_steps=self.update_steps_max, beta=self.beta, ln_eps=1e-5,
+                         update_eps=max(self.update_steps_eps, 0.0), tune_splits=int(self.tune.get("splits", 0) or 0),
+                         tune_flags=tune_flags)
 
     def param_pack(self) -> Dict[str, Optional[Tensor]]:
         """The module's tensors under the hop_params names.  Under no_grad the dict is cached (rebuilt when a
@@ -256,16 +285,36 @@ class HopfieldLayer(nn.Module):
         return pack
 
     # ------------------------------------------------------------------- caching
+    def invalidate(self) -> None:
+        """Drop the prepared pattern operands (K^ / V^ packs) and the captured `forward_host` graphs.  The cache is
+        keyed on (data_ptr, _version) of every pattern-side tensor, which in-place updates through `.data`
+        (old-style optimizers, EMA, clipping) do not bump: call this after such a write.  `train()`, `eval()` and
+        `load_state_dict()` call it themselves."""
+        self.__dict__["_cache"] = None
+        self.__dict__["_cache_key"] = None
+        self.__dict__["_pack_cache"] = None
+        st = self.__dict__.get("_host_state")
+        if st is not None:
+            st["graphs"].clear()
+
+    def train(self, mode: bool = True):
+        self.invalidate()
+        return super().train(mode)
+
+    def _load_from_state_dict(self, *args, **kwargs):
+        self.invalidate()
+        return super()._load_from_state_dict(*args, **kwargs)
+
     def _prepared(self, pack, spec: LayerSpec, path: int):
         """Prepared pattern operands, recomputed only when a pattern-side tensor changed."""
-        key = (path, spec.update_steps) + tuple(
+        key = (path, spec.update_steps, spec.flags, spec.tune_flags) + tuple(
             (None if pack[k] is None else (pack[k].data_ptr(), pack[k]._version, pack[k].device))
             for k in _PATTERN_SIDE)
         if key != self._cache_key:
             with torch.no_grad():
                 self._cache = (prepare_patterns if _eager() else prepare_patterns_op)(
                     *[None if pack[k] is None else pack[k].detach().contiguous() for k in _PATTERN_SIDE],
-                    spec.flags, path, spec.d_assoc, spec.d_v, spec.update_steps, spec.ln_eps)
+                    spec.flags, path, spec.d_assoc, spec.d_v, spec.update_steps, spec.ln_eps, spec.tune_flags)
             self._cache_key = key
         return self._cache
 
@@ -289,29 +338,39 @@ class HopfieldLayer(nn.Module):
         needs_grad = torch.is_grad_enabled() and (
             x.requires_grad or any(t is not None and t.requires_grad for t in pack.values()))
         if needs_grad:
-            out, argmax = HopfieldAssociation.apply(spec, x, *[None if pack[k] is None else pack[k].contiguous()
-                                                               for k in _PARAM_ORDER])
+            out, argmax, lse = HopfieldAssociation.apply(spec, x, *[None if pack[k] is None else pack[k].contiguous()
+                                                                    for k in _PARAM_ORDER])
         else:
-            out, argmax, lse = self._infer(x, spec, pack)
-            self.__dict__["last_lse"] = lse        # (plain attribute: nn.Module.__setattr__ costs ~5 us per set)
+            # upstream's stop rule takes the Frobenius norm per batch item: rows of one (L, D) slice belong together
+            rows_per_item = int(lead[-1]) if len(lead) >= 2 else 0
+            out, argmax, lse = self._infer(x, spec, pack, rows_per_item=rows_per_item)
+        self.__dict__["last_lse"] = lse            # (plain attribute: nn.Module.__setattr__ costs ~5 us per set)
         self.__dict__["last_argmax"] = argmax
         return out.reshape(*lead, out.shape[-1])
 
-    def _infer(self, x: Tensor, spec: LayerSpec, pack, into=None) -> Tuple[Tensor, Tensor, Tensor]:
-        """No-grad retrieval of x (N, Din) -> (out, nearest-pattern index, lse); `into` = caller-owned result
-        buffers (out (N,W), stats (2,N), argmax (N) i32)."""
-        pkey = (spec, x.shape[0], self.quantity)
+    def _path_for(self, spec: LayerSpec, n_rows: int) -> int:
+        pkey = (spec, n_rows, self.quantity)
         path = self._paths.get(pkey)
         if path is None:
-            path = self._paths[pkey] = resolve_path(spec, x.shape[0], self.quantity)
+            path = self._paths[pkey] = resolve_path(spec, n_rows, self.quantity)
+        return path
+
+    def _infer(self, x: Tensor, spec: LayerSpec, pack, into=None, path: Optional[int] = None,
+               rows_per_item: int = 0) -> Tuple[Tensor, Tensor, Tensor]:
+        """No-grad retrieval of x (N, Din) -> (out, nearest-pattern index, lse); `into` = caller-owned result
+        buffers (out (N,W), stats (2,N), argmax (N) i32); `path` = kernel family already resolved by the caller."""
+        if path is None:
+            path = self._path_for(spec, x.shape[0])
         pats = self._prepared(pack, spec, path)
         q = [None if pack[k] is None else pack[k].detach().contiguous() for k in _QUERY_SIDE]
         if _eager():
-            res = retrieve(x.detach(), *pats, *q, spec.flags, path, spec.d_in, spec.d_out, spec.update_steps,
-                           spec.beta, spec.ln_eps, 0, False, False, into)
+            res = retrieve(x.detach(), pats, *q, spec.flags, path, spec.d_in, spec.d_out, spec.update_steps,
+                           spec.beta, spec.ln_eps, 0, False, False, into, spec.update_eps, rows_per_item,
+                           spec.tune_splits, spec.tune_flags)
         else:
-            res = retrieve_op(x.detach(), *pats, *q, spec.flags, path, spec.d_in, spec.d_out, spec.update_steps,
-                              spec.beta, spec.ln_eps, 0, False)
+            res = retrieve_op(x.detach(), pats, *q, spec.flags, path, spec.d_in, spec.d_out, spec.update_steps,
+                              spec.beta, spec.ln_eps, 0, False, spec.update_eps, rows_per_item, spec.tune_splits,
+                              spec.tune_flags)
         return res[0], res[4], res[3]
 
     # ------------------------------------------------------- host-buffer entry point
@@ -327,7 +386,8 @@ class HopfieldLayer(nn.Module):
         busy host cannot starve the GPU (`graph=False`, or HOP_SM100_HOST_GRAPH=0, keeps the eager enqueue).
         Returns once all work is *enqueued*; the current stream waits for the last device->host copy, so a
         synchronize / event on the current stream covers everything.  Inference only (no autograd).
-        `last_argmax` / `last_lse` are views of per-layer staging buffers, valid until the next call."""
+        `last_argmax` / `last_lse` are views of per-layer staging buffers, valid until the next call.  The kernel
+        family is resolved ONCE per call on all N rows and used for every piece."""
         dev = self.lookup_weights.device
         if dev.type != "cuda":
             raise RuntimeError("hflayers.HopfieldLayer (hop_sm100): the layer is on the CPU; no CPU fallback")
@@ -352,33 +412,32 @@ class HopfieldLayer(nn.Module):
                       arg=torch.empty((n,), device=dev, dtype=torch.int32), graphs={})
             self.__dict__["_host_state"] = st
         # (a fresh result buffer per call would mean a fresh capture per call: graphs need caller-owned buffers)
-        use_graph = graph if graph is not None else (not own_out and os.environ.get("HOP_SM100_HOST_GRAPH", "1") != "0")
+        use_graph = graph if graph is not None else not own_out
         with torch.no_grad():
             spec, pack = self.spec(), self.param_pack()
+            path = self._path_for(spec, n)
             if use_graph and _eager():
                 # the prepared pattern operands are baked into the captured launches: their cache key is part of ours
-                path = self._paths.get((spec, bounds[0][1] - bounds[0][0], self.quantity))
-                self._prepared(pack, spec, path if path is not None else
-                               resolve_path(spec, bounds[0][1] - bounds[0][0], self.quantity))
-                key = (x_host.data_ptr(), out_host.data_ptr(), n, tuple(bounds), self._cache_key, self.kernel_path)
+                self._prepared(pack, spec, path)
+                key = (x_host.data_ptr(), out_host.data_ptr(), n, tuple(bounds), self._cache_key, path)
                 g = st["graphs"].get(key)
                 if g is None:
-                    self._host_pipeline(x_host, out_host, bounds, st, spec, pack)      # warm-up: lazy caches, allocator
+                    self._host_pipeline(x_host, out_host, bounds, st, spec, pack, path)   # warm-up: lazy caches, allocator
                     torch.cuda.current_stream(dev).synchronize()
                     g = torch.cuda.CUDAGraph()
                     with torch.cuda.graph(g):
-                        self._host_pipeline(x_host, out_host, bounds, st, spec, pack)
+                        self._host_pipeline(x_host, out_host, bounds, st, spec, pack, path)
                     if len(st["graphs"]) >= 4:
                         st["graphs"].pop(next(iter(st["graphs"])))
                     st["graphs"][key] = g
                 g.replay()
             else:
-                self._host_pipeline(x_host, out_host, bounds, st, spec, pack)
+                self._host_pipeline(x_host, out_host, bounds, st, spec, pack, path)
         self.__dict__["last_argmax"] = st["arg"][:n]
         self.__dict__["last_lse"] = st["stats"][0, :n]
         return out_host
 
-    def _host_pipeline(self, x_host: Tensor, out_host: Tensor, bounds, st, spec: LayerSpec, pack) -> None:
+    def _host_pipeline(self, x_host: Tensor, out_host: Tensor, bounds, st, spec: LayerSpec, pack, path: int) -> None:
         """Enqueue H2D / retrieval / D2H of every piece on the three side streams (fork from and join to the current
         stream, so the same code runs eagerly and under CUDA-graph capture); results go through staging buffers."""
         dev = st["dev"]
@@ -393,7 +452,7 @@ class HopfieldLayer(nn.Module):
                 e1 = h2d.record_event()
             with torch.cuda.stream(comp):
                 comp.wait_event(e1)
-                self._infer(xs, spec, pack, into=(st["y"][a:b], st["stats"][:, a:b], st["arg"][a:b]))
+                self._infer(xs, spec, pack, into=(st["y"][a:b], st["stats"][:, a:b], st["arg"][a:b]), path=path)
                 e2 = comp.record_event()
             with torch.cuda.stream(d2h):
                 d2h.wait_event(e2)

@@ -180,17 +180,22 @@ class CudaBackend:
         `fold=(wo, bo)` and a folded operand in `pats`, the pass returns O_g Wo^T + bo (the shard weights sum
         to 1, so the bias survives the merge unchanged); the second return value says whether it did."""
         from .ops import retrieve
-        khat, vhat, k16, kt16, vt16, vot16 = pats
+        khat, vhat, k16, kt16, vt16, vot16 = pats[:6]
+        kstats = pats[9]
         if over_keys:
             vhat, vt16 = khat, kt16
         empty = vot16.new_empty((0,))
+        # one T = 0 pass per call: no update operands; the nearest-pattern index of a shard is merged across shards
+        # on its 16-bit row maximum, so the per-shard fp32 repair (HOP_F_EXACT_ARGMAX) stays off here
+        flags = flags & ~cabi.F_EXACT_ARGMAX
+        one = lambda vo: [khat, vhat, k16, empty, vt16, vo, empty, empty, empty, kstats]
         if fold is not None and not over_keys and vot16.numel() > 0 and path != cabi.PATH_FP32_SIMT:
             wo, bo = fold
-            res = retrieve(x, khat, vhat, k16, empty, vt16, vot16, ln_w, ln_b, None, None, wo, bo,
+            res = retrieve(x, one(vot16), ln_w, ln_b, None, None, wo, bo,
                            flags | cabi.F_OUT_PROJ, path, d_in, wo.shape[0], 0, beta, ln_eps, pattern_offset, False,
                            False, into)
             return (res[0], res[3], res[5], res[4]), True
-        res = retrieve(x, khat, vhat, k16, empty, vt16, empty, ln_w, ln_b, None, None, None, None,
+        res = retrieve(x, one(empty), ln_w, ln_b, None, None, None, None,
                        flags & ~cabi.F_OUT_PROJ, path, d_in, 1, 0, beta, ln_eps, pattern_offset, True, False, into)
         # no out_proj: out == read-out.  (O_g, lse_g, rowmax_g, argmax_g)
         return (res[0], res[3], res[5], res[4]), False
@@ -286,6 +291,8 @@ class PatternShardedHopfield:
         width = spec.d_assoc if over_keys else (fold[0].shape[0] if will_fold else spec.d_v)
         ex = self._peer.get((n, width))
         if ex is None:
+            if len(self._peer) >= 4:          # variable batch sizes: keep the IPC mappings bounded (collective call:
+                self.close()                  # every rank sees the same sequence of (N, width))
             ex = self._peer[(n, width)] = PeerExchange(n, width, self.group, state.device)
         _, folded = self.backend.retrieve(*args, fold, ex.local_slots())
         start, count = batch_parallel_rows(n, self.world, self.rank)
@@ -303,8 +310,9 @@ class PatternShardedHopfield:
         if self._pats is None:
             # path chosen on the GLOBAL problem so that every rank runs the same kernel family
             self._path = self.backend.resolve_path(spec, n, self.n_patterns)
+            # (every pass is its own T = 0 call on this shard: plain 16-bit update operands, kt16 when T > 0)
             self._pats = self.backend.prepare(self.pack, spec.flags, self._path, spec.d_assoc, spec.d_v,
-                                              spec.update_steps, spec.ln_eps)
+                                              min(spec.update_steps, 1), spec.ln_eps)
         flags = spec.flags & ~cabi.F_OUT_PROJ
         state, st_flags = x2, flags
         ln_w, ln_b = self.pack.get("ln_state_w"), self.pack.get("ln_state_b")
@@ -327,3 +335,14 @@ class PatternShardedHopfield:
         return o.reshape(*lead, o.shape[-1])
 
     __call__ = forward
+
+    def close(self) -> None:
+        """Unmap the peers' exchange blocks (collective: every rank calls it; a barrier first, so that no peer still
+        reads this rank's block).  The object can be used again afterwards (the exchanges are rebuilt on demand)."""
+        if self._peer:
+            torch.cuda.synchronize()
+            if dist.is_initialized():
+                dist.barrier(group=self.group)
+            for ex in self._peer.values():
+                ex.close()
+            self._peer.clear()
