@@ -34,21 +34,24 @@ def test_library_exports_every_declared_symbol(impl):
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in include/hop_sm100.h but not exported"
     assert sorted(impl.cabi.EXPORTS) == declared
-    assert lib.hop_sm100_version() == impl.cabi.ABI_VERSION == 2
+    assert lib.hop_sm100_version() == impl.cabi.ABI_VERSION == 3
 
 
 def test_struct_layouts_match_c(impl, tmp_path):
     src = tmp_path / "probe.c"
     src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "hop_sm100.h"\n'
-                   'int main(void){printf("%zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(hop_desc), sizeof(hop_params),'
+                   'int main(void){printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(hop_desc), sizeof(hop_params),'
                    ' sizeof(hop_patterns), sizeof(hop_grads), offsetof(hop_desc, beta), offsetof(hop_desc, n_patterns),'
-                   ' offsetof(hop_params, wo), offsetof(hop_grads, d_wo)); return 0;}\n')
+                   ' offsetof(hop_params, wo), offsetof(hop_grads, d_wo), offsetof(hop_desc, tune_flags),'
+                   ' offsetof(hop_patterns, kstats), sizeof(hop_pattern_sizes), sizeof(hop_peer_merge)); return 0;}\n')
     exe = tmp_path / "probe"
     subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
     got = [int(v) for v in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()]
     cb = impl.cabi
     want = [C.sizeof(cb.HopDesc), C.sizeof(cb.HopParams), C.sizeof(cb.HopPatterns), C.sizeof(cb.HopGrads),
-            cb.HopDesc.beta.offset, cb.HopDesc.n_patterns.offset, cb.HopParams.wo.offset, cb.HopGrads.d_wo.offset]
+            cb.HopDesc.beta.offset, cb.HopDesc.n_patterns.offset, cb.HopParams.wo.offset, cb.HopGrads.d_wo.offset,
+            cb.HopDesc.tune_flags.offset, cb.HopPatterns.kstats.offset, C.sizeof(cb.HopPatternSizes),
+            C.sizeof(cb.HopPeerMerge)]
     assert got == want
 
 
@@ -73,16 +76,29 @@ def test_error_reporting_without_gpu(impl):
                        update_steps=0, beta=1 / 16)
     assert lib.hop_sm100_select_path(C.byref(big), C.byref(out)) == 0
     assert out.value in (cb.PATH_TC_F16, cb.PATH_FP32_SIMT)
-    sizes = [C.c_size_t(0) for _ in range(6)]
-    assert lib.hop_sm100_pattern_bytes(C.byref(big), *[C.byref(s) for s in sizes]) == 0
-    assert sizes[0].value == 65536 * 256 * 4
-    assert sizes[5].value == 0                      # no HOP_F_OUT_PROJ -> nothing to fold
-    big.flags = cb.F_OUT_PROJ
-    assert lib.hop_sm100_pattern_bytes(C.byref(big), *[C.byref(s) for s in sizes]) == 0
-    assert sizes[5].value == (65536 * 256 * 2 if out.value == cb.PATH_TC_F16 else 0)
+    assert out.value == cb.PATH_FP32_SIMT       # no LayerNorm on the score operands: AUTO keeps fp32 (fp16 range)
+    big.flags = cb.F_NORM_STATE | cb.F_NORM_STORED
+    assert lib.hop_sm100_select_path(C.byref(big), C.byref(out)) == 0 and out.value == cb.PATH_TC_F16
+    sizes = cb.HopPatternSizes()
+    assert lib.hop_sm100_pattern_bytes(C.byref(big), C.byref(sizes)) == 0
+    assert sizes.khat == 65536 * 256 * 4 and sizes.k16 == 65536 * 256 * 2 and sizes.kstats == 16
+    assert sizes.vot16 == 0                          # no HOP_F_OUT_PROJ -> nothing to fold
+    assert sizes.k16lo == 0 and sizes.kt16 == 0 and sizes.v16 == 0
+    big.flags |= cb.F_OUT_PROJ
+    assert lib.hop_sm100_pattern_bytes(C.byref(big), C.byref(sizes)) == 0
+    assert sizes.vot16 == 65536 * 256 * 2
+    # T >= 2 at D <= 256: hi + lo operand pairs for the update passes; HOP_F_TRAIN: the backward's packs
+    big.update_steps = 3
+    assert lib.hop_sm100_pattern_bytes(C.byref(big), C.byref(sizes)) == 0
+    assert sizes.k16lo == sizes.kt16lo == sizes.kt16 == 65536 * 256 * 2
+    big.tune_flags = cb.TUNE_PLAIN_UPDATES
+    assert lib.hop_sm100_pattern_bytes(C.byref(big), C.byref(sizes)) == 0 and sizes.k16lo == 0
+    big.update_steps, big.tune_flags, big.flags = 0, 0, big.flags | cb.F_TRAIN
+    assert lib.hop_sm100_pattern_bytes(C.byref(big), C.byref(sizes)) == 0
+    assert sizes.v16 == sizes.kt16 == 65536 * 256 * 2
 
 
-def test_wide_widths_select_the_tensor_path_and_size_their_workspace(impl, monkeypatch):
+def test_wide_widths_select_the_tensor_path_and_size_their_workspace(impl):
     """Host logic of BASELINE config 5's wide widths, no GPU needed (the SM count falls back to 148): D = 512 and
     1024 resolve to the tcgen05 path (the fp32 kernels stop at 256), unsupported widths are refused there, and the
     forward workspace covers the state buffers plus the split partials under both kernel forms."""
@@ -93,17 +109,17 @@ def test_wide_widths_select_the_tensor_path_and_size_their_workspace(impl, monke
         d = cb.make_desc(flags=0, path=0, n_rows=300, n_patterns=2048, d_in=d_, d_assoc=d_, d_v=d_, d_out=d_,
                          update_steps=0, beta=d_ ** -0.5)
         assert lib.hop_sm100_select_path(C.byref(d), C.byref(out)) == 0 and out.value == cb.PATH_TC_F16
-        sizes = [C.c_size_t(0) for _ in range(6)]
-        assert lib.hop_sm100_pattern_bytes(C.byref(d), *[C.byref(s) for s in sizes]) == 0
-        assert sizes[2].value == 2048 * d_ * 2 and sizes[4].value == 2048 * d_ * 2 and sizes[3].value == 0
+        sizes = cb.HopPatternSizes()
+        assert lib.hop_sm100_pattern_bytes(C.byref(d), C.byref(sizes)) == 0
+        assert sizes.k16 == 2048 * d_ * 2 and sizes.vt16 == 2048 * d_ * 2 and sizes.kt16 == 0
         state = 3 * ((300 * d_ * 4 + 255) // 256 * 256)          # two state buffers + one read-out buffer
         got = {}
-        for halfm in ("1", "0"):
-            monkeypatch.setenv("HOP_TC_HALFM", halfm)
+        for rows128 in (0, cb.TUNE_ROWS128):                      # the 64-row pair form / the 128-row comparison form
+            d.tune_flags = rows128
             ws = C.c_size_t(0)
             assert lib.hop_sm100_workspace_bytes(C.byref(d), 0, C.byref(ws)) == 0
             assert ws.value >= state and (ws.value - state) % 256 == 0
-            got[halfm] = ws.value - state
+            got[rows128] = ws.value - state
         # split partials: (splits x N) rows of D floats + three per-row vectors, for some split count >= 1
         for extra in got.values():
             if extra:
@@ -150,11 +166,141 @@ def test_no_cpu_fallback_and_unsupported_options(impl):
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         layer(torch.randn(2, 3, 8))
     for bad in (dict(num_heads=2), dict(dropout=0.1), dict(normalize_hopfield_space=True),
-                dict(add_zero_association=True), dict(update_steps_max=-1)):
+                dict(add_zero_association=True)):
         with pytest.raises(NotImplementedError):
             hflayers.HopfieldLayer(input_size=8, **bad)
     with pytest.raises(NotImplementedError):
         layer.forward(torch.randn(1, 1, 8), association_mask=torch.zeros(1, 4, dtype=torch.bool))
+
+
+def test_forward_workspace_covers_every_launch_form(impl):
+    """hop_sm100_workspace_bytes must cover whatever schedule hop_sm100_forward picks for the same descriptor.  The
+    window ADVICE r01 flagged -- T >= 1 at D = 64 / 128, P = 128k..384k, N = 2k..16k, where the one-launch-per-pass
+    form used to be free to pick stream-K against a workspace sized for the plain grid -- is swept here on the host
+    heuristics (SM count falls back to 148 without a GPU): the size must not shrink when stream-K is forbidden
+    (every launch of that form now runs the plain grid), must grow monotonically with forced splits, and the tuning
+    fields must be part of what the size depends on (they travel in the descriptor, not in the environment)."""
+    cb = impl.cabi
+    lib = cb.load()
+    flags = cb.F_NORM_STATE | cb.F_NORM_STORED | cb.F_NORM_PROJ
+
+    def ws(**kw):
+        d = cb.make_desc(**{**dict(flags=flags, path=cb.PATH_TC_F16, n_rows=4096, n_patterns=131072, d_in=64,
+                                   d_assoc=64, d_v=64, d_out=1, update_steps=1, beta=0.125), **kw})
+        out = C.c_size_t(0)
+        assert lib.hop_sm100_workspace_bytes(C.byref(d), 0, C.byref(out)) == 0, lib.hop_sm100_last_error()
+        return out.value
+
+    for dd in (64, 128):
+        for p in (131072, 262144, 393216):
+            for n in (2048, 4096, 8192, 16384):
+                for t in (1, 2, 3):
+                    base = ws(n_rows=n, n_patterns=p, d_in=dd, d_assoc=dd, d_v=dd, update_steps=t)
+                    nosk = ws(n_rows=n, n_patterns=p, d_in=dd, d_assoc=dd, d_v=dd, update_steps=t,
+                              tune_flags=cb.TUNE_STREAMK_OFF)
+                    assert base == nosk, (dd, p, n, t)           # T > 0 never sizes (or runs) stream-K
+                    state = 3 * ((n * dd * 4 + 255) // 256 * 256)
+                    chain = -(-(p // 128) // 256)                 # accumulation chains capped at 256 tiles
+                    assert base - state >= chain * n * dd * 4, (dd, p, n, t)
+    a, b = ws(tune_splits=2), ws(tune_splits=5)
+    assert b > a
+    # T = 0: the stream-K slots are covered whenever the heuristic (or the override) may choose them
+    t0 = ws(update_steps=0, n_rows=16384, n_patterns=65536, d_in=256, d_assoc=256, d_v=256)
+    t0_on = ws(update_steps=0, n_rows=16384, n_patterns=65536, d_in=256, d_assoc=256, d_v=256,
+               tune_flags=cb.TUNE_STREAMK_ON)
+    t0_off = ws(update_steps=0, n_rows=16384, n_patterns=65536, d_in=256, d_assoc=256, d_v=256,
+                tune_flags=cb.TUNE_STREAMK_OFF)
+    assert t0 == t0_on >= t0_off
+    # exact nearest-pattern index: the repair's list / keys / compact rows are part of the forward workspace
+    assert ws(flags=flags | cb.F_EXACT_ARGMAX, update_steps=0) > ws(update_steps=0)
+
+
+def test_update_rule_descriptor_validation(impl):
+    """update_steps < 0 (upstream: iterate until convergence) needs the stop rule and the fp32 path."""
+    cb = impl.cabi
+    lib = cb.load()
+    out = C.c_int32(0)
+    mk = lambda **kw: cb.make_desc(**{**dict(flags=3, path=0, n_rows=64, n_patterns=128, d_in=64, d_assoc=64, d_v=64,
+                                             d_out=1, update_steps=-1, beta=0.125), **kw})
+    assert lib.hop_sm100_select_path(C.byref(mk()), C.byref(out)) == 1 and b"update_eps" in lib.hop_sm100_last_error()
+    assert lib.hop_sm100_select_path(C.byref(mk(update_eps=1e-4)), C.byref(out)) == 0 and out.value == cb.PATH_FP32_SIMT
+    assert lib.hop_sm100_select_path(C.byref(mk(update_eps=1e-4, rows_per_item=7)), C.byref(out)) == 2
+    big = mk(update_eps=1e-4, n_rows=16384, n_patterns=65536, d_in=256, d_assoc=256, d_v=256)
+    assert lib.hop_sm100_select_path(C.byref(big), C.byref(out)) == 0 and out.value == cb.PATH_FP32_SIMT
+    # training path: fp32 kernels for the reference's sizes; T > 0 has no backward
+    tr = mk(update_steps=0)
+    assert lib.hop_sm100_select_train_path(C.byref(tr), C.byref(out)) == 0 and out.value == cb.PATH_FP32_SIMT
+    assert lib.hop_sm100_select_train_path(C.byref(mk(update_steps=1)), C.byref(out)) == 7
+    import hflayers
+    layer = hflayers.HopfieldLayer(input_size=8, update_steps_max=-1)
+    assert layer.update_steps_max == -1 and layer.spec().update_eps == pytest.approx(1e-4)
+    with pytest.raises(ValueError):
+        hflayers.HopfieldLayer(input_size=8, update_steps_max=-1, update_steps_eps=0.0)
+    layer.tune = dict(splits=3, streamk=False, rows128=True)
+    sp = layer.spec()
+    assert sp.tune_splits == 3 and sp.tune_flags == cb.TUNE_STREAMK_OFF | cb.TUNE_ROWS128
+    layer.tune = dict(nonsense=1)
+    with pytest.raises(ValueError):
+        layer.spec()
+
+
+REFERENCE = "/root/reference"
+
+
+@pytest.mark.skipif(not os.path.exists(os.path.join(REFERENCE, "HopVAE.py")), reason="reference tree not present")
+def test_unchanged_reference_model_builds_on_this_hflayers(tmp_path):
+    """The boundary claim end to end: with this repository first on sys.path the reference's OWN,
+    unchanged `HopVAE.py` / `utils` / `configs` import `hflayers` from here, `HopVAE(config, device)` constructs
+    (HopVAE.py:128-185), `utils.load_from_checkpoint` loads the shipped `checkpoints/MNIST-28.ckpt` into it
+    (utils/__init__.py:36-49), and `Adam(model.parameters())` / `state_dict()` round-trip (main.py:106,124).
+    Construction and loading need no GPU; run in a subprocess so the reference's sys.path edits stay out of pytest."""
+    script = tmp_path / "probe.py"
+    script.write_text(f"""
+import os, sys
+sys.path.insert(0, {REFERENCE!r})
+sys.path.insert(0, {ROOT!r})          # this repository's `hflayers` wins over anything else named so
+os.environ["WANDB_MODE"] = "disabled"
+import torch
+import hflayers
+assert os.path.dirname(os.path.abspath(hflayers.__file__)) == os.path.join({ROOT!r}, "hflayers")
+import HopVAE as ref_model                      # the reference's file, unchanged
+import utils as ref_utils
+from configs.mnist_28_config import config as cfg_dict
+assert ref_model.HopfieldLayer is hflayers.HopfieldLayer
+config = ref_utils.MakeConfig(cfg_dict)
+device = torch.device("cpu")
+model = ref_model.HopVAE(config, device).to(device)
+layers = [model.hopfield, model.embedding_to_index, model.index_to_embedding]
+assert all(type(l) is hflayers.HopfieldLayer for l in layers)
+before = {{k: v.clone() for k, v in model.state_dict().items()}}
+model = ref_utils.load_from_checkpoint(model, os.path.join({REFERENCE!r}, "checkpoints", "MNIST-28.ckpt"))
+ckpt = torch.load(os.path.join({REFERENCE!r}, "checkpoints", "MNIST-28.ckpt"), map_location="cpu", weights_only=True)
+sd = model.state_dict()
+hop_keys = [k for k in ckpt if k.split(".")[0] in ("hopfield", "embedding_to_index", "index_to_embedding")]
+assert len(hop_keys) == 33
+for k in hop_keys:                               # every Hopfield tensor of the checkpoint landed, none was filtered out
+    assert k in sd and torch.equal(sd[k], ckpt[k]), k
+    assert not torch.equal(sd[k], before[k]) or sd[k].numel() <= 3, k
+opt = torch.optim.Adam(model.parameters(), lr=config.learning_rate)      # main.py:106
+n_hop = sum(p.numel() for l in layers for p in l.parameters())
+assert n_hop == sum(ckpt[k].numel() for k in hop_keys)
+path = os.path.join({str(tmp_path)!r}, "roundtrip.ckpt")
+torch.save(model.state_dict(), path)                                     # main.py:124
+again = ref_model.HopVAE(config, device)
+again = ref_utils.load_from_checkpoint(again, path)
+for k, v in model.state_dict().items():
+    assert torch.equal(v, again.state_dict()[k]), k
+# the layer refuses CPU tensors loudly (no silent fallback), through the reference's own forward
+try:
+    model(torch.zeros(2, 1, 28, 28))
+    raise SystemExit("CPU forward did not raise")
+except RuntimeError as e:
+    assert "no CPU fallback" in str(e)
+print("OK", len(hop_keys), n_hop)
+""")
+    r = subprocess.run([sys.executable, str(script)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    assert r.stdout.strip().startswith("OK 33")
 
 
 def test_product_path_never_imports_oracle():
