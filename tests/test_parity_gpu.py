@@ -105,10 +105,33 @@ def test_update_steps_parity(hf, T, d):
     r = rel_l2(got, want)
     print(f"T={T} d={d}: rel-L2 {r:.3e}")
     assert r < 1e-4
-    # upstream's default eps early-stop stays within the documented O(eps) of fixed-T
-    ref.hopfield.update_steps_eps = 1e-4
+
+
+@pytest.mark.parametrize("T,eps", [(3, 1e-4), (6, 3e-2), (6, 1.0), (-1, 5e-3), (-1, 1e-4)])
+@pytest.mark.parametrize("d", [64, 3])
+def test_update_stop_rule_matches_upstream(hf, T, eps, d):
+    """Upstream's stop rule: behind update t >= 1 the iteration ends when the largest per-image
+    Frobenius norm of A_t - A_(t-1) is <= update_steps_eps; update_steps_max < 0 iterates until then.  Decided on
+    the device by the fp32 kernels (hop_repair.cu); the oracle runs the SAME rule and reports how many updates it
+    made, and the layer must reproduce its output -- also where the rule fires early (eps = 3e-2, 1.0)."""
+    kw = dict(input_size=d, quantity=200, update_steps_max=T, update_steps_eps=eps, scaling=(2.0 if d == 3 else 0.5),
+              **STATIC)
+    ref, dut = make_pair(hf, seed=23, **kw)
+    x = torch.randn(4, 50, d, generator=torch.Generator().manual_seed(24))
     with torch.no_grad():
-        assert rel_l2(got, ref(x)) < REL_L2_BAR
+        want, _, _, steps = ref(x, return_details=True)
+        got = dut(x.cuda())
+        # the same count with fixed semantics (eps = 0) must give the same result: the rule only picks the count
+        fixed = O.HopfieldLayer(**{**kw, "update_steps_max": steps, "update_steps_eps": 0.0})
+        fixed.load_state_dict(ref.state_dict())
+        assert rel_l2(fixed(x), want) < 1e-6
+    r = rel_l2(got, want)
+    print(f"T={T} eps={eps} d={d}: oracle made {steps} updates, rel-L2 {r:.3e}")
+    assert r < 1e-4
+    if T > 0 and eps >= 3e-2:
+        assert steps < T          # the case exists to exercise an early stop
+    if T < 0:
+        assert 1 <= steps < 64
 
 
 def test_2d_input_and_dtype_errors(hf):
@@ -197,7 +220,10 @@ def ckpt_models(hf):
 
 @pytest.mark.parametrize("tag", ["strokes", "randn"])
 def test_checkpoint_golden_parity(ckpt_models, tag):
-    """MNIST-28.ckpt on the committed reference-generated vectors: latents, indices, reconstruction."""
+    """MNIST-28.ckpt on the committed golden vectors: latents, indices, reconstruction.  The `.npz` was produced by
+    the reference's own `HopVAE.py` glue with the ORACLE injected as `hflayers` (tests/golden/make_golden.py:37 --
+    upstream hopfield-layers cannot be installed here): for the Hopfield arithmetic these are oracle outputs routed
+    through the reference's caller code, not outputs of upstream `hflayers`."""
     ref, dut = ckpt_models
     g = load_golden()
     x = torch.from_numpy(g[f"{tag}_x"])
@@ -239,6 +265,37 @@ def test_sample_path_golden_parity(ckpt_models, tag):
     print(f"sample[{tag}]: embeddings rel-L2 {r_emb:.3e}, decoded image rel-L2 {r_x:.3e}")
     assert r_emb < FP32_BAR
     assert r_x < 1e-4                      # cuDNN vs CPU convolutions downstream of identical embeddings
+
+
+def test_config2_ffhq32_random_init(hf):
+    """BASELINE config 2: FFHQ-32 Hop-VAE (configs/ffhq_32_config.py + the two keys it lacks),
+    random init under manual_seed(1265), x = rand(32, 3, 32, 32) - 0.5, one B200: the whole forward through the
+    unchanged caller glue against the CPU oracle -- bottleneck tensors, nearest-pattern indices of all three layers,
+    reconstruction MSE."""
+    torch.manual_seed(1265)
+    ref = H.HopVAEHarness(H.FFHQ_32, O.HopfieldLayer).eval()
+    dut = H.HopVAEHarness(H.FFHQ_32, hf.HopfieldLayer)
+    dut.load_state_dict(ref.state_dict(), strict=True)
+    dut = dut.cuda().eval()
+    x = torch.rand(32, 3, 32, 32, generator=torch.Generator().manual_seed(1265)) - 0.5
+    with torch.no_grad():
+        z = ref.encode(x)
+        want = ref.bottleneck(z)
+        got = dut.bottleneck(z.cuda())
+        for k in ("emb", "logits", "emb_recon"):
+            r = rel_l2(got[k], want[k])
+            print(f"ffhq32 {k}: rel-L2 {r:.3e}")
+            assert r < REL_L2_BAR
+        # nearest pattern of every row of every layer, on the same inputs the oracle layer saw
+        feeds = {"hopfield": z, "embedding_to_index": want["emb"], "index_to_embedding": want["idx"]}
+        for name, feed in feeds.items():
+            layer_r, layer_d = getattr(ref, name), getattr(dut, name)
+            layer_d(feed.cuda())
+            check_argmax(layer_r, feed, layer_d.last_argmax)
+        xr_want, xr_got = ref.decode(want["emb"]), dut.decode(got["emb"])
+        mse_w, mse_g = float(F.mse_loss(xr_want, x)), float(F.mse_loss(xr_got.cpu(), x))
+    print(f"ffhq32 recon MSE {mse_g:.6e} vs {mse_w:.6e}")
+    assert abs(mse_g - mse_w) <= RECON_MSE_REL_BAR * mse_w
 
 
 def test_checkpoint_full_forward(ckpt_models):
@@ -386,7 +443,7 @@ def test_pattern_sharded_merge_single_gpu(hf, G):
                                             pack["ln_stored_b"], pack["ln_proj_w"], pack["ln_proj_b"], None, None,
                                             pack["wv"], pack["bv"], None, spec.flags, impl.cabi.PATH_FP32_SIMT,
                                             spec.d_assoc, spec.d_v, 0, spec.ln_eps)
-            res = impl.retrieve_op(x.cuda(), *pats, pack["ln_state_w"], pack["ln_state_b"], None, None, None, None,
+            res = impl.retrieve_op(x.cuda(), pats, pack["ln_state_w"], pack["ln_state_b"], None, None, None, None,
                                    spec.flags, impl.cabi.PATH_FP32_SIMT, spec.d_in, spec.d_out, 0, spec.beta,
                                    spec.ln_eps, gidx * per)
             outs.append(res[1]); lses.append(res[3]); args.append(res[4]); maxs.append(res[5])
@@ -432,8 +489,9 @@ def test_pattern_sharded_merge_single_gpu_tensor_core(hf, D):
                                             pack["ln_stored_b"], pack["ln_proj_w"], pack["ln_proj_b"], None, None,
                                             pack["wv"], pack["bv"], None, spec.flags, path,
                                             spec.d_assoc, spec.d_v, 0, spec.ln_eps)
-            res = impl.retrieve_op(x.cuda(), *pats, pack["ln_state_w"], pack["ln_state_b"], None, None, None, None,
-                                   spec.flags, path, spec.d_in, spec.d_out, 0, spec.beta, spec.ln_eps, gidx * per)
+            res = impl.retrieve_op(x.cuda(), pats, pack["ln_state_w"], pack["ln_state_b"], None, None, None, None,
+                                   spec.flags & ~impl.cabi.F_EXACT_ARGMAX, path, spec.d_in, spec.d_out, 0, spec.beta,
+                                   spec.ln_eps, gidx * per)
             outs.append(res[1]); lses.append(res[3]); args.append(res[4]); maxs.append(res[5])
         lse_all, max_all, arg_all = torch.stack(lses), torch.stack(maxs), torch.stack(args)
         total = torch.zeros_like(outs[0])
@@ -444,8 +502,10 @@ def test_pattern_sharded_merge_single_gpu_tensor_core(hf, D):
     assert rel_l2(total, want[0]) < REL_L2_BAR
     s = scores.reshape(N, P)
     top2 = s.topk(2, dim=-1).values
+    # per-shard indices come from 16-bit scores and are merged on the 16-bit row maxima (no fp32 repair across
+    # shards): identical wherever the gap exceeds the operand noise, which the planted queries guarantee on ~all rows
     decided = (top2[:, 0] - top2[:, 1]) > 2e-2
-    assert decided.float().mean() > 0.5
+    assert decided.float().mean() > 0.95
     assert torch.equal(arg.cpu().long()[decided], s.argmax(-1)[decided])
     assert (lse.cpu() - torch.logsumexp(s, -1)).abs().max() < 2e-2
 
@@ -462,8 +522,10 @@ TC_CASES = {
     "d256_multi_segment": (256, 20000, 1300, 0),
     "d128_multi_segment": (128, 9000, 2100, 0),
     "d64_T1": (64, 640, 384, 1),
-    "d128_T3": (128, 512, 256, 3),
+    "d128_T3": (128, 512, 256, 3),             # T >= 2: update passes with hi + lo operand pairs, one launch per pass
     "d256_T1": (256, 1024, 256, 1),
+    "d256_T2_pairs": (256, 2048, 384, 2),      # same, the CTA-pair form (more than one row tile at D = 256)
+    "d64_T2": (64, 1000, 130, 2),
     # D = 512: the 64-rows-per-CTA pair kernel (one 512-column read-out), updates run as separate launches
     "d512_p2k": (512, 2048, 512, 0),
     "d512_ragged": (512, 1100, 257, 0),
@@ -489,21 +551,39 @@ def _sweep_layer(hf, D, P, T, seed=31):
     return ref, dut.cuda(), g
 
 
+def assert_same_nearest_pattern(scores, got_idx, t_updates=0):
+    """`nearest-pattern argmax indices identical` (BASELINE.json): every row, no gap mask and no escape quota.  The
+    one exclusion is a row the fp32 ORACLE itself cannot decide -- a top-1 / top-2 gap below its own rounding
+    (1e-5 relative, the bound `check_argmax` uses for the fp32 kernels).  With retrieve updates the final scores are
+    those of an iterated state that carries the 16-bit operand rounding of the earlier passes (2e-4 relative): rows
+    closer than that are undecidable for the kernel's own state and are excluded too."""
+    s = scores.reshape(-1, scores.shape[-1])
+    top2 = s.topk(2, dim=-1).values
+    noise = (1e-5 if t_updates == 0 else 2e-3) * top2[:, 0].abs().clamp_min(1.0)
+    decidable = (top2[:, 0] - top2[:, 1]) > noise
+    got_idx = got_idx.cpu().long().reshape(-1)
+    want = s.argmax(-1)
+    bad = (got_idx != want) & decidable
+    assert int(bad.sum()) == 0, f"{int(bad.sum())} of {int(decidable.sum())} rows differ from the oracle's nearest pattern"
+    assert decidable.float().mean() > 0.99
+    return int(decidable.sum())
+
+
 @pytest.mark.parametrize("splits", [0, 3, "streamk"])
 @pytest.mark.parametrize("name", list(TC_CASES))
-def test_forward_parity_tensor_core(hf, name, splits, monkeypatch):
+def test_forward_parity_tensor_core(hf, name, splits):
     """tcgen05 fp16-operand / fp32-accumulate path against the fp32 oracle: rel-L2 <= 1e-3 (north-star bar),
-    nearest-pattern index identical wherever the oracle's top-1/top-2 gap exceeds the 16-bit operand noise."""
+    nearest-pattern index identical on every row (log-sum-exp certificate + fp32 repair, hop_repair.cu)."""
     D, P, N, T = TC_CASES[name]
-    if splits and T > 0 and D <= 256:
+    if splits and T == 1 and D <= 256:
         pytest.skip("on-chip retrieve updates never split the pattern axis")
+    ref, dut, g = _sweep_layer(hf, D, P, T)
     if splits == "streamk":
         if T > 0:
             pytest.skip("stream-K scheduling is the T = 0 form")
-        monkeypatch.setenv("HOP_TC_STREAMK", "1")      # force it at sizes where the heuristic keeps the plain grid
+        dut.tune = dict(streamk=True)          # force it at sizes where the heuristic keeps the plain grid
     elif splits:
-        monkeypatch.setenv("HOP_TC_SPLITS", str(splits))
-    ref, dut, g = _sweep_layer(hf, D, P, T)
+        dut.tune = dict(splits=splits)
     idx = torch.randint(0, P, (N,), generator=g)
     x = ref.lookup_weights[0, idx].detach() + 0.5 * torch.randn(N, D, generator=g)
     dut.kernel_path = "f16"
@@ -513,14 +593,51 @@ def test_forward_parity_tensor_core(hf, name, splits, monkeypatch):
     r = rel_l2(got, want[0])
     print(f"{name} splits={splits}: rel-L2 {r:.3e}")
     assert r < REL_L2_BAR
-    s = scores.reshape(N, P)
-    top2 = s.topk(2, dim=-1).values
-    decided = (top2[:, 0] - top2[:, 1]) > 2e-2
-    got_idx = dut.last_argmax.cpu().long().reshape(-1)
-    assert torch.equal(got_idx[decided], s.argmax(-1)[decided])
-    assert decided.float().mean() > 0.5
-    lse_want = torch.logsumexp(s, -1)
+    assert_same_nearest_pattern(scores, dut.last_argmax, T)
+    lse_want = torch.logsumexp(scores.reshape(N, P), -1)
     assert (dut.last_lse.cpu().reshape(-1) - lse_want).abs().max() < 2e-2
+
+
+@pytest.mark.parametrize("D,P,N", [(64, 2048, 1500), (256, 4096, 700), (512, 2048, 300), (128, 1000, 257)])
+def test_exact_nearest_pattern_on_diffuse_scores(hf, D, P, N):
+    """Random (un-planted) queries: top-1 / top-2 gaps go down to 1e-4 and the 16-bit scores alone pick another
+    pattern on a few per cent of the rows.  With HOP_F_EXACT_ARGMAX (the layer's default) the undecided rows are
+    re-scored in fp32 and every index equals the oracle's; switching the repair off shows the mismatches it removes."""
+    ref, dut, g = _sweep_layer(hf, D, P, 0)
+    x = torch.randn(N, D, generator=g)
+    dut.kernel_path = "f16"
+    with torch.no_grad():
+        want, _, scores, _ = ref(x[None], return_details=True)
+        got = dut(x.cuda())
+        exact_idx = dut.last_argmax.clone()
+        dut.exact_argmax = False
+        dut(x.cuda())
+        raw_idx = dut.last_argmax.clone()
+    assert rel_l2(got, want[0]) < REL_L2_BAR
+    checked = assert_same_nearest_pattern(scores, exact_idx)
+    raw_bad = int((raw_idx.cpu().long() != scores.reshape(N, P).argmax(-1)).sum())
+    print(f"D={D} P={P}: {checked} rows checked, 16-bit scores alone mismatch on {raw_bad} rows, repaired: 0")
+
+
+@pytest.mark.parametrize("N", [4096, 8192])
+def test_update_passes_never_take_streamk(hf, N):
+    """T >= 1 at D = 64, P = 128k used to let the per-pass launches pick stream-K against a
+    workspace sized for the plain grid (HOP_ERR_WORKSPACE at N = 2k..4k, unbounded accumulation chains at 8k..16k).
+    Every launch of the one-launch-per-pass form now runs the plain grid with chains of at most 256 tiles."""
+    import bench
+    P, D, T = 131072, 64, 1
+    w, wv, wo = bench.make_state(P, D, T)
+    layer = bench.build_layer(hf.HopfieldLayer, P, D, T, w, wv, wo).cuda()
+    layer.kernel_path = "f16"
+    xh, _ = bench.make_queries(w, N)
+    with torch.no_grad():
+        y = layer(xh.cuda())
+        got, got_arg = y[:96].cpu(), layer.last_argmax[:96].cpu().long()
+    want, arg, gap = chunked_oracle(xh[:96], w, wv, wo, T, 1.0 / math.sqrt(D))
+    r = rel_l2(got, want)
+    print(f"N={N}: rel-L2 {r:.3e}")
+    assert r < REL_L2_BAR
+    assert torch.equal(got_arg[gap > 2e-2], arg[gap > 2e-2])
 
 
 @pytest.mark.parametrize("D", [128, 512])
@@ -537,12 +654,11 @@ def test_tensor_core_bf16_runs(hf, D):
 
 
 @pytest.mark.parametrize("D,P,N,T", [(512, 1500, 333, 0), (512, 1024, 200, 1), (1024, 900, 150, 0)])
-def test_wide_widths_on_the_128_row_kernel(hf, D, P, N, T, monkeypatch):
-    """HOP_TC_HALFM=0 keeps D >= 512 on the 128-row kernel (score tile recomputed per 256-column chunk; 64 live rows
-    at D = 1024): the comparison path stays parity-green.  (Shapes no other test uses: the host side caches
-    workspace sizes per shape.)"""
-    monkeypatch.setenv("HOP_TC_HALFM", "0")
+def test_wide_widths_on_the_128_row_kernel(hf, D, P, N, T):
+    """tune rows128 (HOP_TUNE_ROWS128) keeps D >= 512 on the 128-row kernel (score tile recomputed per 256-column
+    chunk; 64 live rows at D = 1024): the comparison path stays parity-green."""
     ref, dut, g = _sweep_layer(hf, D, P, T, seed=47)
+    dut.tune = dict(rows128=True)
     idx = torch.randint(0, P, (N,), generator=g)
     x = ref.lookup_weights[0, idx].detach() + 0.5 * torch.randn(N, D, generator=g)
     dut.kernel_path = "f16"
@@ -550,18 +666,13 @@ def test_wide_widths_on_the_128_row_kernel(hf, D, P, N, T, monkeypatch):
         want, _, scores, _ = ref(x[None], return_details=True)
         got = dut(x.cuda())
     assert rel_l2(got, want[0]) < REL_L2_BAR
-    s = scores.reshape(N, P)
-    top2 = s.topk(2, dim=-1).values
-    decided = (top2[:, 0] - top2[:, 1]) > 2e-2
-    assert torch.equal(dut.last_argmax.cpu().long().reshape(-1)[decided], s.argmax(-1)[decided])
+    assert_same_nearest_pattern(scores, dut.last_argmax, T)
 
 
 @pytest.mark.parametrize("splits", [0, 2])
-def test_folded_out_projection_matches_unfolded(hf, splits, monkeypatch):
+def test_folded_out_projection_matches_unfolded(hf, splits):
     """out_proj folded into the read-out operand (V^ Wo^T, hop_patterns.vot16) vs the two-launch form."""
     impl = hf._impl
-    if splits:
-        monkeypatch.setenv("HOP_TC_SPLITS", str(splits))
     ref, dut, g = _sweep_layer(hf, 128, 1024, 0)
     x = ref.lookup_weights[0, :384].detach() + 0.5 * torch.randn(384, 128, generator=g)
     spec, pack = dut.spec(), dut.param_pack()
@@ -571,12 +682,12 @@ def test_folded_out_projection_matches_unfolded(hf, splits, monkeypatch):
         pats = impl.prepare_patterns_op(*[None if pack[k] is None else pack[k].detach().contiguous()
                                           for k in impl.ops._PATTERN_SIDE], spec.flags, path, spec.d_assoc,
                                         spec.d_v, 0, spec.ln_eps)
-        assert pats[5].numel() == 1024 * 128
+        assert pats[5].numel() == 1024 * 128 and len(pats) == impl.ops.N_PACKS
         q = [None if pack[k] is None else pack[k].detach().contiguous() for k in impl.ops._QUERY_SIDE]
-        two = impl.retrieve_op(x.cuda(), *pats, *q, spec.flags, path, spec.d_in, spec.d_out, 0, spec.beta,
-                               spec.ln_eps, 0, True)
-        one = impl.retrieve_op(x.cuda(), *pats, *q, spec.flags, path, spec.d_in, spec.d_out, 0, spec.beta,
-                               spec.ln_eps, 0, False)
+        two = impl.retrieve_op(x.cuda(), pats, *q, spec.flags, path, spec.d_in, spec.d_out, 0, spec.beta,
+                               spec.ln_eps, 0, True, 0.0, 0, splits, 0)
+        one = impl.retrieve_op(x.cuda(), pats, *q, spec.flags, path, spec.d_in, spec.d_out, 0, spec.beta,
+                               spec.ln_eps, 0, False, 0.0, 0, splits, 0)
     assert one[1].numel() == 0 and two[1].shape == (384, 128)
     r1, r2 = rel_l2(one[0], want), rel_l2(two[0], want)
     print(f"folded rel-L2 {r1:.3e}, two-launch rel-L2 {r2:.3e}")
@@ -618,14 +729,26 @@ def test_forward_host_pipelined_matches_forward(hf):
 
 # --------------------------------------------------------------------------- config-5 sweep points at FULL size
 FULL_CASES = {
-    # name: (P, D, T, rows checked)
+    # name: (P, D, T, rows checked)   -- BASELINE config 5: P in {64k, 256k, 1M} x D in {256, 512, 1024} x T in {0, 1, 3}
     "p64k_d256_T0": (65536, 256, 0, 256),
     "p64k_d256_T1": (65536, 256, 1, 128),
+    "p64k_d256_T3": (65536, 256, 3, 96),
     "p64k_d512_T0": (65536, 512, 0, 128),
     "p64k_d512_T1": (65536, 512, 1, 128),
+    "p64k_d512_T3": (65536, 512, 3, 64),
     # long accumulation chains: one launch per pass with bounded per-CTA chains (was 2.1e-3 on-chip)
     "p256k_d256_T1": (262144, 256, 1, 128),
+    # the bifurcation point of the recipe (nearest-pattern weight 0.79, gain 2.7 per pass): 3.3e-3 with plain
+    # 16-bit update operands in round 1, hi + lo operand pairs now
+    "p256k_d256_T3": (262144, 256, 3, 96),
+    "p256k_d512_T0": (262144, 512, 0, 64),
+    "p256k_d512_T3": (262144, 512, 3, 48),
+    "p1m_d256_T0": (1048576, 256, 0, 64),
+    "p1m_d256_T3": (1048576, 256, 3, 32),
+    "p1m_d512_T0": (1048576, 512, 0, 32),
     "p64k_d1024_T0": (65536, 1024, 0, 64),
+    "p64k_d1024_T3": (65536, 1024, 3, 32),
+    "p256k_d1024_T0": (262144, 1024, 0, 32),
 }
 
 
@@ -642,10 +765,14 @@ def test_sweep_point_full_size_parity(hf, name):
     with torch.no_grad():
         y = layer(xh.cuda())
         got, got_arg = y[:sub].cpu(), layer.last_argmax[:sub].cpu().long()
+    del y
     want, arg, gap = chunked_oracle(xh[:sub], w, wv, wo, T, 1.0 / math.sqrt(D))
     r = rel_l2(got, want)
-    decided = gap > 2e-2
-    print(f"{name}: rel-L2 {r:.3e}, argmax checked on {int(decided.sum())} rows")
+    # every checked row must name the oracle's nearest pattern; the only exclusion is a row the fp32 checker itself
+    # cannot decide (gap below its own rounding; with updates: below the 16-bit rounding its iterated state carries)
+    decidable = gap > (1e-4 if T == 0 else 2e-2)
+    bad = int(((got_arg != arg) & decidable).sum())
+    print(f"{name}: rel-L2 {r:.3e}, nearest pattern identical on {int(decidable.sum())} / {sub} checked rows")
     assert r < REL_L2_BAR
-    assert decided.float().mean() > 0.5
-    assert torch.equal(got_arg[decided], arg[decided])
+    assert bad == 0
+    assert decidable.float().mean() > 0.95
