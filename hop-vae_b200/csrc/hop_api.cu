@@ -206,8 +206,9 @@ int hop_sm100_workspace_bytes(const hop_desc* desc, int for_backward, size_t* by
   HOP_TRY(validate_desc(desc));
   if (!bytes) HOP_FAIL(HOP_ERR_BAD_ARG, "bytes is NULL");
   if (for_backward) {
-    *bytes = simt_backward_workspace(*desc);
-    if (tc_backward_supported(desc->n_rows, desc->n_patterns, desc->d_assoc, desc->d_v) && !(desc->tune_flags & HOP_TUNE_BWD_SIMT))
+    *bytes = simt_backward_workspace(*desc);      // (its total is a multiple of 256: the tensor-core part follows it)
+    if (desc->path != HOP_PATH_FP32_SIMT && desc->path != HOP_PATH_AUTO && !(desc->tune_flags & HOP_TUNE_BWD_SIMT) &&
+        tc_backward_supported(desc->n_rows, desc->n_patterns, desc->d_assoc, desc->d_v))
       *bytes += tc_backward_workspace(desc->n_rows, desc->n_patterns, desc->d_assoc, desc->d_v);
   } else {
     const int path = resolve_path(desc);

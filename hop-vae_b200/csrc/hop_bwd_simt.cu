@@ -861,9 +861,12 @@ size_t simt_backward_workspace(const hop_desc& d) { return carve(d, nullptr).tot
 int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patterns& pt, const float* x,
                          const float* qhat, const float* retrieved, const float* lse, const float* grad_out,
                          const hop_grads& g, void* ws, size_t ws_bytes, cudaStream_t st) {
-  (void)ws_bytes;
-  if (d.d_assoc > 128 || d.d_v > 128)
-    HOP_FAIL(HOP_ERR_UNSUPPORTED, "backward is built for H, Dv <= 128 (got %d, %d)", d.d_assoc, d.d_v);
+  // association core: tcgen05 (hop_bwd_tc.cu) when the step ran on a tensor-core path, else the fp32 kernels below
+  const bool tc_core = d.path != HOP_PATH_FP32_SIMT && d.path != HOP_PATH_AUTO && !(d.tune_flags & HOP_TUNE_BWD_SIMT) &&
+                       tc_backward_supported(d.n_rows, d.n_patterns, d.d_assoc, d.d_v);
+  if (!tc_core && (d.d_assoc > 128 || d.d_v > 128))
+    HOP_FAIL(HOP_ERR_UNSUPPORTED, "fp32 backward core is built for H, Dv <= 128 (got %d, %d); wider layers train on the "
+             "tensor-core path (hop_sm100_select_train_path)", d.d_assoc, d.d_v);
   const BwdWs w = carve(d, ws);
   const int N = d.n_rows, P = d.n_patterns, H = d.d_assoc, Dv = d.d_v, Din = d.d_in;
   const bool out_proj = d.flags & HOP_F_OUT_PROJ, q_proj = d.flags & HOP_F_PROJ_STATE;
@@ -886,6 +889,7 @@ int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patte
     if (out_proj && g.d_wo) { HOP_TRY(zero(g.d_wo, (size_t)d.d_out * Dv)); HOP_TRY(zero(g.d_bo, d.d_out)); }
     HOP_TRY(zero(w.dkhat, (size_t)P * H));
     HOP_TRY(zero(w.dvhat, (size_t)P * Dv));
+    if (tc_core) HOP_TRY(zero(w.dqs, (size_t)N * H));      // the tensor-core core accumulates dq with REDs too
     if (q_proj && g.d_wq) { HOP_TRY(zero(g.d_wq, (size_t)H * Din)); HOP_TRY(zero(g.d_bq, H)); }
     if (g.d_x) { HOP_TRY(zero(g.d_ln_state_w, Din)); HOP_TRY(zero(g.d_ln_state_b, Din)); }
     if (v_proj && g.d_wv) { HOP_TRY(zero(g.d_wv, (size_t)Dv * Din)); HOP_TRY(zero(g.d_bv, Dv)); }
@@ -916,7 +920,16 @@ int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patte
   // 2. association core
   CoreArgs ca{qhat, pt.khat, pt.vhat, lse, dR, retrieved, w.delta, w.dqs, w.dkhat, w.dvhat, N, P, H, Dv, 0};
   const int hc = (H + 63) / 64, dvc = (Dv + 63) / 64;
-  if (H <= 4 && Dv <= 4 && P <= 4096) HOP_TRY(launch_core_tiny(ca, st));
+  if (tc_core) {
+    TcBwdArgs ta{};
+    ta.qs = qhat; ta.lse = lse; ta.dr = dR; ta.r = retrieved;
+    ta.k16 = pt.k16; ta.v16 = pt.v16; ta.kt16 = pt.kt16;
+    ta.dqs = w.dqs; ta.dkhat = w.dkhat; ta.dvhat = w.dvhat;
+    ta.n = N; ta.p = P; ta.h = H; ta.dv = Dv;
+    ta.ws = static_cast<char*>(ws) + w.total;
+    ta.ws_bytes = ws_bytes > w.total ? ws_bytes - w.total : 0;
+    HOP_TRY(launch_tc_backward(ta, st));
+  } else if (H <= 4 && Dv <= 4 && P <= 4096) HOP_TRY(launch_core_tiny(ca, st));
   else if (hc == 1 && dvc == 1) HOP_TRY((launch_core<1, 1>(ca, st)));
   else if (hc == 1 && dvc == 2) HOP_TRY((launch_core<1, 2>(ca, st)));
   else if (hc == 2 && dvc == 1) HOP_TRY((launch_core<2, 1>(ca, st)));

@@ -136,7 +136,7 @@ int launch_tc_forward(const TcPassArgs& a, cudaStream_t st);
 bool tc_supported(int h, int dv);
 // hop_bwd_tc.cu -- association core of the backward on the tensor pipe (dq, dK^, dV^)
 struct TcBwdArgs {
-  const float* qs; const float* lse; const float* dr; const float* delta;   // (N,H), (N), (N,Dv), (N)
+  const float* qs; const float* lse; const float* dr; const float* r;       // (N,H), (N), dR (N,Dv), R = A V^ (N,Dv)
   const void* k16; const void* v16; const void* kt16;                        // pattern packs
   float* dqs; float* dkhat; float* dvhat;                                    // (N,H), (P,H), (P,Dv)
   int n, p, h, dv;

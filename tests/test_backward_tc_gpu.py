@@ -1,0 +1,107 @@
+"""GPU (-m gpu): the tcgen05 backward (hop_bwd_tc.cu) against the oracle's autograd.
+
+What `loss.backward()` at /root/reference/main.py:35 computes through one Hopfield layer, T = 0: gradients of the
+input and of EVERY parameter.  The association core (dq, dK^, dV^ -- five dense contractions) runs on the tensor pipe
+with fp16-encoded operands and fp32 accumulation; LayerNorm / projection backwards stay fp32.  Bar, written here: every
+gradient within rel-L2 <= 5e-3 of the fp32 oracle (16-bit operand rounding, 2^-11 relative per operand, enters the five
+contractions once each; measured values are printed), the forward of the same step within the 1e-3 bar.
+"""
+import pytest
+import torch
+
+from oracle import hflayers_oracle as O
+from util import REL_L2_BAR, rel_l2, randomize_
+
+pytestmark = pytest.mark.gpu
+
+GRAD_BAR = 5e-3
+STATIC = dict(stored_pattern_as_static=True, state_pattern_as_static=True)
+
+
+@pytest.fixture(scope="module")
+def hf():
+    import hflayers
+    hflayers._impl.cabi.load()
+    return hflayers
+
+
+def _pair(hf, D, P, seed, **extra):
+    kw = dict(input_size=D, quantity=P, **STATIC, **extra)
+    ref = randomize_(O.HopfieldLayer(**kw), seed, 1.0)
+    g = torch.Generator().manual_seed(seed + 1)
+    with torch.no_grad():
+        ref.lookup_weights.copy_(torch.randn(1, P, D, generator=g))
+    ref.faithful = False                      # de-duplicated evaluation of the same arithmetic (one flat matmul)
+    dut = hf.HopfieldLayer(**kw)
+    dut.load_state_dict(ref.state_dict())
+    return ref, dut.cuda(), g
+
+
+CASES = {
+    # name: (D, P, N)   -- N x P >= 2^25 selects the tensor-core training path
+    "d256_p4k": (256, 4096, 8192),
+    "d128_p8k": (128, 8192, 4096),
+    "d512_p4k": (512, 4096, 8192),
+    "d256_ragged": (256, 5000, 7001),          # ragged rows and patterns: padded tiles on both axes
+    "d256_p64k": (256, 65536, 2048),           # BASELINE config 5's pattern count
+    "d512_p64k": (512, 65536, 1024),
+}
+
+
+@pytest.mark.parametrize("name", list(CASES))
+def test_backward_parity_tensor_core(hf, name):
+    D, P, N = CASES[name]
+    impl = hf._impl
+    ref, dut, g = _pair(hf, D, P, seed=91)
+    dut.kernel_path = "f16"
+    assert impl.ops.resolve_train_path(dut.spec(), N, P) == impl.cabi.PATH_TC_F16
+    idx = torch.randint(0, P, (N,), generator=g)
+    x = ref.lookup_weights[0, idx].detach() + 0.5 * torch.randn(N, D, generator=g)
+    w = torch.randn(N, D, generator=g)
+    xr = x.clone().requires_grad_(True)
+    xd = x.cuda().requires_grad_(True)
+    yr = ref(xr)
+    (yr * w).sum().backward()
+    l0 = impl.cabi.launch_count()
+    yd = dut(xd)
+    (yd * w.cuda()).sum().backward()
+    torch.cuda.synchronize()
+    print(f"{name}: forward rel-L2 {rel_l2(yd.detach(), yr.detach()):.3e}, launches fwd+bwd {impl.cabi.launch_count() - l0}")
+    assert rel_l2(yd.detach(), yr.detach()) < REL_L2_BAR
+    worst = rel_l2(xd.grad, xr.grad)
+    print(f"{name}: d_x rel-L2 {worst:.3e}")
+    assert worst < GRAD_BAR
+    rp, dp = dict(ref.named_parameters()), dict(dut.named_parameters())
+    for k in rp:
+        assert dp[k].grad is not None, k
+        if k.endswith("norm_stored_pattern.bias"):
+            # exactly 0 in exact arithmetic (softmax is shift invariant): both sides hold rounding noise only
+            scale = float(rp[k.replace(".bias", ".weight")].grad.norm())
+            assert float(dp[k].grad.norm()) < 2e-2 * scale, k
+            continue
+        r = rel_l2(dp[k].grad, rp[k].grad)
+        print(f"{name}: {k} rel-L2 {r:.3e}")
+        assert r < GRAD_BAR, k
+
+
+def test_backward_tensor_core_matches_fp32_kernels(hf):
+    """Same layer, same inputs: the tensor-core step against the library's own fp32 step (tune bwd_simt keeps the whole
+    step on the exact kernels) -- the two cores must agree to the operand rounding, and tiny gradients (1e-6 of the
+    usual scale) must survive the fp16 operand range through the global rescale."""
+    D, P, N = 128, 8192, 4096
+    ref, dut, g = _pair(hf, D, P, seed=95)
+    dut.kernel_path = "f16"
+    x = torch.randn(N, D, generator=g).cuda()
+    w = (1e-6 * torch.randn(N, D, generator=g)).cuda()
+    grads = {}
+    for mode in ("tc", "fp32"):
+        dut.tune = dict(bwd_simt=(mode == "fp32"))
+        dut.zero_grad(set_to_none=True)
+        xd = x.clone().requires_grad_(True)
+        (dut(xd) * w).sum().backward()
+        torch.cuda.synchronize()
+        grads[mode] = (xd.grad.clone(), dut.lookup_weights.grad.clone())
+    for a, b, what in zip(grads["tc"], grads["fp32"], ("d_x", "d_lookup")):
+        r = rel_l2(a, b)
+        print(f"tensor-core vs fp32 core, {what}: rel-L2 {r:.3e}")
+        assert r < GRAD_BAR
