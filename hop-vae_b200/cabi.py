@@ -115,7 +115,7 @@ def load() -> C.CDLL:
     lib.hop_sm100_forward.argtypes = [P(HopDesc), P(HopParams), P(HopPatterns), _fp, _fp, _fp, _fp, _fp, _fp, _fp,
                                       _fp, C.c_size_t, _fp]
     lib.hop_sm100_backward.restype = C.c_int
-    lib.hop_sm100_backward.argtypes = [P(HopDesc), P(HopParams), P(HopPatterns), _fp, _fp, _fp, _fp, _fp,
+    lib.hop_sm100_backward.argtypes = [P(HopDesc), P(HopParams), P(HopPatterns), _fp, _fp, _fp, _fp, _fp, _fp,
                                        P(HopGrads), _fp, C.c_size_t, _fp]
     lib.hop_sm100_merge_shards.restype = C.c_int
     lib.hop_sm100_merge_shards.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int32, _fp, _fp, _fp, _fp, _fp, _fp,

@@ -377,8 +377,9 @@ int hop_sm100_forward(const hop_desc* desc, const hop_params* params, const hop_
 }
 
 int hop_sm100_backward(const hop_desc* desc, const hop_params* params, const hop_patterns* patterns, const float* x,
-                       const float* qhat, const float* retrieved, const float* lse, const float* grad_out,
-                       const hop_grads* grads, void* workspace, size_t workspace_bytes, void* stream) {
+                       const float* qhat, const float* retrieved, const float* lse, const int32_t* argmax,
+                       const float* grad_out, const hop_grads* grads, void* workspace, size_t workspace_bytes,
+                       void* stream) {
   HOP_TRY(validate_desc(desc));
   HOP_TRY(device_info(nullptr));
   if (!params || !patterns || !x || !qhat || !retrieved || !lse || !grad_out || !grads)
@@ -391,7 +392,7 @@ int hop_sm100_backward(const hop_desc* desc, const hop_params* params, const hop
     HOP_FAIL(HOP_ERR_WORKSPACE, "backward workspace of %zu bytes needed, %zu given", need, workspace_bytes);
   if (!aligned16(workspace) || !aligned16(grad_out) || !aligned16(qhat) || !aligned16(retrieved))
     HOP_FAIL(HOP_ERR_BAD_ALIGN, "backward buffers must be 16-byte aligned");
-  return launch_simt_backward(*desc, *params, *patterns, x, qhat, retrieved, lse, grad_out, *grads, workspace,
+  return launch_simt_backward(*desc, *params, *patterns, x, qhat, retrieved, lse, argmax, grad_out, *grads, workspace,
                               workspace_bytes, (cudaStream_t)stream);
 }
 

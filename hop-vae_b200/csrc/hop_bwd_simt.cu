@@ -859,8 +859,8 @@ BwdWs carve(const hop_desc& d, void* ws) {
 size_t simt_backward_workspace(const hop_desc& d) { return carve(d, nullptr).total; }
 
 int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patterns& pt, const float* x,
-                         const float* qhat, const float* retrieved, const float* lse, const float* grad_out,
-                         const hop_grads& g, void* ws, size_t ws_bytes, cudaStream_t st) {
+                         const float* qhat, const float* retrieved, const float* lse, const int32_t* argmax,
+                         const float* grad_out, const hop_grads& g, void* ws, size_t ws_bytes, cudaStream_t st) {
   // association core: tcgen05 (hop_bwd_tc.cu) when the step ran on a tensor-core path, else the fp32 kernels below
   const bool tc_core = d.path != HOP_PATH_FP32_SIMT && d.path != HOP_PATH_AUTO && !(d.tune_flags & HOP_TUNE_BWD_SIMT) &&
                        tc_backward_supported(d.n_rows, d.n_patterns, d.d_assoc, d.d_v);
@@ -923,7 +923,7 @@ int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patte
   if (tc_core) {
     TcBwdArgs ta{};
     ta.qs = qhat; ta.lse = lse; ta.dr = dR; ta.r = retrieved;
-    ta.k16 = pt.k16; ta.v16 = pt.v16; ta.kt16 = pt.kt16;
+    ta.k16 = pt.k16; ta.v16 = pt.v16; ta.kt16 = pt.kt16; ta.khat = pt.khat; ta.argmax = argmax;
     ta.dqs = w.dqs; ta.dkhat = w.dkhat; ta.dvhat = w.dvhat;
     ta.n = N; ta.p = P; ta.h = H; ta.dv = Dv;
     ta.ws = static_cast<char*>(ws) + w.total;

@@ -83,6 +83,7 @@ struct BwdKernelArgs {
   float out_scale;               // constant factor of the output (1/log2 e where the operand carried log2 e)
   int use_g;                     // multiply by *gscale
   float* out;                    // (n_stat, w) fp32, zeroed; accumulated with REDs
+  float* csum;                   // MODE_DQ: per stationary row, sum_j dS_j (zeroed; RED) -- see bwd_fix_dq_kernel
 };
 
 __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
@@ -295,7 +296,7 @@ hop_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
     const bool row_ok = grow < a.n_stat;
     const int cbase = h * (kTP / 2) + sub * Cfg::kC;          // first tile column of this thread
     auto arrive_issuer = [&](uint32_t bar) { ptx::mbar_arrive_cluster(ptx::map_to_cta(bar, 0)); };
-    float lse_r = kPadLse, del_r = 0.f;
+    float lse_r = kPadLse, del_r = 0.f, cacc = 0.f;
     if constexpr (MODE == MODE_DQ) {
       if (row_ok) { lse_r = __ldg(a.row_lse2 + grow); del_r = __ldg(a.row_delta + grow); }
     }
@@ -328,6 +329,7 @@ hop_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
           if constexpr (Cfg::kTwo) w4[e] = p * (__uint_as_float(u[4 * i4 + e]) - d4[e]);
           else w4[e] = p;
         }
+        if constexpr (MODE == MODE_DQ) cacc += (w4[0] + w4[1]) + (w4[2] + w4[3]);
         pk[2 * i4] = pack_h2(w4[0], w4[1]);
         pk[2 * i4 + 1] = pack_h2(w4[2], w4[3]);
       }
@@ -349,6 +351,9 @@ hop_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
       arrive_issuer(p_full(b));
     }
 
+    if constexpr (MODE == MODE_DQ) {
+      if (row_ok && nt > 0 && a.csum) atomicAdd(a.csum + grow, cacc);
+    }
     if (nt > 0) {
       const uint32_t last = nt - 1;
       ptx::mbar_wait(p_empty(last & 1), (last >> 1) & 1);
@@ -450,6 +455,33 @@ __global__ void __launch_bounds__(256) bwd_pack_kernel(PackJob j0, PackJob j1, c
   }
 }
 
+// Softmax-Jacobian consistency.  dS_j = A_j (dA_j - delta) is a difference of nearly equal numbers on a saturated row
+// (A ~ one-hot: dA_top ~ delta), and delta = rowsum(dR o R) is exact fp32 while dA comes from fp16-rounded operands: the
+// mismatch (2^-11 |dA|) becomes a common-mode error c_r = sum_j dS_j != 0 that swamps the (tiny) true gradient --
+// measured: d_x off by 3e-2 at w = 0.999, by 10x at D = 512.  The DQ launch accumulates c_r (one fp32 sum per thread, one
+// RED per row); the delta that is consistent with the rounded dA is delta' = delta + c_r, and the consistent gradient
+//     dq* = dq - c_r sum_j A_j k_j  ~=  dq - c_r K^[nearest pattern]
+// -- the read-out A.K^ only multiplies the rounding-sized c_r, so its leading term (the forward's nearest pattern) is
+// enough: the residual is c_r (1 - w) |k|, second order.  dK^ then runs with delta'.  One warp per query row.
+__global__ void __launch_bounds__(256) bwd_fix_dq_kernel(float* __restrict__ dqs, const float* __restrict__ khat,
+                                                         const int32_t* __restrict__ argmax, const float* __restrict__ csum,
+                                                         const float* __restrict__ gmax, float* __restrict__ deltag,
+                                                         int n, int h) {
+  const int row = (blockIdx.x * 256 + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (row >= n) return;
+  const float c = csum[row];
+  const float cg = c * __ldg(gmax);
+  const float* k = khat + (size_t)argmax[row] * h;
+  float* q = dqs + (size_t)row * h;
+  for (int i = lane * 4; i < h; i += 128) {
+    const float4 kv = __ldg(reinterpret_cast<const float4*>(k + i));
+    float4 v = *reinterpret_cast<float4*>(q + i);
+    v.x = fmaf(-cg, kv.x, v.x); v.y = fmaf(-cg, kv.y, v.y); v.z = fmaf(-cg, kv.z, v.z); v.w = fmaf(-cg, kv.w, v.w);
+    *reinterpret_cast<float4*>(q + i) = v;
+  }
+  if (lane == 0) deltag[row] += c;
+}
+
 // ------------------------------------------------------------------ host side
 using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -483,7 +515,7 @@ int bwd_map(CUtensorMap* m, const void* base, int rows, int cols, int box_rows) 
 
 struct TcBwdWs {
   __half *q16, *qt16, *dr16, *drt16;
-  float *lse2, *delta, *deltag, *gmax;
+  float *lse2, *delta, *deltag, *csum, *gmax;
   size_t total;
 };
 TcBwdWs carve_bwd(void* ws, int n, int h, int dv) {
@@ -502,6 +534,7 @@ TcBwdWs carve_bwd(void* ws, int n, int h, int dv) {
   w.lse2 = reinterpret_cast<float*>(take(npad * 4));
   w.delta = reinterpret_cast<float*>(take(npad * 4));
   w.deltag = reinterpret_cast<float*>(take(npad * 4));
+  w.csum = reinterpret_cast<float*>(take(npad * 4));
   w.gmax = reinterpret_cast<float*>(take(256));
   w.total = off;
   return w;
@@ -563,8 +596,12 @@ int launch_core_tc(const TcBwdArgs& a, const TcBwdWs& w, cudaStream_t st) {
   BwdKernelArgs k{};
   k.w = H; k.gscale = w.gmax; k.out_scale = 1.f; k.use_g = 1;
   // dq: queries stationary, patterns streamed
-  k.n_stat = a.n; k.n_stream = ppad; k.row_lse2 = w.lse2; k.row_delta = w.deltag; k.out = a.dqs;
+  k.n_stat = a.n; k.n_stream = ppad; k.row_lse2 = w.lse2; k.row_delta = w.deltag; k.out = a.dqs; k.csum = w.csum;
   HOP_TRY((launch_mode<H, MODE_DQ>(mq, mdr, mk, mv, mkt, k, npad, st)));
+  k.csum = nullptr;
+  // consistent delta for the dK^ launch, common-mode correction of dq (pattern_offset-free indices of this call)
+  bwd_fix_dq_kernel<<<(a.n + 7) / 8, 256, 0, st>>>(a.dqs, a.khat, a.argmax, w.csum, w.gmax, w.deltag, a.n, H);
+  HOP_LAUNCH_CHECK("bwd_fix_dq_kernel");
   // dK^ and dV^: patterns stationary, queries streamed
   k.n_stat = a.p; k.n_stream = npad; k.row_lse2 = nullptr; k.row_delta = nullptr;
   k.col_lse2 = w.lse2; k.col_delta = w.deltag; k.out = a.dkhat;
@@ -591,11 +628,13 @@ size_t tc_backward_workspace(int n, int p, int h, int dv) {
 int launch_tc_backward(const TcBwdArgs& a, cudaStream_t st) {
   if (!tc_backward_supported(a.n, a.p, a.h, a.dv)) HOP_FAIL(HOP_ERR_UNSUPPORTED, "tensor-core backward: H == Dv in {128, 256, 512}");
   if (!a.k16 || !a.v16 || !a.kt16) HOP_FAIL(HOP_ERR_BAD_ARG, "tensor-core backward needs the k16 / v16 / kt16 packs (HOP_F_TRAIN)");
+  if (!a.argmax || !a.khat) HOP_FAIL(HOP_ERR_BAD_ARG, "tensor-core backward needs the forward's nearest-pattern indices and the fp32 K^");
   const size_t need = tc_backward_workspace(a.n, a.p, a.h, a.dv);
   if (!a.ws || a.ws_bytes < need) HOP_FAIL(HOP_ERR_WORKSPACE, "tensor-core backward needs %zu workspace bytes, %zu given", need, a.ws_bytes);
   const TcBwdWs w = carve_bwd(a.ws, a.n, a.h, a.dv);
   const int npad = round_up(a.n, kTP);
   HOP_CUDA(cudaMemsetAsync(w.gmax, 0, 256, st));
+  HOP_CUDA(cudaMemsetAsync(w.csum, 0, (size_t)npad * sizeof(float), st));
   bwd_stats_kernel<<<(npad + 7) / 8, 256, 0, st>>>(a.dr, a.r, a.lse, a.n, npad, a.dv, w.delta, w.lse2, w.gmax);
   HOP_LAUNCH_CHECK("bwd_stats_kernel");
   PackJob jq{a.qs, a.n, npad, a.h, w.q16, kLog2e, w.qt16, 1.f, 0};

@@ -88,7 +88,7 @@ struct SimtPassArgs {
 int launch_simt_pass(const SimtPassArgs& a, cudaStream_t st);
 // hop_bwd_simt.cu
 int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patterns& pt, const float* x,
-                         const float* qhat, const float* retrieved, const float* lse,
+                         const float* qhat, const float* retrieved, const float* lse, const int32_t* argmax,
                          const float* grad_out, const hop_grads& g, void* ws, size_t ws_bytes,
                          cudaStream_t st);
 size_t simt_backward_workspace(const hop_desc& d);
@@ -138,6 +138,7 @@ bool tc_supported(int h, int dv);
 struct TcBwdArgs {
   const float* qs; const float* lse; const float* dr; const float* r;       // (N,H), (N), dR (N,Dv), R = A V^ (N,Dv)
   const void* k16; const void* v16; const void* kt16;                        // pattern packs
+  const float* khat; const int32_t* argmax;                                  // fp32 K^ (P,H), the forward's nearest pattern (N)
   float* dqs; float* dkhat; float* dvhat;                                    // (N,H), (P,H), (P,Dv)
   int n, p, h, dv;
   void* ws; size_t ws_bytes;

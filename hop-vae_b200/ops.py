@@ -145,7 +145,8 @@ def prepare_patterns(lookup: Tensor, lookup_targets: Optional[Tensor], ln_stored
         _req_cuda_f32(t, name)
     P, d_in = lookup.shape
     d_out = wo.shape[0] if (wo is not None and (flags & cabi.F_OUT_PROJ)) else 1
-    d = _desc(flags, path, 1, P, d_in, d_assoc, d_v, d_out, update_steps, 1.0, ln_eps, 0, 0.0, 0, 0, tune_flags)
+    d = _desc(flags, path, 1, P, d_in, d_assoc, d_v, d_out, update_steps, 1.0, ln_eps, 0,
+              1.0 if update_steps < 0 else 0.0, 0, 0, tune_flags)      # (T < 0 is only valid together with a stop rule)
     dev = lookup.device
     sizes = cabi.HopPatternSizes()
     cabi.check(lib.hop_sm100_pattern_bytes(C.byref(d), C.byref(sizes)), "hop_sm100_pattern_bytes")
@@ -310,8 +311,8 @@ def resolve_train_path(spec: LayerSpec, n_rows: int, n_patterns: int) -> int:
     return int(out.value)
 
 
-def retrieve_backward(grad_out: Tensor, x: Tensor, qhat: Tensor, retrieved: Tensor, lse: Tensor, pats: List[Tensor],
-                      lookup: Tensor, lookup_targets: Optional[Tensor],
+def retrieve_backward(grad_out: Tensor, x: Tensor, qhat: Tensor, retrieved: Tensor, lse: Tensor, argmax: Tensor,
+                      pats: List[Tensor], lookup: Tensor, lookup_targets: Optional[Tensor],
                       ln_state_w: Optional[Tensor], ln_state_b: Optional[Tensor], ln_stored_w: Optional[Tensor],
                       ln_stored_b: Optional[Tensor], ln_proj_w: Optional[Tensor], ln_proj_b: Optional[Tensor],
                       wq: Optional[Tensor], bq: Optional[Tensor], wk: Optional[Tensor], bk: Optional[Tensor],
@@ -352,13 +353,14 @@ def retrieve_backward(grad_out: Tensor, x: Tensor, qhat: Tensor, retrieved: Tens
     go = grad_out.contiguous()
     with _on_device(dev):
         cabi.check(lib.hop_sm100_backward(C.byref(d), C.byref(params), C.byref(ps), cabi.ptr(x), cabi.ptr(qhat),
-                                          cabi.ptr(retrieved), cabi.ptr(lse), cabi.ptr(go), C.byref(grads),
+                                          cabi.ptr(retrieved), cabi.ptr(lse), cabi.ptr(argmax), cabi.ptr(go),
+                                          C.byref(grads),
                                           cabi.ptr(ws), need, _stream(dev)), "hop_sm100_backward")
     return [g[k] for k in _GRAD_ORDER]
 
 
 @torch.library.custom_op("hop_sm100::retrieve_backward", mutates_args=(), device_types="cuda")
-def retrieve_backward_op(grad_out: Tensor, x: Tensor, qhat: Tensor, retrieved: Tensor, lse: Tensor,
+def retrieve_backward_op(grad_out: Tensor, x: Tensor, qhat: Tensor, retrieved: Tensor, lse: Tensor, argmax: Tensor,
                          pats: List[Tensor], lookup: Tensor, lookup_targets: Optional[Tensor],
                          ln_state_w: Optional[Tensor], ln_state_b: Optional[Tensor], ln_stored_w: Optional[Tensor],
                          ln_stored_b: Optional[Tensor], ln_proj_w: Optional[Tensor], ln_proj_b: Optional[Tensor],
@@ -367,14 +369,14 @@ def retrieve_backward_op(grad_out: Tensor, x: Tensor, qhat: Tensor, retrieved: T
                          flags: int, path: int, d_out: int, beta: float, ln_eps: float,
                          tune_flags: int = 0) -> List[Tensor]:
     """torch.compile-visible wrapper of `retrieve_backward` (empty tensors where the parameter is absent)."""
-    res = retrieve_backward(grad_out, x, qhat, retrieved, lse, pats, lookup, lookup_targets, ln_state_w,
+    res = retrieve_backward(grad_out, x, qhat, retrieved, lse, argmax, pats, lookup, lookup_targets, ln_state_w,
                             ln_state_b, ln_stored_w, ln_stored_b, ln_proj_w, ln_proj_b, wq, bq, wk, bk, wv, bv, wo,
                             bo, flags, path, d_out, beta, ln_eps, tune_flags)
     return [r if r is not None else torch.empty((0,), device=x.device) for r in res]
 
 
 @retrieve_backward_op.register_fake
-def _(grad_out, x, qhat, retrieved, lse, pats, lookup, lookup_targets, ln_state_w, ln_state_b, ln_stored_w,
+def _(grad_out, x, qhat, retrieved, lse, argmax, pats, lookup, lookup_targets, ln_state_w, ln_state_b, ln_stored_w,
       ln_stored_b, ln_proj_w, ln_proj_b, wq, bq, wk, bk, wv, bv, wo, bo, flags, path, d_out, beta, ln_eps,
       tune_flags=0):
     like = lambda t: torch.empty_like(t) if t is not None else x.new_empty((0,))
@@ -425,7 +427,7 @@ class HopfieldAssociation(torch.autograd.Function):
         ctx.spec = spec
         ctx.path, ctx.flags = path, flags
         ctx.present = [p is not None for p in params]
-        ctx.save_for_backward(x, qhat, retrieved, lse, *pats, *[p for p in params if p is not None])
+        ctx.save_for_backward(x, qhat, retrieved, lse, argmax, *pats, *[p for p in params if p is not None])
         ctx.mark_non_differentiable(argmax, lse)
         return out, argmax, lse
 
@@ -435,12 +437,12 @@ class HopfieldAssociation(torch.autograd.Function):
         if grad_out is None:
             return (None,) * (2 + len(ctx.present))
         saved = list(ctx.saved_tensors)
-        x, qhat, retrieved, lse = saved[:4]
-        pats = saved[4:4 + N_PACKS]
-        it = iter(saved[4 + N_PACKS:])
+        x, qhat, retrieved, lse, argmax = saved[:5]
+        pats = saved[5:5 + N_PACKS]
+        it = iter(saved[5 + N_PACKS:])
         pd = {k: (next(it) if present else None) for k, present in zip(_PARAM_ORDER, ctx.present)}
         grads = (retrieve_backward if _eager() else retrieve_backward_op)(
-            grad_out.contiguous(), x, qhat, retrieved, lse, pats, *[pd[k] for k in _PARAM_ORDER], ctx.flags,
+            grad_out.contiguous(), x, qhat, retrieved, lse, argmax, pats, *[pd[k] for k in _PARAM_ORDER], ctx.flags,
             ctx.path, spec.d_out, spec.beta, spec.ln_eps, spec.tune_flags)
         gd = dict(zip(_GRAD_ORDER, grads))
         outs = [None, gd["d_x"] if ctx.needs_input_grad[1] else None]

@@ -238,6 +238,8 @@ int hop_sm100_forward(const hop_desc* desc, const hop_params* params,
 int hop_sm100_backward(const hop_desc* desc, const hop_params* params,
                        const hop_patterns* patterns, const float* x,
                        const float* qhat, const float* retrieved, const float* lse,
+                       const int32_t* argmax,   /* the forward's nearest-pattern indices (pattern_offset 0);
+                                                   needed on a tensor-core path, NULL ok on the fp32 path */
                        const float* grad_out, const hop_grads* grads,
                        void* workspace, size_t workspace_bytes, void* stream);
 
