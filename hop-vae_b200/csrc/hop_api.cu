@@ -197,7 +197,7 @@ FwdWs fwd_ws(const hop_desc& d, int path, bool exact) {
   } else if (simt_stop_rule(d)) {
     w.stat = round_up_sz(N * sizeof(float), 256);
   }
-  w.total = 2 * w.q + w.r + w.tc + w.repair + w.qfinal + 2 * w.stat + (w.stat ? 256 : 0);
+  w.total = 2 * w.q + w.r + w.tc + w.repair + w.qfinal + 3 * w.stat + (w.stat ? 256 : 0);   // stat: lse, rowmax, ||q||
   return w;
 }
 }  // namespace
@@ -293,7 +293,7 @@ int hop_sm100_forward(const hop_desc* desc, const hop_params* params, const hop_
     // passes behind a converged iteration become identity passes -- decided on the device, no host synchronisation.
     const int T = simt_update_count(d);
     float* row_scratch = stop_rule ? reinterpret_cast<float*>(region(off_stat)) : nullptr;
-    uint32_t* stopped = stop_rule ? reinterpret_cast<uint32_t*>(region(off_stat + 2 * W.stat)) : nullptr;
+    uint32_t* stopped = stop_rule ? reinterpret_cast<uint32_t*>(region(off_stat + 3 * W.stat)) : nullptr;
     if (stop_rule) HOP_CUDA(cudaMemsetAsync(stopped, 0, sizeof(uint32_t), st));
     float* cur = const_cast<float*>(qs);      // buffer holding the current state (nullptr: still the raw x, fused)
     float* prev = nullptr;
@@ -356,6 +356,12 @@ int hop_sm100_forward(const hop_desc* desc, const hop_params* params, const hop_
   a.ws_bytes = W.tc;
   a.tune = tune_of(d);
   a.zero_words = exact ? reinterpret_cast<uint32_t*>(region(off_repair)) : nullptr;
+  bool cert_done = false;
+  if (exact) {
+    a.cert = repair_cert_args(region(off_repair), d.n_rows, d.d_assoc, patterns->kstats,
+                              reinterpret_cast<float*>(region(off_stat + 2 * W.stat)));
+    a.cert_done = &cert_done;
+  }
   HOP_TRY(launch_tc_forward(a, st));
   if (exact) {
     RepairArgs r{};
@@ -367,6 +373,7 @@ int hop_sm100_forward(const hop_desc* desc, const hop_params* params, const hop_
     r.n = d.n_rows; r.p = d.n_patterns; r.h = d.d_assoc; r.pattern_offset = d.pattern_offset;
     r.lse = lse_w; r.rowmax = rowmax_w; r.argmax = argmax;
     r.ws = region(off_repair); r.ws_bytes = W.repair;
+    r.precertified = cert_done ? 1 : 0;
     HOP_TRY(launch_argmax_repair(r, st));
   }
   if (folded) return HOP_OK;

@@ -104,7 +104,15 @@ struct RepairArgs {
   const float* lse; float* rowmax; int32_t* argmax;   // results of the 16-bit pass; argmax / rowmax are corrected in place
   void* ws; size_t ws_bytes;  // repair_workspace_bytes(n, h); its first 16 bytes are the control words, which the
                               // forward kernel of the same call clears (TcPassArgs::zero_words)
+  int precertified;           // the forward's merge kernel already evaluated the certificate and built the list
 };
+// Where the merge kernels of the tensor-core forward evaluate the certificate themselves (they hold lse and the row
+// maximum of every row in registers): the repair list of hop_repair.cu, the query norms the forward's prologue wrote.
+struct CertArgs {
+  uint32_t* ctrl; int32_t* list; unsigned long long* best;   // repair list (ctrl == nullptr: no certificate)
+  const float* kstats; float* qn;                             // max_j ||K^_j||, per-row ||q|| (N floats, written by the forward)
+};
+CertArgs repair_cert_args(void* ws, int n, int h, const float* kstats, float* qn);
 size_t repair_workspace_bytes(int n, int h);
 int launch_argmax_repair(const RepairArgs& a, cudaStream_t st);
 // ||A_t - A_(t-1)||_F per batch item, max over items, compared with eps: sets *stopped (device) to 1 when the
@@ -127,6 +135,8 @@ struct TcPassArgs {
   void* ws; size_t ws_bytes;   // partial results of the pattern splits (tc_forward_workspace bytes)
   TcTune tune;
   uint32_t* zero_words;        // 4 control words the first launch clears (repair counters) or nullptr
+  CertArgs cert;               // certificate evaluated by the merge kernel of the launch that produces argmax
+  bool* cert_done;             // set when that happened (else the caller runs certify_rows_kernel)
 };
 int tc_choose_splits(int n, int p, int d, int update_steps, const TcTune& tune);
 bool tc_use_pair(int n, int d, const TcTune& tune);

@@ -121,6 +121,7 @@ struct TcKernelArgs {
   int streamk, sk_base, sk_rem, sk_max_seg;
   float* retrieved; float* qsave; float* lse; int32_t* argmax; float* rowmax; int pattern_offset;
   uint32_t* zero_words;                 // 4 control words of the argmax repair, cleared by CTA (0,0,0) (or nullptr)
+  float* qn;                            // per-row ||q|| of the pass (exact-argmax certificate) or nullptr
   // partial outputs when splits > 1: (splits, N, D), (splits, N) x3
   float* part_o; float* part_lse; float* part_max; int32_t* part_arg;
 };
@@ -583,6 +584,14 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
             for (int v = 0; v < kVec; ++v) {
               xv[u][v].x *= qscale; xv[u][v].y *= qscale; xv[u][v].z *= qscale; xv[u][v].w *= qscale;
             }
+          }
+          if (a.qn != nullptr && t0 == 0 && blockIdx.z == 0) {       // ||q|| of the row: bounds the 16-bit score noise
+            float s2 = 0.f;
+#pragma unroll
+            for (int v = 0; v < kVec; ++v)
+              s2 += xv[u][v].x * xv[u][v].x + xv[u][v].y * xv[u][v].y + xv[u][v].z * xv[u][v].z + xv[u][v].w * xv[u][v].w;
+            s2 = warp_sum(s2);
+            if (lane == 0 && gr < a.n) a.qn[gr] = sqrtf(s2);
           }
 #pragma unroll
           for (int v = 0; v < kVec; ++v) {
@@ -1100,6 +1109,14 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
               xv[u][v].x *= qscale; xv[u][v].y *= qscale; xv[u][v].z *= qscale; xv[u][v].w *= qscale;
             }
           }
+          if (a.qn != nullptr && t0 == 0 && blockIdx.z == 0) {       // ||q|| of the row: bounds the 16-bit score noise
+            float s2 = 0.f;
+#pragma unroll
+            for (int v = 0; v < kVec; ++v)
+              s2 += xv[u][v].x * xv[u][v].x + xv[u][v].y * xv[u][v].y + xv[u][v].z * xv[u][v].z + xv[u][v].w * xv[u][v].w;
+            s2 = warp_sum(s2);
+            if (lane == 0 && gr < a.n) a.qn[gr] = sqrtf(s2);
+          }
 #pragma unroll
           for (int v = 0; v < kVec; ++v) {
             const int e = lane * 4 + v * 128;
@@ -1269,13 +1286,23 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
   }
 }
 
+// The exact-argmax certificate of hop_repair.cu, evaluated where lse and the row maximum are already in registers.
+__device__ __forceinline__ void certify_row(const CertArgs& c, long long r, float lse, float rowmax) {
+  if (c.ctrl == nullptr) return;
+  const float tau = 2.f * c.qn[r] * __ldg(c.kstats) * (1.f / 1024.f) * 1.02f + 1e-5f;
+  if (lse - rowmax < log1pf(__expf(-tau)) - 1e-4f) return;            // every other score is more than tau below
+  const uint32_t slot = atomicAdd(c.ctrl, 1u);
+  c.list[slot] = (int32_t)r;
+  c.best[slot] = 0ull;
+}
+
 // Combine `splits` partial results of one row (flash-decoding merge): weights exp(lse_s - lse).
 template <int D>
 __global__ void tc_combine_kernel(int n, int splits, const float* __restrict__ part_o,
                                   const float* __restrict__ part_lse, const float* __restrict__ part_max,
                                   const int32_t* __restrict__ part_arg, const float* __restrict__ bias,
                                   float out_scale, float* __restrict__ retrieved, float* __restrict__ lse,
-                                  int32_t* __restrict__ argmax, float* __restrict__ rowmax) {
+                                  int32_t* __restrict__ argmax, float* __restrict__ rowmax, const CertArgs cert) {
   const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp_global >= n) return;
   const long long r = warp_global;
@@ -1316,6 +1343,7 @@ __global__ void tc_combine_kernel(int n, int splits, const float* __restrict__ p
     if (lse) lse[r] = m + __logf(z);
     if (rowmax) rowmax[r] = best;
     if (argmax) argmax[r] = arg;
+    certify_row(cert, r, m + __logf(z), best);
   }
 }
 
@@ -1333,7 +1361,7 @@ __global__ void tc_combine_streamk_kernel(int n, StreamKPlan sk, const float* __
                                           const float* __restrict__ part_lse, const float* __restrict__ part_max,
                                           const int32_t* __restrict__ part_arg, const float* __restrict__ bias,
                                           float out_scale, float* __restrict__ retrieved, float* __restrict__ lse,
-                                          int32_t* __restrict__ argmax, float* __restrict__ rowmax) {
+                                          int32_t* __restrict__ argmax, float* __restrict__ rowmax, const CertArgs cert) {
   const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp_global >= n) return;
   const long long r = warp_global;
@@ -1383,6 +1411,7 @@ __global__ void tc_combine_streamk_kernel(int n, StreamKPlan sk, const float* __
     if (lse) lse[r] = m + __logf(z);
     if (rowmax) rowmax[r] = best;
     if (argmax) argmax[r] = arg;
+    certify_row(cert, r, m + __logf(z), best);
   }
 }
 
@@ -1460,6 +1489,8 @@ int launch_d(const TcPassArgs& a, int splits, const TcLaunchOpt& opt, cudaStream
   k.retrieved = a.retrieved; k.qsave = a.qsave; k.lse = a.lse; k.argmax = a.argmax; k.rowmax = a.rowmax;
   k.pattern_offset = a.pattern_offset;
   k.zero_words = opt.zero_words;
+  const CertArgs cert = (a.argmax && a.lse && a.rowmax) ? a.cert : CertArgs{};
+  k.qn = cert.ctrl ? cert.qn : nullptr;
   auto* kern = hop_fwd_tc_kernel<H, DV, kBf16, kCluster, kPair, kPrecise>;
   const int row_tiles = (a.n + Cfg::kRows - 1) / Cfg::kRows;
   const int row_groups = (row_tiles + kCluster - 1) / kCluster;
@@ -1515,8 +1546,9 @@ int launch_d(const TcPassArgs& a, int splits, const TcLaunchOpt& opt, cudaStream
       const int threads = 256, rows_per_block = threads / 32;
       tc_combine_streamk_kernel<H><<<(a.n + rows_per_block - 1) / rows_per_block, threads, 0, st>>>(
           a.n, sk, k.part_o, k.part_lse, k.part_max, k.part_arg, a.bias, a.out_scale, a.retrieved, a.lse, a.argmax,
-          a.rowmax);
+          a.rowmax, cert);
       HOP_LAUNCH_CHECK("tc_combine_streamk_kernel");
+      if (cert.ctrl && a.cert_done) *a.cert_done = true;
       return HOP_OK;
     }
   }
@@ -1551,8 +1583,9 @@ int launch_d(const TcPassArgs& a, int splits, const TcLaunchOpt& opt, cudaStream
     const int threads = 256, rows_per_block = threads / 32;
     tc_combine_kernel<H><<<(a.n + rows_per_block - 1) / rows_per_block, threads, 0, st>>>(
         a.n, k.splits, k.part_o, k.part_lse, k.part_max, k.part_arg, a.bias, a.out_scale, a.retrieved, a.lse, a.argmax,
-        a.rowmax);
+        a.rowmax, cert);
     HOP_LAUNCH_CHECK("tc_combine_kernel");
+    if (cert.ctrl && a.cert_done) *a.cert_done = true;
   }
   return HOP_OK;
 }
@@ -1576,6 +1609,8 @@ int launch_h64(const TcPassArgs& a, int splits, const TcLaunchOpt& opt, cudaStre
   k.retrieved = a.retrieved; k.qsave = a.qsave; k.lse = a.lse; k.argmax = a.argmax; k.rowmax = a.rowmax;
   k.pattern_offset = a.pattern_offset;
   k.zero_words = opt.zero_words;
+  const CertArgs cert = (a.argmax && a.lse && a.rowmax) ? a.cert : CertArgs{};
+  k.qn = cert.ctrl ? cert.qn : nullptr;
   if (k.splits > 1) {
     const size_t need = ws_for_splits_fwd(splits, a.n, a.dv);
     if (!a.ws || a.ws_bytes < need)
@@ -1606,8 +1641,9 @@ int launch_h64(const TcPassArgs& a, int splits, const TcLaunchOpt& opt, cudaStre
     const int threads = 256, rows_per_block = threads / 32;
     tc_combine_kernel<H><<<(a.n + rows_per_block - 1) / rows_per_block, threads, 0, st>>>(
         a.n, k.splits, k.part_o, k.part_lse, k.part_max, k.part_arg, a.bias, a.out_scale, a.retrieved, a.lse, a.argmax,
-        a.rowmax);
+        a.rowmax, cert);
     HOP_LAUNCH_CHECK("tc_combine_kernel");
+    if (cert.ctrl && a.cert_done) *a.cert_done = true;
   }
   return HOP_OK;
 }

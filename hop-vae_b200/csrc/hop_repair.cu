@@ -6,8 +6,10 @@
 // whenever the top-1 / top-2 gap exceeds tau = 2 |q| max_j|k_j| 2^-10.  The forward already holds a certificate for
 // that: lse - rowmax = log(1 + sum_{j != top} exp(s_j - s_top)), so  lse - rowmax < log(1 + e^-tau)  proves that EVERY
 // other score lies more than tau below the maximum.  `certify_rows_kernel` evaluates it per row (|q_r| recomputed in
-// fp32 from the raw row, mirroring the forward's LN_q prologue); rows that fail are appended to a compact list together
-// with their fp32 query row, and `argmax_repair_kernel` re-scores exactly those rows against the fp32 K^ on CUDA cores
+// fp32 from the raw row, mirroring the forward's LN_q prologue; where the forward ends in a merge kernel -- every large
+// problem -- that kernel evaluates the certificate itself from the norms the forward's prologue wrote, and this launch
+// is skipped); rows that fail are appended to a compact list, and `argmax_repair_kernel` rebuilds their fp32 query rows
+// from the raw input and re-scores exactly those rows against the fp32 K^ on CUDA cores
 // (64 x 64 register-tiled FFMA), merging (score, index) with a packed 64-bit atomicMax; the last CTA to finish writes
 // the corrected index / row maximum back.  With well-separated retrievals (BASELINE config 5's recipe: gap ~ 10 nats)
 // no row is flagged and the two launches cost ~4 us; with diffuse scores every row is flagged and the repair is a
@@ -31,7 +33,7 @@ constexpr int KC = 64;                // contraction chunk
 constexpr int TS = KC + 4;            // smem stride
 
 struct RepairWs {
-  uint32_t* ctrl; int32_t* list; unsigned long long* best; float* qc; size_t total;
+  uint32_t* ctrl; int32_t* list; unsigned long long* best; size_t total;
 };
 
 RepairWs carve_repair(void* ws, int n, int h) {
@@ -45,7 +47,7 @@ RepairWs carve_repair(void* ws, int n, int h) {
   w.ctrl = reinterpret_cast<uint32_t*>(take(kCtrlBytes));
   w.list = reinterpret_cast<int32_t*>(take((size_t)n * sizeof(int32_t)));
   w.best = reinterpret_cast<unsigned long long*>(take((size_t)n * sizeof(unsigned long long)));
-  w.qc = reinterpret_cast<float*>(take((size_t)n * h * sizeof(float)));
+  (void)h;
   w.total = off;
   return w;
 }
@@ -91,22 +93,22 @@ __global__ void __launch_bounds__(NT) certify_rows_kernel(RepairArgs a, RepairWs
   const float tau = 2.f * sqrtf(qn2) * __ldg(a.kstats) * (1.f / 1024.f) * 1.02f + 1e-5f;
   const bool certified = gap_stat < log1pf(__expf(-tau)) - 1e-4f;
   if (certified) return;
-  uint32_t slot = 0;
   if (lane == 0) {
-    slot = atomicAdd(w.ctrl, 1u);
+    const uint32_t slot = atomicAdd(w.ctrl, 1u);
     w.list[slot] = (int32_t)r;
     w.best[slot] = 0ull;
   }
-  slot = __shfl_sync(0xffffffffu, slot, 0);
-  float* dst = w.qc + (size_t)slot * a.h;
-  for (int i = lane; i < a.h; i += 32) dst[i] = query_elem(a, src, i, ln, mean, rstd);
 }
 
 // (flagged-row tile) x (pattern chunk) work items, 16*RM rows per tile, fp32 FFMA scores, running (max, index)
 template <int RM>
-__device__ __forceinline__ void repair_items(const RepairArgs& a, const RepairWs& w, int count, float* Qs, float* Ks) {
+__device__ __forceinline__ void repair_items(const RepairArgs& a, const RepairWs& w, int count, float* Qs, float* Ks,
+                                             float* s_mean, float* s_rstd, int* s_row) {
   constexpr int BM = 16 * RM;
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int warp = tid >> 5;
+  const float* qsrc = a.x_raw ? a.x_raw : a.qs;
+  const bool ln = a.x_raw && a.has_ln;
   const int chunk_tiles = 4;                                   // 256 patterns per item
   const int n_tiles = (a.p + BP - 1) / BP;
   const int n_pc = (n_tiles + chunk_tiles - 1) / chunk_tiles;
@@ -115,6 +117,16 @@ __device__ __forceinline__ void repair_items(const RepairArgs& a, const RepairWs
   for (long long item = blockIdx.x; item < items; item += gridDim.x) {
     const int rt = (int)(item / n_pc), pc = (int)(item - (long long)rt * n_pc);
     const int slot0 = rt * BM;
+    // the flagged rows of this tile and their LayerNorm statistics (the query rows are rebuilt from the raw input in
+    // the forward's arithmetic: nothing but the row list travels between the kernels)
+    __syncthreads();
+    for (int r = warp; r < BM; r += NT / 32) {
+      const int row = slot0 + r < count ? w.list[slot0 + r] : -1;
+      float mean = 0.f, rstd = 1.f;
+      if (row >= 0 && ln) warp_row_stats(qsrc + (size_t)row * a.h, a.h, a.ln_eps, mean, rstd);
+      if ((tid & 31) == 0) { s_row[r] = row; s_mean[r] = mean; s_rstd[r] = rstd; }
+    }
+    __syncthreads();
     float best[RM];
     int barg[RM];
 #pragma unroll
@@ -132,7 +144,14 @@ __device__ __forceinline__ void repair_items(const RepairArgs& a, const RepairWs
         for (int idx = tid; idx < BM * (KC / 4); idx += NT) {
           const int r = idx / (KC / 4), c = (idx - r * (KC / 4)) * 4;
           float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (slot0 + r < count && k0 + c < a.h) v = *reinterpret_cast<const float4*>(w.qc + (size_t)(slot0 + r) * a.h + k0 + c);
+          const int row = s_row[r];
+          if (row >= 0 && k0 + c < a.h) {
+            const float* src = qsrc + (size_t)row * a.h;
+            v.x = query_elem(a, src, k0 + c, ln, s_mean[r], s_rstd[r]);
+            v.y = query_elem(a, src, k0 + c + 1, ln, s_mean[r], s_rstd[r]);
+            v.z = query_elem(a, src, k0 + c + 2, ln, s_mean[r], s_rstd[r]);
+            v.w = query_elem(a, src, k0 + c + 3, ln, s_mean[r], s_rstd[r]);
+          }
           *reinterpret_cast<float4*>(Qs + r * TS + c) = v;
         }
         for (int idx = tid; idx < BP * (KC / 4); idx += NT) {
@@ -189,11 +208,13 @@ __device__ __forceinline__ void repair_items(const RepairArgs& a, const RepairWs
 __global__ void __launch_bounds__(NT) argmax_repair_kernel(RepairArgs a, RepairWs w) {
   __shared__ __align__(16) float Qs[64 * TS];
   __shared__ __align__(16) float Ks[BP * TS];
+  __shared__ float s_mean[64], s_rstd[64];
+  __shared__ int s_row[64];
   __shared__ int s_last;
   const int count = (int)*reinterpret_cast<volatile uint32_t*>(w.ctrl);
   if (count == 0) return;
-  if (count <= 16) repair_items<1>(a, w, count, Qs, Ks);
-  else repair_items<4>(a, w, count, Qs, Ks);
+  if (count <= 16) repair_items<1>(a, w, count, Qs, Ks, s_mean, s_rstd, s_row);
+  else repair_items<4>(a, w, count, Qs, Ks, s_mean, s_rstd, s_row);
   // the last CTA to finish writes the corrected (index, row maximum) of every flagged row
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -289,6 +310,11 @@ __global__ void __launch_bounds__(NT) delta_decide_kernel(const float* __restric
 
 size_t repair_workspace_bytes(int n, int h) { return carve_repair(nullptr, n, h).total; }
 
+CertArgs repair_cert_args(void* ws, int n, int h, const float* kstats, float* qn) {
+  const RepairWs w = carve_repair(ws, n, h);
+  return CertArgs{w.ctrl, w.list, w.best, kstats, qn};
+}
+
 int launch_argmax_repair(const RepairArgs& a, cudaStream_t st) {
   if (!a.argmax || !a.lse || !a.rowmax || !a.khat || !a.kstats)
     HOP_FAIL(HOP_ERR_BAD_ARG, "exact argmax needs argmax / lse / rowmax outputs, the fp32 K^ and kstats");
@@ -297,8 +323,10 @@ int launch_argmax_repair(const RepairArgs& a, cudaStream_t st) {
   if ((a.h & 3) != 0) HOP_FAIL(HOP_ERR_BAD_SHAPE, "argmax repair needs H %% 4 == 0");
   const RepairWs w = carve_repair(a.ws, a.n, a.h);
   const int rows_per_block = NT / 32;
-  certify_rows_kernel<<<(a.n + rows_per_block - 1) / rows_per_block, NT, 0, st>>>(a, w);
-  HOP_LAUNCH_CHECK("certify_rows_kernel");
+  if (!a.precertified) {
+    certify_rows_kernel<<<(a.n + rows_per_block - 1) / rows_per_block, NT, 0, st>>>(a, w);
+    HOP_LAUNCH_CHECK("certify_rows_kernel");
+  }
   argmax_repair_kernel<<<2 * num_sms(), NT, 0, st>>>(a, w);
   HOP_LAUNCH_CHECK("argmax_repair_kernel");
   return HOP_OK;
