@@ -522,7 +522,10 @@ def gpu_run(args):
         del raw
         layer.invalidate()
         torch.cuda.empty_cache()
-        shard_rec = sharded_record(impl, hflayers, dev, rank, world, n, max(3, args.steps // 2), torch, dist)
+        try:
+            shard_rec = sharded_record(impl, hflayers, dev, rank, world, n, max(3, args.steps // 2), torch, dist)
+        except Exception as e:  # noqa: BLE001  (the headline line must survive a failure of the side record)
+            shard_rec = [{"error": f"{type(e).__name__}: {e}"[:500]}]
 
     if rank == 0:
         pk = peaks()
