@@ -313,6 +313,38 @@ def sustained_kernel(raw, flush, fl, min_seconds, torch):
     return {"seconds": total * 1e-3, "launches": reps, "kernel_ms": k_ms, "achieved": fl / (k_ms * 1e-3) / 1e12}
 
 
+def backward_record(layer_cls, impl, dev, n, p, d, w, wv, wo, pk, torch, steps=5):
+    """Training step of the same layer (forward + `backward()`, main.py:35) on this GPU: device ms of the backward and
+    its algorithmic rate F_bwd = 2 N P (3 D + 2 Dv) against the measured peak.  Everything the backward
+    enqueues is inside: stats / operand packs, the three tcgen05 core launches, the fp32 LayerNorm / projection /
+    weight-gradient kernels.  Gradient parity of this path: tests/test_backward_tc_gpu.py."""
+    layer = build_layer(layer_cls, p, d, 0, w, wv, wo).to(dev).train()
+    layer.kernel_path = "f16"
+    xh, _ = make_queries(w, n)
+    x = xh.to(dev).requires_grad_(True)
+    gout = torch.randn(n, d, device=dev)
+    path = impl.ops.resolve_train_path(layer.spec(), n, p)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    t_f, t_b = [], []
+    for it in range(steps + 2):
+        layer.zero_grad(set_to_none=True)
+        x.grad = None
+        flush.zero_()
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        e[0].record(); y = layer(x); e[1].record(); y.backward(gout); e[2].record()
+        torch.cuda.synchronize()
+        if it >= 2:
+            t_f.append(e[0].elapsed_time(e[1])); t_b.append(e[1].elapsed_time(e[2]))
+    ms_f, ms_b = sorted(t_f)[len(t_f) // 2], sorted(t_b)[len(t_b) // 2]
+    f_bwd = 2.0 * n * p * 5 * d
+    ach = f_bwd / (ms_b * 1e-3) / 1e12
+    return {"train_path": {1: "fp32_simt", 2: "tc_f16", 3: "tc_bf16"}[path], "ms_backward": ms_b,
+            "ms_forward_incl_prep": ms_f, "algorithmic_flops": f_bwd, "achieved": ach, "unit": "TFLOP/s",
+            "peak": pk["bf16_tflops"], "frac": ach / pk["bf16_tflops"],
+            "executed_over_algorithmic": 8.0 / 5.0 if path != 1 else 7.0 / 5.0,
+            "note": "whole backward of the layer (core + fp32 tails), median of %d steps, L2 flushed" % steps}
+
+
 SHARDED_POINTS = [(262144, 256), (1048576, 256), (1048576, 512)]      # (P, D) of BASELINE config 5, T = 0
 
 
@@ -517,6 +549,13 @@ def gpu_run(args):
         arg = runner.last_argmax
         parity = parity_block(y.reshape(n, -1), arg, x_host, w, wv, wo, t, d, 64 if p * d <= (1 << 26) else 32)
 
+    bwd_rec = None
+    if rank == 0 and world == 1 and not sharded and t == 0 and not args.no_backward:
+        try:
+            bwd_rec = backward_record(hflayers.HopfieldLayer, impl, dev, n, p, d, w, wv, wo, peaks(), torch)
+        except Exception as e:  # noqa: BLE001
+            bwd_rec = {"error": f"{type(e).__name__}: {e}"[:400]}
+
     shard_rec = None
     if world > 1 and not sharded and not args.no_sharded_record:
         del raw
@@ -583,6 +622,8 @@ def gpu_run(args):
                             "hbm_peak_gbs": pk["hbm_gbs"]}
         if parity is not None:
             line["parity"] = parity
+        if bwd_rec is not None:
+            line["backward"] = bwd_rec
         if shard_rec is not None:
             line["sharded"] = {"mode": f"pattern-sharded over {world} GPUs (BASELINE config 5), T = 0, "
                                        "f16 operands; times = median of max-over-ranks device times, L2 flushed",
@@ -633,6 +674,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--no-sustained", action="store_true")
+    ap.add_argument("--no-backward", action="store_true")
     ap.add_argument("--sustained-seconds", type=float, default=2.0)
     ap.add_argument("--no-sharded-record", action="store_true",
                     help="multi-GPU batch-parallel runs: skip the pattern-sharded sub-record (config 5 points)")

@@ -10,7 +10,7 @@ tail -5 gpurun_out/r02_bwd_tc.txt
 timeout 300 python __graft_entry__.py smoke > gpurun_out/r02_smoke.txt 2>&1; echo "smoke rc=$?"
 timeout 600 python bench.py --steps 20 --warmup 5 > gpurun_out/r02_bench.json 2> gpurun_out/r02_bench.err; echo "bench rc=$?"
 timeout 600 python scripts/bench_backward.py > gpurun_out/r02_backward.jsonl 2> gpurun_out/r02_backward.err; echo "bwd bench rc=$?"
-BENCH="python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-sustained --no-parity"
+BENCH="python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-sustained --no-parity --no-backward"
 $BENCH > gpurun_out/r02_launches_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/r02_bench_launches.csv $BENCH > gpurun_out/r02_launches_ncu.log 2>&1
 echo "ncu launches rc=$?"
