@@ -73,6 +73,7 @@ struct BwdCfg {
 
 struct BwdKernelArgs {
   int n_stat, n_stream;          // valid stationary / streamed rows (outputs beyond n_stat are not written)
+  int n_stream_valid;            // MODE_DQ: streamed rows (patterns) >= this are padding and get zero weight
   int tiles_per_split;           // streamed tiles (of 128) per CTA pair
   int w;                         // output row pitch (= H)
   const float* row_lse2;         // MODE_DQ: per stationary row  lse * log2(e)   (padded rows: kPadLse)
@@ -311,6 +312,9 @@ hop_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
       ptx::tmem_wait_ld();
       const int slot = j & 1;
       if constexpr (Cfg::kColStats) ptx::mbar_wait(st_full(slot), (j >> 1) & 1);
+      // MODE_DQ: padded patterns have zero K^ rows, i.e. score 0 and weight 2^-lse != 0: they must not enter the row sum
+      // that defines the consistent delta (padded QUERIES carry lse = 1e30 and vanish by themselves)
+      const int valid = MODE == MODE_DQ ? a.n_stream_valid - ((t0 + j) * kTP + cbase) : Cfg::kC;
       uint32_t pk[Cfg::kW];
 #pragma unroll
       for (int i4 = 0; i4 < Cfg::kC / 4; ++i4) {
@@ -328,6 +332,7 @@ hop_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
           const float p = ptx::ex2(__uint_as_float(v[4 * i4 + e]) - l4[e]);
           if constexpr (Cfg::kTwo) w4[e] = p * (__uint_as_float(u[4 * i4 + e]) - d4[e]);
           else w4[e] = p;
+          if (MODE == MODE_DQ && 4 * i4 + e >= valid) w4[e] = 0.f;
         }
         if constexpr (MODE == MODE_DQ) cacc += (w4[0] + w4[1]) + (w4[2] + w4[3]);
         pk[2 * i4] = pack_h2(w4[0], w4[1]);
@@ -596,7 +601,7 @@ int launch_core_tc(const TcBwdArgs& a, const TcBwdWs& w, cudaStream_t st) {
   BwdKernelArgs k{};
   k.w = H; k.gscale = w.gmax; k.out_scale = 1.f; k.use_g = 1;
   // dq: queries stationary, patterns streamed
-  k.n_stat = a.n; k.n_stream = ppad; k.row_lse2 = w.lse2; k.row_delta = w.deltag; k.out = a.dqs; k.csum = w.csum;
+  k.n_stat = a.n; k.n_stream = ppad; k.n_stream_valid = a.p; k.row_lse2 = w.lse2; k.row_delta = w.deltag; k.out = a.dqs; k.csum = w.csum;
   HOP_TRY((launch_mode<H, MODE_DQ>(mq, mdr, mk, mv, mkt, k, npad, st)));
   k.csum = nullptr;
   // consistent delta for the dK^ launch, common-mode correction of dq (pattern_offset-free indices of this call)

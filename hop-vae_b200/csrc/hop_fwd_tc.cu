@@ -1690,6 +1690,11 @@ bool tc_precise_updates(int d, int update_steps, const TcTune& t) {
 // the combine kernel, keep it at the operand-rounding level.
 constexpr int kMaxTilesOnChipUpdates = 512;
 constexpr int kMaxChainTilesUpdate = 256;    // pattern tiles one CTA accumulates when T > 0 (multi-launch form)
+constexpr int kMaxChainTilesPrecise = 32;    // ... in a hi + lo update pass: with the operand rounding gone, the truncation
+                                             // bias of the chain (~2^-25 per accumulate instruction, 16 per tile) is what the
+                                             // iteration amplifies -- measured at P = 256k, D = 256, T = 3: 1.27e-3 with
+                                             // 256-tile chains = 1.2e-4 per pass x (1 + 2.7 + 2.7^2)
+constexpr int kMaxSplitsPrecise = 64;        // (bounds the partial-result traffic: P = 1M keeps 128-tile chains)
 constexpr int kMaxChainTilesReadout = 512;   // ... when T = 0 (errors are not amplified)
 static inline bool tc_multi_launch(int p, int d, int update_steps, const TcTune& t) {
   if (update_steps <= 0) return false;
@@ -1721,7 +1726,11 @@ int tc_choose_splits(int n, int p, int d, int update_steps, const TcTune& t) {
   const int cl = tc_cluster(n, d, t);
   const int row_tiles = ((n + tc_rows(d, t) - 1) / tc_rows(d, t) + cl - 1) / cl * cl * tc_dv_chunks(d, t);
   const int nt_total = padded_patterns(p) / kTileP;
-  const int chain = update_steps > 0 ? kMaxChainTilesUpdate : kMaxChainTilesReadout;
+  int chain = update_steps > 0 ? kMaxChainTilesUpdate : kMaxChainTilesReadout;
+  if (tc_precise_updates(d, update_steps, t)) {
+    chain = kMaxChainTilesPrecise;
+    if ((nt_total + chain - 1) / chain > kMaxSplitsPrecise) chain = (nt_total + kMaxSplitsPrecise - 1) / kMaxSplitsPrecise;
+  }
   const int min_splits = (nt_total + chain - 1) / chain;            // accuracy: bound the accumulation chain
   int max_splits = nt_total < 32 ? nt_total : 32;
   if (max_splits < min_splits + 8) max_splits = min_splits + 8 < nt_total ? min_splits + 8 : nt_total;
