@@ -1,28 +1,23 @@
-"""ncu raw-page CSV (ncu -i X.ncu-rep --page raw --csv) -> the handful of numbers the roofline uses."""
+"""Key metrics per launch of an ncu --set full report:  python scripts/summarize_ncu.py gpurun_out/x.ncu-rep > profiles/x_summary.md"""
 import csv
+import subprocess
 import sys
 
-KEYS = ["gpu__time_duration.sum", "sm__cycles_elapsed.avg.per_second", "launch__registers_per_thread",
-        "launch__grid_size", "launch__block_size", "launch__shared_mem_per_block_dynamic",
-        "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed",
-        "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_elapsed",
-        "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_elapsed",
-        "sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_elapsed",
-        "smsp__issue_active.avg.per_cycle_active", "dram__bytes_read.sum", "dram__bytes_write.sum",
-        "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "lts__t_bytes.sum",
-        "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "sm__warps_active.avg.pct_of_peak_sustained_active"]
-
-
-def main(path):
-    rows = list(csv.reader(open(path)))
-    hdr, units = rows[0], rows[1]
-    for vals in rows[2:]:
-        d = dict(zip(hdr, zip(units, vals)))
-        print("kernel:", d.get("Kernel Name", ("", "?"))[1][:110])
-        for k in KEYS:
-            if k in d:
-                print(f"  {k:75s} {d[k][1]:>14s} {d[k][0]}")
-
-
-if __name__ == "__main__":
-    main(sys.argv[1])
+WANT = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "dram__throughput.avg.pct_of_peak_sustained_elapsed",
+        "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active",
+        "smsp__issue_active.avg.pct_of_peak_sustained_active", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+        "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum", "lts__t_bytes.sum", "lts__t_sector_hit_rate.pct",
+        "launch__registers_per_thread", "launch__grid_size", "launch__cluster_size", "launch__shared_mem_per_block_dynamic",
+        "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__cycles_active.avg", "sm__cycles_elapsed.max"]
+rep = sys.argv[1]
+out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+rows = list(csv.reader(out.splitlines()))
+hdr, units = rows[0], rows[1]
+print(f"# {rep}: `ncu --set full --clock-control none`, one column per captured launch\n")
+names = [r[hdr.index("Kernel Name")].split("(")[0].replace("void ", "").replace("unnamed>::", "") for r in rows[2:]]
+print("| metric | unit | " + " | ".join(names) + " |")
+print("|---|---|" + "---|" * len(names))
+for w in WANT:
+    if w in hdr:
+        i = hdr.index(w)
+        print(f"| `{w}` | {units[i]} | " + " | ".join(r[i] for r in rows[2:]) + " |")
