@@ -43,7 +43,7 @@ class HopDesc(C.Structure):
 
 _PARAM_FIELDS = ["lookup", "lookup_targets", "ln_state_w", "ln_state_b", "ln_stored_w", "ln_stored_b",
                  "ln_proj_w", "ln_proj_b", "wq", "bq", "wk", "bk", "wv", "bv", "wo", "bo"]
-_PATTERN_FIELDS = ["khat", "vhat", "k16", "kt16", "vt16", "vot16", "k16lo", "kt16lo", "v16", "kstats"]
+_PATTERN_FIELDS = ["khat", "vhat", "k16", "kt16", "vt16", "vot16", "k16lo", "kt16lo", "v16", "kstats", "scratch"]
 _GRAD_FIELDS = ["d_x", "d_lookup", "d_lookup_targets", "d_ln_state_w", "d_ln_state_b", "d_ln_stored_w",
                 "d_ln_stored_b", "d_ln_proj_w", "d_ln_proj_b", "d_wq", "d_bq", "d_wk", "d_bk", "d_wv", "d_bv",
                 "d_wo", "d_bo"]

@@ -173,6 +173,7 @@ int hop_sm100_pattern_bytes(const hop_desc* desc, hop_pattern_sizes* sz) {
   sz->kt16lo = precise ? Pp * desc->d_assoc * 2 : 0;
   sz->v16 = train ? Pp * desc->d_v * 2 : 0;
   sz->kstats = tc ? 4 * sizeof(float) : 0;
+  sz->scratch = tc ? prepare_scratch_bytes(*desc) : 0;
   return HOP_OK;
 }
 
@@ -237,7 +238,7 @@ int hop_sm100_prepare_patterns(const hop_desc* desc, const hop_params* params, c
       HOP_FAIL(HOP_ERR_BAD_ARG, "HOP_F_TRAIN: the tensor-core backward needs the kt16 / v16 buffers");
     if (!aligned16(patterns->k16) || !aligned16(patterns->vt16) || !aligned16(patterns->kt16) ||
         !aligned16(patterns->k16lo) || !aligned16(patterns->kt16lo) || !aligned16(patterns->v16) ||
-        !aligned16(patterns->kstats))
+        !aligned16(patterns->kstats) || !aligned16(patterns->scratch))
       HOP_FAIL(HOP_ERR_BAD_ALIGN, "16-bit pattern packs must be 16-byte aligned");
     if (patterns->vot16 && (!out_proj_foldable(*desc) || !params->wo || !aligned16(patterns->vot16)))
       HOP_FAIL(HOP_ERR_BAD_ARG, "vot16 given but out_proj cannot be folded (needs HOP_F_OUT_PROJ, Dout == H == Dv, wo, alignment)");

@@ -144,6 +144,18 @@ bool tc_precise_updates(int d, int update_steps, const TcTune& tune);
 size_t tc_forward_workspace(int n, int p, int d, int update_steps, const TcTune& tune);
 int launch_tc_forward(const TcPassArgs& a, cudaStream_t st);
 bool tc_supported(int h, int dv);
+// hop_gemm_tc.cu -- C[M x N] = A[M x K] . B[N x K]^T (+ bias) on tcgen05, fp16 K-major operand packs, optional hi + lo pairs
+struct TcGemmArgs {
+  const void* a16; const void* a16lo;   // (m_pad, k) fp16, rows >= m zero
+  const void* b16; const void* b16lo;   // (n, k) fp16
+  int m, m_pad, n, k, ldc;
+  const float* bias;                    // (n) or nullptr
+  float* c;                             // (m, ldc) fp32
+  int split;                            // operands are hi + lo pairs: three MMAs per product, ~2^-21 relative
+};
+bool tc_gemm_supported(int n, int k);
+int launch_tc_gemm(const TcGemmArgs& a, cudaStream_t st);
+size_t prepare_scratch_bytes(const hop_desc& d);   // hop_prep.cu: scratch of the tensor-core pattern preparation (0: FFMA form)
 // hop_bwd_tc.cu -- association core of the backward on the tensor pipe (dq, dK^, dV^)
 struct TcBwdArgs {
   const float* qs; const float* lse; const float* dr; const float* r;       // (N,H), (N), dR (N,Dv), R = A V^ (N,Dv)

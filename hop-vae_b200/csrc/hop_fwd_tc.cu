@@ -82,7 +82,11 @@ __device__ long long g_trace[kTraceRoles * kTraceTiles * kTraceEvents];
 // iteration amplifies operand rounding; the Q tile holds both halves, so the ring is shorter.
 template <int H, int DV, bool kPrecise = false>
 struct TcCfg {
-  static constexpr int kPolyPeriod = H >= 256 ? HOP_POLY_D256 : (H >= 128 ? HOP_POLY_D128 : HOP_POLY_D64);
+  // A hi + lo pass computes every exponential on the MUFU: the degree-3 polynomial's 7.5e-5 relative error is systematic,
+  // and the retrieve iteration amplifies it like any other rounding (CPU emulation of the kernel's arithmetic at the
+  // bifurcation point P = 256k, D = 256, T = 3: 2.2e-4 without, 1.1e-3 with the polynomial in the update passes; measured
+  // with it: 0.97e-3).  These passes issue 2.5x the MMA work per exponential, so the MUFU is not their limit.
+  static constexpr int kPolyPeriod = kPrecise ? 0 : (H >= 256 ? HOP_POLY_D256 : (H >= 128 ? HOP_POLY_D128 : HOP_POLY_D64));
   static constexpr int kKChunks = H / 64;                 // 64-wide K chunks of the Q / K^ tiles
   static constexpr int kBStages = DV > 128 ? DV / 128 : 1;  // ring stages of one read-out chunk (DV rows x 64 patterns)
   static constexpr int kBRows = DV / kBStages;            // rows per TMA box of the read-out operand

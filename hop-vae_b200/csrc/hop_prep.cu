@@ -197,7 +197,7 @@ int launch_ln_linear_pair(const LnLinearArgs& a0, const LnLinearArgs& a1, cudaSt
 }
 
 int launch_ln_linear(const LnLinearArgs& a, cudaStream_t st) {
-  const int total_rows = (a.y16 || a.yt16) ? a.rows_pad : a.rows;
+  const int total_rows = (a.y16 || a.yt16 || a.y16lo) ? a.rows_pad : a.rows;
   if (total_rows <= 0) return HOP_OK;
   const int sms = num_sms();
   if (total_rows >= 64 * sms) {
@@ -212,6 +212,38 @@ int launch_ln_linear(const LnLinearArgs& a, cudaStream_t st) {
 }
 
 }  // namespace
+
+// ---- tensor-core form of the V path (V-projection and out_proj fold as tcgen05 GEMMs, hop_gemm_tc.cu) -------------
+// scratch: [A hi | A lo] (Ppad x max(Din, Dv) fp16 each: LN_v(W), later V^), [B hi | B lo] (max(Dv x Din, Dout x Dv)),
+//          V^ Wo^T fp32 (P x Dout)
+namespace {
+struct PrepScratch { char *a_hi, *a_lo, *b_hi, *b_lo; float* vo; size_t total; };
+PrepScratch carve_prep(void* base, const hop_desc& d) {
+  PrepScratch s{};
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    char* p = base ? static_cast<char*>(base) + off : nullptr;
+    off += round_up_sz(bytes, 1024);
+    return p;
+  };
+  const size_t ppad = (size_t)padded_patterns(d.n_patterns);
+  const size_t wa = (size_t)(d.d_in > d.d_v ? d.d_in : d.d_v);
+  size_t wb = (size_t)d.d_v * d.d_in;
+  const bool fold = out_proj_foldable(d);
+  if (fold && (size_t)d.d_out * d.d_v > wb) wb = (size_t)d.d_out * d.d_v;
+  s.a_hi = take(ppad * wa * 2); s.a_lo = take(ppad * wa * 2);
+  s.b_hi = take(wb * 2); s.b_lo = take(wb * 2);
+  s.vo = reinterpret_cast<float*>(take(fold ? (size_t)d.n_patterns * d.d_out * sizeof(float) : 0));
+  s.total = off;
+  return s;
+}
+bool prep_uses_gemm(const hop_desc& d) {
+  return (d.flags & HOP_F_PROJ_PATTERN) && tc_gemm_supported(d.d_v, d.d_in) && d.n_patterns >= 1024 &&
+         (!out_proj_foldable(d) || tc_gemm_supported(d.d_out, d.d_v));
+}
+}  // namespace
+
+size_t prepare_scratch_bytes(const hop_desc& d) { return prep_uses_gemm(d) ? carve_prep(nullptr, d).total : 0; }
 
 int launch_prepare_patterns(const hop_desc& d, const hop_params& p, const hop_patterns& pt, int path,
                             cudaStream_t st) {
@@ -230,15 +262,51 @@ int launch_prepare_patterns(const hop_desc& d, const hop_params& p, const hop_pa
     k.norm_max = pt.kstats;
   }
   if ((d.flags & HOP_F_PROJ_STORED) && !p.wk) HOP_FAIL(HOP_ERR_BAD_ARG, "HOP_F_PROJ_STORED set but params.wk is NULL");
+  if ((d.flags & HOP_F_PROJ_PATTERN) && !p.wv) HOP_FAIL(HOP_ERR_BAD_ARG, "HOP_F_PROJ_PATTERN set but params.wv is NULL");
+  const float* Wt = p.lookup_targets ? p.lookup_targets : p.lookup;
+  const int bf16 = (path == HOP_PATH_TC_BF16);
+
+  if (tc && !bf16 && pt.scratch && prep_uses_gemm(d)) {
+    // V^ = LN_v(Wt) Wv^T + bv and (V^ Wo^T) on the tensor pipe; every pack kernel around them is a pass over HBM
+    const PrepScratch s = carve_prep(pt.scratch, d);
+    HOP_TRY(launch_ln_linear(k, st));                                   // K^ path (no contraction when K is static)
+    auto pack = [&](const float* x, int rows, int rows_pad, int w, int has_ln, const float* lw, const float* lb,
+                    float* y, void* y16, void* y16lo, void* yt16) {
+      LnLinearArgs a{};
+      a.x = x; a.rows = rows; a.rows_pad = rows_pad; a.din = w; a.has_ln = has_ln; a.ln_w = lw; a.ln_b = lb;
+      a.ln_eps = d.ln_eps; a.w = nullptr; a.b = nullptr; a.dout = w; a.scale = 1.f; a.y = y; a.y16 = y16;
+      a.y16lo = y16lo; a.yt16 = yt16; a.bf16 = 0;
+      return launch_ln_linear(a, st);
+    };
+    HOP_TRY(pack(Wt, d.n_patterns, ppad, d.d_in, (d.flags & HOP_F_NORM_PROJ) ? 1 : 0, p.ln_proj_w, p.ln_proj_b, nullptr,
+                 s.a_hi, s.a_lo, nullptr));                             // LN_v(Wt) as a hi + lo pair
+    HOP_TRY(pack(p.wv, d.d_v, d.d_v, d.d_in, 0, nullptr, nullptr, nullptr, s.b_hi, s.b_lo, nullptr));
+    TcGemmArgs g{};
+    g.a16 = s.a_hi; g.a16lo = s.a_lo; g.b16 = s.b_hi; g.b16lo = s.b_lo;
+    g.m = d.n_patterns; g.m_pad = ppad; g.n = d.d_v; g.k = d.d_in; g.ldc = d.d_v; g.bias = p.bv; g.c = pt.vhat; g.split = 1;
+    HOP_TRY(launch_tc_gemm(g, st));
+    const bool fold = pt.vot16 != nullptr;
+    // V^ -> vt16 [, v16]; for the fold also the hi + lo pair of V^ (the A operand of the second product)
+    void* vhi = pt.v16 ? pt.v16 : (fold ? (void*)s.a_hi : nullptr);
+    HOP_TRY(pack(pt.vhat, d.n_patterns, ppad, d.d_v, 0, nullptr, nullptr, nullptr, vhi, fold ? (void*)s.a_lo : nullptr, pt.vt16));
+    if (fold) {
+      HOP_TRY(pack(p.wo, d.d_out, d.d_out, d.d_v, 0, nullptr, nullptr, nullptr, s.b_hi, s.b_lo, nullptr));
+      TcGemmArgs f{};
+      f.a16 = vhi; f.a16lo = s.a_lo; f.b16 = s.b_hi; f.b16lo = s.b_lo;
+      f.m = d.n_patterns; f.m_pad = ppad; f.n = d.d_out; f.k = d.d_v; f.ldc = d.d_out; f.bias = nullptr; f.c = s.vo; f.split = 1;
+      HOP_TRY(launch_tc_gemm(f, st));
+      HOP_TRY(pack(s.vo, d.n_patterns, ppad, d.d_out, 0, nullptr, nullptr, nullptr, nullptr, nullptr, pt.vot16));
+    }
+    return HOP_OK;
+  }
 
   LnLinearArgs v{};
-  v.x = p.lookup_targets ? p.lookup_targets : p.lookup; v.rows = d.n_patterns; v.rows_pad = ppad; v.din = d.d_in;
+  v.x = Wt; v.rows = d.n_patterns; v.rows_pad = ppad; v.din = d.d_in;
   v.has_ln = (d.flags & HOP_F_NORM_PROJ) ? 1 : 0; v.ln_w = p.ln_proj_w; v.ln_b = p.ln_proj_b; v.ln_eps = d.ln_eps;
   v.w = (d.flags & HOP_F_PROJ_PATTERN) ? p.wv : nullptr; v.b = (d.flags & HOP_F_PROJ_PATTERN) ? p.bv : nullptr;
   v.dout = d.d_v; v.scale = 1.f; v.y = pt.vhat;
   v.y16 = tc ? pt.v16 : nullptr; v.yt16 = tc ? pt.vt16 : nullptr;
-  v.bf16 = (path == HOP_PATH_TC_BF16);
-  if ((d.flags & HOP_F_PROJ_PATTERN) && !p.wv) HOP_FAIL(HOP_ERR_BAD_ARG, "HOP_F_PROJ_PATTERN set but params.wv is NULL");
+  v.bf16 = bf16;
   HOP_TRY(launch_ln_linear_pair(k, v, st));     // K^ and V^ packs: same rows, one launch
 
   if (tc && pt.vot16) {
@@ -246,7 +314,7 @@ int launch_prepare_patterns(const hop_desc& d, const hop_params& p, const hop_pa
     LnLinearArgs o{};
     o.x = pt.vhat; o.rows = d.n_patterns; o.rows_pad = ppad; o.din = d.d_v; o.has_ln = 0; o.ln_eps = 0.f;
     o.w = p.wo; o.b = nullptr; o.dout = d.d_out; o.scale = 1.f; o.y = nullptr; o.y16 = nullptr; o.yt16 = pt.vot16;
-    o.bf16 = (path == HOP_PATH_TC_BF16);
+    o.bf16 = bf16;
     HOP_TRY(launch_ln_linear(o, st));
   }
   return HOP_OK;

@@ -124,7 +124,7 @@ def resolve_path(spec: LayerSpec, n_rows: int, n_patterns: int) -> int:
 
 
 # --------------------------------------------------------------------------- prepare_patterns
-N_PACKS = len(cabi._PATTERN_FIELDS)     # khat, vhat, k16, kt16, vt16, vot16, k16lo, kt16lo, v16, kstats
+N_PACKS = len(cabi._PATTERN_FIELDS)     # khat, vhat, k16, kt16, vt16, vot16, k16lo, kt16lo, v16, kstats, scratch
 
 
 def prepare_patterns(lookup: Tensor, lookup_targets: Optional[Tensor], ln_stored_w: Optional[Tensor],
@@ -169,6 +169,7 @@ def prepare_patterns(lookup: Tensor, lookup_targets: Optional[Tensor], ln_stored
     with _on_device(dev):
         cabi.check(lib.hop_sm100_prepare_patterns(C.byref(d), C.byref(params), C.byref(ps), _stream(dev)),
                    "hop_sm100_prepare_patterns")
+    pats[-1] = pats[-1].new_empty((0,))     # the scratch of the preparation is not kept (stream-ordered free)
     return pats
 
 
@@ -199,7 +200,7 @@ def _(lookup, lookup_targets, ln_stored_w, ln_stored_b, ln_proj_w, ln_proj_b, wk
             mk(ppad * d_assoc if tc and (update_steps > 0 or train) else 0), mk(ppad * d_v if tc else 0),
             mk(ppad * d_assoc if fold else 0), mk(ppad * d_assoc if precise else 0),
             mk(ppad * d_assoc if precise else 0), mk(ppad * d_v if train else 0),
-            lookup.new_empty((4 if tc else 0,))]
+            lookup.new_empty((4 if tc else 0,)), mk(0)]
 
 
 # --------------------------------------------------------------------------- retrieve (forward)

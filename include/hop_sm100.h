@@ -153,11 +153,14 @@ typedef struct hop_patterns {
   void*  v16;    /* V^ 16-bit, row-major (Ppad, Dv): tensor-core backward (HOP_F_TRAIN)      */
   float* kstats; /* 4 floats: [0] = max_j ||K^_j||_2 (bounds the 16-bit score noise for the
                     HOP_F_EXACT_ARGMAX certificate); tensor-core paths                       */
+  void*  scratch;/* temporary of hop_sm100_prepare_patterns on the tensor-core paths (operand packs of the
+                    V-projection / out_proj fold, which then run on tcgen05); only that call touches it --
+                    free it afterwards.  NULL: the projection runs on the fp32 CUDA-core kernel instead */
 } hop_patterns;
 
 /* Byte sizes of the hop_patterns buffers (0 where a buffer is not needed).   */
 typedef struct hop_pattern_sizes {
-  size_t khat, vhat, k16, kt16, vt16, vot16, k16lo, kt16lo, v16, kstats;
+  size_t khat, vhat, k16, kt16, vt16, vot16, k16lo, kt16lo, v16, kstats, scratch;
 } hop_pattern_sizes;
 
 /* Gradients written (overwritten, not accumulated) by hop_sm100_backward.
