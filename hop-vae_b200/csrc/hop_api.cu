@@ -198,7 +198,7 @@ FwdWs fwd_ws(const hop_desc& d, int path, bool exact) {
   } else if (simt_stop_rule(d)) {
     w.stat = round_up_sz(N * sizeof(float), 256);
   }
-  w.total = 2 * w.q + w.r + w.tc + w.repair + w.qfinal + 3 * w.stat + (w.stat ? 256 : 0);   // stat: lse, rowmax, ||q||
+  w.total = 2 * w.q + w.r + w.tc + w.repair + w.qfinal + 4 * w.stat + (w.stat ? 256 : 0);   // stat: lse, rowmax, ||q||, runner-up
   return w;
 }
 }  // namespace
@@ -360,7 +360,8 @@ int hop_sm100_forward(const hop_desc* desc, const hop_params* params, const hop_
   bool cert_done = false;
   if (exact) {
     a.cert = repair_cert_args(region(off_repair), d.n_rows, d.d_assoc, patterns->kstats,
-                              reinterpret_cast<float*>(region(off_stat + 2 * W.stat)));
+                              reinterpret_cast<float*>(region(off_stat + 2 * W.stat)),
+                              reinterpret_cast<float*>(region(off_stat + 3 * W.stat)));
     a.cert_done = &cert_done;
   }
   HOP_TRY(launch_tc_forward(a, st));
@@ -372,7 +373,7 @@ int hop_sm100_forward(const hop_desc* desc, const hop_params* params, const hop_
     r.beta = d.beta;
     r.khat = patterns->khat; r.kstats = patterns->kstats;
     r.n = d.n_rows; r.p = d.n_patterns; r.h = d.d_assoc; r.pattern_offset = d.pattern_offset;
-    r.lse = lse_w; r.rowmax = rowmax_w; r.argmax = argmax;
+    r.lse = lse_w; r.rowmax = rowmax_w; r.argmax = argmax; r.rowsec = a.cert.sec;
     r.ws = region(off_repair); r.ws_bytes = W.repair;
     r.precertified = cert_done ? 1 : 0;
     HOP_TRY(launch_argmax_repair(r, st));
@@ -381,6 +382,23 @@ int hop_sm100_forward(const hop_desc* desc, const hop_params* params, const hop_
   if (out_proj) HOP_TRY(launch_linear(d.n_rows, d.d_v, d.d_out, a.retrieved, p.wo, p.bo, out, st));
   else if (retrieved && retrieved != out)
     HOP_CUDA(cudaMemcpyAsync(retrieved, out, (size_t)d.n_rows * d.d_v * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  return HOP_OK;
+}
+
+int hop_sm100_repair_rows(const hop_desc* desc, const void* workspace, void* stream, int32_t* rows_out) {
+  HOP_TRY(validate_desc(desc));
+  if (!rows_out) HOP_FAIL(HOP_ERR_BAD_ARG, "rows_out is NULL");
+  *rows_out = 0;
+  const int path = resolve_path(desc);
+  if (path < 0) return -path;
+  if (path == HOP_PATH_FP32_SIMT || !(desc->flags & HOP_F_EXACT_ARGMAX)) return HOP_OK;
+  if (!workspace) HOP_FAIL(HOP_ERR_BAD_ARG, "workspace is NULL");
+  const FwdWs W = fwd_ws(*desc, path, true);
+  uint32_t flagged = 0;     // first control word of the repair region (hop_repair.cu)
+  HOP_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  HOP_CUDA(cudaMemcpy(&flagged, static_cast<const char*>(workspace) + 2 * W.q + W.r + W.tc, sizeof(flagged),
+                      cudaMemcpyDeviceToHost));
+  *rows_out = (int32_t)flagged;
   return HOP_OK;
 }
 

@@ -102,17 +102,20 @@ struct RepairArgs {
   const float* kstats;        // [0] = max_j ||K^_j||
   int n, p, h, pattern_offset;
   const float* lse; float* rowmax; int32_t* argmax;   // results of the 16-bit pass; argmax / rowmax are corrected in place
+  const float* rowsec;        // the forward's bound on each row's runner-up score (CertArgs::sec); read when !precertified
   void* ws; size_t ws_bytes;  // repair_workspace_bytes(n, h); its first 16 bytes are the control words, which the
                               // forward kernel of the same call clears (TcPassArgs::zero_words)
   int precertified;           // the forward's merge kernel already evaluated the certificate and built the list
 };
-// Where the merge kernels of the tensor-core forward evaluate the certificate themselves (they hold lse and the row
-// maximum of every row in registers): the repair list of hop_repair.cu, the query norms the forward's prologue wrote.
+// Where the merge kernels of the tensor-core forward evaluate the certificate themselves (they hold the row maximum and
+// the runner-up bound of every row in registers): the repair list of hop_repair.cu, the query norms the forward's
+// prologue wrote, and -- for a forward that ends without a merge kernel -- where it leaves the runner-up bound.
 struct CertArgs {
   uint32_t* ctrl; int32_t* list; unsigned long long* best;   // repair list (ctrl == nullptr: no certificate)
   const float* kstats; float* qn;                             // max_j ||K^_j||, per-row ||q|| (N floats, written by the forward)
+  float* sec;                                                 // per-row runner-up bound (N floats, written by the forward)
 };
-CertArgs repair_cert_args(void* ws, int n, int h, const float* kstats, float* qn);
+CertArgs repair_cert_args(void* ws, int n, int h, const float* kstats, float* qn, float* sec);
 size_t repair_workspace_bytes(int n, int h);
 int launch_argmax_repair(const RepairArgs& a, cudaStream_t st);
 // ||A_t - A_(t-1)||_F per batch item, max over items, compared with eps: sets *stopped (device) to 1 when the

@@ -124,11 +124,35 @@ struct TcKernelArgs {
   // cluster; a cluster walks its share segment by segment (a segment = one row group, a contiguous tile range)
   int streamk, sk_base, sk_rem, sk_max_seg;
   float* retrieved; float* qsave; float* lse; int32_t* argmax; float* rowmax; int pattern_offset;
+  float* rowsec;                        // per-row bound on the runner-up score (exact-argmax certificate) or nullptr
   uint32_t* zero_words;                 // 4 control words of the argmax repair, cleared by CTA (0,0,0) (or nullptr)
   float* qn;                            // per-row ||q|| of the pass (exact-argmax certificate) or nullptr
   // partial outputs when splits > 1: (splits, N, D), (splits, N) x3
-  float* part_o; float* part_lse; float* part_max; int32_t* part_arg;
+  float* part_o; float* part_lse; float* part_max; int32_t* part_arg; float* part_sec;
 };
+
+// Runner-up bound of one softmax thread's tile, from what the softmax holds anyway.  The score columns of a thread sit on
+// four max chains `mx[u]` whose exponentials were summed into `ls[u]` (pair i of the packing loop belongs to chain i & 3).
+// The chains that do not hold the tile maximum `hmax` contribute their maxima exactly; in the one that does, the other
+// columns' exponentials add up to ls[u] - 2^(hmax - m_run), and no single one of them can exceed that sum.  The result
+// is >= the true second-largest score of the tile (a duplicate of hmax in the same chain makes the rest >= the top
+// term, i.e. the bound >= hmax): rows certified with it are safe, a loose bound only sends a row to the fp32 repair.
+// `kSecondSlack` covers the rounding of the sum and the 7.5e-5 of the polynomial exponential on the top term.
+constexpr float kSecondSlack = 4e-4f;
+__device__ __forceinline__ float second_bound(const float (&mx)[4], const float (&ls)[4], float hmax, float m_run) {
+  float oth = -INFINITY, lsh = 0.f;
+  bool found = false;
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    const bool hit = !found && mx[u] == hmax;
+    lsh = hit ? ls[u] : lsh;
+    oth = hit ? oth : fmaxf(oth, mx[u]);
+    found = found || hit;
+  }
+  const float pt = ptx::ex2(hmax - m_run);
+  const float rest = fmaxf(lsh - pt, 0.f) + kSecondSlack * pt;
+  return fmaxf(oth, m_run + ptx::lg2(rest));
+}
 
 template <bool kBf16>
 __device__ __forceinline__ uint32_t pack16(float a, float b) {
@@ -623,7 +647,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
       arrive_issuer(q_ready);
 
       // m_run is shared by the pair (identical in both threads of a row); l, tmax, targ are per half
-      float m_run = -INFINITY, l = 0.f, tmax = -INFINITY;
+      float m_run = -INFINITY, l = 0.f, tmax = -INFINITY, tsec = -INFINITY;
       int targ = 0;
       for (int j = 0; j < nt; ++j) {
         const uint32_t gg = g + j;
@@ -670,8 +694,11 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         const float hmax = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
         // publish the half maximum; the row maximum decides the (rare) rescale identically in both halves
         st_shared_f32(xch_at(b, half, row), hmax);
-        // nearest-pattern index, only when the half maximum moved: scan just the chains that hold it
-        if (hmax > tmax) {
+        // nearest-pattern index, only when the half maximum moved: scan just the chains that hold it.  The runner-up
+        // `tsec` takes the old maximum then (and this tile's bound once the exponentials exist), else the tile maximum
+        const bool moved = hmax > tmax;
+        tsec = fmaxf(tsec, moved ? tmax : hmax);
+        if (moved) {
           int idx = kHalfP - 1;
 #pragma unroll
           for (int u = 3; u >= 0; --u) {
@@ -736,6 +763,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         }
         HOP_STRACE(5);
         ptx::tmem_st_x32(lane_base + b * kTileP + half * 32, pk);
+        if (moved) tsec = fmaxf(tsec, second_bound(mx, ls, hmax, m_run));
         l += (ls[0] + ls[1]) + (ls[2] + ls[3]);
         ptx::tmem_wait_st();
         ptx::tc_fence_before();
@@ -759,11 +787,13 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
       if (half == 1) {
         st_shared_f32(xch_at(pl, 1, row), tmax);
         st_shared_f32(xch_at(pl, 0, row), __int_as_float(targ));
+        st_shared_f32(xch_at(pl ^ 1, 0, row), tsec);   // half 0's l slot: this thread was its only reader
       }
       ptx::named_bar_sync(pair_bar, 64);
       if (half == 0) {
         const float om = ld_shared_f32(xch_at(pl, 1, row));
         const int oa = __float_as_int(ld_shared_f32(xch_at(pl, 0, row)));
+        tsec = fmaxf(fmaxf(tsec, ld_shared_f32(xch_at(pl ^ 1, 0, row))), fminf(om, tmax));
         if (om > tmax) { tmax = om; targ = oa; }       // ties keep the lower (half-0) index
       }
       // wait for the last read-out MMA, normalise
@@ -827,9 +857,11 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
           if (a.splits > 1) {
             const long long o = part_row;
             a.part_lse[o] = lse; a.part_max[o] = tmax * kLn2; a.part_arg[o] = targ + a.pattern_offset;
+            a.part_sec[o] = tsec * kLn2;
           } else {
             if (a.lse) a.lse[grow] = lse;
             if (a.rowmax) a.rowmax[grow] = tmax * kLn2;
+            if (a.rowsec) a.rowsec[grow] = tsec * kLn2;
             if (a.argmax) a.argmax[grow] = targ + a.pattern_offset;
           }
         }
@@ -1137,7 +1169,7 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
     ptx::fence_proxy_async_smem();
     arrive_issuer(q_ready);
 
-    float m_run = -INFINITY, l = 0.f, tmax = -INFINITY;
+    float m_run = -INFINITY, l = 0.f, tmax = -INFINITY, tsec = -INFINITY;
     int targ = 0;
     constexpr int kOGroups = DV / 4 / 32;          // 32-column TMEM groups of O handled by this thread
     const int og0 = sub * kOGroups;
@@ -1166,7 +1198,9 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
       }
       const float hmax = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
       st_shared_f32(xmax_at(b, sub, L), hmax);
-      if (hmax > tmax) {
+      const bool moved = hmax > tmax;                // runner-up tracking as in hop_fwd_tc_kernel
+      tsec = fmaxf(tsec, moved ? tmax : hmax);
+      if (moved) {
         int idx = kC - 1;
 #pragma unroll
         for (int i = kC - 1; i >= 0; --i) idx = (__uint_as_float(v[i]) == hmax) ? i : idx;
@@ -1222,6 +1256,7 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
       const uint32_t p_oth = lane_base + b * Cfg::kSCols + (h ^ 1) * (TP / 4) + sub * kW;
       if constexpr (kW == 16) { ptx::tmem_st_x16(p_own, pk); ptx::tmem_st_x16(p_oth, pw); }
       else { ptx::tmem_st_x32(p_own, pk); ptx::tmem_st_x32(p_oth, pw); }
+      if (moved) tsec = fmaxf(tsec, second_bound(mx, ls, hmax, m_run));
       l += (ls[0] + ls[1]) + (ls[2] + ls[3]);
       ptx::tmem_wait_st();
       ptx::tc_fence_before();
@@ -1230,9 +1265,9 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
 
     // ---- end of the pass: the four threads of a row combine (l, tmax, targ) in pattern order
     ptx::named_bar_sync(grp_bar, 128);             // every P~ word of the last tile has been read
-    st_shared_v4(xp_at(0, sub, L), __float_as_uint(l), __float_as_uint(tmax), (uint32_t)targ, 0u);
+    st_shared_v4(xp_at(0, sub, L), __float_as_uint(l), __float_as_uint(tmax), (uint32_t)targ, __float_as_uint(tsec));
     ptx::named_bar_sync(grp_bar, 128);
-    float l_tot = 0.f, best = -INFINITY;
+    float l_tot = 0.f, best = -INFINITY, sec = -INFINITY;
     int best_arg = 0;
 #pragma unroll
     for (int hh = 0; hh < 2; ++hh)
@@ -1242,6 +1277,7 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
         ld_shared_v4(xp_at(0, ss, row + 64 * hh), w0, w1, w2, w3);
         l_tot += __uint_as_float(w0);
         const float om = __uint_as_float(w1);
+        sec = fmaxf(fmaxf(sec, __uint_as_float(w3)), fminf(om, best));
         if (om > best) { best = om; best_arg = (int)w2; }    // pattern order: ties keep the lowest index
       }
     const uint32_t last = nt - 1;
@@ -1273,9 +1309,11 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
       const float lse = kLn2 * (m_run + ptx::lg2(l_tot));
       if (a.splits > 1) {
         a.part_lse[part_row] = lse; a.part_max[part_row] = best * kLn2; a.part_arg[part_row] = best_arg + a.pattern_offset;
+        a.part_sec[part_row] = sec * kLn2;
       } else {
         if (a.lse) a.lse[grow] = lse;
         if (a.rowmax) a.rowmax[grow] = best * kLn2;
+        if (a.rowsec) a.rowsec[grow] = sec * kLn2;
         if (a.argmax) a.argmax[grow] = best_arg + a.pattern_offset;
       }
     }
@@ -1290,11 +1328,12 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
   }
 }
 
-// The exact-argmax certificate of hop_repair.cu, evaluated where lse and the row maximum are already in registers.
-__device__ __forceinline__ void certify_row(const CertArgs& c, long long r, float lse, float rowmax) {
+// The exact-argmax certificate of hop_repair.cu, evaluated where the row maximum and the runner-up bound are already
+// in registers.
+__device__ __forceinline__ void certify_row(const CertArgs& c, long long r, float rowmax, float rowsec) {
   if (c.ctrl == nullptr) return;
   const float tau = 2.f * c.qn[r] * __ldg(c.kstats) * (1.f / 1024.f) * 1.02f + 1e-5f;
-  if (lse - rowmax < log1pf(__expf(-tau)) - 1e-4f) return;            // every other score is more than tau below
+  if (rowmax - rowsec > tau) return;                                   // every other score is more than tau below
   const uint32_t slot = atomicAdd(c.ctrl, 1u);
   c.list[slot] = (int32_t)r;
   c.best[slot] = 0ull;
@@ -1304,8 +1343,8 @@ __device__ __forceinline__ void certify_row(const CertArgs& c, long long r, floa
 template <int D>
 __global__ void tc_combine_kernel(int n, int splits, const float* __restrict__ part_o,
                                   const float* __restrict__ part_lse, const float* __restrict__ part_max,
-                                  const int32_t* __restrict__ part_arg, const float* __restrict__ bias,
-                                  float out_scale, float* __restrict__ retrieved, float* __restrict__ lse,
+                                  const int32_t* __restrict__ part_arg, const float* __restrict__ part_sec,
+                                  const float* __restrict__ bias, float out_scale, float* __restrict__ retrieved, float* __restrict__ lse,
                                   int32_t* __restrict__ argmax, float* __restrict__ rowmax, const CertArgs cert) {
   const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp_global >= n) return;
@@ -1322,12 +1361,13 @@ __global__ void tc_combine_kernel(int n, int splits, const float* __restrict__ p
     const int e = lane * 4 + v * 128;
     acc[v] = (bias && e < D) ? __ldg(reinterpret_cast<const float4*>(bias + e)) : make_float4(0.f, 0.f, 0.f, 0.f);
   }
-  float best = -INFINITY;
+  float best = -INFINITY, sec = -INFINITY;
   int arg = 0;
   for (int s = 0; s < splits; ++s) {
     const long long o = (long long)s * n + r;
     const float w = __expf(part_lse[o] - m) * inv * out_scale;
     const float pm = part_max[o];
+    sec = fmaxf(fmaxf(sec, part_sec[o]), fminf(pm, best));
     if (pm > best) { best = pm; arg = part_arg[o]; }   // splits are in pattern order: ties keep the lowest index
 #pragma unroll
     for (int v = 0; v < kVec; ++v) {
@@ -1347,7 +1387,7 @@ __global__ void tc_combine_kernel(int n, int splits, const float* __restrict__ p
     if (lse) lse[r] = m + __logf(z);
     if (rowmax) rowmax[r] = best;
     if (argmax) argmax[r] = arg;
-    certify_row(cert, r, m + __logf(z), best);
+    certify_row(cert, r, best, sec);
   }
 }
 
@@ -1363,8 +1403,8 @@ __device__ __forceinline__ int sk_cluster_of(const StreamKPlan& s, int u) {
 template <int D>
 __global__ void tc_combine_streamk_kernel(int n, StreamKPlan sk, const float* __restrict__ part_o,
                                           const float* __restrict__ part_lse, const float* __restrict__ part_max,
-                                          const int32_t* __restrict__ part_arg, const float* __restrict__ bias,
-                                          float out_scale, float* __restrict__ retrieved, float* __restrict__ lse,
+                                          const int32_t* __restrict__ part_arg, const float* __restrict__ part_sec,
+                                          const float* __restrict__ bias, float out_scale, float* __restrict__ retrieved, float* __restrict__ lse,
                                           int32_t* __restrict__ argmax, float* __restrict__ rowmax, const CertArgs cert) {
   const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp_global >= n) return;
@@ -1390,12 +1430,13 @@ __global__ void tc_combine_streamk_kernel(int n, StreamKPlan sk, const float* __
     const int e = lane * 4 + v * 128;
     acc[v] = (bias && e < D) ? __ldg(reinterpret_cast<const float4*>(bias + e)) : make_float4(0.f, 0.f, 0.f, 0.f);
   }
-  float best = -INFINITY;
+  float best = -INFINITY, sec = -INFINITY;
   int arg = 0;
   for (int c = c0; c <= c1; ++c) {
     const long long o = slot_row(c);
     const float w = __expf(part_lse[o] - m) * inv * out_scale;
     const float pm = part_max[o];
+    sec = fmaxf(fmaxf(sec, part_sec[o]), fminf(pm, best));
     if (pm > best) { best = pm; arg = part_arg[o]; }   // segments are in pattern order: ties keep the lowest index
 #pragma unroll
     for (int v = 0; v < kVec; ++v) {
@@ -1415,7 +1456,7 @@ __global__ void tc_combine_streamk_kernel(int n, StreamKPlan sk, const float* __
     if (lse) lse[r] = m + __logf(z);
     if (rowmax) rowmax[r] = best;
     if (argmax) argmax[r] = arg;
-    certify_row(cert, r, m + __logf(z), best);
+    certify_row(cert, r, best, sec);
   }
 }
 
@@ -1490,7 +1531,7 @@ int launch_d(const TcPassArgs& a, int splits, const TcLaunchOpt& opt, cudaStream
   const int nt_total = ppad / kTileP;
   k.tiles_per_split = (nt_total + splits - 1) / splits;
   k.splits = (nt_total + k.tiles_per_split - 1) / k.tiles_per_split;   // every split owns >= 1 tile
-  k.retrieved = a.retrieved; k.qsave = a.qsave; k.lse = a.lse; k.argmax = a.argmax; k.rowmax = a.rowmax;
+  k.retrieved = a.retrieved; k.qsave = a.qsave; k.lse = a.lse; k.argmax = a.argmax; k.rowmax = a.rowmax; k.rowsec = a.argmax ? a.cert.sec : nullptr;
   k.pattern_offset = a.pattern_offset;
   k.zero_words = opt.zero_words;
   const CertArgs cert = (a.argmax && a.lse && a.rowmax) ? a.cert : CertArgs{};
@@ -1533,13 +1574,14 @@ int launch_d(const TcPassArgs& a, int splits, const TcLaunchOpt& opt, cudaStream
       sk.base = (int)(units / n_clusters); sk.rem = (int)(units % n_clusters);
       sk.max_seg = (sk.base + 1 + nt_total - 1) / nt_total + 1;
       const size_t rows = (size_t)n_clusters * sk.max_seg * kCluster * kTileM;
-      const size_t need = round_up_sz(rows * a.dv * sizeof(float), 256) + 3 * round_up_sz(rows * sizeof(float), 256);
+      const size_t need = round_up_sz(rows * a.dv * sizeof(float), 256) + 4 * round_up_sz(rows * sizeof(float), 256);
       if (!a.ws || a.ws_bytes < need) HOP_FAIL(HOP_ERR_WORKSPACE, "stream-K forward needs %zu workspace bytes, %zu given", need, a.ws_bytes);
       char* w = static_cast<char*>(a.ws);
       k.part_o = reinterpret_cast<float*>(w); w += round_up_sz(rows * a.dv * sizeof(float), 256);
       k.part_lse = reinterpret_cast<float*>(w); w += round_up_sz(rows * sizeof(float), 256);
       k.part_max = reinterpret_cast<float*>(w); w += round_up_sz(rows * sizeof(float), 256);
-      k.part_arg = reinterpret_cast<int32_t*>(w);
+      k.part_arg = reinterpret_cast<int32_t*>(w); w += round_up_sz(rows * sizeof(int32_t), 256);
+    k.part_sec = reinterpret_cast<float*>(w);
       k.streamk = 1; k.sk_base = sk.base; k.sk_rem = sk.rem; k.sk_max_seg = sk.max_seg;
       k.splits = 2;                       // (> 1: every segment leaves a partial for the merge)
       cudaLaunchConfig_t cfg = oc;
@@ -1549,7 +1591,7 @@ int launch_d(const TcPassArgs& a, int splits, const TcLaunchOpt& opt, cudaStream
       HOP_LAUNCH_CHECK("hop_fwd_tc_kernel");
       const int threads = 256, rows_per_block = threads / 32;
       tc_combine_streamk_kernel<H><<<(a.n + rows_per_block - 1) / rows_per_block, threads, 0, st>>>(
-          a.n, sk, k.part_o, k.part_lse, k.part_max, k.part_arg, a.bias, a.out_scale, a.retrieved, a.lse, a.argmax,
+          a.n, sk, k.part_o, k.part_lse, k.part_max, k.part_arg, k.part_sec, a.bias, a.out_scale, a.retrieved, a.lse, a.argmax,
           a.rowmax, cert);
       HOP_LAUNCH_CHECK("tc_combine_streamk_kernel");
       if (cert.ctrl && a.cert_done) *a.cert_done = true;
@@ -1566,7 +1608,8 @@ int launch_d(const TcPassArgs& a, int splits, const TcLaunchOpt& opt, cudaStream
     k.part_o = reinterpret_cast<float*>(w); w += round_up_sz(rows * a.dv * sizeof(float), 256);
     k.part_lse = reinterpret_cast<float*>(w); w += round_up_sz(rows * sizeof(float), 256);
     k.part_max = reinterpret_cast<float*>(w); w += round_up_sz(rows * sizeof(float), 256);
-    k.part_arg = reinterpret_cast<int32_t*>(w);
+    k.part_arg = reinterpret_cast<int32_t*>(w); w += round_up_sz(rows * sizeof(int32_t), 256);
+    k.part_sec = reinterpret_cast<float*>(w);
   }
 
   // the attribute is per device and cheap to set: do it on every launch so that any current device works
@@ -1586,7 +1629,7 @@ int launch_d(const TcPassArgs& a, int splits, const TcLaunchOpt& opt, cudaStream
   if (k.splits > 1) {
     const int threads = 256, rows_per_block = threads / 32;
     tc_combine_kernel<H><<<(a.n + rows_per_block - 1) / rows_per_block, threads, 0, st>>>(
-        a.n, k.splits, k.part_o, k.part_lse, k.part_max, k.part_arg, a.bias, a.out_scale, a.retrieved, a.lse, a.argmax,
+        a.n, k.splits, k.part_o, k.part_lse, k.part_max, k.part_arg, k.part_sec, a.bias, a.out_scale, a.retrieved, a.lse, a.argmax,
         a.rowmax, cert);
     HOP_LAUNCH_CHECK("tc_combine_kernel");
     if (cert.ctrl && a.cert_done) *a.cert_done = true;
@@ -1610,7 +1653,7 @@ int launch_h64(const TcPassArgs& a, int splits, const TcLaunchOpt& opt, cudaStre
   const int nt_total = (ppad + TP - 1) / TP;          // (rows past ppad read as zeros and are masked)
   k.tiles_per_split = (nt_total + splits - 1) / splits;
   k.splits = (nt_total + k.tiles_per_split - 1) / k.tiles_per_split;
-  k.retrieved = a.retrieved; k.qsave = a.qsave; k.lse = a.lse; k.argmax = a.argmax; k.rowmax = a.rowmax;
+  k.retrieved = a.retrieved; k.qsave = a.qsave; k.lse = a.lse; k.argmax = a.argmax; k.rowmax = a.rowmax; k.rowsec = a.argmax ? a.cert.sec : nullptr;
   k.pattern_offset = a.pattern_offset;
   k.zero_words = opt.zero_words;
   const CertArgs cert = (a.argmax && a.lse && a.rowmax) ? a.cert : CertArgs{};
@@ -1625,7 +1668,8 @@ int launch_h64(const TcPassArgs& a, int splits, const TcLaunchOpt& opt, cudaStre
     k.part_o = reinterpret_cast<float*>(w); w += round_up_sz(rows * a.dv * sizeof(float), 256);
     k.part_lse = reinterpret_cast<float*>(w); w += round_up_sz(rows * sizeof(float), 256);
     k.part_max = reinterpret_cast<float*>(w); w += round_up_sz(rows * sizeof(float), 256);
-    k.part_arg = reinterpret_cast<int32_t*>(w);
+    k.part_arg = reinterpret_cast<int32_t*>(w); w += round_up_sz(rows * sizeof(int32_t), 256);
+    k.part_sec = reinterpret_cast<float*>(w);
   }
   auto* kern = hop_fwd_tc64_kernel<H, DV, TP, kBf16>;
   HOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
@@ -1644,7 +1688,7 @@ int launch_h64(const TcPassArgs& a, int splits, const TcLaunchOpt& opt, cudaStre
   if (k.splits > 1) {
     const int threads = 256, rows_per_block = threads / 32;
     tc_combine_kernel<H><<<(a.n + rows_per_block - 1) / rows_per_block, threads, 0, st>>>(
-        a.n, k.splits, k.part_o, k.part_lse, k.part_max, k.part_arg, a.bias, a.out_scale, a.retrieved, a.lse, a.argmax,
+        a.n, k.splits, k.part_o, k.part_lse, k.part_max, k.part_arg, k.part_sec, a.bias, a.out_scale, a.retrieved, a.lse, a.argmax,
         a.rowmax, cert);
     HOP_LAUNCH_CHECK("tc_combine_kernel");
     if (cert.ctrl && a.cert_done) *a.cert_done = true;
@@ -1756,7 +1800,7 @@ namespace { size_t ws_for_splits_fwd(int splits, int n, int d) { return ws_for_s
 static size_t ws_for_splits(int splits, int n, int d) {
   if (splits <= 1) return 0;
   const size_t rows = (size_t)splits * n;
-  return round_up_sz(rows * d * sizeof(float), 256) + 3 * round_up_sz(rows * sizeof(float), 256);
+  return round_up_sz(rows * d * sizeof(float), 256) + 4 * round_up_sz(rows * sizeof(float), 256);
 }
 
 // Stream-K scheduling of the T = 0 forward (HOP_TUNE_STREAMK_ON / _OFF force it): used when the plain grid would give
@@ -1787,7 +1831,7 @@ static size_t streamk_ws(int n, int d, const TcTune& t) {
   const int cl = tc_cluster(n, d, t);
   const size_t row_groups = ((size_t)(n + kTileM - 1) / kTileM + cl - 1) / cl;
   const size_t rows = (row_groups + 3 * (size_t)(num_sms() / cl)) * cl * kTileM;
-  return round_up_sz(rows * d * sizeof(float), 256) + 3 * round_up_sz(rows * sizeof(float), 256);
+  return round_up_sz(rows * d * sizeof(float), 256) + 4 * round_up_sz(rows * sizeof(float), 256);
 }
 
 // Covers every launch form launch_tc_forward can choose for (n, p, d, T): the plain grid's split partials (all

@@ -3,12 +3,15 @@
 // (1) HOP_F_EXACT_ARGMAX.  The fused tcgen05 forward (hop_fwd_tc.cu) finds each row's nearest pattern on scores whose
 // operands were rounded to 16 bits: |s16 - s| <= |q| |k| 2^-10 (two relative roundings of 2^-11 per product, summed with
 // Cauchy-Schwarz).  Its index equals the fp32 reference's ("nearest-pattern argmax indices identical", BASELINE.json)
-// whenever the top-1 / top-2 gap exceeds tau = 2 |q| max_j|k_j| 2^-10.  The forward already holds a certificate for
-// that: lse - rowmax = log(1 + sum_{j != top} exp(s_j - s_top)), so  lse - rowmax < log(1 + e^-tau)  proves that EVERY
-// other score lies more than tau below the maximum.  `certify_rows_kernel` evaluates it per row (|q_r| recomputed in
-// fp32 from the raw row, mirroring the forward's LN_q prologue; where the forward ends in a merge kernel -- every large
-// problem -- that kernel evaluates the certificate itself from the norms the forward's prologue wrote, and this launch
-// is skipped); rows that fail are appended to a compact list, and `argmax_repair_kernel` rebuilds their fp32 query rows
+// whenever the top-1 / top-2 gap exceeds tau = 2 |q| max_j|k_j| 2^-10.  The forward carries a certificate for that: next
+// to each row's maximum its softmax threads keep an upper bound on the runner-up score (`second_bound` in
+// hop_fwd_tc.cu: exact maxima of every tile and max chain that does not hold the running maximum, and for the 8 .. 16
+// columns sharing a chain with it the log of their summed exponentials -- a bound that does NOT grow with the pattern
+// count, unlike lse - rowmax, whose tail of P - 1 exponentials reaches e^-tau long before P = 10^6);  rowmax - bound > tau
+// proves that EVERY other score lies more than tau below the maximum.  `certify_rows_kernel` evaluates it per row (|q_r|
+// recomputed in fp32 from the raw row, mirroring the forward's LN_q prologue; where the forward ends in a merge kernel --
+// every large problem -- that kernel evaluates the certificate itself from the norms the forward's prologue wrote, and this
+// launch is skipped); rows that fail are appended to a compact list, and `argmax_repair_kernel` rebuilds their fp32 query rows
 // from the raw input and re-scores exactly those rows against the fp32 K^ on CUDA cores
 // (64 x 64 register-tiled FFMA), merging (score, index) with a packed 64-bit atomicMax; the last CTA to finish writes
 // the corrected index / row maximum back.  With well-separated retrievals (BASELINE config 5's recipe: gap ~ 10 nats)
@@ -79,7 +82,7 @@ __global__ void __launch_bounds__(NT) certify_rows_kernel(RepairArgs a, RepairWs
   const int warp = (blockIdx.x * NT + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= a.n) return;
   const long long r = warp;
-  const float gap_stat = a.lse[r] - a.rowmax[r];            // log(1 + sum of the other exponentials)
+  const float gap = a.rowmax[r] - a.rowsec[r];              // lower bound on the top-1 / top-2 gap of the 16-bit scores
   const float* src = (a.x_raw ? a.x_raw : a.qs) + r * a.h;
   float mean = 0.f, rstd = 1.f;
   const bool ln = a.x_raw && a.has_ln;
@@ -91,7 +94,7 @@ __global__ void __launch_bounds__(NT) certify_rows_kernel(RepairArgs a, RepairWs
   }
   qn2 = warp_sum(qn2);
   const float tau = 2.f * sqrtf(qn2) * __ldg(a.kstats) * (1.f / 1024.f) * 1.02f + 1e-5f;
-  const bool certified = gap_stat < log1pf(__expf(-tau)) - 1e-4f;
+  const bool certified = gap > tau;
   if (certified) return;
   if (lane == 0) {
     const uint32_t slot = atomicAdd(w.ctrl, 1u);
@@ -310,14 +313,14 @@ __global__ void __launch_bounds__(NT) delta_decide_kernel(const float* __restric
 
 size_t repair_workspace_bytes(int n, int h) { return carve_repair(nullptr, n, h).total; }
 
-CertArgs repair_cert_args(void* ws, int n, int h, const float* kstats, float* qn) {
+CertArgs repair_cert_args(void* ws, int n, int h, const float* kstats, float* qn, float* sec) {
   const RepairWs w = carve_repair(ws, n, h);
-  return CertArgs{w.ctrl, w.list, w.best, kstats, qn};
+  return CertArgs{w.ctrl, w.list, w.best, kstats, qn, sec};
 }
 
 int launch_argmax_repair(const RepairArgs& a, cudaStream_t st) {
-  if (!a.argmax || !a.lse || !a.rowmax || !a.khat || !a.kstats)
-    HOP_FAIL(HOP_ERR_BAD_ARG, "exact argmax needs argmax / lse / rowmax outputs, the fp32 K^ and kstats");
+  if (!a.argmax || !a.rowmax || !a.khat || !a.kstats || (!a.precertified && !a.rowsec))
+    HOP_FAIL(HOP_ERR_BAD_ARG, "exact argmax needs argmax / rowmax outputs, the runner-up bound, the fp32 K^ and kstats");
   const size_t need = repair_workspace_bytes(a.n, a.h);
   if (!a.ws || a.ws_bytes < need) HOP_FAIL(HOP_ERR_WORKSPACE, "argmax repair needs %zu workspace bytes, %zu given", need, a.ws_bytes);
   if ((a.h & 3) != 0) HOP_FAIL(HOP_ERR_BAD_SHAPE, "argmax repair needs H %% 4 == 0");

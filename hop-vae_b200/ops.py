@@ -204,6 +204,12 @@ def _(lookup, lookup_targets, ln_stored_w, ln_stored_b, ln_proj_w, ln_proj_b, wk
 
 
 # --------------------------------------------------------------------------- retrieve (forward)
+# Diagnostic of exact_argmax (tests, bench): with `count_repairs` set, every tensor-core forward is followed by a
+# (synchronising) read of how many rows failed the top-1 / top-2 certificate and were re-scored in fp32.
+count_repairs = False
+last_repair_rows = 0
+
+
 def retrieve(x: Tensor, pats: List[Tensor], ln_state_w: Optional[Tensor], ln_state_b: Optional[Tensor],
              wq: Optional[Tensor], bq: Optional[Tensor], wo: Optional[Tensor], bo: Optional[Tensor], flags: int,
              path: int, d_in: int, d_out: int, update_steps: int, beta: float, ln_eps: float, pattern_offset: int,
@@ -262,6 +268,12 @@ def retrieve(x: Tensor, pats: List[Tensor], ln_state_w: Optional[Tensor], ln_sta
         cabi.check(lib.hop_sm100_forward(C.byref(d), C.byref(params), C.byref(ps), cabi.ptr(x), cabi.ptr(out),
                                          cabi.ptr(retrieved), cabi.ptr(qhat), cabi.ptr(lse), cabi.ptr(argmax),
                                          cabi.ptr(rowmax), cabi.ptr(ws), need, _stream(dev)), "hop_sm100_forward")
+        if count_repairs and tc and (flags & cabi.F_EXACT_ARGMAX):
+            global last_repair_rows
+            rows = C.c_int32(0)
+            cabi.check(lib.hop_sm100_repair_rows(C.byref(d), cabi.ptr(ws), _stream(dev), C.byref(rows)),
+                       "hop_sm100_repair_rows")
+            last_repair_rows = int(rows.value)
     if qhat is None:
         qhat = _empty_f32(dev)
     if retrieved is None:

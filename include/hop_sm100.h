@@ -246,6 +246,12 @@ int hop_sm100_backward(const hop_desc* desc, const hop_params* params,
                        const float* grad_out, const hop_grads* grads,
                        void* workspace, size_t workspace_bytes, void* stream);
 
+/* Diagnostic of HOP_F_EXACT_ARGMAX: how many rows of the last forward run with
+ * this descriptor (argmax != NULL) into this workspace failed the top-1 / top-2
+ * certificate and were re-scored in fp32.  Waits for `stream`.  0 rows on the
+ * fp32 path (whose index is exact by construction).                            */
+int hop_sm100_repair_rows(const hop_desc* desc, const void* workspace, void* stream, int32_t* rows_out);
+
 /* Pattern-sharded mode (new; the reference is single-device): combine G
  * shard-local results with the log-sum-exp monoid.
  *   lse_all     (G, N)      every shard's lse   (after an all-gather)
