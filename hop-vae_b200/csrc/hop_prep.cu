@@ -238,7 +238,8 @@ PrepScratch carve_prep(void* base, const hop_desc& d) {
   return s;
 }
 bool prep_uses_gemm(const hop_desc& d) {
-  return (d.flags & HOP_F_PROJ_PATTERN) && tc_gemm_supported(d.d_v, d.d_in) && d.n_patterns >= 1024 &&
+  return (d.flags & HOP_F_PROJ_PATTERN) && !(d.tune_flags & HOP_TUNE_PREP_SIMT) && tc_gemm_supported(d.d_v, d.d_in) &&
+         d.n_patterns >= 1024 &&
          (!out_proj_foldable(d) || tc_gemm_supported(d.d_out, d.d_v));
 }
 }  // namespace

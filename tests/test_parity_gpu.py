@@ -811,3 +811,50 @@ def test_sweep_point_full_size_parity(hf, name):
     assert bad == 0
     if T == 0:
         assert decidable.float().mean() > 0.95
+
+
+@pytest.mark.parametrize("D,P,T", [(256, 65536, 0), (64, 4096, 1), (128, 5000, 0), (512, 2048, 0), (256, 3000, 2)])
+def test_pattern_preparation_on_tensor_cores(hf, D, P, T):
+    """hop_gemm_tc.cu: V^ = LN_v(W) Wv^T + bv and the folded read-out operand (V^ Wo^T) on tcgen05 with hi + lo fp16
+    operand pairs (three MMAs per product, ~2^-21 relative) against (a) the library's own fp32 CUDA-core preparation
+    (tune prep_simt) and (b) the oracle's projection.  The fp32 V^ must agree to fp32-accumulation noise, every 16-bit
+    pack to one ulp of its format on a handful of elements at most (a value on a rounding boundary)."""
+    ref, dut, g = _sweep_layer(hf, D, P, T)
+    dut.kernel_path = "f16"
+    x = (ref.lookup_weights[0, torch.randint(0, P, (64,), generator=g)] + 0.5 * torch.randn(64, D, generator=g)).cuda()
+    packs = {}
+    with torch.no_grad():
+        for mode in ("gemm", "fp32"):
+            dut.tune = dict(prep_simt=(mode == "fp32"))
+            dut.invalidate()
+            out = dut(x)
+            packs[mode] = ([t.clone() for t in dut._cache], out.clone())
+        core = ref.hopfield.association_core
+        w = ref.lookup_weights[0]
+        v_in = F.layer_norm(w, (D,), ref.hopfield.norm_pattern_projection.weight, ref.hopfield.norm_pattern_projection.bias)
+        Dv = dut.pattern_size
+        wv, bv = core.in_proj_weight[-Dv:], core.in_proj_bias[-Dv:]
+        vhat_oracle = (v_in.double() @ wv.double().T + bv.double()).float()
+    names = hf._impl.cabi._PATTERN_FIELDS
+    (pg, og), (pf, of) = packs["gemm"], packs["fp32"]
+    r_v = rel_l2(pg[1], vhat_oracle)
+    print(f"D={D} P={P}: V^ (tensor cores) vs float64 oracle rel-L2 {r_v:.3e}; fp32 kernels {rel_l2(pf[1], vhat_oracle):.3e}")
+    assert r_v < 2e-6
+    for i, name in enumerate(names):
+        a, b = pg[i], pf[i]
+        if name == "scratch" or a.numel() == 0:
+            continue
+        assert a.shape == b.shape and a.dtype == b.dtype, name
+        if a.dtype == torch.float32:
+            assert rel_l2(a, b) < 2e-6, name
+        else:                                            # uint8 views of fp16 packs
+            ha, hb = a.view(torch.float16).float(), b.view(torch.float16).float()
+            if name.endswith("lo"):                      # residuals: compare hi + lo through the sum they encode
+                continue
+            diff = (ha - hb).abs()
+            tol = hb.abs().clamp_min(1e-3) * 2.0 ** -10
+            bad = int((diff > tol).sum())
+            print(f"  {name}: {int((diff > 0).sum())} of {ha.numel()} 16-bit words differ, {bad} by more than one ulp")
+            assert bad == 0, name
+            assert int((diff > 0).sum()) <= max(8, ha.numel() // 200), name
+    assert rel_l2(og, of) < 2e-4          # same queries through both sets of packs (16-bit operand noise apart)
