@@ -3,8 +3,10 @@
 
 Per point: device time of `HopfieldLayer.forward` (CUDA events, L2 flushed between steps), algorithmic TFLOP/s
 (2 N P [(2T+1) D + Dv]) against the measured bf16 peak, and PARITY at full size against the
-chunked fp32/fp64 CPU restatement on a 256-row query subsample (rel-L2 of the layer output, nearest-pattern
-index on rows whose top-1/top-2 score gap exceeds the 16-bit operand noise).
+chunked fp32/fp64 CPU restatement on a 256-row query subsample (rel-L2 of the layer output; nearest-pattern index on
+every row the fp32 oracle itself decides -- gap > 1e-4 nats at T = 0, where the layer's exact-index path applies; with
+retrieve updates the iterated state carries the earlier passes' 16-bit rounding and the bar is the 2e-2 of that noise),
+plus how many of the 16,384 rows failed the on-chip top-1 / top-2 certificate and were re-scored in fp32.
     python scripts/sweep_config5.py [--quick] > profiles/rNN_sweep_config5.jsonl"""
 import json
 import math
@@ -55,14 +57,18 @@ for (p, d, t) in points:
             ts.append(e0.elapsed_time(e1))
         ms = sorted(ts)[len(ts) // 2]
         got, got_arg = y[:SUB].cpu(), layer.last_argmax[:SUB].cpu().long()
+        ops = hflayers._impl.ops
+        ops.count_repairs = True
+        layer(x)
+        ops.count_repairs = False
     want, arg, gap = cpu_oracle(xh[:SUB], w, wv, wo, t, 1.0 / math.sqrt(d))
     rel = float((got - want).norm() / want.norm())
-    decided = gap > 2e-2
+    decided = gap > (1e-4 if t == 0 else 2e-2)
     fl = bench.fwd_flops(N, p, d, d, t)
     res = {"patterns": p, "dim": d, "update_steps": t, "rows": N, "ms": ms, "latents_per_s": N / (ms * 1e-3),
            "algorithmic_tflops": fl / (ms * 1e-3) / 1e12, "frac_of_measured_peak": fl / (ms * 1e-3) / 1e12 / peak,
            "parity_rows": SUB, "rel_l2": rel, "argmax_decided_rows": int(decided.sum()),
-           "argmax_mismatch": int((got_arg[decided] != arg[decided]).sum())}
+           "argmax_mismatch": int((got_arg[decided] != arg[decided]).sum()), "rows_rescored_fp32": ops.last_repair_rows}
     print(json.dumps(res), flush=True)
     del layer, x, w, wv, wo
     torch.cuda.empty_cache()
