@@ -148,6 +148,7 @@ size_t tc_forward_workspace(int n, int p, int d, int update_steps, const TcTune&
 int launch_tc_forward(const TcPassArgs& a, cudaStream_t st);
 bool tc_supported(int h, int dv);
 // hop_gemm_tc.cu -- C[M x N] = A[M x K] . B[N x K]^T (+ bias) on tcgen05, fp16 K-major operand packs, optional hi + lo pairs
+constexpr float kGemmLoScale = 2048.f;   // low halves of the GEMM's operand pairs are stored times 2^11
 struct TcGemmArgs {
   const void* a16; const void* a16lo;   // (m_pad, k) fp16, rows >= m zero
   const void* b16; const void* b16lo;   // (n, k) fp16

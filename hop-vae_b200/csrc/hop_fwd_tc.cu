@@ -131,27 +131,21 @@ struct TcKernelArgs {
   float* part_o; float* part_lse; float* part_max; int32_t* part_arg; float* part_sec;
 };
 
-// Runner-up bound of one softmax thread's tile, from what the softmax holds anyway.  The score columns of a thread sit on
-// four max chains `mx[u]` whose exponentials were summed into `ls[u]` (pair i of the packing loop belongs to chain i & 3).
-// The chains that do not hold the tile maximum `hmax` contribute their maxima exactly; in the one that does, the other
-// columns' exponentials add up to ls[u] - 2^(hmax - m_run), and no single one of them can exceed that sum.  The result
-// is >= the true second-largest score of the tile (a duplicate of hmax in the same chain makes the rest >= the top
-// term, i.e. the bound >= hmax): rows certified with it are safe, a loose bound only sends a row to the fp32 repair.
-// `kSecondSlack` covers the rounding of the sum and the 7.5e-5 of the polynomial exponential on the top term.
+// Runner-up bound of one softmax thread (exact-index certificate, hop_repair.cu).  Next to its running maximum `tmax` a
+// thread keeps `tsec`, the exact maximum of everything that is known to lie below it -- the maxima of all other tiles and
+// every previous value of tmax -- at two instructions per tile.  What is left are the other 31 / 63 columns of the one
+// tile that holds tmax: for those it remembers that tile's sum of exponentials and its reference (two predicated moves
+// per tile); no single one of them can exceed the sum of all of them, so at the end of the pass
+//     second <= ref + log2(sum - 2^(tmax - ref))
+// closes the bound with two MUFU operations per pass instead of a second max-scan per tile.  The bound is >= the true
+// runner-up (a duplicate of tmax in the same tile makes the rest >= the top term, i.e. the bound >= tmax): rows
+// certified with it are safe, a loose bound only sends a row to the fp32 repair.  `kSecondSlack` covers the rounding
+// of the sum and the 7.5e-5 of the polynomial exponential on the top term.
 constexpr float kSecondSlack = 4e-4f;
-__device__ __forceinline__ float second_bound(const float (&mx)[4], const float (&ls)[4], float hmax, float m_run) {
-  float oth = -INFINITY, lsh = 0.f;
-  bool found = false;
-#pragma unroll
-  for (int u = 0; u < 4; ++u) {
-    const bool hit = !found && mx[u] == hmax;
-    lsh = hit ? ls[u] : lsh;
-    oth = hit ? oth : fmaxf(oth, mx[u]);
-    found = found || hit;
-  }
-  const float pt = ptx::ex2(hmax - m_run);
-  const float rest = fmaxf(lsh - pt, 0.f) + kSecondSlack * pt;
-  return fmaxf(oth, m_run + ptx::lg2(rest));
+__device__ __forceinline__ float second_bound(float tmax, float top_sum, float top_ref) {
+  const float pt = ptx::ex2(tmax - top_ref);
+  const float rest = fmaxf(top_sum - pt, 0.f) + kSecondSlack * pt;
+  return top_ref + ptx::lg2(rest);
 }
 
 template <bool kBf16>
@@ -647,7 +641,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
       arrive_issuer(q_ready);
 
       // m_run is shared by the pair (identical in both threads of a row); l, tmax, targ are per half
-      float m_run = -INFINITY, l = 0.f, tmax = -INFINITY, tsec = -INFINITY;
+      float m_run = -INFINITY, l = 0.f, tmax = -INFINITY, tsec = -INFINITY, top_sum = 0.f, top_ref = 0.f;
       int targ = 0;
       for (int j = 0; j < nt; ++j) {
         const uint32_t gg = g + j;
@@ -695,9 +689,11 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         // publish the half maximum; the row maximum decides the (rare) rescale identically in both halves
         st_shared_f32(xch_at(b, half, row), hmax);
         // nearest-pattern index, only when the half maximum moved: scan just the chains that hold it.  The runner-up
-        // `tsec` takes the old maximum then (and this tile's bound once the exponentials exist), else the tile maximum
+        // `tsec` takes the old maximum then (see second_bound), else the tile maximum
         const bool moved = hmax > tmax;
+#ifndef HOP_NO_TOP2          // (timing experiments only: without the tracking every row fails the certificate)
         tsec = fmaxf(tsec, moved ? tmax : hmax);
+#endif
         if (moved) {
           int idx = kHalfP - 1;
 #pragma unroll
@@ -763,8 +759,12 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         }
         HOP_STRACE(5);
         ptx::tmem_st_x32(lane_base + b * kTileP + half * 32, pk);
-        if (moved) tsec = fmaxf(tsec, second_bound(mx, ls, hmax, m_run));
-        l += (ls[0] + ls[1]) + (ls[2] + ls[3]);
+        const float tsum = (ls[0] + ls[1]) + (ls[2] + ls[3]);
+#ifndef HOP_NO_TOP2
+        top_sum = moved ? tsum : top_sum;
+        top_ref = moved ? m_run : top_ref;
+#endif
+        l += tsum;
         ptx::tmem_wait_st();
         ptx::tc_fence_before();
         arrive_issuer(p_full(b));
@@ -781,6 +781,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
       }
       // ---- end of the pass: the pair combines (l, tmax, targ); slots of the other parity are idle
       const int pl = (g + nt - 1) & 1;
+      tsec = fmaxf(tsec, second_bound(tmax, top_sum, top_ref));
       st_shared_f32(xch_at(pl ^ 1, half, row), l);
       ptx::named_bar_sync(pair_bar, 64);
       const float l_tot = l + ld_shared_f32(xch_at(pl ^ 1, half ^ 1, row));
@@ -1169,7 +1170,7 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
     ptx::fence_proxy_async_smem();
     arrive_issuer(q_ready);
 
-    float m_run = -INFINITY, l = 0.f, tmax = -INFINITY, tsec = -INFINITY;
+    float m_run = -INFINITY, l = 0.f, tmax = -INFINITY, tsec = -INFINITY, top_sum = 0.f, top_ref = 0.f;
     int targ = 0;
     constexpr int kOGroups = DV / 4 / 32;          // 32-column TMEM groups of O handled by this thread
     const int og0 = sub * kOGroups;
@@ -1256,8 +1257,10 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
       const uint32_t p_oth = lane_base + b * Cfg::kSCols + (h ^ 1) * (TP / 4) + sub * kW;
       if constexpr (kW == 16) { ptx::tmem_st_x16(p_own, pk); ptx::tmem_st_x16(p_oth, pw); }
       else { ptx::tmem_st_x32(p_own, pk); ptx::tmem_st_x32(p_oth, pw); }
-      if (moved) tsec = fmaxf(tsec, second_bound(mx, ls, hmax, m_run));
-      l += (ls[0] + ls[1]) + (ls[2] + ls[3]);
+      const float tsum = (ls[0] + ls[1]) + (ls[2] + ls[3]);
+      top_sum = moved ? tsum : top_sum;
+      top_ref = moved ? m_run : top_ref;
+      l += tsum;
       ptx::tmem_wait_st();
       ptx::tc_fence_before();
       arrive_issuer(p_full(b));
@@ -1265,6 +1268,7 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
 
     // ---- end of the pass: the four threads of a row combine (l, tmax, targ) in pattern order
     ptx::named_bar_sync(grp_bar, 128);             // every P~ word of the last tile has been read
+    tsec = fmaxf(tsec, second_bound(tmax, top_sum, top_ref));
     st_shared_v4(xp_at(0, sub, L), __float_as_uint(l), __float_as_uint(tmax), (uint32_t)targ, __float_as_uint(tsec));
     ptx::named_bar_sync(grp_bar, 128);
     float l_tot = 0.f, best = -INFINITY, sec = -INFINITY;

@@ -6,13 +6,17 @@
 //     C[M x N] (fp32, row-major)  =  A[M x K] . B[N x K]^T  (+ bias[N])
 //
 // A and B are K-major fp16 packs streamed by TMA (128-byte swizzle).  With `split` each operand is a hi + lo pair
-// (fp16(v), fp16(v - fp16(v))) and a product is three MMAs (Ah Bh + Al Bh + Ah Bl): ~2^-21 relative, i.e. the fp32 V^ the
-// other kernels read stays an fp32-grade quantity although it is produced by tcgen05.mma.kind::f16.
+// (fp16(v), fp16(2^11 (v - fp16(v)))) and a product is three MMAs, Ah Bh into one TMEM accumulator and Al Bh + Ah Bl into
+// a second one that the epilogue adds back times 2^-11: ~2^-21 relative, i.e. the fp32 V^ the other kernels read stays an
+// fp32-grade quantity although it is produced by tcgen05.mma.kind::f16.  (The residual is stored scaled because the
+// unscaled one of a weight of magnitude 0.05 is ~2^-16, an fp16 subnormal with 2^-25 absolute spacing -- measured 1.1e-6
+// rel-L2 on V^ against 3e-7 for the fp32 kernels; scaled, the residual has the hi word's own exponent range.)
 //
 // One CTA = one 128-row tile of C, up to 256 columns (grid.y walks wider N): warp 0 TMA producer, warp 1 MMA issuer
 // (cta_group::1, M = 128, N = the tile width in one instruction), warps 2-5 epilogue (TMEM lane = row: 128-byte row
 // segments per thread, bias added, plain stores).  K is short here (64..1024), so a tile is a few microseconds: the grid
-// is the row tiles, several CTAs per SM overlap one tile's epilogue with another's loads (TMEM: 256 columns per CTA).
+// is the row tiles, CTAs of neighbouring tiles overlap one tile's epilogue with another's loads where shared memory lets two reside
+// (TMEM: TN columns per CTA, 2 TN with operand pairs).
 #include <cuda.h>
 
 #include <mutex>
@@ -42,7 +46,7 @@ struct GemmCfg {
   static constexpr int kStageBytes = (kSplit ? 2 : 1) * (kABytes + kBBytes);
   static constexpr int kStages = kSplit ? 2 : 3;
   static constexpr int kSmemBytes = kStages * kStageBytes + 256 + 1024;   // + barriers, + alignment slack
-  static constexpr uint32_t kTmemCols = TN < 32 ? 32 : TN;
+  static constexpr uint32_t kTmemCols = (kSplit ? 2 : 1) * TN;     // 64 .. 512: a power of two
 };
 
 template <int TN, bool kSplit>
@@ -110,9 +114,9 @@ hop_gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
           const uint64_t al = ptx::umma_desc_sw128(base + Cfg::kABytes + Cfg::kBBytes);
           const uint64_t bl = ptx::umma_desc_sw128(base + 2 * Cfg::kABytes + Cfg::kBBytes);
 #pragma unroll
-          for (int k = 0; k < 4; ++k) ptx::umma_f16_ss(tmem_base, al + 2 * k, bh + 2 * k, idesc, 1u);
+          for (int k = 0; k < 4; ++k) ptx::umma_f16_ss(tmem_base + TN, al + 2 * k, bh + 2 * k, idesc, (kc | k) != 0);
 #pragma unroll
-          for (int k = 0; k < 4; ++k) ptx::umma_f16_ss(tmem_base, ah + 2 * k, bl + 2 * k, idesc, 1u);
+          for (int k = 0; k < 4; ++k) ptx::umma_f16_ss(tmem_base + TN, ah + 2 * k, bl + 2 * k, idesc, 1u);
         }
         ptx::umma_commit(empty_bar(s));
       }
@@ -130,7 +134,16 @@ hop_gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
     for (int c = 0; c < TN / 32; ++c) {
       uint32_t o[32];
       ptx::tmem_ld_x32(lane_base + c * 32, o);
-      ptx::tmem_wait_ld();
+      if constexpr (kSplit) {
+        uint32_t ol[32];
+        ptx::tmem_ld_x32(lane_base + TN + c * 32, ol);
+        ptx::tmem_wait_ld();
+#pragma unroll
+        for (int i = 0; i < 32; ++i)
+          o[i] = __float_as_uint(fmaf(__uint_as_float(ol[i]), 1.f / kGemmLoScale, __uint_as_float(o[i])));
+      } else {
+        ptx::tmem_wait_ld();
+      }
       const int gc = col0 + c * 32;
       if (grow < g.m && gc < g.n) {
         float* dst = g.c + grow * g.ldc + gc;

@@ -31,6 +31,8 @@ struct LnLinearArgs {
   int bf16;            // 16-bit encoding: 0 = fp16 (saturating), 1 = bf16
   void* y16lo;         // (rows_pad, dout) 16-bit: y - decode(y16), the low half of a hi + lo operand pair, or nullptr
   void* yt16lo;        // (dout, rows_pad) same, transposed, or nullptr
+  float lo_scale;      // the low halves hold lo_scale * (y - decode(y16)) (0 = 1; hop_gemm_tc.cu takes 2^11, which keeps the
+                       // residual of small-magnitude operands out of the fp16 subnormals)
   float* norm_max;     // [1]: max over rows of ||y_row||_2 (atomic max on the float's bits; zeroed by the caller) or nullptr
 };
 
@@ -45,7 +47,9 @@ __device__ __forceinline__ float from16(uint16_t w, int bf16) {
   return bf16 ? __bfloat162float(__ushort_as_bfloat16(w)) : __half2float(__ushort_as_half(w));
 }
 // low half of a hi + lo operand pair: what the 16-bit encoding of v lost, encoded again
-__device__ __forceinline__ uint16_t to16_lo(float v, int bf16) { return to16(v - from16(to16(v, bf16), bf16), bf16); }
+__device__ __forceinline__ uint16_t to16_lo(float v, int bf16, float scale) {
+  return to16((v - from16(to16(v, bf16), bf16)) * scale, bf16);
+}
 
 template <int RM>
 __device__ __forceinline__ void ln_linear_body(const LnLinearArgs& a) {
@@ -151,7 +155,7 @@ __device__ __forceinline__ void ln_linear_body(const LnLinearArgs& a) {
       const float v = (gr < a.rows) ? Ys[r * YS + c] : 0.f;
       if (a.y && gr < a.rows) a.y[(size_t)gr * a.dout + gc] = v;
       if (a.y16 && gr < a.rows_pad) reinterpret_cast<uint16_t*>(a.y16)[(size_t)gr * a.dout + gc] = to16(v, a.bf16);
-      if (a.y16lo && gr < a.rows_pad) reinterpret_cast<uint16_t*>(a.y16lo)[(size_t)gr * a.dout + gc] = to16_lo(v, a.bf16);
+      if (a.y16lo && gr < a.rows_pad) reinterpret_cast<uint16_t*>(a.y16lo)[(size_t)gr * a.dout + gc] = to16_lo(v, a.bf16, a.lo_scale > 0.f ? a.lo_scale : 1.f);
       if (a.norm_max) atomicAdd(&s_sq[r], v * v);
     }
     if (a.yt16) {
@@ -161,7 +165,7 @@ __device__ __forceinline__ void ln_linear_body(const LnLinearArgs& a) {
         if (gc >= a.dout || gr >= a.rows_pad) continue;
         const float v = (gr < a.rows) ? Ys[r * YS + c] : 0.f;
         reinterpret_cast<uint16_t*>(a.yt16)[(size_t)gc * a.rows_pad + gr] = to16(v, a.bf16);
-        if (a.yt16lo) reinterpret_cast<uint16_t*>(a.yt16lo)[(size_t)gc * a.rows_pad + gr] = to16_lo(v, a.bf16);
+        if (a.yt16lo) reinterpret_cast<uint16_t*>(a.yt16lo)[(size_t)gc * a.rows_pad + gr] = to16_lo(v, a.bf16, a.lo_scale > 0.f ? a.lo_scale : 1.f);
       }
     }
   }
@@ -276,7 +280,7 @@ int launch_prepare_patterns(const hop_desc& d, const hop_params& p, const hop_pa
       LnLinearArgs a{};
       a.x = x; a.rows = rows; a.rows_pad = rows_pad; a.din = w; a.has_ln = has_ln; a.ln_w = lw; a.ln_b = lb;
       a.ln_eps = d.ln_eps; a.w = nullptr; a.b = nullptr; a.dout = w; a.scale = 1.f; a.y = y; a.y16 = y16;
-      a.y16lo = y16lo; a.yt16 = yt16; a.bf16 = 0;
+      a.y16lo = y16lo; a.yt16 = yt16; a.bf16 = 0; a.lo_scale = kGemmLoScale;
       return launch_ln_linear(a, st);
     };
     HOP_TRY(pack(Wt, d.n_patterns, ppad, d.d_in, (d.flags & HOP_F_NORM_PROJ) ? 1 : 0, p.ln_proj_w, p.ln_proj_b, nullptr,

@@ -839,7 +839,7 @@ def test_pattern_preparation_on_tensor_cores(hf, D, P, T):
     (pg, og), (pf, of) = packs["gemm"], packs["fp32"]
     r_v = rel_l2(pg[1], vhat_oracle)
     print(f"D={D} P={P}: V^ (tensor cores) vs float64 oracle rel-L2 {r_v:.3e}; fp32 kernels {rel_l2(pf[1], vhat_oracle):.3e}")
-    assert r_v < 2e-6
+    assert r_v < 1e-6
     for i, name in enumerate(names):
         a, b = pg[i], pf[i]
         if name == "scratch" or a.numel() == 0:
@@ -852,7 +852,9 @@ def test_pattern_preparation_on_tensor_cores(hf, D, P, T):
             if name.endswith("lo"):                      # residuals: compare hi + lo through the sum they encode
                 continue
             diff = (ha - hb).abs()
-            tol = hb.abs().clamp_min(1e-3) * 2.0 ** -10
+            # one ulp of the word, or -- for elements far below the tensor's scale -- the fp32 difference of the two V^
+            # (a few 1e-7 of the rms), which the rounding merely passes through
+            tol = hb.abs().clamp_min(1e-2 * float(hb.pow(2).mean().sqrt())) * 2.0 ** -10
             bad = int((diff > tol).sum())
             print(f"  {name}: {int((diff > 0).sum())} of {ha.numel()} 16-bit words differ, {bad} by more than one ulp")
             assert bad == 0, name
