@@ -9,5 +9,6 @@ from ._loader import load_package
 
 _impl = load_package()
 HopfieldLayer = _impl.HopfieldLayer
+bottleneck_forward = _impl.bottleneck_forward      # HopVAE.forward's three retrievals + glue as one launch (evaluation)
 
-__all__ = ["HopfieldLayer"]
+__all__ = ["HopfieldLayer", "bottleneck_forward"]

@@ -10,10 +10,11 @@ it is imported through `hflayers` (the reference-facing package) or
 """
 from . import cabi
 from .layer import HopfieldLayer
-from . import ops, sharded
+from . import ops, sharded, chain
+from .chain import bottleneck_forward
 from .sharded import PatternShardedHopfield, shard_range, batch_parallel_rows
 from .ops import LayerSpec, HopfieldAssociation, prepare_patterns_op, retrieve_op, retrieve_backward_op, resolve_path
 
 __all__ = ["HopfieldLayer", "LayerSpec", "HopfieldAssociation", "prepare_patterns_op", "retrieve_op",
            "retrieve_backward_op", "resolve_path", "cabi", "ops", "sharded", "PatternShardedHopfield", "shard_range",
-           "batch_parallel_rows"]
+           "batch_parallel_rows", "chain", "bottleneck_forward"]

@@ -19,7 +19,7 @@ CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libhop_sm100.so")
 SOURCES = ["hop_api.cu", "hop_prep.cu", "hop_fwd_simt.cu", "hop_bwd_simt.cu", "hop_merge.cu", "hop_fwd_tc.cu",
-           "hop_repair.cu", "hop_bwd_tc.cu", "hop_gemm_tc.cu"]
+           "hop_repair.cu", "hop_bwd_tc.cu", "hop_gemm_tc.cu", "hop_chain.cu"]
 HEADERS = [os.path.join(CSRC, "hop_common.cuh"), os.path.join(CSRC, "hop_tc_ptx.cuh"),
            os.path.join(HERE, "..", "include", "hop_sm100.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

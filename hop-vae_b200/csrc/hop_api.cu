@@ -385,6 +385,25 @@ int hop_sm100_forward(const hop_desc* desc, const hop_params* params, const hop_
   return HOP_OK;
 }
 
+int hop_sm100_bottleneck_workspace_bytes(int32_t n_rows, size_t* bytes) {
+  if (!bytes || n_rows <= 0) HOP_FAIL(HOP_ERR_BAD_ARG, "bottleneck workspace: bytes is NULL or n_rows <= 0");
+  *bytes = chain_workspace_bytes(n_rows);
+  return HOP_OK;
+}
+
+int hop_sm100_bottleneck_forward(const hop_desc* descs, const hop_params* params, const hop_patterns* patterns,
+                                 int32_t num_levels, const float* z, float* emb, float* logits, float* idx_q,
+                                 float* emb_recon, float* mse, void* workspace, size_t workspace_bytes, void* stream) {
+  if (!descs || !params || !patterns) HOP_FAIL(HOP_ERR_BAD_ARG, "bottleneck: descs / params / patterns is NULL");
+  for (int l = 0; l < 3; ++l) HOP_TRY(validate_desc(descs + l));
+  HOP_TRY(device_info(nullptr));
+  if (num_levels < 2) HOP_FAIL(HOP_ERR_BAD_ARG, "bottleneck: num_levels must be >= 2");
+  if (!emb) HOP_FAIL(HOP_ERR_BAD_ARG, "bottleneck: emb is NULL");
+  if (!aligned16(z) || !aligned16(workspace)) HOP_FAIL(HOP_ERR_BAD_ALIGN, "bottleneck: z / workspace must be 16-byte aligned");
+  return launch_chain(descs, params, patterns, (float)(num_levels - 1), z, emb, logits, idx_q, emb_recon, mse, workspace,
+                      workspace_bytes, (cudaStream_t)stream);
+}
+
 int hop_sm100_repair_rows(const hop_desc* desc, const void* workspace, void* stream, int32_t* rows_out) {
   HOP_TRY(validate_desc(desc));
   if (!rows_out) HOP_FAIL(HOP_ERR_BAD_ARG, "rows_out is NULL");

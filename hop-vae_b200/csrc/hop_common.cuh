@@ -147,6 +147,12 @@ bool tc_precise_updates(int d, int update_steps, const TcTune& tune);
 size_t tc_forward_workspace(int n, int p, int d, int update_steps, const TcTune& tune);
 int launch_tc_forward(const TcPassArgs& a, cudaStream_t st);
 bool tc_supported(int h, int dv);
+// hop_chain.cu -- Hop-VAE's bottleneck (three retrievals + sigmoid / round / mse glue) as one launch, fp32
+size_t chain_workspace_bytes(int n);
+int chain_supported(const hop_desc* d3);
+int launch_chain(const hop_desc* d3, const hop_params* p3, const hop_patterns* pt3, float levels, const float* z,
+                 float* emb, float* logits, float* idx_q, float* emb_recon, float* mse, void* ws, size_t ws_bytes,
+                 cudaStream_t st);
 // hop_gemm_tc.cu -- C[M x N] = A[M x K] . B[N x K]^T (+ bias) on tcgen05, fp16 K-major operand packs, optional hi + lo pairs
 constexpr float kGemmLoScale = 2048.f;   // low halves of the GEMM's operand pairs are stored times 2^11
 struct TcGemmArgs {

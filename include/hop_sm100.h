@@ -248,6 +248,27 @@ int hop_sm100_backward(const hop_desc* desc, const hop_params* params,
                        const float* grad_out, const hop_grads* grads,
                        void* workspace, size_t workspace_bytes, void* stream);
 
+/* Hop-VAE's bottleneck as one launch (replaces the caller's
+ * glue around three HopfieldLayer.forward calls, HopVAE.py:255-272 and
+ * utils/__init__.py:51-55):
+ *   emb       = hopfield(z)                               (N, D)
+ *   logits    = embedding_to_index(emb)                   (N, I)
+ *   idx_q     = round(sigmoid(logits) * (num_levels - 1)) (N, I)  quantised levels
+ *   emb_recon = index_to_embedding(idx_q / (num_levels - 1))      (N, D)
+ *   mse       = mean((emb_recon - emb)^2)                 (1)     device scalar
+ * descs / params / patterns: arrays of 3 (hopfield, embedding_to_index,
+ * index_to_embedding), each prepared with hop_sm100_prepare_patterns on the
+ * fp32 path.  Forward only (evaluation; training keeps the three layer calls
+ * and their autograd).  Every output except emb and mse may be NULL.
+ * HOP_ERR_UNSUPPORTED unless all three layers have the Hop-VAE shape (static
+ * state / stored patterns, widths <= 64, I <= 4, update_steps == 0).          */
+int hop_sm100_bottleneck_workspace_bytes(int32_t n_rows, size_t* bytes);
+int hop_sm100_bottleneck_forward(const hop_desc* descs, const hop_params* params,
+                                 const hop_patterns* patterns, int32_t num_levels,
+                                 const float* z, float* emb, float* logits, float* idx_q,
+                                 float* emb_recon, float* mse,
+                                 void* workspace, size_t workspace_bytes, void* stream);
+
 /* Diagnostic of HOP_F_EXACT_ARGMAX: how many rows of the last forward run with
  * this descriptor (argmax != NULL) into this workspace failed the top-1 / top-2
  * certificate and were re-scored in fp32.  Waits for `stream`.  0 rows on the

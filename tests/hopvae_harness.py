@@ -124,6 +124,15 @@ class HopVAEHarness(nn.Module):
         return dict(emb=emb, logits=logits, idx=idx, emb_recon=emb_recon,
                     emb_recon_loss=F.mse_loss(emb_recon, emb))
 
+    def bottleneck_fused(self, z):
+        """The same bottleneck as ONE launch (this repository's `hflayers.bottleneck_forward`); the
+        patch a maintainer applies to HopVAE.forward for evaluation is in INTEGRATION.md."""
+        import hflayers
+        out = hflayers.bottleneck_forward(self.hopfield, self.embedding_to_index, self.index_to_embedding, z,
+                                          self.cfg.num_levels)
+        return dict(emb=out["emb"], logits=out["logits"], idx=out["idx"], emb_recon=out["emb_recon"],
+                    emb_recon_loss=out["emb_recon_loss"])
+
     def decode(self, emb):
         r = self.cfg.representation_dim
         e = emb.view(-1, r, r, self.cfg.embedding_dim).permute(0, 3, 1, 2).contiguous()
