@@ -27,9 +27,10 @@ _ws_cache: Dict[tuple, Tensor] = {}
 
 
 def bottleneck_forward(hopfield, embedding_to_index, index_to_embedding, z: Tensor, num_levels: int,
-                       want_logits: bool = True, want_recon: bool = True) -> Dict[str, Tensor]:
-    """z (..., D) float32 CUDA -> dict(emb, logits, idx_q, idx, emb_recon, emb_recon_loss) with the reference's shapes
-    (leading dimensions of z kept).  `idx_q` are the integer levels the prior is fitted on (HopVAE.py:279-283)."""
+                       want_logits: bool = True, want_recon: bool = True, want_idx: bool = False) -> Dict[str, Tensor]:
+    """z (..., D) float32 CUDA -> dict(emb, logits, idx_q, emb_recon, emb_recon_loss[, idx]) with the reference's shapes
+    (leading dimensions of z kept).  `idx_q` are the integer levels the prior is fitted on (HopVAE.py:279-283);
+    `idx` = idx_q / (num_levels - 1) costs one more (elementwise) launch and is only built when asked for."""
     import ctypes as C
     layers = (hopfield, embedding_to_index, index_to_embedding)
     if torch.is_grad_enabled() and (z.requires_grad or any(p.requires_grad for l in layers for p in l.parameters())):
@@ -72,8 +73,9 @@ def bottleneck_forward(hopfield, embedding_to_index, index_to_embedding, z: Tens
                                                     cabi.ptr(logits), cabi.ptr(idx_q), cabi.ptr(recon), cabi.ptr(mse),
                                                     cabi.ptr(ws), int(need.value), _stream(dev)),
                    "hop_sm100_bottleneck_forward")
-    out = dict(emb=emb.reshape(*lead, d_emb), idx_q=idx_q.reshape(*lead, d_idx),
-               idx=(idx_q / float(num_levels - 1)).reshape(*lead, d_idx), emb_recon_loss=mse)
+    out = dict(emb=emb.reshape(*lead, d_emb), idx_q=idx_q.reshape(*lead, d_idx), emb_recon_loss=mse)
+    if want_idx:
+        out["idx"] = (idx_q / float(num_levels - 1)).reshape(*lead, d_idx)
     if logits is not None:
         out["logits"] = logits.reshape(*lead, d_idx)
     if recon is not None:

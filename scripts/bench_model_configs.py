@@ -108,6 +108,22 @@ for name, cfg in (("mnist28", H.MNIST_28), ("ffhq32", H.FFHQ_32), ("ffhq64", H.F
         res["us_fwd_ours_graph"] = timed(graphed(fwd(dut)))
     except Exception as e:  # noqa: BLE001
         res["us_fwd_ours_graph"] = f"capture failed: {type(e).__name__}"
+    # the same bottleneck as ONE launch (hop_chain.cu)
+    def fused():
+        with torch.no_grad():
+            hflayers.bottleneck_forward(dut.hopfield, dut.embedding_to_index, dut.index_to_embedding, z, cfg["num_levels"])
+    with torch.no_grad():
+        c = dut.bottleneck_fused(z)
+    res["fused_parity_rel_l2_emb"] = float((c["emb"] - b["emb"]).norm() / b["emb"].norm())
+    res["fused_loss_vs_eager"] = [float(c["emb_recon_loss"]), float(b["emb_recon_loss"])]
+    l0 = impl.cabi.launch_count()
+    fused()
+    res["launches_fwd_fused"] = impl.cabi.launch_count() - l0
+    res["us_fwd_fused"] = timed(fused)
+    try:
+        res["us_fwd_fused_graph"] = timed(graphed(fused))
+    except Exception as e:  # noqa: BLE001
+        res["us_fwd_fused_graph"] = f"capture failed: {type(e).__name__}"
     for layer in (ref.hopfield, ref.embedding_to_index, ref.index_to_embedding):
         layer.faithful = True
     res["us_fwd_eager_upstream_shape"] = timed(fwd(ref))

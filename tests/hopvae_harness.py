@@ -129,7 +129,7 @@ class HopVAEHarness(nn.Module):
         patch a maintainer applies to HopVAE.forward for evaluation is in INTEGRATION.md."""
         import hflayers
         out = hflayers.bottleneck_forward(self.hopfield, self.embedding_to_index, self.index_to_embedding, z,
-                                          self.cfg.num_levels)
+                                          self.cfg.num_levels, want_idx=True)
         return dict(emb=out["emb"], logits=out["logits"], idx=out["idx"], emb_recon=out["emb_recon"],
                     emb_recon_loss=out["emb_recon_loss"])
 
