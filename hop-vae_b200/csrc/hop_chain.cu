@@ -9,15 +9,24 @@
 //
 // for the reference's sizes (P = 512 patterns per layer, 2k .. 9k latent rows per batch), where the three layers are
 // launch- and latency-bound as separate kernels (88 / 105 / 152 us per bottleneck under a CUDA graph at configs 1 / 2 / 3,
-// profiles/r01_model_configs.jsonl).  A CTA of 256 threads owns BM = 16 RM latent rows and walks them through all three
-// layers: LN_q + beta in place, the flash-style association against 64-pattern tiles of that layer's K^ / V^ (cp.async
-// double buffered, exact fp32 FFMA, the arithmetic of hop_fwd_simt.cu), the out-projection, the glue -- the row tile
-// never leaves shared memory between layers.  The squared error is reduced per CTA and the last CTA to finish adds
-// the partials in CTA order (deterministic) and writes the mean.
+// profiles/r01_model_configs.jsonl).  A cluster of S CTAs (256 threads each) owns BM = 64 latent rows and walks them
+// through all three layers: LN_q + beta in place, the flash-style association against 64-pattern tiles of that layer's
+// K^ / V^ (cp.async double buffered, exact fp32 FFMA, the arithmetic of hop_fwd_simt.cu), the out-projection, the glue --
+// the row tile never leaves shared memory between layers.  2,048 rows are only 32 such tiles, so inside a layer the S
+// CTAs of a cluster split the PATTERN axis: each runs its share of the tiles on the same rows, leaves its un-normalised
+// partial (O, max, sum) in its own shared memory, and after a cluster barrier every CTA merges all partials out of its
+// peers' shared memory (DSMEM) in rank order -- so all S CTAs hold the identical layer output and go on to the next
+// layer without exchanging anything else.  (A 16-row tile per CTA instead -- first version -- is shared-memory bound:
+// one K^ load per four FMAs, 100 us at 2,048 rows; 4 x 4 register tiles need 64 rows.)  The squared error is reduced per
+// cluster by its rank-0 CTA and the last one to finish adds the partials in tile order (deterministic) and writes the mean.
 //
 // Inference / evaluation only (no autograd state is saved); every layer is the Hop-VAE shape: static state and stored
 // patterns (H = D_in), pattern projection D_in -> D_in, out-projection.  Widths up to 64.
+#include <cooperative_groups.h>
+
 #include "hop_common.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace hop {
 
@@ -73,18 +82,21 @@ __device__ __forceinline__ void tile_in(float* dst, const float* src, int r0, in
 // One retrieval of the row tile in X (BM x HS, this layer's raw input in columns [0, h)); leaves the layer output in
 // X (columns [0, dout), zeros up to 64) and, when asked, in global memory.  HF = association width padded to 4.
 template <int RM, int HF>
-__device__ __forceinline__ void chain_layer(const ChainLayer& L, float* X, float* Os, float* Ps, float* K0, float* B0,
-                                            int row0, int n) {
+__device__ __forceinline__ void chain_layer(const ChainLayer& L, float* X, float* Os, float* Ps, float* St, float* K0,
+                                            float* B0, int row0, int n, int rank, int splits, bool writer) {
   constexpr int BM = 16 * RM;
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4, warp = tid >> 5, lane = tid & 31;
   const int dv4 = (L.dv + 3) & ~3;
-  const int n_tiles = (L.p + BP - 1) / BP;
+  const int n_tiles_all = (L.p + BP - 1) / BP;
+  const int per = (n_tiles_all + splits - 1) / splits;
+  const int t_begin = min(rank * per, n_tiles_all), t_end = min(t_begin + per, n_tiles_all);
+  const int n_tiles = t_end - t_begin;        // this CTA's share of the pattern tiles (local index 0 .. n_tiles)
   auto issue = [&](int t) {
-    tile_in(K0 + (t & 1) * BP * HS, L.khat, t * BP, BP, L.p, L.h, HF, HS);
-    tile_in(B0 + (t & 1) * BP * DS, L.vhat, t * BP, BP, L.p, L.dv, DS, DS);
+    tile_in(K0 + (t & 1) * BP * HS, L.khat, (t_begin + t) * BP, BP, L.p, L.h, HF, HS);
+    tile_in(B0 + (t & 1) * BP * DS, L.vhat, (t_begin + t) * BP, BP, L.p, L.dv, DS, DS);
     cp_commit();
   };
-  issue(0);                                   // overlaps the LayerNorm below
+  if (n_tiles > 0) issue(0);                  // overlaps the LayerNorm below
   // LN_q + beta in place (a warp per row)
   for (int r = warp; r < BM; r += NT / 32) {
     float* qr = X + r * HS;
@@ -140,7 +152,7 @@ __device__ __forceinline__ void chain_layer(const ChainLayer& L, float* X, float
         }
       }
     }
-    const int p0 = t * BP;
+    const int p0 = (t_begin + t) * BP;
 #pragma unroll
     for (int i = 0; i < RM; ++i) {
       float tmax = -INFINITY;
@@ -188,18 +200,40 @@ __device__ __forceinline__ void chain_layer(const ChainLayer& L, float* X, float
       }
     }
   }
-  // normalised read-out -> Os; Wo -> the first K buffer (both K buffers are free: the last tile's scores are done)
+  // un-normalised partial (O, max, sum) of this CTA's pattern range -> own shared memory
+  __syncthreads();                            // (an empty range never entered the loop: X readers / LN writers meet here)
 #pragma unroll
   for (int i = 0; i < RM; ++i) {
-    const float inv = 1.f / l_run[i];
-    *reinterpret_cast<float4*>(Os + (ty * RM + i) * HS + 4 * tx) =
-        make_float4(o[i][0] * inv, o[i][1] * inv, o[i][2] * inv, o[i][3] * inv);
+    const int r = ty * RM + i;
+    *reinterpret_cast<float4*>(Os + r * HS + 4 * tx) = make_float4(o[i][0], o[i][1], o[i][2], o[i][3]);
+    if (tx == 0) { St[r] = m_run[i]; St[BM + r] = l_run[i]; }
   }
+  cg::cluster_group cluster = cg::this_cluster();
+  cluster.sync();
+  // Wo -> the first K buffer (both K buffers are free: the last tile's scores are done); merge of all partials in rank
+  // order -> Ps (free as well), the same in every CTA of the cluster
   for (int idx = tid; idx < BP * DS; idx += NT) {
     const int oc = idx >> 6, j = idx & 63;
     K0[oc * HS + j] = (oc < L.dout && j < L.dv) ? __ldg(L.wo + (size_t)oc * L.dv + j) : 0.f;
   }
-  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < RM; ++i) {
+    const int r = ty * RM + i;
+    float M = -INFINITY;
+    for (int sp = 0; sp < splits; ++sp) M = fmaxf(M, cluster.map_shared_rank(St, sp)[r]);
+    float Lsum = 0.f;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int sp = 0; sp < splits; ++sp) {
+      const float* pst = cluster.map_shared_rank(St, sp);
+      const float w = __expf(pst[r] - M);                       // exp(-inf) = 0 for an empty range
+      Lsum = fmaf(w, pst[BM + r], Lsum);
+      const float4 v = *reinterpret_cast<const float4*>(cluster.map_shared_rank(Os, sp) + r * HS + 4 * tx);
+      acc.x = fmaf(w, v.x, acc.x); acc.y = fmaf(w, v.y, acc.y); acc.z = fmaf(w, v.z, acc.z); acc.w = fmaf(w, v.w, acc.w);
+    }
+    const float inv = 1.f / Lsum;
+    *reinterpret_cast<float4*>(Ps + r * HS + 4 * tx) = make_float4(acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv);
+  }
+  cluster.sync();                             // peers are done with this CTA's partials; Ps and Wo are complete
   float acc[RM][4];
 #pragma unroll
   for (int i = 0; i < RM; ++i)
@@ -208,7 +242,7 @@ __device__ __forceinline__ void chain_layer(const ChainLayer& L, float* X, float
   for (int k = 0; k < dv4; k += 4) {
     float4 ov[RM];
 #pragma unroll
-    for (int i = 0; i < RM; ++i) ov[i] = *reinterpret_cast<const float4*>(Os + (ty * RM + i) * HS + k);
+    for (int i = 0; i < RM; ++i) ov[i] = *reinterpret_cast<const float4*>(Ps + (ty * RM + i) * HS + k);
 #pragma unroll
     for (int b = 0; b < 4; ++b) {
       const float4 ww = *reinterpret_cast<const float4*>(K0 + (tx + 16 * b) * HS + k);
@@ -229,50 +263,55 @@ __device__ __forceinline__ void chain_layer(const ChainLayer& L, float* X, float
       X[(ty * RM + i) * HS + oc] = oc < L.dout ? acc[i][b] + (L.bo ? __ldg(L.bo + oc) : 0.f) : 0.f;
     }
   __syncthreads();
-  if (L.out != nullptr) {
+  if (L.out != nullptr && writer) {
     for (int idx = tid; idx < BM * L.dout; idx += NT) {
       const int r = idx / L.dout, c = idx - r * L.dout;
       if (row0 + r < n) L.out[(size_t)(row0 + r) * L.dout + c] = X[r * HS + c];
     }
-    __syncthreads();                          // the caller rewrites X next
   }
+  __syncthreads();                            // the caller rewrites X next
 }
 
 template <int RM>
-__global__ void __launch_bounds__(NT) hop_chain_kernel(const __grid_constant__ ChainArgs a) {
+__global__ void __launch_bounds__(NT) hop_chain_kernel(const __grid_constant__ ChainArgs a, int splits) {
   extern __shared__ __align__(16) float smem[];
   constexpr int BM = 16 * RM;
   float* X = smem;                    // the row tile: input / output of the current layer
   float* E = X + BM * HS;             // emb, kept for the squared error
-  float* Os = E + BM * HS;
-  float* Ps = Os + BM * HS;
-  float* K0 = Ps + BM * HS;           // two K^ tiles
+  float* Os = E + BM * HS;            // this CTA's partial read-out (read by the whole cluster)
+  float* Ps = Os + BM * HS;           // probability tile; merged read-out behind the tile loop
+  float* St = Ps + BM * HS;           // this CTA's partial (max, sum) per row
+  float* K0 = St + 2 * BM;            // two K^ tiles
   float* B0 = K0 + 2 * BP * HS;       // two read-out tiles
   __shared__ float red[NT / 32];
   __shared__ bool is_last;
   const int tid = threadIdx.x;
-  const int row0 = blockIdx.x * BM;
+  const int rank = (int)cg::this_cluster().block_rank();
+  const int tile = blockIdx.x / splits, n_row_tiles = gridDim.x / splits;
+  const int row0 = tile * BM;
+  const bool writer = rank == 0;      // every CTA of a cluster holds the same results; one of them stores them
   const int d0 = a.layer[0].h;
 
   tile_in(X, a.z, row0, BM, a.n, d0, 64, HS);
   cp_commit();
   cp_wait<0>();
   __syncthreads();
-  chain_layer<RM, 64>(a.layer[0], X, Os, Ps, K0, B0, row0, a.n);                 // hopfield
+  chain_layer<RM, 64>(a.layer[0], X, Os, Ps, St, K0, B0, row0, a.n, rank, splits, writer);      // hopfield
   for (int idx = tid; idx < BM * 64; idx += NT) E[(idx >> 6) * HS + (idx & 63)] = X[(idx >> 6) * HS + (idx & 63)];
   __syncthreads();
-  chain_layer<RM, 64>(a.layer[1], X, Os, Ps, K0, B0, row0, a.n);                 // embedding_to_index
+  chain_layer<RM, 64>(a.layer[1], X, Os, Ps, St, K0, B0, row0, a.n, rank, splits, writer);      // embedding_to_index
   // sigmoid -> round to the level grid (forward of utils.straight_through_round) -> back to [0, 1]
   const int di = a.layer[1].dout;
   for (int idx = tid; idx < BM * di; idx += NT) {
     const int r = idx / di, c = idx - r * di;
     const float sg = 1.f / (1.f + expf(-X[r * HS + c]));
     const float q = rintf(sg * a.levels);
-    if (a.idx_q != nullptr && row0 + r < a.n) a.idx_q[(size_t)(row0 + r) * di + c] = q;
+    if (a.idx_q != nullptr && writer && row0 + r < a.n) a.idx_q[(size_t)(row0 + r) * di + c] = q;
     X[r * HS + c] = q / a.levels;
   }
   __syncthreads();
-  chain_layer<RM, 4>(a.layer[2], X, Os, Ps, K0, B0, row0, a.n);                  // index_to_embedding
+  chain_layer<RM, 4>(a.layer[2], X, Os, Ps, St, K0, B0, row0, a.n, rank, splits, writer);       // index_to_embedding
+  if (!writer) return;
   // squared error of this tile's valid rows
   const int de = a.layer[2].dout;
   float sq = 0.f;
@@ -289,15 +328,15 @@ __global__ void __launch_bounds__(NT) hop_chain_kernel(const __grid_constant__ C
   if (tid == 0) {
     float tot = 0.f;
     for (int w = 0; w < NT / 32; ++w) tot += red[w];
-    a.partial[blockIdx.x] = tot;
+    a.partial[tile] = tot;
     __threadfence();
-    is_last = atomicAdd(a.done, 1u) == gridDim.x - 1;
+    is_last = atomicAdd(a.done, 1u) == (unsigned)n_row_tiles - 1;
   }
   __syncthreads();
   if (is_last && tid < 32) {
     __threadfence();
-    float tot = 0.f;                  // CTA order, fixed lane assignment: the same sum on every run
-    for (unsigned i = tid; i < gridDim.x; i += 32) tot += __ldcg(a.partial + i);
+    float tot = 0.f;                  // tile order, fixed lane assignment: the same sum on every run
+    for (int i = tid; i < n_row_tiles; i += 32) tot += __ldcg(a.partial + i);
     tot = warp_sum(tot);
     if (tid == 0) {
       *a.mse = tot / ((float)a.n * (float)de);
@@ -306,22 +345,34 @@ __global__ void __launch_bounds__(NT) hop_chain_kernel(const __grid_constant__ C
   }
 }
 
-template <int RM>
-int launch_chain_rm(const ChainArgs& a, cudaStream_t st) {
-  constexpr int BM = 16 * RM;
-  const size_t smem = (size_t)(4 * BM * HS + 2 * BP * HS + 2 * BP * DS) * sizeof(float);
-  auto* kern = hop_chain_kernel<RM>;
-  HOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kern<<<(a.n + BM - 1) / BM, NT, smem, st>>>(a);
-  HOP_LAUNCH_CHECK("hop_chain_kernel");
-  return HOP_OK;
+constexpr int kChainRM = 4;           // 64 rows per cluster: 4 x 4 register tiles
+
+// pattern splits per row tile: fill the SMs once, never more CTAs than that (137 KB of shared memory: one CTA per SM)
+int chain_splits(int n) {
+  const int tiles = (n + 16 * kChainRM - 1) / (16 * kChainRM);
+  int s = 1;
+  while (s < 8 && tiles * s * 2 <= num_sms()) s *= 2;
+  return s;
 }
 
-int chain_rows_per_cta(int n) {
-  const int sms = num_sms();
-  if ((n + 63) / 64 >= 2 * sms) return 64;
-  if ((n + 31) / 32 >= sms) return 32;
-  return 16;
+int launch_chain_inst(const ChainArgs& a, cudaStream_t st) {
+  constexpr int BM = 16 * kChainRM;
+  const size_t smem = (size_t)(4 * BM * HS + 2 * BM + 2 * BP * HS + 2 * BP * DS) * sizeof(float);
+  auto* kern = hop_chain_kernel<kChainRM>;
+  HOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int splits = chain_splits(a.n);
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)((a.n + BM - 1) / BM * splits));
+  cfg.blockDim = dim3(NT);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = (unsigned)splits; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  HOP_CUDA(cudaLaunchKernelEx(&cfg, kern, a, splits));
+  HOP_LAUNCH_CHECK("hop_chain_kernel");
+  return HOP_OK;
 }
 
 }  // namespace
@@ -365,10 +416,7 @@ int launch_chain(const hop_desc* d, const hop_params* p, const hop_patterns* pt,
   a.partial = reinterpret_cast<float*>(static_cast<char*>(ws) + 256);
   a.mse = mse;
   HOP_CUDA(cudaMemsetAsync(a.done, 0, sizeof(uint32_t), st));
-  const int bm = chain_rows_per_cta(n);
-  if (bm == 64) return launch_chain_rm<4>(a, st);
-  if (bm == 32) return launch_chain_rm<2>(a, st);
-  return launch_chain_rm<1>(a, st);
+  return launch_chain_inst(a, st);
 }
 
 }  // namespace hop
