@@ -216,22 +216,48 @@ __device__ __forceinline__ void chain_layer(const ChainLayer& L, float* X, float
     const int oc = idx >> 6, j = idx & 63;
     K0[oc * HS + j] = (oc < L.dout && j < L.dv) ? __ldg(L.wo + (size_t)oc * L.dv + j) : 0.f;
   }
+  // (every DSMEM load of a phase is issued before the first use: a chain of dependent remote loads costs ~1 us each)
+  {
+    constexpr int kMaxSplits = 8;
+    const float* pst[kMaxSplits];
+    const float* pos[kMaxSplits];
 #pragma unroll
-  for (int i = 0; i < RM; ++i) {
-    const int r = ty * RM + i;
-    float M = -INFINITY;
-    for (int sp = 0; sp < splits; ++sp) M = fmaxf(M, cluster.map_shared_rank(St, sp)[r]);
-    float Lsum = 0.f;
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int sp = 0; sp < splits; ++sp) {
-      const float* pst = cluster.map_shared_rank(St, sp);
-      const float w = __expf(pst[r] - M);                       // exp(-inf) = 0 for an empty range
-      Lsum = fmaf(w, pst[BM + r], Lsum);
-      const float4 v = *reinterpret_cast<const float4*>(cluster.map_shared_rank(Os, sp) + r * HS + 4 * tx);
-      acc.x = fmaf(w, v.x, acc.x); acc.y = fmaf(w, v.y, acc.y); acc.z = fmaf(w, v.z, acc.z); acc.w = fmaf(w, v.w, acc.w);
+    for (int sp = 0; sp < kMaxSplits; ++sp) {
+      const int src = sp < splits ? sp : rank;                   // (unused slots alias this CTA: weight 0 below)
+      pst[sp] = cluster.map_shared_rank(St, src);
+      pos[sp] = cluster.map_shared_rank(Os, src);
     }
-    const float inv = 1.f / Lsum;
-    *reinterpret_cast<float4*>(Ps + r * HS + 4 * tx) = make_float4(acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv);
+    float ms[RM][kMaxSplits], ls[RM][kMaxSplits];
+#pragma unroll
+    for (int i = 0; i < RM; ++i)
+#pragma unroll
+      for (int sp = 0; sp < kMaxSplits; ++sp) {
+        const int r = ty * RM + i;
+        ms[i][sp] = sp < splits ? pst[sp][r] : -INFINITY;
+        ls[i][sp] = sp < splits ? pst[sp][BM + r] : 0.f;
+      }
+#pragma unroll
+    for (int i = 0; i < RM; ++i) {
+      const int r = ty * RM + i;
+      float M = -INFINITY;
+#pragma unroll
+      for (int sp = 0; sp < kMaxSplits; ++sp) M = fmaxf(M, ms[i][sp]);
+      float4 v[kMaxSplits];
+#pragma unroll
+      for (int sp = 0; sp < kMaxSplits; ++sp)
+        v[sp] = sp < splits ? *reinterpret_cast<const float4*>(pos[sp] + r * HS + 4 * tx) : make_float4(0.f, 0.f, 0.f, 0.f);
+      float Lsum = 0.f;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int sp = 0; sp < kMaxSplits; ++sp) {                  // rank order: the same sum in every CTA
+        const float w = __expf(ms[i][sp] - M);                   // exp(-inf) = 0 for an empty range / unused slot
+        Lsum = fmaf(w, ls[i][sp], Lsum);
+        acc.x = fmaf(w, v[sp].x, acc.x); acc.y = fmaf(w, v[sp].y, acc.y);
+        acc.z = fmaf(w, v[sp].z, acc.z); acc.w = fmaf(w, v[sp].w, acc.w);
+      }
+      const float inv = 1.f / Lsum;
+      *reinterpret_cast<float4*>(Ps + r * HS + 4 * tx) = make_float4(acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv);
+    }
   }
   cluster.sync();                             // peers are done with this CTA's partials; Ps and Wo are complete
   float acc[RM][4];
