@@ -50,7 +50,7 @@ def bottleneck_forward(hopfield, embedding_to_index, index_to_embedding, z: Tens
         prepared = layer._prepared(pack, spec, cabi.PATH_FP32_SIMT)      # fp32 K^ / V^ (cached per parameter version)
         keep.append((pack, prepared))
         descs[i] = _desc(spec.flags, cabi.PATH_FP32_SIMT, n, layer.quantity, spec.d_in, spec.d_assoc, spec.d_v,
-                         max(spec.d_out, 1), spec.update_steps, spec.beta, spec.ln_eps)
+                         max(spec.d_out, 1), spec.update_steps, spec.beta, spec.ln_eps, tune_splits=spec.tune_splits)
         q = {k: (None if pack[k] is None else pack[k].detach().contiguous()) for k in _QUERY_KEYS}
         keep.append(q)
         params[i] = cabi.HopParams(**{k: cabi.ptr(v) for k, v in q.items()})

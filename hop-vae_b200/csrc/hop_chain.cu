@@ -91,12 +91,13 @@ __device__ __forceinline__ void chain_layer(const ChainLayer& L, float* X, float
   const int per = (n_tiles_all + splits - 1) / splits;
   const int t_begin = min(rank * per, n_tiles_all), t_end = min(t_begin + per, n_tiles_all);
   const int n_tiles = t_end - t_begin;        // this CTA's share of the pattern tiles (local index 0 .. n_tiles)
-  auto issue = [&](int t) {
-    tile_in(K0 + (t & 1) * BP * HS, L.khat, (t_begin + t) * BP, BP, L.p, L.h, HF, HS);
+  // one K^ tile buffer (tile t+1 is fetched behind the scores of tile t, under its read-out), two read-out buffers
+  auto issue_k = [&](int t) { tile_in(K0, L.khat, (t_begin + t) * BP, BP, L.p, L.h, HF, HS); cp_commit(); };
+  auto issue_b = [&](int t) {
     tile_in(B0 + (t & 1) * BP * DS, L.vhat, (t_begin + t) * BP, BP, L.p, L.dv, DS, DS);
     cp_commit();
   };
-  if (n_tiles > 0) issue(0);                  // overlaps the LayerNorm below
+  if (n_tiles > 0) { issue_k(0); issue_b(0); }   // overlap the LayerNorm below
   // LN_q + beta in place (a warp per row)
   for (int r = warp; r < BM; r += NT / 32) {
     float* qr = X + r * HS;
@@ -125,9 +126,9 @@ __device__ __forceinline__ void chain_layer(const ChainLayer& L, float* X, float
     for (int e = 0; e < 4; ++e) o[i][e] = 0.f;
   }
   for (int t = 0; t < n_tiles; ++t) {
-    __syncthreads();                          // the other buffer's readers are done; X is normalised
-    if (t + 1 < n_tiles) { issue(t + 1); cp_wait<1>(); } else { cp_wait<0>(); }
-    const float* Ks = K0 + (t & 1) * BP * HS;
+    __syncthreads();                          // the other read-out buffer's readers are done; X is normalised
+    if (t + 1 < n_tiles) { issue_b(t + 1); cp_wait<1>(); } else { cp_wait<0>(); }   // K(t), B(t) have landed
+    const float* Ks = K0;
     const float* Bs = B0 + (t & 1) * BP * DS;
     __syncthreads();
     float s[RM][4];
@@ -140,17 +141,26 @@ __device__ __forceinline__ void chain_layer(const ChainLayer& L, float* X, float
       float4 q[RM];
 #pragma unroll
       for (int i = 0; i < RM; ++i) q[i] = *reinterpret_cast<const float4*>(X + (ty * RM + i) * HS + k);
+      float4 kk[4];
 #pragma unroll
-      for (int b = 0; b < 4; ++b) {
-        const float4 kk = *reinterpret_cast<const float4*>(Ks + (tx + 16 * b) * HS + k);
+      for (int b = 0; b < 4; ++b) kk[b] = *reinterpret_cast<const float4*>(Ks + (tx + 16 * b) * HS + k);
+      // sixteen independent accumulators between two FMAs on the same one
 #pragma unroll
-        for (int i = 0; i < RM; ++i) {
-          s[i][b] = fmaf(q[i].x, kk.x, s[i][b]);
-          s[i][b] = fmaf(q[i].y, kk.y, s[i][b]);
-          s[i][b] = fmaf(q[i].z, kk.z, s[i][b]);
-          s[i][b] = fmaf(q[i].w, kk.w, s[i][b]);
-        }
-      }
+      for (int b = 0; b < 4; ++b)
+#pragma unroll
+        for (int i = 0; i < RM; ++i) s[i][b] = fmaf(q[i].x, kk[b].x, s[i][b]);
+#pragma unroll
+      for (int b = 0; b < 4; ++b)
+#pragma unroll
+        for (int i = 0; i < RM; ++i) s[i][b] = fmaf(q[i].y, kk[b].y, s[i][b]);
+#pragma unroll
+      for (int b = 0; b < 4; ++b)
+#pragma unroll
+        for (int i = 0; i < RM; ++i) s[i][b] = fmaf(q[i].z, kk[b].z, s[i][b]);
+#pragma unroll
+      for (int b = 0; b < 4; ++b)
+#pragma unroll
+        for (int i = 0; i < RM; ++i) s[i][b] = fmaf(q[i].w, kk[b].w, s[i][b]);
     }
     const int p0 = (t_begin + t) * BP;
 #pragma unroll
@@ -179,7 +189,8 @@ __device__ __forceinline__ void chain_layer(const ChainLayer& L, float* X, float
 #pragma unroll
       for (int e = 0; e < 4; ++e) o[i][e] *= corr;
     }
-    __syncthreads();
+    __syncthreads();                          // scores of tile t are done: the K buffer is free
+    if (t + 1 < n_tiles) issue_k(t + 1);
     if (4 * tx < dv4) {                       // (index_to_embedding reads out 3 columns: one thread per row group)
       for (int j = 0; j < BP; j += 4) {
         float4 pv[RM];
@@ -299,16 +310,17 @@ __device__ __forceinline__ void chain_layer(const ChainLayer& L, float* X, float
 }
 
 template <int RM>
-__global__ void __launch_bounds__(NT) hop_chain_kernel(const __grid_constant__ ChainArgs a, int splits) {
+__global__ void __launch_bounds__(NT, 2) hop_chain_kernel(const __grid_constant__ ChainArgs a, int splits) {
   extern __shared__ __align__(16) float smem[];
   constexpr int BM = 16 * RM;
   float* X = smem;                    // the row tile: input / output of the current layer
   float* E = X + BM * HS;             // emb, kept for the squared error
-  float* Os = E + BM * HS;            // this CTA's partial read-out (read by the whole cluster)
-  float* Ps = Os + BM * HS;           // probability tile; merged read-out behind the tile loop
+  float* Ps = E + BM * HS;            // probability tile; merged read-out behind the tile loop
   float* St = Ps + BM * HS;           // this CTA's partial (max, sum) per row
-  float* K0 = St + 2 * BM;            // two K^ tiles
-  float* B0 = K0 + 2 * BP * HS;       // two read-out tiles
+  float* K0 = St + 2 * BM;            // one K^ tile
+  float* B0 = K0 + BP * HS;           // two read-out tiles
+  float* Os = B0;                     // this CTA's partial read-out (read by the whole cluster), behind the tile loop
+  static_assert(BM * HS <= 2 * BP * DS, "the partial read-out must fit the read-out tile buffers");
   __shared__ float red[NT / 32];
   __shared__ bool is_last;
   const int tid = threadIdx.x;
@@ -322,10 +334,14 @@ __global__ void __launch_bounds__(NT) hop_chain_kernel(const __grid_constant__ C
   cp_commit();
   cp_wait<0>();
   __syncthreads();
-  chain_layer<RM, 64>(a.layer[0], X, Os, Ps, St, K0, B0, row0, a.n, rank, splits, writer);      // hopfield
-  for (int idx = tid; idx < BM * 64; idx += NT) E[(idx >> 6) * HS + (idx & 63)] = X[(idx >> 6) * HS + (idx & 63)];
-  __syncthreads();
-  chain_layer<RM, 64>(a.layer[1], X, Os, Ps, St, K0, B0, row0, a.n, rank, splits, writer);      // embedding_to_index
+#pragma unroll 1
+  for (int l = 0; l < 2; ++l) {       // hopfield, embedding_to_index: one copy of the 64-wide layer code
+    chain_layer<RM, 64>(a.layer[l], X, Os, Ps, St, K0, B0, row0, a.n, rank, splits, writer);
+    if (l == 0) {
+      for (int idx = tid; idx < BM * 64; idx += NT) E[(idx >> 6) * HS + (idx & 63)] = X[(idx >> 6) * HS + (idx & 63)];
+      __syncthreads();
+    }
+  }
   // sigmoid -> round to the level grid (forward of utils.straight_through_round) -> back to [0, 1]
   const int di = a.layer[1].dout;
   for (int idx = tid; idx < BM * di; idx += NT) {
@@ -373,20 +389,21 @@ __global__ void __launch_bounds__(NT) hop_chain_kernel(const __grid_constant__ C
 
 constexpr int kChainRM = 4;           // 64 rows per cluster: 4 x 4 register tiles
 
-// pattern splits per row tile: fill the SMs once, never more CTAs than that (137 KB of shared memory: one CTA per SM)
+// pattern splits per row tile: up to two CTAs per SM (103 KB of shared memory, 128 registers x 256 threads each)
 int chain_splits(int n) {
   const int tiles = (n + 16 * kChainRM - 1) / (16 * kChainRM);
   int s = 1;
-  while (s < 8 && tiles * s * 2 <= num_sms()) s *= 2;
+  while (s < 8 && tiles * s * 2 <= 2 * num_sms()) s *= 2;
   return s;
 }
 
-int launch_chain_inst(const ChainArgs& a, cudaStream_t st) {
+int launch_chain_inst(const ChainArgs& a, int tune_splits, cudaStream_t st) {
   constexpr int BM = 16 * kChainRM;
-  const size_t smem = (size_t)(4 * BM * HS + 2 * BM + 2 * BP * HS + 2 * BP * DS) * sizeof(float);
+  const size_t smem = (size_t)(3 * BM * HS + 2 * BM + BP * HS + 2 * BP * DS) * sizeof(float);
   auto* kern = hop_chain_kernel<kChainRM>;
   HOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int splits = chain_splits(a.n);
+  const int splits = (tune_splits == 1 || tune_splits == 2 || tune_splits == 4 || tune_splits == 8) ? tune_splits
+                                                                                                  : chain_splits(a.n);
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3((unsigned)((a.n + BM - 1) / BM * splits));
   cfg.blockDim = dim3(NT);
@@ -442,7 +459,7 @@ int launch_chain(const hop_desc* d, const hop_params* p, const hop_patterns* pt,
   a.partial = reinterpret_cast<float*>(static_cast<char*>(ws) + 256);
   a.mse = mse;
   HOP_CUDA(cudaMemsetAsync(a.done, 0, sizeof(uint32_t), st));
-  return launch_chain_inst(a, st);
+  return launch_chain_inst(a, d[0].tune_splits, st);      // (hop_desc.tune_splits of the first layer: experiments)
 }
 
 }  // namespace hop
