@@ -191,7 +191,25 @@ __device__ __forceinline__ void chain_layer(const ChainLayer& L, float* X, float
     }
     __syncthreads();                          // scores of tile t are done: the K buffer is free
     if (t + 1 < n_tiles) issue_k(t + 1);
-    if (4 * tx < dv4) {                       // (index_to_embedding reads out 3 columns: one thread per row group)
+    if (HF == 4 && dv4 == 4) {
+      // index_to_embedding reads out <= 4 columns: the 16 threads of a row group split the 64 PATTERNS of the tile
+      // (4 each) instead of the columns and keep private partial sums, reduced across the group once per layer
+      float4 pv[RM];
+#pragma unroll
+      for (int i = 0; i < RM; ++i) pv[i] = *reinterpret_cast<const float4*>(Ps + (ty * RM + i) * HS + 4 * tx);
+#pragma unroll
+      for (int jj = 0; jj < 4; ++jj) {
+        const float4 v = *reinterpret_cast<const float4*>(Bs + (4 * tx + jj) * DS);
+#pragma unroll
+        for (int i = 0; i < RM; ++i) {
+          const float pr = jj == 0 ? pv[i].x : jj == 1 ? pv[i].y : jj == 2 ? pv[i].z : pv[i].w;
+          o[i][0] = fmaf(pr, v.x, o[i][0]);
+          o[i][1] = fmaf(pr, v.y, o[i][1]);
+          o[i][2] = fmaf(pr, v.z, o[i][2]);
+          o[i][3] = fmaf(pr, v.w, o[i][3]);
+        }
+      }
+    } else if (4 * tx < dv4) {
       for (int j = 0; j < BP; j += 4) {
         float4 pv[RM];
 #pragma unroll
@@ -210,6 +228,17 @@ __device__ __forceinline__ void chain_layer(const ChainLayer& L, float* X, float
         }
       }
     }
+  }
+  if (HF == 4 && dv4 == 4) {                  // pattern-split read-out: sum the group's partials, keep them in tx == 0
+#pragma unroll
+    for (int i = 0; i < RM; ++i)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        float v = o[i][e];
+#pragma unroll
+        for (int off = 8; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+        o[i][e] = tx == 0 ? v : 0.f;
+      }
   }
   // un-normalised partial (O, max, sum) of this CTA's pattern range -> own shared memory
   __syncthreads();                            // (an empty range never entered the loop: X readers / LN writers meet here)
@@ -389,11 +418,16 @@ __global__ void __launch_bounds__(NT, 2) hop_chain_kernel(const __grid_constant_
 
 constexpr int kChainRM = 4;           // 64 rows per cluster: 4 x 4 register tiles
 
-// pattern splits per row tile: up to two CTAs per SM (103 KB of shared memory, 128 registers x 256 threads each)
+// Pattern splits per row tile.  Measured (B200, graph replays, `scripts/probes/chain_time.py`): 2,048 rows (32 tiles)
+// 166 / 111 / 86 / 119 us with 1 / 2 / 4 / 8 splits, 2,592 rows (41 tiles) 167 / 111 / 112 / 218, 9,248 rows (145 tiles)
+// 170 / 158 / 291 / 536: fill the SMs once -- a second co-resident CTA (103 KB of shared memory, 128 registers x 256
+// threads each) helps a little, a second wave or more merge partners than that do not.
 int chain_splits(int n) {
   const int tiles = (n + 16 * kChainRM - 1) / (16 * kChainRM);
+  const int sms = num_sms();
+  if (2 * tiles >= sms) return tiles * 2 <= 2 * sms ? 2 : 1;
   int s = 1;
-  while (s < 8 && tiles * s * 2 <= 2 * num_sms()) s *= 2;
+  while (s < 8 && tiles * s * 2 <= sms + sms / 8) s *= 2;
   return s;
 }
 
@@ -402,6 +436,8 @@ int launch_chain_inst(const ChainArgs& a, int tune_splits, cudaStream_t st) {
   const size_t smem = (size_t)(3 * BM * HS + 2 * BM + BP * HS + 2 * BP * DS) * sizeof(float);
   auto* kern = hop_chain_kernel<kChainRM>;
   HOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // two CTAs per SM need 2 x 103 KB: ask for the full shared-memory carve-out (the default keeps more L1 and fits one)
+  HOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
   const int splits = (tune_splits == 1 || tune_splits == 2 || tune_splits == 4 || tune_splits == 8) ? tune_splits
                                                                                                   : chain_splits(a.n);
   cudaLaunchConfig_t cfg{};
