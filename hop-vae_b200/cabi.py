@@ -22,6 +22,7 @@ F_EXACT_ARGMAX, F_TRAIN = 1 << 7, 1 << 8
 # hop_desc.tune_flags (tests / experiments; 0 = the library's heuristics)
 TUNE_STREAMK_ON, TUNE_STREAMK_OFF, TUNE_ROWS128, TUNE_MULTI_ON, TUNE_MULTI_OFF = 1 << 0, 1 << 1, 1 << 2, 1 << 3, 1 << 4
 TUNE_PAIR_ON, TUNE_PAIR_OFF, TUNE_PLAIN_UPDATES, TUNE_BWD_SIMT, TUNE_PREP_SIMT = 1 << 5, 1 << 6, 1 << 7, 1 << 8, 1 << 9
+TUNE_BWD_TAILS_SIMT = 1 << 10
 # hop_desc.path
 PATH_AUTO, PATH_FP32_SIMT, PATH_TC_F16, PATH_TC_BF16 = 0, 1, 2, 3
 PATH_NAMES = {"auto": PATH_AUTO, "fp32": PATH_FP32_SIMT, "f16": PATH_TC_F16, "bf16": PATH_TC_BF16}

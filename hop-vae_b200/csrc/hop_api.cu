@@ -210,7 +210,7 @@ int hop_sm100_workspace_bytes(const hop_desc* desc, int for_backward, size_t* by
     *bytes = simt_backward_workspace(*desc);      // (its total is a multiple of 256: the tensor-core part follows it)
     if (desc->path != HOP_PATH_FP32_SIMT && desc->path != HOP_PATH_AUTO && !(desc->tune_flags & HOP_TUNE_BWD_SIMT) &&
         tc_backward_supported(desc->n_rows, desc->n_patterns, desc->d_assoc, desc->d_v))
-      *bytes += tc_backward_workspace(desc->n_rows, desc->n_patterns, desc->d_assoc, desc->d_v);
+      *bytes += tc_backward_workspace(desc->n_rows, desc->n_patterns, desc->d_assoc, desc->d_v) + gemm_tail_workspace(*desc);
   } else {
     const int path = resolve_path(desc);
     if (path < 0) return -path;

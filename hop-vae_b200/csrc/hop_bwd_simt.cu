@@ -828,6 +828,111 @@ __global__ void __launch_bounds__(NT) multi_zero_kernel(ZeroBatch z) {
     p[i] = 0.f;
 }
 
+// ------------------------------------------------------------ GEMM-shaped tails on the tensor pipe
+// Around the tensor-core association core (hop_bwd_tc.cu) the out-projection and V-projection backwards are four dense
+// products -- dR = G Wo, dWo = G^T R, dVn = dV^ Wv, dWv = dV^^T LN_v(W) -- that the FFMA job kernels above run at ~10
+// TFLOP/s (2.06 ms of a 5.5 ms backward at N = 16k, P = 64k, D = 256; profiles/r02_bwd_launches.csv).  Where the widths
+// are multiples of 128 they go to hop_gemm_tc.cu instead: every operand is packed once as an fp16 hi + lo pair (one HBM
+// pass, row-major and transposed as the product needs it), the gradient operands divided by their own max|.| first (a
+// device scalar from absmax_kernel, multiplied back in the GEMM's epilogue) so that gradients of any magnitude sit in
+// fp16's range; the weight gradients contract over N or P rows and run split over that axis with fp32 REDs.  The bias
+// gradients are column sums.  LayerNorm backwards stay on the job kernels (they are HBM passes).
+__global__ void __launch_bounds__(NT) absmax_kernel(const float* __restrict__ x, size_t n, float* __restrict__ out) {
+  float m = 0.f;
+  const size_t n4 = n >> 2;
+  for (size_t i = (size_t)blockIdx.x * NT + threadIdx.x; i < n4; i += (size_t)gridDim.x * NT) {
+    const float4 v = __ldg(reinterpret_cast<const float4*>(x) + i);
+    m = fmaxf(fmaxf(m, fmaxf(fabsf(v.x), fabsf(v.y))), fmaxf(fabsf(v.z), fabsf(v.w)));
+  }
+  for (size_t i = (n4 << 2) + (size_t)blockIdx.x * NT + threadIdx.x; i < n; i += (size_t)gridDim.x * NT) m = fmaxf(m, fabsf(x[i]));
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, off));
+  if ((threadIdx.x & 31) == 0 && m > 0.f) atomicMax(reinterpret_cast<int*>(out), __float_as_int(m));   // (>= 0: bit order = value order)
+}
+
+// out[c] += scale * sum_r x[r][c]   (out zeroed by the caller); 64 columns x a row range per CTA
+__global__ void __launch_bounds__(NT) colsum_kernel(const float* __restrict__ x, int rows, int cols, int rows_per_cta,
+                                                    float* __restrict__ out) {
+  __shared__ float red[4][64];
+  const int c = blockIdx.x * 64 + (threadIdx.x & 63), part = threadIdx.x >> 6;
+  const int r0 = blockIdx.y * rows_per_cta, r1 = min(rows, r0 + rows_per_cta);
+  float acc = 0.f;
+  if (c < cols)
+    for (int r = r0 + part; r < r1; r += 4) acc += __ldg(x + (size_t)r * cols + c);
+  red[part][threadIdx.x & 63] = acc;
+  __syncthreads();
+  if (part == 0 && c < cols) atomicAdd(out + c, (red[0][threadIdx.x] + red[1][threadIdx.x]) + (red[2][threadIdx.x] + red[3][threadIdx.x]));
+}
+
+int launch_absmax(const float* x, size_t n, float* out, cudaStream_t st) {
+  size_t blocks = (n / 4 + NT - 1) / NT;
+  const size_t cap = (size_t)num_sms() * 8;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  absmax_kernel<<<(int)blocks, NT, 0, st>>>(x, n, out);
+  HOP_LAUNCH_CHECK("absmax_kernel");
+  return HOP_OK;
+}
+int launch_colsum(const float* x, int rows, int cols, float* out, cudaStream_t st) {
+  const int cgrid = (cols + 63) / 64;
+  int splits = (2 * num_sms() + cgrid - 1) / cgrid;
+  if (splits > (rows + 63) / 64) splits = (rows + 63) / 64;
+  if (splits < 1) splits = 1;
+  const int per = (rows + splits - 1) / splits;
+  colsum_kernel<<<dim3(cgrid, (rows + per - 1) / per), NT, 0, st>>>(x, rows, cols, per, out);
+  HOP_LAUNCH_CHECK("colsum_kernel");
+  return HOP_OK;
+}
+
+struct TailWs {
+  float* range;                                   // [0] = max|G|, [1] = max|dV^| (zeroed with the accumulation targets)
+  void *g_hi, *g_lo, *gt_hi, *gt_lo;              // G (Npad, Dout) and G^T (Dout, Npad)
+  void *rt_hi, *rt_lo;                            // R^T (Dv, Npad)
+  void *wot_hi, *wot_lo;                          // Wo^T (Dv, Dout)
+  void *dv_hi, *dv_lo, *dvt_hi, *dvt_lo;          // dV^ (Ppad, Dv) and dV^^T (Dv, Ppad)
+  void *xt_hi, *xt_lo;                            // LN_v(Wt)^T (Din, Ppad)
+  void *wvt_hi, *wvt_lo;                          // Wv^T (Din, Dv)
+  size_t total;
+};
+// which of the two tails run as tensor-core GEMMs for this layer (needs the tensor-core core)
+static inline bool tail_out_gemm(const hop_desc& d) {
+  return (d.flags & HOP_F_OUT_PROJ) && d.d_out % 128 == 0 && d.d_v % 128 == 0 && d.d_out <= 1024 && d.d_v <= 1024;
+}
+static inline bool tail_v_gemm(const hop_desc& d) {
+  return (d.flags & HOP_F_PROJ_PATTERN) && d.d_v % 128 == 0 && d.d_in % 128 == 0 && d.d_in <= 1024;
+}
+TailWs carve_tail(const hop_desc& d, void* ws) {
+  TailWs w{};
+  size_t off = 0;
+  auto take = [&](size_t bytes) -> void* {
+    void* p = ws ? static_cast<char*>(ws) + off : nullptr;
+    off += round_up_sz(bytes, 256);
+    return p;
+  };
+  const size_t npad = round_up(d.n_rows, 128), ppad = padded_patterns(d.n_patterns);
+  w.range = static_cast<float*>(take(256));
+  if (tail_out_gemm(d)) {
+    w.g_hi = take(npad * d.d_out * 2); w.g_lo = take(npad * d.d_out * 2);
+    w.gt_hi = take(npad * d.d_out * 2); w.gt_lo = take(npad * d.d_out * 2);
+    w.rt_hi = take(npad * d.d_v * 2); w.rt_lo = take(npad * d.d_v * 2);
+    w.wot_hi = take((size_t)d.d_out * d.d_v * 2); w.wot_lo = take((size_t)d.d_out * d.d_v * 2);
+  }
+  if (tail_v_gemm(d)) {
+    w.dv_hi = take(ppad * d.d_v * 2); w.dv_lo = take(ppad * d.d_v * 2);
+    w.dvt_hi = take(ppad * d.d_v * 2); w.dvt_lo = take(ppad * d.d_v * 2);
+    w.xt_hi = take(ppad * d.d_in * 2); w.xt_lo = take(ppad * d.d_in * 2);
+    w.wvt_hi = take((size_t)d.d_in * d.d_v * 2); w.wvt_lo = take((size_t)d.d_in * d.d_v * 2);
+  }
+  w.total = off;
+  return w;
+}
+int weight_grad_splits(int m, int n, int kchunks) {
+  const int tiles = ((m + 127) / 128) * ((n + 255) / 256);
+  int s = (num_sms() + tiles - 1) / tiles;
+  if (s > kchunks) s = kchunks;
+  return s < 1 ? 1 : s;
+}
+
 struct BwdWs {
   float *dr, *dqs, *delta, *dkhat, *dvhat, *dvn, *dkn, *dqn;
   size_t total;
@@ -857,6 +962,10 @@ BwdWs carve(const hop_desc& d, void* ws) {
 }  // namespace
 
 size_t simt_backward_workspace(const hop_desc& d) { return carve(d, nullptr).total; }
+size_t gemm_tail_workspace(const hop_desc& d) {
+  if (d.tune_flags & HOP_TUNE_BWD_TAILS_SIMT) return 0;
+  return (tail_out_gemm(d) || tail_v_gemm(d)) ? carve_tail(d, nullptr).total : 0;
+}
 
 int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patterns& pt, const float* x,
                          const float* qhat, const float* retrieved, const float* lse, const int32_t* argmax,
@@ -869,6 +978,17 @@ int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patte
              "tensor-core path (hop_sm100_select_train_path)", d.d_assoc, d.d_v);
   const BwdWs w = carve(d, ws);
   const int N = d.n_rows, P = d.n_patterns, H = d.d_assoc, Dv = d.d_v, Din = d.d_in;
+  // GEMM-shaped tails on the tensor pipe (see carve_tail); their packs sit behind the tensor-core core's workspace
+  const bool tails_tc = tc_core && !(d.tune_flags & HOP_TUNE_BWD_TAILS_SIMT);
+  const bool out_gemm = tails_tc && tail_out_gemm(d), v_gemm = tails_tc && tail_v_gemm(d);
+  const size_t tc_ws = tc_core ? tc_backward_workspace(N, P, H, Dv) : 0;
+  TailWs tw{};
+  if (out_gemm || v_gemm) {
+    tw = carve_tail(d, static_cast<char*>(ws) + w.total + tc_ws);
+    if (ws_bytes < w.total + tc_ws + tw.total)
+      HOP_FAIL(HOP_ERR_WORKSPACE, "backward: %zu workspace bytes needed, %zu given", w.total + tc_ws + tw.total, ws_bytes);
+  }
+  const int npad = round_up(N, 128), ppad = padded_patterns(P);
   const bool out_proj = d.flags & HOP_F_OUT_PROJ, q_proj = d.flags & HOP_F_PROJ_STATE;
   const bool k_proj = d.flags & HOP_F_PROJ_STORED, v_proj = d.flags & HOP_F_PROJ_PATTERN;
   const bool sep_targets = p.lookup_targets != nullptr;
@@ -887,6 +1007,7 @@ int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patte
   {
     const bool has_wt = (sep_targets ? g.d_lookup_targets : g.d_lookup) != nullptr;
     if (out_proj && g.d_wo) { HOP_TRY(zero(g.d_wo, (size_t)d.d_out * Dv)); HOP_TRY(zero(g.d_bo, d.d_out)); }
+    if (out_gemm || v_gemm) HOP_TRY(zero(tw.range, 4));
     HOP_TRY(zero(w.dkhat, (size_t)P * H));
     HOP_TRY(zero(w.dvhat, (size_t)P * Dv));
     if (tc_core) HOP_TRY(zero(w.dqs, (size_t)N * H));      // the tensor-core core accumulates dq with REDs too
@@ -907,7 +1028,30 @@ int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patte
   // 1. out-projection backward: dR = G . Wo and dWo = G^T . R are independent -> one launch
   BwdJobBatch stage[3] = {};
   const float* dR = grad_out;
-  if (out_proj) {
+  if (out_proj && out_gemm) {
+    HOP_TRY(launch_absmax(grad_out, (size_t)N * d.d_out, tw.range, st));
+    Pack16Args pg{grad_out, N, npad, d.d_out, 0, nullptr, nullptr, 0.f, tw.range, tw.g_hi, tw.g_lo,
+                  g.d_wo ? tw.gt_hi : nullptr, g.d_wo ? tw.gt_lo : nullptr};
+    HOP_TRY(launch_pack16(pg, st));
+    Pack16Args pw{p.wo, d.d_out, d.d_out, Dv, 0, nullptr, nullptr, 0.f, nullptr, nullptr, nullptr, tw.wot_hi, tw.wot_lo};
+    HOP_TRY(launch_pack16(pw, st));
+    TcGemmArgs m1{};                      // dR (N, Dv) = G (N, Dout) . Wo
+    m1.a16 = tw.g_hi; m1.a16lo = tw.g_lo; m1.b16 = tw.wot_hi; m1.b16lo = tw.wot_lo;
+    m1.m = N; m1.m_pad = npad; m1.n = Dv; m1.k = d.d_out; m1.ldc = Dv; m1.c = w.dr; m1.split = 1; m1.out_scale_dev = tw.range;
+    HOP_TRY(launch_tc_gemm(m1, st));
+    dR = w.dr;
+    if (g.d_wo) {
+      Pack16Args pr{retrieved, N, npad, Dv, 0, nullptr, nullptr, 0.f, nullptr, nullptr, nullptr, tw.rt_hi, tw.rt_lo};
+      HOP_TRY(launch_pack16(pr, st));
+      TcGemmArgs m2{};                    // dWo (Dout, Dv) += G^T . R, contraction over the N rows split across CTAs
+      m2.a16 = tw.gt_hi; m2.a16lo = tw.gt_lo; m2.b16 = tw.rt_hi; m2.b16lo = tw.rt_lo;
+      m2.m = d.d_out; m2.m_pad = d.d_out; m2.n = Dv; m2.k = npad; m2.ldc = Dv; m2.c = g.d_wo; m2.split = 1;
+      m2.k_splits = weight_grad_splits(d.d_out, Dv, npad / 64); m2.out_scale_dev = tw.range;
+      if (m2.k_splits < 2) m2.k_splits = 2;         // (always the accumulating form: d_wo is zeroed above)
+      HOP_TRY(launch_tc_gemm(m2, st));
+      if (g.d_bo) HOP_TRY(launch_colsum(grad_out, N, d.d_out, g.d_bo, st));
+    }
+  } else if (out_proj) {
     HOP_TRY(batch_add_linear_nn(stage[0], grad_out, p.wo, w.dr, N, d.d_out, Dv));
     dR = w.dr;
     if (g.d_wo) {
@@ -983,7 +1127,31 @@ int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patte
     const float* Wt = sep_targets ? p.lookup_targets : p.lookup;
     float* d_wt = sep_targets ? g.d_lookup_targets : g.d_lookup;
     const float* gv = w.dvhat;
-    if (v_proj) {
+    if (v_proj && v_gemm) {
+      HOP_TRY(launch_absmax(w.dvhat, (size_t)P * Dv, tw.range + 1, st));
+      Pack16Args pd{w.dvhat, P, ppad, Dv, 0, nullptr, nullptr, 0.f, tw.range + 1, tw.dv_hi, tw.dv_lo,
+                    g.d_wv ? tw.dvt_hi : nullptr, g.d_wv ? tw.dvt_lo : nullptr};
+      HOP_TRY(launch_pack16(pd, st));
+      Pack16Args pw{p.wv, Dv, Dv, Din, 0, nullptr, nullptr, 0.f, nullptr, nullptr, nullptr, tw.wvt_hi, tw.wvt_lo};
+      HOP_TRY(launch_pack16(pw, st));
+      TcGemmArgs m3{};                    // dVn (P, Din) = dV^ (P, Dv) . Wv
+      m3.a16 = tw.dv_hi; m3.a16lo = tw.dv_lo; m3.b16 = tw.wvt_hi; m3.b16lo = tw.wvt_lo;
+      m3.m = P; m3.m_pad = ppad; m3.n = Din; m3.k = Dv; m3.ldc = Din; m3.c = w.dvn; m3.split = 1; m3.out_scale_dev = tw.range + 1;
+      HOP_TRY(launch_tc_gemm(m3, st));
+      if (g.d_wv) {
+        Pack16Args px{Wt, P, ppad, Din, (d.flags & HOP_F_NORM_PROJ) ? 1 : 0, p.ln_proj_w, p.ln_proj_b, d.ln_eps, nullptr,
+                      nullptr, nullptr, tw.xt_hi, tw.xt_lo};
+        HOP_TRY(launch_pack16(px, st));
+        TcGemmArgs m4{};                  // dWv (Dv, Din) += dV^^T . LN_v(Wt), contraction over the P patterns split
+        m4.a16 = tw.dvt_hi; m4.a16lo = tw.dvt_lo; m4.b16 = tw.xt_hi; m4.b16lo = tw.xt_lo;
+        m4.m = Dv; m4.m_pad = Dv; m4.n = Din; m4.k = ppad; m4.ldc = Din; m4.c = g.d_wv; m4.split = 1;
+        m4.k_splits = weight_grad_splits(Dv, Din, ppad / 64); m4.out_scale_dev = tw.range + 1;
+        if (m4.k_splits < 2) m4.k_splits = 2;
+        HOP_TRY(launch_tc_gemm(m4, st));
+        if (g.d_bv) HOP_TRY(launch_colsum(w.dvhat, P, Dv, g.d_bv, st));
+      }
+      gv = w.dvn;
+    } else if (v_proj) {
       if (g.d_wv) {
         WgradArgs wa{w.dvhat, Wt, P, Dv, Din, (d.flags & HOP_F_NORM_PROJ) ? 1 : 0, p.ln_proj_w, p.ln_proj_b, d.ln_eps,
                      g.d_wv, g.d_bv, 0, 1.f};

@@ -92,6 +92,7 @@ int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patte
                          const float* grad_out, const hop_grads& g, void* ws, size_t ws_bytes,
                          cudaStream_t st);
 size_t simt_backward_workspace(const hop_desc& d);
+size_t gemm_tail_workspace(const hop_desc& d);   // packs of the GEMM-shaped tails (behind the tensor-core core's workspace)
 // hop_repair.cu -- exact nearest-pattern index behind the 16-bit tensor-core scores (HOP_F_EXACT_ARGMAX) and the
 // fp32 path's stop rule of the retrieve updates (update_eps)
 struct RepairArgs {
@@ -162,9 +163,21 @@ struct TcGemmArgs {
   const float* bias;                    // (n) or nullptr
   float* c;                             // (m, ldc) fp32
   int split;                            // operands are hi + lo pairs: three MMAs per product, ~2^-21 relative
+  int k_splits;                         // > 1: the contraction is cut into that many ranges (grid.z), every CTA adds its
+                                        // partial tile into a ZEROED c with fp32 REDs (short-and-wide products: weight gradients)
+  const float* out_scale_dev;           // device scalar multiplied into the result (undoes an operand's range scaling) or nullptr
 };
 bool tc_gemm_supported(int n, int k);
 int launch_tc_gemm(const TcGemmArgs& a, cudaStream_t st);
+// hop_prep.cu: one HBM pass x [-> LayerNorm] [/ *range_dev] -> fp16 hi + lo operand packs of hop_gemm_tc.cu (low halves
+// times kGemmLoScale), row-major (rows_pad, width) and / or transposed (width, rows_pad); rows >= `rows` are zeros
+struct Pack16Args {
+  const float* x; int rows, rows_pad, width;
+  int has_ln; const float* ln_w; const float* ln_b; float ln_eps;
+  const float* range_dev;
+  void* y16; void* y16lo; void* yt16; void* yt16lo;
+};
+int launch_pack16(const Pack16Args& p, cudaStream_t st);
 size_t prepare_scratch_bytes(const hop_desc& d);   // hop_prep.cu: scratch of the tensor-core pattern preparation (0: FFMA form)
 // hop_bwd_tc.cu -- association core of the backward on the tensor pipe (dq, dK^, dV^)
 struct TcBwdArgs {

@@ -36,6 +36,9 @@ struct GemmArgs {
   int ldc;
   const float* bias;           // (n) or nullptr
   float* c;
+  int chunks_per_split;        // 64-wide K chunks per grid.z slice
+  int atomic;                  // add into c with REDs (split-K) instead of storing
+  const float* out_scale_dev;  // device scalar multiplied into the result or nullptr
 };
 
 // TN = columns of C per CTA (64 | 128 | 256), kSplit = hi + lo operand pairs
@@ -65,7 +68,8 @@ hop_gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
   const uint32_t tmem_slot = acc_full + 8u;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row0 = blockIdx.x * kGM, col0 = blockIdx.y * TN;
-  const int kchunks = g.k / 64;
+  const int kc_begin = blockIdx.z * g.chunks_per_split;
+  const int kchunks = min(g.k / 64 - kc_begin, g.chunks_per_split);      // (the host leaves no slice empty)
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < Cfg::kStages; ++s) { ptx::mbar_init(full_bar(s), 1); ptx::mbar_init(empty_bar(s), 1); }
@@ -90,11 +94,12 @@ hop_gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
         ptx::mbar_wait(empty_bar(s), ((kc / Cfg::kStages) & 1) ^ 1);
         ptx::mbar_arrive_expect_tx(full_bar(s), Cfg::kStageBytes);
         const uint32_t base = ring + s * Cfg::kStageBytes;
-        ptx::tma_load_2d(base, &tm_a, full_bar(s), kc * 64, row0);
-        ptx::tma_load_2d(base + Cfg::kABytes, &tm_b, full_bar(s), kc * 64, col0);
+        const int kx = (kc_begin + kc) * 64;
+        ptx::tma_load_2d(base, &tm_a, full_bar(s), kx, row0);
+        ptx::tma_load_2d(base + Cfg::kABytes, &tm_b, full_bar(s), kx, col0);
         if constexpr (kSplit) {
-          ptx::tma_load_2d(base + Cfg::kABytes + Cfg::kBBytes, &tm_alo, full_bar(s), kc * 64, row0);
-          ptx::tma_load_2d(base + 2 * Cfg::kABytes + Cfg::kBBytes, &tm_blo, full_bar(s), kc * 64, col0);
+          ptx::tma_load_2d(base + Cfg::kABytes + Cfg::kBBytes, &tm_alo, full_bar(s), kx, row0);
+          ptx::tma_load_2d(base + 2 * Cfg::kABytes + Cfg::kBBytes, &tm_blo, full_bar(s), kx, col0);
         }
       }
     }
@@ -130,6 +135,7 @@ hop_gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
     const long long grow = (long long)row0 + wq * 32 + lane;
     ptx::mbar_wait(acc_full, 0);
     ptx::tc_fence_after();
+    const float osc = g.out_scale_dev ? __ldg(g.out_scale_dev) : 1.f;
 #pragma unroll 1
     for (int c = 0; c < TN / 32; ++c) {
       uint32_t o[32];
@@ -149,8 +155,16 @@ hop_gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
         float* dst = g.c + grow * g.ldc + gc;
 #pragma unroll
         for (int q4 = 0; q4 < 8; ++q4) {
-          float4 r = make_float4(__uint_as_float(o[4 * q4]), __uint_as_float(o[4 * q4 + 1]),
-                                 __uint_as_float(o[4 * q4 + 2]), __uint_as_float(o[4 * q4 + 3]));
+          float4 r = make_float4(__uint_as_float(o[4 * q4]) * osc, __uint_as_float(o[4 * q4 + 1]) * osc,
+                                 __uint_as_float(o[4 * q4 + 2]) * osc, __uint_as_float(o[4 * q4 + 3]) * osc);
+          if (g.atomic) {
+            if (gc + 4 * q4 + 3 < g.n) atomicAdd(reinterpret_cast<float4*>(dst) + q4, r);
+            else {
+              const float rv[4] = {r.x, r.y, r.z, r.w};
+              for (int e = 0; e < 4; ++e) if (gc + 4 * q4 + e < g.n) atomicAdd(dst + 4 * q4 + e, rv[e]);
+            }
+            continue;
+          }
           if (g.bias) {
             const float4 bb = __ldg(reinterpret_cast<const float4*>(g.bias + gc) + q4);
             r.x += bb.x; r.y += bb.y; r.z += bb.z; r.w += bb.w;
@@ -213,10 +227,14 @@ int launch_gemm_inst(const TcGemmArgs& a, cudaStream_t st) {
     HOP_TRY(gemm_map(&tal, a.a16lo, a.m_pad, a.k, a.k, kGM));
     HOP_TRY(gemm_map(&tbl, a.b16lo, a.n, a.k, a.k, TN));
   } else { tal = ta; tbl = tb; }
-  GemmArgs g{a.m, a.n, a.k, a.ldc, a.bias, a.c};
+  const int kchunks = a.k / 64;
+  const int want = a.k_splits > 1 ? (a.k_splits < kchunks ? a.k_splits : kchunks) : 1;
+  const int per = (kchunks + want - 1) / want;
+  const int zs = (kchunks + per - 1) / per;                    // no empty slice
+  GemmArgs g{a.m, a.n, a.k, a.ldc, a.bias, a.c, per, zs > 1 || a.k_splits > 1 ? 1 : 0, a.out_scale_dev};
   auto* kern = hop_gemm_tc_kernel<TN, kSplit>;
   HOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
-  kern<<<dim3((a.m + kGM - 1) / kGM, (a.n + TN - 1) / TN), kGThreads, Cfg::kSmemBytes, st>>>(ta, tal, tb, tbl, g);
+  kern<<<dim3((a.m + kGM - 1) / kGM, (a.n + TN - 1) / TN, zs), kGThreads, Cfg::kSmemBytes, st>>>(ta, tal, tb, tbl, g);
   HOP_LAUNCH_CHECK("hop_gemm_tc_kernel");
   return HOP_OK;
 }
@@ -229,6 +247,7 @@ int launch_tc_gemm(const TcGemmArgs& a, cudaStream_t st) {
   if (!tc_gemm_supported(a.n, a.k)) HOP_FAIL(HOP_ERR_UNSUPPORTED, "tensor-core GEMM: N and K must be multiples of 64");
   if (!a.a16 || !a.b16 || !a.c || (a.split && (!a.a16lo || !a.b16lo))) HOP_FAIL(HOP_ERR_BAD_ARG, "tensor-core GEMM: NULL operand");
   if ((a.ldc & 3) != 0) HOP_FAIL(HOP_ERR_BAD_ALIGN, "tensor-core GEMM: ldc must be a multiple of 4");
+  if (a.k_splits > 1 && a.bias) HOP_FAIL(HOP_ERR_BAD_ARG, "tensor-core GEMM: a split contraction takes no bias");
   const int tn = a.n % 256 == 0 ? 256 : (a.n % 128 == 0 ? 128 : 64);
   if (a.split) {
     if (tn == 256) return launch_gemm_inst<256, true>(a, st);

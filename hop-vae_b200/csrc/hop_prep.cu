@@ -34,6 +34,7 @@ struct LnLinearArgs {
   float lo_scale;      // the low halves hold lo_scale * (y - decode(y16)) (0 = 1; hop_gemm_tc.cu takes 2^11, which keeps the
                        // residual of small-magnitude operands out of the fp16 subnormals)
   float* norm_max;     // [1]: max over rows of ||y_row||_2 (atomic max on the float's bits; zeroed by the caller) or nullptr
+  const float* range_dev;   // device scalar r > 0: the output is divided by it (gradients of any magnitude -> fp16's range) or nullptr
 };
 
 __device__ __forceinline__ uint16_t to16(float v, int bf16) {
@@ -63,6 +64,8 @@ __device__ __forceinline__ void ln_linear_body(const LnLinearArgs& a) {
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
   const int warp = tid >> 5, lane = tid & 31;
   const int row0 = blockIdx.x * BR;
+  float out_scale = a.scale;
+  if (a.range_dev) { const float r = __ldg(a.range_dev); out_scale = r > 0.f ? a.scale / r : a.scale; }
 
   // per-row LayerNorm statistics
   for (int r = warp; r < BR; r += NT / 32) {
@@ -145,7 +148,7 @@ __device__ __forceinline__ void ln_linear_body(const LnLinearArgs& a) {
         const int c = tx + 16 * bb;
         float v = acc[i][bb];
         if (a.w && a.b && c0 + c < a.dout) v += __ldg(a.b + c0 + c);
-        Ys[(ty * RM + i) * YS + c] = v * a.scale;
+        Ys[(ty * RM + i) * YS + c] = v * out_scale;
       }
     __syncthreads();
     for (int idx = tid; idx < BR * TN; idx += NT) {
@@ -323,6 +326,15 @@ int launch_prepare_patterns(const hop_desc& d, const hop_params& p, const hop_pa
     HOP_TRY(launch_ln_linear(o, st));
   }
   return HOP_OK;
+}
+
+int launch_pack16(const Pack16Args& p, cudaStream_t st) {
+  LnLinearArgs a{};
+  a.x = p.x; a.rows = p.rows; a.rows_pad = p.rows_pad; a.din = p.width; a.has_ln = p.has_ln; a.ln_w = p.ln_w; a.ln_b = p.ln_b;
+  a.ln_eps = p.ln_eps; a.w = nullptr; a.b = nullptr; a.dout = p.width; a.scale = 1.f; a.y = nullptr;
+  a.y16 = p.y16; a.y16lo = p.y16lo; a.yt16 = p.yt16; a.yt16lo = p.yt16lo; a.bf16 = 0; a.lo_scale = kGemmLoScale;
+  a.range_dev = p.range_dev;
+  return launch_ln_linear(a, st);
 }
 
 int launch_prepare_queries(const hop_desc& d, const hop_params& p, const float* x, float* qhat, cudaStream_t st) {

@@ -33,7 +33,7 @@ from .ops import (LayerSpec, HopfieldAssociation, prepare_patterns, prepare_patt
 _TUNE_NAMES = {"streamk": (cabi.TUNE_STREAMK_ON, cabi.TUNE_STREAMK_OFF), "multi_launch": (cabi.TUNE_MULTI_ON, cabi.TUNE_MULTI_OFF),
                "pair": (cabi.TUNE_PAIR_ON, cabi.TUNE_PAIR_OFF), "rows128": (cabi.TUNE_ROWS128, 0),
                "plain_updates": (cabi.TUNE_PLAIN_UPDATES, 0), "bwd_simt": (cabi.TUNE_BWD_SIMT, 0),
-               "prep_simt": (cabi.TUNE_PREP_SIMT, 0)}
+               "prep_simt": (cabi.TUNE_PREP_SIMT, 0), "bwd_tails_simt": (cabi.TUNE_BWD_TAILS_SIMT, 0)}
 
 _NOT_BUILT = dict(num_heads=1, normalize_hopfield_space=False, normalize_hopfield_space_affine=False,
                   pattern_projection_as_connected=False, association_activation=None, dropout=0.0,

@@ -79,8 +79,10 @@ enum {
   HOP_TUNE_PLAIN_UPDATES = 1u << 7, /* retrieve updates with plain 16-bit operands even when T >= 2 (default: the
                                        update passes of T >= 2 use hi + lo operand pairs)   */
   HOP_TUNE_BWD_SIMT     = 1u << 8,  /* backward on the fp32 CUDA-core kernels even where the tcgen05 one applies */
-  HOP_TUNE_PREP_SIMT    = 1u << 9   /* pattern preparation on the fp32 CUDA-core kernels even where the tcgen05
+  HOP_TUNE_PREP_SIMT    = 1u << 9,  /* pattern preparation on the fp32 CUDA-core kernels even where the tcgen05
                                        GEMM applies (hop_patterns.scratch given, widths multiples of 64)      */
+  HOP_TUNE_BWD_TAILS_SIMT = 1u << 10 /* projection / weight-gradient products of a tensor-core backward on the fp32
+                                       CUDA-core kernels even where the tcgen05 GEMM applies (widths % 128)   */
 };
 
 /* hop_desc.path -- which kernel family evaluates the association.            */

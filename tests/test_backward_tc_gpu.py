@@ -109,21 +109,30 @@ def test_backward_parity_tensor_core(hf, name):
 def test_backward_tensor_core_matches_fp32_kernels(hf):
     """Same layer, same inputs: the tensor-core step against the library's own fp32 step (tune bwd_simt keeps the whole
     step on the exact kernels) -- the two cores must agree to the operand rounding, and tiny gradients (1e-6 of the
-    usual scale) must survive the fp16 operand range through the global rescale."""
+    usual scale) must survive the fp16 operand range through the global rescale.  In between: the tensor-core core with
+    the projection / weight-gradient products on the fp32 kernels (tune bwd_tails_simt), which isolates the tcgen05 GEMM
+    tails (hi + lo operand pairs, range-scaled gradients, split contraction): they must match the fp32 tails to 1e-5."""
     D, P, N = 128, 8192, 4096
     ref, dut, g = _pair(hf, D, P, seed=95)
     dut.kernel_path = "f16"
     x = torch.randn(N, D, generator=g).cuda()
     w = (1e-6 * torch.randn(N, D, generator=g)).cuda()
     grads = {}
-    for mode in ("tc", "fp32"):
-        dut.tune = dict(bwd_simt=(mode == "fp32"))
+    for mode in ("tc", "tc_tails_fp32", "fp32"):
+        dut.tune = dict(bwd_simt=(mode == "fp32"), bwd_tails_simt=(mode == "tc_tails_fp32"))
         dut.zero_grad(set_to_none=True)
         xd = x.clone().requires_grad_(True)
         (dut(xd) * w).sum().backward()
         torch.cuda.synchronize()
-        grads[mode] = (xd.grad.clone(), dut.lookup_weights.grad.clone())
-    for a, b, what in zip(grads["tc"], grads["fp32"], ("d_x", "d_lookup")):
-        r = rel_l2(a, b)
+        grads[mode] = dict(d_x=xd.grad.clone(), **{k: v.grad.clone() for k, v in dut.named_parameters() if v.grad is not None})
+    for what in ("d_x", "lookup_weights"):
+        r = rel_l2(grads["tc"][what], grads["fp32"][what])
         print(f"tensor-core vs fp32 core, {what}: rel-L2 {r:.3e}")
         assert r < GRAD_BAR
+    for what, a in grads["tc"].items():
+        b = grads["tc_tails_fp32"][what]
+        if what.endswith("norm_stored_pattern.bias"):
+            continue                                      # rounding noise around an exact zero on both sides
+        r = rel_l2(a, b)
+        print(f"GEMM tails vs fp32 tails, {what}: rel-L2 {r:.3e}")
+        assert r < 1e-5, what
