@@ -989,6 +989,11 @@ int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patte
       HOP_FAIL(HOP_ERR_WORKSPACE, "backward: %zu workspace bytes needed, %zu given", w.total + tc_ws + tw.total, ws_bytes);
   }
   const int npad = round_up(N, 128), ppad = padded_patterns(P);
+#ifdef HOP_TAIL_NO_RANGE        // (experiment: operands packed unscaled)
+  float* const range_g = nullptr; float* const range_v = nullptr;
+#else
+  float* const range_g = tw.range; float* const range_v = tw.range ? tw.range + 1 : nullptr;
+#endif
   const bool out_proj = d.flags & HOP_F_OUT_PROJ, q_proj = d.flags & HOP_F_PROJ_STATE;
   const bool k_proj = d.flags & HOP_F_PROJ_STORED, v_proj = d.flags & HOP_F_PROJ_PATTERN;
   const bool sep_targets = p.lookup_targets != nullptr;
@@ -1030,14 +1035,14 @@ int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patte
   const float* dR = grad_out;
   if (out_proj && out_gemm) {
     HOP_TRY(launch_absmax(grad_out, (size_t)N * d.d_out, tw.range, st));
-    Pack16Args pg{grad_out, N, npad, d.d_out, 0, nullptr, nullptr, 0.f, tw.range, tw.g_hi, tw.g_lo,
+    Pack16Args pg{grad_out, N, npad, d.d_out, 0, nullptr, nullptr, 0.f, range_g, tw.g_hi, tw.g_lo,
                   g.d_wo ? tw.gt_hi : nullptr, g.d_wo ? tw.gt_lo : nullptr};
     HOP_TRY(launch_pack16(pg, st));
     Pack16Args pw{p.wo, d.d_out, d.d_out, Dv, 0, nullptr, nullptr, 0.f, nullptr, nullptr, nullptr, tw.wot_hi, tw.wot_lo};
     HOP_TRY(launch_pack16(pw, st));
     TcGemmArgs m1{};                      // dR (N, Dv) = G (N, Dout) . Wo
     m1.a16 = tw.g_hi; m1.a16lo = tw.g_lo; m1.b16 = tw.wot_hi; m1.b16lo = tw.wot_lo;
-    m1.m = N; m1.m_pad = npad; m1.n = Dv; m1.k = d.d_out; m1.ldc = Dv; m1.c = w.dr; m1.split = 1; m1.out_scale_dev = tw.range;
+    m1.m = N; m1.m_pad = npad; m1.n = Dv; m1.k = d.d_out; m1.ldc = Dv; m1.c = w.dr; m1.split = 1; m1.out_scale_dev = range_g;
     HOP_TRY(launch_tc_gemm(m1, st));
     dR = w.dr;
     if (g.d_wo) {
@@ -1046,7 +1051,7 @@ int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patte
       TcGemmArgs m2{};                    // dWo (Dout, Dv) += G^T . R, contraction over the N rows split across CTAs
       m2.a16 = tw.gt_hi; m2.a16lo = tw.gt_lo; m2.b16 = tw.rt_hi; m2.b16lo = tw.rt_lo;
       m2.m = d.d_out; m2.m_pad = d.d_out; m2.n = Dv; m2.k = npad; m2.ldc = Dv; m2.c = g.d_wo; m2.split = 1;
-      m2.k_splits = weight_grad_splits(d.d_out, Dv, npad / 64); m2.out_scale_dev = tw.range;
+      m2.k_splits = weight_grad_splits(d.d_out, Dv, npad / 64); m2.out_scale_dev = range_g;
       if (m2.k_splits < 2) m2.k_splits = 2;         // (always the accumulating form: d_wo is zeroed above)
       HOP_TRY(launch_tc_gemm(m2, st));
       if (g.d_bo) HOP_TRY(launch_colsum(grad_out, N, d.d_out, g.d_bo, st));
@@ -1129,14 +1134,14 @@ int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patte
     const float* gv = w.dvhat;
     if (v_proj && v_gemm) {
       HOP_TRY(launch_absmax(w.dvhat, (size_t)P * Dv, tw.range + 1, st));
-      Pack16Args pd{w.dvhat, P, ppad, Dv, 0, nullptr, nullptr, 0.f, tw.range + 1, tw.dv_hi, tw.dv_lo,
+      Pack16Args pd{w.dvhat, P, ppad, Dv, 0, nullptr, nullptr, 0.f, range_v, tw.dv_hi, tw.dv_lo,
                     g.d_wv ? tw.dvt_hi : nullptr, g.d_wv ? tw.dvt_lo : nullptr};
       HOP_TRY(launch_pack16(pd, st));
       Pack16Args pw{p.wv, Dv, Dv, Din, 0, nullptr, nullptr, 0.f, nullptr, nullptr, nullptr, tw.wvt_hi, tw.wvt_lo};
       HOP_TRY(launch_pack16(pw, st));
       TcGemmArgs m3{};                    // dVn (P, Din) = dV^ (P, Dv) . Wv
       m3.a16 = tw.dv_hi; m3.a16lo = tw.dv_lo; m3.b16 = tw.wvt_hi; m3.b16lo = tw.wvt_lo;
-      m3.m = P; m3.m_pad = ppad; m3.n = Din; m3.k = Dv; m3.ldc = Din; m3.c = w.dvn; m3.split = 1; m3.out_scale_dev = tw.range + 1;
+      m3.m = P; m3.m_pad = ppad; m3.n = Din; m3.k = Dv; m3.ldc = Din; m3.c = w.dvn; m3.split = 1; m3.out_scale_dev = range_v;
       HOP_TRY(launch_tc_gemm(m3, st));
       if (g.d_wv) {
         Pack16Args px{Wt, P, ppad, Din, (d.flags & HOP_F_NORM_PROJ) ? 1 : 0, p.ln_proj_w, p.ln_proj_b, d.ln_eps, nullptr,
@@ -1145,7 +1150,7 @@ int launch_simt_backward(const hop_desc& d, const hop_params& p, const hop_patte
         TcGemmArgs m4{};                  // dWv (Dv, Din) += dV^^T . LN_v(Wt), contraction over the P patterns split
         m4.a16 = tw.dvt_hi; m4.a16lo = tw.dvt_lo; m4.b16 = tw.xt_hi; m4.b16lo = tw.xt_lo;
         m4.m = Dv; m4.m_pad = Dv; m4.n = Din; m4.k = ppad; m4.ldc = Din; m4.c = g.d_wv; m4.split = 1;
-        m4.k_splits = weight_grad_splits(Dv, Din, ppad / 64); m4.out_scale_dev = tw.range + 1;
+        m4.k_splits = weight_grad_splits(Dv, Din, ppad / 64); m4.out_scale_dev = range_v;
         if (m4.k_splits < 2) m4.k_splits = 2;
         HOP_TRY(launch_tc_gemm(m4, st));
         if (g.d_bv) HOP_TRY(launch_colsum(w.dvhat, P, Dv, g.d_bv, st));
