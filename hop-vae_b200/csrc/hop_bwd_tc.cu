@@ -54,7 +54,12 @@ struct BwdCfg {
   static constexpr int kXBytes = (kTwo ? 2 : 1) * kXTileBytes;
   static constexpr int kSCols = kTP / 2;                   // TMEM columns of one N = 128 score tile
   static constexpr int kBufCols = (kTwo ? 2 : 1) * kSCols; // one buffer: S [, dA]
-  static constexpr uint32_t kTmemAcc = 2 * kBufCols;
+  // Score buffers in TMEM.  S(j+1) overwrites the buffer whose W~ the accumulate MMAs of an earlier tile read as their A
+  // operand, and the tensor pipe does not interlock that read against a later instruction's D write: those MMAs must
+  // have COMPLETED before S(j+1) is issued.  With three buffers that is tile j-2 -- long done, no bubble; H = 512 has
+  // TMEM room for two, where the issuer waits for tile j-1 (a short bubble per tile).
+  static constexpr int kBufs = (3 * kBufCols + (H >= 256 ? H / 2 : H / 2) <= 512) ? 3 : 2;
+  static constexpr uint32_t kTmemAcc = kBufs * kBufCols;
   static constexpr int kAccN = H >= 256 ? 256 : H;         // N of one accumulate instruction
   static constexpr int kNH = H / kAccN;                    // instructions per K step
   static constexpr int kAccStageBytes = (kAccN / 2) * 128; // this CTA's half of one (64-k, N) operand slice
@@ -125,13 +130,14 @@ hop_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
   auto full_bar = [&](int s) { return bars + 8u * s; };
   auto empty_bar = [&](int s) { return bars + 8u * (Cfg::kStages + s); };
   const uint32_t misc = bars + 16u * Cfg::kStages;
-  auto s_full = [&](int b) { return misc + 8u * b; };
-  auto p_full = [&](int b) { return misc + 16u + 8u * b; };
-  auto p_empty = [&](int b) { return misc + 32u + 8u * b; };
-  const uint32_t x_ready = misc + 48u;
-  auto st_full = [&](int s) { return misc + 56u + 8u * s; };
-  auto st_empty = [&](int s) { return misc + 72u + 8u * s; };
-  const uint32_t tmem_slot = misc + 88u;
+  auto s_full = [&](int b) { return misc + 8u * b; };                 // (three slots each: Cfg::kBufs <= 3)
+  auto p_full = [&](int b) { return misc + 24u + 8u * b; };
+  auto p_empty = [&](int b) { return misc + 48u + 8u * b; };
+  const uint32_t x_ready = misc + 72u;
+  auto st_full = [&](int s) { return misc + 80u + 8u * s; };
+  auto st_empty = [&](int s) { return misc + 96u + 8u * s; };
+  const uint32_t tmem_slot = misc + 112u;
+  constexpr int kBufs = Cfg::kBufs;
   const uint32_t stat = bars + Cfg::kBarBytes;
   auto stat_at = [&](int slot, int which, int col) { return stat + (uint32_t)(((slot * 2 + which) * kTP + col) * 4); };
   const uint32_t xp = stat + Cfg::kStatBytes;
@@ -148,11 +154,11 @@ hop_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < Cfg::kStages; ++s) { ptx::mbar_init(full_bar(s), 1); ptx::mbar_init(empty_bar(s), 1); }
-    for (int b = 0; b < 2; ++b) {
+    for (int b = 0; b < kBufs; ++b) {
       ptx::mbar_init(s_full(b), 1);
       ptx::mbar_init(p_full(b), kArrivers); ptx::mbar_init(p_empty(b), 1);
-      ptx::mbar_init(st_full(b), 1); ptx::mbar_init(st_empty(b), kSoftThreads);
     }
+    for (int b = 0; b < 2; ++b) { ptx::mbar_init(st_full(b), 1); ptx::mbar_init(st_empty(b), kSoftThreads); }
     ptx::mbar_init(x_ready, 1);
     ptx::fence_barrier_init();
     ptx::prefetch_tmap(&tm_x); ptx::prefetch_tmap(&tm_y); ptx::prefetch_tmap(&tm_z);
@@ -241,7 +247,7 @@ hop_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
       ptx::mbar_wait_cluster(x_ready, 0);
       ptx::tc_fence_after();
       auto issue_scores = [&](int j) {
-        const int b = j & 1;
+        const int b = j % kBufs;
         for (int two = 0; two < (Cfg::kTwo ? 2 : 1); ++two)
           for (int ks = 0; ks < kKStages; ++ks) {
             const int s = it % Cfg::kStages;
@@ -263,9 +269,19 @@ hop_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
       };
       issue_scores(0);
       for (int j = 0; j < nt; ++j) {
-        if (j + 1 < nt) issue_scores(j + 1);
-        const int b = j & 1;
-        ptx::mbar_wait_cluster(p_full(b), (j >> 1) & 1);
+        if (j + 1 < nt) {
+          // the accumulate MMAs that read W~ out of S(j+1)'s buffer (tile j + 1 - kBufs) must have completed -- measured
+          // without this: 16-row blocks of dV^ off by 1-4 % from run to run wherever the score operands were already
+          // waiting in the ring (see BwdCfg::kBufs)
+          if (j + 1 >= kBufs) {
+            const int jp = j + 1 - kBufs;
+            ptx::mbar_wait_cluster(p_empty(jp % kBufs), (jp / kBufs) & 1);
+            ptx::tc_fence_after();
+          }
+          issue_scores(j + 1);
+        }
+        const int b = j % kBufs;
+        ptx::mbar_wait_cluster(p_full(b), (j / kBufs) & 1);
         ptx::tc_fence_after();
         for (int kc = 0; kc < Cfg::kPC; ++kc)
           for (int nh = 0; nh < Cfg::kNH; ++nh) {
@@ -303,8 +319,8 @@ hop_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
     }
 
     for (int j = 0; j < nt; ++j) {
-      const int b = j & 1;
-      ptx::mbar_wait(s_full(b), (j >> 1) & 1);
+      const int b = j % kBufs;
+      ptx::mbar_wait(s_full(b), (j / kBufs) & 1);
       ptx::tc_fence_after();
       uint32_t v[Cfg::kC], u[Cfg::kTwo ? Cfg::kC : 1];
       ptx::tmem_ld_x32p(lane_base + b * Cfg::kBufCols + sub * Cfg::kC, v);
@@ -361,7 +377,7 @@ hop_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
     }
     if (nt > 0) {
       const uint32_t last = nt - 1;
-      ptx::mbar_wait(p_empty(last & 1), (last >> 1) & 1);
+      ptx::mbar_wait(p_empty(last % kBufs), (last / kBufs) & 1);
       ptx::tc_fence_after();
       float osc = a.out_scale;
       if (a.use_g) osc *= __ldg(a.gscale);

@@ -1,8 +1,14 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 120 python scripts/probes/bwd_once.py --simt-tails
-timeout 900 compute-sanitizer --tool initcheck --track-unused-memory no python scripts/probes/bwd_once.py --simt-tails > gpurun_out/r02i_initcheck.txt 2>&1; echo "initcheck rc=$?"
-grep -c "Uninitialized" gpurun_out/r02i_initcheck.txt; grep -A12 "Uninitialized" gpurun_out/r02i_initcheck.txt | head -60
-timeout 900 compute-sanitizer --tool racecheck python scripts/probes/bwd_once.py --simt-tails > gpurun_out/r02i_racecheck.txt 2>&1; echo "racecheck rc=$?"
-grep -c "hazard" gpurun_out/r02i_racecheck.txt; grep -B2 -A10 "hazard" gpurun_out/r02i_racecheck.txt | head -80
-tail -5 gpurun_out/r02i_racecheck.txt
+timeout 600 python scripts/probes/tails_probe.py 2>&1 | tail -8 | cut -c1-170
+for i in 1 2; do
+timeout 900 python -m pytest tests/test_backward_tc_gpu.py -m gpu -q -s > gpurun_out/r02h_bwd_tests_$i.txt 2>&1; echo "pytest rc=$?"
+grep -E "passed|failed|bad" gpurun_out/r02h_bwd_tests_$i.txt | tail -4
+done
+grep "GEMM tails" gpurun_out/r02h_bwd_tests_2.txt | tail -24
+timeout 600 python scripts/bench_backward.py > gpurun_out/r02h_backward.jsonl 2> gpurun_out/r02h_backward.err; echo "bwd bench rc=$?"
+cat gpurun_out/r02h_backward.jsonl | cut -c1-330; tail -3 gpurun_out/r02h_backward.err
+BWD="python scripts/bench_backward.py --points=16384,65536,256"
+timeout 300 $BWD > gpurun_out/r02h_bwd_plain.log 2>&1 &&
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/r02h_bwd_launches.csv $BWD > gpurun_out/r02h_bwd_launches_ncu.log 2>&1
+echo "ncu rc=$?"

@@ -1,4 +1,4 @@
-"""Run-to-run differences of the tensor-core backward's gradients (same inputs, fp32 tails): which of dq / dK^ / dV^ moves."""
+"""Where do two runs of the same tensor-core backward differ?  (rows of d lookup_weights = pattern rows of dV^ / dK^)"""
 import os, sys, json
 import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -6,7 +6,7 @@ sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
 import hflayers
 from oracle import hflayers_oracle as O
 from util import randomize_, rel_l2
-for (D, P, N) in [(256, 5000, 7001), (256, 4096, 8192), (256, 65536, 2048), (128, 8192, 4096)]:
+for (D, P, N) in [(256, 4096, 8192), (256, 65536, 2048)]:
     kw = dict(input_size=D, quantity=P, stored_pattern_as_static=True, state_pattern_as_static=True)
     ref = randomize_(O.HopfieldLayer(**kw), 95, 1.0)
     g = torch.Generator().manual_seed(96)
@@ -19,15 +19,13 @@ for (D, P, N) in [(256, 5000, 7001), (256, 4096, 8192), (256, 65536, 2048), (128
         dut.zero_grad(set_to_none=True)
         xd = x.clone().requires_grad_(True)
         (dut(xd) * w).sum().backward(); torch.cuda.synchronize()
-        out = {k: v.grad.clone() for k, v in dut.named_parameters()}
-        out["d_x"] = xd.grad.clone()
-        return out
+        return dut.lookup_weights.grad[0].clone()
     base = run()
-    keys = {"d_x": "dq", "hopfield.norm_stored_pattern.weight": "dK", "hopfield.association_core.in_proj_bias": "dV",
-            "hopfield.association_core.out_proj.weight": "fwd"}
-    worst = {v: 0.0 for v in keys.values()}
-    for i in range(8):
+    for i in range(4):
         a = run()
-        for k, tag in keys.items():
-            worst[tag] = max(worst[tag], float(rel_l2(a[k], base[k])))
-    print(json.dumps({"D": D, "P": P, "N": N, "worst_run_to_run": worst}), flush=True)
+        d = (a - base).norm(dim=1) / base.norm(dim=1).clamp_min(1e-30)
+        bad = (d > 1e-5).nonzero().flatten()
+        top = torch.topk(d, 8)
+        print(json.dumps({"D": D, "P": P, "N": N, "rel_l2": float(rel_l2(a, base)), "rows_over_1e-5": int(bad.numel()),
+                          "first_bad": bad[:12].tolist(), "last_bad": bad[-4:].tolist(),
+                          "top_rows": top.indices.tolist(), "top_vals": [round(float(v), 5) for v in top.values]}), flush=True)
