@@ -399,6 +399,11 @@ hop_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
                                   __uint_as_float(o[4 * q4 + 2]) * osc, __uint_as_float(o[4 * q4 + 3]) * osc));
         }
       }
+      // The REDs above must be PERFORMED before this CTA retires: without the fence the kernels that read the result right
+      // behind this launch (absmax / pack / column sums of dV^, the dq fix-up) saw run-to-run differences of 1e-4 .. 1e-3
+      // wherever the grid ran in more than one wave or several CTAs added into the same rows (measured with
+      // scripts/probes/bwd_determinism.py; 1e-7 with the fence)
+      __threadfence();
       ptx::tc_fence_before();
     }
   }
@@ -563,6 +568,9 @@ TcBwdWs carve_bwd(void* ws, int n, int h, int dv) {
 
 // streamed-axis splits: the smallest count that fills >= 90 % of the last wave of CTA pairs, >= 8 tiles each
 int bwd_splits(int pairs, int tiles) {
+#ifdef HOP_BWD_SPLITS           // (experiment builds)
+  return HOP_BWD_SPLITS < tiles ? HOP_BWD_SPLITS : tiles;
+#endif
   const int slots = num_sms() / 2;
   int best = 1;
   double best_eff = 0.0;

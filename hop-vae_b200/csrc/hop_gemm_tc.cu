@@ -177,6 +177,7 @@ hop_gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
         }
       }
     }
+    if (g.atomic) __threadfence();      // REDs performed before the CTA retires (see hop_bwd_tc.cu's epilogue)
     ptx::tc_fence_before();
   }
   __syncthreads();

@@ -1,11 +1,10 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 600 python scripts/probes/tails_probe.py 2>&1 | tail -8 | cut -c1-170
+timeout 600 python scripts/probes/bwd_determinism.py > gpurun_out/r02h_bwd_determinism.jsonl 2>&1; cut -c1-330 gpurun_out/r02h_bwd_determinism.jsonl | tail -7
 for i in 1 2; do
 timeout 900 python -m pytest tests/test_backward_tc_gpu.py -m gpu -q -s > gpurun_out/r02h_bwd_tests_$i.txt 2>&1; echo "pytest rc=$?"
-grep -E "passed|failed|bad" gpurun_out/r02h_bwd_tests_$i.txt | tail -4
+grep -E "passed|failed|bad" gpurun_out/r02h_bwd_tests_$i.txt | tail -3
 done
-grep "GEMM tails" gpurun_out/r02h_bwd_tests_2.txt | tail -24
 timeout 600 python scripts/bench_backward.py > gpurun_out/r02h_backward.jsonl 2> gpurun_out/r02h_backward.err; echo "bwd bench rc=$?"
 cat gpurun_out/r02h_backward.jsonl | cut -c1-330; tail -3 gpurun_out/r02h_backward.err
 BWD="python scripts/bench_backward.py --points=16384,65536,256"
