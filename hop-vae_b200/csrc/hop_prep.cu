@@ -280,11 +280,9 @@ int launch_prepare_patterns(const hop_desc& d, const hop_params& p, const hop_pa
     HOP_TRY(launch_ln_linear(k, st));                                   // K^ path (no contraction when K is static)
     auto pack = [&](const float* x, int rows, int rows_pad, int w, int has_ln, const float* lw, const float* lb,
                     float* y, void* y16, void* y16lo, void* yt16) {
-      LnLinearArgs a{};
-      a.x = x; a.rows = rows; a.rows_pad = rows_pad; a.din = w; a.has_ln = has_ln; a.ln_w = lw; a.ln_b = lb;
-      a.ln_eps = d.ln_eps; a.w = nullptr; a.b = nullptr; a.dout = w; a.scale = 1.f; a.y = y; a.y16 = y16;
-      a.y16lo = y16lo; a.yt16 = yt16; a.bf16 = 0; a.lo_scale = kGemmLoScale;
-      return launch_ln_linear(a, st);
+      (void)y;                            // (no fp32 copy is needed anywhere on this path)
+      Pack16Args a{x, rows, rows_pad, w, has_ln, lw, lb, d.ln_eps, nullptr, y16, y16lo, yt16, nullptr};
+      return launch_pack16(a, st);
     };
     HOP_TRY(pack(Wt, d.n_patterns, ppad, d.d_in, (d.flags & HOP_F_NORM_PROJ) ? 1 : 0, p.ln_proj_w, p.ln_proj_b, nullptr,
                  s.a_hi, s.a_lo, nullptr));                             // LN_v(Wt) as a hi + lo pair
@@ -328,7 +326,108 @@ int launch_prepare_patterns(const hop_desc& d, const hop_params& p, const hop_pa
   return HOP_OK;
 }
 
+// ------------------------------------------------------------------ dedicated pack pass
+// x [-> LayerNorm] [/ *range] -> fp16 hi [+ lo] packs, row-major and / or transposed, as ONE streaming pass: 64 rows per
+// CTA, 64-column chunks through a shared-memory tile for the transposed layout (each column's 64 rows leave as one
+// 128-byte segment).  ln_linear_kernel does the same through its GEMM tiling at ~1.3 TB/s; this is the copy it should be.
+struct PackArgs {
+  const float* x; int rows, rows_pad, width;
+  int has_ln; const float* ln_w; const float* ln_b; float ln_eps;
+  const float* range_dev; float lo_scale;
+  uint16_t* y16; uint16_t* y16lo; uint16_t* yt16; uint16_t* yt16lo;
+};
+__global__ void __launch_bounds__(NT) pack16_kernel(const PackArgs a) {
+  __shared__ float tile[64][65];
+  __shared__ float s_mean[64], s_rstd[64];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int row0 = blockIdx.x * 64;
+  float sc = 1.f;
+  if (a.range_dev) { const float r = __ldg(a.range_dev); sc = r > 0.f ? 1.f / r : 1.f; }
+  if (a.has_ln) {
+    for (int r = warp; r < 64; r += NT / 32) {
+      float mean = 0.f, rstd = 1.f;
+      if (row0 + r < a.rows) warp_row_stats(a.x + (size_t)(row0 + r) * a.width, a.width, a.ln_eps, mean, rstd);
+      if (lane == 0) { s_mean[r] = mean; s_rstd[r] = rstd; }
+    }
+    __syncthreads();
+  }
+  const bool tr = a.yt16 != nullptr;
+  const int c4 = (tid & 15) * 4, rq = tid >> 4;            // this thread's 4 columns of the chunk, its row within 16
+  for (int c0 = 0; c0 < a.width; c0 += 64) {
+    const int c = c0 + c4;
+    float4 w4 = make_float4(1.f, 1.f, 1.f, 1.f), b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (a.has_ln && c < a.width) {
+      if (a.ln_w) w4 = __ldg(reinterpret_cast<const float4*>(a.ln_w + c));
+      if (a.ln_b) b4 = __ldg(reinterpret_cast<const float4*>(a.ln_b + c));
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int r = rq + 16 * i, gr = row0 + r;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (gr < a.rows && c < a.width) {
+        v = __ldg(reinterpret_cast<const float4*>(a.x + (size_t)gr * a.width + c));
+        if (a.has_ln) {
+          const float m = s_mean[r], rs = s_rstd[r];
+          v.x = (v.x - m) * rs * w4.x + b4.x; v.y = (v.y - m) * rs * w4.y + b4.y;
+          v.z = (v.z - m) * rs * w4.z + b4.z; v.w = (v.w - m) * rs * w4.w + b4.w;
+        }
+        v.x *= sc; v.y *= sc; v.z *= sc; v.w *= sc;
+      }
+      if (gr < a.rows_pad && c < a.width) {
+        const uint16_t h0 = to16(v.x, 0), h1 = to16(v.y, 0), h2 = to16(v.z, 0), h3 = to16(v.w, 0);
+        if (a.y16)
+          *reinterpret_cast<uint2*>(a.y16 + (size_t)gr * a.width + c) = make_uint2(h0 | ((uint32_t)h1 << 16), h2 | ((uint32_t)h3 << 16));
+        if (a.y16lo) {
+          const uint16_t l0 = to16((v.x - from16(h0, 0)) * a.lo_scale, 0), l1 = to16((v.y - from16(h1, 0)) * a.lo_scale, 0);
+          const uint16_t l2 = to16((v.z - from16(h2, 0)) * a.lo_scale, 0), l3 = to16((v.w - from16(h3, 0)) * a.lo_scale, 0);
+          *reinterpret_cast<uint2*>(a.y16lo + (size_t)gr * a.width + c) = make_uint2(l0 | ((uint32_t)l1 << 16), l2 | ((uint32_t)l3 << 16));
+        }
+      }
+      if (tr) { tile[r][c4] = v.x; tile[r][c4 + 1] = v.y; tile[r][c4 + 2] = v.z; tile[r][c4 + 3] = v.w; }
+    }
+    if (tr) {
+      __syncthreads();
+      // column (tid >> 2) of the chunk, rows 16 (tid & 3) .. +15: 32 contiguous bytes per thread, 128 per column
+      const int col = tid >> 2, rs0 = (tid & 3) * 16, gc = c0 + col;
+      if (gc < a.width && row0 + rs0 < a.rows_pad) {
+        uint32_t hi[8], lo[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float v0 = tile[rs0 + 2 * e][col], v1 = tile[rs0 + 2 * e + 1][col];
+          const uint16_t h0 = to16(v0, 0), h1 = to16(v1, 0);
+          hi[e] = h0 | ((uint32_t)h1 << 16);
+          lo[e] = to16((v0 - from16(h0, 0)) * a.lo_scale, 0) | ((uint32_t)to16((v1 - from16(h1, 0)) * a.lo_scale, 0) << 16);
+        }
+        uint4* dst = reinterpret_cast<uint4*>(a.yt16 + (size_t)gc * a.rows_pad + row0 + rs0);
+        dst[0] = make_uint4(hi[0], hi[1], hi[2], hi[3]); dst[1] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+        if (a.yt16lo) {
+          uint4* dl = reinterpret_cast<uint4*>(a.yt16lo + (size_t)gc * a.rows_pad + row0 + rs0);
+          dl[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]); dl[1] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+        }
+      }
+      __syncthreads();
+    }
+  }
+}
+// applies when the layouts allow the vector accesses above; else the caller takes ln_linear_kernel
+static bool pack16_fast_ok(const Pack16Args& p) {
+  auto al = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+  return p.width % 4 == 0 && p.rows_pad % 64 == 0 && p.rows_pad > 0 && al(p.x) && al(p.ln_w) && al(p.ln_b) && al(p.y16) &&
+         al(p.y16lo) && al(p.yt16) && al(p.yt16lo);
+}
+static int launch_pack16_fast(const PackArgs& a, cudaStream_t st) {
+  pack16_kernel<<<a.rows_pad / 64, NT, 0, st>>>(a);
+  HOP_LAUNCH_CHECK("pack16_kernel");
+  return HOP_OK;
+}
+
 int launch_pack16(const Pack16Args& p, cudaStream_t st) {
+  if (pack16_fast_ok(p)) {
+    PackArgs f{p.x, p.rows, p.rows_pad, p.width, p.has_ln, p.ln_w, p.ln_b, p.ln_eps, p.range_dev, kGemmLoScale,
+               static_cast<uint16_t*>(p.y16), static_cast<uint16_t*>(p.y16lo), static_cast<uint16_t*>(p.yt16),
+               static_cast<uint16_t*>(p.yt16lo)};
+    return launch_pack16_fast(f, st);
+  }
   LnLinearArgs a{};
   a.x = p.x; a.rows = p.rows; a.rows_pad = p.rows_pad; a.din = p.width; a.has_ln = p.has_ln; a.ln_w = p.ln_w; a.ln_b = p.ln_b;
   a.ln_eps = p.ln_eps; a.w = nullptr; a.b = nullptr; a.dout = p.width; a.scale = 1.f; a.y = nullptr;
