@@ -508,13 +508,17 @@ def gpu_run(args):
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         return float(tt.item())
 
-    # one-off pattern-side preparation (cached per parameter version; outside `value` and `e2e`): timed once, cold
+    # one-off pattern-side preparation (cached per parameter version; outside `value` and `e2e`): the SECOND call of the
+    # process (the first one also pays the lazy loading of its kernels), caches cold (L2 flushed)
     prep_ms = None
     if not sharded:
-        layer.invalidate()
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         with torch.no_grad():
+            layer.invalidate()
+            layer._prepared(layer.param_pack(), layer.spec(), path)
+            layer.invalidate()
+            torch.empty(256 << 20, dtype=torch.uint8, device=dev).zero_()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record(); layer._prepared(layer.param_pack(), layer.spec(), path); e1.record()
         torch.cuda.synchronize()
         prep_ms = e0.elapsed_time(e1)

@@ -253,6 +253,8 @@ bool prep_uses_gemm(const hop_desc& d) {
 
 size_t prepare_scratch_bytes(const hop_desc& d) { return prep_uses_gemm(d) ? carve_prep(nullptr, d).total : 0; }
 
+int launch_ln_pack(const LnLinearArgs& a, cudaStream_t st);   // below: the pack pass where the job is a pure LayerNorm
+
 int launch_prepare_patterns(const hop_desc& d, const hop_params& p, const hop_patterns& pt, int path,
                             cudaStream_t st) {
   const bool tc = (path == HOP_PATH_TC_F16 || path == HOP_PATH_TC_BF16);
@@ -277,7 +279,7 @@ int launch_prepare_patterns(const hop_desc& d, const hop_params& p, const hop_pa
   if (tc && !bf16 && pt.scratch && prep_uses_gemm(d)) {
     // V^ = LN_v(Wt) Wv^T + bv and (V^ Wo^T) on the tensor pipe; every pack kernel around them is a pass over HBM
     const PrepScratch s = carve_prep(pt.scratch, d);
-    HOP_TRY(launch_ln_linear(k, st));                                   // K^ path (no contraction when K is static)
+    HOP_TRY(launch_ln_pack(k, st));                                     // K^ path (no contraction when K is static)
     auto pack = [&](const float* x, int rows, int rows_pad, int w, int has_ln, const float* lw, const float* lb,
                     float* y, void* y16, void* y16lo, void* yt16) {
       (void)y;                            // (no fp32 copy is needed anywhere on this path)
@@ -335,6 +337,8 @@ struct PackArgs {
   int has_ln; const float* ln_w; const float* ln_b; float ln_eps;
   const float* range_dev; float lo_scale;
   uint16_t* y16; uint16_t* y16lo; uint16_t* yt16; uint16_t* yt16lo;
+  float* y;            // fp32 copy (rows, width) or nullptr
+  float* norm_max;     // [1]: max over rows of ||y_row||_2 (atomic max on the float's bits; zeroed by the caller) or nullptr
 };
 __global__ void __launch_bounds__(NT) pack16_kernel(const PackArgs a) {
   __shared__ float tile[64][65];
@@ -353,6 +357,7 @@ __global__ void __launch_bounds__(NT) pack16_kernel(const PackArgs a) {
   }
   const bool tr = a.yt16 != nullptr;
   const int c4 = (tid & 15) * 4, rq = tid >> 4;            // this thread's 4 columns of the chunk, its row within 16
+  float sq[4] = {0.f, 0.f, 0.f, 0.f};                      // partial ||row||^2 of this thread's four rows
   for (int c0 = 0; c0 < a.width; c0 += 64) {
     const int c = c0 + c4;
     float4 w4 = make_float4(1.f, 1.f, 1.f, 1.f), b4 = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -372,6 +377,8 @@ __global__ void __launch_bounds__(NT) pack16_kernel(const PackArgs a) {
           v.z = (v.z - m) * rs * w4.z + b4.z; v.w = (v.w - m) * rs * w4.w + b4.w;
         }
         v.x *= sc; v.y *= sc; v.z *= sc; v.w *= sc;
+        if (a.y) *reinterpret_cast<float4*>(a.y + (size_t)gr * a.width + c) = v;
+        sq[i] += (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
       }
       if (gr < a.rows_pad && c < a.width) {
         const uint16_t h0 = to16(v.x, 0), h1 = to16(v.y, 0), h2 = to16(v.z, 0), h3 = to16(v.w, 0);
@@ -408,6 +415,15 @@ __global__ void __launch_bounds__(NT) pack16_kernel(const PackArgs a) {
       __syncthreads();
     }
   }
+  if (a.norm_max) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float v = sq[i];
+#pragma unroll
+      for (int off = 8; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);     // the 16 threads of a row
+      if ((tid & 15) == 0 && v > 0.f) atomicMax(reinterpret_cast<int*>(a.norm_max), __float_as_int(sqrtf(v)));
+    }
+  }
 }
 // applies when the layouts allow the vector accesses above; else the caller takes ln_linear_kernel
 static bool pack16_fast_ok(const Pack16Args& p) {
@@ -421,11 +437,23 @@ static int launch_pack16_fast(const PackArgs& a, cudaStream_t st) {
   return HOP_OK;
 }
 
+int launch_ln_pack(const LnLinearArgs& a, cudaStream_t st) {
+  auto al = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+  const bool fast = a.w == nullptr && !a.bf16 && a.scale == 1.f && a.dout == a.din && a.din % 4 == 0 && a.rows_pad % 64 == 0 &&
+                    a.rows_pad >= a.rows && (a.y16 || a.yt16 || a.y16lo) && al(a.x) && al(a.ln_w) && al(a.ln_b) && al(a.y) &&
+                    al(a.y16) && al(a.y16lo) && al(a.yt16) && al(a.yt16lo) && (a.yt16 || !a.yt16lo);
+  if (!fast) return launch_ln_linear(a, st);
+  PackArgs f{a.x, a.rows, a.rows_pad, a.din, a.has_ln, a.ln_w, a.ln_b, a.ln_eps, a.range_dev, a.lo_scale > 0.f ? a.lo_scale : 1.f,
+             static_cast<uint16_t*>(a.y16), static_cast<uint16_t*>(a.y16lo), static_cast<uint16_t*>(a.yt16),
+             static_cast<uint16_t*>(a.yt16lo), a.y, a.norm_max};
+  return launch_pack16_fast(f, st);
+}
+
 int launch_pack16(const Pack16Args& p, cudaStream_t st) {
   if (pack16_fast_ok(p)) {
     PackArgs f{p.x, p.rows, p.rows_pad, p.width, p.has_ln, p.ln_w, p.ln_b, p.ln_eps, p.range_dev, kGemmLoScale,
                static_cast<uint16_t*>(p.y16), static_cast<uint16_t*>(p.y16lo), static_cast<uint16_t*>(p.yt16),
-               static_cast<uint16_t*>(p.yt16lo)};
+               static_cast<uint16_t*>(p.yt16lo), nullptr, nullptr};
     return launch_pack16_fast(f, st);
   }
   LnLinearArgs a{};

@@ -116,3 +116,25 @@ def test_bottleneck_chain_refuses_training_and_foreign_shapes(hf):
     wide = hf.HopfieldLayer(input_size=128, quantity=64, stored_pattern_as_static=True, state_pattern_as_static=True).cuda()
     with torch.no_grad(), pytest.raises(Exception):
         hf.bottleneck_forward(wide, dut.embedding_to_index, dut.index_to_embedding, torch.randn(4, 128, device="cuda"), 512)
+
+
+def test_channels_last_conv_stacks_hand_the_latents_over_without_a_copy(hf):
+    """SURVEY.md 8(f)-2.  With the conv stacks in `channels_last` (one `.to(memory_format=...)` by the caller, cuDNN's
+    preferred layout on this GPU anyway) `pre_vq_conv`'s output already IS the (B, H, W, C) order the Hopfield layer
+    reads: the reference's `z.permute(0, 2, 3, 1).contiguous()` (HopVAE.py:252) returns a view of the same storage
+    instead of launching a transpose copy, and the layer consumes it as is -- same latents as the NCHW run."""
+    ref, dut = _pair(hf, H.FFHQ_64)
+    x = (torch.rand(8, 3, 64, 64, generator=torch.Generator().manual_seed(3)) - 0.5).cuda()
+    with torch.no_grad():
+        z_nchw = dut.pre_vq_conv(dut.encoder(x))
+        want = dut.bottleneck(dut.encode(x))
+        dut_cl = dut.to(memory_format=torch.channels_last)
+        z_cl = dut_cl.pre_vq_conv(dut_cl.encoder(x.contiguous(memory_format=torch.channels_last)))
+        assert z_cl.is_contiguous(memory_format=torch.channels_last)
+        handed = z_cl.permute(0, 2, 3, 1)
+        assert handed.is_contiguous()                                  # the reference's .contiguous() is a no-op here ...
+        assert handed.contiguous().data_ptr() == z_cl.data_ptr()       # ... it returns the same storage: no copy kernel
+        r = dut.cfg.representation_dim
+        got = dut_cl.bottleneck_fused(handed.contiguous().view(-1, r * r, dut.cfg.embedding_dim))
+    assert rel_l2(z_cl, z_nchw) < 1e-4            # cuDNN picks another algorithm for the other layout
+    assert rel_l2(got["emb"], want["emb"]) < 1e-4
