@@ -79,7 +79,8 @@ class HopPeerMerge(C.Structure):
 
 EXPORTS = ["hop_sm100_peer_merge", "hop_sm100_enable_peer_access", "hop_sm100_ipc_export", "hop_sm100_ipc_import",
            "hop_sm100_ipc_close", "hop_sm100_select_train_path", "hop_sm100_repair_rows", "hop_sm100_bottleneck_forward",
-           "hop_sm100_bottleneck_workspace_bytes", "hop_sm100_version", "hop_sm100_last_error", "hop_sm100_select_path", "hop_sm100_pattern_bytes",
+           "hop_sm100_bottleneck_workspace_bytes", "hop_sm100_bottleneck_forward_static",
+           "hop_sm100_bottleneck_static_max_rows", "hop_sm100_version", "hop_sm100_last_error", "hop_sm100_select_path", "hop_sm100_pattern_bytes",
            "hop_sm100_workspace_bytes", "hop_sm100_prepare_patterns", "hop_sm100_forward", "hop_sm100_backward",
            "hop_sm100_merge_shards", "hop_sm100_out_projection", "hop_sm100_launch_count"]
 
@@ -110,6 +111,10 @@ def load() -> C.CDLL:
     lib.hop_sm100_bottleneck_forward.restype = C.c_int
     lib.hop_sm100_bottleneck_forward.argtypes = [P(HopDesc), P(HopParams), P(HopPatterns), C.c_int32] + [C.c_void_p] * 7 + [
         C.c_size_t, C.c_void_p]
+    lib.hop_sm100_bottleneck_forward_static.restype = C.c_int
+    lib.hop_sm100_bottleneck_forward_static.argtypes = [P(HopDesc), P(HopParams), P(HopPatterns), C.c_int32] + [C.c_void_p] * 7
+    lib.hop_sm100_bottleneck_static_max_rows.restype = C.c_int
+    lib.hop_sm100_bottleneck_static_max_rows.argtypes = []
     lib.hop_sm100_repair_rows.restype = C.c_int
     lib.hop_sm100_repair_rows.argtypes = [P(HopDesc), C.c_void_p, C.c_void_p, P(C.c_int32)]
     lib.hop_sm100_select_train_path.restype = C.c_int

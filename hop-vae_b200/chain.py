@@ -27,7 +27,8 @@ _ws_cache: Dict[tuple, Tensor] = {}
 
 
 def bottleneck_forward(hopfield, embedding_to_index, index_to_embedding, z: Tensor, num_levels: int,
-                       want_logits: bool = True, want_recon: bool = True, want_idx: bool = False) -> Dict[str, Tensor]:
+                       want_logits: bool = True, want_recon: bool = True, want_idx: bool = False,
+                       static_scratch: bool = False) -> Dict[str, Tensor]:
     """z (..., D) float32 CUDA -> dict(emb, logits, idx_q, emb_recon, emb_recon_loss[, idx]) with the reference's shapes
     (leading dimensions of z kept).  `idx_q` are the integer levels the prior is fitted on (HopVAE.py:279-283);
     `idx` = idx_q / (num_levels - 1) costs one more (elementwise) launch and is only built when asked for."""
@@ -62,6 +63,15 @@ def bottleneck_forward(hopfield, embedding_to_index, index_to_embedding, z: Tens
     idx_q = torch.empty((n, d_idx), device=dev, dtype=torch.float32)
     recon = torch.empty((n, d_emb), device=dev, dtype=torch.float32) if want_recon else None
     mse = torch.empty((), device=dev, dtype=torch.float32)
+    if static_scratch:
+        # the library's built-in scratch (hop_sm100_bottleneck_forward_static): no workspace, nothing allocated by the
+        # call; rows <= hop_sm100_bottleneck_static_max_rows(), calls on one GPU must not overlap
+        with _on_device(dev):
+            cabi.check(lib.hop_sm100_bottleneck_forward_static(descs, params, pats, int(num_levels), cabi.ptr(x),
+                                                               cabi.ptr(emb), cabi.ptr(logits), cabi.ptr(idx_q),
+                                                               cabi.ptr(recon), cabi.ptr(mse), _stream(dev)),
+                       "hop_sm100_bottleneck_forward_static")
+        return _results(emb, logits, idx_q, recon, mse, lead, d_emb, d_idx, num_levels, want_idx)
     need = C.c_size_t(0)
     cabi.check(lib.hop_sm100_bottleneck_workspace_bytes(n, C.byref(need)), "hop_sm100_bottleneck_workspace_bytes")
     key = (dev, int(need.value))
@@ -73,6 +83,10 @@ def bottleneck_forward(hopfield, embedding_to_index, index_to_embedding, z: Tens
                                                     cabi.ptr(logits), cabi.ptr(idx_q), cabi.ptr(recon), cabi.ptr(mse),
                                                     cabi.ptr(ws), int(need.value), _stream(dev)),
                    "hop_sm100_bottleneck_forward")
+    return _results(emb, logits, idx_q, recon, mse, lead, d_emb, d_idx, num_levels, want_idx)
+
+
+def _results(emb, logits, idx_q, recon, mse, lead, d_emb, d_idx, num_levels, want_idx):
     out = dict(emb=emb.reshape(*lead, d_emb), idx_q=idx_q.reshape(*lead, d_idx), emb_recon_loss=mse)
     if want_idx:
         out["idx"] = (idx_q / float(num_levels - 1)).reshape(*lead, d_idx)

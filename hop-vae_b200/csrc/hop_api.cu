@@ -404,6 +404,21 @@ int hop_sm100_bottleneck_forward(const hop_desc* descs, const hop_params* params
                       workspace_bytes, (cudaStream_t)stream);
 }
 
+int hop_sm100_bottleneck_forward_static(const hop_desc* descs, const hop_params* params, const hop_patterns* patterns,
+                                        int32_t num_levels, const float* z, float* emb, float* logits, float* idx_q,
+                                        float* emb_recon, float* mse, void* stream) {
+  if (!descs || !params || !patterns) HOP_FAIL(HOP_ERR_BAD_ARG, "bottleneck: descs / params / patterns is NULL");
+  for (int l = 0; l < 3; ++l) HOP_TRY(validate_desc(descs + l));
+  HOP_TRY(device_info(nullptr));
+  if (num_levels < 2) HOP_FAIL(HOP_ERR_BAD_ARG, "bottleneck: num_levels must be >= 2");
+  if (!emb) HOP_FAIL(HOP_ERR_BAD_ARG, "bottleneck: emb is NULL");
+  if (!aligned16(z)) HOP_FAIL(HOP_ERR_BAD_ALIGN, "bottleneck: z must be 16-byte aligned");
+  return launch_chain_static(descs, params, patterns, (float)(num_levels - 1), z, emb, logits, idx_q, emb_recon, mse,
+                             (cudaStream_t)stream);
+}
+
+int hop_sm100_bottleneck_static_max_rows(void) { return chain_static_max_rows(); }
+
 int hop_sm100_repair_rows(const hop_desc* desc, const void* workspace, void* stream, int32_t* rows_out) {
   HOP_TRY(validate_desc(desc));
   if (!rows_out) HOP_FAIL(HOP_ERR_BAD_ARG, "rows_out is NULL");

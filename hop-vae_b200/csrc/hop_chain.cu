@@ -24,6 +24,8 @@
 // patterns (H = D_in), pattern projection D_in -> D_in, out-projection.  Widths up to 64.
 #include <cooperative_groups.h>
 
+#include <mutex>
+
 #include "hop_common.cuh"
 
 namespace cg = cooperative_groups;
@@ -496,6 +498,47 @@ int launch_chain(const hop_desc* d, const hop_params* p, const hop_patterns* pt,
   a.mse = mse;
   HOP_CUDA(cudaMemsetAsync(a.done, 0, sizeof(uint32_t), st));
   return launch_chain_inst(a, d[0].tune_splits, st);      // (hop_desc.tune_splits of the first layer: experiments)
+}
+
+// ------------------------------------------------------------------ allocation-free variant
+// hop_sm100_bottleneck_forward_static: the same launch with its workspace (completion counter + per-tile squared-error
+// partials) in a file-scope device array instead of caller memory -- for callers that cannot allocate (CUDA graph
+// capture, tight serving loops).  Every GPU that loads the library holds the array until exit; every call on a device
+// shares it, so calls that overlap on that GPU (two streams) race on the counter and the partials.  The launch clears
+// the counter itself (launch_chain's 4-byte memset) and every partial slot it reads is written first, so nothing else
+// has to start at zero.
+constexpr int kStaticMaxRows = 262144;                       // 28 x config 3's 9,248 latent rows
+constexpr size_t kStaticScratchBytes = 256 + (size_t)(kStaticMaxRows / 16) * sizeof(float);     // = chain_workspace_bytes(max)
+static __device__ __align__(256) unsigned char g_chain_scratch[kStaticScratchBytes];
+
+int chain_static_max_rows() { return kStaticMaxRows; }
+
+int launch_chain_static(const hop_desc* d, const hop_params* p, const hop_patterns* pt, float levels, const float* z,
+                        float* emb, float* logits, float* idx_q, float* emb_recon, float* mse, cudaStream_t st) {
+  if (d[0].n_rows > kStaticMaxRows)
+    HOP_FAIL(HOP_ERR_BAD_SHAPE, "bottleneck (static scratch): %d rows exceed the built-in maximum of %d; use "
+             "hop_sm100_bottleneck_forward with a caller workspace", d[0].n_rows, kStaticMaxRows);
+  // In host code `g_chain_scratch` is only a stand-in for the symbol: its device address is looked up once per device,
+  // with that device current, and that pointer is what the kernel gets.
+  constexpr int kMaxDevices = 64;
+  static void* addr[kMaxDevices] = {};
+  static std::mutex mu;
+  int dev = -1;
+  HOP_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) HOP_FAIL(HOP_ERR_CUDA, "bottleneck (static scratch): device ordinal %d out of range", dev);
+  void* ptr = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    if (addr[dev] == nullptr) {
+      void* q = nullptr;
+      const cudaError_t e = cudaGetSymbolAddress(&q, g_chain_scratch);
+      if (e != cudaSuccess || q == nullptr)
+        HOP_FAIL(HOP_ERR_CUDA, "bottleneck (static scratch): cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+      addr[dev] = q;
+    }
+    ptr = addr[dev];
+  }
+  return launch_chain(d, p, pt, levels, z, emb, logits, idx_q, emb_recon, mse, ptr, kStaticScratchBytes, st);
 }
 
 }  // namespace hop

@@ -154,6 +154,10 @@ int chain_supported(const hop_desc* d3);
 int launch_chain(const hop_desc* d3, const hop_params* p3, const hop_patterns* pt3, float levels, const float* z,
                  float* emb, float* logits, float* idx_q, float* emb_recon, float* mse, void* ws, size_t ws_bytes,
                  cudaStream_t st);
+// (allocation-free variant: the workspace is a file-scope device array of hop_chain.cu, rows <= chain_static_max_rows())
+int chain_static_max_rows();
+int launch_chain_static(const hop_desc* d3, const hop_params* p3, const hop_patterns* pt3, float levels, const float* z,
+                        float* emb, float* logits, float* idx_q, float* emb_recon, float* mse, cudaStream_t st);
 // hop_gemm_tc.cu -- C[M x N] = A[M x K] . B[N x K]^T (+ bias) on tcgen05, fp16 K-major operand packs, optional hi + lo pairs
 constexpr float kGemmLoScale = 2048.f;   // low halves of the GEMM's operand pairs are stored times 2^11
 struct TcGemmArgs {

@@ -271,6 +271,23 @@ int hop_sm100_bottleneck_forward(const hop_desc* descs, const hop_params* params
                                  float* emb_recon, float* mse,
                                  void* workspace, size_t workspace_bytes, void* stream);
 
+/* hop_sm100_bottleneck_forward without ANY allocation and without a caller
+ * workspace.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid it).  The kernel's
+ * scratch (completion counter + per-tile partial sums, 65,792 bytes) lives in a
+ * file-scope __device__ array of the library, held by every GPU that loads it
+ * until exit.  Limits: n_rows <= hop_sm100_bottleneck_static_max_rows()
+ * (262,144; HOP_ERR_BAD_SHAPE beyond -- use the workspace form); all calls on
+ * one GPU share the array, so calls that OVERLAP on that GPU (two streams)
+ * race -- serialise them.  Same arguments and results as
+ * hop_sm100_bottleneck_forward otherwise; calls no cudaMalloc / cudaFree.      */
+int hop_sm100_bottleneck_forward_static(const hop_desc* descs, const hop_params* params,
+                                        const hop_patterns* patterns, int32_t num_levels,
+                                        const float* z, float* emb, float* logits, float* idx_q,
+                                        float* emb_recon, float* mse, void* stream);
+int hop_sm100_bottleneck_static_max_rows(void);
+
 /* Diagnostic of HOP_F_EXACT_ARGMAX: how many rows of the last forward run with
  * this descriptor (argmax != NULL) into this workspace failed the top-1 / top-2
  * certificate and were re-scored in fp32.  Waits for `stream`.  0 rows on the
