@@ -58,7 +58,11 @@ struct BwdCfg {
   // operand, and the tensor pipe does not interlock that read against a later instruction's D write: those MMAs must
   // have COMPLETED before S(j+1) is issued.  With three buffers that is tile j-2 -- long done, no bubble; H = 512 has
   // TMEM room for two, where the issuer waits for tile j-1 (a short bubble per tile).
-  static constexpr int kBufs = (3 * kBufCols + (H >= 256 ? H / 2 : H / 2) <= 512) ? 3 : 2;
+#ifdef HOP_BWD_BUFS             // (experiment builds)
+  static constexpr int kBufs = HOP_BWD_BUFS;
+#else
+  static constexpr int kBufs = (3 * kBufCols + H / 2 <= 512) ? 3 : 2;
+#endif
   static constexpr uint32_t kTmemAcc = kBufs * kBufCols;
   static constexpr int kAccN = H >= 256 ? 256 : H;         // N of one accumulate instruction
   static constexpr int kNH = H / kAccN;                    // instructions per K step
@@ -403,7 +407,9 @@ hop_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
       // behind this launch (absmax / pack / column sums of dV^, the dq fix-up) saw run-to-run differences of 1e-4 .. 1e-3
       // wherever the grid ran in more than one wave or several CTAs added into the same rows (measured with
       // scripts/probes/bwd_determinism.py; 1e-7 with the fence)
+#ifndef HOP_BWD_NO_FENCE        // (experiment builds)
       __threadfence();
+#endif
       ptx::tc_fence_before();
     }
   }
