@@ -1,6 +1,4 @@
 #!/bin/bash
-P="--points=16384,65536,256"
-for t in default nofence bufs2 default nofence bufs2; do
-  if [ $t = default ]; then L=""; else L=$PWD/hop-vae_b200/libhop_sm100_$t.so; fi
-  echo -n "$t "; HOP_SM100_LIB=$L timeout 300 python scripts/bench_backward.py $P 2>&1 | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print(d['ms_backward'])"
-done
+mkdir -p gpurun_out
+timeout 1500 python scripts/sweep_config5.py "--points=65536,1024,0;262144,1024,0;65536,1024,1;65536,128,0;262144,128,0;65536,64,0;65536,128,3;65536,64,1" > gpurun_out/r02z_sweep_other_widths.jsonl 2> gpurun_out/r02z_sweep_other.err; echo "rc=$?"
+cut -c1-260 gpurun_out/r02z_sweep_other_widths.jsonl; tail -3 gpurun_out/r02z_sweep_other.err

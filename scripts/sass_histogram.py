@@ -29,7 +29,8 @@ print(f"# cuobjdump -sass {os.path.relpath(lib, ROOT)}: selected opcodes per ker
 for k in sorted(hist, key=lambda k: -hist[k]["(all instructions)"]):
     c = hist[k]
     name = subprocess.run(["c++filt", k], capture_output=True, text=True).stdout.strip()
-    name = re.sub(r"\(.*", "", name)
+    name = name.replace("(anonymous namespace)::", "").replace("void ", "")
+    name = re.sub(r"\((CUtensorMap_st|hop::|int|float|const|unsigned).*", "", name)      # drop the parameter list
     print(f"\n{name}")
     print("  " + ", ".join(f"{op} {n}" for op, n in sorted(c.items(), key=lambda t: (-t[1], t[0]))))
 tot = collections.Counter()
