@@ -116,7 +116,7 @@ def load() -> C.CDLL:
     lib.hop_sm100_bottleneck_static_max_rows.restype = C.c_int
     lib.hop_sm100_bottleneck_static_max_rows.argtypes = []
     lib.hop_sm100_repair_rows.restype = C.c_int
-    lib.hop_sm100_repair_rows.argtypes = [P(HopDesc), C.c_void_p, C.c_void_p, P(C.c_int32)]
+    lib.hop_sm100_repair_rows.argtypes = [P(HopDesc), C.c_void_p, C.c_void_p, P(C.c_int32), P(C.c_int32)]
     lib.hop_sm100_select_train_path.restype = C.c_int
     lib.hop_sm100_select_train_path.argtypes = [P(HopDesc), P(C.c_int32)]
     lib.hop_sm100_pattern_bytes.restype = C.c_int

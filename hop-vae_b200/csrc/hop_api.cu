@@ -198,7 +198,7 @@ FwdWs fwd_ws(const hop_desc& d, int path, bool exact) {
   } else if (simt_stop_rule(d)) {
     w.stat = round_up_sz(N * sizeof(float), 256);
   }
-  w.total = 2 * w.q + w.r + w.tc + w.repair + w.qfinal + 4 * w.stat + (w.stat ? 256 : 0);   // stat: lse, rowmax, ||q||, runner-up
+  w.total = 2 * w.q + w.r + w.tc + w.repair + w.qfinal + 5 * w.stat + (w.stat ? 256 : 0);   // stat: lse, rowmax, ||q||, runner-up (others, top tile)
   return w;
 }
 }  // namespace
@@ -361,7 +361,8 @@ int hop_sm100_forward(const hop_desc* desc, const hop_params* params, const hop_
   if (exact) {
     a.cert = repair_cert_args(region(off_repair), d.n_rows, d.d_assoc, patterns->kstats,
                               reinterpret_cast<float*>(region(off_stat + 2 * W.stat)),
-                              reinterpret_cast<float*>(region(off_stat + 3 * W.stat)));
+                              reinterpret_cast<float*>(region(off_stat + 3 * W.stat)),
+                              reinterpret_cast<float*>(region(off_stat + 4 * W.stat)));
     a.cert_done = &cert_done;
   }
   HOP_TRY(launch_tc_forward(a, st));
@@ -373,7 +374,7 @@ int hop_sm100_forward(const hop_desc* desc, const hop_params* params, const hop_
     r.beta = d.beta;
     r.khat = patterns->khat; r.kstats = patterns->kstats;
     r.n = d.n_rows; r.p = d.n_patterns; r.h = d.d_assoc; r.pattern_offset = d.pattern_offset;
-    r.lse = lse_w; r.rowmax = rowmax_w; r.argmax = argmax; r.rowsec = a.cert.sec;
+    r.lse = lse_w; r.rowmax = rowmax_w; r.argmax = argmax; r.rowsec = a.cert.sec; r.rowtop = a.cert.top;
     r.ws = region(off_repair); r.ws_bytes = W.repair;
     r.precertified = cert_done ? 1 : 0;
     HOP_TRY(launch_argmax_repair(r, st));
@@ -419,7 +420,8 @@ int hop_sm100_bottleneck_forward_static(const hop_desc* descs, const hop_params*
 
 int hop_sm100_bottleneck_static_max_rows(void) { return chain_static_max_rows(); }
 
-int hop_sm100_repair_rows(const hop_desc* desc, const void* workspace, void* stream, int32_t* rows_out) {
+int hop_sm100_repair_rows(const hop_desc* desc, const void* workspace, void* stream, int32_t* rows_out,
+                          int32_t* flagged_out) {
   HOP_TRY(validate_desc(desc));
   if (!rows_out) HOP_FAIL(HOP_ERR_BAD_ARG, "rows_out is NULL");
   *rows_out = 0;
@@ -428,11 +430,12 @@ int hop_sm100_repair_rows(const hop_desc* desc, const void* workspace, void* str
   if (path == HOP_PATH_FP32_SIMT || !(desc->flags & HOP_F_EXACT_ARGMAX)) return HOP_OK;
   if (!workspace) HOP_FAIL(HOP_ERR_BAD_ARG, "workspace is NULL");
   const FwdWs W = fwd_ws(*desc, path, true);
-  uint32_t flagged = 0;     // first control word of the repair region (hop_repair.cu)
+  uint32_t ctrl[4] = {0, 0, 0, 0};   // control words of the repair region (hop_repair.cu): [0] rows that failed the
+                                     // certificate, [2] rows the block check could not settle -> full fp32 pass
   HOP_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
-  HOP_CUDA(cudaMemcpy(&flagged, static_cast<const char*>(workspace) + 2 * W.q + W.r + W.tc, sizeof(flagged),
-                      cudaMemcpyDeviceToHost));
-  *rows_out = (int32_t)flagged;
+  HOP_CUDA(cudaMemcpy(ctrl, static_cast<const char*>(workspace) + 2 * W.q + W.r + W.tc, sizeof(ctrl), cudaMemcpyDeviceToHost));
+  *rows_out = (int32_t)ctrl[2];
+  if (flagged_out) *flagged_out = (int32_t)ctrl[0];
   return HOP_OK;
 }
 

@@ -103,7 +103,8 @@ struct RepairArgs {
   const float* kstats;        // [0] = max_j ||K^_j||
   int n, p, h, pattern_offset;
   const float* lse; float* rowmax; int32_t* argmax;   // results of the 16-bit pass; argmax / rowmax are corrected in place
-  const float* rowsec;        // the forward's bound on each row's runner-up score (CertArgs::sec); read when !precertified
+  float* rowsec;              // CertArgs::sec: exact maximum of the 16-bit scores outside each row's top 64-column tile
+  const float* rowtop;        // CertArgs::top: bound on the other columns of that tile (read when !precertified)
   void* ws; size_t ws_bytes;  // repair_workspace_bytes(n, h); its first 16 bytes are the control words, which the
                               // forward kernel of the same call clears (TcPassArgs::zero_words)
   int precertified;           // the forward's merge kernel already evaluated the certificate and built the list
@@ -114,9 +115,11 @@ struct RepairArgs {
 struct CertArgs {
   uint32_t* ctrl; int32_t* list; unsigned long long* best;   // repair list (ctrl == nullptr: no certificate)
   const float* kstats; float* qn;                             // max_j ||K^_j||, per-row ||q|| (N floats, written by the forward)
-  float* sec;                                                 // per-row runner-up bound (N floats, written by the forward)
+  float* sec;       // per row: EXACT maximum of the 16-bit scores outside the top 64-column thread tile (N floats; written by
+                    // the forward without a merge kernel, else by the merge kernel for the rows it flags)
+  float* top;       // per row: bound on the other columns of the top tile (N floats; forward without a merge kernel only)
 };
-CertArgs repair_cert_args(void* ws, int n, int h, const float* kstats, float* qn, float* sec);
+CertArgs repair_cert_args(void* ws, int n, int h, const float* kstats, float* qn, float* sec, float* top);
 size_t repair_workspace_bytes(int n, int h);
 int launch_argmax_repair(const RepairArgs& a, cudaStream_t st);
 // ||A_t - A_(t-1)||_F per batch item, max over items, compared with eps: sets *stopped (device) to 1 when the

@@ -124,11 +124,12 @@ struct TcKernelArgs {
   // cluster; a cluster walks its share segment by segment (a segment = one row group, a contiguous tile range)
   int streamk, sk_base, sk_rem, sk_max_seg;
   float* retrieved; float* qsave; float* lse; int32_t* argmax; float* rowmax; int pattern_offset;
-  float* rowsec;                        // per-row bound on the runner-up score (exact-argmax certificate) or nullptr
+  float* rowsec;                        // per-row EXACT maximum of the 16-bit scores outside the top 64-column thread tile
+  float* rowtop;                        // per-row bound on the other columns of that tile (both: certificate) or nullptr
   uint32_t* zero_words;                 // 4 control words of the argmax repair, cleared by CTA (0,0,0) (or nullptr)
   float* qn;                            // per-row ||q|| of the pass (exact-argmax certificate) or nullptr
   // partial outputs when splits > 1: (splits, N, D), (splits, N) x3
-  float* part_o; float* part_lse; float* part_max; int32_t* part_arg; float* part_sec;
+  float* part_o; float* part_lse; float* part_max; int32_t* part_arg; float* part_sec; float* part_top;
 };
 
 // Runner-up bound of one softmax thread (exact-index certificate, hop_repair.cu).  Next to its running maximum `tmax` a
@@ -781,7 +782,7 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
       }
       // ---- end of the pass: the pair combines (l, tmax, targ); slots of the other parity are idle
       const int pl = (g + nt - 1) & 1;
-      tsec = fmaxf(tsec, second_bound(tmax, top_sum, top_ref));
+      float ttop = second_bound(tmax, top_sum, top_ref);   // (tsec stays the exact maximum outside the top tile)
       st_shared_f32(xch_at(pl ^ 1, half, row), l);
       ptx::named_bar_sync(pair_bar, 64);
       const float l_tot = l + ld_shared_f32(xch_at(pl ^ 1, half ^ 1, row));
@@ -791,11 +792,20 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
         st_shared_f32(xch_at(pl ^ 1, 0, row), tsec);   // half 0's l slot: this thread was its only reader
       }
       ptx::named_bar_sync(pair_bar, 64);
+      float om = -INFINITY, osec = -INFINITY;
+      int oa = 0;
       if (half == 0) {
-        const float om = ld_shared_f32(xch_at(pl, 1, row));
-        const int oa = __float_as_int(ld_shared_f32(xch_at(pl, 0, row)));
-        tsec = fmaxf(fmaxf(tsec, ld_shared_f32(xch_at(pl ^ 1, 0, row))), fminf(om, tmax));
-        if (om > tmax) { tmax = om; targ = oa; }       // ties keep the lower (half-0) index
+        om = ld_shared_f32(xch_at(pl, 1, row));
+        oa = __float_as_int(ld_shared_f32(xch_at(pl, 0, row)));
+        osec = ld_shared_f32(xch_at(pl ^ 1, 0, row));
+      }
+      ptx::named_bar_sync(pair_bar, 64);               // (a fourth value needs a slot that half 0 has finished reading)
+      if (half == 1) st_shared_f32(xch_at(pl, 1, row), ttop);
+      ptx::named_bar_sync(pair_bar, 64);
+      if (half == 0) {
+        // everything the losing half saw lies at or below ITS maximum; the winner keeps its own tile's bound
+        if (om > tmax) { tsec = fmaxf(osec, tmax); ttop = ld_shared_f32(xch_at(pl, 1, row)); tmax = om; targ = oa; }
+        else tsec = fmaxf(tsec, om);                   // ties keep the lower (half-0) index
       }
       // wait for the last read-out MMA, normalise
       const uint32_t last = g + nt - 1;
@@ -858,11 +868,11 @@ hop_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constan
           if (a.splits > 1) {
             const long long o = part_row;
             a.part_lse[o] = lse; a.part_max[o] = tmax * kLn2; a.part_arg[o] = targ + a.pattern_offset;
-            a.part_sec[o] = tsec * kLn2;
+            a.part_sec[o] = tsec * kLn2; a.part_top[o] = ttop * kLn2;
           } else {
             if (a.lse) a.lse[grow] = lse;
             if (a.rowmax) a.rowmax[grow] = tmax * kLn2;
-            if (a.rowsec) a.rowsec[grow] = tsec * kLn2;
+            if (a.rowsec) { a.rowsec[grow] = tsec * kLn2; a.rowtop[grow] = ttop * kLn2; }
             if (a.argmax) a.argmax[grow] = targ + a.pattern_offset;
           }
         }
@@ -1268,10 +1278,11 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
 
     // ---- end of the pass: the four threads of a row combine (l, tmax, targ) in pattern order
     ptx::named_bar_sync(grp_bar, 128);             // every P~ word of the last tile has been read
-    tsec = fmaxf(tsec, second_bound(tmax, top_sum, top_ref));
+    const float ttop = second_bound(tmax, top_sum, top_ref);    // (tsec stays the exact maximum outside the top tile)
     st_shared_v4(xp_at(0, sub, L), __float_as_uint(l), __float_as_uint(tmax), (uint32_t)targ, __float_as_uint(tsec));
+    st_shared_v4(xp_at(1, sub, L), __float_as_uint(ttop), 0u, 0u, 0u);
     ptx::named_bar_sync(grp_bar, 128);
-    float l_tot = 0.f, best = -INFINITY, sec = -INFINITY;
+    float l_tot = 0.f, best = -INFINITY, sec = -INFINITY, top = -INFINITY;
     int best_arg = 0;
 #pragma unroll
     for (int hh = 0; hh < 2; ++hh)
@@ -1281,8 +1292,14 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
         ld_shared_v4(xp_at(0, ss, row + 64 * hh), w0, w1, w2, w3);
         l_tot += __uint_as_float(w0);
         const float om = __uint_as_float(w1);
-        sec = fmaxf(fmaxf(sec, __uint_as_float(w3)), fminf(om, best));
-        if (om > best) { best = om; best_arg = (int)w2; }    // pattern order: ties keep the lowest index
+        if (om > best) {                                     // pattern order: ties keep the lowest index
+          uint32_t t0w, t1w, t2w, t3w;
+          ld_shared_v4(xp_at(1, ss, row + 64 * hh), t0w, t1w, t2w, t3w);
+          sec = fmaxf(__uint_as_float(w3), best); top = __uint_as_float(t0w);
+          best = om; best_arg = (int)w2;
+        } else {
+          sec = fmaxf(sec, om);
+        }
       }
     const uint32_t last = nt - 1;
     ptx::mbar_wait(p_empty(last & 1), (last >> 1) & 1);
@@ -1313,11 +1330,11 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
       const float lse = kLn2 * (m_run + ptx::lg2(l_tot));
       if (a.splits > 1) {
         a.part_lse[part_row] = lse; a.part_max[part_row] = best * kLn2; a.part_arg[part_row] = best_arg + a.pattern_offset;
-        a.part_sec[part_row] = sec * kLn2;
+        a.part_sec[part_row] = sec * kLn2; a.part_top[part_row] = top * kLn2;
       } else {
         if (a.lse) a.lse[grow] = lse;
         if (a.rowmax) a.rowmax[grow] = best * kLn2;
-        if (a.rowsec) a.rowsec[grow] = sec * kLn2;
+        if (a.rowsec) { a.rowsec[grow] = sec * kLn2; a.rowtop[grow] = top * kLn2; }
         if (a.argmax) a.argmax[grow] = best_arg + a.pattern_offset;
       }
     }
@@ -1334,10 +1351,11 @@ hop_fwd_tc64_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
 
 // The exact-argmax certificate of hop_repair.cu, evaluated where the row maximum and the runner-up bound are already
 // in registers.
-__device__ __forceinline__ void certify_row(const CertArgs& c, long long r, float rowmax, float rowsec) {
+__device__ __forceinline__ void certify_row(const CertArgs& c, long long r, float rowmax, float others, float top) {
   if (c.ctrl == nullptr) return;
   const float tau = 2.f * c.qn[r] * __ldg(c.kstats) * (1.f / 1024.f) * 1.02f + 1e-5f;
-  if (rowmax - rowsec > tau) return;                                   // every other score is more than tau below
+  if (rowmax - fmaxf(others, top) > tau) return;                       // every other score is more than tau below
+  c.sec[r] = others;                                                   // for the block check of hop_repair.cu
   const uint32_t slot = atomicAdd(c.ctrl, 1u);
   c.list[slot] = (int32_t)r;
   c.best[slot] = 0ull;
@@ -1347,7 +1365,7 @@ __device__ __forceinline__ void certify_row(const CertArgs& c, long long r, floa
 template <int D>
 __global__ void tc_combine_kernel(int n, int splits, const float* __restrict__ part_o,
                                   const float* __restrict__ part_lse, const float* __restrict__ part_max,
-                                  const int32_t* __restrict__ part_arg, const float* __restrict__ part_sec,
+                                  const int32_t* __restrict__ part_arg, const float* __restrict__ part_sec, const float* __restrict__ part_top,
                                   const float* __restrict__ bias, float out_scale, float* __restrict__ retrieved, float* __restrict__ lse,
                                   int32_t* __restrict__ argmax, float* __restrict__ rowmax, const CertArgs cert) {
   const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
@@ -1365,14 +1383,14 @@ __global__ void tc_combine_kernel(int n, int splits, const float* __restrict__ p
     const int e = lane * 4 + v * 128;
     acc[v] = (bias && e < D) ? __ldg(reinterpret_cast<const float4*>(bias + e)) : make_float4(0.f, 0.f, 0.f, 0.f);
   }
-  float best = -INFINITY, sec = -INFINITY;
+  float best = -INFINITY, sec = -INFINITY, top = -INFINITY;
   int arg = 0;
   for (int s = 0; s < splits; ++s) {
     const long long o = (long long)s * n + r;
     const float w = __expf(part_lse[o] - m) * inv * out_scale;
     const float pm = part_max[o];
-    sec = fmaxf(fmaxf(sec, part_sec[o]), fminf(pm, best));
-    if (pm > best) { best = pm; arg = part_arg[o]; }   // splits are in pattern order: ties keep the lowest index
+    if (pm > best) { sec = fmaxf(part_sec[o], best); top = part_top[o]; best = pm; arg = part_arg[o]; }
+    else sec = fmaxf(sec, pm);                         // splits are in pattern order: ties keep the lowest index
 #pragma unroll
     for (int v = 0; v < kVec; ++v) {
       const int e = lane * 4 + v * 128;
@@ -1391,7 +1409,7 @@ __global__ void tc_combine_kernel(int n, int splits, const float* __restrict__ p
     if (lse) lse[r] = m + __logf(z);
     if (rowmax) rowmax[r] = best;
     if (argmax) argmax[r] = arg;
-    certify_row(cert, r, best, sec);
+    certify_row(cert, r, best, sec, top);
   }
 }
 
@@ -1407,7 +1425,7 @@ __device__ __forceinline__ int sk_cluster_of(const StreamKPlan& s, int u) {
 template <int D>
 __global__ void tc_combine_streamk_kernel(int n, StreamKPlan sk, const float* __restrict__ part_o,
                                           const float* __restrict__ part_lse, const float* __restrict__ part_max,
-                                          const int32_t* __restrict__ part_arg, const float* __restrict__ part_sec,
+                                          const int32_t* __restrict__ part_arg, const float* __restrict__ part_sec, const float* __restrict__ part_top,
                                           const float* __restrict__ bias, float out_scale, float* __restrict__ retrieved, float* __restrict__ lse,
                                           int32_t* __restrict__ argmax, float* __restrict__ rowmax, const CertArgs cert) {
   const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
@@ -1434,14 +1452,14 @@ __global__ void tc_combine_streamk_kernel(int n, StreamKPlan sk, const float* __
     const int e = lane * 4 + v * 128;
     acc[v] = (bias && e < D) ? __ldg(reinterpret_cast<const float4*>(bias + e)) : make_float4(0.f, 0.f, 0.f, 0.f);
   }
-  float best = -INFINITY, sec = -INFINITY;
+  float best = -INFINITY, sec = -INFINITY, top = -INFINITY;
   int arg = 0;
   for (int c = c0; c <= c1; ++c) {
     const long long o = slot_row(c);
     const float w = __expf(part_lse[o] - m) * inv * out_scale;
     const float pm = part_max[o];
-    sec = fmaxf(fmaxf(sec, part_sec[o]), fminf(pm, best));
-    if (pm > best) { best = pm; arg = part_arg[o]; }   // segments are in pattern order: ties keep the lowest index
+    if (pm > best) { sec = fmaxf(part_sec[o], best); top = part_top[o]; best = pm; arg = part_arg[o]; }
+    else sec = fmaxf(sec, pm);                         // segments are in pattern order: ties keep the lowest index
 #pragma unroll
     for (int v = 0; v < kVec; ++v) {
       const int e = lane * 4 + v * 128;
@@ -1460,7 +1478,7 @@ __global__ void tc_combine_streamk_kernel(int n, StreamKPlan sk, const float* __
     if (lse) lse[r] = m + __logf(z);
     if (rowmax) rowmax[r] = best;
     if (argmax) argmax[r] = arg;
-    certify_row(cert, r, best, sec);
+    certify_row(cert, r, best, sec, top);
   }
 }
 
@@ -1535,7 +1553,7 @@ int launch_d(const TcPassArgs& a, int splits, const TcLaunchOpt& opt, cudaStream
   const int nt_total = ppad / kTileP;
   k.tiles_per_split = (nt_total + splits - 1) / splits;
   k.splits = (nt_total + k.tiles_per_split - 1) / k.tiles_per_split;   // every split owns >= 1 tile
-  k.retrieved = a.retrieved; k.qsave = a.qsave; k.lse = a.lse; k.argmax = a.argmax; k.rowmax = a.rowmax; k.rowsec = a.argmax ? a.cert.sec : nullptr;
+  k.retrieved = a.retrieved; k.qsave = a.qsave; k.lse = a.lse; k.argmax = a.argmax; k.rowmax = a.rowmax; k.rowsec = a.argmax ? a.cert.sec : nullptr; k.rowtop = a.argmax ? a.cert.top : nullptr;
   k.pattern_offset = a.pattern_offset;
   k.zero_words = opt.zero_words;
   const CertArgs cert = (a.argmax && a.lse && a.rowmax) ? a.cert : CertArgs{};
@@ -1578,14 +1596,15 @@ int launch_d(const TcPassArgs& a, int splits, const TcLaunchOpt& opt, cudaStream
       sk.base = (int)(units / n_clusters); sk.rem = (int)(units % n_clusters);
       sk.max_seg = (sk.base + 1 + nt_total - 1) / nt_total + 1;
       const size_t rows = (size_t)n_clusters * sk.max_seg * kCluster * kTileM;
-      const size_t need = round_up_sz(rows * a.dv * sizeof(float), 256) + 4 * round_up_sz(rows * sizeof(float), 256);
+      const size_t need = round_up_sz(rows * a.dv * sizeof(float), 256) + 5 * round_up_sz(rows * sizeof(float), 256);
       if (!a.ws || a.ws_bytes < need) HOP_FAIL(HOP_ERR_WORKSPACE, "stream-K forward needs %zu workspace bytes, %zu given", need, a.ws_bytes);
       char* w = static_cast<char*>(a.ws);
       k.part_o = reinterpret_cast<float*>(w); w += round_up_sz(rows * a.dv * sizeof(float), 256);
       k.part_lse = reinterpret_cast<float*>(w); w += round_up_sz(rows * sizeof(float), 256);
       k.part_max = reinterpret_cast<float*>(w); w += round_up_sz(rows * sizeof(float), 256);
       k.part_arg = reinterpret_cast<int32_t*>(w); w += round_up_sz(rows * sizeof(int32_t), 256);
-    k.part_sec = reinterpret_cast<float*>(w);
+    k.part_sec = reinterpret_cast<float*>(w); w += round_up_sz(rows * sizeof(float), 256);
+    k.part_top = reinterpret_cast<float*>(w);
       k.streamk = 1; k.sk_base = sk.base; k.sk_rem = sk.rem; k.sk_max_seg = sk.max_seg;
       k.splits = 2;                       // (> 1: every segment leaves a partial for the merge)
       cudaLaunchConfig_t cfg = oc;
@@ -1595,7 +1614,7 @@ int launch_d(const TcPassArgs& a, int splits, const TcLaunchOpt& opt, cudaStream
       HOP_LAUNCH_CHECK("hop_fwd_tc_kernel");
       const int threads = 256, rows_per_block = threads / 32;
       tc_combine_streamk_kernel<H><<<(a.n + rows_per_block - 1) / rows_per_block, threads, 0, st>>>(
-          a.n, sk, k.part_o, k.part_lse, k.part_max, k.part_arg, k.part_sec, a.bias, a.out_scale, a.retrieved, a.lse, a.argmax,
+          a.n, sk, k.part_o, k.part_lse, k.part_max, k.part_arg, k.part_sec, k.part_top, a.bias, a.out_scale, a.retrieved, a.lse, a.argmax,
           a.rowmax, cert);
       HOP_LAUNCH_CHECK("tc_combine_streamk_kernel");
       if (cert.ctrl && a.cert_done) *a.cert_done = true;
@@ -1613,7 +1632,8 @@ int launch_d(const TcPassArgs& a, int splits, const TcLaunchOpt& opt, cudaStream
     k.part_lse = reinterpret_cast<float*>(w); w += round_up_sz(rows * sizeof(float), 256);
     k.part_max = reinterpret_cast<float*>(w); w += round_up_sz(rows * sizeof(float), 256);
     k.part_arg = reinterpret_cast<int32_t*>(w); w += round_up_sz(rows * sizeof(int32_t), 256);
-    k.part_sec = reinterpret_cast<float*>(w);
+    k.part_sec = reinterpret_cast<float*>(w); w += round_up_sz(rows * sizeof(float), 256);
+    k.part_top = reinterpret_cast<float*>(w);
   }
 
   // the attribute is per device and cheap to set: do it on every launch so that any current device works
@@ -1633,7 +1653,7 @@ int launch_d(const TcPassArgs& a, int splits, const TcLaunchOpt& opt, cudaStream
   if (k.splits > 1) {
     const int threads = 256, rows_per_block = threads / 32;
     tc_combine_kernel<H><<<(a.n + rows_per_block - 1) / rows_per_block, threads, 0, st>>>(
-        a.n, k.splits, k.part_o, k.part_lse, k.part_max, k.part_arg, k.part_sec, a.bias, a.out_scale, a.retrieved, a.lse, a.argmax,
+        a.n, k.splits, k.part_o, k.part_lse, k.part_max, k.part_arg, k.part_sec, k.part_top, a.bias, a.out_scale, a.retrieved, a.lse, a.argmax,
         a.rowmax, cert);
     HOP_LAUNCH_CHECK("tc_combine_kernel");
     if (cert.ctrl && a.cert_done) *a.cert_done = true;
@@ -1657,7 +1677,7 @@ int launch_h64(const TcPassArgs& a, int splits, const TcLaunchOpt& opt, cudaStre
   const int nt_total = (ppad + TP - 1) / TP;          // (rows past ppad read as zeros and are masked)
   k.tiles_per_split = (nt_total + splits - 1) / splits;
   k.splits = (nt_total + k.tiles_per_split - 1) / k.tiles_per_split;
-  k.retrieved = a.retrieved; k.qsave = a.qsave; k.lse = a.lse; k.argmax = a.argmax; k.rowmax = a.rowmax; k.rowsec = a.argmax ? a.cert.sec : nullptr;
+  k.retrieved = a.retrieved; k.qsave = a.qsave; k.lse = a.lse; k.argmax = a.argmax; k.rowmax = a.rowmax; k.rowsec = a.argmax ? a.cert.sec : nullptr; k.rowtop = a.argmax ? a.cert.top : nullptr;
   k.pattern_offset = a.pattern_offset;
   k.zero_words = opt.zero_words;
   const CertArgs cert = (a.argmax && a.lse && a.rowmax) ? a.cert : CertArgs{};
@@ -1673,7 +1693,8 @@ int launch_h64(const TcPassArgs& a, int splits, const TcLaunchOpt& opt, cudaStre
     k.part_lse = reinterpret_cast<float*>(w); w += round_up_sz(rows * sizeof(float), 256);
     k.part_max = reinterpret_cast<float*>(w); w += round_up_sz(rows * sizeof(float), 256);
     k.part_arg = reinterpret_cast<int32_t*>(w); w += round_up_sz(rows * sizeof(int32_t), 256);
-    k.part_sec = reinterpret_cast<float*>(w);
+    k.part_sec = reinterpret_cast<float*>(w); w += round_up_sz(rows * sizeof(float), 256);
+    k.part_top = reinterpret_cast<float*>(w);
   }
   auto* kern = hop_fwd_tc64_kernel<H, DV, TP, kBf16>;
   HOP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
@@ -1692,7 +1713,7 @@ int launch_h64(const TcPassArgs& a, int splits, const TcLaunchOpt& opt, cudaStre
   if (k.splits > 1) {
     const int threads = 256, rows_per_block = threads / 32;
     tc_combine_kernel<H><<<(a.n + rows_per_block - 1) / rows_per_block, threads, 0, st>>>(
-        a.n, k.splits, k.part_o, k.part_lse, k.part_max, k.part_arg, k.part_sec, a.bias, a.out_scale, a.retrieved, a.lse, a.argmax,
+        a.n, k.splits, k.part_o, k.part_lse, k.part_max, k.part_arg, k.part_sec, k.part_top, a.bias, a.out_scale, a.retrieved, a.lse, a.argmax,
         a.rowmax, cert);
     HOP_LAUNCH_CHECK("tc_combine_kernel");
     if (cert.ctrl && a.cert_done) *a.cert_done = true;
@@ -1804,7 +1825,7 @@ namespace { size_t ws_for_splits_fwd(int splits, int n, int d) { return ws_for_s
 static size_t ws_for_splits(int splits, int n, int d) {
   if (splits <= 1) return 0;
   const size_t rows = (size_t)splits * n;
-  return round_up_sz(rows * d * sizeof(float), 256) + 4 * round_up_sz(rows * sizeof(float), 256);
+  return round_up_sz(rows * d * sizeof(float), 256) + 5 * round_up_sz(rows * sizeof(float), 256);
 }
 
 // Stream-K scheduling of the T = 0 forward (HOP_TUNE_STREAMK_ON / _OFF force it): used when the plain grid would give
@@ -1835,7 +1856,7 @@ static size_t streamk_ws(int n, int d, const TcTune& t) {
   const int cl = tc_cluster(n, d, t);
   const size_t row_groups = ((size_t)(n + kTileM - 1) / kTileM + cl - 1) / cl;
   const size_t rows = (row_groups + 3 * (size_t)(num_sms() / cl)) * cl * kTileM;
-  return round_up_sz(rows * d * sizeof(float), 256) + 4 * round_up_sz(rows * sizeof(float), 256);
+  return round_up_sz(rows * d * sizeof(float), 256) + 5 * round_up_sz(rows * sizeof(float), 256);
 }
 
 // Covers every launch form launch_tc_forward can choose for (n, p, d, T): the plain grid's split partials (all

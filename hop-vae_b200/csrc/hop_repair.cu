@@ -30,13 +30,14 @@ namespace hop {
 namespace {
 
 constexpr int NT = 256;
-constexpr int kCtrlBytes = 256;       // ctrl[0] = flagged rows, ctrl[1] = CTAs done (both cleared by the forward kernel)
+constexpr int kCtrlBytes = 256;       // ctrl[0] = rows that failed the certificate, ctrl[1] = CTAs done, ctrl[2] = rows left for
+                                      // the full pass (all cleared by the forward kernel)
 constexpr int BP = 64;                // patterns per tile
 constexpr int KC = 64;                // contraction chunk
 constexpr int TS = KC + 4;            // smem stride
 
 struct RepairWs {
-  uint32_t* ctrl; int32_t* list; unsigned long long* best; size_t total;
+  uint32_t* ctrl; int32_t* list; unsigned long long* best; int32_t* list2; size_t total;
 };
 
 RepairWs carve_repair(void* ws, int n, int h) {
@@ -50,6 +51,7 @@ RepairWs carve_repair(void* ws, int n, int h) {
   w.ctrl = reinterpret_cast<uint32_t*>(take(kCtrlBytes));
   w.list = reinterpret_cast<int32_t*>(take((size_t)n * sizeof(int32_t)));
   w.best = reinterpret_cast<unsigned long long*>(take((size_t)n * sizeof(unsigned long long)));
+  w.list2 = reinterpret_cast<int32_t*>(take((size_t)n * sizeof(int32_t)));
   (void)h;
   w.total = off;
   return w;
@@ -82,7 +84,7 @@ __global__ void __launch_bounds__(NT) certify_rows_kernel(RepairArgs a, RepairWs
   const int warp = (blockIdx.x * NT + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= a.n) return;
   const long long r = warp;
-  const float gap = a.rowmax[r] - a.rowsec[r];              // lower bound on the top-1 / top-2 gap of the 16-bit scores
+  const float gap = a.rowmax[r] - fmaxf(a.rowsec[r], a.rowtop[r]);   // lower bound on the top-1 / top-2 gap of the 16-bit scores
   const float* src = (a.x_raw ? a.x_raw : a.qs) + r * a.h;
   float mean = 0.f, rstd = 1.f;
   const bool ln = a.x_raw && a.has_ln;
@@ -100,6 +102,65 @@ __global__ void __launch_bounds__(NT) certify_rows_kernel(RepairArgs a, RepairWs
     const uint32_t slot = atomicAdd(w.ctrl, 1u);
     w.list[slot] = (int32_t)r;
     w.best[slot] = 0ull;
+  }
+}
+
+// Block check.  A row fails the certificate when the BOUND on the other columns of its top tile is too loose (a diffuse
+// retrieval: the 63 neighbours of the top column sum to more than the top term), which says nothing about its true gap.
+// What the forward knows exactly is `others`, the maximum 16-bit score outside the 64-aligned pattern block B that holds the
+// 16-bit winner; with |s16 - s| <= eps = |q| max|k| 2^-10 every fp32 score outside B is <= others + eps.  So one warp
+// per flagged row re-scores just the 64 patterns of B in fp32 (64 x H FMAs): if the block's fp32 maximum b1 exceeds both
+// the block's second value and others + eps, the fp32 nearest pattern is that column -- settled.  Only rows whose true gap
+// is within the 16-bit noise go on to the full pass (list2).  On random queries against 64k patterns that is a few per
+// cent of the rows instead of all of them.
+__global__ void __launch_bounds__(NT) block_check_kernel(RepairArgs a, RepairWs w) {
+  const int count = (int)*reinterpret_cast<volatile uint32_t*>(w.ctrl);
+  const int lane = threadIdx.x & 31;
+  for (int slot = (blockIdx.x * NT + threadIdx.x) >> 5; slot < count; slot += (gridDim.x * NT) >> 5) {
+    const int row = w.list[slot];
+    const float* src = (a.x_raw ? a.x_raw : a.qs) + (size_t)row * a.h;
+    float mean = 0.f, rstd = 1.f;
+    const bool ln = a.x_raw && a.has_ln;
+    if (ln) warp_row_stats(src, a.h, a.ln_eps, mean, rstd);
+    const int p0 = (a.argmax[row] - a.pattern_offset) & ~63;
+    const int j0 = p0 + lane, j1 = p0 + lane + 32;               // this lane's two patterns of the block
+    const float* k0 = a.khat + (size_t)min(j0, a.p - 1) * a.h;
+    const float* k1 = a.khat + (size_t)min(j1, a.p - 1) * a.h;
+    float s0 = 0.f, s1 = 0.f, qn2 = 0.f;
+    for (int i = 0; i < a.h; i += 4) {
+      float q[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) q[e] = query_elem(a, src, i + e, ln, mean, rstd);
+      const float4 a0 = __ldg(reinterpret_cast<const float4*>(k0 + i)), a1 = __ldg(reinterpret_cast<const float4*>(k1 + i));
+      s0 = fmaf(q[0], a0.x, fmaf(q[1], a0.y, fmaf(q[2], a0.z, fmaf(q[3], a0.w, s0))));
+      s1 = fmaf(q[0], a1.x, fmaf(q[1], a1.y, fmaf(q[2], a1.z, fmaf(q[3], a1.w, s1))));
+      qn2 = fmaf(q[0], q[0], fmaf(q[1], q[1], fmaf(q[2], q[2], fmaf(q[3], q[3], qn2))));
+    }
+    if (j0 >= a.p) s0 = -INFINITY;
+    if (j1 >= a.p) s1 = -INFINITY;
+    // block maximum (lowest index on ties), then the maximum of everything else in the block
+    float b1 = s0 >= s1 ? s0 : s1;
+    int i1 = s0 >= s1 ? j0 : j1;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+      const float om = __shfl_xor_sync(0xffffffffu, b1, off);
+      const int oi = __shfl_xor_sync(0xffffffffu, i1, off);
+      if (om > b1 || (om == b1 && oi < i1)) { b1 = om; i1 = oi; }
+    }
+    float b2 = fmaxf(j0 == i1 ? -INFINITY : s0, j1 == i1 ? -INFINITY : s1);
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) b2 = fmaxf(b2, __shfl_xor_sync(0xffffffffu, b2, off));
+    const float eps = sqrtf(qn2) * __ldg(a.kstats) * (1.f / 1024.f) * 1.02f + 5e-6f;
+    const bool settled = b1 > b2 && b1 > a.rowsec[row] + eps;
+    if (lane == 0) {
+      if (settled) {
+        a.argmax[row] = i1 + a.pattern_offset;
+        a.rowmax[row] = b1;
+      } else {
+        const uint32_t s2 = atomicAdd(w.ctrl + 2, 1u);
+        w.list2[s2] = row;
+      }
+    }
   }
 }
 
@@ -124,7 +185,7 @@ __device__ __forceinline__ void repair_items(const RepairArgs& a, const RepairWs
     // the forward's arithmetic: nothing but the row list travels between the kernels)
     __syncthreads();
     for (int r = warp; r < BM; r += NT / 32) {
-      const int row = slot0 + r < count ? w.list[slot0 + r] : -1;
+      const int row = slot0 + r < count ? w.list2[slot0 + r] : -1;
       float mean = 0.f, rstd = 1.f;
       if (row >= 0 && ln) warp_row_stats(qsrc + (size_t)row * a.h, a.h, a.ln_eps, mean, rstd);
       if ((tid & 31) == 0) { s_row[r] = row; s_mean[r] = mean; s_rstd[r] = rstd; }
@@ -214,7 +275,7 @@ __global__ void __launch_bounds__(NT) argmax_repair_kernel(RepairArgs a, RepairW
   __shared__ float s_mean[64], s_rstd[64];
   __shared__ int s_row[64];
   __shared__ int s_last;
-  const int count = (int)*reinterpret_cast<volatile uint32_t*>(w.ctrl);
+  const int count = (int)*reinterpret_cast<volatile uint32_t*>(w.ctrl + 2);
   if (count == 0) return;
   if (count <= 16) repair_items<1>(a, w, count, Qs, Ks, s_mean, s_rstd, s_row);
   else repair_items<4>(a, w, count, Qs, Ks, s_mean, s_rstd, s_row);
@@ -230,7 +291,7 @@ __global__ void __launch_bounds__(NT) argmax_repair_kernel(RepairArgs a, RepairW
   for (int slot = threadIdx.x; slot < count; slot += NT) {
     const unsigned long long key = __ldcg(w.best + slot);
     if (key == 0ull) continue;
-    const int row = w.list[slot];
+    const int row = w.list2[slot];
     a.argmax[row] = (int32_t)(0xffffffffu - (uint32_t)(key & 0xffffffffull)) + a.pattern_offset;
     if (a.rowmax) a.rowmax[row] = from_ordered((uint32_t)(key >> 32));
   }
@@ -313,13 +374,13 @@ __global__ void __launch_bounds__(NT) delta_decide_kernel(const float* __restric
 
 size_t repair_workspace_bytes(int n, int h) { return carve_repair(nullptr, n, h).total; }
 
-CertArgs repair_cert_args(void* ws, int n, int h, const float* kstats, float* qn, float* sec) {
+CertArgs repair_cert_args(void* ws, int n, int h, const float* kstats, float* qn, float* sec, float* top) {
   const RepairWs w = carve_repair(ws, n, h);
-  return CertArgs{w.ctrl, w.list, w.best, kstats, qn, sec};
+  return CertArgs{w.ctrl, w.list, w.best, kstats, qn, sec, top};
 }
 
 int launch_argmax_repair(const RepairArgs& a, cudaStream_t st) {
-  if (!a.argmax || !a.rowmax || !a.khat || !a.kstats || (!a.precertified && !a.rowsec))
+  if (!a.argmax || !a.rowmax || !a.khat || !a.kstats || !a.rowsec || (!a.precertified && !a.rowtop))
     HOP_FAIL(HOP_ERR_BAD_ARG, "exact argmax needs argmax / rowmax outputs, the runner-up bound, the fp32 K^ and kstats");
   const size_t need = repair_workspace_bytes(a.n, a.h);
   if (!a.ws || a.ws_bytes < need) HOP_FAIL(HOP_ERR_WORKSPACE, "argmax repair needs %zu workspace bytes, %zu given", need, a.ws_bytes);
@@ -330,6 +391,8 @@ int launch_argmax_repair(const RepairArgs& a, cudaStream_t st) {
     certify_rows_kernel<<<(a.n + rows_per_block - 1) / rows_per_block, NT, 0, st>>>(a, w);
     HOP_LAUNCH_CHECK("certify_rows_kernel");
   }
+  block_check_kernel<<<2 * num_sms(), NT, 0, st>>>(a, w);
+  HOP_LAUNCH_CHECK("block_check_kernel");
   argmax_repair_kernel<<<2 * num_sms(), NT, 0, st>>>(a, w);
   HOP_LAUNCH_CHECK("argmax_repair_kernel");
   return HOP_OK;

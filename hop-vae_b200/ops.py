@@ -207,7 +207,8 @@ def _(lookup, lookup_targets, ln_stored_w, ln_stored_b, ln_proj_w, ln_proj_b, wk
 # Diagnostic of exact_argmax (tests, bench): with `count_repairs` set, every tensor-core forward is followed by a
 # (synchronising) read of how many rows failed the top-1 / top-2 certificate and were re-scored in fp32.
 count_repairs = False
-last_repair_rows = 0
+last_repair_rows = 0          # rows that took the full fp32 re-scoring pass
+last_flagged_rows = 0         # rows that failed the on-chip certificate (most are settled by the 64-pattern block check)
 
 
 def retrieve(x: Tensor, pats: List[Tensor], ln_state_w: Optional[Tensor], ln_state_b: Optional[Tensor],
@@ -269,11 +270,11 @@ def retrieve(x: Tensor, pats: List[Tensor], ln_state_w: Optional[Tensor], ln_sta
                                          cabi.ptr(retrieved), cabi.ptr(qhat), cabi.ptr(lse), cabi.ptr(argmax),
                                          cabi.ptr(rowmax), cabi.ptr(ws), need, _stream(dev)), "hop_sm100_forward")
         if count_repairs and tc and (flags & cabi.F_EXACT_ARGMAX):
-            global last_repair_rows
-            rows = C.c_int32(0)
-            cabi.check(lib.hop_sm100_repair_rows(C.byref(d), cabi.ptr(ws), _stream(dev), C.byref(rows)),
+            global last_repair_rows, last_flagged_rows
+            rows, flagged = C.c_int32(0), C.c_int32(0)
+            cabi.check(lib.hop_sm100_repair_rows(C.byref(d), cabi.ptr(ws), _stream(dev), C.byref(rows), C.byref(flagged)),
                        "hop_sm100_repair_rows")
-            last_repair_rows = int(rows.value)
+            last_repair_rows, last_flagged_rows = int(rows.value), int(flagged.value)
     if qhat is None:
         qhat = _empty_f32(dev)
     if retrieved is None:

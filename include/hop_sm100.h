@@ -288,11 +288,14 @@ int hop_sm100_bottleneck_forward_static(const hop_desc* descs, const hop_params*
                                         float* emb_recon, float* mse, void* stream);
 int hop_sm100_bottleneck_static_max_rows(void);
 
-/* Diagnostic of HOP_F_EXACT_ARGMAX: how many rows of the last forward run with
- * this descriptor (argmax != NULL) into this workspace failed the top-1 / top-2
- * certificate and were re-scored in fp32.  Waits for `stream`.  0 rows on the
- * fp32 path (whose index is exact by construction).                            */
-int hop_sm100_repair_rows(const hop_desc* desc, const void* workspace, void* stream, int32_t* rows_out);
+/* Diagnostic of HOP_F_EXACT_ARGMAX: of the last forward run with this descriptor
+ * (argmax != NULL) into this workspace, how many rows took the full fp32
+ * re-scoring pass (rows_out) and how many had failed the on-chip top-1 / top-2
+ * certificate before the 64-pattern block check settled most of them
+ * (flagged_out, NULL ok).  Waits for `stream`.  0 on the fp32 path (whose index
+ * is exact by construction).                                                   */
+int hop_sm100_repair_rows(const hop_desc* desc, const void* workspace, void* stream, int32_t* rows_out,
+                          int32_t* flagged_out);
 
 /* Pattern-sharded mode (new; the reference is single-device): combine G
  * shard-local results with the log-sum-exp monoid.

@@ -68,7 +68,8 @@ for (p, d, t) in points:
     res = {"patterns": p, "dim": d, "update_steps": t, "rows": N, "ms": ms, "latents_per_s": N / (ms * 1e-3),
            "algorithmic_tflops": fl / (ms * 1e-3) / 1e12, "frac_of_measured_peak": fl / (ms * 1e-3) / 1e12 / peak,
            "parity_rows": SUB, "rel_l2": rel, "argmax_decided_rows": int(decided.sum()),
-           "argmax_mismatch": int((got_arg[decided] != arg[decided]).sum()), "rows_rescored_fp32": ops.last_repair_rows}
+           "argmax_mismatch": int((got_arg[decided] != arg[decided]).sum()), "rows_rescored_fp32": ops.last_repair_rows,
+           "rows_failed_certificate": ops.last_flagged_rows}
     if ops.last_repair_rows > N // 100:
         # a diffuse retrieval (the iteration left the planted pattern's basin): the exact index costs an fp32 score pass
         # over the flagged rows; the tensor-core pass alone, for the split of the two

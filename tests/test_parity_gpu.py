@@ -614,7 +614,7 @@ def test_exact_nearest_pattern_on_diffuse_scores(hf, D, P, N):
             got = dut(x.cuda())
         finally:
             ops.count_repairs = False
-        flagged = ops.last_repair_rows
+        flagged, rescored = ops.last_flagged_rows, ops.last_repair_rows
         exact_idx = dut.last_argmax.clone()
         dut.exact_argmax = False
         dut(x.cuda())
@@ -623,10 +623,11 @@ def test_exact_nearest_pattern_on_diffuse_scores(hf, D, P, N):
     checked = assert_same_nearest_pattern(scores, exact_idx)
     raw_bad = int((raw_idx.cpu().long() != scores.reshape(N, P).argmax(-1)).sum())
     print(f"D={D} P={P}: {checked} rows checked, 16-bit scores alone mismatch on {raw_bad} rows, repaired: 0; "
-          f"{flagged} of {N} rows failed the certificate and were re-scored")
-    # (diffuse scores are the certificate's worst case: the 63 other columns of the top tile sum to more than the top
-    # term, so nearly every row takes the fp32 pass -- the price of an exact index there; config 5's planted queries are
-    # the case below)
+          f"{flagged} of {N} rows failed the on-chip certificate, the 64-pattern block check settled {flagged - rescored}, "
+          f"{rescored} took the full fp32 pass")
+    # diffuse scores are the certificate's worst case (the 63 neighbours of the top column sum to more than the top term),
+    # but only rows whose true gap is within the 16-bit noise may reach the full pass
+    assert rescored <= max(8, N // 4)
 
 
 @pytest.mark.parametrize("D,P,N,T", [(256, 1 << 20, 4096, 0), (256, 1 << 18, 8192, 0), (512, 1 << 18, 2048, 0),
