@@ -11,12 +11,13 @@
 // proves that EVERY other score lies more than tau below the maximum.  `certify_rows_kernel` evaluates it per row (|q_r|
 // recomputed in fp32 from the raw row, mirroring the forward's LN_q prologue; where the forward ends in a merge kernel --
 // every large problem -- that kernel evaluates the certificate itself from the norms the forward's prologue wrote, and this
-// launch is skipped); rows that fail are appended to a compact list, and `argmax_repair_kernel` rebuilds their fp32 query rows
-// from the raw input and re-scores exactly those rows against the fp32 K^ on CUDA cores
-// (64 x 64 register-tiled FFMA), merging (score, index) with a packed 64-bit atomicMax; the last CTA to finish writes
-// the corrected index / row maximum back.  With well-separated retrievals (BASELINE config 5's recipe: gap ~ 10 nats)
-// no row is flagged and the two launches cost ~4 us; with diffuse scores every row is flagged and the repair is a
-// full fp32 score pass -- the price of an exact index there.
+// launch is skipped); rows that fail are appended to a compact list.  `block_check_kernel` then settles every row whose
+// bound was merely loose by re-scoring the 64 patterns around the 16-bit winner in fp32 (see its comment); what is left --
+// rows whose true gap is within the 16-bit noise -- `argmax_repair_kernel` re-scores against all of the fp32 K^ on CUDA
+// cores (64 x 64 register-tiled FFMA, query rows rebuilt from the raw input), merging (score, index) with a packed
+// 64-bit atomicMax; the last CTA to finish writes the corrected index / row maximum back.  With well-separated
+// retrievals (BASELINE config 5's recipe: gap ~ 10 nats) no row is flagged and the launches cost ~5 us; with diffuse
+// scores every row is flagged, the block check settles all but a few per cent, and the full pass runs on those.
 //
 // (2) update_eps (upstream hflayers: `update_steps_eps`).  After update t >= 1 the iteration stops when
 // max over batch items of ||A_t - A_(t-1)||_F <= eps.  `delta_rows_kernel` recomputes both score rows in fp32 (two
