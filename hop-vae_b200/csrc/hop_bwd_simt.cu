@@ -491,10 +491,14 @@ __device__ __forceinline__ void ln_bwd_body(const LnBwdArgs& a, float* sh, int v
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const bool want_affine = a.has_ln && (a.dgamma || a.dbeta);
   constexpr int kRegCols = 8;                       // columns per lane held in registers: widths up to 256
+  const bool reg_row = a.has_ln && a.d <= 32 * kRegCols;       // the row fits the lanes' registers
   const bool reg_affine = want_affine && a.d <= 32 * kRegCols;
-  float ag[kRegCols], ab[kRegCols];
+  float ag[kRegCols], ab[kRegCols], gam[kRegCols];
 #pragma unroll
-  for (int k = 0; k < kRegCols; ++k) { ag[k] = 0.f; ab[k] = 0.f; }
+  for (int k = 0; k < kRegCols; ++k) {
+    ag[k] = 0.f; ab[k] = 0.f;
+    gam[k] = (reg_row && a.gamma && lane + 32 * k < a.d) ? __ldg(a.gamma + lane + 32 * k) : 1.f;
+  }
   if (want_affine) {
     for (int i = threadIdx.x; i < 2 * a.d; i += NT) sh[i] = 0.f;
     __syncthreads();
@@ -507,6 +511,48 @@ __device__ __forceinline__ void ln_bwd_body(const LnBwdArgs& a, float* sh, int v
       for (int i = lane; i < a.d; i += 32) {
         const float v = a.scale * gr[i];
         dxr[i] = a.accumulate ? dxr[i] + v : v;
+      }
+      continue;
+    }
+    if (reg_row) {
+      // the whole row lives in registers: x and g are read ONCE (16 independent loads per lane in flight), the statistics
+      // are warp reductions over registers in warp_row_stats' order, the column sums stay in registers across rows.
+      // (Before: five passes over x / g through L1 with dependent reductions between them -- 234 us per P x D matrix at
+      // P = 64k, D = 256, against ~35 us for the bytes.)
+      float xv[kRegCols], gv[kRegCols];
+#pragma unroll
+      for (int k = 0; k < kRegCols; ++k) {
+        const int i = lane + 32 * k;
+        xv[k] = i < a.d ? __ldg(xr + i) : 0.f;
+        gv[k] = i < a.d ? a.scale * __ldg(gr + i) : 0.f;
+      }
+      float sm = 0.f;
+#pragma unroll
+      for (int k = 0; k < kRegCols; ++k) sm += xv[k];
+      const float mean = warp_sum(sm) / (float)a.d;
+      float sv = 0.f;
+#pragma unroll
+      for (int k = 0; k < kRegCols; ++k) { const float c = xv[k] - mean; sv += (lane + 32 * k < a.d) ? c * c : 0.f; }
+      const float rstd = rsqrtf(warp_sum(sv) / (float)a.d + a.eps);
+      float c1 = 0.f, c2 = 0.f;
+#pragma unroll
+      for (int k = 0; k < kRegCols; ++k) {
+        xv[k] = (xv[k] - mean) * rstd;                          // x^
+        const float gy = gv[k] * gam[k];
+        c1 += (lane + 32 * k < a.d) ? gy : 0.f;
+        c2 += (lane + 32 * k < a.d) ? gy * xv[k] : 0.f;
+      }
+      c1 = warp_sum(c1) / (float)a.d;
+      c2 = warp_sum(c2) / (float)a.d;
+#pragma unroll
+      for (int k = 0; k < kRegCols; ++k) {
+        const int i = lane + 32 * k;
+        if (i < a.d) {
+          const float v = rstd * (gv[k] * gam[k] - c1 - xv[k] * c2);
+          dxr[i] = a.accumulate ? dxr[i] + v : v;
+          ag[k] = fmaf(gv[k], xv[k], ag[k]);
+          ab[k] += gv[k];
+        }
       }
       continue;
     }
@@ -551,7 +597,7 @@ __device__ __forceinline__ void ln_bwd_body(const LnBwdArgs& a, float* sh, int v
       }
     }
   }
-  if (reg_affine) {
+  if (reg_affine) {            // (reg_row implies the sums are in ag / ab; without affine outputs they are dropped)
 #pragma unroll
     for (int k = 0; k < kRegCols; ++k) {
       const int i = lane + 32 * k;
@@ -569,7 +615,7 @@ __device__ __forceinline__ void ln_bwd_body(const LnBwdArgs& a, float* sh, int v
 
 int ln_bwd_grid(const LnBwdArgs& a) {
   int grid = (a.rows + 7) / 8;
-  if (grid > 2 * num_sms()) grid = 2 * num_sms();
+  if (grid > 4 * num_sms()) grid = 4 * num_sms();
   return grid < 1 ? 1 : grid;
 }
 

@@ -1,12 +1,12 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 1500 python -m pytest tests/test_parity_gpu.py tests/test_zz_no_alloc.py -m gpu -x -q -s > gpurun_out/r02m_tests.txt 2>&1; echo "pytest rc=$?"
-grep -E "passed|failed|block check|rows re-scored|Error" gpurun_out/r02m_tests.txt | tail -16
-timeout 1500 python scripts/sweep_config5.py "--points=65536,256,0;65536,64,1;65536,128,3;262144,256,3;1048576,256,3;65536,256,3" > gpurun_out/r02m_sweep.jsonl 2> gpurun_out/r02m_sweep.err; echo "rc=$?"
-python - <<'PY'
+timeout 900 python -m pytest tests/test_backward_tc_gpu.py tests/test_parity_gpu.py -m gpu -x -q -k "backward or train or grad" > gpurun_out/r02n_tests.txt 2>&1; echo "pytest rc=$?"; tail -2 gpurun_out/r02n_tests.txt
+timeout 300 python __graft_entry__.py smoke 2>&1 | tail -3
+timeout 600 python scripts/bench_backward.py > gpurun_out/r02n_backward.jsonl 2>/dev/null; python -c "
 import json
-for l in open("gpurun_out/r02m_sweep.jsonl"):
-    d=json.loads(l); print(d["patterns"],d["dim"],d["update_steps"],"ms %.3f frac %.3f rel %.2e mism %d/%d flagged %d rescored %d"%(d["ms"],d["frac_of_measured_peak"],d["rel_l2"],d["argmax_mismatch"],d["argmax_decided_rows"],d["rows_failed_certificate"],d["rows_rescored_fp32"]), d.get("ms_without_exact_index"))
-PY
-tail -3 gpurun_out/r02m_sweep.err
-timeout 300 python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-sustained --no-backward 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('bench value %.2fM frac %.3f kernel_ms %.4f'%(d['value']/1e6,d['roofline']['frac'],d['roofline']['kernel_ms']))"
+for l in open('gpurun_out/r02n_backward.jsonl'):
+    b=json.loads(l); print(b['rows'],b['patterns'],b['dim'],'fwd+prep %.2f bwd %.2f frac %.3f'%(b['ms_forward_incl_prep'],b['ms_backward'],b['bwd_frac_of_measured_peak']))"
+BWD="python scripts/bench_backward.py --points=16384,65536,256"
+timeout 300 $BWD > gpurun_out/r02n_bwd_plain.log 2>&1 &&
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/r02n_bwd_launches.csv $BWD > gpurun_out/r02n_bwd_launches_ncu.log 2>&1
+echo "ncu rc=$?"
