@@ -52,13 +52,19 @@ def main():
     ap.add_argument("--config", default="ffhq64", choices=["mnist28", "ffhq32", "ffhq64"])
     ap.add_argument("--epochs", type=int, default=2)
     ap.add_argument("--steps-per-epoch", type=int, default=10)
-    ap.add_argument("--batch", type=int, default=32)
+    ap.add_argument("--batch", type=int, default=32, help="images per GPU (weak scaling)")
+    ap.add_argument("--global-batch", type=int, default=0,
+                    help="strong scaling (SURVEY.md 8d config 3: global B = 256 split over the ranks); overrides --batch")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "train_ddp"))
     ap.add_argument("--resume", default=None, help="checkpoint written by this driver (or a bare reference state_dict)")
     ap.add_argument("--reference-format", action="store_true", help="also write the bare state_dict main.py:124 writes")
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
+    if args.global_batch:
+        if args.global_batch % world:
+            raise SystemExit(f"--global-batch {args.global_batch} is not divisible by {world} ranks")
+        args.batch = args.global_batch // world
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
@@ -150,6 +156,7 @@ def main():
         rows = {"mnist28": 64, "ffhq32": 81, "ffhq64": 289}[args.config]
         ms = ms_steps[-1]                               # the last epoch: steady state (the first one carries the warm-up)
         print(json.dumps({"config": args.config, "n_gpus": world, "batch_per_gpu": args.batch,
+                          "scaling": "strong" if args.global_batch else "weak", "global_batch": world * args.batch,
                           "epochs": [start_epoch, start_epoch + args.epochs], "steps_per_epoch": args.steps_per_epoch,
                           "ms_per_step": ms, "images_per_s": world * args.batch / (ms * 1e-3),
                           "latents_per_s": world * args.batch * rows * 3 / (ms * 1e-3), "loss_per_epoch": losses,
