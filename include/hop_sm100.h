@@ -61,7 +61,7 @@ enum {
   HOP_F_OUT_PROJ     = 1u << 6,  /* out_proj present       (disable_out_projection=False)  */
   /* behaviour switches of this library (no upstream counterpart) */
   HOP_F_EXACT_ARGMAX = 1u << 7,  /* tensor-core paths: rows whose nearest pattern the 16-bit score arithmetic cannot
-                                    decide (log-sum-exp certificate, see hop_sm100_forward) are re-scored in fp32 */
+                                    decide (on-chip top-1 / top-2 bound, see hop_sm100_forward) are re-scored in fp32 */
   HOP_F_TRAIN        = 1u << 8   /* prepare_patterns also writes the packs only the tensor-core backward reads
                                     (kt16, v16) */
 };

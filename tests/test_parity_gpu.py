@@ -573,7 +573,7 @@ def assert_same_nearest_pattern(scores, got_idx, t_updates=0):
 @pytest.mark.parametrize("name", list(TC_CASES))
 def test_forward_parity_tensor_core(hf, name, splits):
     """tcgen05 fp16-operand / fp32-accumulate path against the fp32 oracle: rel-L2 <= 1e-3 (north-star bar),
-    nearest-pattern index identical on every row (log-sum-exp certificate + fp32 repair, hop_repair.cu)."""
+    nearest-pattern index identical on every row (on-chip runner-up bound, fp32 block check, fp32 repair of what is left: hop_repair.cu)."""
     D, P, N, T = TC_CASES[name]
     if splits and T == 1 and D <= 256:
         pytest.skip("on-chip retrieve updates never split the pattern axis")
