@@ -1,9 +1,16 @@
 #!/bin/bash
-# round 2, 2-GPU pass on the final tree: sharded tests, bench at N = 2 (sharded sub-record), other-width sweep points
+# round 2, last 2-GPU pass: whole -m gpu suite + smoke on the final tree, config 3 weak / strong at 1 and 2 GPUs
 mkdir -p gpurun_out
-timeout 1500 python -m pytest tests/test_sharded_gpu.py -m gpu -q -rs > gpurun_out/r02_g2_sharded_tests.txt 2>&1
-echo "pytest rc=$?" >> gpurun_out/r02_g2_sharded_tests.txt; tail -4 gpurun_out/r02_g2_sharded_tests.txt
+timeout 2400 python -m pytest tests -m gpu -x -q -rs > gpurun_out/r02_last_tests.txt 2>&1; echo "suite rc=$?"; tail -3 gpurun_out/r02_last_tests.txt
+timeout 400 python __graft_entry__.py smoke > gpurun_out/r02_last_smoke.txt 2>&1; echo "smoke rc=$?"; tail -6 gpurun_out/r02_last_smoke.txt
+: > gpurun_out/r02_train_ddp_g12.jsonl
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511"
-timeout 1200 $TR bench.py --gpus 2 --steps 10 --warmup 3 --no-backward > gpurun_out/r02_g2_bench.json 2> gpurun_out/r02_g2_bench.err; echo "bench2 rc=$?"
-tail -c 300 gpurun_out/r02_g2_bench.err
-timeout 1500 python scripts/sweep_config5.py "--points=65536,1024,0;262144,1024,0;65536,1024,1;65536,128,0;262144,128,0;65536,64,0;65536,128,3;65536,64,1" > gpurun_out/r02z_sweep_other_widths.jsonl 2> gpurun_out/r02z_sweep_other.err; echo "sweep rc=$?"
+for mode in "--global-batch 256" "--batch 32"; do
+  timeout 400 $TR scripts/train_ddp.py --config ffhq64 $mode --epochs 2 --steps-per-epoch 20 --out gpurun_out/t2 2>/dev/null | grep '"config"' >> gpurun_out/r02_train_ddp_g12.jsonl
+  timeout 400 python scripts/train_ddp.py --config ffhq64 $mode --epochs 2 --steps-per-epoch 20 --out gpurun_out/t1 2>/dev/null | grep '"config"' >> gpurun_out/r02_train_ddp_g12.jsonl
+done
+rm -rf gpurun_out/t1 gpurun_out/t2
+python -c "
+import json
+for l in open('gpurun_out/r02_train_ddp_g12.jsonl'):
+    d=json.loads(l); print(d['scaling'], d['n_gpus'], d['batch_per_gpu'], 'ms %.2f img/s %.0f'%(d['ms_per_step'], d['images_per_s']))"

