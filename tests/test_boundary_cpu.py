@@ -331,3 +331,18 @@ def test_host_pipeline_pieces_cover_the_rows(impl):
     assert bounds_of(0, 4) == []
     with pytest.raises(ValueError):
         bounds_of(1000, (0, 0))
+
+
+def test_bottleneck_entry_points_report_their_limits_without_a_gpu():
+    """Host-only queries of the one-launch bottleneck (include/hop_sm100.h): workspace size and the row limit of the
+    allocation-free variant, whose scratch is a fixed device array inside the library."""
+    import ctypes as C
+    import hflayers
+    lib = hflayers._impl.cabi.load()
+    assert lib.hop_sm100_bottleneck_static_max_rows() == 262144
+    need = C.c_size_t(0)
+    assert lib.hop_sm100_bottleneck_workspace_bytes(9248, C.byref(need)) == 0
+    assert need.value == 256 + ((9248 + 15) // 16 * 4 + 255) // 256 * 256
+    # the static array is sized by the same formula at the row limit: 65,792 bytes
+    assert lib.hop_sm100_bottleneck_workspace_bytes(262144, C.byref(need)) == 0 and need.value == 65792
+    assert lib.hop_sm100_bottleneck_workspace_bytes(0, C.byref(need)) == 1          # HOP_ERR_BAD_ARG
